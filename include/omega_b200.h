@@ -1,0 +1,257 @@
+/* omega_b200.h -- C ABI of the B200-native Omega hot path.
+ *
+ * Drop-in boundary for the per-step path of E3SM Omega (components/omega):
+ * every entry point below is what the body of one reference C++ method
+ * forwards to.  The reference has no FFI seam (it is plain C++ classes over
+ * Kokkos Views), so the seam is "same class, same method, body calls C";
+ * INTEGRATION.md shows the binding for each method.  File:line references
+ * are relative to components/omega/ of the reference.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no C++/torch types; every function
+ *    returns 0 on success, non-zero on error (omega_last_error() has text);
+ *    nothing throws, nothing synchronises unless the name says so;
+ *  - "host order"   = Omega's local element order (Decomp.cpp local
+ *    numbering: owned, then halo layers; row N*All is the boundary slot,
+ *    arrays are N*Size = N*All+1 rows, src/base/Decomp.cpp:1081-1082);
+ *  - "device order" = the library's space-filling-curve order of the same
+ *    rows (owned block and halo block sorted separately, boundary slot
+ *    last); omega_mesh_perm() returns the bit-exact maps;
+ *  - fields are fp64, layout [element][level] (LayoutRight,
+ *    src/base/DataTypes.h:58-61), tracers [tracer][cell][level];
+ *  - device pointers handed to compute entry points are in DEVICE order and
+ *    must have been allocated with row count N*Size.
+ */
+#ifndef OMEGA_B200_H
+#define OMEGA_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* src/base/Halo.h:45 */
+typedef enum { OMEGA_ON_CELL = 0, OMEGA_ON_EDGE = 1, OMEGA_ON_VERTEX = 2 } OmegaMeshElement;
+
+/* Host-side description of one rank's local mesh: the public members of
+ * HorzMesh the hot path reads (src/ocn/HorzMesh.h:100-265), host order,
+ * 0-based local indices, boundary slot = N*All. */
+typedef struct OmegaMeshDesc {
+   int NCellsOwned, NCellsAll, NCellsSize;
+   int NEdgesOwned, NEdgesAll, NEdgesSize;
+   int NVerticesOwned, NVerticesAll, NVerticesSize;
+   int MaxEdges, MaxEdges2, VertexDegree;
+   int NVertLayers;
+   const int *NEdgesOnCell;   /* [NCellsSize] */
+   const int *EdgesOnCell;    /* [NCellsSize][MaxEdges] */
+   const int *CellsOnEdge;    /* [NEdgesSize][2] */
+   const int *VerticesOnEdge; /* [NEdgesSize][2] */
+   const int *NEdgesOnEdge;   /* [NEdgesSize] */
+   const int *EdgesOnEdge;    /* [NEdgesSize][MaxEdges2] */
+   const int *CellsOnVertex;  /* [NVerticesSize][VertexDegree] */
+   const int *EdgesOnVertex;  /* [NVerticesSize][VertexDegree] */
+   const double *AreaCell, *BottomDepth, *XCell, *YCell, *ZCell;  /* [NCellsSize] */
+   const double *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge; /* [NEdgesSize] */
+   const double *WeightsOnEdge;     /* [NEdgesSize][MaxEdges2] */
+   const double *AreaTriangle, *FVertex; /* [NVerticesSize] */
+   const double *KiteAreasOnVertex; /* [NVerticesSize][VertexDegree] */
+} OmegaMeshDesc;
+
+/* Tendencies: + Advection: + WindStress: config groups
+ * (configs/Default.yml:25-52, src/ocn/Tendencies.cpp:123-213,
+ * src/ocn/AuxiliaryState.cpp:267-310) and the manufactured-solution custom
+ * tendencies (src/ocn/CustomTendencyTerms.cpp:18-102). */
+typedef struct OmegaTendConfig {
+   int ThicknessFluxTendencyEnable, PVTendencyEnable, KETendencyEnable,
+       SSHTendencyEnable, VelDiffTendencyEnable, VelHyperDiffTendencyEnable,
+       WindForcingTendencyEnable, BottomDragTendencyEnable,
+       TracerHorzAdvTendencyEnable, TracerDiffTendencyEnable,
+       TracerHyperDiffTendencyEnable;
+   int FluxThicknessType;   /* 0 Center, 1 Upwind */
+   int FluxTracerType;      /* 0 Center, 1 Upwind */
+   int WindStressInterpType; /* 0 Isotropic, 1 Anisotropic */
+   int ManufacturedSolutionTendency; /* adds the two custom terms */
+   double ViscDel2, ViscDel4, DivFactor, Density0, BottomDragCoeff,
+       EddyDiff2, EddyDiff4;
+   /* ManufacturedSolution: group (configs/Default.yml:143-146) */
+   double ManufacturedWavelengthX, ManufacturedWavelengthY, ManufacturedAmplitude;
+} OmegaTendConfig;
+
+/* Public array members of AuxiliaryState's six aux-var groups
+ * (src/ocn/auxiliaryVars/*.h).  Device order for the GPU library, host
+ * order for the oracle.  Cell/edge/vertex arrays are [N*Size][NVertLayers];
+ * HTracersEdge [NTracers][NEdgesSize][K]; Del2TracersCell
+ * [NTracers][NCellsSize][K]; the three wind arrays are 1-D. */
+typedef struct OmegaAuxArrays {
+   double *KineticEnergyCell, *VelocityDivCell;
+   double *FluxLayerThickEdge, *MeanLayerThickEdge, *SshCell;
+   double *RelVortVertex, *NormRelVortVertex, *NormPlanetVortVertex;
+   double *NormRelVortEdge, *NormPlanetVortEdge;
+   double *Del2Edge, *Del2DivCell, *Del2RelVortVertex;
+   double *HTracersEdge, *Del2TracersCell;
+   double *NormalStressEdge, *ZonalStressCell, *MeridStressCell;
+} OmegaAuxArrays;
+
+/* Tendencies::LayerThicknessTend / NormalVelocityTend / TracerTend
+ * (src/ocn/Tendencies.h:55-57). */
+typedef struct OmegaTendArrays {
+   double *LayerThicknessTend; /* [NCellsSize][K] */
+   double *NormalVelocityTend; /* [NEdgesSize][K] */
+   double *TracerTend;         /* [NTracers][NCellsSize][K] */
+} OmegaTendArrays;
+
+/* OceanState + Tracers time-level rings (src/ocn/OceanState.cpp:65-117,
+ * 348-365,394-407; src/ocn/Tracers.cpp:269-277,457-496). */
+typedef struct OmegaStateArrays {
+   int NTimeLevels;      /* 2 for every stepper in the reference */
+   int CurTimeIndex;     /* OceanState::CurTimeIndex */
+   int TracerCurTimeIndex; /* Tracers::CurTimeIndex */
+   int NTracers;
+   double *LayerThickness[2]; /* [NCellsSize][K] per ring slot */
+   double *NormalVelocity[2]; /* [NEdgesSize][K] */
+   double *Tracers[2];        /* [NTracers][NCellsSize][K] */
+} OmegaStateArrays;
+
+/* Stage coefficients already multiplied by the time step and evaluated the
+ * way TimeInterval::get does (src/infra/TimeMgr.cpp:382-391), in seconds;
+ * StageTime = elapsed seconds (since the manufactured-solution reference
+ * time) at which stage s evaluates its tendencies. */
+typedef struct OmegaStepCoeffs {
+   int NStages;
+   double A[4], B[4];
+   double StageTime[4];
+   double Dt;
+} OmegaStepCoeffs;
+
+typedef enum { OMEGA_STEPPER_RK4 = 0, OMEGA_STEPPER_RK2 = 1, OMEGA_STEPPER_FB = 2 } OmegaStepperType;
+
+typedef struct OmegaMesh OmegaMesh;       /* device-resident HorzMesh */
+typedef struct OmegaStepper OmegaStepper; /* Tendencies + AuxiliaryState + TimeStepper workspace */
+typedef struct OmegaHalo OmegaHalo;       /* Halo exchange lists on device */
+
+const char *omega_last_error(void);
+int omega_b200_abi_version(void);
+
+/* ---- device memory (replaces Kokkos View allocation, zero-initialised) -- */
+int omega_dev_alloc(void **ptr, unsigned long long bytes);
+int omega_dev_free(void *ptr);
+int omega_dev_sync(void *stream);
+
+/* ---- HorzMesh (src/ocn/HorzMesh.cpp:49-150,527-647) ---------------------- */
+/* Builds the SFC permutation (Reorder=1) or keeps host order (Reorder=0),
+ * derives EdgeSignOnCell/EdgeSignOnVertex/EdgeMask/MeshScalingDel2,4 and
+ * stages everything to the current device as structure-of-arrays. */
+int omega_mesh_create(const OmegaMeshDesc *Desc, int Reorder, OmegaMesh **Mesh);
+int omega_mesh_destroy(OmegaMesh *Mesh);
+/* Perm[new] = old (host-order row of device row `new`), IPerm[old] = new;
+ * both length N*Size for the element kind. */
+int omega_mesh_perm(const OmegaMesh *Mesh, OmegaMeshElement Elem, int *Perm, int *IPerm);
+/* Derived host-order arrays, for parity with HorzMesh::computeEdgeSign /
+ * setMasks: EdgeSignOnCell [NCellsSize][MaxEdges], EdgeSignOnVertex
+ * [NVerticesSize][VertexDegree], EdgeMask [NEdgesSize] (level-independent). */
+int omega_mesh_derived(const OmegaMesh *Mesh, double *EdgeSignOnCell,
+                       double *EdgeSignOnVertex, double *EdgeMask);
+
+/* ---- host <-> device field transfer with the permutation applied -------
+ * Host array [NOuter][N*Size][NInner] in host order <-> device array of the
+ * same shape in device order (OceanState::copyToDevice/copyToHost,
+ * src/ocn/OceanState.cpp:300-328). Host may be pageable or pinned. */
+int omega_field_to_device(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
+                          int NInner, const double *Host, double *Dev, void *Stream);
+int omega_field_to_host(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
+                        int NInner, const double *Dev, double *Host, void *Stream);
+
+/* ---- Tendencies + AuxiliaryState + TimeStepper -------------------------- */
+int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int NTracers,
+                         OmegaStepper **Stepper);
+int omega_stepper_destroy(OmegaStepper *Stepper);
+int omega_stepper_set_config(OmegaStepper *Stepper, const OmegaTendConfig *Cfg);
+/* The library owns the aux / tendency arrays (as AuxiliaryState and
+ * Tendencies do); these return the device pointers so host Views can alias
+ * them (src/ocn/Tendencies.h:55-57, src/ocn/AuxiliaryState.h:37-42). */
+int omega_stepper_aux_arrays(OmegaStepper *Stepper, OmegaAuxArrays *Aux);
+int omega_stepper_tend_arrays(OmegaStepper *Stepper, OmegaTendArrays *Tend);
+/* wind stress input on cells, host order (WindForcingAuxVars.h:14-17) */
+int omega_stepper_set_wind_stress(OmegaStepper *Stepper, const double *ZonalStressCellHost,
+                                  const double *MeridStressCellHost, void *Stream);
+
+/* AuxiliaryState::computeMomAux / computeAll (src/ocn/AuxiliaryState.cpp:60-185) */
+int omega_aux_compute_mom(OmegaStepper *S, const double *LayerThickCell,
+                          const double *NormalVelEdge, void *Stream);
+int omega_aux_compute_all(OmegaStepper *S, const double *LayerThickCell,
+                          const double *NormalVelEdge, const double *TracerArray,
+                          void *Stream);
+/* Tendencies::compute*TendenciesOnly (src/ocn/Tendencies.cpp:257-486);
+ * NormalVelEdgeRaw is State->NormalVelocity[VelTimeLevel] indexed RAW as the
+ * reference does for bottom drag / tracer advection (:322,:445). */
+int omega_tend_thickness_only(OmegaStepper *S, const double *NormalVelEdge, double Time,
+                              void *Stream);
+int omega_tend_velocity_only(OmegaStepper *S, const double *NormalVelEdge,
+                             const double *NormalVelEdgeRaw, double Time, void *Stream);
+int omega_tend_tracer_only(OmegaStepper *S, const double *NormalVelEdgeRaw,
+                           const double *TracerArray, void *Stream);
+/* Tendencies::computeThickness/Velocity/Tracer/AllTendencies (:488-600) */
+int omega_tend_thickness(OmegaStepper *S, const double *LayerThickCell,
+                         const double *NormalVelEdge, double Time, void *Stream);
+int omega_tend_velocity(OmegaStepper *S, const double *LayerThickCell,
+                        const double *NormalVelEdge, const double *NormalVelEdgeRaw,
+                        double Time, void *Stream);
+int omega_tend_tracer(OmegaStepper *S, const double *LayerThickCellRaw,
+                      const double *NormalVelEdgeRaw, const double *TracerArray,
+                      void *Stream);
+int omega_tend_all(OmegaStepper *S, const double *LayerThickCell,
+                   const double *NormalVelEdge, const double *NormalVelEdgeRaw,
+                   const double *TracerArray, double Time, void *Stream);
+
+/* TimeStepper::doStep (src/timeStepping/RungeKutta4Stepper.cpp:68-137,
+ * RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:27-82).
+ * Advances State by one step and rotates both time-level rings.  Fused=1
+ * runs the fused per-stage pipeline (no aux/tendency arrays materialised),
+ * Fused=0 the kernel-per-term path that fills every public array.
+ * RawTimeLevelCompat=1 reproduces the reference's raw time-level indexing
+ * (SURVEY.md 3.5 P1); 0 maps every level through the ring.
+ * Halo may be NULL on a single rank. */
+int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,
+                          const OmegaStepCoeffs *Coeffs, OmegaHalo *Halo, int Fused,
+                          int RawTimeLevelCompat, void *Stream);
+/* The same step cut at its halo-exchange points, for callers that run the
+ * exchange themselves (NCCL in another library, an emulated multi-rank
+ * test): Phase p runs everything up to (not including) exchange point p. */
+int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,
+                             const OmegaStepCoeffs *Coeffs, int Phase, int Fused,
+                             int RawTimeLevelCompat, void *Stream);
+/* Arrays to exchange after Phase p (device pointers, element kind, NOuter). */
+int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type,
+                                const OmegaStateArrays *State, int Phase, double **Ptrs,
+                                int *Elems, int *NOuter, int *NArrays);
+/* kernels launched by this stepper since creation (bench gpu_launches) */
+long long omega_stepper_launch_count(const OmegaStepper *S);
+
+/* ---- Halo (src/base/Halo.h:62-917, src/base/Halo.cpp:455-757) ----------- */
+/* Exchange lists for one rank, host order: for each neighbour n and element
+ * kind e, SendIdx/RecvIdx are the concatenation over halo layers
+ * (Halo.cpp:543-597). Offsets are CSR-style [NNeighbors+1] per kind. */
+typedef struct OmegaHaloDesc {
+   int MyTask, NNeighbors;
+   const int *NeighborTasks;            /* [NNeighbors] ascending */
+   const int *SendOffsets[3], *SendIdx[3];
+   const int *RecvOffsets[3], *RecvIdx[3];
+} OmegaHaloDesc;
+int omega_halo_create(const OmegaMesh *Mesh, const OmegaHaloDesc *Desc, OmegaHalo **Halo);
+int omega_halo_destroy(OmegaHalo *Halo);
+/* Halo::exchangeFullArrayHalo split into its two device halves so the
+ * transport (NCCL send/recv, peer copies, or an in-process loop) stays with
+ * the caller: pack gathers [NOuter][elem][NInner] rows of every neighbour's
+ * send list into one contiguous buffer per neighbour (Halo.h:304-502 buffer
+ * order); unpack scatters a received buffer into the halo rows
+ * (Halo.h:545-760). Counts are in doubles. */
+int omega_halo_buffer_counts(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter,
+                             int NInner, long long *SendCounts, long long *RecvCounts);
+int omega_halo_pack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
+                    const double *Array, double *SendBuf, void *Stream);
+int omega_halo_unpack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
+                      const double *RecvBuf, double *Array, void *Stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OMEGA_B200_H */
