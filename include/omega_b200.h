@@ -223,6 +223,11 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
 int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type,
                                 const OmegaStateArrays *State, int Phase, double **Ptrs,
                                 int *Elems, int *NOuter, int *NArrays);
+/* OceanState::updateTimeLevels + Tracers::updateTimeLevels minus the exchange:
+ * advance both ring indices (src/ocn/OceanState.cpp:348-365). */
+int omega_state_rotate(OmegaStateArrays *State);
+/* ProvisState / ProvisTracers of the RK4 stepper (RungeKutta4Stepper.cpp:43-64) */
+int omega_stepper_provis_arrays(OmegaStepper *Stepper, double **H, double **U, double **Tr);
 /* kernels launched by this stepper since creation (bench gpu_launches) */
 long long omega_stepper_launch_count(const OmegaStepper *S);
 

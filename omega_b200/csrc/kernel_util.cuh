@@ -1,0 +1,62 @@
+// kernel_util.cuh -- thread mapping and vector load/store shared by all kernels.
+//
+// Fields are [element][level] with level innermost.  One thread owns V
+// consecutive levels (V=2 -> one 16-byte double2 access) of one element; the
+// work index runs level-fastest so a warp covers 32*V consecutive levels of
+// as few elements as possible: with 64 levels a warp is exactly one 512-byte
+// element row, every neighbour gather is one fully coalesced row read and the
+// element's connectivity/geometry loads are warp-uniform broadcasts.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace omega {
+
+constexpr int kBlock = 256;
+
+template <int V> __device__ __forceinline__ void ldv(double (&r)[V], const double *__restrict__ p);
+template <> __device__ __forceinline__ void ldv<1>(double (&r)[1], const double *__restrict__ p) {
+   r[0] = __ldg(p);
+}
+template <> __device__ __forceinline__ void ldv<2>(double (&r)[2], const double *__restrict__ p) {
+   const double2 t = __ldg(reinterpret_cast<const double2 *>(p));
+   r[0] = t.x;
+   r[1] = t.y;
+}
+// plain (coherent) load for read-modify-write targets
+template <int V> __device__ __forceinline__ void ldp(double (&r)[V], const double *p);
+template <> __device__ __forceinline__ void ldp<1>(double (&r)[1], const double *p) { r[0] = *p; }
+template <> __device__ __forceinline__ void ldp<2>(double (&r)[2], const double *p) {
+   const double2 t = *reinterpret_cast<const double2 *>(p);
+   r[0] = t.x;
+   r[1] = t.y;
+}
+template <int V> __device__ __forceinline__ void stv(double *p, const double (&r)[V]);
+template <> __device__ __forceinline__ void stv<1>(double *p, const double (&r)[1]) { *p = r[0]; }
+template <> __device__ __forceinline__ void stv<2>(double *p, const double (&r)[2]) {
+   *reinterpret_cast<double2 *>(p) = make_double2(r[0], r[1]);
+}
+
+// work index -> (element i, first level k); returns false past the end
+template <int V> __device__ __forceinline__ bool elem_k(int N, int K, int &i, int &k) {
+   const int KV      = K / V;
+   const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+   if (w >= (long long)N * KV) return false;
+   i = (int)(w / KV);
+   k = ((int)(w - (long long)i * KV)) * V;
+   return true;
+}
+
+inline unsigned grid_for(long long NWork) { return (unsigned)((NWork + kBlock - 1) / kBlock); }
+
+// dispatch on vector width: V=2 when K is even, else 1
+#define OMEGA_LAUNCH_V(KERNEL, N, K, STREAM, ...)                                              \
+   do {                                                                                        \
+      if ((N) > 0) {                                                                           \
+         if (((K) & 1) == 0)                                                                   \
+            KERNEL<2><<<::omega::grid_for((long long)(N) * ((K) / 2)), ::omega::kBlock, 0, STREAM>>>(__VA_ARGS__); \
+         else                                                                                  \
+            KERNEL<1><<<::omega::grid_for((long long)(N) * (K)), ::omega::kBlock, 0, STREAM>>>(__VA_ARGS__);       \
+      }                                                                                        \
+   } while (0)
+
+} // namespace omega

@@ -1,0 +1,107 @@
+// kernels_update.cu -- the stage-update kernels of TimeStepper
+// (components/omega/src/timeStepping/TimeStepper.cpp:378-524) and the row
+// permutation used by field transfers and the halo pack/unpack.
+#include "kernel_util.cuh"
+#include "omega_dev.h"
+
+namespace omega {
+
+// updateThicknessByTend / updateVelocityByTend (:378-430): Y1 = Y2 + c*T
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_axpy(int N, int K, double *Y1, const double *Y2, double C, const double *__restrict__ T) {
+   int i, k;
+   if (!elem_k<V>(N, K, i, k)) return;
+   const size_t o = (size_t)i * K + k;
+   double y[V], t[V];
+   ldp<V>(y, Y2 + o);
+   ldv<V>(t, T + o);
+#pragma unroll
+   for (int q = 0; q < V; ++q) y[q] = y[q] + C * t[q];
+   stv<V>(Y1 + o, y);
+}
+
+// Mode 0 updateTracersByTend (:446-469)  Next = (Cur*H2 + c*T)/H1
+// Mode 1 weightTracers (:473-487)        Next = Cur*H1
+// Mode 2 accumulateTracersUpdate (:492-507) Next += c*T
+// Mode 3 finalizeTracersUpdate (:511-524)   Next /= H1
+template <int V, int Mode>
+__global__ void __launch_bounds__(kBlock)
+k_tracer_update(int NAll, int NSize, int K, int NTracers, double *Next, const double *Cur,
+                const double *H1, const double *H2, double C, const double *__restrict__ T) {
+   int i, k;
+   if (!elem_k<V>(NAll, K, i, k)) return;
+   const size_t o = (size_t)i * K + k, CS = (size_t)NSize * K;
+   double h1[V], h2[V];
+   if (Mode != 2) ldp<V>(h1, H1 + o);
+   if (Mode == 0) ldp<V>(h2, H2 + o);
+   for (int l = 0; l < NTracers; ++l) {
+      double r[V], a[V], t[V];
+      if (Mode == 0 || Mode == 1) ldp<V>(a, Cur + l * CS + o);
+      if (Mode == 2 || Mode == 3) ldp<V>(a, Next + l * CS + o);
+      if (Mode == 0 || Mode == 2) ldv<V>(t, T + l * CS + o);
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         if (Mode == 0) r[q] = (a[q] * h2[q] + C * t[q]) / h1[q];
+         if (Mode == 1) r[q] = a[q] * h1[q];
+         if (Mode == 2) r[q] = a[q] + C * t[q];
+         if (Mode == 3) r[q] = a[q] / h1[q];
+      }
+      stv<V>(Next + l * CS + o, r);
+   }
+}
+
+// Dst[o][r][:] = Src[o][SrcRowOfDst[r]][:]
+__global__ void __launch_bounds__(kBlock)
+k_permute_rows(int NOuter, int NRows, int NInner, const int *__restrict__ SrcRowOfDst,
+               const double *__restrict__ Src, double *__restrict__ Dst) {
+   const long long w     = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+   const long long total = (long long)NOuter * NRows * NInner;
+   if (w >= total) return;
+   const int k       = (int)(w % NInner);
+   const long long t = w / NInner;
+   const int r       = (int)(t % NRows);
+   const int o       = (int)(t / NRows);
+   Dst[w] = Src[((size_t)o * NRows + SrcRowOfDst[r]) * NInner + k];
+}
+
+void launch_axpy(const Launch &L, int NAll, int K, double *Y1, const double *Y2, double C, const double *T) {
+   OMEGA_LAUNCH_V(k_axpy, NAll, K, L.Stream, NAll, K, Y1, Y2, C, T);
+   ++*L.Count;
+}
+
+#define OMEGA_LAUNCH_TR(MODE, ...)                                                                \
+   do {                                                                                           \
+      if (NAll > 0 && NTracers > 0) {                                                             \
+         if ((K & 1) == 0)                                                                        \
+            k_tracer_update<2, MODE><<<grid_for((long long)NAll * (K / 2)), kBlock, 0, L.Stream>>>(__VA_ARGS__); \
+         else                                                                                     \
+            k_tracer_update<1, MODE><<<grid_for((long long)NAll * K), kBlock, 0, L.Stream>>>(__VA_ARGS__);       \
+         ++*L.Count;                                                                              \
+      }                                                                                           \
+   } while (0)
+
+void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                           const double *Cur, const double *H1, const double *H2, double C, const double *T) {
+   OMEGA_LAUNCH_TR(0, NAll, NSize, K, NTracers, Next, Cur, H1, H2, C, T);
+}
+void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                           const double *Cur, const double *H) {
+   OMEGA_LAUNCH_TR(1, NAll, NSize, K, NTracers, Next, Cur, H, nullptr, 0.0, nullptr);
+}
+void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Accum,
+                               double C, const double *T) {
+   OMEGA_LAUNCH_TR(2, NAll, NSize, K, NTracers, Accum, nullptr, nullptr, nullptr, C, T);
+}
+void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                             const double *H) {
+   OMEGA_LAUNCH_TR(3, NAll, NSize, K, NTracers, Next, nullptr, H, nullptr, 0.0, nullptr);
+}
+
+void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
+                         const double *Src, double *Dst) {
+   const long long total = (long long)NOuter * NRows * NInner;
+   if (total > 0) k_permute_rows<<<grid_for(total), kBlock, 0, S>>>(NOuter, NRows, NInner, SrcRowOfDst, Src, Dst);
+}
+
+} // namespace omega

@@ -1,0 +1,316 @@
+// mesh.cu -- device-resident HorzMesh: space-filling-curve reordering with
+// explicit permutation maps, derived fields, structure-of-arrays staging, and
+// permuting host<->device field transfers.
+// Reference behaviour restated: components/omega/src/ocn/HorzMesh.cpp:527-647
+// (computeEdgeSign, setMasks, setMeshScaling, copyToDevice).
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <numeric>
+
+#include "omega_dev.h"
+
+namespace omega {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string &msg) { g_last_error = msg; }
+
+// 3-D Morton key, 21 bits per axis
+static inline uint64_t spread3(uint64_t x) {
+   x &= 0x1fffff;
+   x = (x | x << 32) & 0x1f00000000ffffULL;
+   x = (x | x << 16) & 0x1f0000ff0000ffULL;
+   x = (x | x << 8) & 0x100f00f00f00f00fULL;
+   x = (x | x << 4) & 0x10c30c30c30c30c3ULL;
+   x = (x | x << 2) & 0x1249249249249249ULL;
+   return x;
+}
+
+// order [lo,hi) by key (stable), append to perm
+template <class Key>
+static void sort_block(std::vector<int> &perm, int lo, int hi, const std::vector<Key> &key) {
+   std::vector<int> idx(hi - lo);
+   std::iota(idx.begin(), idx.end(), lo);
+   std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return key[a] < key[b]; });
+   perm.insert(perm.end(), idx.begin(), idx.end());
+}
+
+template <class T> static int to_device(OmegaMesh *M, const std::vector<T> &h, const T **out) {
+   void *d = nullptr;
+   size_t bytes = std::max<size_t>(h.size() * sizeof(T), 16);
+   OMEGA_CUDA_CHECK(cudaMalloc(&d, bytes));
+   M->Allocs.push_back(d);
+   if (!h.empty()) OMEGA_CUDA_CHECK(cudaMemcpy(d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+   *out = static_cast<const T *>(d);
+   return 0;
+}
+
+// rows of a host-order table gathered into device order
+template <class T>
+static std::vector<T> gather_rows(const T *src, const std::vector<int> &perm, int width) {
+   std::vector<T> out(perm.size() * (size_t)width);
+   for (size_t i = 0; i < perm.size(); ++i)
+      std::memcpy(&out[i * width], &src[(size_t)perm[i] * width], sizeof(T) * width);
+   return out;
+}
+// same, and translate the stored indices through iperm of the target kind
+static std::vector<int> gather_index_rows(const int *src, const std::vector<int> &perm, int width,
+                                          const std::vector<int> &iperm_target) {
+   std::vector<int> out(perm.size() * (size_t)width);
+   for (size_t i = 0; i < perm.size(); ++i)
+      for (int j = 0; j < width; ++j) {
+         int t = src[(size_t)perm[i] * width + j];
+         if (t < 0 || t >= (int)iperm_target.size()) t = (int)iperm_target.size() - 1; // boundary slot
+         out[i * width + j] = iperm_target[t];
+      }
+   return out;
+}
+
+} // namespace omega
+
+using namespace omega;
+
+extern "C" {
+
+const char *omega_last_error(void) { return g_last_error.c_str(); }
+int omega_b200_abi_version(void) { return 1; }
+
+int omega_dev_alloc(void **ptr, unsigned long long bytes) {
+   OMEGA_CUDA_CHECK(cudaMalloc(ptr, bytes ? bytes : 16));
+   OMEGA_CUDA_CHECK(cudaMemset(*ptr, 0, bytes));
+   return 0;
+}
+int omega_dev_free(void *ptr) {
+   OMEGA_CUDA_CHECK(cudaFree(ptr));
+   return 0;
+}
+int omega_dev_sync(void *stream) {
+   OMEGA_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+   return 0;
+}
+
+int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
+   OMEGA_REQUIRE(D && Out, "omega_mesh_create: null argument");
+   OMEGA_REQUIRE(D->VertexDegree == 3, "omega_mesh_create: VertexDegree must be 3");
+   OMEGA_REQUIRE(D->NCellsSize == D->NCellsAll + 1 && D->NEdgesSize == D->NEdgesAll + 1 &&
+                     D->NVerticesSize == D->NVerticesAll + 1,
+                 "omega_mesh_create: N*Size must equal N*All+1 (Decomp.cpp:1081-1082)");
+   OmegaMesh *M = new OmegaMesh();
+   M->Sizes     = *D;
+   M->Reordered = Reorder;
+   const int NC = D->NCellsAll, NE = D->NEdgesAll, NV = D->NVerticesAll;
+   const int ME = D->MaxEdges, ME2 = D->MaxEdges2;
+
+   // ---- derived fields in host order (HorzMesh.cpp:527-626) ----------------
+   M->EdgeSignOnCellH.assign((size_t)D->NCellsSize * ME, 0.0);
+   M->EdgeSignOnVertexH.assign((size_t)D->NVerticesSize * 3, 0.0);
+   M->EdgeMaskH.assign(D->NEdgesSize, 1.0);
+   for (int c = 0; c < NC; ++c)
+      for (int i = 0; i < D->NEdgesOnCell[c]; ++i) {
+         const int e = D->EdgesOnCell[c * ME + i];
+         M->EdgeSignOnCellH[(size_t)c * ME + i] = (c == D->CellsOnEdge[2 * e]) ? -1.0 : 1.0;
+      }
+   for (int v = 0; v < NV; ++v)
+      for (int i = 0; i < 3; ++i) {
+         const int e = D->EdgesOnVertex[v * 3 + i];
+         M->EdgeSignOnVertexH[(size_t)v * 3 + i] = (v == D->VerticesOnEdge[2 * e]) ? -1.0 : 1.0;
+      }
+   for (int e = 0; e < NE; ++e) {
+      const int c1 = D->CellsOnEdge[2 * e], c2 = D->CellsOnEdge[2 * e + 1];
+      if (!(c1 >= 0 && c1 < NC) || !(c2 >= 0 && c2 < NC)) M->EdgeMaskH[e] = 0.0;
+   }
+   std::vector<double> Scale2(D->NEdgesSize, 0.0), Scale4(D->NEdgesSize, 0.0);
+   for (int e = 0; e < NE; ++e) Scale2[e] = Scale4[e] = 1.0;
+
+   // ---- permutations: Perm[new] = old -----------------------------------
+   std::vector<int> &PC = M->Perm[0], &PE = M->Perm[1], &PV = M->Perm[2];
+   if (Reorder) {
+      double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+      const double *X[3] = {D->XCell, D->YCell, D->ZCell};
+      for (int a = 0; a < 3; ++a)
+         for (int c = 0; c < NC; ++c) {
+            lo[a] = std::min(lo[a], X[a][c]);
+            hi[a] = std::max(hi[a], X[a][c]);
+         }
+      std::vector<uint64_t> key(NC);
+      for (int c = 0; c < NC; ++c) {
+         uint64_t q[3];
+         for (int a = 0; a < 3; ++a) {
+            const double span = hi[a] - lo[a];
+            const double t    = span > 0 ? (X[a][c] - lo[a]) / span : 0.0;
+            q[a]              = (uint64_t)std::min(2097151.0, std::floor(t * 2097152.0));
+         }
+         key[c] = spread3(q[0]) | (spread3(q[1]) << 1) | (spread3(q[2]) << 2);
+      }
+      sort_block(PC, 0, D->NCellsOwned, key);
+      sort_block(PC, D->NCellsOwned, NC, key);
+   } else {
+      PC.resize(NC);
+      std::iota(PC.begin(), PC.end(), 0);
+   }
+   PC.push_back(NC); // boundary slot stays last
+   M->IPerm[0].assign(D->NCellsSize, 0);
+   for (int i = 0; i < D->NCellsSize; ++i) M->IPerm[0][PC[i]] = i;
+   auto dual_perm = [&](int NAll, int NOwned, const int *CellsOnX, int width, std::vector<int> &P,
+                        std::vector<int> &IP) {
+      if (Reorder) {
+         std::vector<int> key(NAll);
+         for (int x = 0; x < NAll; ++x) {
+            int best = INT32_MAX;
+            for (int j = 0; j < width; ++j) {
+               const int c = CellsOnX[x * width + j];
+               if (c >= 0 && c < NC) best = std::min(best, M->IPerm[0][c]);
+            }
+            key[x] = best;
+         }
+         sort_block(P, 0, NOwned, key);
+         sort_block(P, NOwned, NAll, key);
+      } else {
+         P.resize(NAll);
+         std::iota(P.begin(), P.end(), 0);
+      }
+      P.push_back(NAll);
+      IP.assign(NAll + 1, 0);
+      for (int i = 0; i <= NAll; ++i) IP[P[i]] = i;
+   };
+   dual_perm(NE, D->NEdgesOwned, D->CellsOnEdge, 2, PE, M->IPerm[1]);
+   dual_perm(NV, D->NVerticesOwned, D->CellsOnVertex, 3, PV, M->IPerm[2]);
+   const std::vector<int> &IC = M->IPerm[0], &IE = M->IPerm[1], &IV = M->IPerm[2];
+
+   // ---- device SoA in device order ---------------------------------------
+   DMesh &G = M->D;
+   G.NCellsAll = NC; G.NEdgesAll = NE; G.NVerticesAll = NV;
+   G.NCellsOwned = D->NCellsOwned; G.NEdgesOwned = D->NEdgesOwned; G.NVerticesOwned = D->NVerticesOwned;
+   G.NCellsSize = D->NCellsSize; G.NEdgesSize = D->NEdgesSize; G.NVerticesSize = D->NVerticesSize;
+   G.K = D->NVertLayers; G.MaxEdges = ME; G.MaxEdges2 = ME2;
+   int rc = 0;
+#define STAGE(dst, vec) rc |= to_device(M, (vec), &(dst))
+   STAGE(G.NEdgesOnCell, gather_rows(D->NEdgesOnCell, PC, 1));
+   STAGE(G.EdgesOnCell, gather_index_rows(D->EdgesOnCell, PC, ME, IE));
+   STAGE(G.EdgeSignOnCell, gather_rows(M->EdgeSignOnCellH.data(), PC, ME));
+   STAGE(G.AreaCell, gather_rows(D->AreaCell, PC, 1));
+   STAGE(G.BottomDepth, gather_rows(D->BottomDepth, PC, 1));
+   STAGE(G.XCell, gather_rows(D->XCell, PC, 1));
+   STAGE(G.YCell, gather_rows(D->YCell, PC, 1));
+   {
+      std::vector<int> coe = gather_index_rows(D->CellsOnEdge, PE, 2, IC);
+      std::vector<int> voe = gather_index_rows(D->VerticesOnEdge, PE, 2, IV);
+      const int *p = nullptr;
+      rc |= to_device(M, coe, &p); G.CellsOnEdge = reinterpret_cast<const int2 *>(p);
+      rc |= to_device(M, voe, &p); G.VerticesOnEdge = reinterpret_cast<const int2 *>(p);
+   }
+   {
+      // EdgesOnEdge / WeightsOnEdge; trailing boundary-slot entries (zero weight
+      // padding that Decomp.cpp:2186-2200 counts) are trimmed from the count
+      std::vector<int> eoe  = gather_index_rows(D->EdgesOnEdge, PE, ME2, IE);
+      std::vector<int> neoe = gather_rows(D->NEdgesOnEdge, PE, 1);
+      std::vector<double> w = gather_rows(D->WeightsOnEdge, PE, ME2);
+      for (int e = 0; e < NE; ++e) {
+         int n = neoe[e];
+         while (n > 0 && eoe[(size_t)e * ME2 + n - 1] == NE && w[(size_t)e * ME2 + n - 1] == 0.0) --n;
+         neoe[e] = n;
+      }
+      STAGE(G.NEdgesOnEdge, neoe);
+      STAGE(G.EdgesOnEdge, eoe);
+      STAGE(G.WeightsOnEdge, w);
+   }
+   STAGE(G.DcEdge, gather_rows(D->DcEdge, PE, 1));
+   STAGE(G.DvEdge, gather_rows(D->DvEdge, PE, 1));
+   STAGE(G.AngleEdge, gather_rows(D->AngleEdge, PE, 1));
+   STAGE(G.FEdge, gather_rows(D->FEdge, PE, 1));
+   STAGE(G.XEdge, gather_rows(D->XEdge, PE, 1));
+   STAGE(G.YEdge, gather_rows(D->YEdge, PE, 1));
+   STAGE(G.EdgeMask, gather_rows(M->EdgeMaskH.data(), PE, 1));
+   STAGE(G.MeshScalingDel2, gather_rows(Scale2.data(), PE, 1));
+   STAGE(G.MeshScalingDel4, gather_rows(Scale4.data(), PE, 1));
+   STAGE(G.CellsOnVertex, gather_index_rows(D->CellsOnVertex, PV, 3, IC));
+   STAGE(G.EdgesOnVertex, gather_index_rows(D->EdgesOnVertex, PV, 3, IE));
+   STAGE(G.EdgeSignOnVertex, gather_rows(M->EdgeSignOnVertexH.data(), PV, 3));
+   STAGE(G.KiteAreasOnVertex, gather_rows(D->KiteAreasOnVertex, PV, 3));
+   STAGE(G.AreaTriangle, gather_rows(D->AreaTriangle, PV, 1));
+   STAGE(G.FVertex, gather_rows(D->FVertex, PV, 1));
+#undef STAGE
+   for (int kind = 0; kind < 3; ++kind) {
+      const int *p = nullptr;
+      rc |= to_device(M, M->Perm[kind], &p);
+      M->DPerm[kind] = const_cast<int *>(p);
+      rc |= to_device(M, M->IPerm[kind], &p);
+      M->DIPerm[kind] = const_cast<int *>(p);
+   }
+   if (rc) {
+      omega_mesh_destroy(M);
+      return 1;
+   }
+   // scalar-only copy of the descriptor
+   OmegaMeshDesc S = *D;
+   std::memset(&S.NEdgesOnCell, 0, sizeof(S) - offsetof(OmegaMeshDesc, NEdgesOnCell));
+   M->Sizes = S;
+   *Out     = M;
+   return 0;
+}
+
+int omega_mesh_destroy(OmegaMesh *M) {
+   if (!M) return 0;
+   for (void *p : M->Allocs) cudaFree(p);
+   delete M;
+   return 0;
+}
+
+int omega_mesh_perm(const OmegaMesh *M, OmegaMeshElement Elem, int *Perm, int *IPerm) {
+   OMEGA_REQUIRE(M && Elem >= 0 && Elem < 3, "omega_mesh_perm: bad argument");
+   if (Perm) std::memcpy(Perm, M->Perm[Elem].data(), sizeof(int) * M->Perm[Elem].size());
+   if (IPerm) std::memcpy(IPerm, M->IPerm[Elem].data(), sizeof(int) * M->IPerm[Elem].size());
+   return 0;
+}
+
+int omega_mesh_derived(const OmegaMesh *M, double *EdgeSignOnCell, double *EdgeSignOnVertex, double *EdgeMask) {
+   OMEGA_REQUIRE(M, "omega_mesh_derived: null mesh");
+   if (EdgeSignOnCell) std::memcpy(EdgeSignOnCell, M->EdgeSignOnCellH.data(), sizeof(double) * M->EdgeSignOnCellH.size());
+   if (EdgeSignOnVertex) std::memcpy(EdgeSignOnVertex, M->EdgeSignOnVertexH.data(), sizeof(double) * M->EdgeSignOnVertexH.size());
+   if (EdgeMask) std::memcpy(EdgeMask, M->EdgeMaskH.data(), sizeof(double) * M->EdgeMaskH.size());
+   return 0;
+}
+
+int omega_field_to_device(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
+                          const double *Host, double *Dev, void *Stream) {
+   OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3, "omega_field_to_device: bad argument");
+   cudaStream_t S     = (cudaStream_t)Stream;
+   const int NRows    = n_size(M, Elem);
+   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
+   if (!M->Reordered) {
+      OMEGA_CUDA_CHECK(cudaMemcpyAsync(Dev, Host, bytes, cudaMemcpyHostToDevice, S));
+      return 0;
+   }
+   double *stage = nullptr;
+   OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, bytes, S));
+   OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));
+   launch_permute_rows(S, NOuter, NRows, NInner, M->DPerm[Elem], stage, Dev);
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   OMEGA_CUDA_CHECK(cudaFreeAsync(stage, S));
+   return 0;
+}
+
+int omega_field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
+                        const double *Dev, double *Host, void *Stream) {
+   OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3, "omega_field_to_host: bad argument");
+   cudaStream_t S     = (cudaStream_t)Stream;
+   const int NRows    = n_size(M, Elem);
+   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
+   if (!M->Reordered) {
+      OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, Dev, bytes, cudaMemcpyDeviceToHost, S));
+      OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
+      return 0;
+   }
+   // host row r comes from device row IPerm[r]
+   double *stage = nullptr;
+   OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, bytes, S));
+   launch_permute_rows(S, NOuter, NRows, NInner, M->DIPerm[Elem], Dev, stage);
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, stage, bytes, cudaMemcpyDeviceToHost, S));
+   OMEGA_CUDA_CHECK(cudaFreeAsync(stage, S));
+   OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
+   return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,134 @@
+// omega_dev.h -- internal declarations of libomega_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "omega_b200.h"
+
+namespace omega {
+
+void set_error(const std::string &msg);
+
+#define OMEGA_CUDA_CHECK(expr)                                                         \
+   do {                                                                                \
+      cudaError_t e_ = (expr);                                                         \
+      if (e_ != cudaSuccess) {                                                         \
+         ::omega::set_error(std::string(#expr) + ": " + cudaGetErrorString(e_));       \
+         return 1;                                                                     \
+      }                                                                                \
+   } while (0)
+
+#define OMEGA_REQUIRE(cond, msg)                                                       \
+   do {                                                                                \
+      if (!(cond)) {                                                                   \
+         ::omega::set_error(msg);                                                      \
+         return 2;                                                                     \
+      }                                                                                \
+   } while (0)
+
+// Device-resident HorzMesh, structure of arrays, DEVICE order.  Passed to
+// kernels by value (fits the 4 KB parameter space many times over).
+struct DMesh {
+   int NCellsAll, NEdgesAll, NVerticesAll;
+   int NCellsOwned, NEdgesOwned, NVerticesOwned;
+   int NCellsSize, NEdgesSize, NVerticesSize;
+   int K;        // NVertLayers
+   int MaxEdges; // row stride of the per-cell tables
+   int MaxEdges2;
+   // cells
+   const int *NEdgesOnCell;       // [C]
+   const int *EdgesOnCell;        // [C][MaxEdges]
+   const double *EdgeSignOnCell;  // [C][MaxEdges]
+   const double *AreaCell, *BottomDepth, *XCell, *YCell;
+   // edges
+   const int2 *CellsOnEdge, *VerticesOnEdge; // [E]
+   const int *NEdgesOnEdge;                  // [E] trimmed of trailing boundary-slot entries
+   const int *EdgesOnEdge;                   // [E][MaxEdges2]
+   const double *WeightsOnEdge;              // [E][MaxEdges2]
+   const double *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge;
+   const double *EdgeMask, *MeshScalingDel2, *MeshScalingDel4; // [E]
+   // vertices (VertexDegree == 3)
+   const int *CellsOnVertex, *EdgesOnVertex;               // [V][3]
+   const double *EdgeSignOnVertex, *KiteAreasOnVertex;     // [V][3]
+   const double *AreaTriangle, *FVertex;
+};
+
+} // namespace omega
+
+struct OmegaMesh {
+   omega::DMesh D;
+   OmegaMeshDesc Sizes; // scalar members only (pointers nulled)
+   int Reordered;
+   // host copies of the permutations (Perm[new] = old) and derived fields (host order)
+   std::vector<int> Perm[3], IPerm[3];
+   std::vector<double> EdgeSignOnCellH, EdgeSignOnVertexH, EdgeMaskH;
+   // device permutation tables for field transfers
+   int *DPerm[3], *DIPerm[3];
+   std::vector<void *> Allocs; // every device allocation owned by the mesh
+};
+
+namespace omega {
+
+inline int n_size(const OmegaMesh *M, int Elem) {
+   return Elem == OMEGA_ON_CELL ? M->D.NCellsSize : Elem == OMEGA_ON_EDGE ? M->D.NEdgesSize : M->D.NVerticesSize;
+}
+inline int n_all(const OmegaMesh *M, int Elem) {
+   return Elem == OMEGA_ON_CELL ? M->D.NCellsAll : Elem == OMEGA_ON_EDGE ? M->D.NEdgesAll : M->D.NVerticesAll;
+}
+
+// ---- kernels_aux.cu / kernels_tend.cu / kernels_update.cu launchers --------
+struct AuxPtrs {
+   double *KE, *Div, *Flux, *Mean, *Ssh, *RelVort, *NormRelVort, *NormPlanetVort, *NormRelVortEdge,
+       *NormPlanetVortEdge, *Del2Edge, *Del2Div, *Del2RelVort, *HTr, *Del2Tr, *NormalStress,
+       *ZonalStress, *MeridStress;
+};
+
+struct Launch {
+   cudaStream_t Stream;
+   long long *Count; // launch counter of the owning stepper
+};
+
+void launch_vertex_aux1(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A);
+void launch_cell_aux1(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A);
+void launch_wind_aux(const Launch &L, const DMesh &M, const AuxPtrs &A, int Aniso);
+void launch_edge_aux2(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A,
+                      int FluxUpwind, int ThickOnly);
+void launch_vertex_aux2(const Launch &L, const DMesh &M, const AuxPtrs &A);
+void launch_cell_aux2(const Launch &L, const DMesh &M, const AuxPtrs &A);
+void launch_tracer_aux_edge(const Launch &L, const DMesh &M, const double *H, const double *U,
+                            const double *Tr, int NTracers, const AuxPtrs &A, int Upwind);
+void launch_tracer_aux_cell(const Launch &L, const DMesh &M, const double *Tr, int NTracers,
+                            const AuxPtrs &A);
+
+struct ManufacturedParams {
+   int Enabled;
+   double H0, Eta0, Kx, Ky, AngFreq, Time;
+};
+
+void launch_thick_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
+                       const double *U, double *HTend, const ManufacturedParams &MS);
+void launch_vel_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
+                     const double *U, const double *URaw, double *UTend, const ManufacturedParams &MS);
+void launch_tracer_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
+                        const double *URaw, const double *Tr, int NTracers, double *TrTend);
+
+// Y1 = Y2 + c*T over rows [0,NAll)
+void launch_axpy(const Launch &L, int NAll, int K, double *Y1, const double *Y2, double C, const double *T);
+// Next = (Cur*H2 + c*T)/H1 ; Next = Cur*H ; Accum += c*T ; Next /= H   (all tracers)
+void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                           const double *Cur, const double *H1, const double *H2, double C, const double *T);
+void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                           const double *Cur, const double *H);
+void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Accum,
+                               double C, const double *T);
+void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
+                             const double *H);
+
+// gather/scatter rows through a permutation (field transfer, halo)
+void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
+                         const double *Src, double *Dst);
+
+} // namespace omega

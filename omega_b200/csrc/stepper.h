@@ -1,0 +1,31 @@
+// stepper.h -- the object behind OmegaStepper*: config, aux/tendency arrays
+// (owned, as AuxiliaryState and Tendencies own theirs) and the provisional
+// state of the Runge-Kutta steppers.
+#pragma once
+#include "omega_dev.h"
+
+struct ProvisArrays {
+   double *H[2], *U[2], *Tr[2];
+};
+
+struct OmegaStepper {
+   const OmegaMesh *M;
+   OmegaTendConfig Cfg;
+   int NTracers;
+   double BottomDepth0;
+   omega::AuxPtrs A;
+   OmegaTendArrays T;
+   ProvisArrays P;
+   long long Launches;
+   int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
+   std::vector<void *> Allocs;
+};
+
+namespace omega {
+int stepper_alloc(OmegaStepper *S, double **p, size_t n);
+ManufacturedParams manufactured(const OmegaStepper *S, double Time);
+int ensure_htr(OmegaStepper *S);
+// fused.cu: one RK4 phase on the fused per-stage pipeline
+int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
+                    cudaStream_t Stream);
+} // namespace omega

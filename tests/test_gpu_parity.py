@@ -1,0 +1,177 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against
+the CPU oracle on the same inputs.  Thresholds are BASELINE.json's: indices,
+permutations and derived sign/mask arrays bit-exact; per-field tendencies
+after one right-hand side <= 1e-12 relative max (max|a-b|/max|b|); prognostic
+state after many steps <= 1e-10 relative L2."""
+import numpy as np
+import pytest
+
+from omega_b200 import capi
+from tests import cases
+from tests.cases import rel_l2, rel_max
+
+pytestmark = pytest.mark.gpu
+
+TOL_TEND = 1e-12
+TOL_STATE = 1e-10
+
+
+def gpu_objects(L, cfg, T, reorder=True):
+    from omega_b200 import model
+    mesh = model.HorzMesh(L, reorder=reorder)
+    return mesh, model.Stepper(mesh, cfg, T), model.OceanState(mesh, T)
+
+
+CASES = {
+    "sphere3_K4_T2": lambda: cases.sphere_case(3, 4, 2),
+    "sphere2_K3_T1": lambda: cases.sphere_case(2, 3, 1),      # odd level count -> scalar path
+    "sphere3_K64_T3": lambda: cases.sphere_case(3, 64, 3),    # warp == one element row
+    "plane16_K1_T0": lambda: cases.plane_case(16, 1, 0),      # config-1 shape: 1 level, no tracers
+    "plane12_K10_T2": lambda: cases.plane_case(12, 10, 2),
+}
+
+
+@pytest.fixture(scope="module", params=list(CASES))
+def case(request):
+    return request.param, CASES[request.param]()
+
+
+@pytest.mark.parametrize("reorder", [True, False])
+def test_permutation_and_transfer_bit_exact(case, reorder):
+    _, (L, cfg, (h, u, tr), dt) = case
+    mesh, st, state = gpu_objects(L, cfg, tr.shape[0], reorder)
+    for kind in range(3):
+        p, ip = mesh.perm(kind)
+        n = mesh.NSize[kind]
+        assert np.array_equal(np.sort(p), np.arange(n)), "perm is not a bijection"
+        assert np.array_equal(ip[p], np.arange(n))
+        assert p[-1] == n - 1, "boundary slot must stay last"
+        own = mesh.NOwned[kind]
+        assert np.array_equal(np.sort(p[:own]), np.arange(own)), "owned block must stay first"
+    for kind, a in ((capi.ON_CELL, h), (capi.ON_EDGE, u)):
+        d = mesh.to_device(kind, a)
+        p, _ = mesh.perm(kind)
+        assert np.array_equal(d.cpu().numpy(), a[p]), "device order must be host[perm]"
+        assert np.array_equal(mesh.to_host(kind, d), a)
+    if tr.shape[0]:
+        d = mesh.to_device(capi.ON_CELL, tr)
+        assert np.array_equal(mesh.to_host(capi.ON_CELL, d), tr)
+    st.close(); mesh.close()
+
+
+def test_derived_mesh_fields_bit_exact(case):
+    from tests.oracle_lib import Oracle
+    _, (L, cfg, (h, u, tr), dt) = case
+    mesh, st, state = gpu_objects(L, cfg, tr.shape[0])
+    o = Oracle(L, cfg, tr.shape[0])
+    for a, b in zip(mesh.derived(), o.derived()):
+        assert np.array_equal(a, b)
+    o.close(); st.close(); mesh.close()
+
+
+@pytest.mark.parametrize("reorder", [True, False])
+def test_aux_and_tendencies_one_rhs(case, reorder):
+    from tests.oracle_lib import Oracle
+    name, (L, cfg, (h, u, tr), dt) = case
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T, reorder)
+    o = Oracle(L, cfg, T)
+    o.tend_all(h, u, tr, time=0.0)
+    dh, du = mesh.to_device(capi.ON_CELL, h), mesh.to_device(capi.ON_EDGE, u)
+    dtr = mesh.to_device(capi.ON_CELL, tr) if T else None
+    st.computeAllTendencies(dh, du, dtr, 0.0)
+    aux = st.aux_to_host()
+    for n in capi.AUX_FIELDS:
+        if n in ("ZonalStressCell", "MeridStressCell", "NormalStressEdge"):
+            continue
+        assert rel_max(aux[n], o.aux[n]) <= TOL_TEND, (name, n, rel_max(aux[n], o.aux[n]))
+    tend = st.tend_to_host()
+    for n in tend:
+        assert rel_max(tend[n], o.tend[n]) <= TOL_TEND, (name, n, rel_max(tend[n], o.tend[n]))
+        if tend[n].size:
+            assert np.abs(o.tend[n]).max() > 0, "degenerate case: tendency is identically zero"
+    o.close(); st.close(); mesh.close()
+
+
+def test_all_optional_terms_one_rhs():
+    """wind forcing + bottom drag + upwind fluxes (off in Default.yml)."""
+    from tests.oracle_lib import Oracle
+    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case()
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T)
+    o = Oracle(L, cfg, T)
+    o.set_wind_stress(zonal, merid)
+    st.set_wind_stress(zonal, merid)
+    o.tend_all(h, u, tr)
+    dh, du, dtr = mesh.to_device(capi.ON_CELL, h), mesh.to_device(capi.ON_EDGE, u), mesh.to_device(capi.ON_CELL, tr)
+    st.computeAllTendencies(dh, du, dtr)
+    aux, tend = st.aux_to_host(), st.tend_to_host()
+    for n in capi.AUX_FIELDS:
+        assert rel_max(aux[n], o.aux[n]) <= TOL_TEND, (n, rel_max(aux[n], o.aux[n]))
+    for n in tend:
+        assert rel_max(tend[n], o.tend[n]) <= TOL_TEND, (n, rel_max(tend[n], o.tend[n]))
+    o.close(); st.close(); mesh.close()
+
+
+def test_manufactured_solution_rhs():
+    """config 1: single layer planar hex with the custom source terms."""
+    from omega_b200 import analytic
+    from tests.oracle_lib import Oracle
+    L, cfg, _, dt = cases.plane_case(16, 1, 0, ManufacturedSolutionTendency=1, ManufacturedWavelengthX=16 * 5.0e6 / 64,
+                                     ManufacturedWavelengthY=16 * 5.0e6 / 64 * np.sqrt(3) / 2,
+                                     TracerHorzAdvTendencyEnable=0, TracerDiffTendencyEnable=0,
+                                     TracerHyperDiffTendencyEnable=0)
+    h, u = analytic.manufactured(L, cfg)
+    tr = np.zeros((0, h.shape[0], 1))
+    mesh, st, state = gpu_objects(L, cfg, 0)
+    o = Oracle(L, cfg, 0)
+    o.tend_all(h, u, tr, time=123.0)
+    st.computeAllTendencies(mesh.to_device(capi.ON_CELL, h), mesh.to_device(capi.ON_EDGE, u), None, 123.0)
+    tend = st.tend_to_host()
+    for n in ("LayerThicknessTend", "NormalVelocityTend"):
+        assert rel_max(tend[n], o.tend[n]) <= TOL_TEND, (n, rel_max(tend[n], o.tend[n]))
+    o.close(); st.close(); mesh.close()
+
+
+def run_steps(L, cfg, init, dt, stepper, nsteps, fused, compat, reorder=True):
+    from tests.oracle_lib import Oracle
+    h, u, tr = init
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T, reorder)
+    o = Oracle(L, cfg, T)
+    o.make_state(h, u, tr)
+    state.copyToDevice(h, u, tr)
+    co = capi.rk_coeffs(stepper, dt)
+    for _ in range(nsteps):
+        o.do_step(stepper, co, compat=int(compat))
+        st.doStep(state, stepper, co, fused=fused, compat=compat)
+    got, exp = state.copyToHost(0), o.current()
+    errs = [rel_l2(got[0], exp[0]), rel_l2(got[1], exp[1])]
+    if T:
+        errs.append(rel_l2(got[2], exp[2]))
+    assert np.all(np.isfinite(exp[0])) and np.all(np.isfinite(exp[1]))
+    o.close(); st.close(); mesh.close()
+    return errs
+
+
+@pytest.mark.parametrize("stepper", [capi.RK4, capi.RK2, capi.FB])
+@pytest.mark.parametrize("compat", [True, False])
+def test_steppers_kernel_per_term_path(case, stepper, compat):
+    name, (L, cfg, init, dt) = case
+    errs = run_steps(L, cfg, init, dt, stepper, 5, fused=False, compat=compat)
+    assert max(errs) <= TOL_STATE, (name, errs)
+
+
+@pytest.mark.parametrize("compat", [True, False])
+def test_rk4_fused_path(case, compat):
+    name, (L, cfg, init, dt) = case
+    errs = run_steps(L, cfg, init, dt, capi.RK4, 5, fused=True, compat=compat)
+    assert max(errs) <= TOL_STATE, (name, errs)
+
+
+def test_rk4_100_steps_state_parity():
+    """BASELINE.json: prognostic state after 100 RK4 steps, relative L2 <= 1e-10."""
+    L, cfg, init, dt = cases.sphere_case(3, 8, 3)
+    for fused in (False, True):
+        errs = run_steps(L, cfg, init, dt, capi.RK4, 100, fused=fused, compat=True)
+        assert max(errs) <= TOL_STATE, (fused, errs)
