@@ -10,6 +10,8 @@ from omega_b200 import analytic, capi, decomp, meshgen
 
 def rel_max(a, b):
     """BASELINE.json parity metric: max|a-b| / max|b|."""
+    if b.size == 0:
+        return 0.0
     s = np.abs(b).max()
     d = np.abs(a - b).max()
     return d / s if s > 0 else d
