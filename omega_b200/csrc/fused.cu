@@ -1,9 +1,676 @@
-// fused.cu -- placeholder until the fused per-stage pipeline lands
+// fused.cu -- the fused per-stage RK4 pipeline (TimeStepper::doStep hot path).
+//
+// One RK4 stage of the reference is ~27 kernel launches that stream
+// (177 + 24 T) doubles per cell-layer through HBM.  Here a stage
+// is at most five launches and no tendency, edge-aux or tracer-flux array is
+// ever materialised:
+//
+//   fA  cells+vertices : h,u            -> KE, Div | RelVort, PV(vertex)
+//   fB  cells+vertices : Div, RelVort   -> Del2Div | Del2RelVort   (Del4 only;
+//                        Del2Edge is recomputed on the fly, never stored)
+//   fT2 cells          : tracers, h     -> Del2Tracers             (tracer Del4 only)
+//   fC  cells          : thickness + every tracer tendency of every tracer,
+//                        with the RK updates of h and tracers as epilogue
+//   fE  edges          : every velocity tendency term + the RK update of u
+//
+// The stage update  q_next (+)= b_s dt R,  q_provis' = q_cur + a_{s+1} dt R  is
+// applied in the epilogue of the kernel that produced R, into the OTHER of two
+// provisional buffers (neighbours still read this stage's provisional state).
+//
+// Work assignment: a CTA owns a contiguous block of rows in space-filling-curve
+// order and its warps sweep it together, so neighbour rows fetched by one warp
+// are L1/L2 hits for the next; fA/fB process the vertex range that belongs to
+// the same patch in the same CTA so u / Div rows are fetched once.
+//
+// Reference semantics restated: src/timeStepping/RungeKutta4Stepper.cpp:68-137,
+// src/timeStepping/TimeStepper.cpp:378-524, src/ocn/Tendencies.cpp:257-486,
+// src/ocn/AuxiliaryState.cpp:60-185 and the functors cited at each block.
+#include <algorithm>
+
+#include "kernel_util.cuh"
 #include "omega_dev.h"
 #include "stepper.h"
+
 namespace omega {
-int fused_rk4_phase(OmegaStepper *, OmegaStateArrays *, const OmegaStepCoeffs *, int, int, cudaStream_t) {
-   set_error("fused RK4 pipeline not built");
-   return 3;
+
+// rows [r0, r0+n) of this CTA for an index space of N rows split over gridDim.x CTAs
+__device__ __forceinline__ void cta_rows(int N, int &r0, int &n) {
+   const long long per = ((long long)N + gridDim.x - 1) / gridDim.x;
+   const long long a   = per * blockIdx.x;
+   r0                  = (int)(a < N ? a : N);
+   const long long b   = a + per;
+   n                   = (int)((b < N ? b : N) - r0);
 }
+
+// sweep (row, level-vector) items of a row block: consecutive threads take
+// consecutive level vectors of a row, then the next row
+#define OMEGA_FOR_ROWS(ROW, KLEV, R0, NROWS, KV, V)                                        \
+   for (int w_ = threadIdx.x, ROW = (R0) + w_ / (KV), KLEV = (w_ % (KV)) * (V);           \
+        w_ < (NROWS) * (KV);                                                               \
+        w_ += blockDim.x, ROW = (R0) + w_ / (KV), KLEV = (w_ % (KV)) * (V))
+
+// ---------------------------------------------------------------------------
+// fA: KineticAuxVars::computeVarsOnCell (KineticAuxVars.h:20-47) on the CTA's
+// cells, VorticityAuxVars::computeVarsOnVertex (VorticityAuxVars.h:24-59) on
+// the matching vertex range.  PV(vertex) = NormRelVort + NormPlanetVort is
+// stored as ONE array (the edge kernel only ever needs their sum).
+// ---------------------------------------------------------------------------
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double *__restrict__ KE,
+     double *__restrict__ Div, double *__restrict__ RelVort, double *__restrict__ PVv) {
+   const int KV = M.K / V;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      const double InvA = 1.0 / M.AreaCell[c];
+      const int ne      = M.NEdgesOnCell[c];
+      double ke[V] = {0}, dv[V] = {0};
+      for (int j = 0; j < ne; ++j) {
+         const int e        = M.EdgesOnCell[c * M.MaxEdges + j];
+         const double dve   = M.DvEdge[e];
+         const double kcoef = 0.5 * dve * M.DcEdge[e] * 0.5 * InvA;
+         const double dcoef = dve * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
+         double u[V];
+         ldv<V>(u, U + (size_t)e * M.K + k);
+#pragma unroll
+         for (int q = 0; q < V; ++q) {
+            ke[q] += kcoef * u[q] * u[q];
+            dv[q] -= dcoef * u[q];
+         }
+      }
+      stv<V>(KE + (size_t)c * M.K + k, ke);
+      stv<V>(Div + (size_t)c * M.K + k, dv);
+   }
+   cta_rows(M.NVerticesAll, r0, n);
+   OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
+      const double InvAt = 1.0 / M.AreaTriangle[v];
+      double hv[V] = {0}, rv[V] = {0};
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+         const int c       = M.CellsOnVertex[v * 3 + j];
+         const int e       = M.EdgesOnVertex[v * 3 + j];
+         const double kite = InvAt * M.KiteAreasOnVertex[v * 3 + j];
+         const double dcs  = InvAt * M.DcEdge[e] * M.EdgeSignOnVertex[v * 3 + j];
+         double h[V], u[V];
+         ldv<V>(h, H + (size_t)c * M.K + k);
+         ldv<V>(u, U + (size_t)e * M.K + k);
+#pragma unroll
+         for (int q = 0; q < V; ++q) {
+            hv[q] += kite * h[q];
+            rv[q] += dcs * u[q];
+         }
+      }
+      const double f = M.FVertex[v];
+      double pv[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         const double inv = 1.0 / hv[q];
+         pv[q]            = rv[q] * inv + f * inv;
+      }
+      stv<V>(RelVort + (size_t)v * M.K + k, rv);
+      stv<V>(PVv + (size_t)v * M.K + k, pv);
+   }
+}
+
+// Del2Edge of VelocityDel2AuxVars::computeVarsOnEdge (VelocityDel2AuxVars.h:21-45)
+template <int V>
+__device__ __forceinline__ void del2_edge(const DMesh &M, int e, int k, const double *__restrict__ Div,
+                                          const double *__restrict__ RelVort, double (&out)[V]) {
+   const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
+   const double dc = M.DcEdge[e], dv = M.DvEdge[e];
+   const double InvDc = 1.0 / dc, InvDv = 1.0 / fmax(dv, 0.25 * dc), mask = M.EdgeMask[e];
+   double d0[V], d1[V], r0[V], r1[V];
+   ldv<V>(d0, Div + (size_t)cc.x * M.K + k);
+   ldv<V>(d1, Div + (size_t)cc.y * M.K + k);
+   ldv<V>(r0, RelVort + (size_t)vv.x * M.K + k);
+   ldv<V>(r1, RelVort + (size_t)vv.y * M.K + k);
+#pragma unroll
+   for (int q = 0; q < V; ++q) {
+      const double GradDiv  = (d1[q] - d0[q]) * InvDc;
+      const double CurlVort = -(r1[q] - r0[q]) * InvDv;
+      out[q]                = mask * GradDiv + CurlVort;
+   }
+}
+
+// ---------------------------------------------------------------------------
+// fB: VelocityDel2AuxVars::computeVarsOnCell / computeVarsOnVertex
+// (VelocityDel2AuxVars.h:47-89) with Del2Edge recomputed per use.
+// ---------------------------------------------------------------------------
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort,
+     double *__restrict__ Del2Div, double *__restrict__ Del2RelVort) {
+   const int KV = M.K / V;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      const double InvA = 1.0 / M.AreaCell[c];
+      const int ne      = M.NEdgesOnCell[c];
+      double t[V] = {0};
+      for (int j = 0; j < ne; ++j) {
+         const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
+         const double cf = M.DvEdge[e] * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
+         double d2[V];
+         del2_edge<V>(M, e, k, Div, RelVort, d2);
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] -= cf * d2[q];
+      }
+      stv<V>(Del2Div + (size_t)c * M.K + k, t);
+   }
+   cta_rows(M.NVerticesAll, r0, n);
+   OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
+      const double InvAt = 1.0 / M.AreaTriangle[v];
+      double t[V] = {0};
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+         const int e     = M.EdgesOnVertex[v * 3 + j];
+         const double cf = InvAt * M.DcEdge[e] * M.EdgeSignOnVertex[v * 3 + j];
+         double d2[V];
+         del2_edge<V>(M, e, k, Div, RelVort, d2);
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] += cf * d2[q];
+      }
+      stv<V>(Del2RelVort + (size_t)v * M.K + k, t);
+   }
+}
+
+// ---------------------------------------------------------------------------
+// fT2: TracerAuxVars::computeVarsOnCells (TracerAuxVars.h:61-91) for every
+// tracer; MeanLayerThickEdge is recomputed from h.  s*(phi(c1)-phi(c0)) ==
+// phi(self)-phi(nbr) exactly, so only the neighbour row is fetched.
+// ---------------------------------------------------------------------------
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_fT2(DMesh M, const double *__restrict__ H, const double *__restrict__ Tr, int NTracers,
+      double *__restrict__ Del2Tr) {
+   const int KV = M.K / V;
+   const size_t CS = (size_t)M.NCellsSize * M.K;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      const double InvA = 1.0 / M.AreaCell[c];
+      const int ne      = M.NEdgesOnCell[c];
+      const size_t o    = (size_t)c * M.K + k;
+      double hs[V];
+      ldv<V>(hs, H + o);
+      // per-edge coefficient  mask*sign*(dv/dc)*mean  and neighbour offset
+      double cf[6][V];
+      size_t on[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+         if (j < ne) {
+            const int e   = M.EdgesOnCell[c * M.MaxEdges + j];
+            const int2 cc = M.CellsOnEdge[e];
+            const int nb  = cc.x == c ? cc.y : cc.x;
+            on[j]         = (size_t)nb * M.K + k;
+            const double g = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * (M.DvEdge[e] / M.DcEdge[e]);
+            double h0[V], h1[V];
+            ldv<V>(h0, H + (size_t)cc.x * M.K + k);
+            ldv<V>(h1, H + (size_t)cc.y * M.K + k);
+            const double sgn = cc.x == c ? -1.0 : 1.0; // phi(c1)-phi(c0) = sgn*(phi(self)-phi(nbr))
+#pragma unroll
+            for (int q = 0; q < V; ++q) cf[j][q] = g * (0.5 * (h0[q] + h1[q])) * sgn;
+         }
+      }
+      for (int l = 0; l < NTracers; ++l) {
+         const double *T = Tr + l * CS;
+         double ts[V], t[V] = {0};
+         ldv<V>(ts, T + o);
+#pragma unroll
+         for (int j = 0; j < 6; ++j) {
+            if (j < ne) {
+               double tn[V];
+               ldv<V>(tn, T + on[j]);
+#pragma unroll
+               for (int q = 0; q < V; ++q) t[q] -= cf[j][q] * (ts[q] - tn[q]);
+            }
+         }
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] *= InvA;
+         stv<V>(Del2Tr + l * CS + o, t);
+      }
+   }
+}
+
+
+// ---------------------------------------------------------------------------
+// fC: cell pass.  ThicknessFluxDivOnCell (TendencyTerms.h:35-58) with
+// LayerThicknessAuxVars::computeVarsOnEdge (LayerThicknessAuxVars.h:25-61)
+// recomputed per edge; TracerHorzAdvOnCell / TracerDiffOnCell /
+// TracerHyperDiffOnCell (TendencyTerms.h:349-480) with
+// TracerAuxVars::computeVarsOnEdge (TracerAuxVars.h:25-59) recomputed; then
+// updateThicknessByTend, weightTracers, accumulateTracersUpdate,
+// updateTracersByTend, finalizeTracersUpdate (TimeStepper.cpp:378-524) as the
+// epilogue.  Per-edge coefficients live in registers and serve every tracer.
+// ---------------------------------------------------------------------------
+struct CellArgs {
+   const double *Hs, *Us, *UTr, *Trs, *Del2Tr; // stage state; UTr = velocity seen by tracer advection
+   const double *Hcur;
+   double *Hnext, *Hprov;                      // Hprov == nullptr on the last stage
+   const double *TrCur;
+   double *TrNext, *TrProv;
+   double A, B;                                // a_{s+1} dt, b_s dt
+   int First, Last, NTracers;
+   int WSel;   // stage-0 weight thickness: 0 = Hcur, 1 = Hnext before this stage writes it
+   int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext
+   int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
+   int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
+   double EddyDiff2, EddyDiff4;
+   ManufacturedParams MS;
+};
+
+constexpr int kME = 6; // max edges per cell on the fused path (checked at launch)
+
+template <int V, bool UPW>
+__global__ void __launch_bounds__(kBlock)
+k_fC(DMesh M, CellArgs P) {
+   const int KV = M.K / V;
+   const size_t CS = (size_t)M.NCellsSize * M.K;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      const double InvA = 1.0 / M.AreaCell[c];
+      const int ne      = M.NEdgesOnCell[c];
+      const size_t o    = (size_t)c * M.K + k;
+      double hs[V];
+      ldv<V>(hs, P.Hs + o);
+      double hn[kME][V], w[kME][V]; // neighbour thickness; mask*dv*sign*u_tr/A
+      double cd[kME], ch[kME];      // -k2/A*mask*sign*scale2*dv/dc*sgn ; +k4/A*mask*sign*scale4*dv/dc*sgn
+      int nb[kME];
+      bool self0[kME];
+      double su[UPW ? kME : 1][V]; // sign of the stage velocity (upwind options only)
+      double hT[V] = {0};
+#pragma unroll
+      for (int j = 0; j < kME; ++j) {
+         if (j < ne) {
+            const int e       = M.EdgesOnCell[c * M.MaxEdges + j];
+            const int2 cc     = M.CellsOnEdge[e];
+            self0[j]          = cc.x == c;
+            nb[j]             = self0[j] ? cc.y : cc.x;
+            const double sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
+            const double mask = M.EdgeMask[e], dve = M.DvEdge[e];
+            const double rdc  = dve / M.DcEdge[e];
+            const double sgn  = self0[j] ? -1.0 : 1.0;
+            cd[j] = -(P.EddyDiff2 * InvA) * (mask * sg * (M.MeshScalingDel2[e] * rdc)) * sgn;
+            ch[j] = (P.EddyDiff4 * InvA) * (mask * sg * (M.MeshScalingDel4[e] * rdc)) * sgn;
+            double us[V], ut[V];
+            ldv<V>(hn[j], P.Hs + (size_t)nb[j] * M.K + k);
+            ldv<V>(us, P.Us + (size_t)e * M.K + k);
+            if (P.UTr == P.Us) {
+#pragma unroll
+               for (int q = 0; q < V; ++q) ut[q] = us[q];
+            } else {
+               ldv<V>(ut, P.UTr + (size_t)e * M.K + k);
+            }
+            const double cf = dve * sg;
+#pragma unroll
+            for (int q = 0; q < V; ++q) {
+               // FluxLayerThickEdge: centred, or upwind on the sign of u (h0 is cell 0 of the edge)
+               double flux;
+               if (UPW) su[j][q] = us[q] > 0 ? 1.0 : (us[q] < 0 ? -1.0 : 0.0);
+               if (!UPW || !P.FluxUpwind) flux = 0.5 * (hs[q] + hn[j][q]);
+               else {
+                  const double h0 = self0[j] ? hs[q] : hn[j][q], h1 = self0[j] ? hn[j][q] : hs[q];
+                  flux = us[q] > 0 ? h0 : (us[q] < 0 ? h1 : fmax(h0, h1));
+               }
+               hT[q] += cf * flux * us[q] * InvA; // Tend -= (-sum) (TendencyTerms.h:48-56)
+               w[j][q] = mask * dve * sg * ut[q] * InvA;
+            }
+         }
+      }
+      if (!P.FluxDivOn) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) hT[q] = 0.0;
+      }
+      if (P.MS.Enabled) {
+         const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
+         const double src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
+                                         P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * cos(2.0 * Phase));
+#pragma unroll
+         for (int q = 0; q < V; ++q) hT[q] += src;
+      }
+      // ---- thickness updates (updateThicknessByTend) ----
+      double hcur[V], hnext_old[V], hnext[V], hprov[V];
+      if (P.First && P.Hcur == P.Hs) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) hcur[q] = hs[q];
+      } else {
+         ldp<V>(hcur, P.Hcur + o);
+      }
+      if (!P.First || P.WSel) ldp<V>(hnext_old, P.Hnext + o);
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         hnext[q] = (P.First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
+         hprov[q] = hcur[q] + P.A * hT[q];
+      }
+      stv<V>(P.Hnext + o, hnext);
+      if (!P.Last) stv<V>(P.Hprov + o, hprov);
+      // ---- tracers ----
+      double hw[V], h2[V], hfin[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         hw[q]   = P.WSel ? hnext_old[q] : hcur[q];
+         h2[q]   = P.H2Sel ? hnext[q] : hcur[q];
+         hfin[q] = P.FinSel ? hcur[q] : hnext[q];
+      }
+      for (int l = 0; l < P.NTracers; ++l) {
+         const double *T  = P.Trs + l * CS;
+         const double *D2 = P.Del2Tr + l * CS;
+         double ts[V], d2s[V], tend[V] = {0};
+         ldv<V>(ts, T + o);
+         if (P.HypOn) ldv<V>(d2s, D2 + o);
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            if (j < ne) {
+               const size_t on = (size_t)nb[j] * M.K + k;
+               double tn[V];
+               ldv<V>(tn, T + on);
+#pragma unroll
+               for (int q = 0; q < V; ++q) {
+                  if (P.AdvOn) {
+                     const double a = hs[q] * ts[q], b = hn[j][q] * tn[q];
+                     double htr;
+                     if (!UPW || !P.TrUpwind) htr = 0.5 * (a + b);
+                     else {
+                        // TracerAuxVars upwinds on the velocity of the aux call (the stage velocity)
+                        const double h0t = self0[j] ? a : b, h1t = self0[j] ? b : a;
+                        const double sgnu = su[UPW ? j : 0][q];
+                        htr = sgnu > 0 ? h0t : (sgnu < 0 ? h1t : fmax(h0t, h1t));
+                     }
+                     tend[q] += htr * w[j][q];
+                  }
+                  if (P.DiffOn) tend[q] += cd[j] * (0.5 * (hs[q] + hn[j][q])) * (ts[q] - tn[q]);
+               }
+               if (P.HypOn) {
+                  double d2n[V];
+                  ldv<V>(d2n, D2 + on);
+#pragma unroll
+                  for (int q = 0; q < V; ++q) tend[q] += ch[j] * (d2s[q] - d2n[q]);
+               }
+            }
+         }
+         // epilogue: weight/accumulate/provisional/finalise (TimeStepper.cpp:446-524)
+         double tcur[V], acc[V], out[V];
+         if (P.First && P.TrCur == P.Trs) {
+#pragma unroll
+            for (int q = 0; q < V; ++q) tcur[q] = ts[q];
+         } else if (P.First || !P.Last) {
+            ldp<V>(tcur, P.TrCur + l * CS + o);
+         }
+         if (!P.First) ldp<V>(acc, P.TrNext + l * CS + o);
+#pragma unroll
+         for (int q = 0; q < V; ++q) {
+            const double base = P.First ? tcur[q] * hw[q] : acc[q];
+            out[q]            = base + P.B * tend[q];
+            if (P.Last) out[q] = out[q] / hfin[q];
+         }
+         stv<V>(P.TrNext + l * CS + o, out);
+         if (!P.Last) {
+#pragma unroll
+            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / hprov[q];
+            stv<V>(P.TrProv + l * CS + o, out);
+         }
+      }
+   }
+}
+
+
+// ---------------------------------------------------------------------------
+// fE: edge pass.  PotentialVortHAdvOnEdge, KEGradOnEdge, SSHGradOnEdge,
+// VelocityDiffusionOnEdge, VelocityHyperDiffOnEdge, WindForcingOnEdge,
+// BottomDragOnEdge (TendencyTerms.h:81-334) + the manufactured source, with
+// the edge aux vars they consume recomputed from cell/vertex fields
+// (VorticityAuxVars.h:61-76, LayerThicknessAuxVars.h:25-82), then
+// updateVelocityByTend (TimeStepper.cpp:407-430) as the epilogue.
+// ---------------------------------------------------------------------------
+struct EdgeArgs {
+   const double *Hs, *Us, *URaw;                       // stage state; URaw = velocity seen by bottom drag
+   const double *KE, *Div, *RelVort, *PVv, *Del2Div, *Del2RelVort, *NormalStress;
+   const double *Ucur;
+   double *Unext, *Uprov;
+   double A, B;
+   int First, Last;
+   OmegaTendConfig G;
+   ManufacturedParams MS;
+};
+
+template <int V> __device__ __forceinline__ void flux_edge(const DMesh &M, int e, int k, const double *H,
+                                                           const double (&u)[V], int Upwind, double (&flux)[V]) {
+   const int2 cc = M.CellsOnEdge[e];
+   double h0[V], h1[V];
+   ldv<V>(h0, H + (size_t)cc.x * M.K + k);
+   ldv<V>(h1, H + (size_t)cc.y * M.K + k);
+#pragma unroll
+   for (int q = 0; q < V; ++q) {
+      if (!Upwind) flux[q] = 0.5 * (h0[q] + h1[q]);
+      else flux[q] = u[q] > 0 ? h0[q] : (u[q] < 0 ? h1[q] : fmax(h0[q], h1[q]));
+   }
+}
+
+template <int V> __device__ __forceinline__ void pv_edge(const DMesh &M, int e, int k, const double *PVv,
+                                                         double (&pv)[V]) {
+   const int2 vv = M.VerticesOnEdge[e];
+   double a[V], b[V];
+   ldv<V>(a, PVv + (size_t)vv.x * M.K + k);
+   ldv<V>(b, PVv + (size_t)vv.y * M.K + k);
+#pragma unroll
+   for (int q = 0; q < V; ++q) pv[q] = 0.5 * (a[q] + b[q]);
+}
+
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_fE(DMesh M, EdgeArgs P) {
+   const int KV = M.K / V;
+   const OmegaTendConfig &G = P.G;
+   int r0, n;
+   cta_rows(M.NEdgesAll, r0, n);
+   OMEGA_FOR_ROWS(e, k, r0, n, KV, V) {
+      const size_t o    = (size_t)e * M.K + k;
+      const double mask = M.EdgeMask[e];
+      const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
+      const double InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
+      double tend[V] = {0};
+      double us[V], h0[V], h1[V];
+      ldv<V>(us, P.Us + o);
+      ldv<V>(h0, P.Hs + (size_t)cc.x * M.K + k);
+      ldv<V>(h1, P.Hs + (size_t)cc.y * M.K + k);
+      if (G.PVTendencyEnable) {
+         double qe[V], acc[V] = {0};
+         pv_edge<V>(M, e, k, P.PVv, qe);
+         const int ne = M.NEdgesOnEdge[e];
+         for (int j = 0; j < ne; ++j) {
+            const int je   = M.EdgesOnEdge[e * M.MaxEdges2 + j];
+            const double w = M.WeightsOnEdge[e * M.MaxEdges2 + j];
+            double uj[V], fl[V], qj[V];
+            ldv<V>(uj, P.Us + (size_t)je * M.K + k);
+            flux_edge<V>(M, je, k, P.Hs, uj, G.FluxThicknessType, fl);
+            pv_edge<V>(M, je, k, P.PVv, qj);
+#pragma unroll
+            for (int q = 0; q < V; ++q) acc[q] += w * fl[q] * uj[q] * ((qe[q] + qj[q]) * 0.5);
+         }
+#pragma unroll
+         for (int q = 0; q < V; ++q) tend[q] += mask * acc[q];
+      }
+      if (G.KETendencyEnable || G.BottomDragTendencyEnable) {
+         double a0[V], a1[V];
+         ldv<V>(a0, P.KE + (size_t)cc.x * M.K + k);
+         ldv<V>(a1, P.KE + (size_t)cc.y * M.K + k);
+         if (G.KETendencyEnable) {
+#pragma unroll
+            for (int q = 0; q < V; ++q) tend[q] -= mask * (a1[q] - a0[q]) * InvDc;
+         }
+         if (G.BottomDragTendencyEnable) { // applied after the diffusion terms in the reference; the
+            // terms are independent so only the summation order differs (within tolerance)
+            const int KBot = M.K - 1;
+            if (KBot >= k && KBot < k + V) {
+               const int q           = KBot - k;
+               const double VelNorm  = sqrt(a0[q] + a1[q]);
+               const double InvThick = 1.0 / (0.5 * (h0[q] + h1[q]));
+               tend[q] -= mask * G.BottomDragCoeff * VelNorm * InvThick * __ldg(P.URaw + (size_t)e * M.K + KBot);
+            }
+         }
+      }
+      if (G.SSHTendencyEnable) {
+         const double Grav = 9.80665, b0 = M.BottomDepth[cc.x], b1 = M.BottomDepth[cc.y];
+#pragma unroll
+         for (int q = 0; q < V; ++q) tend[q] -= mask * Grav * ((h1[q] - b1) - (h0[q] - b0)) * InvDc;
+      }
+      if (G.VelDiffTendencyEnable) {
+         double d0[V], d1[V], q0[V], q1[V];
+         ldv<V>(d0, P.Div + (size_t)cc.x * M.K + k);
+         ldv<V>(d1, P.Div + (size_t)cc.y * M.K + k);
+         ldv<V>(q0, P.RelVort + (size_t)vv.x * M.K + k);
+         ldv<V>(q1, P.RelVort + (size_t)vv.y * M.K + k);
+         const double cf = mask * G.ViscDel2 * M.MeshScalingDel2[e];
+#pragma unroll
+         for (int q = 0; q < V; ++q) tend[q] += cf * ((d1[q] - d0[q]) * InvDc - (q1[q] - q0[q]) * InvDv);
+      }
+      if (G.VelHyperDiffTendencyEnable) {
+         double d0[V], d1[V], q0[V], q1[V];
+         ldv<V>(d0, P.Del2Div + (size_t)cc.x * M.K + k);
+         ldv<V>(d1, P.Del2Div + (size_t)cc.y * M.K + k);
+         ldv<V>(q0, P.Del2RelVort + (size_t)vv.x * M.K + k);
+         ldv<V>(q1, P.Del2RelVort + (size_t)vv.y * M.K + k);
+         const double cf = mask * G.ViscDel4 * M.MeshScalingDel4[e];
+#pragma unroll
+         for (int q = 0; q < V; ++q)
+            tend[q] -= cf * (G.DivFactor * (d1[q] - d0[q]) * InvDc - (q1[q] - q0[q]) * InvDv);
+      }
+      if (G.WindForcingTendencyEnable && k == 0) {
+         const double InvThick = 1.0 / (0.5 * (h0[0] + h1[0]));
+         tend[0] += mask * InvThick * P.NormalStress[e] / G.Density0;
+      }
+      if (P.MS.Enabled) {
+         const double Grav  = 9.80665;
+         const double Phase = P.MS.Kx * M.XEdge[e] + P.MS.Ky * M.YEdge[e] - P.MS.AngFreq * P.MS.Time;
+         const double Src0  = P.MS.AngFreq * sin(Phase) - 0.5 * P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * sin(2.0 * Phase);
+         const double f     = M.FEdge[e];
+         double Uu = P.MS.Eta0 * ((-f + Grav * P.MS.Kx) * cos(Phase) + Src0);
+         double Vv = P.MS.Eta0 * ((f + Grav * P.MS.Ky) * cos(Phase) + Src0);
+         const double Kx2 = P.MS.Kx * P.MS.Kx, Ky2 = P.MS.Ky * P.MS.Ky;
+         if (G.VelDiffTendencyEnable) {
+            Uu += G.ViscDel2 * P.MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
+            Vv += G.ViscDel2 * P.MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
+         }
+         if (G.VelHyperDiffTendencyEnable) {
+            const double Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
+            Uu -= G.ViscDel4 * P.MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
+            Vv -= G.ViscDel4 * P.MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
+         }
+         const double a   = M.AngleEdge[e];
+         const double src = cos(a) * Uu + sin(a) * Vv;
+#pragma unroll
+         for (int q = 0; q < V; ++q) tend[q] += src;
+      }
+      // epilogue: updateVelocityByTend for the next-level and provisional states
+      double ucur[V], base[V], out[V];
+      if (P.First && P.Ucur == P.Us) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) ucur[q] = us[q];
+      } else if (P.First || !P.Last) {
+         ldp<V>(ucur, P.Ucur + o);
+      }
+      if (!P.First) ldp<V>(base, P.Unext + o);
+#pragma unroll
+      for (int q = 0; q < V; ++q) out[q] = (P.First ? ucur[q] : base[q]) + P.B * tend[q];
+      stv<V>(P.Unext + o, out);
+      if (!P.Last) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) out[q] = ucur[q] + P.A * tend[q];
+         stv<V>(P.Uprov + o, out);
+      }
+   }
+}
+
+// ---------------------------------------------------------------------------
+// host side: one RK4 phase on the fused kernels
+// ---------------------------------------------------------------------------
+static unsigned fused_grid(int NRows, int K, int V) {
+   // a CTA sweeps its row block in iterations of kBlock/KV rows; aim at 8
+   // iterations per CTA but keep >= 4 CTAs per SM (148 SMs) when the mesh allows
+   const int KV          = K / V;
+   const int rowsPerIter = KV >= kBlock ? 1 : kBlock / KV;
+   long long ctas        = ((long long)NRows + 8LL * rowsPerIter - 1) / (8LL * rowsPerIter);
+   const long long want  = 148LL * 4;
+   if (ctas < want) ctas = std::min<long long>(want, ((long long)NRows + rowsPerIter - 1) / rowsPerIter);
+   return (unsigned)std::max<long long>(ctas, 1);
+}
+
+static inline int tix(int Level, int Cur, int NTL) { return (Level + Cur + NTL) % NTL; }
+
+int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
+                    cudaStream_t St) {
+   const DMesh &D           = S->M->D;
+   const OmegaTendConfig &G = S->Cfg;
+   OMEGA_REQUIRE(S->M->MaxEdgesUsed <= kME,
+                 "fused path supports at most 6 edges per cell; use Fused=0");
+   const int V = (D.K & 1) ? 1 : 2, T = S->NTracers;
+   const int ci = X->CurTimeIndex, ni = tix(1, ci, 2);
+   const int tci = X->TracerCurTimeIndex, tni = tix(1, tci, 2);
+   double *Hcur = X->LayerThickness[ci], *Hnext = X->LayerThickness[ni];
+   double *Ucur = X->NormalVelocity[ci], *Unext = X->NormalVelocity[ni];
+   double *TrCur = X->Tracers[tci], *TrNext = X->Tracers[tni];
+   // raw time-level indexing of the reference: with
+   // CurTimeIndex == 1 the "current" raw slot is the NEXT buffer and vice versa
+   const bool swapped = Compat && ci == 1;
+   S->ProvisExchangeSlot = 0;
+   const bool vel4 = G.VelHyperDiffTendencyEnable, tr4 = G.TracerHyperDiffTendencyEnable && T > 0;
+   const bool upw = G.FluxThicknessType || G.FluxTracerType;
+   Launch L{St, &S->Launches};
+   if (G.WindForcingTendencyEnable && Phase == 0) launch_wind_aux(L, D, S->A, G.WindStressInterpType);
+   const int s0 = Phase == 0 ? 0 : 2, s1 = Phase == 0 ? 1 : 3;
+   for (int s = s0; s <= s1; ++s) {
+      // provisional state of stage s lives in P[s % 2] (stage 2 -> slot 0, the exchanged one)
+      const double *Hs = s == 0 ? Hcur : S->P.H[s % 2];
+      const double *Us = s == 0 ? Ucur : S->P.U[s % 2];
+      const double *Trs = s == 0 ? TrCur : S->P.Tr[s % 2];
+      double *Hp = s == 3 ? nullptr : S->P.H[(s + 1) % 2];
+      double *Up = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
+      double *Tp = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
+      const unsigned gc = fused_grid(D.NCellsAll, D.K, V), ge = fused_grid(D.NEdgesAll, D.K, V);
+#define LAUNCH_V(KERNEL, GRID, ...)                                     \
+   do {                                                                 \
+      if (V == 2) KERNEL<2><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);       \
+      else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
+      ++S->Launches;                                                    \
+   } while (0)
+      LAUNCH_V(k_fA, gc, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
+      if (vel4) LAUNCH_V(k_fB, gc, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
+      if (tr4) LAUNCH_V(k_fT2, gc, D, Hs, Trs, T, S->A.Del2Tr);
+      // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
+      // advection reads the stale next-level velocity the edge pass overwrites
+      CellArgs ca;
+      ca.Hs = Hs; ca.Us = Us; ca.Trs = Trs; ca.Del2Tr = S->A.Del2Tr;
+      ca.UTr = (s == 0 && swapped) ? Unext : Us;
+      ca.Hcur = Hcur; ca.Hnext = Hnext; ca.Hprov = Hp;
+      ca.TrCur = TrCur; ca.TrNext = TrNext; ca.TrProv = Tp;
+      ca.A = s < 3 ? C->A[s + 1] : 0.0; ca.B = C->B[s];
+      ca.First = s == 0; ca.Last = s == 3; ca.NTracers = T;
+      ca.WSel = swapped; ca.H2Sel = swapped; ca.FinSel = swapped;
+      ca.FluxDivOn = G.ThicknessFluxTendencyEnable; ca.AdvOn = G.TracerHorzAdvTendencyEnable;
+      ca.DiffOn = G.TracerDiffTendencyEnable; ca.HypOn = tr4;
+      ca.FluxUpwind = G.FluxThicknessType; ca.TrUpwind = G.FluxTracerType;
+      ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
+      ca.MS = manufactured(S, C->StageTime[s]);
+      if (V == 2) {
+         if (upw) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<2, false><<<gc, kBlock, 0, St>>>(D, ca);
+      } else {
+         if (upw) k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, false><<<gc, kBlock, 0, St>>>(D, ca);
+      }
+      ++S->Launches;
+      EdgeArgs ea;
+      ea.Hs = Hs; ea.Us = Us; ea.URaw = (s == 0 && swapped) ? Unext : Us;
+      ea.KE = S->A.KE; ea.Div = S->A.Div; ea.RelVort = S->A.RelVort; ea.PVv = S->A.NormRelVort;
+      ea.Del2Div = S->A.Del2Div; ea.Del2RelVort = S->A.Del2RelVort; ea.NormalStress = S->A.NormalStress;
+      ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
+      ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
+      ea.G = G; ea.MS = ca.MS;
+      LAUNCH_V(k_fE, ge, D, ea);
+#undef LAUNCH_V
+   }
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   return 0;
+}
+
 } // namespace omega

@@ -99,6 +99,8 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    OmegaMesh *M = new OmegaMesh();
    M->Sizes     = *D;
    M->Reordered = Reorder;
+   M->MaxEdgesUsed = 0;
+   for (int c = 0; c < D->NCellsAll; ++c) M->MaxEdgesUsed = std::max(M->MaxEdgesUsed, D->NEdgesOnCell[c]);
    const int NC = D->NCellsAll, NE = D->NEdgesAll, NV = D->NVerticesAll;
    const int ME = D->MaxEdges, ME2 = D->MaxEdges2;
 

@@ -62,6 +62,7 @@ struct OmegaMesh {
    omega::DMesh D;
    OmegaMeshDesc Sizes; // scalar members only (pointers nulled)
    int Reordered;
+   int MaxEdgesUsed; // max NEdgesOnCell over local cells
    // host copies of the permutations (Perm[new] = old) and derived fields (host order)
    std::vector<int> Perm[3], IPerm[3];
    std::vector<double> EdgeSignOnCellH, EdgeSignOnVertexH, EdgeMaskH;
