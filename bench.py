@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""bench.py -- Omega RK4 step throughput on B200 (BASELINE.json metric).
+
+A "step" is one RK4 step (TimeStepper::doStep) of the whole hot path: aux
+state + every tendency term + stage updates (+ halo exchange for N > 1) on the
+workload of BASELINE.json configs[2]: synthetic icosahedral mesh, 655,362 cells
+x 64 levels, 10 tracers, Del2 + Del4 on velocity and tracers, dt = 60 s.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (icosahedral level, levels, tracers, dt seconds, CPU-sample levels)
+    "config3": (8, 64, 10, 60.0, 8),
+    "config2": (6, 64, 2, 240.0, 16),
+    "small": (5, 16, 3, 480.0, 16),
+}
+
+
+def workload_cfg(capi, dc):
+    """Default.yml terms + tracer hyperdiffusion on (configs[2]: 'Del2+Del4')."""
+    return capi.TendConfig.default(ViscDel2=1.0e3 * (dc / 30.0e3) ** 2, ViscDel4=1.2e11 * (dc / 30.0e3) ** 4,
+                                   EddyDiff2=10.0 * (dc / 30.0e3) ** 2, EddyDiff4=1.0e10 * (dc / 30.0e3) ** 4)
+
+
+def build_problem(name, ntasks):
+    from omega_b200 import analytic, capi, decomp, meshgen
+    level, K, T, dt, ks = WORKLOADS[name]
+    m = meshgen.icosahedral(level)
+    m.bottomDepth = analytic.tc5_bottom_depth(m)
+    cfg = workload_cfg(capi, float(np.mean(m.dcEdge)))
+    return m, cfg, K, T, dt, ks
+
+
+class ClockSampler:
+    """nvidia-smi clocks during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out = self.p.communicate()[0]
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_rate(name, steps, warmup, threads=None):
+    """Reference CPU implementation of the same step on the host cores: the
+    reference's own sources over the host Kokkos stand-in (oracle/_ref) when
+    built, else the plain-C port (oracle/).  Bounded sample: the full
+    horizontal mesh with `ks` of the K levels (levels are independent in
+    Omega-0, cost is linear in them)."""
+    from omega_b200 import analytic, capi, decomp
+    from tests import oracle_lib
+    m, cfg, K, T, dt, ks = build_problem(name, 1)
+    L = decomp.build_all(m, 1, ks)[0]
+    h, u, tr = analytic.tc5(L, T)
+    if os.path.exists(oracle_lib.REF):
+        path, kind = oracle_lib.REF, "reference"
+    else:
+        if not os.path.exists(oracle_lib.FAST):
+            oracle_lib.build_oracle()
+        path, kind = oracle_lib.FAST, "port"
+    o = oracle_lib.Oracle(L, cfg, T, lib_path=path)
+    o.make_state(h, u, tr)
+    co = capi.rk_coeffs(capi.RK4, dt)
+    for _ in range(warmup):
+        o.do_step(capi.RK4, co, compat=1)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        o.do_step(capi.RK4, co, compat=1)
+    el = time.perf_counter() - t0
+    o.close()
+    rate = m.nCells * ks * steps / el
+    return {"value": rate, "unit": "cell-layer updates/s", "cores": os.cpu_count(), "kind": kind,
+            "sample": f"{m.nCells} cells x {ks} of {K} levels, {T} tracers, {steps} RK4 step(s), "
+                      f"{el / steps:.2f} s/step, OpenMP over all host cores"}, el / steps, dt, m.nCells, ks
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warm = max(1, min(args.steps, 3)), min(args.warmup, 1)
+    cb, s_per_step, dt, ncells, ks = cpu_reference_rate(args.workload, steps, warm)
+    level, K, T, _, _ = WORKLOADS[args.workload]
+    # seconds per full-depth step = sample time scaled by K/ks
+    full = s_per_step * K / ks
+    line = {"impl": "reference", "metric": "cell-layer updates/s", "value": cb["value"], "unit": "cell-layer updates/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": full * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "sypd": dt / (365.0 * full),
+            "config": {"workload": f"{args.workload}: icosahedral {ncells} cells x {K} levels, {T} tracers, RK4 dt={dt:g}s, "
+                                   "Del2+Del4 (CPU sample scaled by levels)"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "cell-layer updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="config3", choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--unfused", action="store_true", help="time the kernel-per-term path instead")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    from omega_b200 import analytic, capi, decomp, model
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    W = max(args.warmup, 3)
+    K_steps = args.steps
+
+    m, cfg, K, T, dt, ks = build_problem(args.workload, world)
+    co = capi.rk_coeffs(capi.RK4, dt)
+    if world == 1:
+        L = decomp.build_all(m, 1, K)[0]
+        halo = None
+    else:
+        from omega_b200 import parallel
+        L, halo_desc = parallel.local_problem(m, world, rank, K)
+    h, u, tr = analytic.tc5(L, T)
+    mesh = model.HorzMesh(L, reorder=True, device=dev)
+    st = model.Stepper(mesh, cfg, T)
+    state = model.OceanState(mesh, T)
+    state.copyToDevice(h, u, tr)
+    if world > 1:
+        halo = parallel.HaloExchanger(mesh, halo_desc, T)
+
+    fused = not args.unfused
+
+    def step():
+        if world == 1:
+            st.doStep(state, capi.RK4, co, fused=fused, compat=True)
+        else:
+            halo.do_step(st, state, capi.RK4, co, fused=fused, compat=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(W):
+        step()
+    barrier()
+    n0 = st.launch_count()
+    st.lib.omega_stepper_set_profiling(st.h, 1 if fused else 0)
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K_steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    launches = st.launch_count() - n0
+    import ctypes as C
+    kms, kcnt = (C.c_double * 5)(), (C.c_int * 5)()
+    st.lib.omega_stepper_get_profile(st.h, kms, kcnt, 5)
+    st.lib.omega_stepper_set_profiling(st.h, 0)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # sanity: the state must still be finite after W + K steps
+    hh = state.getLayerThickness(0)
+    assert bool(torch.isfinite(hh).all()), "state blew up"
+
+    ncl = m.nCells * K                       # cell-layers of the whole job
+    t_step = ms / 1e3 / K_steps
+    value = ncl / t_step
+    peaks = {}
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk_path):
+        peaks = json.load(open(pk_path))
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    alg_step = 128.0 * (4 + T)               # bytes per cell-layer per RK4 step
+
+    # ---- e2e: HOST buffers in, HOST buffers out, every step -----------------
+    e2e = None
+    if not args.no_e2e and world == 1:
+        hp = [torch.from_numpy(a).pin_memory() for a in (h, u, tr)]
+        outp = [torch.empty_like(x).pin_memory() for x in hp]
+        ne = min(K_steps, 5)
+
+        def e2e_step():
+            mesh.to_device(capi.ON_CELL, hp[0].numpy(), state.getLayerThickness(0))
+            mesh.to_device(capi.ON_EDGE, hp[1].numpy(), state.getNormalVelocity(0))
+            mesh.to_device(capi.ON_CELL, hp[2].numpy(), state.getTracers(0))
+            st.doStep(state, capi.RK4, co, fused=fused, compat=True)
+            mesh.to_host(capi.ON_CELL, state.getLayerThickness(0), outp[0].numpy())
+            mesh.to_host(capi.ON_EDGE, state.getNormalVelocity(0), outp[1].numpy())
+            mesh.to_host(capi.ON_CELL, state.getTracers(0), outp[2].numpy())
+
+        e2e_step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(ne):
+            e2e_step()
+        torch.cuda.synchronize()
+        te = (time.perf_counter() - t0) / ne
+        nbytes = sum(x.numel() * 8 for x in hp)
+        e2e = {"value": ncl / te, "unit": "cell-layer updates/s", "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": nbytes, "ms_per_step": te * 1e3, "steps": ne,
+               "api": "omega_field_to_device x3 + omega_stepper_do_step + omega_field_to_host x3 (pinned host state)"}
+
+    if rank != 0:
+        return
+    names = ["fA_cell_vertex_aux", "fB_del2_aux", "fT2_tracer_del2", "fC_cell_thick_tracers", "fE_edge_velocity"]
+    kern = {n: {"ms_per_launch": kms[i] / kcnt[i], "launches": kcnt[i], "share": kms[i] / ms}
+            for i, n in enumerate(names) if kcnt[i]}
+    roofline = None
+    if fused and kcnt[3]:
+        # dominant kernel fC: per launch it owns the (1+T) cell-centred fields of one stage
+        # = (3+5+5+3)/4 * 8 * (1+T) bytes per cell-layer on average
+        cl_local = mesh.NAll[0] * K
+        alg_fc = 32.0 * (1 + T) * cl_local
+        ach = alg_fc / (kms[3] / kcnt[3] * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "k_fC", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg_fc}
+    ach_step = alg_step * ncl / world / t_step / 1e9
+    line = {"metric": "cell-layer updates/s", "value": value, "unit": "cell-layer updates/s", "n_gpus": world,
+            "steps": K_steps, "warmup": W, "ms_per_step": t_step * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "sypd": dt / (365.0 * t_step),
+            "config": {"workload": f"{args.workload}: icosahedral {m.nCells} cells x {K} levels, {T} tracers, RK4 dt={dt:g}s, "
+                                   "Del2+Del4 on velocity and tracers, TC5-style state",
+                       "path": "fused" if fused else "kernel-per-term", "parallelism": f"domain decomposition x{world}",
+                       "l2": "state per step (>= 5 GB) exceeds the 126 MB L2; no flush needed"},
+            "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
+            "roofline_step": {"bound": "hbm", "achieved": ach_step, "peak": peak, "unit": "GB/s", "frac": ach_step / peak,
+                              "algorithmic_bytes_per_cell_layer_step": alg_step, "per_gpu": True},
+            "kernels": kern}
+    if world == 1 and not args.no_cpu_baseline:
+        cb, *_ = cpu_reference_rate(args.workload, 1, 0)
+        line["cpu_baseline"] = cb
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

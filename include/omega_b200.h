@@ -230,6 +230,11 @@ int omega_state_rotate(OmegaStateArrays *State);
 int omega_stepper_provis_arrays(OmegaStepper *Stepper, double **H, double **U, double **Tr);
 /* kernels launched by this stepper since creation (bench gpu_launches) */
 long long omega_stepper_launch_count(const OmegaStepper *S);
+/* per-kernel CUDA-event timing of the fused pipeline: sums in ms and launch
+ * counts per kernel kind (0 fA, 1 fB, 2 fT2, 3 fC, 4 fE) since the last call;
+ * get_profile synchronises the device. */
+int omega_stepper_set_profiling(OmegaStepper *S, int Enable);
+int omega_stepper_get_profile(OmegaStepper *S, double *Ms, int *Counts, int NKinds);
 
 /* ---- Halo (src/base/Halo.h:62-917, src/base/Halo.cpp:455-757) ----------- */
 /* Exchange lists for one rank, host order: for each neighbour n and element

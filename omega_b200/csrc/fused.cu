@@ -597,6 +597,27 @@ static unsigned fused_grid(int NRows, int K, int V) {
    return (unsigned)std::max<long long>(ctas, 1);
 }
 
+struct ScopedTimer {
+   OmegaStepper *S;
+   cudaStream_t St;
+   OmegaStepper::Timed T;
+   bool On;
+   ScopedTimer(OmegaStepper *S_, cudaStream_t St_, int Kind) : S(S_), St(St_), On(S_->Profiling != 0) {
+      if (On) {
+         T.Kind = Kind;
+         cudaEventCreate(&T.Start);
+         cudaEventCreate(&T.Stop);
+         cudaEventRecord(T.Start, St);
+      }
+   }
+   ~ScopedTimer() {
+      if (On) {
+         cudaEventRecord(T.Stop, St);
+         S->Events.push_back(T);
+      }
+   }
+};
+
 static inline int tix(int Level, int Cur, int NTL) { return (Level + Cur + NTL) % NTL; }
 
 int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
@@ -629,15 +650,16 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       double *Up = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
       double *Tp = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
       const unsigned gc = fused_grid(D.NCellsAll, D.K, V), ge = fused_grid(D.NEdgesAll, D.K, V);
-#define LAUNCH_V(KERNEL, GRID, ...)                                     \
+#define LAUNCH_V(KIND, KERNEL, GRID, ...)                               \
    do {                                                                 \
+      ScopedTimer tm_(S, St, KIND);                                     \
       if (V == 2) KERNEL<2><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);       \
       else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
       ++S->Launches;                                                    \
    } while (0)
-      LAUNCH_V(k_fA, gc, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
-      if (vel4) LAUNCH_V(k_fB, gc, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
-      if (tr4) LAUNCH_V(k_fT2, gc, D, Hs, Trs, T, S->A.Del2Tr);
+      LAUNCH_V(kFA, k_fA, gc, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
+      if (vel4) LAUNCH_V(kFB, k_fB, gc, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
+      if (tr4) LAUNCH_V(kFT2, k_fT2, gc, D, Hs, Trs, T, S->A.Del2Tr);
       // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
       // advection reads the stale next-level velocity the edge pass overwrites
       CellArgs ca;
@@ -653,12 +675,15 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.FluxUpwind = G.FluxThicknessType; ca.TrUpwind = G.FluxTracerType;
       ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
       ca.MS = manufactured(S, C->StageTime[s]);
+      {
+      ScopedTimer tm_(S, St, kFC);
       if (V == 2) {
          if (upw) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<2, false><<<gc, kBlock, 0, St>>>(D, ca);
       } else {
          if (upw) k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, false><<<gc, kBlock, 0, St>>>(D, ca);
       }
       ++S->Launches;
+      }
       EdgeArgs ea;
       ea.Hs = Hs; ea.Us = Us; ea.URaw = (s == 0 && swapped) ? Unext : Us;
       ea.KE = S->A.KE; ea.Div = S->A.Div; ea.RelVort = S->A.RelVort; ea.PVv = S->A.NormRelVort;
@@ -666,7 +691,7 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
       ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
       ea.G = G; ea.MS = ca.MS;
-      LAUNCH_V(k_fE, ge, D, ea);
+      LAUNCH_V(kFE, k_fE, ge, D, ea);
 #undef LAUNCH_V
    }
    OMEGA_CUDA_CHECK(cudaGetLastError());

@@ -59,6 +59,7 @@ int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int 
    S->NTracers = NTracers;
    S->Launches = 0;
    S->ProvisExchangeSlot = 0;
+   S->Profiling = 0;
    std::memset(&S->A, 0, sizeof(S->A));
    std::memset(&S->T, 0, sizeof(S->T));
    std::memset(&S->P, 0, sizeof(S->P));
@@ -150,6 +151,30 @@ int omega_stepper_set_wind_stress(OmegaStepper *S, const double *Zonal, const do
 }
 
 long long omega_stepper_launch_count(const OmegaStepper *S) { return S ? S->Launches : 0; }
+
+int omega_stepper_set_profiling(OmegaStepper *S, int Enable) {
+   OMEGA_REQUIRE(S, "omega_stepper_set_profiling: null argument");
+   S->Profiling = Enable;
+   return 0;
+}
+
+// Sums (ms) and launch counts per fused kernel kind since the last call;
+// synchronises the device. Kinds: 0 fA, 1 fB, 2 fT2, 3 fC, 4 fE.
+int omega_stepper_get_profile(OmegaStepper *S, double *Ms, int *Counts, int NKinds) {
+   OMEGA_REQUIRE(S && Ms && Counts && NKinds >= kNumFused, "omega_stepper_get_profile: bad argument");
+   OMEGA_CUDA_CHECK(cudaDeviceSynchronize());
+   for (int i = 0; i < NKinds; ++i) { Ms[i] = 0; Counts[i] = 0; }
+   for (auto &t : S->Events) {
+      float ms = 0;
+      OMEGA_CUDA_CHECK(cudaEventElapsedTime(&ms, t.Start, t.Stop));
+      Ms[t.Kind] += ms;
+      Counts[t.Kind] += 1;
+      cudaEventDestroy(t.Start);
+      cudaEventDestroy(t.Stop);
+   }
+   S->Events.clear();
+   return 0;
+}
 
 // ---- AuxiliaryState ---------------------------------------------------------
 int omega_aux_compute_mom(OmegaStepper *S, const double *H, const double *U, void *Stream) {

@@ -19,9 +19,14 @@ struct OmegaStepper {
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
    std::vector<void *> Allocs;
+   // optional per-kernel CUDA-event timing of the fused pipeline (bench roofline)
+   int Profiling;
+   struct Timed { int Kind; cudaEvent_t Start, Stop; };
+   std::vector<Timed> Events;
 };
 
 namespace omega {
+enum FusedKernel { kFA = 0, kFB = 1, kFT2 = 2, kFC = 3, kFE = 4, kNumFused = 5 };
 int stepper_alloc(OmegaStepper *S, double **p, size_t n);
 ManufacturedParams manufactured(const OmegaStepper *S, double Time);
 int ensure_htr(OmegaStepper *S);
