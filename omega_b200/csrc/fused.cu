@@ -26,6 +26,7 @@
 // src/timeStepping/TimeStepper.cpp:378-524, src/ocn/Tendencies.cpp:257-486,
 // src/ocn/AuxiliaryState.cpp:60-185 and the functors cited at each block.
 #include <algorithm>
+#include <cstdlib>
 
 #include "kernel_util.cuh"
 #include "omega_dev.h"
@@ -417,6 +418,154 @@ k_fC(DMesh M, CellArgs P) {
 
 
 // ---------------------------------------------------------------------------
+// fC, centred-flux variant (the Default.yml configuration and every BASELINE
+// workload): same arithmetic as k_fC above with the per-edge work of one cell
+// folded into ONE coefficient per (edge, level):
+//    tend_l = phi_l(self)*S0 + sum_j E_j*phi_l(nbr_j)
+//           + d2_l(self)*SH  - sum_j ch_j*d2_l(nbr_j)
+//    E_j  = 0.5*h(nbr_j)*w_j - D_j,   S0 = sum_j (0.5*h(self)*w_j + D_j)
+//    w_j  = mask*dv*sign*u/A,         D_j = -(k2/A)*mask*sign*(dv/dc)*mean_h_j*sgn_j
+// so a thread keeps 6*(V+1) doubles for all tracers instead of 6*(2V+2); that
+// is what lets 16 cells (512 threads) share one SM's L1 in lockstep.  The
+// reassociation moves results by a few ulp of the largest term (parity tests
+// hold the 1e-12 bound on every case).
+// ---------------------------------------------------------------------------
+constexpr int kCellThreads = 512;
+
+template <int V>
+__global__ void __launch_bounds__(kCellThreads, 1)
+k_fC_center(DMesh M, CellArgs P) {
+   const int KV = M.K / V;
+   const size_t CS = (size_t)M.NCellsSize * M.K;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      const double InvA = 1.0 / M.AreaCell[c];
+      const int ne      = M.NEdgesOnCell[c];
+      const size_t o    = (size_t)c * M.K + k;
+      double hs[V];
+      ldv<V>(hs, P.Hs + o);
+      double E[kME][V], ch[kME], S0[V] = {0}, SH = 0.0, hT[V] = {0};
+      int nb[kME];
+      const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = P.HypOn ? P.EddyDiff4 * InvA : 0.0;
+#pragma unroll
+      for (int j = 0; j < kME; ++j) {
+         if (j < ne) {
+            const int e       = M.EdgesOnCell[c * M.MaxEdges + j];
+            const int2 cc     = M.CellsOnEdge[e];
+            const bool self0  = cc.x == c;
+            nb[j]             = self0 ? cc.y : cc.x;
+            const double sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
+            const double mask = M.EdgeMask[e], dve = M.DvEdge[e];
+            const double rdc  = dve / M.DcEdge[e];
+            const double sgn  = self0 ? -1.0 : 1.0;
+            const double cd   = -k2 * (mask * sg * (M.MeshScalingDel2[e] * rdc)) * sgn;
+            ch[j]             = k4 * (mask * sg * (M.MeshScalingDel4[e] * rdc)) * sgn;
+            SH += ch[j];
+            double hn[V], us[V], ut[V];
+            ldv<V>(hn, P.Hs + (size_t)nb[j] * M.K + k);
+            ldv<V>(us, P.Us + (size_t)e * M.K + k);
+            if (P.UTr == P.Us) {
+#pragma unroll
+               for (int q = 0; q < V; ++q) ut[q] = us[q];
+            } else {
+               ldv<V>(ut, P.UTr + (size_t)e * M.K + k);
+            }
+            const double cf = dve * sg;
+            const double wa = P.AdvOn ? mask * dve * sg : 0.0;
+#pragma unroll
+            for (int q = 0; q < V; ++q) {
+               const double mean = 0.5 * (hs[q] + hn[q]);
+               hT[q] += cf * mean * us[q] * InvA;
+               const double w = wa * ut[q] * InvA;
+               const double D = cd * mean;
+               E[j][q]        = 0.5 * hn[q] * w - D;
+               S0[q] += 0.5 * hs[q] * w + D;
+            }
+         }
+      }
+      if (!P.FluxDivOn) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) hT[q] = 0.0;
+      }
+      if (P.MS.Enabled) {
+         const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
+         const double src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
+                                         P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * cos(2.0 * Phase));
+#pragma unroll
+         for (int q = 0; q < V; ++q) hT[q] += src;
+      }
+      double hcur[V], hnext_old[V], hnext[V], hprov[V];
+      if (P.First && P.Hcur == P.Hs) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) hcur[q] = hs[q];
+      } else {
+         ldp<V>(hcur, P.Hcur + o);
+      }
+      if (!P.First || P.WSel) ldp<V>(hnext_old, P.Hnext + o);
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         hnext[q] = (P.First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
+         hprov[q] = hcur[q] + P.A * hT[q];
+      }
+      stv<V>(P.Hnext + o, hnext);
+      if (!P.Last) stv<V>(P.Hprov + o, hprov);
+      // hx: stage 0 -> weight thickness; last stage -> final thickness; else unused
+      double hx[V], h2[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+         hx[q] = P.First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
+         h2[q] = P.H2Sel ? hnext[q] : hcur[q];
+      }
+      for (int l = 0; l < P.NTracers; ++l) {
+         const double *T  = P.Trs + l * CS;
+         const double *D2 = P.Del2Tr + l * CS;
+         double ts[V], d2s[V], tend[V];
+         ldv<V>(ts, T + o);
+         if (P.HypOn) ldv<V>(d2s, D2 + o);
+#pragma unroll
+         for (int q = 0; q < V; ++q) tend[q] = ts[q] * S0[q] + (P.HypOn ? d2s[q] * SH : 0.0);
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            if (j < ne) {
+               const size_t on = (size_t)nb[j] * M.K + k;
+               double tn[V];
+               ldv<V>(tn, T + on);
+#pragma unroll
+               for (int q = 0; q < V; ++q) tend[q] += E[j][q] * tn[q];
+               if (P.HypOn) {
+                  double d2n[V];
+                  ldv<V>(d2n, D2 + on);
+#pragma unroll
+                  for (int q = 0; q < V; ++q) tend[q] -= ch[j] * d2n[q];
+               }
+            }
+         }
+         double tcur[V], acc[V], out[V];
+         if (P.First && P.TrCur == P.Trs) {
+#pragma unroll
+            for (int q = 0; q < V; ++q) tcur[q] = ts[q];
+         } else if (P.First || !P.Last) {
+            ldp<V>(tcur, P.TrCur + l * CS + o);
+         }
+         if (!P.First) ldp<V>(acc, P.TrNext + l * CS + o);
+#pragma unroll
+         for (int q = 0; q < V; ++q) {
+            const double base = P.First ? tcur[q] * hx[q] : acc[q];
+            out[q]            = base + P.B * tend[q];
+            if (P.Last) out[q] = out[q] / hx[q];
+         }
+         stv<V>(P.TrNext + l * CS + o, out);
+         if (!P.Last) {
+#pragma unroll
+            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / hprov[q];
+            stv<V>(P.TrProv + l * CS + o, out);
+         }
+      }
+   }
+}
+
+// ---------------------------------------------------------------------------
 // fE: edge pass.  PotentialVortHAdvOnEdge, KEGradOnEdge, SSHGradOnEdge,
 // VelocityDiffusionOnEdge, VelocityHyperDiffOnEdge, WindForcingOnEdge,
 // BottomDragOnEdge (TendencyTerms.h:81-334) + the manufactured source, with
@@ -586,15 +735,21 @@ k_fE(DMesh M, EdgeArgs P) {
 // ---------------------------------------------------------------------------
 // host side: one RK4 phase on the fused kernels
 // ---------------------------------------------------------------------------
-static unsigned fused_grid(int NRows, int K, int V) {
+static int env_int(const char *name, int dflt) {
+   const char *v = getenv(name);
+   return v ? atoi(v) : dflt;
+}
+
+static unsigned fused_grid(int NRows, int K, int V, int Threads = kBlock, int Iters = 1) {
    // a CTA sweeps its row block in iterations of kBlock/KV rows; aim at 8
    // iterations per CTA but keep >= 4 CTAs per SM (148 SMs) when the mesh allows
+   // one sweep iteration per CTA: consecutive CTAs (same wave, different SMs) then work on
+   // SFC-adjacent row groups at the same time and meet in L2 (profiles/r01: a CTA that
+   // sweeps 8 groups re-reads its neighbours' rows from DRAM, 1.85x read amplification)
    const int KV          = K / V;
-   const int rowsPerIter = KV >= kBlock ? 1 : kBlock / KV;
-   long long ctas        = ((long long)NRows + 8LL * rowsPerIter - 1) / (8LL * rowsPerIter);
-   const long long want  = 148LL * 4;
-   if (ctas < want) ctas = std::min<long long>(want, ((long long)NRows + rowsPerIter - 1) / rowsPerIter);
-   return (unsigned)std::max<long long>(ctas, 1);
+   const int rowsPerIter = KV >= Threads ? 1 : Threads / KV;
+   const long long per = (long long)rowsPerIter * std::max(Iters, 1);
+   return (unsigned)std::max<long long>(((long long)NRows + per - 1) / per, 1);
 }
 
 struct ScopedTimer {
@@ -649,7 +804,13 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       double *Hp = s == 3 ? nullptr : S->P.H[(s + 1) % 2];
       double *Up = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
       double *Tp = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
-      const unsigned gc = fused_grid(D.NCellsAll, D.K, V), ge = fused_grid(D.NEdgesAll, D.K, V);
+      // sweep iterations per CTA (tuning knobs, defaults from profiles/r01 measurements)
+      const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 1),
+                       itT = env_int("OMEGA_ITERS_T2", 1), itC = env_int("OMEGA_ITERS_C", 1),
+                       itE = env_int("OMEGA_ITERS_E", 8);
+      const unsigned gc = fused_grid(D.NCellsAll, D.K, V, kBlock, itC), ge = fused_grid(D.NEdgesAll, D.K, V, kBlock, itE);
+      const unsigned gA = fused_grid(D.NCellsAll, D.K, V, kBlock, itA), gB = fused_grid(D.NCellsAll, D.K, V, kBlock, itB),
+                     gT = fused_grid(D.NCellsAll, D.K, V, kBlock, itT);
 #define LAUNCH_V(KIND, KERNEL, GRID, ...)                               \
    do {                                                                 \
       ScopedTimer tm_(S, St, KIND);                                     \
@@ -657,9 +818,9 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
       ++S->Launches;                                                    \
    } while (0)
-      LAUNCH_V(kFA, k_fA, gc, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
-      if (vel4) LAUNCH_V(kFB, k_fB, gc, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
-      if (tr4) LAUNCH_V(kFT2, k_fT2, gc, D, Hs, Trs, T, S->A.Del2Tr);
+      LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
+      if (vel4) LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
+      if (tr4) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
       // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
       // advection reads the stale next-level velocity the edge pass overwrites
       CellArgs ca;
@@ -677,10 +838,11 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.MS = manufactured(S, C->StageTime[s]);
       {
       ScopedTimer tm_(S, St, kFC);
+      const unsigned gcc = fused_grid(D.NCellsAll, D.K, V, kCellThreads, itC);
       if (V == 2) {
-         if (upw) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<2, false><<<gc, kBlock, 0, St>>>(D, ca);
+         if (upw) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC_center<2><<<gcc, kCellThreads, 0, St>>>(D, ca);
       } else {
-         if (upw) k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, false><<<gc, kBlock, 0, St>>>(D, ca);
+         if (upw) k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC_center<1><<<gcc, kCellThreads, 0, St>>>(D, ca);
       }
       ++S->Launches;
       }
