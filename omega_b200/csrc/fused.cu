@@ -432,8 +432,8 @@ k_fC(DMesh M, CellArgs P) {
 // ---------------------------------------------------------------------------
 constexpr int kCellThreads = 512;
 
-template <int V>
-__global__ void __launch_bounds__(kCellThreads, 1)
+template <int V, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
 k_fC_center(DMesh M, CellArgs P) {
    const int KV = M.K / V;
    const size_t CS = (size_t)M.NCellsSize * M.K;
@@ -838,11 +838,23 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.MS = manufactured(S, C->StageTime[s]);
       {
       ScopedTimer tm_(S, St, kFC);
-      const unsigned gcc = fused_grid(D.NCellsAll, D.K, V, kCellThreads, itC);
-      if (V == 2) {
-         if (upw) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC_center<2><<<gcc, kCellThreads, 0, St>>>(D, ca);
-      } else {
-         if (upw) k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC_center<1><<<gcc, kCellThreads, 0, St>>>(D, ca);
+      const int variant = env_int("OMEGA_FC_VARIANT", 3);
+      if (upw) {
+         if (V == 2) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca);
+      } else if (V == 1) {
+         k_fC_center<1, 512, 1><<<fused_grid(D.NCellsAll, D.K, 1, 512, itC), 512, 0, St>>>(D, ca);
+      } else if (variant == 0) {
+         k_fC_center<2, 512, 1><<<fused_grid(D.NCellsAll, D.K, 2, 512, itC), 512, 0, St>>>(D, ca);
+      } else if (variant == 1) { // scalar levels, 2 CTAs of 512 (<= 64 regs)
+         k_fC_center<1, 512, 2><<<fused_grid(D.NCellsAll, D.K, 1, 512, itC), 512, 0, St>>>(D, ca);
+      } else if (variant == 2) { // 3 CTAs of 256 (<= 85 regs)
+         k_fC_center<2, 256, 3><<<fused_grid(D.NCellsAll, D.K, 2, 256, itC), 256, 0, St>>>(D, ca);
+      } else if (variant == 3) { // 1024 threads (<= 64 regs)
+         k_fC_center<2, 1024, 1><<<fused_grid(D.NCellsAll, D.K, 2, 1024, itC), 1024, 0, St>>>(D, ca);
+      } else if (variant == 4) { // scalar levels, 1 CTA of 1024
+         k_fC_center<1, 1024, 1><<<fused_grid(D.NCellsAll, D.K, 1, 1024, itC), 1024, 0, St>>>(D, ca);
+      } else { // 2 CTAs of 256, V=2 (<= 128 regs)
+         k_fC_center<2, 256, 2><<<fused_grid(D.NCellsAll, D.K, 2, 256, itC), 256, 0, St>>>(D, ca);
       }
       ++S->Launches;
       }
