@@ -10,6 +10,11 @@
 #include <array>
 #include <cmath>
 #include <cstddef>
+#include <cstdint>
+#include <functional>
+#include <iostream>
+#include <map>
+#include <vector>
 #include <cstring>
 #include <memory>
 #include <string>
