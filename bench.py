@@ -99,8 +99,8 @@ def cpu_reference_rate(name, steps, warmup, threads=None):
     m, cfg, K, T, dt, ks = build_problem(name, 1)
     L = decomp.build_all(m, 1, ks)[0]
     h, u, tr = analytic.tc5(L, T)
-    if os.path.exists(oracle_lib.REF):
-        path, kind = oracle_lib.REF, "reference"
+    if os.path.exists(oracle_lib.REF_FAST) and ks % 8 == 0:
+        path, kind = oracle_lib.REF_FAST, "reference"
     else:
         if not os.path.exists(oracle_lib.FAST):
             oracle_lib.build_oracle()

@@ -17,6 +17,7 @@ ORACLE_DIR = os.path.join(ROOT, "oracle")
 STRICT = os.path.join(ORACLE_DIR, "libomega_oracle.so")
 FAST = os.path.join(ORACLE_DIR, "libomega_oracle_fast.so")
 REF = os.path.join(ORACLE_DIR, "_ref", "libomega_ref.so")
+REF_FAST = os.path.join(ORACLE_DIR, "_ref", "libomega_ref_fast.so")  # -O3, OMEGA_VECTOR_LENGTH=8
 
 
 def build_oracle():
