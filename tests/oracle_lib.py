@@ -125,3 +125,25 @@ class Oracle:
     # generic operators for the known-answer tests
     def op(self, name, src, dst, *extra):
         getattr(self.lib, "oracle_op_" + name)(self.h, _p(src), *extra, _p(dst))
+
+    # ---- phase-wise stepping for the multi-rank emulation (C oracle only) ----
+    def step_phase(self, stepper, coeffs, phase, compat=1):
+        self.lib.oracle_stepper_step_phase(self.h, stepper, C.byref(self.state), C.byref(coeffs), phase, 0, compat)
+
+    def exchange_arrays(self, stepper, phase):
+        """numpy views (host order) of the arrays to halo-exchange after `phase`:
+        [(kind name, array)]"""
+        ptrs = (_dp * 3)()
+        elems, nouter, n = (C.c_int * 3)(), (C.c_int * 3)(), C.c_int()
+        self.lib.oracle_stepper_exchange_list(self.h, stepper, C.byref(self.state), phase, ptrs, elems, nouter, C.byref(n))
+        out = []
+        for i in range(n.value):
+            kind = int(elems[i])
+            has_t = nouter[i] > 1 or (i == 2)
+            if i == 2 and self.T == 0:
+                continue
+            out.append((("Cell", "Edge", "Vertex")[kind], self._view(ptrs[i], kind, 1, 1 if i == 2 else 0)))
+        return out
+
+    def rotate(self):
+        self.lib.oracle_state_rotate(C.byref(self.state))

@@ -175,3 +175,67 @@ def test_rk4_100_steps_state_parity():
     for fused in (False, True):
         errs = run_steps(L, cfg, init, dt, capi.RK4, 100, fused=fused, compat=True)
         assert max(errs) <= TOL_STATE, (fused, errs)
+
+
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("ntasks", [2, 3])
+def test_multirank_emulated_on_one_gpu(ntasks, fused):
+    """N ranks' partitions stepped on one GPU in one process: the library's halo
+    pack/unpack kernels, exchange lists in device order and phase-split stepping,
+    with device-to-device copies standing in for NCCL.  Checked against the
+    1-rank oracle on every local element (HaloWidth 4: see
+    test_multirank_cpu.test_reference_needs_halo_width_4_with_del4)."""
+    import ctypes as C
+    from omega_b200 import analytic, decomp, model, parallel
+    from tests.oracle_lib import Oracle
+    K, T, nsteps = 4, 2, 3
+    mesh_g = cases.sphere_mesh(3)
+    L1, cfg, (h, u, tr), dt = cases.sphere_case(3, K, T)
+    ref = Oracle(L1, cfg, T)
+    ref.make_state(h, u, tr)
+    for s in range(nsteps):
+        ref.do_step(capi.RK4, capi.rk_coeffs(capi.RK4, dt, t0=s * dt))
+    gh, gu, gt = ref.current()
+    cell_of, edge_of = L1.CellID[:-1] - 1, L1.EdgeID[:-1] - 1
+    H = np.empty_like(gh[:-1]); H[cell_of] = gh[:-1]
+    U = np.empty_like(gu[:-1]); U[edge_of] = gu[:-1]
+    TR = np.empty_like(gt[:, :-1]); TR[:, cell_of] = gt[:, :-1]
+    locs = decomp.build_all(mesh_g, ntasks, K, 4)
+    lists = parallel.build_halo_lists(locs)
+    ranks = []
+    for L, hl in zip(locs, lists):
+        m = model.HorzMesh(L, reorder=True)
+        st, state = model.Stepper(m, cfg, T), model.OceanState(m, T)
+        state.copyToDevice(*analytic.tc5(L, T))
+        ranks.append((L, m, st, state, parallel.HaloExchanger(m, hl, T)))
+    for s in range(nsteps):
+        co = capi.rk_coeffs(capi.RK4, dt, t0=s * dt)
+        for p in range(2):
+            rounds = []
+            for L, m, st, state, ex in ranks:
+                st.stepPhase(state, capi.RK4, co, p, fused=fused, compat=True)
+                ptrs = ex.exchange_list(st, state, capi.RK4, p)
+                ex.pack(ptrs)
+                rounds.append(ptrs)
+            # transport: my send segment to nbr is nbr's recv segment from me
+            segs = [{} for _ in ranks]
+            for t, (rk, ptrs) in enumerate(zip(ranks, rounds)):
+                for i, (nbr, sb, rb) in enumerate(rk[4].segments(ptrs)):
+                    segs[t].setdefault(nbr, []).append((sb, rb))
+            for t in range(len(ranks)):
+                for nbr, pairs in segs[t].items():
+                    for (sb, _), (_, rb) in zip(pairs, segs[nbr][t]):
+                        rb.copy_(sb)
+            for (L, m, st, state, ex), ptrs in zip(ranks, rounds):
+                ex.unpack(ptrs)
+        for L, m, st, state, ex in ranks:
+            m.lib.omega_state_rotate(C.byref(state.c))
+    worst = 0.0
+    for L, m, st, state, ex in ranks:
+        lh, lu, lt = state.copyToHost(0)
+        ci, ei = L.CellID[:L.NCellsAll] - 1, L.EdgeID[:L.NEdgesAll] - 1
+        for a, b in ((lh[:L.NCellsAll], H[ci]), (lu[:L.NEdgesAll], U[ei]), (lt[:, :L.NCellsAll], TR[:, ci])):
+            worst = max(worst, rel_l2(a, b))
+        ex.close(); st.close(); m.close()
+    ref.close()
+    assert worst <= TOL_STATE, worst
