@@ -178,7 +178,9 @@ def main():
         halo = None
     else:
         from omega_b200 import parallel
-        L, halo_desc = parallel.local_problem(m, world, rank, K)
+        # HaloWidth 4: with the biharmonic terms on, the default 3 makes the reference algorithm itself
+        # partition dependent (tests/test_multirank_cpu.py::test_reference_needs_halo_width_4_with_del4)
+        L, halo_desc = parallel.local_problem(m, world, rank, K, halo_width=4)
     h, u, tr = analytic.tc5(L, T)
     mesh = model.HorzMesh(L, reorder=True, device=dev)
     st = model.Stepper(mesh, cfg, T)
@@ -266,6 +268,10 @@ def main():
                "d2h_bytes_per_step": nbytes, "ms_per_step": te * 1e3, "steps": ne,
                "api": "omega_field_to_device x3 + omega_stepper_do_step + omega_field_to_host x3 (pinned host state)"}
 
+    if world > 1:
+        bytes_round = halo.bytes_per_round
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     names = ["fA_cell_vertex_aux", "fB_del2_aux", "fT2_tracer_del2", "fC_cell_thick_tracers", "fE_edge_velocity"]
@@ -294,6 +300,10 @@ def main():
             "roofline_step": {"bound": "hbm", "achieved": ach_step, "peak": peak, "unit": "GB/s", "frac": ach_step / peak,
                               "algorithmic_bytes_per_cell_layer_step": alg_step, "per_gpu": True},
             "kernels": kern}
+    if world > 1:
+        # two exchange rounds per RK4 step; bytes one rank sends per round, against NVLink 900 GB/s/direction
+        line["halo"] = {"rounds_per_step": 2, "send_bytes_per_round_rank0": bytes_round, "halo_width": 4,
+                        "transport": "NCCL send/recv (torch.distributed batch_isend_irecv), pack/unpack CUDA kernels"}
     if world == 1 and not args.no_cpu_baseline:
         cb, *_ = cpu_reference_rate(args.workload, 1, 0)
         line["cpu_baseline"] = cb
