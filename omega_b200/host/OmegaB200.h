@@ -1,0 +1,226 @@
+// OmegaB200.h -- C++ host mirror of the reference's hot-path classes over the
+// C ABI of include/omega_b200.h.  Same class names, method names, argument
+// meaning and error behaviour (int 0 = ok / abort on unusable state) as
+// components/omega: HorzMesh (src/ocn/HorzMesh.h), OceanState
+// (src/ocn/OceanState.h:113-129), Tracers (src/ocn/Tracers.h),
+// AuxiliaryState (src/ocn/AuxiliaryState.h:74-82), Tendencies
+// (src/ocn/Tendencies.h:73-102), TimeStepper (src/timeStepping/TimeStepper.h:82-84),
+// Halo (src/base/Halo.h:768-771).  Header-only; link libomega_b200.so.
+// Arrays are device allocations in DEVICE order behind a small View-like
+// handle (pointer + extents + label), the role Kokkos::View plays upstream.
+#pragma once
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "omega_b200.h"
+
+namespace OMEGA {
+
+using I4   = int;
+using R8   = double;
+using Real = double;
+
+[[noreturn]] inline void abortError(const std::string &Msg) { // ABORT_ERROR, src/infra/Error.h:207-210
+   std::fprintf(stderr, "[omega_b200] %s: %s\n", Msg.c_str(), omega_last_error());
+   std::abort();
+}
+#define OMEGA_B200_CHECK(call, what) \
+   do { if ((call) != 0) ::OMEGA::abortError(what); } while (0)
+
+enum MeshElement { OnCell = OMEGA_ON_CELL, OnEdge = OMEGA_ON_EDGE, OnVertex = OMEGA_ON_VERTEX };
+
+/// Device array handle: ref-counted, zero-initialised (like Kokkos::View)
+template <int Rank> class DeviceArray {
+ public:
+   DeviceArray() = default;
+   DeviceArray(const std::string &Label, std::initializer_list<long> Ext) : Label_(Label) {
+      int i = 0;
+      Size_ = 1;
+      for (long e : Ext) { Ext_[i++] = e; Size_ *= e; }
+      void *p = nullptr;
+      OMEGA_B200_CHECK(omega_dev_alloc(&p, (unsigned long long)Size_ * sizeof(double)), "DeviceArray alloc " + Label);
+      Data_ = std::shared_ptr<double>(static_cast<double *>(p), [](double *q) { omega_dev_free(q); });
+   }
+   /// non-owning alias of library-owned memory (tendency / aux arrays)
+   DeviceArray(const std::string &Label, double *Ptr, std::initializer_list<long> Ext) : Label_(Label) {
+      int i = 0;
+      Size_ = 1;
+      for (long e : Ext) { Ext_[i++] = e; Size_ *= e; }
+      Data_ = std::shared_ptr<double>(Ptr, [](double *) {});
+   }
+   double *data() const { return Data_.get(); }
+   long extent(int i) const { return Ext_[i]; }
+   int extent_int(int i) const { return (int)Ext_[i]; }
+   long size() const { return Size_; }
+   const std::string &label() const { return Label_; }
+
+ private:
+   std::string Label_;
+   std::shared_ptr<double> Data_;
+   long Ext_[Rank > 0 ? Rank : 1] = {0};
+   long Size_ = 0;
+};
+using Array1DReal = DeviceArray<1>;
+using Array2DReal = DeviceArray<2>;
+using Array3DReal = DeviceArray<3>;
+
+/// HorzMesh: device-resident mesh built from host-order arrays
+class HorzMesh {
+ public:
+   I4 NCellsOwned, NCellsAll, NCellsSize, NEdgesOwned, NEdgesAll, NEdgesSize;
+   I4 NVerticesOwned, NVerticesAll, NVerticesSize, MaxEdges, MaxEdges2, VertexDegree, NVertLayers;
+   OmegaMesh *Handle = nullptr;
+
+   HorzMesh(const OmegaMeshDesc &D, bool Reorder = true) {
+      NCellsOwned = D.NCellsOwned; NCellsAll = D.NCellsAll; NCellsSize = D.NCellsSize;
+      NEdgesOwned = D.NEdgesOwned; NEdgesAll = D.NEdgesAll; NEdgesSize = D.NEdgesSize;
+      NVerticesOwned = D.NVerticesOwned; NVerticesAll = D.NVerticesAll; NVerticesSize = D.NVerticesSize;
+      MaxEdges = D.MaxEdges; MaxEdges2 = D.MaxEdges2; VertexDegree = D.VertexDegree; NVertLayers = D.NVertLayers;
+      OMEGA_B200_CHECK(omega_mesh_create(&D, Reorder ? 1 : 0, &Handle), "HorzMesh: omega_mesh_create");
+   }
+   ~HorzMesh() { omega_mesh_destroy(Handle); }
+   HorzMesh(const HorzMesh &) = delete;
+   I4 size(MeshElement E) const { return E == OnCell ? NCellsSize : E == OnEdge ? NEdgesSize : NVerticesSize; }
+   /// host-order -> device-order copy (OceanState::copyToDevice) and back
+   void copyToDevice(MeshElement E, int NOuter, int NInner, const double *Host, double *Dev, void *Stream = nullptr) const {
+      OMEGA_B200_CHECK(omega_field_to_device(Handle, (OmegaMeshElement)E, NOuter, NInner, Host, Dev, Stream), "copyToDevice");
+   }
+   void copyToHost(MeshElement E, int NOuter, int NInner, const double *Dev, double *Host, void *Stream = nullptr) const {
+      OMEGA_B200_CHECK(omega_field_to_host(Handle, (OmegaMeshElement)E, NOuter, NInner, Dev, Host, Stream), "copyToHost");
+   }
+};
+
+/// Halo: exchange lists on device; the transport (NCCL, peer copies) is supplied
+/// by the caller as a callback over the packed per-neighbour buffers.
+class Halo {
+ public:
+   using Transport = int (*)(void *User, int NNeighbors, const int *Tasks, const double *SendBuf,
+                             const long long *SendCounts, double *RecvBuf, const long long *RecvCounts, void *Stream);
+   OmegaHalo *Handle = nullptr;
+   const HorzMesh *Mesh;
+   std::vector<int> Neighbors;
+   Transport Xfer = nullptr;
+   void *XferUser = nullptr;
+
+   Halo(const HorzMesh *M, const OmegaHaloDesc &D) : Mesh(M), Neighbors(D.NeighborTasks, D.NeighborTasks + D.NNeighbors) {
+      OMEGA_B200_CHECK(omega_halo_create(M->Handle, &D, &Handle), "Halo: omega_halo_create");
+   }
+   ~Halo() { omega_halo_destroy(Handle); }
+   Halo(const Halo &) = delete;
+
+   /// Halo::exchangeFullArrayHalo(Array, Elem), src/base/Halo.h:768-915.  The
+   /// element dimension is second to last, as upstream.
+   template <int Rank> int exchangeFullArrayHalo(DeviceArray<Rank> &Array, MeshElement Elem, void *Stream = nullptr) {
+      static_assert(Rank == 2 || Rank == 3, "state arrays are [elem][level] or [tracer][elem][level]");
+      const int NOuter = Rank == 3 ? Array.extent_int(0) : 1, NInner = Array.extent_int(Rank - 1);
+      const int NN = (int)Neighbors.size();
+      if (NN == 0) return 0;
+      std::vector<long long> SC(NN), RC(NN);
+      if (omega_halo_buffer_counts(Handle, (OmegaMeshElement)Elem, NOuter, NInner, SC.data(), RC.data())) return -1;
+      long long ST = 0, RT = 0;
+      for (int i = 0; i < NN; ++i) { ST += SC[i]; RT += RC[i]; }
+      DeviceArray<1> SendBuf("HaloSend", {ST}), RecvBuf("HaloRecv", {RT});
+      if (omega_halo_pack(Handle, (OmegaMeshElement)Elem, NOuter, NInner, Array.data(), SendBuf.data(), Stream)) return -1;
+      if (!Xfer) return -2; // no transport installed
+      if (Xfer(XferUser, NN, Neighbors.data(), SendBuf.data(), SC.data(), RecvBuf.data(), RC.data(), Stream)) return -1;
+      if (omega_halo_unpack(Handle, (OmegaMeshElement)Elem, NOuter, NInner, RecvBuf.data(), Array.data(), Stream)) return -1;
+      return 0;
+   }
+};
+
+/// OceanState: h and u time-level rings (src/ocn/OceanState.cpp:65-117,333-407)
+class OceanState {
+ public:
+   std::vector<Array2DReal> LayerThickness, NormalVelocity;
+   I4 NTimeLevels, NVertLayers, CurTimeIndex = 0;
+   const HorzMesh *Mesh;
+   Halo *MeshHalo;
+
+   OceanState(const std::string &Name, const HorzMesh *M, Halo *H, int NVertLayers_, int NTimeLevels_)
+       : NTimeLevels(NTimeLevels_), NVertLayers(NVertLayers_), Mesh(M), MeshHalo(H) {
+      for (int i = 0; i < NTimeLevels; ++i) {
+         LayerThickness.emplace_back("LayerThickness" + Name + std::to_string(i), std::initializer_list<long>{M->NCellsSize, NVertLayers});
+         NormalVelocity.emplace_back("NormalVelocity" + Name + std::to_string(i), std::initializer_list<long>{M->NEdgesSize, NVertLayers});
+      }
+   }
+   I4 getTimeIndex(I4 &TimeIndex, I4 TimeLevel) const { // OceanState.cpp:394-407
+      if (NTimeLevels > 1 && (TimeLevel > 1 || (TimeLevel + NTimeLevels) <= 1)) return -1;
+      TimeIndex = (TimeLevel + CurTimeIndex + NTimeLevels) % NTimeLevels;
+      return 0;
+   }
+   I4 getLayerThickness(Array2DReal &Out, I4 TimeLevel) const {
+      I4 i; I4 Err = getTimeIndex(i, TimeLevel);
+      if (!Err) Out = LayerThickness[i];
+      return Err;
+   }
+   I4 getNormalVelocity(Array2DReal &Out, I4 TimeLevel) const {
+      I4 i; I4 Err = getTimeIndex(i, TimeLevel);
+      if (!Err) Out = NormalVelocity[i];
+      return Err;
+   }
+   I4 copyToDevice(I4 TimeLevel, const double *H, const double *U) {
+      I4 i; if (getTimeIndex(i, TimeLevel)) return -1;
+      Mesh->copyToDevice(OnCell, 1, NVertLayers, H, LayerThickness[i].data());
+      Mesh->copyToDevice(OnEdge, 1, NVertLayers, U, NormalVelocity[i].data());
+      return 0;
+   }
+   I4 copyToHost(I4 TimeLevel, double *H, double *U) const {
+      I4 i; if (getTimeIndex(i, TimeLevel)) return -1;
+      Mesh->copyToHost(OnCell, 1, NVertLayers, LayerThickness[i].data(), H);
+      Mesh->copyToHost(OnEdge, 1, NVertLayers, NormalVelocity[i].data(), U);
+      return 0;
+   }
+   I4 exchangeHalo(I4 TimeLevel) { // OceanState.cpp:333-344
+      I4 i; if (getTimeIndex(i, TimeLevel)) return -1;
+      if (!MeshHalo) return 0;
+      I4 Err = MeshHalo->exchangeFullArrayHalo(LayerThickness[i], OnCell);
+      Err |= MeshHalo->exchangeFullArrayHalo(NormalVelocity[i], OnEdge);
+      return Err;
+   }
+   void updateTimeLevels() { // OceanState.cpp:348-365
+      if (NTimeLevels == 1) abortError("OceanState: can't update time levels for NTimeLevels == 1");
+      exchangeHalo(1);
+      CurTimeIndex = (CurTimeIndex + 1) % NTimeLevels;
+   }
+};
+
+/// Tracers: [NTracers][NCellsSize][NVertLayers] per time level (src/ocn/Tracers.cpp:269-277,457-525).
+/// An instance instead of the reference's static class; NTracers is a plain integer.
+class Tracers {
+ public:
+   std::vector<Array3DReal> TracerArrays;
+   I4 NTracers, NTimeLevels, CurTimeIndex = 0;
+   Halo *MeshHalo;
+   Tracers(const HorzMesh *M, Halo *H, int NTracers_, int NVertLayers, int NTimeLevels_)
+       : NTracers(NTracers_), NTimeLevels(NTimeLevels_), MeshHalo(H) {
+      for (int i = 0; i < NTimeLevels; ++i)
+         TracerArrays.emplace_back("Tracers" + std::to_string(i), std::initializer_list<long>{NTracers, M->NCellsSize, NVertLayers});
+   }
+   I4 getNumTracers() const { return NTracers; }
+   I4 getTimeIndex(I4 &TimeIndex, I4 TimeLevel) const {
+      if (NTimeLevels > 1 && (TimeLevel > 1 || (TimeLevel + NTimeLevels) <= 1)) return -1;
+      TimeIndex = (TimeLevel + CurTimeIndex + NTimeLevels) % NTimeLevels;
+      return 0;
+   }
+   I4 getAll(Array3DReal &Out, I4 TimeLevel) const {
+      I4 i; I4 Err = getTimeIndex(i, TimeLevel);
+      if (!Err) Out = TracerArrays[i];
+      return Err;
+   }
+   I4 exchangeHalo(I4 TimeLevel) {
+      I4 i; if (getTimeIndex(i, TimeLevel)) return -1;
+      return MeshHalo ? MeshHalo->exchangeFullArrayHalo(TracerArrays[i], OnCell) : 0;
+   }
+   void updateTimeLevels() {
+      exchangeHalo(1);
+      CurTimeIndex = (CurTimeIndex + 1) % NTimeLevels;
+   }
+};
+
+} // namespace OMEGA
+
+#include "OmegaB200Stepper.h"

@@ -1,0 +1,187 @@
+// OmegaB200Stepper.h -- AuxiliaryState, Tendencies, TimeStepper mirrors (see
+// OmegaB200.h).  One OmegaStepper handle of the C library backs the three
+// objects; their public array members alias the library-owned device arrays
+// (src/ocn/AuxiliaryState.h:37-42, src/ocn/Tendencies.h:55-57).
+#pragma once
+#include "OmegaB200.h"
+
+namespace OMEGA {
+
+class AuxiliaryState {
+ public:
+   // the public arrays of the six aux-var groups, flattened
+   Array2DReal KineticEnergyCell, VelocityDivCell, FluxLayerThickEdge, MeanLayerThickEdge, SshCell,
+       RelVortVertex, NormRelVortVertex, NormPlanetVortVertex, NormRelVortEdge, NormPlanetVortEdge,
+       Del2Edge, Del2DivCell, Del2RelVortVertex;
+   Array3DReal HTracersEdge, Del2TracersCell;
+   OmegaStepper *Handle = nullptr;
+   const HorzMesh *Mesh;
+   I4 NTracers;
+
+   AuxiliaryState(const std::string &Name, const HorzMesh *M, Halo *, int NVertLayers, int NTracers_,
+                  const OmegaTendConfig &Cfg)
+       : Mesh(M), NTracers(NTracers_) {
+      OMEGA_B200_CHECK(omega_stepper_create(M->Handle, &Cfg, NTracers, &Handle), "AuxiliaryState: omega_stepper_create");
+      OmegaAuxArrays A;
+      OMEGA_B200_CHECK(omega_stepper_aux_arrays(Handle, &A), "omega_stepper_aux_arrays");
+      const long K = NVertLayers, C = M->NCellsSize, E = M->NEdgesSize, V = M->NVerticesSize, T = NTracers;
+#define OMEGA_ALIAS2(N, R) N = Array2DReal(#N + Name, A.N, {R, K})
+      OMEGA_ALIAS2(KineticEnergyCell, C); OMEGA_ALIAS2(VelocityDivCell, C); OMEGA_ALIAS2(FluxLayerThickEdge, E);
+      OMEGA_ALIAS2(MeanLayerThickEdge, E); OMEGA_ALIAS2(SshCell, C); OMEGA_ALIAS2(RelVortVertex, V);
+      OMEGA_ALIAS2(NormRelVortVertex, V); OMEGA_ALIAS2(NormPlanetVortVertex, V); OMEGA_ALIAS2(NormRelVortEdge, E);
+      OMEGA_ALIAS2(NormPlanetVortEdge, E); OMEGA_ALIAS2(Del2Edge, E); OMEGA_ALIAS2(Del2DivCell, C);
+      OMEGA_ALIAS2(Del2RelVortVertex, V);
+#undef OMEGA_ALIAS2
+      HTracersEdge    = Array3DReal("HTracersEdge" + Name, A.HTracersEdge, {T, E, K});
+      Del2TracersCell = Array3DReal("Del2TracersCell" + Name, A.Del2TracersCell, {T, C, K});
+   }
+   ~AuxiliaryState() { omega_stepper_destroy(Handle); }
+   AuxiliaryState(const AuxiliaryState &) = delete;
+
+   /// src/ocn/AuxiliaryState.cpp:60-143
+   void computeMomAux(const OceanState *State, int ThickTimeLevel, int VelTimeLevel, void *Stream = nullptr) const {
+      Array2DReal H, U;
+      State->getLayerThickness(H, ThickTimeLevel);
+      State->getNormalVelocity(U, VelTimeLevel);
+      OMEGA_B200_CHECK(omega_aux_compute_mom(Handle, H.data(), U.data(), Stream), "computeMomAux");
+   }
+   /// src/ocn/AuxiliaryState.cpp:146-191
+   void computeAll(const OceanState *State, const Array3DReal &TracerArray, int ThickTimeLevel, int VelTimeLevel,
+                   void *Stream = nullptr) const {
+      Array2DReal H, U;
+      State->getLayerThickness(H, ThickTimeLevel);
+      State->getNormalVelocity(U, VelTimeLevel);
+      OMEGA_B200_CHECK(omega_aux_compute_all(Handle, H.data(), U.data(), TracerArray.data(), Stream), "computeAll");
+   }
+   void computeAll(const OceanState *State, const Array3DReal &TracerArray, int TimeLevel) const {
+      computeAll(State, TracerArray, TimeLevel, TimeLevel);
+   }
+};
+
+class Tendencies {
+ public:
+   Array2DReal LayerThicknessTend, NormalVelocityTend;
+   Array3DReal TracerTend;
+   OmegaStepper *Handle; // shared with the AuxiliaryState it was built on
+
+   Tendencies(const std::string &Name, const HorzMesh *M, const AuxiliaryState *Aux, int NVertLayers) : Handle(Aux->Handle) {
+      OmegaTendArrays T;
+      OMEGA_B200_CHECK(omega_stepper_tend_arrays(Handle, &T), "omega_stepper_tend_arrays");
+      const long K = NVertLayers;
+      LayerThicknessTend = Array2DReal("LayerThicknessTend" + Name, T.LayerThicknessTend, {M->NCellsSize, K});
+      NormalVelocityTend = Array2DReal("NormalVelocityTend" + Name, T.NormalVelocityTend, {M->NEdgesSize, K});
+      TracerTend         = Array3DReal("TracerTend" + Name, T.TracerTend, {Aux->NTracers, M->NCellsSize, K});
+   }
+   void readTendConfig(const OmegaTendConfig &Cfg) { OMEGA_B200_CHECK(omega_stepper_set_config(Handle, &Cfg), "readTendConfig"); }
+
+   // raw vector indexing where the reference indexes raw (src/ocn/Tendencies.cpp:322,445,546-547)
+   static double *rawU(const OceanState *S, int Level) { return S->NormalVelocity[Level].data(); }
+   static double *rawH(const OceanState *S, int Level) { return S->LayerThickness[Level].data(); }
+   static double *mapU(const OceanState *S, int Level) { Array2DReal A; S->getNormalVelocity(A, Level); return A.data(); }
+   static double *mapH(const OceanState *S, int Level) { Array2DReal A; S->getLayerThickness(A, Level); return A.data(); }
+
+   /// src/ocn/Tendencies.cpp:257-486
+   void computeThicknessTendenciesOnly(const OceanState *S, const AuxiliaryState *, int, int VelLvl, double Time, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_thickness_only(Handle, mapU(S, VelLvl), Time, St), "computeThicknessTendenciesOnly");
+   }
+   void computeVelocityTendenciesOnly(const OceanState *S, const AuxiliaryState *, int, int VelLvl, double Time, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_velocity_only(Handle, mapU(S, VelLvl), rawU(S, VelLvl), Time, St), "computeVelocityTendenciesOnly");
+   }
+   void computeTracerTendenciesOnly(const OceanState *S, const AuxiliaryState *, const Array3DReal &Tr, int, int VelLvl, double, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_tracer_only(Handle, rawU(S, VelLvl), Tr.data(), St), "computeTracerTendenciesOnly");
+   }
+   /// src/ocn/Tendencies.cpp:488-600
+   void computeThicknessTendencies(const OceanState *S, const AuxiliaryState *, int ThickLvl, int VelLvl, double Time, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_thickness(Handle, mapH(S, ThickLvl), mapU(S, VelLvl), Time, St), "computeThicknessTendencies");
+   }
+   void computeVelocityTendencies(const OceanState *S, const AuxiliaryState *, int ThickLvl, int VelLvl, double Time, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_velocity(Handle, mapH(S, ThickLvl), mapU(S, VelLvl), rawU(S, VelLvl), Time, St), "computeVelocityTendencies");
+   }
+   void computeTracerTendencies(const OceanState *S, const AuxiliaryState *, const Array3DReal &Tr, int ThickLvl, int VelLvl, double, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_tracer(Handle, rawH(S, ThickLvl), rawU(S, VelLvl), Tr.data(), St), "computeTracerTendencies");
+   }
+   void computeAllTendencies(const OceanState *S, const AuxiliaryState *, const Array3DReal &Tr, int ThickLvl, int VelLvl, double Time, void *St = nullptr) {
+      OMEGA_B200_CHECK(omega_tend_all(Handle, mapH(S, ThickLvl), mapU(S, VelLvl), rawU(S, VelLvl), Tr.data(), Time, St), "computeAllTendencies");
+   }
+};
+
+enum class TimeStepperType { ForwardBackward, RungeKutta4, RungeKutta2, Invalid };
+
+/// TimeStepper::doStep (src/timeStepping/TimeStepper.h:82-84).  SimTime is
+/// elapsed seconds; Coeffs are the stage coefficients in seconds as
+/// TimeInterval::get evaluates them (src/infra/TimeMgr.cpp:382-391).
+class TimeStepper {
+ public:
+   TimeStepperType Type;
+   OmegaStepCoeffs Coeffs;
+   Tendencies *Tend;
+   AuxiliaryState *AuxState;
+   Tracers *Tr;
+   bool Fused = true, RawTimeLevelCompat = true;
+
+   TimeStepper(TimeStepperType T, double Dt, Tendencies *Td, AuxiliaryState *Ax, Tracers *Trc) : Type(T), Tend(Td), AuxState(Ax), Tr(Trc) {
+      setTimeStep(Dt);
+   }
+   /// dt an integer number of seconds: b*dt for RKB = 1/6, 1/3 evaluated as Whole + Numer/Denom
+   void setTimeStep(double Dt) {
+      Coeffs = OmegaStepCoeffs();
+      Coeffs.Dt = Dt;
+      auto frac = [&](long long num, long long den) { // (num/den)*Dt for integer Dt
+         const long long d = (long long)Dt, n = num * d;
+         const long long whole = n / den, rem = n % den;
+         if (rem == 0) return (double)whole;
+         long long a = rem, b = den; while (b) { long long t = a % b; a = b; b = t; }
+         return (double)whole + (double)(rem / a) / (double)(den / a);
+      };
+      if (Type == TimeStepperType::RungeKutta4) {
+         Coeffs.NStages = 4;
+         const long long an[4] = {0, 1, 1, 1}, ad[4] = {1, 2, 2, 1}, bn[4] = {1, 1, 1, 1}, bd[4] = {6, 3, 3, 6};
+         for (int s = 0; s < 4; ++s) { Coeffs.A[s] = frac(an[s], ad[s]); Coeffs.B[s] = frac(bn[s], bd[s]); }
+      } else if (Type == TimeStepperType::RungeKutta2) {
+         Coeffs.NStages = 2; Coeffs.A[1] = frac(1, 2); Coeffs.B[1] = Dt;
+      } else {
+         Coeffs.NStages = 1;
+      }
+   }
+   void doStep(OceanState *State, double &SimTime, void *Stream = nullptr) {
+      OmegaStateArrays X;
+      X.NTimeLevels = State->NTimeLevels; X.CurTimeIndex = State->CurTimeIndex;
+      X.TracerCurTimeIndex = Tr->CurTimeIndex; X.NTracers = Tr->NTracers;
+      for (int i = 0; i < 2; ++i) {
+         X.LayerThickness[i] = State->LayerThickness[i].data();
+         X.NormalVelocity[i] = State->NormalVelocity[i].data();
+         X.Tracers[i] = Tr->TracerArrays[i].data();
+      }
+      OmegaStepperType T = Type == TimeStepperType::RungeKutta4 ? OMEGA_STEPPER_RK4
+                           : Type == TimeStepperType::RungeKutta2 ? OMEGA_STEPPER_RK2 : OMEGA_STEPPER_FB;
+      for (int s = 0; s < 4; ++s) Coeffs.StageTime[s] = SimTime + (T == OMEGA_STEPPER_FB ? (s ? Coeffs.Dt : 0.0) : Coeffs.A[s]);
+      const int NPhases = T == OMEGA_STEPPER_RK4 ? 2 : 1;
+      for (int p = 0; p < NPhases; ++p) {
+         OMEGA_B200_CHECK(omega_stepper_step_phase(AuxState->Handle, T, &X, &Coeffs, p, Fused, RawTimeLevelCompat, Stream), "doStep");
+         if (State->MeshHalo && !State->MeshHalo->Neighbors.empty()) exchange(State, T, &X, p, Stream);
+      }
+      // State->updateTimeLevels(); Tracers::updateTimeLevels(): the exchange of level 1 ran above
+      State->CurTimeIndex = (State->CurTimeIndex + 1) % State->NTimeLevels;
+      Tr->CurTimeIndex    = (Tr->CurTimeIndex + 1) % Tr->NTimeLevels;
+      SimTime += Coeffs.Dt;
+   }
+
+ private:
+   void exchange(OceanState *State, OmegaStepperType T, OmegaStateArrays *X, int Phase, void *Stream) {
+      double *Ptrs[3]; int Elems[3], NOuter[3], N = 0;
+      OMEGA_B200_CHECK(omega_stepper_exchange_list(AuxState->Handle, T, X, Phase, Ptrs, Elems, NOuter, &N), "exchange list");
+      const HorzMesh *M = State->Mesh;
+      for (int i = 0; i < N; ++i) {
+         const long K = State->NVertLayers, R = M->size((MeshElement)Elems[i]);
+         if (NOuter[i] > 1 || i == 2) {
+            Array3DReal A("exch", Ptrs[i], {NOuter[i], R, K});
+            OMEGA_B200_CHECK(State->MeshHalo->exchangeFullArrayHalo(A, (MeshElement)Elems[i], Stream), "halo exchange");
+         } else {
+            Array2DReal A("exch", Ptrs[i], {R, K});
+            OMEGA_B200_CHECK(State->MeshHalo->exchangeFullArrayHalo(A, (MeshElement)Elems[i], Stream), "halo exchange");
+         }
+      }
+   }
+};
+
+} // namespace OMEGA
