@@ -257,6 +257,7 @@ struct CellArgs {
    int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext
    int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
    int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
+   int Prefetch; // 0 off, 1 next tracer's rows into L1, 2 into L2
    double EddyDiff2, EddyDiff4;
    ManufacturedParams MS;
 };
@@ -520,6 +521,20 @@ k_fC_center(DMesh M, CellArgs P) {
       for (int l = 0; l < P.NTracers; ++l) {
          const double *T  = P.Trs + l * CS;
          const double *D2 = P.Del2Tr + l * CS;
+         if (P.Prefetch && l + 1 < P.NTracers) {
+            const double *Tn = T + CS, *Dn = D2 + CS;
+            prefetch_row(Tn + o, P.Prefetch);
+            if (P.HypOn) prefetch_row(Dn + o, P.Prefetch);
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               if (j < ne) {
+                  prefetch_row(Tn + (size_t)nb[j] * M.K + k, P.Prefetch);
+                  if (P.HypOn) prefetch_row(Dn + (size_t)nb[j] * M.K + k, P.Prefetch);
+               }
+            }
+            if (!(P.First && P.TrCur == P.Trs) && (P.First || !P.Last)) prefetch_row(P.TrCur + (l + 1) * CS + o, P.Prefetch);
+            if (!P.First) prefetch_row(P.TrNext + (l + 1) * CS + o, P.Prefetch);
+         }
          double ts[V], d2s[V], tend[V];
          ldv<V>(ts, T + o);
          if (P.HypOn) ldv<V>(d2s, D2 + o);
@@ -607,8 +622,8 @@ template <int V> __device__ __forceinline__ void pv_edge(const DMesh &M, int e, 
    for (int q = 0; q < V; ++q) pv[q] = 0.5 * (a[q] + b[q]);
 }
 
-template <int V>
-__global__ void __launch_bounds__(kBlock)
+template <int V, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB)
 k_fE(DMesh M, EdgeArgs P) {
    const int KV = M.K / V;
    const OmegaTendConfig &G = P.G;
@@ -835,6 +850,7 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.DiffOn = G.TracerDiffTendencyEnable; ca.HypOn = tr4;
       ca.FluxUpwind = G.FluxThicknessType; ca.TrUpwind = G.FluxTracerType;
       ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
+      ca.Prefetch = env_int("OMEGA_FC_PREFETCH", 0);
       ca.MS = manufactured(S, C->StageTime[s]);
       {
       ScopedTimer tm_(S, St, kFC);
@@ -865,7 +881,16 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
       ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
       ea.G = G; ea.MS = ca.MS;
-      LAUNCH_V(kFE, k_fE, ge, D, ea);
+      {
+         // occupancy variants measured on B200 (profiles/r01): 4 CTAs/SM (64 regs, some spills) is fastest
+         const int fev = env_int("OMEGA_FE_VARIANT", 3);
+         ScopedTimer tm_(S, St, kFE);
+         if (V == 1) k_fE<1, 2><<<ge, kBlock, 0, St>>>(D, ea);
+         else if (fev == 2) k_fE<2, 3><<<ge, kBlock, 0, St>>>(D, ea);
+         else if (fev == 3) k_fE<2, 4><<<ge, kBlock, 0, St>>>(D, ea);
+         else k_fE<2, 2><<<ge, kBlock, 0, St>>>(D, ea);
+         ++S->Launches;
+      }
 #undef LAUNCH_V
    }
    OMEGA_CUDA_CHECK(cudaGetLastError());

@@ -36,6 +36,13 @@ template <> __device__ __forceinline__ void stv<2>(double *p, const double (&r)[
    *reinterpret_cast<double2 *>(p) = make_double2(r[0], r[1]);
 }
 
+// fire-and-forget prefetch of this lane's part of a row: raises the bytes in flight
+// per SM without landing registers (mode 1: into L1, mode 2: into L2 only)
+__device__ __forceinline__ void prefetch_row(const double *p, int mode) {
+   if (mode == 1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+   else if (mode == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 // work index -> (element i, first level k); returns false past the end
 template <int V> __device__ __forceinline__ bool elem_k(int N, int K, int &i, int &k) {
    const int KV      = K / V;

@@ -195,9 +195,9 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    STAGE(G.BottomDepth, gather_rows(D->BottomDepth, PC, 1));
    STAGE(G.XCell, gather_rows(D->XCell, PC, 1));
    STAGE(G.YCell, gather_rows(D->YCell, PC, 1));
+   std::vector<int> coe = gather_index_rows(D->CellsOnEdge, PE, 2, IC);
+   std::vector<int> voe = gather_index_rows(D->VerticesOnEdge, PE, 2, IV);
    {
-      std::vector<int> coe = gather_index_rows(D->CellsOnEdge, PE, 2, IC);
-      std::vector<int> voe = gather_index_rows(D->VerticesOnEdge, PE, 2, IV);
       const int *p = nullptr;
       rc |= to_device(M, coe, &p); G.CellsOnEdge = reinterpret_cast<const int2 *>(p);
       rc |= to_device(M, voe, &p); G.VerticesOnEdge = reinterpret_cast<const int2 *>(p);
@@ -216,6 +216,19 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
       STAGE(G.NEdgesOnEdge, neoe);
       STAGE(G.EdgesOnEdge, eoe);
       STAGE(G.WeightsOnEdge, w);
+      // flattened gather tables of the fused edge kernel: cells and vertices of every
+      // EdgesOnEdge entry, so a neighbour costs one index level instead of three
+      std::vector<int> ec((size_t)(NE + 1) * ME2 * 2, NC), ev((size_t)(NE + 1) * ME2 * 2, NV);
+      for (int e = 0; e < NE; ++e)
+         for (int j = 0; j < neoe[e]; ++j) {
+            const int je = eoe[(size_t)e * ME2 + j];
+            const size_t o = ((size_t)e * ME2 + j) * 2;
+            ec[o] = coe[(size_t)je * 2]; ec[o + 1] = coe[(size_t)je * 2 + 1];
+            ev[o] = voe[(size_t)je * 2]; ev[o + 1] = voe[(size_t)je * 2 + 1];
+         }
+      const int *q = nullptr;
+      rc |= to_device(M, ec, &q); G.EoECells = reinterpret_cast<const int2 *>(q);
+      rc |= to_device(M, ev, &q); G.EoEVerts = reinterpret_cast<const int2 *>(q);
    }
    STAGE(G.DcEdge, gather_rows(D->DcEdge, PE, 1));
    STAGE(G.DvEdge, gather_rows(D->DvEdge, PE, 1));

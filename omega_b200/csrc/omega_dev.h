@@ -48,6 +48,7 @@ struct DMesh {
    const int *NEdgesOnEdge;                  // [E] trimmed of trailing boundary-slot entries
    const int *EdgesOnEdge;                   // [E][MaxEdges2]
    const double *WeightsOnEdge;              // [E][MaxEdges2]
+   const int2 *EoECells, *EoEVerts;          // [E][MaxEdges2] cells / vertices of each EdgesOnEdge entry
    const double *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge;
    const double *EdgeMask, *MeshScalingDel2, *MeshScalingDel4; // [E]
    // vertices (VertexDegree == 3)
