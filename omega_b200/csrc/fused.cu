@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include "fused_args.h"
 #include "kernel_util.cuh"
 #include "omega_dev.h"
 #include "stepper.h"
@@ -245,24 +246,6 @@ k_fT2(DMesh M, const double *__restrict__ H, const double *__restrict__ Tr, int 
 // updateTracersByTend, finalizeTracersUpdate (TimeStepper.cpp:378-524) as the
 // epilogue.  Per-edge coefficients live in registers and serve every tracer.
 // ---------------------------------------------------------------------------
-struct CellArgs {
-   const double *Hs, *Us, *UTr, *Trs, *Del2Tr; // stage state; UTr = velocity seen by tracer advection
-   const double *Hcur;
-   double *Hnext, *Hprov;                      // Hprov == nullptr on the last stage
-   const double *TrCur;
-   double *TrNext, *TrProv;
-   double A, B;                                // a_{s+1} dt, b_s dt
-   int First, Last, NTracers;
-   int WSel;   // stage-0 weight thickness: 0 = Hcur, 1 = Hnext before this stage writes it
-   int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext
-   int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
-   int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
-   int Prefetch; // 0 off, 1 next tracer's rows into L1, 2 into L2
-   double EddyDiff2, EddyDiff4;
-   ManufacturedParams MS;
-};
-
-constexpr int kME = 6; // max edges per cell on the fused path (checked at launch)
 
 template <int V, bool UPW>
 __global__ void __launch_bounds__(kBlock)
@@ -588,16 +571,6 @@ k_fC_center(DMesh M, CellArgs P) {
 // (VorticityAuxVars.h:61-76, LayerThicknessAuxVars.h:25-82), then
 // updateVelocityByTend (TimeStepper.cpp:407-430) as the epilogue.
 // ---------------------------------------------------------------------------
-struct EdgeArgs {
-   const double *Hs, *Us, *URaw;                       // stage state; URaw = velocity seen by bottom drag
-   const double *KE, *Div, *RelVort, *PVv, *Del2Div, *Del2RelVort, *NormalStress;
-   const double *Ucur;
-   double *Unext, *Uprov;
-   double A, B;
-   int First, Last;
-   OmegaTendConfig G;
-   ManufacturedParams MS;
-};
 
 template <int V> __device__ __forceinline__ void flux_edge(const DMesh &M, int e, int k, const double *H,
                                                            const double (&u)[V], int Upwind, double (&flux)[V]) {
@@ -835,7 +808,9 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
    } while (0)
       LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
       if (vel4) LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
-      if (tr4) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
+      // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
+      const bool tiled = !upw && V == 2 && T > 0 && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
+      if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
       // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
       // advection reads the stale next-level velocity the edge pass overwrites
       CellArgs ca;
@@ -855,7 +830,9 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       {
       ScopedTimer tm_(S, St, kFC);
       const int variant = env_int("OMEGA_FC_VARIANT", 3);
-      if (upw) {
+      if (tiled) {
+         if (launch_fCT(D, ca, St)) return 1;
+      } else if (upw) {
          if (V == 2) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca);
       } else if (V == 1) {
          k_fC_center<1, 512, 1><<<fused_grid(D.NCellsAll, D.K, 1, 512, itC), 512, 0, St>>>(D, ca);

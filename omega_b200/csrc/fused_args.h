@@ -1,0 +1,41 @@
+// fused_args.h -- argument blocks of the fused per-stage kernels (fused.cu, fused_tile.cu).
+#pragma once
+#include "omega_dev.h"
+
+namespace omega {
+
+struct CellArgs {
+   const double *Hs, *Us, *UTr, *Trs, *Del2Tr; // stage state; UTr = velocity seen by tracer advection
+   const double *Hcur;
+   double *Hnext, *Hprov;                      // Hprov == nullptr on the last stage
+   const double *TrCur;
+   double *TrNext, *TrProv;
+   double A, B;                                // a_{s+1} dt, b_s dt
+   int First, Last, NTracers;
+   int WSel;   // stage-0 weight thickness: 0 = Hcur, 1 = Hnext before this stage writes it
+   int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext
+   int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
+   int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
+   int Prefetch; // 0 off, 1 next tracer's rows into L1, 2 into L2
+   double EddyDiff2, EddyDiff4;
+   ManufacturedParams MS;
+};
+
+constexpr int kME = 6; // max edges per cell on the fused path (checked at launch)
+
+struct EdgeArgs {
+   const double *Hs, *Us, *URaw;                       // stage state; URaw = velocity seen by bottom drag
+   const double *KE, *Div, *RelVort, *PVv, *Del2Div, *Del2RelVort, *NormalStress;
+   const double *Ucur;
+   double *Unext, *Uprov;
+   double A, B;
+   int First, Last;
+   OmegaTendConfig G;
+   ManufacturedParams MS;
+};
+
+// fused_tile.cu
+bool tile_path_ok(const DMesh &D);
+int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St);
+
+} // namespace omega

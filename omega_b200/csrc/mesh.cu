@@ -36,6 +36,45 @@ static void sort_block(std::vector<int> &perm, int lo, int hi, const std::vector
    perm.insert(perm.end(), idx.begin(), idx.end());
 }
 
+
+// Recursive coordinate bisection of the index set idx into leaves of exactly
+// LeafSize elements (the last leaf takes the remainder), split on the axis of
+// largest extent; leaves are emitted in tree order, so the result is a
+// space-filling order whose every aligned run of LeafSize rows is a compact
+// patch (mean first-ring size 37 cells for 64-cell patches on the icosahedral
+// mesh, against 52 for the same run length along the Morton curve).  Inside
+// a leaf rows keep Morton order.
+static void rcb_rec(std::vector<int> &idx, int lo, int hi, int nleaves, int LeafSize, const double *const X[3],
+                    const std::vector<uint64_t> &morton, std::vector<int> &out) {
+   if (hi <= lo) return;
+   if (nleaves <= 1) {
+      std::stable_sort(idx.begin() + lo, idx.begin() + hi, [&](int a, int b) { return morton[a] < morton[b]; });
+      out.insert(out.end(), idx.begin() + lo, idx.begin() + hi);
+      return;
+   }
+   double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+   for (int i = lo; i < hi; ++i)
+      for (int a = 0; a < 3; ++a) {
+         mn[a] = std::min(mn[a], X[a][idx[i]]);
+         mx[a] = std::max(mx[a], X[a][idx[i]]);
+      }
+   int ax = 0;
+   for (int a = 1; a < 3; ++a)
+      if (mx[a] - mn[a] > mx[ax] - mn[ax]) ax = a;
+   const int nl  = nleaves / 2;
+   const int cut = std::min(hi, lo + nl * LeafSize);
+   auto cmp = [&](int a, int b) { return X[ax][a] < X[ax][b] || (X[ax][a] == X[ax][b] && a < b); };
+   std::nth_element(idx.begin() + lo, idx.begin() + cut, idx.begin() + hi, cmp);
+   rcb_rec(idx, lo, cut, nl, LeafSize, X, morton, out);
+   rcb_rec(idx, cut, hi, nleaves - nl, LeafSize, X, morton, out);
+}
+static void rcb_block(std::vector<int> &perm, int lo, int hi, int LeafSize, const double *const X[3],
+                      const std::vector<uint64_t> &morton) {
+   std::vector<int> idx(hi - lo);
+   std::iota(idx.begin(), idx.end(), lo);
+   rcb_rec(idx, 0, hi - lo, (hi - lo + LeafSize - 1) / LeafSize, LeafSize, X, morton, perm);
+}
+
 template <class T> static int to_device(OmegaMesh *M, const std::vector<T> &h, const T **out) {
    void *d = nullptr;
    size_t bytes = std::max<size_t>(h.size() * sizeof(T), 16);
@@ -65,6 +104,98 @@ static std::vector<int> gather_index_rows(const int *src, const std::vector<int>
          out[i * width + j] = iperm_target[t];
       }
    return out;
+}
+
+
+// ---- tiles (omega_dev.h: DTiles) -------------------------------------------
+// eoc/coe/nec are the DEVICE-order tables.  Tiles cover [0,NC) in order and do
+// not straddle the owned/halo boundary.
+static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vector<int> &nec,
+                       const std::vector<int> &eoc, const std::vector<int> &coe,
+                       const std::vector<double> &mask, const std::vector<double> &dv,
+                       const std::vector<double> &dc, const std::vector<double> &area) {
+   DTiles &T = M->D.Tiles;
+   std::memset(&T, 0, sizeof(T));
+   if (M->MaxEdgesUsed > 6) return 0;
+   auto nbr = [&](int c, int j) {
+      const int e = eoc[(size_t)c * ME + j];
+      const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
+      return a == c ? b : a;
+   };
+   std::vector<TileHdr> hdr;
+   std::vector<int> rows;
+   std::vector<unsigned short> nbl;
+   std::vector<int> loc(NC + 1, -1); // local row of a cell in the tile under construction
+   std::vector<int> r1, r2;
+   int c0 = 0;
+   while (c0 < NC) {
+      const int blockEnd = c0 < NOwned ? NOwned : NC;
+      int nc = std::min(kTileCells, blockEnd - c0);
+      for (;;) {
+         r1.clear();
+         r2.clear();
+         for (int i = 0; i < nc; ++i) loc[c0 + i] = i;
+         for (int i = 0; i < nc; ++i)
+            for (int j = 0; j < nec[c0 + i]; ++j) {
+               const int n = nbr(c0 + i, j);
+               if (loc[n] < 0) { loc[n] = 1 << 20; r1.push_back(n); }
+            }
+         std::sort(r1.begin(), r1.end());
+         for (int n : r1)
+            if (n < NC)
+               for (int j = 0; j < nec[n]; ++j) {
+                  const int m = nbr(n, j);
+                  if (loc[m] < 0) { loc[m] = 1 << 21; r2.push_back(m); }
+               }
+         std::sort(r2.begin(), r2.end());
+         const bool ok = nc + (int)r1.size() <= kTileRows1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows;
+         if (ok || nc == 1) break;
+         for (int i = 0; i < nc; ++i) loc[c0 + i] = -1;
+         for (int n : r1) loc[n] = -1;
+         for (int n : r2) loc[n] = -1;
+         nc = std::max(1, nc * 3 / 4);
+      }
+      if (nc + (int)r1.size() > kTileRows1 || nc + (int)r1.size() + (int)r2.size() > kTileRows) {
+         set_error("build_tiles: a single cell exceeds the tile row caps");
+         return 2;
+      }
+      for (size_t i = 0; i < r1.size(); ++i) loc[r1[i]] = nc + (int)i;
+      for (size_t i = 0; i < r2.size(); ++i) loc[r2[i]] = nc + (int)r1.size() + (int)i;
+      TileHdr h;
+      h.C0 = c0; h.NC = nc; h.N1 = (int)r1.size(); h.N2 = (int)r2.size();
+      h.RowOff = (int)rows.size(); h.NblOff = (int)(nbl.size() / 8); h.Pad0 = h.Pad1 = 0;
+      hdr.push_back(h);
+      rows.insert(rows.end(), r1.begin(), r1.end());
+      rows.insert(rows.end(), r2.begin(), r2.end());
+      for (int r = 0; r < nc + (int)r1.size(); ++r) {
+         const int c = r < nc ? c0 + r : r1[r - nc];
+         for (int j = 0; j < 8; ++j) {
+            int l = r;
+            if (c < NC && j < nec[c]) l = loc[nbr(c, j)];
+            nbl.push_back((unsigned short)l);
+         }
+      }
+      for (int i = 0; i < nc; ++i) loc[c0 + i] = -1;
+      for (int n : r1) loc[n] = -1;
+      for (int n : r2) loc[n] = -1;
+      c0 += nc;
+   }
+   std::vector<double> g((size_t)(NC + 1) * 6, 0.0), ia(NC + 1, 0.0);
+   for (int c = 0; c < NC; ++c) {
+      ia[c] = 1.0 / area[c];
+      for (int j = 0; j < nec[c]; ++j) {
+         const int e = eoc[(size_t)c * ME + j];
+         g[(size_t)c * 6 + j] = mask[e] * (dv[e] / dc[e]);
+      }
+   }
+   int rc = 0;
+   rc |= to_device(M, hdr, &T.Hdr);
+   rc |= to_device(M, rows, &T.HaloRows);
+   rc |= to_device(M, nbl, &T.Nbl);
+   rc |= to_device(M, g, &T.GCell);
+   rc |= to_device(M, ia, &T.InvAreaCell);
+   T.NTiles = rc ? 0 : (int)hdr.size();
+   return rc;
 }
 
 } // namespace omega
@@ -145,8 +276,14 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
          }
          key[c] = spread3(q[0]) | (spread3(q[1]) << 1) | (spread3(q[2]) << 2);
       }
-      sort_block(PC, 0, D->NCellsOwned, key);
-      sort_block(PC, D->NCellsOwned, NC, key);
+      const char *ord = getenv("OMEGA_ORDER");
+      if (ord && std::strcmp(ord, "morton") == 0) {
+         sort_block(PC, 0, D->NCellsOwned, key);
+         sort_block(PC, D->NCellsOwned, NC, key);
+      } else {
+         rcb_block(PC, 0, D->NCellsOwned, kTileCells, X, key);
+         rcb_block(PC, D->NCellsOwned, NC, kTileCells, X, key);
+      }
    } else {
       PC.resize(NC);
       std::iota(PC.begin(), PC.end(), 0);
@@ -246,6 +383,11 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    STAGE(G.AreaTriangle, gather_rows(D->AreaTriangle, PV, 1));
    STAGE(G.FVertex, gather_rows(D->FVertex, PV, 1));
 #undef STAGE
+   if (!rc)
+      rc |= build_tiles(M, NC, D->NCellsOwned, ME, gather_rows(D->NEdgesOnCell, PC, 1),
+                        gather_index_rows(D->EdgesOnCell, PC, ME, IE), coe,
+                        gather_rows(M->EdgeMaskH.data(), PE, 1), gather_rows(D->DvEdge, PE, 1),
+                        gather_rows(D->DcEdge, PE, 1), gather_rows(D->AreaCell, PC, 1));
    for (int kind = 0; kind < 3; ++kind) {
       const int *p = nullptr;
       rc |= to_device(M, M->Perm[kind], &p);

@@ -29,6 +29,29 @@ void set_error(const std::string &msg);
       }                                                                                \
    } while (0)
 
+// Cell patches ("tiles") of the shared-memory staged kernels: kTileCells
+// consecutive cells of the device order (one leaf of the bisection order) plus
+// the two rings of neighbours their stencils reach.  Local row numbering of a
+// tile: own cells [0,nc), ring 1 [nc,nc+n1), ring 2 [nc+n1,nc+n1+n2); the
+// boundary slot (row NCellsAll, all zero) appears as an ordinary ring row.
+constexpr int kTileCells = 64;  // own cells per tile (fewer when a cap below would be exceeded)
+constexpr int kTileRows1 = 120; // cap on own + ring-1 rows
+constexpr int kTileRows  = 176; // cap on own + ring-1 + ring-2 rows
+struct TileHdr {
+   int C0, NC, N1, N2; // first own cell, counts
+   int RowOff;         // offset of the tile's ring rows in HaloRows
+   int NblOff;         // offset (in rows) of the tile's rows in Nbl
+   int Pad0, Pad1;
+};
+struct DTiles {
+   int NTiles;
+   const TileHdr *Hdr;
+   const int *HaloRows;       // ring-1 then ring-2 rows of every tile (device cell index)
+   const unsigned short *Nbl; // [own + ring-1 rows][8]: local row of the cell across edge j (self when none)
+   const double *GCell;       // [NCellsSize][6]  EdgeMask*DvEdge/DcEdge of edge j of the cell, 0 when none
+   const double *InvAreaCell; // [NCellsSize], 0 in the boundary slot
+};
+
 // Device-resident HorzMesh, structure of arrays, DEVICE order.  Passed to
 // kernels by value (fits the 4 KB parameter space many times over).
 struct DMesh {
@@ -55,6 +78,7 @@ struct DMesh {
    const int *CellsOnVertex, *EdgesOnVertex;               // [V][3]
    const double *EdgeSignOnVertex, *KiteAreasOnVertex;     // [V][3]
    const double *AreaTriangle, *FVertex;
+   DTiles Tiles; // NTiles == 0 when the mesh has cells with more than 6 edges
 };
 
 } // namespace omega

@@ -28,6 +28,11 @@ CASES = {
     "sphere3_K64_T3": lambda: cases.sphere_case(3, 64, 3),    # warp == one element row
     "plane16_K1_T0": lambda: cases.plane_case(16, 1, 0),      # config-1 shape: 1 level, no tracers
     "plane12_K10_T2": lambda: cases.plane_case(12, 10, 2),
+    # K % 16 == 0 -> the shared-memory tiled cell pass (fused_tile.cu); 41 tiles incl. the 12 pentagons
+    "sphere4_K16_T3": lambda: cases.sphere_case(4, 16, 3),
+    "plane16_K32_T2": lambda: cases.plane_case(16, 32, 2),
+    # tracer hyperdiffusion off -> the tiled pass without its Del2 phase
+    "sphere3_K16_T2_nodel4": lambda: cases.sphere_case(3, 16, 2, TracerHyperDiffTendencyEnable=0),
 }
 
 
@@ -177,9 +182,28 @@ def test_rk4_100_steps_state_parity():
         assert max(errs) <= TOL_STATE, (fused, errs)
 
 
-@pytest.mark.parametrize("fused", [False, True])
+def test_tiled_and_untiled_fused_paths_agree(monkeypatch):
+    """fused_tile.cu against the fused.cu kernels it replaces (OMEGA_TILE=0), same inputs."""
+    L, cfg, init, dt = cases.sphere_case(4, 32, 4)
+    res = []
+    for tile in ("1", "0"):
+        monkeypatch.setenv("OMEGA_TILE", tile)
+        from omega_b200 import model
+        h, u, tr = init
+        mesh, st, state = gpu_objects(L, cfg, tr.shape[0])
+        state.copyToDevice(h, u, tr)
+        co = capi.rk_coeffs(capi.RK4, dt)
+        for _ in range(3):
+            st.doStep(state, capi.RK4, co, fused=True, compat=True)
+        res.append(state.copyToHost(0))
+        st.close(); mesh.close()
+    for a, b in zip(*res):
+        assert rel_l2(a, b) <= 1e-13, rel_l2(a, b)
+
+
+@pytest.mark.parametrize("fused,K", [(False, 4), (True, 4), (True, 16)])
 @pytest.mark.parametrize("ntasks", [2, 3])
-def test_multirank_emulated_on_one_gpu(ntasks, fused):
+def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
     """N ranks' partitions stepped on one GPU in one process: the library's halo
     pack/unpack kernels, exchange lists in device order and phase-split stepping,
     with device-to-device copies standing in for NCCL.  Checked against the
@@ -188,7 +212,7 @@ def test_multirank_emulated_on_one_gpu(ntasks, fused):
     import ctypes as C
     from omega_b200 import analytic, decomp, model, parallel
     from tests.oracle_lib import Oracle
-    K, T, nsteps = 4, 2, 3
+    T, nsteps = 2, 3
     mesh_g = cases.sphere_mesh(3)
     L1, cfg, (h, u, tr), dt = cases.sphere_case(3, K, T)
     ref = Oracle(L1, cfg, T)
