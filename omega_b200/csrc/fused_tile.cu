@@ -4,22 +4,27 @@
 // materialises Del2Tracers: a CTA owns one tile (omega_dev.h: <= 64 cells and
 // the two rings of neighbours around them) x 16 levels.  Rows of h and of one
 // tracer after the other are gathered into shared memory with cp.async
-// (LDGSTS, 16 B per lane, three tracers in flight), so
+// (LDGSTS, 16 B per lane, up to three tracers in flight), so
 //   * every row a tile needs crosses L2 -> SM once per tile instead of once
 //     per neighbour that reads it, with no index chain in front of it;
-//   * the thread that owns (cell, 2 levels) keeps its per-edge coefficients in
-//     registers for all tracers and addresses neighbours by precomputed
-//     shared-memory offsets;
+//   * per-edge coefficients stay in registers for all tracers and neighbours
+//     are addressed by precomputed shared-memory offsets;
 //   * Del2(phi) of the own cells AND of ring 1 is computed in shared memory
 //     (ring 1 redundantly, ~0.6 extra rows per own row), which removes the
 //     3 T doubles per cell-layer the Del2Tracers array costs in HBM.
+// With tracer hyperdiffusion on the CTA is split into two roles of 16 warps:
+//   D role: Del2(phi_m) of own + ring-1 rows into one of two D2 buffers
+//   T role: issues the copies, then tendency + RK update of tracer l = m - 1
+// handing buffers over with named barriers (bar.arrive / bar.sync), so the two
+// halves of the stencil overlap and each role fits 64 registers per thread.
 // Algorithmic DRAM traffic per cell-layer and stage: 8 + 4 T doubles
 // (h, hcur, hnext r/w, hprov, 3 u | phi, cur, next r/w or prov) against
 // 9 + 8 T for k_fT2 + k_fC_center.
 //
 // Reference semantics: the same functors and update rules as k_fC_center
 // (TendencyTerms.h:35-58,349-480, TracerAuxVars.h:25-91,
-// LayerThicknessAuxVars.h:25-61, TimeStepper.cpp:378-524).
+// LayerThicknessAuxVars.h:25-61, TimeStepper.cpp:378-524); MeshScalingDel2/4
+// are 1 (HorzMesh.cpp:604-626), which the per-cell tables assume.
 #include "fused_args.h"
 #include "kernel_util.cuh"
 #include "omega_dev.h"
@@ -27,16 +32,17 @@
 
 namespace omega {
 
-constexpr int kTKC      = 16;  // levels per tile
-constexpr int kTLanes   = 8;   // threads per row (2 levels each)
-constexpr int kTThreads = kTileCells * kTLanes;
-constexpr int kTStages  = 3;   // tracer rows in flight
+constexpr int kTKC     = 16;                    // levels per tile
+constexpr int kTLanes  = 8;                     // threads per row (2 levels each)
+constexpr int kTRole   = kTileCells * kTLanes;  // threads per role
+constexpr int kTStages = 4;                     // tracer row-set buffers
 
 struct TileSmem {
    double H[kTileRows][kTKC];
    double Phi[kTStages][kTileRows][kTKC];
-   double D2[kTileRows1][kTKC];
+   double D2[2][kTileRows1][kTKC];
    double G[kTileRows1][6];
+   double Ch[kTileCells][6];
    double InvA[kTileRows1];
    unsigned short Nbl[kTileRows1][8];
    int GRow[kTileRows];
@@ -49,144 +55,235 @@ __device__ __forceinline__ void cp_async16(unsigned dst, const void *src) {
 }
 __device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+// (PTX: when the barrier completes, the prior memory accesses of every participating
+// thread -- arriving or waiting -- are performed relative to all participants)
+__device__ __forceinline__ void bar_arrive(int id, int n) {
+   asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ double2 lds2(const unsigned char *base, unsigned off) {
+   return *reinterpret_cast<const double2 *>(base + off);
+}
+__device__ __forceinline__ void sts2(unsigned char *base, unsigned off, double a, double b) {
+   *reinterpret_cast<double2 *>(base + off) = make_double2(a, b);
+}
+// local row of neighbour j from the packed 8 x u16 row of Nbl
+__device__ __forceinline__ unsigned nbl_get(const uint4 &t, int j) {
+   const unsigned w = j < 2 ? t.x : (j < 4 ? t.y : t.z);
+   return (w >> ((j & 1) * 16)) & 0xffffu;
+}
 
-__device__ __forceinline__ double2 lds2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
+// named barriers (0 is __syncthreads)
+constexpr int kBarDRole = 1; // the D role among itself
+__device__ __forceinline__ int bar_d2_ready(int l) { return 3 + (l & 1); }
+__device__ __forceinline__ int bar_d2_free(int l) { return 5 + (l & 1); }
 
-template <bool HYP>
-__global__ void __launch_bounds__(kTThreads, 1)
-k_fCT(DMesh M, CellArgs P, int NChunks) {
-   extern __shared__ __align__(16) unsigned char smem_raw[];
-   TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
-   const int tid = threadIdx.x;
-   const int tile = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
-   const int K = M.K;
-   const size_t CS = (size_t)M.NCellsSize * K;
+// the common view of a tile a thread needs in either role
+struct TileCtx {
+   int c0, nc, n1, nR1, nR; // tile geometry
+   int t, i, p, li;         // thread in role, own row, 16-byte piece, clamped own row
+   bool own;
+   unsigned myoff;          // byte offset of the own piece inside a [row][16] buffer
+};
 
-   if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
-      reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
-   __syncthreads();
-   const int c0 = S.Hdr.C0, nc = S.Hdr.NC, n1 = S.Hdr.N1, nR1 = nc + n1, nR = nR1 + S.Hdr.N2;
-   for (int r = tid; r < nR; r += kTThreads) S.GRow[r] = r < nc ? c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - nc];
-   __syncthreads();
-
-   // ---- this thread's share of a row-set copy: items q = tid + 512 i -> row q/8, 16-byte piece q%8
-   int goff[3];      // element offset of the source piece inside one [cell][level] field
-   unsigned soff[3]; // byte offset of the destination piece inside one [row][16] buffer
-   int ncopy = 0;
-#pragma unroll
-   for (int i = 0; i < 3; ++i) {
-      const int q = tid + i * kTThreads, r = q >> 3, p = q & 7;
-      goff[i] = 0;
-      soff[i] = 0;
-      if (r < nR) {
-         goff[i] = S.GRow[r] * K + kc0 + 2 * p;
-         soff[i] = (unsigned)(r * kTKC + 2 * p) * 8u;
-         ncopy   = i + 1;
-      }
-   }
-   auto copy_rows = [&](const double *F, double *Dst) {
-      const unsigned d = smem_u32(Dst);
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-         if (i < ncopy) cp_async16(d + soff[i], F + goff[i]);
-   };
-   copy_rows(P.Hs, &S.H[0][0]);
-   cp_commit();
-   const int T = P.NTracers;
-#pragma unroll
-   for (int s = 0; s < kTStages - 1; ++s) {
-      if (s < T) copy_rows(P.Trs + s * CS, &S.Phi[s][0][0]);
-      cp_commit();
-   }
-
-   // ---- static tables of the own + ring-1 rows
-   for (int q = tid; q < nR1 * 6; q += kTThreads) {
+// static tables of the own + ring-1 rows (all threads of the CTA take part)
+template <int NT>
+__device__ __forceinline__ void load_tables(const DMesh &M, TileSmem &S, int tid, int nR1) {
+   for (int q = tid; q < nR1 * 6; q += NT) {
       const int r = q / 6, j = q - r * 6;
       S.G[r][j] = M.Tiles.GCell[(size_t)S.GRow[r] * 6 + j];
    }
-   for (int r = tid; r < nR1; r += kTThreads) {
+   for (int r = tid; r < nR1; r += NT) {
       S.InvA[r] = M.Tiles.InvAreaCell[S.GRow[r]];
       *reinterpret_cast<uint4 *>(&S.Nbl[r][0]) =
           *reinterpret_cast<const uint4 *>(M.Tiles.Nbl + (size_t)(S.Hdr.NblOff + r) * 8);
    }
+}
 
-   // ---- own cell of this thread
-   const int i = tid >> 3, p = tid & 7;
-   const bool own = i < nc;
-   const int c = c0 + (own ? i : 0);
-   const int k = kc0 + 2 * p;
-   const size_t o = (size_t)c * K + k;
-   const int ne = own ? M.NEdgesOnCell[c] : 0;
-   const double InvA = 1.0 / M.AreaCell[c];
-   const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = HYP ? P.EddyDiff4 * InvA : 0.0;
-   double us[kME][2], ut[kME][2], cfu[kME], wa[kME], cd[kME], ch[kME];
+// One role's share of a row-set copy (h or one tracer) into a [row][16] buffer: item
+// q = t + 512 i is row q/8, 16-byte piece q%8, and lands at byte 16 q of the buffer.
+struct RowCopier {
+   int goff[3]; // element offset of the source piece inside one [cell][level] field
+   int n;
+   unsigned t16;
+   __device__ __forceinline__ void init(const TileSmem &S, int t, int nR, int K, int kc0) {
+      n = 0;
+      t16 = 16u * t;
 #pragma unroll
-   for (int j = 0; j < kME; ++j) {
-      us[j][0] = us[j][1] = ut[j][0] = ut[j][1] = 0.0;
-      cfu[j] = wa[j] = cd[j] = ch[j] = 0.0;
-      if (j < ne) {
-         const int e       = M.EdgesOnCell[c * M.MaxEdges + j];
-         const double sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
-         const double mask = M.EdgeMask[e], dve = M.DvEdge[e];
-         const double rdc  = dve / M.DcEdge[e];
-         // s*(phi(c1)-phi(c0)) == phi(self)-phi(nbr): sign and sgn of k_fC_center cancel exactly
-         cd[j]  = -k2 * (mask * (M.MeshScalingDel2[e] * rdc));
-         ch[j]  = -k4 * (mask * (M.MeshScalingDel4[e] * rdc));
-         cfu[j] = dve * sg;
-         wa[j]  = P.AdvOn ? mask * dve * sg : 0.0;
-         ldv<2>(us[j], P.Us + (size_t)e * K + k);
-         if (P.UTr == P.Us) {
-            ut[j][0] = us[j][0];
-            ut[j][1] = us[j][1];
-         } else {
-            ldv<2>(ut[j], P.UTr + (size_t)e * K + k);
+      for (int i = 0; i < 3; ++i) {
+         const int q = t + i * kTRole, r = q >> 3;
+         goff[i] = 0;
+         if (r < nR) {
+            goff[i] = S.GRow[r] * K + kc0 + 2 * (q & 7);
+            n       = i + 1;
          }
       }
    }
-   double hcur[2] = {1.0, 1.0}, hnext_old[2] = {1.0, 1.0};
-   const bool hcur_is_hs = P.First && P.Hcur == P.Hs;
-   if (own) {
-      if (!hcur_is_hs) ldp<2>(hcur, P.Hcur + o);
-      if (!P.First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+   __device__ __forceinline__ void copy(const double *F, const void *Dst) const {
+      const unsigned d = smem_u32(Dst) + t16;
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+         if (i < n) cp_async16(d + i * (16u * kTRole), F + goff[i]);
    }
+};
 
-   cp_wait<kTStages - 1>(); // h rows have landed (this thread's pieces)
-   __syncthreads();         // ... and everybody else's; tables are visible
+// =================== D role: Del2(phi) of own + ring-1 rows ===================
+// (TracerAuxVars.h:61-91; s*(phi(c1)-phi(c0)) == phi(self)-phi(nbr) exactly)
+__device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int tid) {
+   const int T = P.NTracers, K = M.K;
+   const size_t CS = (size_t)M.NCellsSize * K;
+   // the D role also feeds the pipeline: h, then tracer m+2 while it works on tracer m
+   RowCopier cp;
+   cp.init(S, X.t, X.nR, K, kc0);
+   cp.copy(P.Hs, &S.H[0][0]);
+   cp_commit();
+#pragma unroll
+   for (int s = 0; s < 2; ++s) {
+      if (s < T) cp.copy(P.Trs + s * CS, &S.Phi[s][0][0]);
+      cp_commit();
+   }
+   load_tables<2 * kTRole>(M, S, tid, X.nR1);
+   cp_wait<1>();    // h and phi_0 have landed (this thread's pieces)
+   __syncthreads(); // ... and everybody else's; tables are visible
+   unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
+   const int p = X.p;
+   unsigned nboff[kME];
+   {
+      const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
+#pragma unroll
+      for (int j = 0; j < kME; ++j) nboff[j] = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
+   }
+   const double InvA = S.InvA[X.li];
+   double cfA[kME][2];
+   {
+      const double2 hs = lds2(Hb, X.myoff);
+#pragma unroll
+      for (int j = 0; j < kME; ++j) {
+         const double2 hn = lds2(Hb, nboff[j]);
+         const double g   = S.G[X.li][j];
+         cfA[j][0]        = g * (0.5 * (hs.x + hn.x));
+         cfA[j][1]        = g * (0.5 * (hs.y + hn.y));
+      }
+   }
+   for (int m = 0; m < T; ++m) {
+      if (m > 0) {
+         cp_wait<1>();                  // phi_m has landed (this thread's pieces)
+         bar_sync(kBarDRole, kTRole);   // ... and the other D threads'
+      }
+      // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
+      if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
+      if (m + 2 < T) cp.copy(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(m + 2) % kTStages][0][0]);
+      cp_commit();
+      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[m % kTStages][0][0]);
+      unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
+      if (X.own) {
+         const double2 ts = lds2(Pb, X.myoff);
+         double d0 = 0, d1 = 0;
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const double2 tn = lds2(Pb, nboff[j]);
+            d0 -= cfA[j][0] * (ts.x - tn.x);
+            d1 -= cfA[j][1] * (ts.y - tn.y);
+         }
+         sts2(Db, X.myoff, d0 * InvA, d1 * InvA);
+      }
+      for (int q = X.t; q < X.n1 * kTLanes; q += kTRole) {
+         const int r       = X.nc + (q >> 3);
+         const unsigned ro = (r * kTKC + 2 * p) * 8u;
+         const double2 hr = lds2(Hb, ro), pr = lds2(Pb, ro);
+         const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[r][0]);
+         double e0 = 0, e1 = 0;
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const unsigned lo = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
+            const double2 hn = lds2(Hb, lo), pn = lds2(Pb, lo);
+            const double g   = S.G[r][j];
+            e0 -= g * (0.5 * (hr.x + hn.x)) * (pr.x - pn.x);
+            e1 -= g * (0.5 * (hr.y + hn.y)) * (pr.y - pn.y);
+         }
+         const double ia = S.InvA[r];
+         sts2(Db, ro, e0 * ia, e1 * ia);
+      }
+      bar_arrive(bar_d2_ready(m), 2 * kTRole); // phi_m and Del2(phi_m) are ready for the T role
+   }
+   cp_wait<0>();
+}
+
+// =================== T role: copies, thickness, tracer tendencies + RK updates ===================
+template <bool HYP, int STAGE>
+__device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int tid) {
+   constexpr int NT = HYP ? 2 * kTRole : kTRole;
+   constexpr bool First = STAGE == 0, Last = STAGE == 2; // stage kind: first, middle, last (RK4: 0 | 1,2 | 3)
+   const int K = M.K, T = P.NTracers, t = X.t, p = X.p, li = X.li;
+   const size_t CS = (size_t)M.NCellsSize * K;
+   const bool own  = X.own;
+   RowCopier cp; // without the D role this role feeds the pipeline itself
+   if (!HYP) {
+      cp.init(S, t, X.nR, K, kc0);
+      cp.copy(P.Hs, &S.H[0][0]);
+      cp_commit();
+#pragma unroll
+      for (int s = 0; s < kTStages - 1; ++s) {
+         if (s < T) cp.copy(P.Trs + s * CS, &S.Phi[s][0][0]);
+         cp_commit();
+      }
+   }
+   load_tables<NT>(M, S, tid, X.nR1);
+
+   const int c    = X.c0 + li;
+   const int k    = kc0 + 2 * p;
+   const size_t o = (size_t)c * K + k;
+   unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
+   // edge indices and velocity rows of the own cell: in flight while h lands
+   double us[kME][2], ut[kME][2];
+   {
+      int e[kME];
+#pragma unroll
+      for (int j = 0; j < kME; ++j) e[j] = M.Tiles.EocCell[(size_t)c * 6 + j];
+#pragma unroll
+      for (int j = 0; j < kME; ++j) ldv<2>(us[j], P.Us + (size_t)e[j] * K + k);
+      if (P.UTr != P.Us) {
+#pragma unroll
+         for (int j = 0; j < kME; ++j) ldv<2>(ut[j], P.UTr + (size_t)e[j] * K + k);
+      }
+   }
+   if (!HYP) cp_wait<kTStages - 2>(); // h and phi_0 have landed (this thread's pieces)
+   __syncthreads();                   // ... and everybody else's; tables are visible
 
    unsigned nboff[kME]; // byte offset of the neighbour's piece inside a [row][16] buffer
    {
-      const uint4 t = *reinterpret_cast<const uint4 *>(&S.Nbl[own ? i : 0][0]);
-      const unsigned w[3] = {t.x, t.y, t.z};
+      const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[li][0]);
+#pragma unroll
+      for (int j = 0; j < kME; ++j) nboff[j] = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
+   }
+   const unsigned myoff = X.myoff;
+   const double InvA    = S.InvA[li];
+   const double2 hs     = lds2(Hb, myoff);
+   // per-edge coefficients of the own cell (as k_fC_center, fused.cu):
+   //   tend = phi(self)*S0 + sum_j E_j*phi(nbr_j) + d2(self)*SH + sum_j ch_j*d2(nbr_j)
+   double E[kME][2], S0[2] = {0, 0}, SH = 0.0, hT[2] = {0, 0};
+   {
+      const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = HYP ? P.EddyDiff4 * InvA : 0.0;
+      const bool sameU = P.UTr == P.Us;
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
-         const unsigned l = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-         nboff[j]         = (l * kTKC + 2 * p) * 8u;
-      }
-   }
-   const unsigned myoff = ((own ? i : 0) * kTKC + 2 * p) * 8u;
-   const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
-   double E[kME][2], cfA[kME][2], S0[2] = {0, 0}, SH = 0.0, hT[2] = {0, 0};
-   double hs[2];
-   {
-      const double2 t = lds2(reinterpret_cast<const double *>(Hb + myoff));
-      hs[0] = t.x;
-      hs[1] = t.y;
-   }
+         const double2 hn2 = lds2(Hb, nboff[j]);
+         const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
+         const double g   = S.G[li][j];
+         const double cfu = M.Tiles.CfUCell[(size_t)c * 6 + j];
+         const double wa  = P.AdvOn ? M.Tiles.WaCell[(size_t)c * 6 + j] : 0.0;
+         const double cd = -k2 * g, ch = -k4 * g;
+         SH -= ch;
+         if (HYP && p == j) S.Ch[li][j] = ch;
 #pragma unroll
-   for (int j = 0; j < kME; ++j) {
-      const double2 hn2 = lds2(reinterpret_cast<const double *>(Hb + nboff[j]));
-      const double hn[2] = {hn2.x, hn2.y};
-      const double g     = S.G[own ? i : 0][j];
-      SH -= ch[j];
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-         const double mean = 0.5 * (hs[q] + hn[q]);
-         hT[q] += cfu[j] * mean * us[j][q] * InvA;
-         const double w = wa[j] * ut[j][q] * InvA;
-         const double D = cd[j] * mean;
-         E[j][q]        = 0.5 * hn[q] * w - D;
-         S0[q] += 0.5 * hs[q] * w + D;
-         cfA[j][q] = g * mean;
+         for (int q = 0; q < 2; ++q) {
+            const double mean = 0.5 * (hh[q] + hn[q]);
+            hT[q] += cfu * mean * us[j][q] * InvA;
+            const double w = wa * (sameU ? us[j][q] : ut[j][q]) * InvA;
+            const double D = cd * mean;
+            E[j][q]        = 0.5 * hn[q] * w - D;
+            S0[q] += 0.5 * hh[q] * w + D;
+         }
       }
    }
    if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
@@ -197,138 +294,157 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
       hT[0] += src;
       hT[1] += src;
    }
-   // ---- thickness updates (updateThicknessByTend, TimeStepper.cpp:378-405)
-   double hx[2], h2[2], rhp[2];
+   // ---- thickness updates (updateThicknessByTend, TimeStepper.cpp:378-405) and the
+   // per-level constants of the tracer updates (TimeStepper.cpp:446-524):
+   //   first stage : next = cur*w0 + B*tend          (w0 = weight thickness)
+   //   other stages: next = next + B*tend, last: next = (next + B*tend)*w0 (w0 = 1/h_final)
+   //   not last    : prov = cur*w1 + tend*w2         (w1 = h2/hprov, w2 = A/hprov)
+   double w0[2], w1[2], w2[2];
    {
-      double hnext[2], hprov[2];
+      double hcur[2] = {hs.x, hs.y}, hnext_old[2] = {1.0, 1.0}, hnext[2], hprov[2];
+      if (own) {
+         if (!(First && P.Hcur == P.Hs)) ldp<2>(hcur, P.Hcur + o);
+         if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+      }
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
-         if (hcur_is_hs) hcur[q] = hs[q];
-         hnext[q] = (P.First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
+         hnext[q] = (First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
          hprov[q] = hcur[q] + P.A * hT[q];
-         hx[q]    = P.First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
-         h2[q]    = P.H2Sel ? hnext[q] : hcur[q];
-         rhp[q]   = 1.0 / hprov[q];
+         const double hx  = First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
+         const double h2  = P.H2Sel ? hnext[q] : hcur[q];
+         const double rhp = 1.0 / hprov[q];
+         w0[q] = Last ? 1.0 / hx : hx;
+         w1[q] = h2 * rhp;
+         w2[q] = P.A * rhp;
       }
       if (own) {
          stv<2>(P.Hnext + o, hnext);
-         if (!P.Last) stv<2>(P.Hprov + o, hprov);
-      }
-      if (P.Last) {
-         rhp[0] = 1.0 / hx[0];
-         rhp[1] = 1.0 / hx[1];
+         if (!Last) stv<2>(P.Hprov + o, hprov);
       }
    }
 
    // ---- tracers
-   const bool tcur_is_ts = P.First && P.TrCur == P.Trs;
-   const bool need_cur   = !tcur_is_ts && (P.First || !P.Last);
+   const bool tcur_is_ts = First && P.TrCur == P.Trs;
+   const bool need_cur   = !tcur_is_ts && (First || !Last);
+   if (own && T > 0) { // lines of the first tracer's cur / next rows towards L2
+      if (need_cur) prefetch_row(P.TrCur + o, 2);
+      if (!First) prefetch_row(P.TrNext + o, 2);
+   }
    for (int l = 0; l < T; ++l) {
-      const int buf = l % kTStages;
-      cp_wait<kTStages - 2>();
-      __syncthreads(); // phi_l visible; every thread is done with tracer l-1
-      if (l + kTStages - 1 < T) copy_rows(P.Trs + (size_t)(l + kTStages - 1) * CS, &S.Phi[(l + kTStages - 1) % kTStages][0][0]);
-      cp_commit();
+      if (own && l + 1 < T) { // next tracer's lines towards L2; no register is held for them
+         if (need_cur) prefetch_row(P.TrCur + (size_t)(l + 1) * CS + o, 2);
+         if (!First) prefetch_row(P.TrNext + (size_t)(l + 1) * CS + o, 2);
+      }
+      if (HYP) {
+         bar_sync(bar_d2_ready(l), 2 * kTRole); // phi_l and Del2(phi_l) are complete
+      } else {
+         cp_wait<kTStages - 2>();
+         __syncthreads(); // phi_l visible; every thread is done with tracer l-1
+         if (l + kTStages - 1 < T) cp.copy(P.Trs + (size_t)(l + kTStages - 1) * CS, &S.Phi[(l + kTStages - 1) % kTStages][0][0]);
+         cp_commit();
+      }
       double tcur[2] = {0, 0}, acc[2] = {0, 0};
       if (own) {
-         if (need_cur) ldp<2>(tcur, P.TrCur + l * CS + o);
-         if (!P.First) ldp<2>(acc, P.TrNext + l * CS + o);
+         if (need_cur) ldp<2>(tcur, P.TrCur + (size_t)l * CS + o);
+         if (!First) ldp<2>(acc, P.TrNext + (size_t)l * CS + o);
       }
-      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[buf][0][0]);
-      const double2 ts2 = lds2(reinterpret_cast<const double *>(Pb + myoff));
-      const double ts[2] = {ts2.x, ts2.y};
-      double tend[2];
-      tend[0] = ts[0] * S0[0];
-      tend[1] = ts[1] * S0[1];
+      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[l % kTStages][0][0]);
+      const double2 ts = lds2(Pb, myoff);
+      double tend[2] = {ts.x * S0[0], ts.y * S0[1]};
+#pragma unroll
+      for (int j = 0; j < kME; ++j) {
+         const double2 tn = lds2(Pb, nboff[j]);
+         tend[0] += E[j][0] * tn.x;
+         tend[1] += E[j][1] * tn.y;
+      }
       if (HYP) {
-         // Del2(phi) of the own cell (TracerAuxVars.h:61-91) ...
-         double d[2] = {0, 0};
-#pragma unroll
-         for (int j = 0; j < kME; ++j) {
-            const double2 tn = lds2(reinterpret_cast<const double *>(Pb + nboff[j]));
-            d[0] -= cfA[j][0] * (ts[0] - tn.x);
-            d[1] -= cfA[j][1] * (ts[1] - tn.y);
-            tend[0] += E[j][0] * tn.x;
-            tend[1] += E[j][1] * tn.y;
-         }
-         d[0] *= InvA;
-         d[1] *= InvA;
-         if (own) *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(&S.D2[0][0]) + myoff) = make_double2(d[0], d[1]);
-         // ... and of one ring-1 row piece
-         for (int q = tid; q < n1 * kTLanes; q += kTThreads) {
-            const int r = nc + (q >> 3);
-            const unsigned ro = (r * kTKC + 2 * p) * 8u;
-            const double2 hr = lds2(reinterpret_cast<const double *>(Hb + ro));
-            const double2 pr = lds2(reinterpret_cast<const double *>(Pb + ro));
-            const uint4 t = *reinterpret_cast<const uint4 *>(&S.Nbl[r][0]);
-            const unsigned w[3] = {t.x, t.y, t.z};
-            double e0 = 0, e1 = 0;
-#pragma unroll
-            for (int j = 0; j < kME; ++j) {
-               const unsigned lo = (((w[j >> 1] >> ((j & 1) * 16)) & 0xffffu) * kTKC + 2 * p) * 8u;
-               const double2 hn = lds2(reinterpret_cast<const double *>(Hb + lo));
-               const double2 pn = lds2(reinterpret_cast<const double *>(Pb + lo));
-               const double g   = S.G[r][j];
-               e0 -= g * (0.5 * (hr.x + hn.x)) * (pr.x - pn.x);
-               e1 -= g * (0.5 * (hr.y + hn.y)) * (pr.y - pn.y);
-            }
-            const double ia = S.InvA[r];
-            *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(&S.D2[0][0]) + ro) = make_double2(e0 * ia, e1 * ia);
-         }
-         __syncthreads(); // Del2(phi) of own + ring-1 rows complete
-         const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[0][0]);
-         const double2 ds = lds2(reinterpret_cast<const double *>(Db + myoff));
+         const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
+         const double2 ds = lds2(Db, myoff);
          tend[0] += ds.x * SH;
          tend[1] += ds.y * SH;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 dn = lds2(reinterpret_cast<const double *>(Db + nboff[j]));
-            tend[0] += ch[j] * dn.x;
-            tend[1] += ch[j] * dn.y;
+            const double2 dn = lds2(Db, nboff[j]);
+            const double ch  = S.Ch[li][j];
+            tend[0] += ch * dn.x;
+            tend[1] += ch * dn.y;
          }
-      } else {
-#pragma unroll
-         for (int j = 0; j < kME; ++j) {
-            const double2 tn = lds2(reinterpret_cast<const double *>(Pb + nboff[j]));
-            tend[0] += E[j][0] * tn.x;
-            tend[1] += E[j][1] * tn.y;
-         }
+         if (l + 2 < T) bar_arrive(bar_d2_free(l), 2 * kTRole);
       }
-      // epilogue: weight / accumulate / provisional / finalise (TimeStepper.cpp:446-524)
       if (own) {
          double out[2];
+         if (tcur_is_ts) {
+            tcur[0] = ts.x;
+            tcur[1] = ts.y;
+         }
 #pragma unroll
          for (int q = 0; q < 2; ++q) {
-            if (tcur_is_ts) tcur[q] = ts[q];
-            const double base = P.First ? tcur[q] * hx[q] : acc[q];
-            out[q]            = base + P.B * tend[q];
-            if (P.Last) out[q] = out[q] * rhp[q];
+            out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
+            if (Last) out[q] *= w0[q];
          }
          stv<2>(P.TrNext + l * CS + o, out);
-         if (!P.Last) {
+         if (!Last) {
 #pragma unroll
-            for (int q = 0; q < 2; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) * rhp[q];
+            for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
             stv<2>(P.TrProv + l * CS + o, out);
          }
       }
    }
-   cp_wait<0>();
+   if (!HYP) cp_wait<0>();
+}
+
+template <bool HYP, int STAGE>
+__global__ void __launch_bounds__(HYP ? 2 * kTRole : kTRole, 1)
+k_fCT(DMesh M, CellArgs P, int NChunks) {
+   extern __shared__ __align__(16) unsigned char smem_raw[];
+   TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
+   constexpr int NT = HYP ? 2 * kTRole : kTRole;
+   const int tid = threadIdx.x;
+   const int tile = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
+
+   if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
+      reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
+   __syncthreads();
+   TileCtx X;
+   X.c0 = S.Hdr.C0; X.nc = S.Hdr.NC; X.n1 = S.Hdr.N1; X.nR1 = X.nc + X.n1; X.nR = X.nR1 + S.Hdr.N2;
+   for (int r = tid; r < X.nR; r += NT) S.GRow[r] = r < X.nc ? X.c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - X.nc];
+   __syncthreads();
+   X.t = tid & (kTRole - 1); X.i = X.t >> 3; X.p = X.t & 7;
+   X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
+   X.myoff = (X.li * kTKC + 2 * X.p) * 8u;
+   if (HYP) {
+      // 1024 threads leave 64 registers each: the T role needs more, the D role less
+      if (tid >= kTRole) {
+         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+         role_D(M, P, S, X, kc0, tid);
+      } else {
+         asm volatile("setmaxnreg.inc.sync.aligned.u32 72;");
+         role_T<true, STAGE>(M, P, S, X, kc0, tid);
+      }
+   } else {
+      role_T<false, STAGE>(M, P, S, X, kc0, tid);
+   }
 }
 
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
-int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    static bool attr = false;
    if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<HYP, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
       attr = true;
    }
    const int nch = D.K / kTKC;
    const unsigned grid = (unsigned)D.Tiles.NTiles * nch;
-   if (ca.HypOn) k_fCT<true><<<grid, kTThreads, sizeof(TileSmem), St>>>(D, ca, nch);
-   else k_fCT<false><<<grid, kTThreads, sizeof(TileSmem), St>>>(D, ca, nch);
+   k_fCT<HYP, STAGE><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, nch);
    return 0;
+}
+
+int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+   OMEGA_REQUIRE(!(ca.First && ca.Last), "launch_fCT: a stage cannot be both first and last");
+   const int stage = ca.First ? 0 : (ca.Last ? 2 : 1);
+   if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St) : launch_fCT_t<true, 2>(D, ca, St);
+   return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St) : launch_fCT_t<false, 2>(D, ca, St);
 }
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }

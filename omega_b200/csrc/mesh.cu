@@ -113,7 +113,8 @@ static std::vector<int> gather_index_rows(const int *src, const std::vector<int>
 static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vector<int> &nec,
                        const std::vector<int> &eoc, const std::vector<int> &coe,
                        const std::vector<double> &mask, const std::vector<double> &dv,
-                       const std::vector<double> &dc, const std::vector<double> &area) {
+                       const std::vector<double> &dc, const std::vector<double> &area,
+                       const std::vector<double> &sign, int NE) {
    DTiles &T = M->D.Tiles;
    std::memset(&T, 0, sizeof(T));
    if (M->MaxEdgesUsed > 6) return 0;
@@ -180,12 +181,17 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
       for (int n : r2) loc[n] = -1;
       c0 += nc;
    }
-   std::vector<double> g((size_t)(NC + 1) * 6, 0.0), ia(NC + 1, 0.0);
+   std::vector<double> g((size_t)(NC + 1) * 6, 0.0), ia(NC + 1, 0.0), cfu(g), wa(g);
+   std::vector<int> eoc6((size_t)(NC + 1) * 6, NE);
    for (int c = 0; c < NC; ++c) {
       ia[c] = 1.0 / area[c];
       for (int j = 0; j < nec[c]; ++j) {
          const int e = eoc[(size_t)c * ME + j];
-         g[(size_t)c * 6 + j] = mask[e] * (dv[e] / dc[e]);
+         const double sg = sign[(size_t)c * ME + j];
+         g[(size_t)c * 6 + j]    = mask[e] * (dv[e] / dc[e]);
+         cfu[(size_t)c * 6 + j]  = dv[e] * sg;
+         wa[(size_t)c * 6 + j]   = mask[e] * dv[e] * sg;
+         eoc6[(size_t)c * 6 + j] = e;
       }
    }
    int rc = 0;
@@ -194,6 +200,9 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    rc |= to_device(M, nbl, &T.Nbl);
    rc |= to_device(M, g, &T.GCell);
    rc |= to_device(M, ia, &T.InvAreaCell);
+   rc |= to_device(M, cfu, &T.CfUCell);
+   rc |= to_device(M, wa, &T.WaCell);
+   rc |= to_device(M, eoc6, &T.EocCell);
    T.NTiles = rc ? 0 : (int)hdr.size();
    return rc;
 }
@@ -387,7 +396,8 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
       rc |= build_tiles(M, NC, D->NCellsOwned, ME, gather_rows(D->NEdgesOnCell, PC, 1),
                         gather_index_rows(D->EdgesOnCell, PC, ME, IE), coe,
                         gather_rows(M->EdgeMaskH.data(), PE, 1), gather_rows(D->DvEdge, PE, 1),
-                        gather_rows(D->DcEdge, PE, 1), gather_rows(D->AreaCell, PC, 1));
+                        gather_rows(D->DcEdge, PE, 1), gather_rows(D->AreaCell, PC, 1),
+                        gather_rows(M->EdgeSignOnCellH.data(), PC, ME), NE);
    for (int kind = 0; kind < 3; ++kind) {
       const int *p = nullptr;
       rc |= to_device(M, M->Perm[kind], &p);

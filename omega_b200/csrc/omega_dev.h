@@ -49,6 +49,9 @@ struct DTiles {
    const int *HaloRows;       // ring-1 then ring-2 rows of every tile (device cell index)
    const unsigned short *Nbl; // [own + ring-1 rows][8]: local row of the cell across edge j (self when none)
    const double *GCell;       // [NCellsSize][6]  EdgeMask*DvEdge/DcEdge of edge j of the cell, 0 when none
+   const double *CfUCell;     // [NCellsSize][6]  DvEdge*EdgeSignOnCell
+   const double *WaCell;      // [NCellsSize][6]  EdgeMask*DvEdge*EdgeSignOnCell
+   const int *EocCell;        // [NCellsSize][6]  EdgesOnCell, boundary slot when none
    const double *InvAreaCell; // [NCellsSize], 0 in the boundary slot
 };
 

@@ -86,10 +86,18 @@ def test_aux_and_tendencies_one_rhs(case, reorder):
     dtr = mesh.to_device(capi.ON_CELL, tr) if T else None
     st.computeAllTendencies(dh, du, dtr, 0.0)
     aux = st.aux_to_host()
+    # the TC5 flow is non-divergent: VelocityDivCell (and Del2DivCell) are cancellation residue
+    # (>= 1000x below the terms that cancel), so their error is measured against the size of
+    # those terms (|u|/dc, |u|/dc^3) instead of against the residue itself
+    dc, umax = float(np.mean(L.DcEdge[:-1])), float(np.abs(u).max())
+    floor = {"VelocityDivCell": umax / dc, "Del2DivCell": umax / dc**3}
     for n in capi.AUX_FIELDS:
         if n in ("ZonalStressCell", "MeridStressCell", "NormalStressEdge"):
             continue
-        assert rel_max(aux[n], o.aux[n]) <= TOL_TEND, (name, n, rel_max(aux[n], o.aux[n]))
+        err = rel_max(aux[n], o.aux[n])
+        if n in floor and np.abs(o.aux[n]).max() < 1e-3 * floor[n]:
+            err = np.abs(aux[n] - o.aux[n]).max() / floor[n]
+        assert err <= TOL_TEND, (name, n, err)
     tend = st.tend_to_host()
     for n in tend:
         assert rel_max(tend[n], o.tend[n]) <= TOL_TEND, (name, n, rel_max(tend[n], o.tend[n]))
