@@ -25,6 +25,8 @@
 // (TendencyTerms.h:35-58,349-480, TracerAuxVars.h:25-91,
 // LayerThicknessAuxVars.h:25-61, TimeStepper.cpp:378-524); MeshScalingDel2/4
 // are 1 (HorzMesh.cpp:604-626), which the per-cell tables assume.
+#include <cstdlib>
+
 #include "fused_args.h"
 #include "kernel_util.cuh"
 #include "omega_dev.h"
@@ -41,8 +43,10 @@ struct TileSmem {
    double H[kTileRows][kTKC];
    double Phi[kTStages][kTileRows][kTKC];
    double D2[2][kTileRows1][kTKC];
+   double Cf1[kTileRing1][6][kTKC]; // ring-1 rows: G * mean thickness per edge (private to the thread that uses it)
    double G[kTileRows1][6];
    double Ch[kTileCells][6];
+   double CfU[kTileCells][6], Wa[kTileCells][6]; // own rows: dv*sign, mask*dv*sign per edge
    double InvA[kTileRows1];
    unsigned short Nbl[kTileRows1][8];
    int GRow[kTileRows];
@@ -88,7 +92,12 @@ struct TileCtx {
 
 // static tables of the own + ring-1 rows (all threads of the CTA take part)
 template <int NT>
-__device__ __forceinline__ void load_tables(const DMesh &M, TileSmem &S, int tid, int nR1) {
+__device__ __forceinline__ void load_tables(const DMesh &M, TileSmem &S, int tid, int nR1, int nc) {
+   for (int q = tid; q < nc * 6; q += NT) {
+      const size_t g = (size_t)S.Hdr.C0 * 6 + q;
+      (&S.CfU[0][0])[q] = M.Tiles.CfUCell[g];
+      (&S.Wa[0][0])[q]  = M.Tiles.WaCell[g];
+   }
    for (int q = tid; q < nR1 * 6; q += NT) {
       const int r = q / 6, j = q - r * 6;
       S.G[r][j] = M.Tiles.GCell[(size_t)S.GRow[r] * 6 + j];
@@ -132,37 +141,66 @@ struct RowCopier {
 __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int tid) {
    const int T = P.NTracers, K = M.K;
    const size_t CS = (size_t)M.NCellsSize * K;
-   // the D role also feeds the pipeline: h, then tracer m+2 while it works on tracer m
-   RowCopier cp;
-   cp.init(S, X.t, X.nR, K, kc0);
-   cp.copy(P.Hs, &S.H[0][0]);
+   // The D role also feeds the pipeline: h, then tracer m+2 while it works on tracer m.
+   // Item q = t + 512 i of a row-set copy is row q/8, 16-byte piece q%8, and lands at byte
+   // 16 q of the [row][16] buffer; source offsets are re-derived from GRow on every copy
+   // (three shared loads) rather than held in registers.
+   const int t = X.t, p = X.p;
+   auto copy_rows = [&](const double *F, const void *Dst) {
+      const unsigned d = smem_u32(Dst) + 16u * t;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+         const int r = (t >> 3) + i * (kTRole / kTLanes);
+         if (r < X.nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc0 + 2 * p));
+      }
+   };
+   copy_rows(P.Hs, &S.H[0][0]);
    cp_commit();
 #pragma unroll
    for (int s = 0; s < 2; ++s) {
-      if (s < T) cp.copy(P.Trs + s * CS, &S.Phi[s][0][0]);
+      if (s < T) copy_rows(P.Trs + s * CS, &S.Phi[s][0][0]);
       cp_commit();
    }
-   load_tables<2 * kTRole>(M, S, tid, X.nR1);
+   load_tables<2 * kTRole>(M, S, tid, X.nR1, X.nc);
    cp_wait<1>();    // h and phi_0 have landed (this thread's pieces)
    __syncthreads(); // ... and everybody else's; tables are visible
    unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
-   const int p = X.p;
-   unsigned nboff[kME];
+   // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
+   unsigned nb2[3];
    {
       const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
 #pragma unroll
-      for (int j = 0; j < kME; ++j) nboff[j] = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
+      for (int j = 0; j < 3; ++j)
+         nb2[j] = ((nbl_get(tt, 2 * j) * kTKC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * kTKC + 2 * p) * 8u) << 16);
    }
-   const double InvA = S.InvA[X.li];
+   // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
    double cfA[kME][2];
    {
+      const double nia = -S.InvA[X.li];
       const double2 hs = lds2(Hb, X.myoff);
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
-         const double2 hn = lds2(Hb, nboff[j]);
-         const double g   = S.G[X.li][j];
+         const double2 hn = lds2(Hb, (j & 1) ? nb2[j >> 1] >> 16 : nb2[j >> 1] & 0xffffu);
+         const double g   = S.G[X.li][j] * nia;
          cfA[j][0]        = g * (0.5 * (hs.x + hn.x));
          cfA[j][1]        = g * (0.5 * (hs.y + hn.y));
+      }
+   }
+   // the ring-1 row piece of this thread (n1 <= 56 rows x 8 pieces < 512 threads): the same
+   // coefficients, kept in shared memory (private to this thread) for all tracers
+   const bool ring = t < X.n1 * kTLanes;
+   const int r1    = X.nc + (ring ? X.i : 0);
+   const unsigned ro1 = (r1 * kTKC + 2 * p) * 8u;
+   unsigned char *Cb  = reinterpret_cast<unsigned char *>(&S.Cf1[ring ? X.i : 0][0][0]) + 16u * p;
+   if (ring) {
+      const double nia = -S.InvA[r1];
+      const double2 hr = lds2(Hb, ro1);
+      const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[r1][0]);
+#pragma unroll
+      for (int j = 0; j < kME; ++j) {
+         const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+         const double g   = S.G[r1][j] * nia;
+         sts2(Cb, j * (kTKC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
       }
    }
    for (int m = 0; m < T; ++m) {
@@ -172,7 +210,7 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
       }
       // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
       if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
-      if (m + 2 < T) cp.copy(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(m + 2) % kTStages][0][0]);
+      if (m + 2 < T) copy_rows(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(m + 2) % kTStages][0][0]);
       cp_commit();
       const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[m % kTStages][0][0]);
       unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
@@ -181,28 +219,24 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
          double d0 = 0, d1 = 0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 tn = lds2(Pb, nboff[j]);
-            d0 -= cfA[j][0] * (ts.x - tn.x);
-            d1 -= cfA[j][1] * (ts.y - tn.y);
+            const double2 tn = lds2(Pb, (j & 1) ? nb2[j >> 1] >> 16 : nb2[j >> 1] & 0xffffu);
+            d0 += cfA[j][0] * (ts.x - tn.x);
+            d1 += cfA[j][1] * (ts.y - tn.y);
          }
-         sts2(Db, X.myoff, d0 * InvA, d1 * InvA);
+         sts2(Db, X.myoff, d0, d1);
       }
-      for (int q = X.t; q < X.n1 * kTLanes; q += kTRole) {
-         const int r       = X.nc + (q >> 3);
-         const unsigned ro = (r * kTKC + 2 * p) * 8u;
-         const double2 hr = lds2(Hb, ro), pr = lds2(Pb, ro);
-         const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[r][0]);
+      if (ring) {
+         const double2 pr = lds2(Pb, ro1);
+         const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[r1][0]);
          double e0 = 0, e1 = 0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const unsigned lo = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
-            const double2 hn = lds2(Hb, lo), pn = lds2(Pb, lo);
-            const double g   = S.G[r][j];
-            e0 -= g * (0.5 * (hr.x + hn.x)) * (pr.x - pn.x);
-            e1 -= g * (0.5 * (hr.y + hn.y)) * (pr.y - pn.y);
+            const double2 pn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+            const double2 cf = lds2(Cb, j * (kTKC * 8u));
+            e0 += cf.x * (pr.x - pn.x);
+            e1 += cf.y * (pr.y - pn.y);
          }
-         const double ia = S.InvA[r];
-         sts2(Db, ro, e0 * ia, e1 * ia);
+         sts2(Db, ro1, e0, e1);
       }
       bar_arrive(bar_d2_ready(m), 2 * kTRole); // phi_m and Del2(phi_m) are ready for the T role
    }
@@ -228,7 +262,7 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          cp_commit();
       }
    }
-   load_tables<NT>(M, S, tid, X.nR1);
+   load_tables<NT>(M, S, tid, X.nR1, X.nc);
 
    const int c    = X.c0 + li;
    const int k    = kc0 + 2 * p;
@@ -247,15 +281,24 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          for (int j = 0; j < kME; ++j) ldv<2>(ut[j], P.UTr + (size_t)e[j] * K + k);
       }
    }
+   double hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
+   const bool hcur_is_hs = First && P.Hcur == P.Hs;
+   if (own) {
+      if (!hcur_is_hs) ldp<2>(hcur, P.Hcur + o);
+      if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+   }
    if (!HYP) cp_wait<kTStages - 2>(); // h and phi_0 have landed (this thread's pieces)
    __syncthreads();                   // ... and everybody else's; tables are visible
 
-   unsigned nboff[kME]; // byte offset of the neighbour's piece inside a [row][16] buffer
+   // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
+   unsigned nb2[3];
    {
       const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[li][0]);
 #pragma unroll
-      for (int j = 0; j < kME; ++j) nboff[j] = (nbl_get(tt, j) * kTKC + 2 * p) * 8u;
+      for (int j = 0; j < 3; ++j)
+         nb2[j] = ((nbl_get(tt, 2 * j) * kTKC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * kTKC + 2 * p) * 8u) << 16);
    }
+#define NBOFF(j) (((j) & 1) ? nb2[(j) >> 1] >> 16 : nb2[(j) >> 1] & 0xffffu)
    const unsigned myoff = X.myoff;
    const double InvA    = S.InvA[li];
    const double2 hs     = lds2(Hb, myoff);
@@ -267,14 +310,14 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
       const bool sameU = P.UTr == P.Us;
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
-         const double2 hn2 = lds2(Hb, nboff[j]);
+         const double2 hn2 = lds2(Hb, NBOFF(j));
          const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
          const double g   = S.G[li][j];
-         const double cfu = M.Tiles.CfUCell[(size_t)c * 6 + j];
-         const double wa  = P.AdvOn ? M.Tiles.WaCell[(size_t)c * 6 + j] : 0.0;
+         const double cfu = S.CfU[li][j];
+         const double wa  = P.AdvOn ? S.Wa[li][j] : 0.0;
          const double cd = -k2 * g, ch = -k4 * g;
          SH -= ch;
-         if (HYP && p == j) S.Ch[li][j] = ch;
+         if (HYP && own && p == j) S.Ch[li][j] = ch;
 #pragma unroll
          for (int q = 0; q < 2; ++q) {
             const double mean = 0.5 * (hh[q] + hn[q]);
@@ -301,10 +344,10 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
    //   not last    : prov = cur*w1 + tend*w2         (w1 = h2/hprov, w2 = A/hprov)
    double w0[2], w1[2], w2[2];
    {
-      double hcur[2] = {hs.x, hs.y}, hnext_old[2] = {1.0, 1.0}, hnext[2], hprov[2];
-      if (own) {
-         if (!(First && P.Hcur == P.Hs)) ldp<2>(hcur, P.Hcur + o);
-         if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+      double hnext[2], hprov[2];
+      if (hcur_is_hs || !own) {
+         hcur[0] = hs.x;
+         hcur[1] = hs.y;
       }
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -326,15 +369,14 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
    // ---- tracers
    const bool tcur_is_ts = First && P.TrCur == P.Trs;
    const bool need_cur   = !tcur_is_ts && (First || !Last);
-   if (own && T > 0) { // lines of the first tracer's cur / next rows towards L2
-      if (need_cur) prefetch_row(P.TrCur + o, 2);
-      if (!First) prefetch_row(P.TrNext + o, 2);
+   // cur / next of tracer l are loaded at the END of iteration l-1 (their registers are dead
+   // by then), so they are in flight during the barrier wait and the stencil of iteration l
+   double tcur[2] = {0, 0}, acc[2] = {0, 0};
+   if (own && T > 0) {
+      if (need_cur) ldp<2>(tcur, P.TrCur + o);
+      if (!First) ldp<2>(acc, P.TrNext + o);
    }
    for (int l = 0; l < T; ++l) {
-      if (own && l + 1 < T) { // next tracer's lines towards L2; no register is held for them
-         if (need_cur) prefetch_row(P.TrCur + (size_t)(l + 1) * CS + o, 2);
-         if (!First) prefetch_row(P.TrNext + (size_t)(l + 1) * CS + o, 2);
-      }
       if (HYP) {
          bar_sync(bar_d2_ready(l), 2 * kTRole); // phi_l and Del2(phi_l) are complete
       } else {
@@ -343,17 +385,12 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          if (l + kTStages - 1 < T) cp.copy(P.Trs + (size_t)(l + kTStages - 1) * CS, &S.Phi[(l + kTStages - 1) % kTStages][0][0]);
          cp_commit();
       }
-      double tcur[2] = {0, 0}, acc[2] = {0, 0};
-      if (own) {
-         if (need_cur) ldp<2>(tcur, P.TrCur + (size_t)l * CS + o);
-         if (!First) ldp<2>(acc, P.TrNext + (size_t)l * CS + o);
-      }
       const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[l % kTStages][0][0]);
       const double2 ts = lds2(Pb, myoff);
       double tend[2] = {ts.x * S0[0], ts.y * S0[1]};
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
-         const double2 tn = lds2(Pb, nboff[j]);
+         const double2 tn = lds2(Pb, NBOFF(j));
          tend[0] += E[j][0] * tn.x;
          tend[1] += E[j][1] * tn.y;
       }
@@ -364,7 +401,7 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          tend[1] += ds.y * SH;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 dn = lds2(Db, nboff[j]);
+            const double2 dn = lds2(Db, NBOFF(j));
             const double ch  = S.Ch[li][j];
             tend[0] += ch * dn.x;
             tend[1] += ch * dn.y;
@@ -388,12 +425,18 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
             for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
             stv<2>(P.TrProv + l * CS + o, out);
          }
+         if (l + 1 < T) {
+            if (need_cur) ldp<2>(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
+            if (!First) ldp<2>(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+         }
       }
    }
    if (!HYP) cp_wait<0>();
 }
 
-template <bool HYP, int STAGE>
+#undef NBOFF
+
+template <bool HYP, int STAGE, int RS = 0>
 __global__ void __launch_bounds__(HYP ? 2 * kTRole : kTRole, 1)
 k_fCT(DMesh M, CellArgs P, int NChunks) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -415,10 +458,14 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
    if (HYP) {
       // 1024 threads leave 64 registers each: the T role needs more, the D role less
       if (tid >= kTRole) {
-         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+         if (RS == 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+         if (RS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+         if (RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
          role_D(M, P, S, X, kc0, tid);
       } else {
-         asm volatile("setmaxnreg.inc.sync.aligned.u32 72;");
+         if (RS == 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 72;");
+         if (RS == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
+         if (RS == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 64;");
          role_T<true, STAGE>(M, P, S, X, kc0, tid);
       }
    } else {
@@ -428,16 +475,22 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
 
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
-template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    static bool attr = false;
    if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<HYP, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<HYP, STAGE, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
       attr = true;
    }
    const int nch = D.K / kTKC;
    const unsigned grid = (unsigned)D.Tiles.NTiles * nch;
-   k_fCT<HYP, STAGE><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, nch);
+   k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, nch);
    return 0;
+}
+template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+   static const int rs = getenv("OMEGA_TILE_REGS") ? atoi(getenv("OMEGA_TILE_REGS")) : 0;
+   if (HYP && rs == 1) return launch_fCT_r<HYP, STAGE, HYP ? 1 : 0>(D, ca, St);
+   if (HYP && rs == 2) return launch_fCT_r<HYP, STAGE, HYP ? 2 : 0>(D, ca, St);
+   return launch_fCT_r<HYP, STAGE, 0>(D, ca, St);
 }
 
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {

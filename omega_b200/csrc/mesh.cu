@@ -149,14 +149,14 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
                   if (loc[m] < 0) { loc[m] = 1 << 21; r2.push_back(m); }
                }
          std::sort(r2.begin(), r2.end());
-         const bool ok = nc + (int)r1.size() <= kTileRows1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows;
+         const bool ok = (int)r1.size() <= kTileRing1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows;
          if (ok || nc == 1) break;
          for (int i = 0; i < nc; ++i) loc[c0 + i] = -1;
          for (int n : r1) loc[n] = -1;
          for (int n : r2) loc[n] = -1;
          nc = std::max(1, nc * 3 / 4);
       }
-      if (nc + (int)r1.size() > kTileRows1 || nc + (int)r1.size() + (int)r2.size() > kTileRows) {
+      if ((int)r1.size() > kTileRing1 || nc + (int)r1.size() + (int)r2.size() > kTileRows) {
          set_error("build_tiles: a single cell exceeds the tile row caps");
          return 2;
       }

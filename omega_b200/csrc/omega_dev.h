@@ -35,7 +35,8 @@ void set_error(const std::string &msg);
 // tile: own cells [0,nc), ring 1 [nc,nc+n1), ring 2 [nc+n1,nc+n1+n2); the
 // boundary slot (row NCellsAll, all zero) appears as an ordinary ring row.
 constexpr int kTileCells = 64;  // own cells per tile (fewer when a cap below would be exceeded)
-constexpr int kTileRows1 = 120; // cap on own + ring-1 rows
+constexpr int kTileRing1 = 56;  // cap on ring-1 rows
+constexpr int kTileRows1 = kTileCells + kTileRing1; // cap on own + ring-1 rows
 constexpr int kTileRows  = 176; // cap on own + ring-1 + ring-2 rows
 struct TileHdr {
    int C0, NC, N1, N2; // first own cell, counts
