@@ -60,7 +60,8 @@ __device__ __forceinline__ void cta_rows(int N, int &r0, int &n) {
 template <int V>
 __global__ void __launch_bounds__(kBlock)
 k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double *__restrict__ KE,
-     double *__restrict__ Div, double *__restrict__ RelVort, double *__restrict__ PVv) {
+     double *__restrict__ Div, double *__restrict__ RelVort, double *__restrict__ PVv, int XMode, double aKE,
+     double aSSH) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
@@ -80,6 +81,15 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
             ke[q] += kcoef * u[q] * u[q];
             dv[q] -= dcoef * u[q];
          }
+      }
+      if (XMode) {
+         // tiled edge pass: KE and SSH gradients share (X(c1)-X(c0))/dc, X = aKE*KE + aSSH*g*(h - b)
+         // (KEGradOnEdge, SSHGradOnEdge, TendencyTerms.h:127-173; LayerThicknessAuxVars.h:63-82)
+         double h[V];
+         ldv<V>(h, H + (size_t)c * M.K + k);
+         const double b = M.BottomDepth[c];
+#pragma unroll
+         for (int q = 0; q < V; ++q) ke[q] = aKE * ke[q] + aSSH * (9.80665 * (h[q] - b));
       }
       stv<V>(KE + (size_t)c * M.K + k, ke);
       stv<V>(Div + (size_t)c * M.K + k, dv);
@@ -142,7 +152,8 @@ __device__ __forceinline__ void del2_edge(const DMesh &M, int e, int k, const do
 template <int V>
 __global__ void __launch_bounds__(kBlock)
 k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort,
-     double *__restrict__ Del2Div, double *__restrict__ Del2RelVort) {
+     double *__restrict__ Del2Div, double *__restrict__ Del2RelVort, int YMode, double Nu2, double Nu4Div,
+     double Nu4) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
@@ -158,6 +169,15 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
 #pragma unroll
          for (int q = 0; q < V; ++q) t[q] -= cf * d2[q];
       }
+      if (YMode) {
+         // tiled edge pass: Del2 and Del4 velocity terms share one difference per element kind,
+         // Y(c) = nu2*Div - nu4*DivFactor*Del2Div, Z(v) = nu2*RelVort - nu4*Del2RelVort
+         // (VelocityDiffusionOnEdge, VelocityHyperDiffOnEdge, TendencyTerms.h:195-269)
+         double d[V];
+         ldv<V>(d, Div + (size_t)c * M.K + k);
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * d[q] - Nu4Div * t[q];
+      }
       stv<V>(Del2Div + (size_t)c * M.K + k, t);
    }
    cta_rows(M.NVerticesAll, r0, n);
@@ -172,6 +192,12 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
          del2_edge<V>(M, e, k, Div, RelVort, d2);
 #pragma unroll
          for (int q = 0; q < V; ++q) t[q] += cf * d2[q];
+      }
+      if (YMode) {
+         double z[V];
+         ldv<V>(z, RelVort + (size_t)v * M.K + k);
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * z[q] - Nu4 * t[q];
       }
       stv<V>(Del2RelVort + (size_t)v * M.K + k, t);
    }
@@ -806,8 +832,16 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
       ++S->Launches;                                                    \
    } while (0)
-      LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort);
-      if (vel4) LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort);
+      // shared-memory staged edge pass (fused_tile.cu) replaces fE when it applies; fA / fB then
+      // write the combined fields it differences
+      const bool tiledE = V == 2 && tile_edge_path_ok(D) && !G.FluxThicknessType && !G.WindForcingTendencyEnable &&
+                          !G.BottomDragTendencyEnable && !G.ManufacturedSolutionTendency && env_int("OMEGA_TILE_E", 1);
+      const double nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
+      LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
+               G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0);
+      if (vel4)
+         LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
+                  G.ViscDel4 * G.DivFactor, G.ViscDel4);
       // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
       const bool tiled = !upw && V == 2 && T > 0 && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
       if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
@@ -858,7 +892,18 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
       ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
       ea.G = G; ea.MS = ca.MS;
-      {
+      if (tiledE) {
+         ScopedTimer tm_(S, St, kFE);
+         EdgeTileArgs ta;
+         ta.Us = Us; ta.Hs = Hs; ta.PVv = S->A.NormRelVort; ta.X = S->A.KE;
+         ta.Y = vel4 ? S->A.Del2Div : S->A.Div; ta.Z = vel4 ? S->A.Del2RelVort : S->A.RelVort;
+         ta.SY = vel4 ? 1.0 : nu2; ta.SZ = ta.SY;
+         ta.Ucur = Ucur; ta.Unext = Unext; ta.Uprov = Up;
+         ta.A = ca.A; ta.B = ca.B; ta.First = ca.First; ta.Last = ca.Last;
+         ta.PVOn = G.PVTendencyEnable; ta.XOn = G.KETendencyEnable || G.SSHTendencyEnable;
+         if (launch_fET(D, ta, St)) return 1;
+         ++S->Launches;
+      } else {
          // occupancy variants measured on B200 (profiles/r01): 4 CTAs/SM (64 regs, some spills) is fastest
          const int fev = env_int("OMEGA_FE_VARIANT", 3);
          ScopedTimer tm_(S, St, kFE);

@@ -34,8 +34,21 @@ struct EdgeArgs {
    ManufacturedParams MS;
 };
 
+// tiled edge pass: tend = m*PV term + m*[(-(X1-X0) + SY*(Y1-Y0))/dc - SZ*(Z1-Z0)/dv]
+struct EdgeTileArgs {
+   const double *Us, *Hs, *PVv; // stage velocity / thickness, PV on vertices
+   const double *X, *Y, *Z;     // combined cell / cell / vertex fields written by fA and fB
+   double SY, SZ;
+   const double *Ucur;
+   double *Unext, *Uprov;
+   double A, B;
+   int First, Last, PVOn, XOn;
+};
+
 // fused_tile.cu
 bool tile_path_ok(const DMesh &D);
+bool tile_edge_path_ok(const DMesh &D);
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St);
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St);
 
 } // namespace omega

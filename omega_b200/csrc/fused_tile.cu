@@ -502,4 +502,128 @@ int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
 
+// ---------------------------------------------------------------------------
+// k_fET: shared-memory staged edge pass (the work of k_fE, fused.cu).  A CTA owns the
+// edges of one tile x 16 levels.  PotentialVortHAdvOnEdge (TendencyTerms.h:81-108) sums
+// w_j * F(e_j) * (q(e) + q(e_j))/2 over up to 10 neighbour edges, with
+//   F(e) = FluxLayerThickEdge(e) * u(e)   (LayerThicknessAuxVars.h:25-61, centred)
+//   q(e) = NormRelVortEdge + NormPlanetVortEdge   (VorticityAuxVars.h:61-76)
+// each needing five gathered rows: pass 1 evaluates F and q ONCE per staged edge of the
+// tile (every edge of the own + ring-1 cells) into shared memory, pass 2 does the sum for
+// the own edges from shared memory through precomputed local indices.  The gradient and
+// diffusion terms difference the combined fields X, Y, Z that fA / fB write (see there),
+// six gathered rows instead of twelve.  updateVelocityByTend (TimeStepper.cpp:407-430) is
+// the epilogue, as in k_fE.
+// ---------------------------------------------------------------------------
+constexpr int kEThreads = 512;
+
+struct ETileSmem {
+   double F[kTileEdges][kTKC];
+   double Q[kTileEdges][kTKC];
+   int SRow[kTileEdges];
+   unsigned short EoE[kTileEdgesOwn][12];
+   TileHdr Hdr;
+};
+
+__global__ void __launch_bounds__(kEThreads, 2)
+k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
+   extern __shared__ __align__(16) unsigned char smem_raw[];
+   ETileSmem &S = *reinterpret_cast<ETileSmem *>(smem_raw);
+   const int tid = threadIdx.x;
+   const int tile = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
+   const int K = M.K;
+   if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
+      reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
+   __syncthreads();
+   const int nOwn = S.Hdr.NEOwn, nSt = S.Hdr.NEStaged;
+   for (int r = tid; r < nSt; r += kEThreads) S.SRow[r] = M.Tiles.EdgeRows[S.Hdr.ERowOff + r];
+   {
+      const unsigned *src = reinterpret_cast<const unsigned *>(M.Tiles.EoELocal + (size_t)S.Hdr.EoEOff * 12);
+      unsigned *dst       = reinterpret_cast<unsigned *>(&S.EoE[0][0]);
+      for (int q = tid; q < nOwn * 6; q += kEThreads) dst[q] = src[q];
+   }
+   __syncthreads();
+   const int p = tid & 7, k = kc0 + 2 * p;
+   // ---- pass 1: F and q of every staged edge
+   for (int q = tid; q < nSt * kTLanes; q += kEThreads) {
+      const int r = q >> 3, e = S.SRow[r];
+      const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
+      double u[2], h0[2], h1[2], a[2], b[2];
+      ldv<2>(u, P.Us + (size_t)e * K + k);
+      ldv<2>(h0, P.Hs + (size_t)cc.x * K + k);
+      ldv<2>(h1, P.Hs + (size_t)cc.y * K + k);
+      ldv<2>(a, P.PVv + (size_t)vv.x * K + k);
+      ldv<2>(b, P.PVv + (size_t)vv.y * K + k);
+      *reinterpret_cast<double2 *>(&S.F[r][2 * p]) = make_double2(0.5 * (h0[0] + h1[0]) * u[0], 0.5 * (h0[1] + h1[1]) * u[1]);
+      *reinterpret_cast<double2 *>(&S.Q[r][2 * p]) = make_double2(0.5 * (a[0] + b[0]), 0.5 * (a[1] + b[1]));
+   }
+   __syncthreads();
+   // ---- pass 2: own edges
+   const unsigned char *Fb = reinterpret_cast<const unsigned char *>(&S.F[0][0]);
+   const unsigned char *Qb = reinterpret_cast<const unsigned char *>(&S.Q[0][0]);
+   for (int q = tid; q < nOwn * kTLanes; q += kEThreads) {
+      const int r = q >> 3, e = S.SRow[r];
+      const size_t o = (size_t)e * K + k;
+      const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
+      const double mask = M.EdgeMask[e];
+      const double InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
+      // the gathered rows of the gradient / diffusion terms and the RK operands: in flight
+      // while the neighbour sum runs from shared memory
+      double x0[2], x1[2], y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
+      ldv<2>(x0, P.X + (size_t)cc.x * K + k);
+      ldv<2>(x1, P.X + (size_t)cc.y * K + k);
+      ldv<2>(y0, P.Y + (size_t)cc.x * K + k);
+      ldv<2>(y1, P.Y + (size_t)cc.y * K + k);
+      ldv<2>(z0, P.Z + (size_t)vv.x * K + k);
+      ldv<2>(z1, P.Z + (size_t)vv.y * K + k);
+      const bool ucur_is_us = P.First && P.Ucur == P.Us;
+      if (P.First || !P.Last) ldp<2>(ucur, (ucur_is_us ? P.Us : P.Ucur) + o);
+      if (!P.First) ldp<2>(base, P.Unext + o);
+      double tend[2] = {0, 0};
+      if (P.PVOn) {
+         const unsigned po = (unsigned)(2 * p) * 8u;
+         const double2 qe = lds2(Qb, r * (kTKC * 8u) + po);
+         const int ne = M.NEdgesOnEdge[e];
+         const double *W = M.WeightsOnEdge + (size_t)e * M.MaxEdges2;
+         double acc0 = 0, acc1 = 0;
+         for (int j = 0; j < ne; ++j) {
+            const unsigned lo = S.EoE[r][j] * (kTKC * 8u) + po;
+            const double w    = W[j];
+            const double2 f = lds2(Fb, lo), qj = lds2(Qb, lo);
+            acc0 += w * f.x * ((qe.x + qj.x) * 0.5);
+            acc1 += w * f.y * ((qe.y + qj.y) * 0.5);
+         }
+         tend[0] = mask * acc0;
+         tend[1] = mask * acc1;
+      }
+#pragma unroll
+      for (int q2 = 0; q2 < 2; ++q2) {
+         if (P.XOn) tend[q2] -= mask * (x1[q2] - x0[q2]) * InvDc;
+         tend[q2] += mask * (P.SY * (y1[q2] - y0[q2]) * InvDc - P.SZ * (z1[q2] - z0[q2]) * InvDv);
+      }
+      double out[2];
+#pragma unroll
+      for (int q2 = 0; q2 < 2; ++q2) out[q2] = (P.First ? ucur[q2] : base[q2]) + P.B * tend[q2];
+      stv<2>(P.Unext + o, out);
+      if (!P.Last) {
+#pragma unroll
+         for (int q2 = 0; q2 < 2; ++q2) out[q2] = ucur[q2] + P.A * tend[q2];
+         stv<2>(P.Uprov + o, out);
+      }
+   }
+}
+
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St) {
+   static bool attr = false;
+   if (!attr) {
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fET, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ETileSmem)));
+      attr = true;
+   }
+   const int nch = D.K / kTKC;
+   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch);
+   return 0;
+}
+
+bool tile_edge_path_ok(const DMesh &D) { return tile_path_ok(D) && D.Tiles.EdgeTilesOK; }
+
 } // namespace omega

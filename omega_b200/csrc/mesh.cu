@@ -114,7 +114,8 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
                        const std::vector<int> &eoc, const std::vector<int> &coe,
                        const std::vector<double> &mask, const std::vector<double> &dv,
                        const std::vector<double> &dc, const std::vector<double> &area,
-                       const std::vector<double> &sign, int NE) {
+                       const std::vector<double> &sign, int NE, int ME2, const std::vector<int> &neoe,
+                       const std::vector<int> &eoe) {
    DTiles &T = M->D.Tiles;
    std::memset(&T, 0, sizeof(T));
    if (M->MaxEdgesUsed > 6) return 0;
@@ -126,6 +127,10 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    std::vector<TileHdr> hdr;
    std::vector<int> rows;
    std::vector<unsigned short> nbl;
+   std::vector<int> erows;
+   std::vector<unsigned short> eoel;
+   std::vector<int> eloc(NE + 1, -1);
+   bool edgeOK = true;
    std::vector<int> loc(NC + 1, -1); // local row of a cell in the tile under construction
    std::vector<int> r1, r2;
    int c0 = 0;
@@ -165,6 +170,49 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
       TileHdr h;
       h.C0 = c0; h.NC = nc; h.N1 = (int)r1.size(); h.N2 = (int)r2.size();
       h.RowOff = (int)rows.size(); h.NblOff = (int)(nbl.size() / 8); h.Pad0 = h.Pad1 = 0;
+      // ---- edge side: own edges = edges whose lowest-ranked valid cell is an own cell; staged =
+      // every edge of the own + ring-1 cells (all EdgesOnEdge entries of the own edges are among them)
+      h.NEOwn = h.NEStaged = 0; h.ERowOff = (int)erows.size(); h.EoEOff = (int)(eoel.size() / 12);
+      if (edgeOK) {
+         std::vector<int> own_e, oth_e;
+         auto visit = [&](int c) {
+            for (int j = 0; j < nec[c]; ++j) {
+               const int e = eoc[(size_t)c * ME + j];
+               if (eloc[e] >= 0) continue;
+               const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
+               const int lo = std::min(a < NC ? a : INT32_MAX, b < NC ? b : INT32_MAX);
+               eloc[e] = 1 << 20;
+               (lo >= c0 && lo < c0 + nc ? own_e : oth_e).push_back(e);
+            }
+         };
+         for (int i = 0; i < nc; ++i) visit(c0 + i);
+         for (int n : r1)
+            if (n < NC) visit(n);
+         std::sort(own_e.begin(), own_e.end());
+         std::sort(oth_e.begin(), oth_e.end());
+         if ((int)own_e.size() > kTileEdgesOwn || (int)(own_e.size() + oth_e.size()) > kTileEdges || ME2 > 12) edgeOK = false;
+         for (size_t i = 0; i < own_e.size(); ++i) eloc[own_e[i]] = (int)i;
+         for (size_t i = 0; i < oth_e.size(); ++i) eloc[oth_e[i]] = (int)(own_e.size() + i);
+         for (size_t i = 0; edgeOK && i < own_e.size(); ++i) {
+            const int e = own_e[i];
+            for (int j = 0; j < 12; ++j) {
+               int l = (int)i;
+               if (j < neoe[e]) {
+                  const int je = eoe[(size_t)e * ME2 + j];
+                  if (je < NE) {
+                     if (eloc[je] < 0 || eloc[je] >= (1 << 20)) edgeOK = false;
+                     else l = eloc[je];
+                  } // boundary-slot entries carry zero weight: any staged row serves
+               }
+               eoel.push_back((unsigned short)l);
+            }
+         }
+         h.NEOwn = (int)own_e.size(); h.NEStaged = (int)(own_e.size() + oth_e.size());
+         erows.insert(erows.end(), own_e.begin(), own_e.end());
+         erows.insert(erows.end(), oth_e.begin(), oth_e.end());
+         for (int e : own_e) eloc[e] = -1;
+         for (int e : oth_e) eloc[e] = -1;
+      }
       hdr.push_back(h);
       rows.insert(rows.end(), r1.begin(), r1.end());
       rows.insert(rows.end(), r2.begin(), r2.end());
@@ -203,6 +251,9 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    rc |= to_device(M, cfu, &T.CfUCell);
    rc |= to_device(M, wa, &T.WaCell);
    rc |= to_device(M, eoc6, &T.EocCell);
+   rc |= to_device(M, erows, &T.EdgeRows);
+   rc |= to_device(M, eoel, &T.EoELocal);
+   T.EdgeTilesOK = edgeOK && !rc;
    T.NTiles = rc ? 0 : (int)hdr.size();
    return rc;
 }
@@ -341,6 +392,7 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    STAGE(G.BottomDepth, gather_rows(D->BottomDepth, PC, 1));
    STAGE(G.XCell, gather_rows(D->XCell, PC, 1));
    STAGE(G.YCell, gather_rows(D->YCell, PC, 1));
+   std::vector<int> eoe_dev, neoe_dev; // device-order EdgesOnEdge / trimmed counts (tiles need them too)
    std::vector<int> coe = gather_index_rows(D->CellsOnEdge, PE, 2, IC);
    std::vector<int> voe = gather_index_rows(D->VerticesOnEdge, PE, 2, IV);
    {
@@ -351,8 +403,9 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    {
       // EdgesOnEdge / WeightsOnEdge; trailing boundary-slot entries (zero weight
       // padding that Decomp.cpp:2186-2200 counts) are trimmed from the count
-      std::vector<int> eoe  = gather_index_rows(D->EdgesOnEdge, PE, ME2, IE);
-      std::vector<int> neoe = gather_rows(D->NEdgesOnEdge, PE, 1);
+      std::vector<int> &eoe = eoe_dev, &neoe = neoe_dev;
+      eoe  = gather_index_rows(D->EdgesOnEdge, PE, ME2, IE);
+      neoe = gather_rows(D->NEdgesOnEdge, PE, 1);
       std::vector<double> w = gather_rows(D->WeightsOnEdge, PE, ME2);
       for (int e = 0; e < NE; ++e) {
          int n = neoe[e];
@@ -397,7 +450,7 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
                         gather_index_rows(D->EdgesOnCell, PC, ME, IE), coe,
                         gather_rows(M->EdgeMaskH.data(), PE, 1), gather_rows(D->DvEdge, PE, 1),
                         gather_rows(D->DcEdge, PE, 1), gather_rows(D->AreaCell, PC, 1),
-                        gather_rows(M->EdgeSignOnCellH.data(), PC, ME), NE);
+                        gather_rows(M->EdgeSignOnCellH.data(), PC, ME), NE, ME2, neoe_dev, eoe_dev);
    for (int kind = 0; kind < 3; ++kind) {
       const int *p = nullptr;
       rc |= to_device(M, M->Perm[kind], &p);

@@ -38,10 +38,15 @@ constexpr int kTileCells = 64;  // own cells per tile (fewer when a cap below wo
 constexpr int kTileRing1 = 56;  // cap on ring-1 rows
 constexpr int kTileRows1 = kTileCells + kTileRing1; // cap on own + ring-1 rows
 constexpr int kTileRows  = 176; // cap on own + ring-1 + ring-2 rows
+constexpr int kTileEdgesOwn = 256; // cap on own edges of a tile (edges whose lowest-ranked cell is an own cell)
+constexpr int kTileEdges    = 400; // cap on staged edges: every edge of the own + ring-1 cells, own edges first
 struct TileHdr {
    int C0, NC, N1, N2; // first own cell, counts
    int RowOff;         // offset of the tile's ring rows in HaloRows
    int NblOff;         // offset (in rows) of the tile's rows in Nbl
+   int NEOwn, NEStaged; // edge counts
+   int ERowOff;        // offset of the tile's staged edges in EdgeRows
+   int EoEOff;         // offset (in own edges) of the tile's rows in EoELocal
    int Pad0, Pad1;
 };
 struct DTiles {
@@ -53,6 +58,10 @@ struct DTiles {
    const double *CfUCell;     // [NCellsSize][6]  DvEdge*EdgeSignOnCell
    const double *WaCell;      // [NCellsSize][6]  EdgeMask*DvEdge*EdgeSignOnCell
    const int *EocCell;        // [NCellsSize][6]  EdgesOnCell, boundary slot when none
+   // edge side (the shared-memory staged edge pass): valid when EdgeTilesOK
+   int EdgeTilesOK;
+   const int *EdgeRows;            // staged edges of every tile (device edge index), own edges first
+   const unsigned short *EoELocal; // [own edges][12]: staged row of EdgesOnEdge entry j (self when none)
    const double *InvAreaCell; // [NCellsSize], 0 in the boundary slot
 };
 

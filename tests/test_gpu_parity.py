@@ -191,11 +191,12 @@ def test_rk4_100_steps_state_parity():
 
 
 def test_tiled_and_untiled_fused_paths_agree(monkeypatch):
-    """fused_tile.cu against the fused.cu kernels it replaces (OMEGA_TILE=0), same inputs."""
+    """fused_tile.cu against the fused.cu kernels it replaces (OMEGA_TILE=0, OMEGA_TILE_E=0), same inputs."""
     L, cfg, init, dt = cases.sphere_case(4, 32, 4)
     res = []
     for tile in ("1", "0"):
         monkeypatch.setenv("OMEGA_TILE", tile)
+        monkeypatch.setenv("OMEGA_TILE_E", tile)
         from omega_b200 import model
         h, u, tr = init
         mesh, st, state = gpu_objects(L, cfg, tr.shape[0])
