@@ -66,7 +66,7 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const double InvA = M.InvAreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       double ke[V] = {0}, dv[V] = {0};
       for (int j = 0; j < ne; ++j) {
@@ -96,7 +96,7 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      const double InvAt = 1.0 / M.AreaTriangle[v];
+      const double InvAt = M.InvAreaTriangle[v];
       double hv[V] = {0}, rv[V] = {0};
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
@@ -130,8 +130,7 @@ template <int V>
 __device__ __forceinline__ void del2_edge(const DMesh &M, int e, int k, const double *__restrict__ Div,
                                           const double *__restrict__ RelVort, double (&out)[V]) {
    const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
-   const double dc = M.DcEdge[e], dv = M.DvEdge[e];
-   const double InvDc = 1.0 / dc, InvDv = 1.0 / fmax(dv, 0.25 * dc), mask = M.EdgeMask[e];
+   const double InvDc = M.InvDcEdge[e], InvDv = M.InvDvEffEdge[e], mask = M.EdgeMask[e];
    double d0[V], d1[V], r0[V], r1[V];
    ldv<V>(d0, Div + (size_t)cc.x * M.K + k);
    ldv<V>(d1, Div + (size_t)cc.y * M.K + k);
@@ -158,7 +157,7 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const double InvA = M.InvAreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       double t[V] = {0};
       for (int j = 0; j < ne; ++j) {
@@ -182,7 +181,7 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      const double InvAt = 1.0 / M.AreaTriangle[v];
+      const double InvAt = M.InvAreaTriangle[v];
       double t[V] = {0};
 #pragma unroll
       for (int j = 0; j < 3; ++j) {

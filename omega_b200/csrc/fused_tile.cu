@@ -566,7 +566,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
       const size_t o = (size_t)e * K + k;
       const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
       const double mask = M.EdgeMask[e];
-      const double InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
+      const double InvDc = M.InvDcEdge[e], InvDv = M.InvDvEdge[e];
       // the gathered rows of the gradient / diffusion terms and the RK operands: in flight
       // while the neighbour sum runs from shared memory
       double x0[2], x1[2], y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};

@@ -444,6 +444,24 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    STAGE(G.KiteAreasOnVertex, gather_rows(D->KiteAreasOnVertex, PV, 3));
    STAGE(G.AreaTriangle, gather_rows(D->AreaTriangle, PV, 1));
    STAGE(G.FVertex, gather_rows(D->FVertex, PV, 1));
+   {
+      std::vector<double> dc = gather_rows(D->DcEdge, PE, 1), dv = gather_rows(D->DvEdge, PE, 1);
+      std::vector<double> ar = gather_rows(D->AreaCell, PC, 1), at = gather_rows(D->AreaTriangle, PV, 1);
+      std::vector<double> idc(dc.size(), 0.0), idv(dc.size(), 0.0), idve(dc.size(), 0.0), iar(ar.size(), 0.0),
+          iat(at.size(), 0.0);
+      for (int e = 0; e < NE; ++e) {
+         idc[e]  = 1.0 / dc[e];
+         idv[e]  = 1.0 / dv[e];
+         idve[e] = 1.0 / std::max(dv[e], 0.25 * dc[e]);
+      }
+      for (int c = 0; c < NC; ++c) iar[c] = 1.0 / ar[c];
+      for (int v = 0; v < NV; ++v) iat[v] = 1.0 / at[v];
+      STAGE(G.InvDcEdge, idc);
+      STAGE(G.InvDvEdge, idv);
+      STAGE(G.InvDvEffEdge, idve);
+      STAGE(G.InvAreaCell, iar);
+      STAGE(G.InvAreaTriangle, iat);
+   }
 #undef STAGE
    if (!rc)
       rc |= build_tiles(M, NC, D->NCellsOwned, ME, gather_rows(D->NEdgesOnCell, PC, 1),

@@ -91,6 +91,9 @@ struct DMesh {
    const int *CellsOnVertex, *EdgesOnVertex;               // [V][3]
    const double *EdgeSignOnVertex, *KiteAreasOnVertex;     // [V][3]
    const double *AreaTriangle, *FVertex;
+   // reciprocals evaluated once on the host (IEEE division, the same bits the kernels' own
+   // 1.0/x gave): 1/dc, 1/dv, 1/max(dv, 0.25 dc) per edge; 1/AreaCell; 1/AreaTriangle
+   const double *InvDcEdge, *InvDvEdge, *InvDvEffEdge, *InvAreaCell, *InvAreaTriangle;
    DTiles Tiles; // NTiles == 0 when the mesh has cells with more than 6 edges
 };
 
