@@ -284,8 +284,14 @@ def main():
         cl_local = mesh.NAll[0] * K
         alg_fc = 32.0 * (1 + T) * cl_local
         ach = alg_fc / (kms[3] / kcnt[3] * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "k_fC", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": peak_src,
+        # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/)
+        traffic = None
+        tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr_path) and args.workload == "config3" and world == 1:
+            traffic = json.load(open(tr_path)).get("k_fCT_dram_bytes_per_launch")
+        roofline = {"bound": "hbm", "kernel": "k_fCT (tiled cell pass: thickness + all tracer tendencies + RK updates)",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg_fc}
     ach_step = alg_step * ncl / world / t_step / 1e9
     line = {"metric": "cell-layer updates/s", "value": value, "unit": "cell-layer updates/s", "n_gpus": world,
