@@ -165,22 +165,15 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
    cp_wait<1>();    // h and phi_0 have landed (this thread's pieces)
    __syncthreads(); // ... and everybody else's; tables are visible
    unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
-   // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
-   unsigned nb2[3];
-   {
-      const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
-#pragma unroll
-      for (int j = 0; j < 3; ++j)
-         nb2[j] = ((nbl_get(tt, 2 * j) * kTKC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * kTKC + 2 * p) * 8u) << 16);
-   }
    // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
    double cfA[kME][2];
    {
       const double nia = -S.InvA[X.li];
       const double2 hs = lds2(Hb, X.myoff);
+      const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
-         const double2 hn = lds2(Hb, (j & 1) ? nb2[j >> 1] >> 16 : nb2[j >> 1] & 0xffffu);
+         const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
          const double g   = S.G[X.li][j] * nia;
          cfA[j][0]        = g * (0.5 * (hs.x + hn.x));
          cfA[j][1]        = g * (0.5 * (hs.y + hn.y));
@@ -215,11 +208,14 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
       const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[m % kTStages][0][0]);
       unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
       if (X.own) {
+         // neighbour rows are re-read from the Nbl table every tracer: one shared load instead
+         // of three registers held (and spilled) across the loop
          const double2 ts = lds2(Pb, X.myoff);
+         const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
          double d0 = 0, d1 = 0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 tn = lds2(Pb, (j & 1) ? nb2[j >> 1] >> 16 : nb2[j >> 1] & 0xffffu);
+            const double2 tn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
             d0 += cfA[j][0] * (ts.x - tn.x);
             d1 += cfA[j][1] * (ts.y - tn.y);
          }
