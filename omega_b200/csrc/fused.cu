@@ -69,17 +69,21 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
       const double InvA = M.InvAreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       double ke[V] = {0}, dv[V] = {0};
-      for (int j = 0; j < ne; ++j) {
-         const int e        = M.EdgesOnCell[c * M.MaxEdges + j];
-         const double dve   = M.DvEdge[e];
-         const double kcoef = 0.5 * dve * M.DcEdge[e] * 0.5 * InvA;
-         const double dcoef = dve * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
-         double u[V];
-         ldv<V>(u, U + (size_t)e * M.K + k);
+      // unrolled over the (at most 6, checked at launch) edges: all u-row gathers in flight together
 #pragma unroll
-         for (int q = 0; q < V; ++q) {
-            ke[q] += kcoef * u[q] * u[q];
-            dv[q] -= dcoef * u[q];
+      for (int j = 0; j < 6; ++j) {
+         if (j < ne) {
+            const int e        = M.EdgesOnCell[c * M.MaxEdges + j];
+            const double dve   = M.DvEdge[e];
+            const double kcoef = 0.5 * dve * M.DcEdge[e] * 0.5 * InvA;
+            const double dcoef = dve * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
+            double u[V];
+            ldv<V>(u, U + (size_t)e * M.K + k);
+#pragma unroll
+            for (int q = 0; q < V; ++q) {
+               ke[q] += kcoef * u[q] * u[q];
+               dv[q] -= dcoef * u[q];
+            }
          }
       }
       if (XMode) {
@@ -160,13 +164,16 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
       const double InvA = M.InvAreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       double t[V] = {0};
-      for (int j = 0; j < ne; ++j) {
-         const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
-         const double cf = M.DvEdge[e] * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
-         double d2[V];
-         del2_edge<V>(M, e, k, Div, RelVort, d2);
 #pragma unroll
-         for (int q = 0; q < V; ++q) t[q] -= cf * d2[q];
+      for (int j = 0; j < 6; ++j) {
+         if (j < ne) {
+            const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
+            const double cf = M.DvEdge[e] * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
+            double d2[V];
+            del2_edge<V>(M, e, k, Div, RelVort, d2);
+#pragma unroll
+            for (int q = 0; q < V; ++q) t[q] -= cf * d2[q];
+         }
       }
       if (YMode) {
          // tiled edge pass: Del2 and Del4 velocity terms share one difference per element kind,

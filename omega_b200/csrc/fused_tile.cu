@@ -517,7 +517,8 @@ struct ETileSmem {
    double F[kTileEdges][kTKC];
    double Q[kTileEdges][kTKC];
    int SRow[kTileEdges];
-   unsigned short EoE[kTileEdgesOwn][12];
+   int4 CV[kTileEdges]; // cells (x,y) and vertices (z,w) of every staged edge
+   unsigned short EoE[kTileEdgesOwn][10];
    TileHdr Hdr;
 };
 
@@ -532,26 +533,39 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
    __syncthreads();
    const int nOwn = S.Hdr.NEOwn, nSt = S.Hdr.NEStaged;
-   for (int r = tid; r < nSt; r += kEThreads) S.SRow[r] = M.Tiles.EdgeRows[S.Hdr.ERowOff + r];
+   for (int r = tid; r < nSt; r += kEThreads) {
+      S.SRow[r] = M.Tiles.EdgeRows[S.Hdr.ERowOff + r];
+      S.CV[r]   = M.Tiles.EdgeCV[S.Hdr.ERowOff + r];
+   }
    {
-      const unsigned *src = reinterpret_cast<const unsigned *>(M.Tiles.EoELocal + (size_t)S.Hdr.EoEOff * 12);
+      const unsigned *src = reinterpret_cast<const unsigned *>(M.Tiles.EoELocal + (size_t)S.Hdr.EoEOff * 10);
       unsigned *dst       = reinterpret_cast<unsigned *>(&S.EoE[0][0]);
-      for (int q = tid; q < nOwn * 6; q += kEThreads) dst[q] = src[q];
+      for (int q = tid; q < nOwn * 5; q += kEThreads) dst[q] = src[q];
    }
    __syncthreads();
    const int p = tid & 7, k = kc0 + 2 * p;
-   // ---- pass 1: F and q of every staged edge
-   for (int q = tid; q < nSt * kTLanes; q += kEThreads) {
-      const int r = q >> 3, e = S.SRow[r];
-      const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
-      double u[2], h0[2], h1[2], a[2], b[2];
+   // ---- pass 1: F and q of every staged edge, two edges per trip (ten gathered rows in flight)
+   auto fq = [&](int r, double (&u)[2], double (&h0)[2], double (&h1)[2], double (&a)[2], double (&b)[2]) {
+      const int e   = S.SRow[r];
+      const int4 cv = S.CV[r];
       ldv<2>(u, P.Us + (size_t)e * K + k);
-      ldv<2>(h0, P.Hs + (size_t)cc.x * K + k);
-      ldv<2>(h1, P.Hs + (size_t)cc.y * K + k);
-      ldv<2>(a, P.PVv + (size_t)vv.x * K + k);
-      ldv<2>(b, P.PVv + (size_t)vv.y * K + k);
+      ldv<2>(h0, P.Hs + (size_t)cv.x * K + k);
+      ldv<2>(h1, P.Hs + (size_t)cv.y * K + k);
+      ldv<2>(a, P.PVv + (size_t)cv.z * K + k);
+      ldv<2>(b, P.PVv + (size_t)cv.w * K + k);
+   };
+   auto put = [&](int r, const double (&u)[2], const double (&h0)[2], const double (&h1)[2], const double (&a)[2],
+                  const double (&b)[2]) {
       *reinterpret_cast<double2 *>(&S.F[r][2 * p]) = make_double2(0.5 * (h0[0] + h1[0]) * u[0], 0.5 * (h0[1] + h1[1]) * u[1]);
       *reinterpret_cast<double2 *>(&S.Q[r][2 * p]) = make_double2(0.5 * (a[0] + b[0]), 0.5 * (a[1] + b[1]));
+   };
+   for (int q = tid; q < nSt * kTLanes; q += 2 * kEThreads) {
+      const int r = q >> 3, r2 = r + kEThreads / kTLanes;
+      double u[2], h0[2], h1[2], a[2], b[2], u2[2], g0[2], g1[2], a2[2], b2[2];
+      fq(r, u, h0, h1, a, b);
+      if (r2 < nSt) fq(r2, u2, g0, g1, a2, b2);
+      put(r, u, h0, h1, a, b);
+      if (r2 < nSt) put(r2, u2, g0, g1, a2, b2);
    }
    __syncthreads();
    // ---- pass 2: own edges
@@ -560,7 +574,8 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
    for (int q = tid; q < nOwn * kTLanes; q += kEThreads) {
       const int r = q >> 3, e = S.SRow[r];
       const size_t o = (size_t)e * K + k;
-      const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
+      const int4 cv = S.CV[r];
+      const int2 cc = make_int2(cv.x, cv.y), vv = make_int2(cv.z, cv.w);
       const double mask = M.EdgeMask[e];
       const double InvDc = M.InvDcEdge[e], InvDv = M.InvDvEdge[e];
       // the gathered rows of the gradient / diffusion terms and the RK operands: in flight

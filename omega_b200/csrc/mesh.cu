@@ -115,7 +115,7 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
                        const std::vector<double> &mask, const std::vector<double> &dv,
                        const std::vector<double> &dc, const std::vector<double> &area,
                        const std::vector<double> &sign, int NE, int ME2, const std::vector<int> &neoe,
-                       const std::vector<int> &eoe) {
+                       const std::vector<int> &eoe, const std::vector<int> &voe) {
    DTiles &T = M->D.Tiles;
    std::memset(&T, 0, sizeof(T));
    if (M->MaxEdgesUsed > 6) return 0;
@@ -172,7 +172,7 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
       h.RowOff = (int)rows.size(); h.NblOff = (int)(nbl.size() / 8); h.Pad0 = h.Pad1 = 0;
       // ---- edge side: own edges = edges whose lowest-ranked valid cell is an own cell; staged =
       // every edge of the own + ring-1 cells (all EdgesOnEdge entries of the own edges are among them)
-      h.NEOwn = h.NEStaged = 0; h.ERowOff = (int)erows.size(); h.EoEOff = (int)(eoel.size() / 12);
+      h.NEOwn = h.NEStaged = 0; h.ERowOff = (int)erows.size(); h.EoEOff = (int)(eoel.size() / 10);
       if (edgeOK) {
          std::vector<int> own_e, oth_e;
          auto visit = [&](int c) {
@@ -190,12 +190,13 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
             if (n < NC) visit(n);
          std::sort(own_e.begin(), own_e.end());
          std::sort(oth_e.begin(), oth_e.end());
-         if ((int)own_e.size() > kTileEdgesOwn || (int)(own_e.size() + oth_e.size()) > kTileEdges || ME2 > 12) edgeOK = false;
+         if ((int)own_e.size() > kTileEdgesOwn || (int)(own_e.size() + oth_e.size()) > kTileEdges ) edgeOK = false;
          for (size_t i = 0; i < own_e.size(); ++i) eloc[own_e[i]] = (int)i;
          for (size_t i = 0; i < oth_e.size(); ++i) eloc[oth_e[i]] = (int)(own_e.size() + i);
          for (size_t i = 0; edgeOK && i < own_e.size(); ++i) {
             const int e = own_e[i];
-            for (int j = 0; j < 12; ++j) {
+            if (neoe[e] > 10) edgeOK = false; // cells of at most 6 edges give at most 10 entries
+            for (int j = 0; j < 10; ++j) {
                int l = (int)i;
                if (j < neoe[e]) {
                   const int je = eoe[(size_t)e * ME2 + j];
@@ -252,6 +253,17 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    rc |= to_device(M, wa, &T.WaCell);
    rc |= to_device(M, eoc6, &T.EocCell);
    rc |= to_device(M, erows, &T.EdgeRows);
+   {
+      std::vector<int> cv(erows.size() * 4);
+      for (size_t i = 0; i < erows.size(); ++i) {
+         const int e = erows[i];
+         cv[4 * i] = coe[(size_t)e * 2]; cv[4 * i + 1] = coe[(size_t)e * 2 + 1];
+         cv[4 * i + 2] = voe[(size_t)e * 2]; cv[4 * i + 3] = voe[(size_t)e * 2 + 1];
+      }
+      const int *q = nullptr;
+      rc |= to_device(M, cv, &q);
+      T.EdgeCV = reinterpret_cast<const int4 *>(q);
+   }
    rc |= to_device(M, eoel, &T.EoELocal);
    T.EdgeTilesOK = edgeOK && !rc;
    T.NTiles = rc ? 0 : (int)hdr.size();
@@ -468,7 +480,7 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
                         gather_index_rows(D->EdgesOnCell, PC, ME, IE), coe,
                         gather_rows(M->EdgeMaskH.data(), PE, 1), gather_rows(D->DvEdge, PE, 1),
                         gather_rows(D->DcEdge, PE, 1), gather_rows(D->AreaCell, PC, 1),
-                        gather_rows(M->EdgeSignOnCellH.data(), PC, ME), NE, ME2, neoe_dev, eoe_dev);
+                        gather_rows(M->EdgeSignOnCellH.data(), PC, ME), NE, ME2, neoe_dev, eoe_dev, voe);
    for (int kind = 0; kind < 3; ++kind) {
       const int *p = nullptr;
       rc |= to_device(M, M->Perm[kind], &p);

@@ -61,7 +61,8 @@ struct DTiles {
    // edge side (the shared-memory staged edge pass): valid when EdgeTilesOK
    int EdgeTilesOK;
    const int *EdgeRows;            // staged edges of every tile (device edge index), own edges first
-   const unsigned short *EoELocal; // [own edges][12]: staged row of EdgesOnEdge entry j (self when none)
+   const int4 *EdgeCV;             // per staged edge: CellsOnEdge (x,y), VerticesOnEdge (z,w), same order as EdgeRows
+   const unsigned short *EoELocal; // [own edges][10]: staged row of EdgesOnEdge entry j (self when none)
    const double *InvAreaCell; // [NCellsSize], 0 in the boundary slot
 };
 
