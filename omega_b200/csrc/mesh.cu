@@ -154,7 +154,30 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
                   if (loc[m] < 0) { loc[m] = 1 << 21; r2.push_back(m); }
                }
          std::sort(r2.begin(), r2.end());
-         const bool ok = (int)r1.size() <= kTileRing1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows;
+         // edge side of the same tile: own edges (lowest-ranked valid cell is an own cell) and
+         // staged edges (every edge of the own + ring-1 cells) must fit their caps as well
+         int nOwnE = 0, nStE = 0;
+         {
+            std::vector<int> seen;
+            auto count = [&](int c) {
+               for (int j = 0; j < nec[c]; ++j) {
+                  const int e = eoc[(size_t)c * ME + j];
+                  if (eloc[e] >= 0) continue;
+                  eloc[e] = 0;
+                  seen.push_back(e);
+                  const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
+                  const int lo = std::min(a < NC ? a : INT32_MAX, b < NC ? b : INT32_MAX);
+                  ++nStE;
+                  if (lo >= c0 && lo < c0 + nc) ++nOwnE;
+               }
+            };
+            for (int i = 0; i < nc; ++i) count(c0 + i);
+            for (int n : r1)
+               if (n < NC) count(n);
+            for (int e : seen) eloc[e] = -1;
+         }
+         const bool ok = (int)r1.size() <= kTileRing1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows &&
+                         nOwnE <= kTileEdgesOwn && nStE <= kTileEdges;
          if (ok || nc == 1) break;
          for (int i = 0; i < nc; ++i) loc[c0 + i] = -1;
          for (int n : r1) loc[n] = -1;
@@ -195,19 +218,28 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
          for (size_t i = 0; i < oth_e.size(); ++i) eloc[oth_e[i]] = (int)(own_e.size() + i);
          for (size_t i = 0; edgeOK && i < own_e.size(); ++i) {
             const int e = own_e[i];
-            if (neoe[e] > 10) edgeOK = false; // cells of at most 6 edges give at most 10 entries
+            if (neoe[e] > 10) { // cells of at most 6 edges give at most 10 entries
+               edgeOK = false;
+               if (getenv("OMEGA_DEBUG")) fprintf(stderr, "edge tiles off: edge %d has %d EdgesOnEdge entries\n", e, neoe[e]);
+            }
             for (int j = 0; j < 10; ++j) {
                int l = (int)i;
                if (j < neoe[e]) {
                   const int je = eoe[(size_t)e * ME2 + j];
                   if (je < NE) {
-                     if (eloc[je] < 0 || eloc[je] >= (1 << 20)) edgeOK = false;
-                     else l = eloc[je];
+                     // an entry that is not an edge of the own + ring-1 cells: only behind a rim edge whose
+                     // second cell is the boundary slot (outermost halo); stage it as well
+                     if (eloc[je] < 0) {
+                        eloc[je] = (int)(own_e.size() + oth_e.size());
+                        oth_e.push_back(je);
+                     }
+                     l = eloc[je];
                   } // boundary-slot entries carry zero weight: any staged row serves
                }
                eoel.push_back((unsigned short)l);
             }
          }
+         if ((int)(own_e.size() + oth_e.size()) > kTileEdges) edgeOK = false;
          h.NEOwn = (int)own_e.size(); h.NEStaged = (int)(own_e.size() + oth_e.size());
          erows.insert(erows.end(), own_e.begin(), own_e.end());
          erows.insert(erows.end(), oth_e.begin(), oth_e.end());
