@@ -50,6 +50,7 @@ struct TileSmem {
    double InvA[kTileRows1];
    unsigned short Nbl[kTileRows1][8];
    int GRow[kTileRows];
+   int Eoc[kTileCells][6]; // own rows: EdgesOnCell (boundary slot when none)
    TileHdr Hdr;
 };
 
@@ -79,6 +80,7 @@ __device__ __forceinline__ unsigned nbl_get(const uint4 &t, int j) {
 
 // named barriers (0 is __syncthreads)
 constexpr int kBarDRole = 1; // the D role among itself
+constexpr int kBarHFree = 7; // the T role has built its coefficients: the thickness rows may be overwritten
 __device__ __forceinline__ int bar_d2_ready(int l) { return 3 + (l & 1); }
 __device__ __forceinline__ int bar_d2_free(int l) { return 5 + (l & 1); }
 
@@ -95,6 +97,7 @@ template <int NT>
 __device__ __forceinline__ void load_tables(const DMesh &M, TileSmem &S, int tid, int nR1, int nc) {
    for (int q = tid; q < nc * 6; q += NT) {
       const size_t g = (size_t)S.Hdr.C0 * 6 + q;
+      (&S.Eoc[0][0])[q] = M.Tiles.EocCell[g];
       (&S.CfU[0][0])[q] = M.Tiles.CfUCell[g];
       (&S.Wa[0][0])[q]  = M.Tiles.WaCell[g];
    }
@@ -138,110 +141,124 @@ struct RowCopier {
 
 // =================== D role: Del2(phi) of own + ring-1 rows ===================
 // (TracerAuxVars.h:61-91; s*(phi(c1)-phi(c0)) == phi(self)-phi(nbr) exactly)
-__device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int tid) {
+// With NCh > 1 the CTA walks the NCh level chunks of its tile one after the other: tables
+// are loaded once, and h / the first two tracers of chunk c+1 are copied during the last
+// two tracers of chunk c, so only the first chunk pays the start-up latency of a tile.
+__device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int NCh,
+                                       int tid) {
    const int T = P.NTracers, K = M.K;
    const size_t CS = (size_t)M.NCellsSize * K;
-   // The D role also feeds the pipeline: h, then tracer m+2 while it works on tracer m.
-   // Item q = t + 512 i of a row-set copy is row q/8, 16-byte piece q%8, and lands at byte
-   // 16 q of the [row][16] buffer; source offsets are re-derived from GRow on every copy
-   // (three shared loads) rather than held in registers.
+   // The D role also feeds the pipeline: one row set (h or a tracer) per tracer worked on,
+   // two ahead.  Item q = t + 512 i of a row-set copy is row q/8, 16-byte piece q%8, and
+   // lands at byte 16 q of the [row][16] buffer; source offsets are re-derived from GRow
+   // on every copy (three shared loads) rather than held in registers.
    const int t = X.t, p = X.p;
-   auto copy_rows = [&](const double *F, const void *Dst) {
+   auto copy_rows = [&](const double *F, const void *Dst, int kc) {
       const unsigned d = smem_u32(Dst) + 16u * t;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
          const int r = (t >> 3) + i * (kTRole / kTLanes);
-         if (r < X.nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc0 + 2 * p));
+         if (r < X.nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc + 2 * p));
       }
    };
-   copy_rows(P.Hs, &S.H[0][0]);
+   // tracer m of chunk c is item c*T + m of the stream and lives in buffer (c*T + m) % kTStages
+   copy_rows(P.Hs, &S.H[0][0], kc0);
    cp_commit();
-#pragma unroll
-   for (int s = 0; s < 2; ++s) {
-      if (s < T) copy_rows(P.Trs + s * CS, &S.Phi[s][0][0]);
-      cp_commit();
-   }
+   copy_rows(P.Trs, &S.Phi[0][0][0], kc0);
+   cp_commit();
    load_tables<2 * kTRole>(M, S, tid, X.nR1, X.nc);
-   cp_wait<1>();    // h and phi_0 have landed (this thread's pieces)
-   __syncthreads(); // ... and everybody else's; tables are visible
-   unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
-   // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
-   double cfA[kME][2];
-   {
-      const double nia = -S.InvA[X.li];
-      const double2 hs = lds2(Hb, X.myoff);
-      const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
-#pragma unroll
-      for (int j = 0; j < kME; ++j) {
-         const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
-         const double g   = S.G[X.li][j] * nia;
-         cfA[j][0]        = g * (0.5 * (hs.x + hn.x));
-         cfA[j][1]        = g * (0.5 * (hs.y + hn.y));
-      }
-   }
-   // the ring-1 row piece of this thread (n1 <= 56 rows x 8 pieces < 512 threads): the same
-   // coefficients, kept in shared memory (private to this thread) for all tracers
-   const bool ring = t < X.n1 * kTLanes;
+   const bool ring = t < X.n1 * kTLanes; // this thread's ring-1 row piece (n1 <= 56 rows x 8 pieces < 512 threads)
    const int r1    = X.nc + (ring ? X.i : 0);
    const unsigned ro1 = (r1 * kTKC + 2 * p) * 8u;
    unsigned char *Cb  = reinterpret_cast<unsigned char *>(&S.Cf1[ring ? X.i : 0][0][0]) + 16u * p;
-   if (ring) {
-      const double nia = -S.InvA[r1];
-      const double2 hr = lds2(Hb, ro1);
-      const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[r1][0]);
-#pragma unroll
-      for (int j = 0; j < kME; ++j) {
-         const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
-         const double g   = S.G[r1][j] * nia;
-         sts2(Cb, j * (kTKC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
-      }
-   }
-   for (int m = 0; m < T; ++m) {
-      if (m > 0) {
-         cp_wait<1>();                  // phi_m has landed (this thread's pieces)
-         bar_sync(kBarDRole, kTRole);   // ... and the other D threads'
-      }
-      // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
-      if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
-      if (m + 2 < T) copy_rows(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(m + 2) % kTStages][0][0]);
+   for (int c = 0; c < NCh; ++c) {
+      const int kc = kc0 + c * kTKC, it0 = c * T;
+      copy_rows(P.Trs + CS, &S.Phi[(it0 + 1) % kTStages][0][0], kc); // tracer 1 of this chunk (T >= 2)
       cp_commit();
-      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[m % kTStages][0][0]);
-      unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
-      if (X.own) {
-         // neighbour rows are re-read from the Nbl table every tracer: one shared load instead
-         // of three registers held (and spilled) across the loop
-         const double2 ts = lds2(Pb, X.myoff);
+      cp_wait<1>();    // h and tracer 0 of this chunk have landed (this thread's pieces)
+      __syncthreads(); // ... and everybody else's; the T role is done with the previous chunk
+      const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+      // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
+      double cfA[kME][2];
+      {
+         const double nia = -S.InvA[X.li];
+         const double2 hs = lds2(Hb, X.myoff);
          const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
-         double d0 = 0, d1 = 0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 tn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
-            d0 += cfA[j][0] * (ts.x - tn.x);
-            d1 += cfA[j][1] * (ts.y - tn.y);
+            const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+            const double g   = S.G[X.li][j] * nia;
+            cfA[j][0]        = g * (0.5 * (hs.x + hn.x));
+            cfA[j][1]        = g * (0.5 * (hs.y + hn.y));
          }
-         sts2(Db, X.myoff, d0, d1);
       }
+      // ring-1 row piece: the same coefficients, kept in shared memory (private to this thread)
       if (ring) {
-         const double2 pr = lds2(Pb, ro1);
+         const double nia = -S.InvA[r1];
+         const double2 hr = lds2(Hb, ro1);
          const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[r1][0]);
-         double e0 = 0, e1 = 0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 pn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
-            const double2 cf = lds2(Cb, j * (kTKC * 8u));
-            e0 += cf.x * (pr.x - pn.x);
-            e1 += cf.y * (pr.y - pn.y);
+            const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+            const double g   = S.G[r1][j] * nia;
+            sts2(Cb, j * (kTKC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
          }
-         sts2(Db, ro1, e0, e1);
       }
-      bar_arrive(bar_d2_ready(m), 2 * kTRole); // phi_m and Del2(phi_m) are ready for the T role
+      for (int m = 0; m < T; ++m) {
+         if (m > 0) {
+            cp_wait<1>();                // tracer m has landed (this thread's pieces)
+            bar_sync(kBarDRole, kTRole); // ... and the other D threads'
+         }
+         // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
+         if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
+         // next item of the stream, two ahead: a tracer of this chunk, then h and tracer 0 of the next
+         if (m + 2 < T) copy_rows(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(it0 + m + 2) % kTStages][0][0], kc);
+         else if (c + 1 < NCh) {
+            if (m + 2 == T) {
+               bar_sync(kBarHFree, 2 * kTRole); // both roles have read this chunk's thickness rows
+               copy_rows(P.Hs, &S.H[0][0], kc + kTKC);
+            }
+            else copy_rows(P.Trs, &S.Phi[(it0 + T) % kTStages][0][0], kc + kTKC);
+         }
+         cp_commit();
+         const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + m) % kTStages][0][0]);
+         unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
+         if (X.own) {
+            // neighbour rows are re-read from the Nbl table every tracer: one shared load instead
+            // of three registers held (and spilled) across the loop
+            const double2 ts = lds2(Pb, X.myoff);
+            const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[X.li][0]);
+            double d0 = 0, d1 = 0;
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               const double2 tn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+               d0 += cfA[j][0] * (ts.x - tn.x);
+               d1 += cfA[j][1] * (ts.y - tn.y);
+            }
+            sts2(Db, X.myoff, d0, d1);
+         }
+         if (ring) {
+            const double2 pr = lds2(Pb, ro1);
+            const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[r1][0]);
+            double e0 = 0, e1 = 0;
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               const double2 pn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+               const double2 cf = lds2(Cb, j * (kTKC * 8u));
+               e0 += cf.x * (pr.x - pn.x);
+               e1 += cf.y * (pr.y - pn.y);
+            }
+            sts2(Db, ro1, e0, e1);
+         }
+         bar_arrive(bar_d2_ready(m), 2 * kTRole); // tracer m and its Del2 are ready for the T role
+      }
    }
    cp_wait<0>();
 }
 
 // =================== T role: copies, thickness, tracer tendencies + RK updates ===================
 template <bool HYP, int STAGE>
-__device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int tid) {
+__device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int NCh, int tid) {
    constexpr int NT = HYP ? 2 * kTRole : kTRole;
    constexpr bool First = STAGE == 0, Last = STAGE == 2; // stage kind: first, middle, last (RK4: 0 | 1,2 | 3)
    const int K = M.K, T = P.NTracers, t = X.t, p = X.p, li = X.li;
@@ -260,16 +277,19 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
    }
    load_tables<NT>(M, S, tid, X.nR1, X.nc);
 
-   const int c    = X.c0 + li;
-   const int k    = kc0 + 2 * p;
+   const int c = X.c0 + li;
+   // with the D role the CTA walks the NCh level chunks of its tile (see role_D)
+   for (int ch = 0; ch < NCh; ++ch) {
+   const int k    = kc0 + ch * kTKC + 2 * p;
+   const int it0  = ch * T; // stream index of this chunk's tracer 0 (phi buffer = index % kTStages)
    const size_t o = (size_t)c * K + k;
-   unsigned char *Hb = reinterpret_cast<unsigned char *>(&S.H[0][0]);
+   const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
    // edge indices and velocity rows of the own cell: in flight while h lands
    double us[kME][2], ut[kME][2];
    {
       int e[kME];
 #pragma unroll
-      for (int j = 0; j < kME; ++j) e[j] = M.Tiles.EocCell[(size_t)c * 6 + j];
+      for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
 #pragma unroll
       for (int j = 0; j < kME; ++j) ldv<2>(us[j], P.Us + (size_t)e[j] * K + k);
       if (P.UTr != P.Us) {
@@ -325,6 +345,7 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          }
       }
    }
+   if (HYP && ch + 1 < NCh) bar_arrive(kBarHFree, 2 * kTRole); // last read of this chunk's thickness rows
    if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
    if (P.MS.Enabled) {
       const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
@@ -381,7 +402,7 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          if (l + kTStages - 1 < T) cp.copy(P.Trs + (size_t)(l + kTStages - 1) * CS, &S.Phi[(l + kTStages - 1) % kTStages][0][0]);
          cp_commit();
       }
-      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[l % kTStages][0][0]);
+      const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + l) % kTStages][0][0]);
       const double2 ts = lds2(Pb, myoff);
       double tend[2] = {ts.x * S0[0], ts.y * S0[1]};
 #pragma unroll
@@ -426,7 +447,17 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
             if (!First) ldp<2>(acc, P.TrNext + (size_t)(l + 1) * CS + o);
          }
       }
+      if (HYP && l == T - 2 && ch + 1 < NCh) {
+         // the next chunk's velocity / thickness lines towards L2 while this chunk finishes
+#pragma unroll
+         for (int j = 0; j < kME; ++j) prefetch_row(P.Us + (size_t)S.Eoc[li][j] * K + k + kTKC, 2);
+         if (own) {
+            if (!hcur_is_hs) prefetch_row(P.Hcur + o + kTKC, 2);
+            if (!First || P.WSel) prefetch_row(P.Hnext + o + kTKC, 2);
+         }
+      }
    }
+   } // level chunks
    if (!HYP) cp_wait<0>();
 }
 
@@ -439,7 +470,9 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
    TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
    constexpr int NT = HYP ? 2 * kTRole : kTRole;
    const int tid = threadIdx.x;
-   const int tile = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
+   // NChunks > 0: one CTA per (tile, level chunk); NChunks < 0: one CTA per tile walking -NChunks chunks
+   const int NChunksPerCta = NChunks > 0 ? 1 : -NChunks;
+   const int tile = NChunks > 0 ? blockIdx.x / NChunks : blockIdx.x, kc0 = NChunks > 0 ? (blockIdx.x % NChunks) * kTKC : 0;
 
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
@@ -457,15 +490,15 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
          if (RS == 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
          if (RS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
          if (RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
-         role_D(M, P, S, X, kc0, tid);
+         role_D(M, P, S, X, kc0, NChunksPerCta, tid);
       } else {
          if (RS == 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 72;");
          if (RS == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
          if (RS == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 64;");
-         role_T<true, STAGE>(M, P, S, X, kc0, tid);
+         role_T<true, STAGE>(M, P, S, X, kc0, NChunksPerCta, tid);
       }
    } else {
-      role_T<false, STAGE>(M, P, S, X, kc0, tid);
+      role_T<false, STAGE>(M, P, S, X, kc0, 1, tid);
    }
 }
 
@@ -478,8 +511,11 @@ template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, c
       attr = true;
    }
    const int nch = D.K / kTKC;
-   const unsigned grid = (unsigned)D.Tiles.NTiles * nch;
-   k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, nch);
+   // with the D role (which needs two tracers to prime its pipeline) a CTA walks all chunks of its tile
+   static const int persist = getenv("OMEGA_TILE_PERSIST") ? atoi(getenv("OMEGA_TILE_PERSIST")) : 1;
+   const bool walk = HYP && persist;
+   const unsigned grid = (unsigned)D.Tiles.NTiles * (walk ? 1 : nch);
+   k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, walk ? -nch : nch);
    return 0;
 }
 template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
