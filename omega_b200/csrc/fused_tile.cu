@@ -37,7 +37,7 @@ namespace omega {
 constexpr int kTKC     = 16;                    // levels per tile
 constexpr int kTLanes  = 8;                     // threads per row (2 levels each)
 constexpr int kTRole   = kTileCells * kTLanes;  // threads per role
-constexpr int kTStages = 4;                     // tracer row-set buffers
+constexpr int kTStages = 5;                     // tracer row-set buffers
 
 struct TileSmem {
    double H[kTileRows][kTKC];
@@ -161,11 +161,15 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
          if (r < X.nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc + 2 * p));
       }
    };
-   // tracer m of chunk c is item c*T + m of the stream and lives in buffer (c*T + m) % kTStages
+   // tracer m of chunk c is item c*T + m of the stream and lives in buffer (c*T + m) % kTStages;
+   // while tracer m is worked on, the item `lead` places ahead is copied
+   const int lead = T >= 3 ? 3 : 2;
    copy_rows(P.Hs, &S.H[0][0], kc0);
    cp_commit();
-   copy_rows(P.Trs, &S.Phi[0][0][0], kc0);
-   cp_commit();
+   for (int s = 0; s + 1 < lead; ++s) {
+      copy_rows(P.Trs + s * CS, &S.Phi[s][0][0], kc0);
+      cp_commit();
+   }
    load_tables<2 * kTRole>(M, S, tid, X.nR1, X.nc);
    const bool ring = t < X.n1 * kTLanes; // this thread's ring-1 row piece (n1 <= 56 rows x 8 pieces < 512 threads)
    const int r1    = X.nc + (ring ? X.i : 0);
@@ -173,9 +177,10 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
    unsigned char *Cb  = reinterpret_cast<unsigned char *>(&S.Cf1[ring ? X.i : 0][0][0]) + 16u * p;
    for (int c = 0; c < NCh; ++c) {
       const int kc = kc0 + c * kTKC, it0 = c * T;
-      copy_rows(P.Trs + CS, &S.Phi[(it0 + 1) % kTStages][0][0], kc); // tracer 1 of this chunk (T >= 2)
+      copy_rows(P.Trs + (size_t)(lead - 1) * CS, &S.Phi[(it0 + lead - 1) % kTStages][0][0], kc); // T >= 2
       cp_commit();
-      cp_wait<1>();    // h and tracer 0 of this chunk have landed (this thread's pieces)
+      // h and tracer 0 of this chunk have landed (this thread's pieces)
+      if (lead == 3) cp_wait<2>(); else cp_wait<1>();
       __syncthreads(); // ... and everybody else's; the T role is done with the previous chunk
       const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
       // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
@@ -206,19 +211,24 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
       }
       for (int m = 0; m < T; ++m) {
          if (m > 0) {
-            cp_wait<1>();                // tracer m has landed (this thread's pieces)
+            if (lead == 3) cp_wait<2>(); else cp_wait<1>(); // tracer m has landed (this thread's pieces)
             bar_sync(kBarDRole, kTRole); // ... and the other D threads'
          }
          // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
          if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
-         // next item of the stream, two ahead: a tracer of this chunk, then h and tracer 0 of the next
-         if (m + 2 < T) copy_rows(P.Trs + (size_t)(m + 2) * CS, &S.Phi[(it0 + m + 2) % kTStages][0][0], kc);
-         else if (c + 1 < NCh) {
-            if (m + 2 == T) {
-               bar_sync(kBarHFree, 2 * kTRole); // both roles have read this chunk's thickness rows
-               copy_rows(P.Hs, &S.H[0][0], kc + kTKC);
+         // next item of the stream, `lead` ahead: a tracer of this chunk, then h and the first
+         // tracers of the next chunk
+         {
+            const int n = m + lead;
+            if (n < T) copy_rows(P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % kTStages][0][0], kc);
+            else if (c + 1 < NCh) {
+               if (n == T) {
+                  bar_sync(kBarHFree, 2 * kTRole); // both roles have read this chunk's thickness rows
+                  copy_rows(P.Hs, &S.H[0][0], kc + kTKC);
+               } else {
+                  copy_rows(P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % kTStages][0][0], kc + kTKC);
+               }
             }
-            else copy_rows(P.Trs, &S.Phi[(it0 + T) % kTStages][0][0], kc + kTKC);
          }
          cp_commit();
          const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + m) % kTStages][0][0]);
