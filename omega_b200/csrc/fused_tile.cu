@@ -613,59 +613,81 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
       put(r, u, h0, h1, a, b);
       if (r2 < nSt) put(r2, u2, g0, g1, a2, b2);
    }
+   // ---- pass 2a: gradient / diffusion terms and RK operands of the own edges.  A thread owns
+   // the same (edge, piece) items as in pass 1, at most kTileEdgesOwn*8/512 = 4 of them; all
+   // their gathered rows are in flight together, and what survives the barrier is
+   //   p1 = (first stage ? u_cur : u_next) + B*m*G,   p2 = u_cur + A*m*G     (two registers pairs per item)
+   constexpr int kItems = kTileEdgesOwn * kTLanes / kEThreads;
+   double p1[kItems][2], p2[kItems][2];
+   const bool ucur_is_us = P.First && P.Ucur == P.Us;
+#pragma unroll
+   for (int it = 0; it < kItems; ++it) {
+      const int r = (tid >> 3) + it * (kEThreads / kTLanes);
+      p1[it][0] = p1[it][1] = p2[it][0] = p2[it][1] = 0.0;
+      if (r < nOwn) {
+         const int e    = S.SRow[r];
+         const size_t o = (size_t)e * K + k;
+         const int4 cv  = S.CV[r];
+         const double mask = M.EdgeMask[e];
+         const double InvDc = M.InvDcEdge[e] * mask, InvDv = M.InvDvEdge[e] * mask;
+         if (P.PVOn) prefetch_row(M.WeightsOnEdge + (size_t)e * M.MaxEdges2 + p, 1); // weights towards L1 for pass 2b
+         double x0[2], x1[2], y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
+         ldv<2>(x0, P.X + (size_t)cv.x * K + k);
+         ldv<2>(x1, P.X + (size_t)cv.y * K + k);
+         ldv<2>(y0, P.Y + (size_t)cv.x * K + k);
+         ldv<2>(y1, P.Y + (size_t)cv.y * K + k);
+         ldv<2>(z0, P.Z + (size_t)cv.z * K + k);
+         ldv<2>(z1, P.Z + (size_t)cv.w * K + k);
+         if (P.First || !P.Last) ldp<2>(ucur, (ucur_is_us ? P.Us : P.Ucur) + o);
+         if (!P.First) ldp<2>(base, P.Unext + o);
+#pragma unroll
+         for (int q2 = 0; q2 < 2; ++q2) {
+            double g = (P.SY * (y1[q2] - y0[q2])) * InvDc - (P.SZ * (z1[q2] - z0[q2])) * InvDv;
+            if (P.XOn) g -= (x1[q2] - x0[q2]) * InvDc;
+            p1[it][q2] = (P.First ? ucur[q2] : base[q2]) + P.B * g;
+            p2[it][q2] = ucur[q2] + P.A * g;
+         }
+      }
+   }
    __syncthreads();
-   // ---- pass 2: own edges
+   // ---- pass 2b: neighbour sum of the own edges from shared memory (always 10 entries: the
+   // weight table is zero behind the edge's count and the local index then points at the edge
+   // itself), then the update
    const unsigned char *Fb = reinterpret_cast<const unsigned char *>(&S.F[0][0]);
    const unsigned char *Qb = reinterpret_cast<const unsigned char *>(&S.Q[0][0]);
-   for (int q = tid; q < nOwn * kTLanes; q += kEThreads) {
-      const int r = q >> 3, e = S.SRow[r];
-      const size_t o = (size_t)e * K + k;
-      const int4 cv = S.CV[r];
-      const int2 cc = make_int2(cv.x, cv.y), vv = make_int2(cv.z, cv.w);
-      const double mask = M.EdgeMask[e];
-      const double InvDc = M.InvDcEdge[e], InvDv = M.InvDvEdge[e];
-      // the gathered rows of the gradient / diffusion terms and the RK operands: in flight
-      // while the neighbour sum runs from shared memory
-      double x0[2], x1[2], y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
-      ldv<2>(x0, P.X + (size_t)cc.x * K + k);
-      ldv<2>(x1, P.X + (size_t)cc.y * K + k);
-      ldv<2>(y0, P.Y + (size_t)cc.x * K + k);
-      ldv<2>(y1, P.Y + (size_t)cc.y * K + k);
-      ldv<2>(z0, P.Z + (size_t)vv.x * K + k);
-      ldv<2>(z1, P.Z + (size_t)vv.y * K + k);
-      const bool ucur_is_us = P.First && P.Ucur == P.Us;
-      if (P.First || !P.Last) ldp<2>(ucur, (ucur_is_us ? P.Us : P.Ucur) + o);
-      if (!P.First) ldp<2>(base, P.Unext + o);
-      double tend[2] = {0, 0};
-      if (P.PVOn) {
-         const unsigned po = (unsigned)(2 * p) * 8u;
-         const double2 qe = lds2(Qb, r * (kTKC * 8u) + po);
-         const int ne = M.NEdgesOnEdge[e];
-         const double *W = M.WeightsOnEdge + (size_t)e * M.MaxEdges2;
+   const unsigned po = (unsigned)(2 * p) * 8u;
+#pragma unroll
+   for (int it = 0; it < kItems; ++it) {
+      const int r = (tid >> 3) + it * (kEThreads / kTLanes);
+      if (r < nOwn) {
+         const int e    = S.SRow[r];
+         const size_t o = (size_t)e * K + k;
          double acc0 = 0, acc1 = 0;
-         for (int j = 0; j < ne; ++j) {
-            const unsigned lo = S.EoE[r][j] * (kTKC * 8u) + po;
-            const double w    = W[j];
-            const double2 f = lds2(Fb, lo), qj = lds2(Qb, lo);
-            acc0 += w * f.x * ((qe.x + qj.x) * 0.5);
-            acc1 += w * f.y * ((qe.y + qj.y) * 0.5);
+         if (P.PVOn) {
+            const double2 qe = lds2(Qb, r * (kTKC * 8u) + po);
+            const double2 *W = reinterpret_cast<const double2 *>(M.WeightsOnEdge + (size_t)e * M.MaxEdges2);
+#pragma unroll
+            for (int j2 = 0; j2 < 5; ++j2) {
+               const double2 w = __ldg(W + j2);
+               const unsigned ix = *reinterpret_cast<const unsigned *>(&S.EoE[r][2 * j2]);
+               const unsigned la = (ix & 0xffffu) * (kTKC * 8u) + po, lb = (ix >> 16) * (kTKC * 8u) + po;
+               const double2 fa = lds2(Fb, la), qa = lds2(Qb, la), fb = lds2(Fb, lb), qb = lds2(Qb, lb);
+               acc0 += w.x * fa.x * ((qe.x + qa.x) * 0.5);
+               acc1 += w.x * fa.y * ((qe.y + qa.y) * 0.5);
+               acc0 += w.y * fb.x * ((qe.x + qb.x) * 0.5);
+               acc1 += w.y * fb.y * ((qe.y + qb.y) * 0.5);
+            }
+            const double mask = M.EdgeMask[e];
+            acc0 *= mask;
+            acc1 *= mask;
          }
-         tend[0] = mask * acc0;
-         tend[1] = mask * acc1;
-      }
-#pragma unroll
-      for (int q2 = 0; q2 < 2; ++q2) {
-         if (P.XOn) tend[q2] -= mask * (x1[q2] - x0[q2]) * InvDc;
-         tend[q2] += mask * (P.SY * (y1[q2] - y0[q2]) * InvDc - P.SZ * (z1[q2] - z0[q2]) * InvDv);
-      }
-      double out[2];
-#pragma unroll
-      for (int q2 = 0; q2 < 2; ++q2) out[q2] = (P.First ? ucur[q2] : base[q2]) + P.B * tend[q2];
-      stv<2>(P.Unext + o, out);
-      if (!P.Last) {
-#pragma unroll
-         for (int q2 = 0; q2 < 2; ++q2) out[q2] = ucur[q2] + P.A * tend[q2];
-         stv<2>(P.Uprov + o, out);
+         double out[2] = {p1[it][0] + P.B * acc0, p1[it][1] + P.B * acc1};
+         stv<2>(P.Unext + o, out);
+         if (!P.Last) {
+            out[0] = p2[it][0] + P.A * acc0;
+            out[1] = p2[it][1] + P.A * acc1;
+            stv<2>(P.Uprov + o, out);
+         }
       }
    }
 }

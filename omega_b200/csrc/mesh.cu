@@ -458,6 +458,9 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
       }
       STAGE(G.NEdgesOnEdge, neoe);
       STAGE(G.EdgesOnEdge, eoe);
+      // zero weight behind the (trimmed) count: the tiled edge pass always sums 10 entries
+      for (int e = 0; e < NE; ++e)
+         for (int j = neoe[e]; j < ME2; ++j) w[(size_t)e * ME2 + j] = 0.0;
       STAGE(G.WeightsOnEdge, w);
       // flattened gather tables of the fused edge kernel: cells and vertices of every
       // EdgesOnEdge entry, so a neighbour costs one index level instead of three
