@@ -159,6 +159,12 @@ int omega_field_to_device(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOut
                           int NInner, const double *Host, double *Dev, void *Stream);
 int omega_field_to_host(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
                         int NInner, const double *Dev, double *Host, void *Stream);
+/* Same, without the final stream synchronisation: Host must be pinned and is valid
+ * once the caller has synchronised Stream (or an event recorded after the call).
+ * omega_field_to_device never synchronises; with a pinned Host it is asynchronous too,
+ * so transfers on other streams overlap the step (bench.py e2e pipeline). */
+int omega_field_to_host_async(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
+                              int NInner, const double *Dev, double *Host, void *Stream);
 
 /* ---- Tendencies + AuxiliaryState + TimeStepper -------------------------- */
 int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int NTracers,

@@ -576,15 +576,15 @@ int omega_field_to_device(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
    return 0;
 }
 
-int omega_field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
-                        const double *Dev, double *Host, void *Stream) {
+static int field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, const double *Dev,
+                         double *Host, void *Stream, bool Sync) {
    OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3, "omega_field_to_host: bad argument");
    cudaStream_t S     = (cudaStream_t)Stream;
    const int NRows    = n_size(M, Elem);
    const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
    if (!M->Reordered) {
       OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, Dev, bytes, cudaMemcpyDeviceToHost, S));
-      OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
+      if (Sync) OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
       return 0;
    }
    // host row r comes from device row IPerm[r]
@@ -594,8 +594,18 @@ int omega_field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, i
    OMEGA_CUDA_CHECK(cudaGetLastError());
    OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, stage, bytes, cudaMemcpyDeviceToHost, S));
    OMEGA_CUDA_CHECK(cudaFreeAsync(stage, S));
-   OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
+   if (Sync) OMEGA_CUDA_CHECK(cudaStreamSynchronize(S));
    return 0;
+}
+
+int omega_field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
+                        const double *Dev, double *Host, void *Stream) {
+   return field_to_host(M, Elem, NOuter, NInner, Dev, Host, Stream, true);
+}
+
+int omega_field_to_host_async(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
+                              const double *Dev, double *Host, void *Stream) {
+   return field_to_host(M, Elem, NOuter, NInner, Dev, Host, Stream, false);
 }
 
 } // extern "C"

@@ -67,23 +67,27 @@ class HorzMesh:
         shape = ((nouter,) if nouter else ()) + (self.NSize[kind],) + ((self.K,) if levels else ())
         return torch.zeros(shape, dtype=torch.float64, device=self.device)
 
-    def to_device(self, kind, host: np.ndarray, out: torch.Tensor | None = None):
-        """host-order numpy [..., NSize, K] -> device-order tensor."""
+    def to_device(self, kind, host: np.ndarray, out: torch.Tensor | None = None, sync: bool = True):
+        """host-order numpy [..., NSize, K] -> device-order tensor.  sync=False: asynchronous on the
+        current stream (host must be pinned and stay alive until the stream has passed the copy)."""
         host = np.ascontiguousarray(host, np.float64)
         nouter = host.shape[0] if host.ndim == 3 else 1
         ninner = host.shape[-1] if host.ndim >= 2 else 1
         if out is None:
             out = torch.empty(host.shape, dtype=torch.float64, device=self.device)
         _chk(self.lib, self.lib.omega_field_to_device(self.h, kind, nouter, ninner, host.ctypes.data_as(capi.c_dbl_p), _dptr(out), _stream()), "omega_field_to_device")
-        torch.cuda.current_stream().synchronize()  # host buffer may be a temporary
+        if sync:
+            torch.cuda.current_stream().synchronize()  # host buffer may be a temporary
         return out
 
-    def to_host(self, kind, dev: torch.Tensor, out: np.ndarray | None = None):
+    def to_host(self, kind, dev: torch.Tensor, out: np.ndarray | None = None, sync: bool = True):
+        """sync=False: asynchronous on the current stream into a pinned `out`."""
         nouter = dev.shape[0] if dev.dim() == 3 else 1
         ninner = dev.shape[-1] if dev.dim() >= 2 else 1
         if out is None:
             out = np.empty(tuple(dev.shape), np.float64)
-        _chk(self.lib, self.lib.omega_field_to_host(self.h, kind, nouter, ninner, _dptr(dev), out.ctypes.data_as(capi.c_dbl_p), _stream()), "omega_field_to_host")
+        fn = self.lib.omega_field_to_host if sync else self.lib.omega_field_to_host_async
+        _chk(self.lib, fn(self.h, kind, nouter, ninner, _dptr(dev), out.ctypes.data_as(capi.c_dbl_p), _stream()), "omega_field_to_host")
         return out
 
     def close(self):
