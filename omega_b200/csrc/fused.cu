@@ -129,28 +129,12 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    }
 }
 
-// Del2Edge of VelocityDel2AuxVars::computeVarsOnEdge (VelocityDel2AuxVars.h:21-45)
-template <int V>
-__device__ __forceinline__ void del2_edge(const DMesh &M, int e, int k, const double *__restrict__ Div,
-                                          const double *__restrict__ RelVort, double (&out)[V]) {
-   const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
-   const double InvDc = M.InvDcEdge[e], InvDv = M.InvDvEffEdge[e], mask = M.EdgeMask[e];
-   double d0[V], d1[V], r0[V], r1[V];
-   ldv<V>(d0, Div + (size_t)cc.x * M.K + k);
-   ldv<V>(d1, Div + (size_t)cc.y * M.K + k);
-   ldv<V>(r0, RelVort + (size_t)vv.x * M.K + k);
-   ldv<V>(r1, RelVort + (size_t)vv.y * M.K + k);
-#pragma unroll
-   for (int q = 0; q < V; ++q) {
-      const double GradDiv  = (d1[q] - d0[q]) * InvDc;
-      const double CurlVort = -(r1[q] - r0[q]) * InvDv;
-      out[q]                = mask * GradDiv + CurlVort;
-   }
-}
-
 // ---------------------------------------------------------------------------
 // fB: VelocityDel2AuxVars::computeVarsOnCell / computeVarsOnVertex
-// (VelocityDel2AuxVars.h:47-89) with Del2Edge recomputed per use.
+// (VelocityDel2AuxVars.h:47-89) with Del2Edge (VelocityDel2AuxVars.h:21-45) never
+// stored: its two differences are folded, per (cell, edge) and per (vertex,
+// edge), into the flattened stencils of omega_dev.h (B2*), so one element costs
+// two table loads and three gathered rows per edge instead of nine loads and four rows.
 // ---------------------------------------------------------------------------
 template <int V>
 __global__ void __launch_bounds__(kBlock)
@@ -161,49 +145,46 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = M.InvAreaCell[c];
-      const int ne      = M.NEdgesOnCell[c];
-      double t[V] = {0};
+      double ds[V], t[V] = {0};
+      ldv<V>(ds, Div + (size_t)c * M.K + k);
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-         if (j < ne) {
-            const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
-            const double cf = M.DvEdge[e] * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
-            double d2[V];
-            del2_edge<V>(M, e, k, Div, RelVort, d2);
+         const int4 ix    = M.B2CellIdx[c * 6 + j];
+         const double2 cf = M.B2CellCf[c * 6 + j];
+         double dn[V], z0[V], z1[V];
+         ldv<V>(dn, Div + (size_t)ix.x * M.K + k);
+         ldv<V>(z0, RelVort + (size_t)ix.y * M.K + k);
+         ldv<V>(z1, RelVort + (size_t)ix.z * M.K + k);
 #pragma unroll
-            for (int q = 0; q < V; ++q) t[q] -= cf * d2[q];
-         }
+         for (int q = 0; q < V; ++q) t[q] += cf.x * (dn[q] - ds[q]) + cf.y * (z1[q] - z0[q]);
       }
       if (YMode) {
          // tiled edge pass: Del2 and Del4 velocity terms share one difference per element kind,
          // Y(c) = nu2*Div - nu4*DivFactor*Del2Div, Z(v) = nu2*RelVort - nu4*Del2RelVort
          // (VelocityDiffusionOnEdge, VelocityHyperDiffOnEdge, TendencyTerms.h:195-269)
-         double d[V];
-         ldv<V>(d, Div + (size_t)c * M.K + k);
 #pragma unroll
-         for (int q = 0; q < V; ++q) t[q] = Nu2 * d[q] - Nu4Div * t[q];
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * ds[q] - Nu4Div * t[q];
       }
       stv<V>(Del2Div + (size_t)c * M.K + k, t);
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      const double InvAt = M.InvAreaTriangle[v];
-      double t[V] = {0};
+      double zs[V], t[V] = {0};
+      ldv<V>(zs, RelVort + (size_t)v * M.K + k);
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
-         const int e     = M.EdgesOnVertex[v * 3 + j];
-         const double cf = InvAt * M.DcEdge[e] * M.EdgeSignOnVertex[v * 3 + j];
-         double d2[V];
-         del2_edge<V>(M, e, k, Div, RelVort, d2);
+         const int4 ix    = M.B2VertIdx[v * 3 + j];
+         const double2 cf = M.B2VertCf[v * 3 + j];
+         double d0[V], d1[V], zo[V];
+         ldv<V>(d0, Div + (size_t)ix.x * M.K + k);
+         ldv<V>(d1, Div + (size_t)ix.y * M.K + k);
+         ldv<V>(zo, RelVort + (size_t)ix.z * M.K + k);
 #pragma unroll
-         for (int q = 0; q < V; ++q) t[q] += cf * d2[q];
+         for (int q = 0; q < V; ++q) t[q] += cf.x * (d1[q] - d0[q]) + cf.y * (zo[q] - zs[q]);
       }
       if (YMode) {
-         double z[V];
-         ldv<V>(z, RelVort + (size_t)v * M.K + k);
 #pragma unroll
-         for (int q = 0; q < V; ++q) t[q] = Nu2 * z[q] - Nu4 * t[q];
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * zs[q] - Nu4 * t[q];
       }
       stv<V>(Del2RelVort + (size_t)v * M.K + k, t);
    }

@@ -509,6 +509,54 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
       STAGE(G.InvAreaCell, iar);
       STAGE(G.InvAreaTriangle, iat);
    }
+   {
+      // k_fB tables (omega_dev.h).  Del2Edge(e) = mask (Div(c1)-Div(c0))/dc - (RelVort(v1)-RelVort(v0))/max(dv, dc/4)
+      // (VelocityDel2AuxVars.h:21-45); Div(c1)-Div(c0) = -sign_c (Div(nbr)-Div(c)), RelVort(v1)-RelVort(v0) =
+      // -sign_v (RelVort(vo)-RelVort(v)) with the edge signs of HorzMesh.cpp:527-566.
+      std::vector<int> eoc = gather_index_rows(D->EdgesOnCell, PC, ME, IE), nec = gather_rows(D->NEdgesOnCell, PC, 1);
+      std::vector<int> eov = gather_index_rows(D->EdgesOnVertex, PV, 3, IE);
+      std::vector<double> sc = gather_rows(M->EdgeSignOnCellH.data(), PC, ME), sv = gather_rows(M->EdgeSignOnVertexH.data(), PV, 3);
+      std::vector<double> dc = gather_rows(D->DcEdge, PE, 1), dv = gather_rows(D->DvEdge, PE, 1);
+      std::vector<double> mk = gather_rows(M->EdgeMaskH.data(), PE, 1);
+      std::vector<double> ar = gather_rows(D->AreaCell, PC, 1), at = gather_rows(D->AreaTriangle, PV, 1);
+      std::vector<int> ci((size_t)(NC + 1) * 6 * 4, 0), vi((size_t)(NV + 1) * 3 * 4, 0);
+      std::vector<double> cc((size_t)(NC + 1) * 6 * 2, 0.0), vc((size_t)(NV + 1) * 3 * 2, 0.0);
+      for (int c = 0; c <= NC; ++c)
+         for (int j = 0; j < 6; ++j) {
+            const size_t o = ((size_t)c * 6 + j);
+            ci[o * 4] = c; ci[o * 4 + 1] = NV; ci[o * 4 + 2] = NV;
+            if (c < NC && j < nec[c] && j < ME) {
+               const int e = eoc[(size_t)c * ME + j];
+               const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
+               ci[o * 4] = a == c ? b : a; ci[o * 4 + 1] = voe[(size_t)e * 2]; ci[o * 4 + 2] = voe[(size_t)e * 2 + 1];
+               const double cf = dv[e] * (1.0 / ar[c]) * sc[(size_t)c * ME + j];
+               cc[o * 2]     = cf * sc[(size_t)c * ME + j] * mk[e] * (1.0 / dc[e]);
+               cc[o * 2 + 1] = cf * (1.0 / std::max(dv[e], 0.25 * dc[e]));
+            }
+         }
+      for (int v = 0; v <= NV; ++v)
+         for (int j = 0; j < 3; ++j) {
+            const size_t o = ((size_t)v * 3 + j);
+            vi[o * 4] = NC; vi[o * 4 + 1] = NC; vi[o * 4 + 2] = v;
+            if (v < NV) {
+               const int e = eov[(size_t)v * 3 + j];
+               if (e < NE) {
+                  vi[o * 4] = coe[(size_t)e * 2]; vi[o * 4 + 1] = coe[(size_t)e * 2 + 1];
+                  const int a = voe[(size_t)e * 2], b = voe[(size_t)e * 2 + 1];
+                  vi[o * 4 + 2] = a == v ? b : a;
+                  const double cf = (1.0 / at[v]) * dc[e] * sv[(size_t)v * 3 + j];
+                  vc[o * 2]     = cf * mk[e] * (1.0 / dc[e]);
+                  vc[o * 2 + 1] = cf * sv[(size_t)v * 3 + j] * (1.0 / std::max(dv[e], 0.25 * dc[e]));
+               }
+            }
+         }
+      const int *qi = nullptr;
+      const double *qd = nullptr;
+      rc |= to_device(M, ci, &qi); G.B2CellIdx = reinterpret_cast<const int4 *>(qi);
+      rc |= to_device(M, vi, &qi); G.B2VertIdx = reinterpret_cast<const int4 *>(qi);
+      rc |= to_device(M, cc, &qd); G.B2CellCf = reinterpret_cast<const double2 *>(qd);
+      rc |= to_device(M, vc, &qd); G.B2VertCf = reinterpret_cast<const double2 *>(qd);
+   }
 #undef STAGE
    if (!rc)
       rc |= build_tiles(M, NC, D->NCellsOwned, ME, gather_rows(D->NEdgesOnCell, PC, 1),

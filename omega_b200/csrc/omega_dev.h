@@ -95,6 +95,13 @@ struct DMesh {
    // reciprocals evaluated once on the host (IEEE division, the same bits the kernels' own
    // 1.0/x gave): 1/dc, 1/dv, 1/max(dv, 0.25 dc) per edge; 1/AreaCell; 1/AreaTriangle
    const double *InvDcEdge, *InvDvEdge, *InvDvEffEdge, *InvAreaCell, *InvAreaTriangle;
+   // flattened stencils of k_fB (velocity Del2 of Del2): per (cell, edge j) the rows
+   // {neighbour cell, v0, v1} and the coefficients {A, B} of
+   //   Del2Div(c) = sum_j A_j (Div(nbr_j) - Div(c)) + B_j (RelVort(v1_j) - RelVort(v0_j)),
+   // per (vertex, edge j) the rows {c0, c1, other vertex} and {A', B'} of
+   //   Del2RelVort(v) = sum_j A'_j (Div(c1_j) - Div(c0_j)) + B'_j (RelVort(vo_j) - RelVort(v))
+   const int4 *B2CellIdx, *B2VertIdx;
+   const double2 *B2CellCf, *B2VertCf;
    DTiles Tiles; // NTiles == 0 when the mesh has cells with more than 6 edges
 };
 
