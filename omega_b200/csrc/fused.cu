@@ -66,24 +66,19 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = M.InvAreaCell[c];
-      const int ne      = M.NEdgesOnCell[c];
       double ke[V] = {0}, dv[V] = {0};
-      // unrolled over the (at most 6, checked at launch) edges: all u-row gathers in flight together
+      // six table entries per cell (omega_dev.h: ACell*; edge row = boundary slot and zero
+      // coefficients when the cell has fewer edges): all u-row gathers in flight together
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-         if (j < ne) {
-            const int e        = M.EdgesOnCell[c * M.MaxEdges + j];
-            const double dve   = M.DvEdge[e];
-            const double kcoef = 0.5 * dve * M.DcEdge[e] * 0.5 * InvA;
-            const double dcoef = dve * InvA * M.EdgeSignOnCell[c * M.MaxEdges + j];
-            double u[V];
-            ldv<V>(u, U + (size_t)e * M.K + k);
+         const int e      = M.ACellEdge[c * 6 + j];
+         const double2 cf = M.ACellCf[c * 6 + j];
+         double u[V];
+         ldv<V>(u, U + (size_t)e * M.K + k);
 #pragma unroll
-            for (int q = 0; q < V; ++q) {
-               ke[q] += kcoef * u[q] * u[q];
-               dv[q] -= dcoef * u[q];
-            }
+         for (int q = 0; q < V; ++q) {
+            ke[q] += cf.x * u[q] * u[q];
+            dv[q] -= cf.y * u[q];
          }
       }
       if (XMode) {
@@ -100,21 +95,18 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      const double InvAt = M.InvAreaTriangle[v];
       double hv[V] = {0}, rv[V] = {0};
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
-         const int c       = M.CellsOnVertex[v * 3 + j];
-         const int e       = M.EdgesOnVertex[v * 3 + j];
-         const double kite = InvAt * M.KiteAreasOnVertex[v * 3 + j];
-         const double dcs  = InvAt * M.DcEdge[e] * M.EdgeSignOnVertex[v * 3 + j];
+         const int2 ix    = M.AVertIdx[v * 3 + j];
+         const double2 cf = M.AVertCf[v * 3 + j];
          double h[V], u[V];
-         ldv<V>(h, H + (size_t)c * M.K + k);
-         ldv<V>(u, U + (size_t)e * M.K + k);
+         ldv<V>(h, H + (size_t)ix.x * M.K + k);
+         ldv<V>(u, U + (size_t)ix.y * M.K + k);
 #pragma unroll
          for (int q = 0; q < V; ++q) {
-            hv[q] += kite * h[q];
-            rv[q] += dcs * u[q];
+            hv[q] += cf.x * h[q];
+            rv[q] += cf.y * u[q];
          }
       }
       const double f = M.FVertex[v];

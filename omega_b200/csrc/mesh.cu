@@ -550,6 +550,41 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
                }
             }
          }
+      // k_fA tables (KineticAuxVars.h:20-47, VorticityAuxVars.h:24-59), coefficients evaluated in the
+      // kernels' former order so the bits are unchanged
+      {
+         std::vector<int> cov = gather_index_rows(D->CellsOnVertex, PV, 3, IC);
+         std::vector<double> kite = gather_rows(D->KiteAreasOnVertex, PV, 3);
+         std::vector<int> ae((size_t)(NC + 1) * 6, NE), avi((size_t)(NV + 1) * 3 * 2, 0);
+         std::vector<double> ac((size_t)(NC + 1) * 6 * 2, 0.0), avc((size_t)(NV + 1) * 3 * 2, 0.0);
+         for (int c = 0; c < NC; ++c) {
+            const double InvA = 1.0 / ar[c];
+            for (int j = 0; j < nec[c] && j < 6 && j < ME; ++j) {
+               const int e = eoc[(size_t)c * ME + j];
+               ae[(size_t)c * 6 + j] = e;
+               ac[((size_t)c * 6 + j) * 2]     = 0.5 * dv[e] * dc[e] * 0.5 * InvA;
+               ac[((size_t)c * 6 + j) * 2 + 1] = dv[e] * InvA * sc[(size_t)c * ME + j];
+            }
+         }
+         for (int v = 0; v <= NV; ++v)
+            for (int j = 0; j < 3; ++j) {
+               const size_t o = (size_t)v * 3 + j;
+               avi[o * 2] = NC; avi[o * 2 + 1] = NE;
+               if (v < NV) {
+                  const double InvAt = 1.0 / at[v];
+                  const int e = eov[o];
+                  avi[o * 2] = cov[o]; avi[o * 2 + 1] = e;
+                  avc[o * 2]     = InvAt * kite[o];
+                  avc[o * 2 + 1] = InvAt * (e < NE ? dc[e] : 0.0) * sv[o];
+               }
+            }
+         const int *qi2 = nullptr;
+         const double *qd2 = nullptr;
+         rc |= to_device(M, ae, &G.ACellEdge);
+         rc |= to_device(M, avi, &qi2); G.AVertIdx = reinterpret_cast<const int2 *>(qi2);
+         rc |= to_device(M, ac, &qd2); G.ACellCf = reinterpret_cast<const double2 *>(qd2);
+         rc |= to_device(M, avc, &qd2); G.AVertCf = reinterpret_cast<const double2 *>(qd2);
+      }
       const int *qi = nullptr;
       const double *qd = nullptr;
       rc |= to_device(M, ci, &qi); G.B2CellIdx = reinterpret_cast<const int4 *>(qi);
