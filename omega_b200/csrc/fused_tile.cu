@@ -79,10 +79,8 @@ __device__ __forceinline__ unsigned nbl_get(const uint4 &t, int j) {
 }
 
 // named barriers (0 is __syncthreads)
-constexpr int kBarDRole = 1; // the D role among itself
-constexpr int kBarHFree = 7; // the T role has built its coefficients: the thickness rows may be overwritten
-__device__ __forceinline__ int bar_d2_ready(int l) { return 3 + (l & 1); }
-__device__ __forceinline__ int bar_d2_free(int l) { return 5 + (l & 1); }
+__device__ __forceinline__ int bar_phi_ready(int l) { return 1 + (l & 1); } // T -> D: tracer l has landed
+__device__ __forceinline__ int bar_d2_ready(int l) { return 3 + (l & 1); }  // D -> T: Del2 of tracer l is complete
 
 // the common view of a tile a thread needs in either role
 struct TileCtx {
@@ -139,6 +137,18 @@ struct RowCopier {
    }
 };
 
+// One role's share (512 threads) of a row-set copy (h or one tracer) of level chunk kc into a
+// [row][16] buffer: item q = t + 512 i is row q/8, 16-byte piece q%8, and lands at byte 16 q.
+// Source offsets are re-derived from GRow on every copy (three shared loads), not held in registers.
+__device__ __forceinline__ void copy_rows_g(const TileSmem &S, int nR, int K, int t, const double *F, const void *Dst, int kc) {
+   const unsigned d = smem_u32(Dst) + 16u * t;
+#pragma unroll
+   for (int i = 0; i < 3; ++i) {
+      const int r = (t >> 3) + i * (kTRole / kTLanes);
+      if (r < nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc + 2 * (t & 7)));
+   }
+}
+
 // =================== D role: Del2(phi) of own + ring-1 rows ===================
 // (TracerAuxVars.h:61-91; s*(phi(c1)-phi(c0)) == phi(self)-phi(nbr) exactly)
 // With NCh > 1 the CTA walks the NCh level chunks of its tile one after the other: tables
@@ -146,42 +156,16 @@ struct RowCopier {
 // two tracers of chunk c, so only the first chunk pays the start-up latency of a tile.
 __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int kc0, int NCh,
                                        int tid) {
-   const int T = P.NTracers, K = M.K;
-   const size_t CS = (size_t)M.NCellsSize * K;
-   // The D role also feeds the pipeline: one row set (h or a tracer) per tracer worked on,
-   // two ahead.  Item q = t + 512 i of a row-set copy is row q/8, 16-byte piece q%8, and
-   // lands at byte 16 q of the [row][16] buffer; source offsets are re-derived from GRow
-   // on every copy (three shared loads) rather than held in registers.
+   const int T = P.NTracers;
    const int t = X.t, p = X.p;
-   auto copy_rows = [&](const double *F, const void *Dst, int kc) {
-      const unsigned d = smem_u32(Dst) + 16u * t;
-#pragma unroll
-      for (int i = 0; i < 3; ++i) {
-         const int r = (t >> 3) + i * (kTRole / kTLanes);
-         if (r < X.nR) cp_async16(d + i * (16u * kTRole), F + ((size_t)S.GRow[r] * K + kc + 2 * p));
-      }
-   };
-   // tracer m of chunk c is item c*T + m of the stream and lives in buffer (c*T + m) % kTStages;
-   // while tracer m is worked on, the item `lead` places ahead is copied
-   const int lead = T >= 3 ? 3 : 2;
-   copy_rows(P.Hs, &S.H[0][0], kc0);
-   cp_commit();
-   for (int s = 0; s + 1 < lead; ++s) {
-      copy_rows(P.Trs + s * CS, &S.Phi[s][0][0], kc0);
-      cp_commit();
-   }
    load_tables<2 * kTRole>(M, S, tid, X.nR1, X.nc);
    const bool ring = t < X.n1 * kTLanes; // this thread's ring-1 row piece (n1 <= 56 rows x 8 pieces < 512 threads)
    const int r1    = X.nc + (ring ? X.i : 0);
    const unsigned ro1 = (r1 * kTKC + 2 * p) * 8u;
    unsigned char *Cb  = reinterpret_cast<unsigned char *>(&S.Cf1[ring ? X.i : 0][0][0]) + 16u * p;
    for (int c = 0; c < NCh; ++c) {
-      const int kc = kc0 + c * kTKC, it0 = c * T;
-      copy_rows(P.Trs + (size_t)(lead - 1) * CS, &S.Phi[(it0 + lead - 1) % kTStages][0][0], kc); // T >= 2
-      cp_commit();
-      // h and tracer 0 of this chunk have landed (this thread's pieces)
-      if (lead == 3) cp_wait<2>(); else cp_wait<1>();
-      __syncthreads(); // ... and everybody else's; the T role is done with the previous chunk
+      const int it0 = c * T;
+      __syncthreads(); // h and tracer 0 of this chunk have landed (copied by the T role); tables are visible
       const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
       // own row: -(1/A) * G * mean thickness per edge, in registers for all tracers
       double cfA[kME][2];
@@ -210,27 +194,9 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
          }
       }
       for (int m = 0; m < T; ++m) {
-         if (m > 0) {
-            if (lead == 3) cp_wait<2>(); else cp_wait<1>(); // tracer m has landed (this thread's pieces)
-            bar_sync(kBarDRole, kTRole); // ... and the other D threads'
-         }
-         // the T role is done with tracer m-2: its D2 buffer and its phi buffer are free
-         if (m >= 2) bar_sync(bar_d2_free(m), 2 * kTRole);
-         // next item of the stream, `lead` ahead: a tracer of this chunk, then h and the first
-         // tracers of the next chunk
-         {
-            const int n = m + lead;
-            if (n < T) copy_rows(P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % kTStages][0][0], kc);
-            else if (c + 1 < NCh) {
-               if (n == T) {
-                  bar_sync(kBarHFree, 2 * kTRole); // both roles have read this chunk's thickness rows
-                  copy_rows(P.Hs, &S.H[0][0], kc + kTKC);
-               } else {
-                  copy_rows(P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % kTStages][0][0], kc + kTKC);
-               }
-            }
-         }
-         cp_commit();
+         // tracer m has landed (T role, at the top of its iteration m-1: it is then also done with
+         // tracer m-2, whose D2 buffer this iteration overwrites)
+         if (m > 0) bar_sync(bar_phi_ready(m), 2 * kTRole);
          const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + m) % kTStages][0][0]);
          unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[m & 1][0][0]);
          if (X.own) {
@@ -260,10 +226,9 @@ __device__ __forceinline__ void role_D(const DMesh &M, const CellArgs &P, TileSm
             }
             sts2(Db, ro1, e0, e1);
          }
-         bar_arrive(bar_d2_ready(m), 2 * kTRole); // tracer m and its Del2 are ready for the T role
+         bar_arrive(bar_d2_ready(m), 2 * kTRole); // Del2 of tracer m is ready for the T role
       }
    }
-   cp_wait<0>();
 }
 
 // =================== T role: copies, thickness, tracer tendencies + RK updates ===================
@@ -285,6 +250,19 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          cp_commit();
       }
    }
+   // With the D role this role feeds the pipeline too (its iterations are the shorter ones).
+   // Tracer m of chunk c is item c*T + m of the copy stream and lives in buffer (c*T + m) % kTStages;
+   // iteration l copies the item `lead` places ahead: a tracer of this chunk, then h and the
+   // first tracers of the next chunk.
+   const int lead = T >= 3 ? 3 : 2;
+   if (HYP) {
+      copy_rows_g(S, X.nR, K, t, P.Hs, &S.H[0][0], kc0);
+      cp_commit();
+      for (int s = 0; s + 1 < lead; ++s) {
+         copy_rows_g(S, X.nR, K, t, P.Trs + s * CS, &S.Phi[s][0][0], kc0);
+         cp_commit();
+      }
+   }
    load_tables<NT>(M, S, tid, X.nR1, X.nc);
 
    const int c = X.c0 + li;
@@ -294,6 +272,10 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
    const int it0  = ch * T; // stream index of this chunk's tracer 0 (phi buffer = index % kTStages)
    const size_t o = (size_t)c * K + k;
    const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+   if (HYP) { // tracer lead-1 of this chunk (T >= 2); h and the tracers before it are already on their way
+      copy_rows_g(S, X.nR, K, t, P.Trs + (size_t)(lead - 1) * CS, &S.Phi[(it0 + lead - 1) % kTStages][0][0], kc0 + ch * kTKC);
+      cp_commit();
+   }
    // edge indices and velocity rows of the own cell: in flight while h lands
    double us[kME][2], ut[kME][2];
    {
@@ -313,8 +295,11 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
       if (!hcur_is_hs) ldp<2>(hcur, P.Hcur + o);
       if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
    }
-   if (!HYP) cp_wait<kTStages - 2>(); // h and phi_0 have landed (this thread's pieces)
-   __syncthreads();                   // ... and everybody else's; tables are visible
+   // h and tracer 0 have landed (this thread's pieces)
+   if (!HYP) cp_wait<kTStages - 2>();
+   else if (lead == 3) cp_wait<2>();
+   else cp_wait<1>();
+   __syncthreads(); // ... and everybody else's; tables are visible
 
    // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
    unsigned nb2[3];
@@ -355,7 +340,6 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          }
       }
    }
-   if (HYP && ch + 1 < NCh) bar_arrive(kBarHFree, 2 * kTRole); // last read of this chunk's thickness rows
    if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
    if (P.MS.Enabled) {
       const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
@@ -405,7 +389,18 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
    }
    for (int l = 0; l < T; ++l) {
       if (HYP) {
-         bar_sync(bar_d2_ready(l), 2 * kTRole); // phi_l and Del2(phi_l) are complete
+         if (l + 1 < T) { // hand tracer l+1 to the D role (copied two iterations ago)
+            if (lead == 3) cp_wait<1>(); else cp_wait<0>();
+            bar_arrive(bar_phi_ready(l + 1), 2 * kTRole);
+         }
+         bar_sync(bar_d2_ready(l), 2 * kTRole); // Del2(phi_l) is complete (and the D role past its use of h)
+         const int n = l + lead, kc = kc0 + ch * kTKC;
+         if (n < T) copy_rows_g(S, X.nR, K, t, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % kTStages][0][0], kc);
+         else if (ch + 1 < NCh) {
+            if (n == T) copy_rows_g(S, X.nR, K, t, P.Hs, &S.H[0][0], kc + kTKC);
+            else copy_rows_g(S, X.nR, K, t, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % kTStages][0][0], kc + kTKC);
+         }
+         cp_commit();
       } else {
          cp_wait<kTStages - 2>();
          __syncthreads(); // phi_l visible; every thread is done with tracer l-1
@@ -433,7 +428,6 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
             tend[0] += ch * dn.x;
             tend[1] += ch * dn.y;
          }
-         if (l + 2 < T) bar_arrive(bar_d2_free(l), 2 * kTRole);
       }
       if (own) {
          double out[2];
@@ -468,7 +462,7 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
       }
    }
    } // level chunks
-   if (!HYP) cp_wait<0>();
+   cp_wait<0>();
 }
 
 #undef NBOFF
