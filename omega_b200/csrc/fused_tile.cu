@@ -506,6 +506,324 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
    }
 }
 
+
+// ---------------------------------------------------------------------------
+// k_fCT2: the cell pass with the own-row Del2 folded into the tendency threads.
+// ncu on k_fCT shows its LSU data pipe 2/3 busy (45 % of peak in shared loads
+// alone): it is bound by shared-memory wavefronts, and a quarter of them are the
+// neighbour tracer rows read twice (T role: advection sum, D role: Del2 of the own
+// rows).  Here a T thread reads each neighbour row once and feeds both sums, which
+// needs both coefficient sets in registers (96 per thread: setmaxnreg), and the
+// helper role R (8 warps) keeps what cannot be shared: the copies and the Del2 of
+// the ring-1 rows.  An iteration i of the T role runs the neighbour pass A of tracer
+// i and the Del4 pass + RK update B of tracer i-1, which are independent; one
+// __syncthreads per iteration is the whole protocol (everything a role writes in
+// iteration i is first read in iteration i+1).
+// ---------------------------------------------------------------------------
+constexpr int kRThreads = 256;
+constexpr int kT2Threads = kTRole + kRThreads;
+
+template <int NT>
+__device__ __forceinline__ void copy_rows_n(const TileSmem &S, int nR, int K, int r, const double *F, const void *Dst, int kc) {
+   // item q = r + NT i of a row-set copy is row q/8, 16-byte piece q%8, and lands at byte 16 q
+   const unsigned d = smem_u32(Dst) + 16u * r;
+#pragma unroll
+   for (int i = 0; i < (kTileRows * kTLanes + NT - 1) / NT; ++i) {
+      const int row = (r >> 3) + i * (NT / kTLanes);
+      if (row < nR) cp_async16(d + i * (16u * NT), F + ((size_t)S.GRow[row] * K + kc + 2 * (r & 7)));
+   }
+}
+
+// R role: copies (tracer i+3 while tracer i is worked on) and Del2 of the ring-1 rows
+__device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, TileSmem &S, int c0, int nc, int n1, int nR, int NCh,
+                                       int tid) {
+   const int T = P.NTracers, K = M.K, r = tid - kTRole, p = r & 7;
+   const size_t CS = (size_t)M.NCellsSize * K;
+   copy_rows_n<kRThreads>(S, nR, K, r, P.Hs, &S.H[0][0], 0);
+   cp_commit();
+   copy_rows_n<kRThreads>(S, nR, K, r, P.Trs, &S.Phi[0][0][0], 0);
+   cp_commit();
+   copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + CS, &S.Phi[1][0][0], 0);
+   cp_commit();
+   load_tables<kT2Threads>(M, S, tid, nc + n1, nc);
+   // ring-1 row pieces of this thread: items r and r + 256 of n1*8 (n1 <= 56)
+   const int nTask = (r < n1 * kTLanes) + (r + kRThreads < n1 * kTLanes);
+   const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+   for (int c = 0; c < NCh; ++c) {
+      const int it0 = c * T, kc = c * kTKC;
+      if (c == 0) copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + 2 * CS, &S.Phi[2][0][0], 0);
+      if (c == 0) cp_commit();
+      cp_wait<2>();    // h and tracer 0 of this chunk have landed (this thread's pieces)
+      __syncthreads(); // ... and everybody else's; tables are visible; the T role is done with the previous chunk
+      for (int u = 0; u < nTask; ++u) { // coefficients of the ring rows: -(1/A) G mean thickness, private slots in Cf1
+         const int ri = (r >> 3) + u * (kRThreads / kTLanes), row = nc + ri;
+         unsigned char *Cb = reinterpret_cast<unsigned char *>(&S.Cf1[ri][0][0]) + 16u * p;
+         const double nia = -S.InvA[row];
+         const double2 hr = lds2(Hb, (row * kTKC + 2 * p) * 8u);
+         const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+            const double g   = S.G[row][j] * nia;
+            sts2(Cb, j * (kTKC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
+         }
+      }
+      for (int i = 0; i <= T; ++i) {
+         if (i > 0 && i < T) cp_wait<2>(); // tracer i has landed (this thread's pieces)
+         __syncthreads();                  // iteration i: the T role has finished iteration i-1
+         {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
+            const int n = i + 3;
+            if (n < T) copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % kTStages][0][0], kc);
+            else if (c + 1 < NCh) {
+               if (n == T) copy_rows_n<kRThreads>(S, nR, K, r, P.Hs, &S.H[0][0], kc + kTKC);
+               else copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % kTStages][0][0], kc + kTKC);
+            }
+            cp_commit();
+         }
+         if (i < T) {
+            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % kTStages][0][0]);
+            unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]);
+            for (int u = 0; u < nTask; ++u) {
+               const int ri = (r >> 3) + u * (kRThreads / kTLanes), row = nc + ri;
+               const unsigned char *Cb = reinterpret_cast<const unsigned char *>(&S.Cf1[ri][0][0]) + 16u * p;
+               const unsigned ro = (row * kTKC + 2 * p) * 8u;
+               const double2 pr = lds2(Pb, ro);
+               const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
+               double e0 = 0, e1 = 0;
+#pragma unroll
+               for (int j = 0; j < kME; ++j) {
+                  const double2 pn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+                  const double2 cf = lds2(Cb, j * (kTKC * 8u));
+                  e0 += cf.x * (pr.x - pn.x);
+                  e1 += cf.y * (pr.y - pn.y);
+               }
+               sts2(Db, ro, e0, e1);
+            }
+         }
+      }
+   }
+   cp_wait<0>();
+}
+
+
+// T role of k_fCT2
+template <int STAGE>
+__device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int NCh, int tid) {
+   constexpr bool First = STAGE == 0, Last = STAGE == 2;
+   const int K = M.K, T = P.NTracers, p = X.p, li = X.li;
+   const size_t CS = (size_t)M.NCellsSize * K;
+   const bool own  = X.own;
+   load_tables<kT2Threads>(M, S, tid, X.nR1, X.nc);
+   const int c = X.c0 + li;
+   const unsigned myoff = X.myoff;
+   const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+   const bool sameU = P.UTr == P.Us;
+   const bool hcur_is_hs = First && P.Hcur == P.Hs;
+   const bool tcur_is_ts = First && P.TrCur == P.Trs;
+   const bool need_cur   = !tcur_is_ts && (First || !Last);
+   for (int ch = 0; ch < NCh; ++ch) {
+      const int k = ch * kTKC + 2 * p, it0 = ch * T;
+      const size_t o = (size_t)c * K + k;
+      // velocity rows of the own cell and the thickness operands: in flight while h lands
+      double us[kME][2];
+      {
+         int e[kME];
+#pragma unroll
+         for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
+#pragma unroll
+         for (int j = 0; j < kME; ++j) ldv<2>(us[j], P.Us + (size_t)e[j] * K + k);
+      }
+      double hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
+      if (own) {
+         if (!hcur_is_hs) ldp<2>(hcur, P.Hcur + o);
+         if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+      }
+      __syncthreads(); // h and tracer 0 of this chunk are in shared memory; tables are visible
+      unsigned nb2[3]; // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
+      {
+         const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[li][0]);
+#pragma unroll
+         for (int j = 0; j < 3; ++j)
+            nb2[j] = ((nbl_get(tt, 2 * j) * kTKC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * kTKC + 2 * p) * 8u) << 16);
+      }
+#define NBOFF(j) (((j) & 1) ? nb2[(j) >> 1] >> 16 : nb2[(j) >> 1] & 0xffffu)
+      const double InvA = S.InvA[li];
+      const double2 hs  = lds2(Hb, myoff);
+      // per-edge coefficients of the own cell, for all tracers:
+      //   A:  adv = phi(self)*S0 + sum_j E_j*phi(nbr_j)     d2(self) = sum_j cfA_j*(phi(self) - phi(nbr_j))
+      //   B:  tend = adv + d2(self)*SH + sum_j ch_j*d2(nbr_j)
+      double E[kME][2], cfA[kME][2], S0[2] = {0, 0}, SH = 0.0, hT[2] = {0, 0};
+      {
+         const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = P.EddyDiff4 * InvA;
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const double2 hn2 = lds2(Hb, NBOFF(j));
+            const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
+            const double g   = S.G[li][j];
+            const double cfu = S.CfU[li][j];
+            const double wa  = P.AdvOn ? S.Wa[li][j] : 0.0;
+            const double cd = -k2 * g, chj = -k4 * g, ga = -InvA * g;
+            SH -= chj;
+            if (own && p == j) S.Ch[li][j] = chj;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+               const double mean = 0.5 * (hh[q] + hn[q]);
+               hT[q] += cfu * mean * us[j][q] * InvA;
+               const double w = wa * us[j][q] * InvA;
+               const double D = cd * mean;
+               E[j][q]        = 0.5 * hn[q] * w - D;
+               S0[q] += 0.5 * hh[q] * w + D;
+               cfA[j][q] = ga * mean;
+            }
+         }
+         if (!sameU && P.AdvOn) {
+            // stage 0 of an odd step with raw time-level indexing: tracer advection sees the
+            // other velocity level; redo the advective part with it (cold path)
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               double ut[2];
+               ldv<2>(ut, P.UTr + (size_t)S.Eoc[li][j] * K + k);
+               const double2 hn2 = lds2(Hb, NBOFF(j));
+               const double wa = S.Wa[li][j];
+               const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
+#pragma unroll
+               for (int q = 0; q < 2; ++q) {
+                  const double dw = wa * (ut[q] - us[j][q]) * InvA;
+                  E[j][q] += 0.5 * hn[q] * dw;
+                  S0[q] += 0.5 * hh[q] * dw;
+               }
+            }
+         }
+      }
+      if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
+      // thickness updates (updateThicknessByTend, TimeStepper.cpp:378-405) and the per-level
+      // constants of the tracer updates (TimeStepper.cpp:446-524), as in role_T
+      double w0[2], w1[2], w2[2];
+      {
+         double hnext[2], hprov[2];
+         if (hcur_is_hs || !own) {
+            hcur[0] = hs.x;
+            hcur[1] = hs.y;
+         }
+#pragma unroll
+         for (int q = 0; q < 2; ++q) {
+            hnext[q] = (First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
+            hprov[q] = hcur[q] + P.A * hT[q];
+            const double hx  = First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
+            const double h2  = P.H2Sel ? hnext[q] : hcur[q];
+            const double rhp = 1.0 / hprov[q];
+            w0[q] = Last ? 1.0 / hx : hx;
+            w1[q] = h2 * rhp;
+            w2[q] = P.A * rhp;
+         }
+         if (own) {
+            stv<2>(P.Hnext + o, hnext);
+            if (!Last) stv<2>(P.Hprov + o, hprov);
+         }
+      }
+      double tcur[2] = {0, 0}, acc[2] = {0, 0}; // cur / next of the tracer pass B handles next
+      if (own) {
+         if (need_cur) ldp<2>(tcur, P.TrCur + o);
+         if (!First) ldp<2>(acc, P.TrNext + o);
+      }
+      double adv[2] = {0, 0}, tsp[2] = {0, 0}; // advective part and own value of the tracer pass A handled last
+      for (int i = 0; i <= T; ++i) {
+         __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
+         double advn[2] = {0, 0}, tsn[2] = {0, 0};
+         if (i < T) { // ---- pass A of tracer i: every neighbour row once, two sums
+            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % kTStages][0][0]);
+            const double2 ts = lds2(Pb, myoff);
+            double d0 = 0, d1 = 0;
+            advn[0] = ts.x * S0[0];
+            advn[1] = ts.y * S0[1];
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               const double2 tn = lds2(Pb, NBOFF(j));
+               advn[0] += E[j][0] * tn.x;
+               advn[1] += E[j][1] * tn.y;
+               d0 += cfA[j][0] * (ts.x - tn.x);
+               d1 += cfA[j][1] * (ts.y - tn.y);
+            }
+            if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]), myoff, d0, d1);
+            tsn[0] = ts.x;
+            tsn[1] = ts.y;
+         }
+         if (i > 0) { // ---- pass B of tracer l = i-1: Del4 from the Del2 rows, then the RK update
+            const int l = i - 1;
+            const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
+            const double2 ds = lds2(Db, myoff);
+            double tend[2] = {adv[0] + ds.x * SH, adv[1] + ds.y * SH};
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               const double2 dn = lds2(Db, NBOFF(j));
+               const double chj = S.Ch[li][j];
+               tend[0] += chj * dn.x;
+               tend[1] += chj * dn.y;
+            }
+            if (own) {
+               double out[2];
+               if (tcur_is_ts) {
+                  tcur[0] = tsp[0];
+                  tcur[1] = tsp[1];
+               }
+#pragma unroll
+               for (int q = 0; q < 2; ++q) {
+                  out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
+                  if (Last) out[q] *= w0[q];
+               }
+               stv<2>(P.TrNext + l * CS + o, out);
+               if (!Last) {
+#pragma unroll
+                  for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
+                  stv<2>(P.TrProv + l * CS + o, out);
+               }
+               if (l + 1 < T) {
+                  if (need_cur) ldp<2>(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
+                  if (!First) ldp<2>(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+               }
+            }
+         }
+         adv[0] = advn[0]; adv[1] = advn[1];
+         tsp[0] = tsn[0]; tsp[1] = tsn[1];
+      }
+#undef NBOFF
+   }
+}
+
+template <int STAGE>
+__global__ void __launch_bounds__(kT2Threads, 1)
+k_fCT2(DMesh M, CellArgs P, int NCh) {
+   extern __shared__ __align__(16) unsigned char smem_raw[];
+   TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
+   const int tid = threadIdx.x, tile = blockIdx.x;
+   if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
+      reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
+   __syncthreads();
+   TileCtx X;
+   X.c0 = S.Hdr.C0; X.nc = S.Hdr.NC; X.n1 = S.Hdr.N1; X.nR1 = X.nc + X.n1; X.nR = X.nR1 + S.Hdr.N2;
+   for (int r = tid; r < X.nR; r += kT2Threads) S.GRow[r] = r < X.nc ? X.c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - X.nc];
+   __syncthreads();
+   if (tid >= kTRole) {
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+      role_R(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid);
+   } else {
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
+      X.t = tid; X.i = tid >> 3; X.p = tid & 7;
+      X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
+      X.myoff = (X.li * kTKC + 2 * X.p) * 8u;
+      role_T2<STAGE>(M, P, S, X, NCh, tid);
+   }
+}
+
+template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+   static bool attr = false;
+   if (!attr) {
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT2<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
+      attr = true;
+   }
+   k_fCT2<STAGE><<<(unsigned)D.Tiles.NTiles, kT2Threads, sizeof(TileSmem), St>>>(D, ca, D.K / kTKC);
+   return 0;
+}
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
 template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
@@ -532,6 +850,9 @@ template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const Cel
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    OMEGA_REQUIRE(!(ca.First && ca.Last), "launch_fCT: a stage cannot be both first and last");
    const int stage = ca.First ? 0 : (ca.Last ? 2 : 1);
+   static const int v2 = getenv("OMEGA_TILE_V2") ? atoi(getenv("OMEGA_TILE_V2")) : 1;
+   if (ca.HypOn && v2 && ca.NTracers >= 3 && !ca.MS.Enabled)
+      return stage == 0 ? launch_fCT2_t<0>(D, ca, St) : stage == 1 ? launch_fCT2_t<1>(D, ca, St) : launch_fCT2_t<2>(D, ca, St);
    if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St) : launch_fCT_t<true, 2>(D, ca, St);
    return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St) : launch_fCT_t<false, 2>(D, ca, St);
 }
