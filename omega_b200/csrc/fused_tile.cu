@@ -39,11 +39,12 @@ constexpr int kTLanes  = 8;                     // threads per row (2 levels eac
 constexpr int kTRole   = kTileCells * kTLanes;  // threads per role
 constexpr int kTStages = 5;                     // tracer row-set buffers
 
-struct TileSmem {
-   double H[kTileRows][kTKC];
-   double Phi[kTStages][kTileRows][kTKC];
-   double D2[2][kTileRows1][kTKC];
-   double Cf1[kTileRing1][6][kTKC]; // ring-1 rows: G * mean thickness per edge (private to the thread that uses it)
+// KC levels per chunk, NS tracer row-set buffers
+template <int KC, int NS> struct TileSmemT {
+   double H[kTileRows][KC];
+   double Phi[NS][kTileRows][KC];
+   double D2[2][kTileRows1][KC];
+   double Cf1[kTileRing1][6][KC]; // ring-1 rows: G * mean thickness per edge (private to the thread that uses it)
    double G[kTileRows1][6];
    double Ch[kTileCells][6];
    double CfU[kTileCells][6], Wa[kTileCells][6]; // own rows: dv*sign, mask*dv*sign per edge
@@ -53,6 +54,7 @@ struct TileSmem {
    int Eoc[kTileCells][6]; // own rows: EdgesOnCell (boundary slot when none)
    TileHdr Hdr;
 };
+using TileSmem = TileSmemT<kTKC, kTStages>;
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(unsigned dst, const void *src) {
@@ -91,8 +93,8 @@ struct TileCtx {
 };
 
 // static tables of the own + ring-1 rows (all threads of the CTA take part)
-template <int NT>
-__device__ __forceinline__ void load_tables(const DMesh &M, TileSmem &S, int tid, int nR1, int nc) {
+template <int NT, class SM>
+__device__ __forceinline__ void load_tables(const DMesh &M, SM &S, int tid, int nR1, int nc) {
    for (int q = tid; q < nc * 6; q += NT) {
       const size_t g = (size_t)S.Hdr.C0 * 6 + q;
       (&S.Eoc[0][0])[q] = M.Tiles.EocCell[g];
@@ -513,59 +515,81 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
 // alone): it is bound by shared-memory wavefronts, and a quarter of them are the
 // neighbour tracer rows read twice (T role: advection sum, D role: Del2 of the own
 // rows).  Here a T thread reads each neighbour row once and feeds both sums, which
-// needs both coefficient sets in registers (96 per thread: setmaxnreg), and the
-// helper role R (8 warps) keeps what cannot be shared: the copies and the Del2 of
-// the ring-1 rows.  An iteration i of the T role runs the neighbour pass A of tracer
+// needs both coefficient sets in registers (setmaxnreg), and the helper role R (half
+// as many threads) keeps what cannot be shared: the copies and the Del2 of the
+// ring-1 rows.  An iteration i of the T role runs the neighbour pass A of tracer
 // i and the Del4 pass + RK update B of tracer i-1, which are independent; one
 // __syncthreads per iteration is the whole protocol (everything a role writes in
 // iteration i is first read in iteration i+1).
+//
+// Two shapes (Cfg2<KC>): 16 levels per chunk, 768 threads, one CTA per SM; and 8 levels
+// per chunk, 384 threads, two CTAs per SM.  The second keeps the SM busy while one CTA
+// sits in the latency of its chunk prologue or at a barrier.
 // ---------------------------------------------------------------------------
-constexpr int kRThreads = 256;
-constexpr int kT2Threads = kTRole + kRThreads;
+template <int KC_, int RS_ = 0> struct Cfg2 {
+   static constexpr int KC = KC_;
+   static constexpr int RS = RS_;            // 0: T 96 / R 40 registers, 2: 96/48, 3: 96/40 with 384 R threads            // levels per chunk
+   static constexpr int L  = KC / 2;         // threads per row piece set (2 levels each)
+   static constexpr int LS = KC == 16 ? 3 : 2; // log2(L)
+   static constexpr int TT = kTileCells * L; // T role threads
+   static constexpr int RT = RS_ == 3 ? 3 * TT / 4 : TT / 2; // R role threads
+   static constexpr int NT = TT + RT;
+   static constexpr int NS = 4;              // tracer row-set buffers (copy lead 3 needs 4)
+   static constexpr int CTAs = KC == 16 ? 1 : 2;
+   struct Smem : TileSmemT<KC, NS> {
+      double2 W[3][TT]; // per T thread: the three per-level weights of the RK update (private slots, spares 12 registers)
+   };
+};
+static_assert(sizeof(Cfg2<16>::Smem) <= 232448, "k_fCT2 shared memory");
 
-template <int NT>
-__device__ __forceinline__ void copy_rows_n(const TileSmem &S, int nR, int K, int r, const double *F, const void *Dst, int kc) {
-   // item q = r + NT i of a row-set copy is row q/8, 16-byte piece q%8, and lands at byte 16 q
+template <class C>
+__device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, int K, int r, const double *F, const void *Dst, int kc) {
+   // item q = r + RT i of a row-set copy is row q/L, 16-byte piece q%L, and lands at byte 16 q
    const unsigned d = smem_u32(Dst) + 16u * r;
 #pragma unroll
-   for (int i = 0; i < (kTileRows * kTLanes + NT - 1) / NT; ++i) {
-      const int row = (r >> 3) + i * (NT / kTLanes);
-      if (row < nR) cp_async16(d + i * (16u * NT), F + ((size_t)S.GRow[row] * K + kc + 2 * (r & 7)));
+   for (int i = 0; i < (kTileRows * C::L + C::RT - 1) / C::RT; ++i) {
+      const int row = (r >> C::LS) + i * (C::RT / C::L);
+      if (row < nR) cp_async16(d + i * (16u * C::RT), F + ((size_t)S.GRow[row] * K + kc + 2 * (r & (C::L - 1))));
    }
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // R role: copies (tracer i+3 while tracer i is worked on) and Del2 of the ring-1 rows
-__device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, TileSmem &S, int c0, int nc, int n1, int nR, int NCh,
-                                       int tid) {
-   const int T = P.NTracers, K = M.K, r = tid - kTRole, p = r & 7;
+template <class C>
+__device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typename C::Smem &S, int c0, int nc, int n1, int nR,
+                                       int NCh, int tid, bool Pf) {
+   constexpr int KC = C::KC, L = C::L, RT = C::RT, NS = C::NS;
+   const int T = P.NTracers, K = M.K, r = tid - C::TT, p = r & (L - 1);
    const size_t CS = (size_t)M.NCellsSize * K;
-   copy_rows_n<kRThreads>(S, nR, K, r, P.Hs, &S.H[0][0], 0);
+   copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], 0);
    cp_commit();
-   copy_rows_n<kRThreads>(S, nR, K, r, P.Trs, &S.Phi[0][0][0], 0);
+   copy_rows_n<C>(S, nR, K, r, P.Trs, &S.Phi[0][0][0], 0);
    cp_commit();
-   copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + CS, &S.Phi[1][0][0], 0);
+   copy_rows_n<C>(S, nR, K, r, P.Trs + CS, &S.Phi[1][0][0], 0);
    cp_commit();
-   load_tables<kT2Threads>(M, S, tid, nc + n1, nc);
-   // ring-1 row pieces of this thread: items r and r + 256 of n1*8 (n1 <= 56)
-   const int nTask = (r < n1 * kTLanes) + (r + kRThreads < n1 * kTLanes);
+   load_tables<C::NT>(M, S, tid, nc + n1, nc);
+   // ring-1 row pieces of this thread: items r and r + RT of n1*L (n1 <= 56)
+   const int nTask = (r < n1 * L) + (r + RT < n1 * L);
    const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+   const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
    for (int c = 0; c < NCh; ++c) {
-      const int it0 = c * T, kc = c * kTKC;
-      if (c == 0) copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + 2 * CS, &S.Phi[2][0][0], 0);
+      const int it0 = c * T, kc = c * KC;
+      if (c == 0) copy_rows_n<C>(S, nR, K, r, P.Trs + 2 * CS, &S.Phi[2][0][0], 0);
       if (c == 0) cp_commit();
       cp_wait<2>();    // h and tracer 0 of this chunk have landed (this thread's pieces)
       __syncthreads(); // ... and everybody else's; tables are visible; the T role is done with the previous chunk
       for (int u = 0; u < nTask; ++u) { // coefficients of the ring rows: -(1/A) G mean thickness, private slots in Cf1
-         const int ri = (r >> 3) + u * (kRThreads / kTLanes), row = nc + ri;
+         const int ri = (r >> C::LS) + u * (RT / L), row = nc + ri;
          unsigned char *Cb = reinterpret_cast<unsigned char *>(&S.Cf1[ri][0][0]) + 16u * p;
          const double nia = -S.InvA[row];
-         const double2 hr = lds2(Hb, (row * kTKC + 2 * p) * 8u);
+         const double2 hr = lds2(Hb, (row * KC + 2 * p) * 8u);
          const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
-            const double2 hn = lds2(Hb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
+            const double2 hn = lds2(Hb, (nbl_get(tt, j) * KC + 2 * p) * 8u);
             const double g   = S.G[row][j] * nia;
-            sts2(Cb, j * (kTKC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
+            sts2(Cb, j * (KC * 8u), g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
          }
       }
       for (int i = 0; i <= T; ++i) {
@@ -573,27 +597,37 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, TileSm
          __syncthreads();                  // iteration i: the T role has finished iteration i-1
          {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
             const int n = i + 3;
-            if (n < T) copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % kTStages][0][0], kc);
+            if (n < T) copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc);
             else if (c + 1 < NCh) {
-               if (n == T) copy_rows_n<kRThreads>(S, nR, K, r, P.Hs, &S.H[0][0], kc + kTKC);
-               else copy_rows_n<kRThreads>(S, nR, K, r, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % kTStages][0][0], kc + kTKC);
+               if (n == T) copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], kc + KC);
+               else copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % NS][0][0], kc + KC);
             }
             cp_commit();
          }
+         if (i == 1 && c + 1 < NCh && Pf) {
+            // pull what the T role's next chunk prologue reads from global memory into L2:
+            // six velocity rows per own cell, and the thickness operands
+            for (int q = r; q < nc * 8; q += RT) {
+               const int cell = q >> 3, j = q & 7;
+               const size_t o = (size_t)(c0 + cell) * K + kc + KC;
+               if (j < 6) prefetch_l2(P.Us + (size_t)S.Eoc[cell][j] * K + kc + KC);
+               else if (j == 6 ? pfHcur : pfHnext) prefetch_l2((j == 6 ? P.Hcur : P.Hnext) + o);
+            }
+         }
          if (i < T) {
-            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % kTStages][0][0]);
+            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
             unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]);
             for (int u = 0; u < nTask; ++u) {
-               const int ri = (r >> 3) + u * (kRThreads / kTLanes), row = nc + ri;
+               const int ri = (r >> C::LS) + u * (RT / L), row = nc + ri;
                const unsigned char *Cb = reinterpret_cast<const unsigned char *>(&S.Cf1[ri][0][0]) + 16u * p;
-               const unsigned ro = (row * kTKC + 2 * p) * 8u;
+               const unsigned ro = (row * KC + 2 * p) * 8u;
                const double2 pr = lds2(Pb, ro);
                const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
                double e0 = 0, e1 = 0;
 #pragma unroll
                for (int j = 0; j < kME; ++j) {
-                  const double2 pn = lds2(Pb, (nbl_get(tt, j) * kTKC + 2 * p) * 8u);
-                  const double2 cf = lds2(Cb, j * (kTKC * 8u));
+                  const double2 pn = lds2(Pb, (nbl_get(tt, j) * KC + 2 * p) * 8u);
+                  const double2 cf = lds2(Cb, j * (KC * 8u));
                   e0 += cf.x * (pr.x - pn.x);
                   e1 += cf.y * (pr.y - pn.y);
                }
@@ -605,15 +639,27 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, TileSm
    cp_wait<0>();
 }
 
+// global accesses of the T role that bypass L1 allocation: what little L1 is left beside
+// 226 KB of shared memory then keeps the few spilled registers of the tracer loop
+__device__ __forceinline__ void ldg_na(double (&r)[2], const double *p) {
+   asm volatile("ld.global.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(r[0]), "=d"(r[1]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void ldg_nc_na(double (&r)[2], const double *p) {
+   asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(r[0]), "=d"(r[1]) : "l"(p));
+}
+__device__ __forceinline__ void stg_na(double *p, const double (&r)[2]) {
+   asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(r[0]), "d"(r[1]) : "memory");
+}
 
 // T role of k_fCT2
-template <int STAGE>
-__device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileSmem &S, const TileCtx &X, int NCh, int tid) {
+template <class C, int STAGE>
+__device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typename C::Smem &S, const TileCtx &X, int NCh, int tid) {
    constexpr bool First = STAGE == 0, Last = STAGE == 2;
+   constexpr int KC = C::KC, NS = C::NS;
    const int K = M.K, T = P.NTracers, p = X.p, li = X.li;
    const size_t CS = (size_t)M.NCellsSize * K;
    const bool own  = X.own;
-   load_tables<kT2Threads>(M, S, tid, X.nR1, X.nc);
+   load_tables<C::NT>(M, S, tid, X.nR1, X.nc);
    const int c = X.c0 + li;
    const unsigned myoff = X.myoff;
    const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
@@ -622,7 +668,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
    const bool tcur_is_ts = First && P.TrCur == P.Trs;
    const bool need_cur   = !tcur_is_ts && (First || !Last);
    for (int ch = 0; ch < NCh; ++ch) {
-      const int k = ch * kTKC + 2 * p, it0 = ch * T;
+      const int k = ch * KC + 2 * p, it0 = ch * T;
       const size_t o = (size_t)c * K + k;
       // velocity rows of the own cell and the thickness operands: in flight while h lands
       double us[kME][2];
@@ -631,12 +677,12 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
 #pragma unroll
          for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
 #pragma unroll
-         for (int j = 0; j < kME; ++j) ldv<2>(us[j], P.Us + (size_t)e[j] * K + k);
+         for (int j = 0; j < kME; ++j) ldg_nc_na(us[j], P.Us + (size_t)e[j] * K + k);
       }
       double hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
       if (own) {
-         if (!hcur_is_hs) ldp<2>(hcur, P.Hcur + o);
-         if (!First || P.WSel) ldp<2>(hnext_old, P.Hnext + o);
+         if (!hcur_is_hs) ldg_na(hcur, P.Hcur + o);
+         if (!First || P.WSel) ldg_na(hnext_old, P.Hnext + o);
       }
       __syncthreads(); // h and tracer 0 of this chunk are in shared memory; tables are visible
       unsigned nb2[3]; // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
@@ -644,7 +690,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
          const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[li][0]);
 #pragma unroll
          for (int j = 0; j < 3; ++j)
-            nb2[j] = ((nbl_get(tt, 2 * j) * kTKC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * kTKC + 2 * p) * 8u) << 16);
+            nb2[j] = ((nbl_get(tt, 2 * j) * KC + 2 * p) * 8u) | (((nbl_get(tt, 2 * j + 1) * KC + 2 * p) * 8u) << 16);
       }
 #define NBOFF(j) (((j) & 1) ? nb2[(j) >> 1] >> 16 : nb2[(j) >> 1] & 0xffffu)
       const double InvA = S.InvA[li];
@@ -664,7 +710,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
             const double wa  = P.AdvOn ? S.Wa[li][j] : 0.0;
             const double cd = -k2 * g, chj = -k4 * g, ga = -InvA * g;
             SH -= chj;
-            if (own && p == j) S.Ch[li][j] = chj;
+            if (own && p == (j & (C::L - 1))) S.Ch[li][j] = chj;
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                const double mean = 0.5 * (hh[q] + hn[q]);
@@ -682,7 +728,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
 #pragma unroll
             for (int j = 0; j < kME; ++j) {
                double ut[2];
-               ldv<2>(ut, P.UTr + (size_t)S.Eoc[li][j] * K + k);
+               ldg_nc_na(ut, P.UTr + (size_t)S.Eoc[li][j] * K + k);
                const double2 hn2 = lds2(Hb, NBOFF(j));
                const double wa = S.Wa[li][j];
                const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
@@ -698,8 +744,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
       if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
       // thickness updates (updateThicknessByTend, TimeStepper.cpp:378-405) and the per-level
       // constants of the tracer updates (TimeStepper.cpp:446-524), as in role_T
-      double w0[2], w1[2], w2[2];
       {
+         double w0[2], w1[2], w2[2];
          double hnext[2], hprov[2];
          if (hcur_is_hs || !own) {
             hcur[0] = hs.x;
@@ -717,21 +763,26 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
             w2[q] = P.A * rhp;
          }
          if (own) {
-            stv<2>(P.Hnext + o, hnext);
-            if (!Last) stv<2>(P.Hprov + o, hprov);
+            stg_na(P.Hnext + o, hnext);
+            if (!Last) stg_na(P.Hprov + o, hprov);
+         }
+         if (First || Last) S.W[0][tid] = make_double2(w0[0], w0[1]);
+         if (!Last) {
+            S.W[1][tid] = make_double2(w1[0], w1[1]);
+            S.W[2][tid] = make_double2(w2[0], w2[1]);
          }
       }
       double tcur[2] = {0, 0}, acc[2] = {0, 0}; // cur / next of the tracer pass B handles next
       if (own) {
-         if (need_cur) ldp<2>(tcur, P.TrCur + o);
-         if (!First) ldp<2>(acc, P.TrNext + o);
+         if (need_cur) ldg_na(tcur, P.TrCur + o);
+         if (!First) ldg_na(acc, P.TrNext + o);
       }
       double adv[2] = {0, 0}, tsp[2] = {0, 0}; // advective part and own value of the tracer pass A handled last
       for (int i = 0; i <= T; ++i) {
          __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
          double advn[2] = {0, 0}, tsn[2] = {0, 0};
          if (i < T) { // ---- pass A of tracer i: every neighbour row once, two sums
-            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % kTStages][0][0]);
+            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
             const double2 ts = lds2(Pb, myoff);
             double d0 = 0, d1 = 0;
             advn[0] = ts.x * S0[0];
@@ -754,14 +805,19 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
             const double2 ds = lds2(Db, myoff);
             double tend[2] = {adv[0] + ds.x * SH, adv[1] + ds.y * SH};
 #pragma unroll
-            for (int j = 0; j < kME; ++j) {
-               const double2 dn = lds2(Db, NBOFF(j));
-               const double chj = S.Ch[li][j];
-               tend[0] += chj * dn.x;
-               tend[1] += chj * dn.y;
+            for (int j = 0; j < kME; j += 2) {
+               const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
+               const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
+               tend[0] += c2.x * da.x;
+               tend[1] += c2.x * da.y;
+               tend[0] += c2.y * db.x;
+               tend[1] += c2.y * db.y;
             }
             if (own) {
                double out[2];
+               double2 w0v = make_double2(0, 0);
+               if (First || Last) w0v = S.W[0][tid];
+               const double w0[2] = {w0v.x, w0v.y};
                if (tcur_is_ts) {
                   tcur[0] = tsp[0];
                   tcur[1] = tsp[1];
@@ -771,15 +827,17 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
                   out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
                   if (Last) out[q] *= w0[q];
                }
-               stv<2>(P.TrNext + l * CS + o, out);
+               stg_na(P.TrNext + l * CS + o, out);
                if (!Last) {
+                  const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
+                  const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
 #pragma unroll
                   for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
-                  stv<2>(P.TrProv + l * CS + o, out);
+                  stg_na(P.TrProv + l * CS + o, out);
                }
                if (l + 1 < T) {
-                  if (need_cur) ldp<2>(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
-                  if (!First) ldp<2>(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+                  if (need_cur) ldg_na(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
+                  if (!First) ldg_na(acc, P.TrNext + (size_t)(l + 1) * CS + o);
                }
             }
          }
@@ -790,39 +848,48 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, TileS
    }
 }
 
-template <int STAGE>
-__global__ void __launch_bounds__(kT2Threads, 1)
-k_fCT2(DMesh M, CellArgs P, int NCh) {
+template <class C, int STAGE>
+__global__ void __launch_bounds__(C::NT, C::CTAs)
+k_fCT2(DMesh M, CellArgs P, int NCh, int Pf) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
-   TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
+   typename C::Smem &S = *reinterpret_cast<typename C::Smem *>(smem_raw);
    const int tid = threadIdx.x, tile = blockIdx.x;
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
    __syncthreads();
    TileCtx X;
    X.c0 = S.Hdr.C0; X.nc = S.Hdr.NC; X.n1 = S.Hdr.N1; X.nR1 = X.nc + X.n1; X.nR = X.nR1 + S.Hdr.N2;
-   for (int r = tid; r < X.nR; r += kT2Threads) S.GRow[r] = r < X.nc ? X.c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - X.nc];
+   for (int r = tid; r < X.nR; r += C::NT) S.GRow[r] = r < X.nc ? X.c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - X.nc];
    __syncthreads();
-   if (tid >= kTRole) {
-      asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-      role_R(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid);
+   if (tid >= C::TT) {
+      if (C::RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+      else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+      role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0);
    } else {
       asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
-      X.t = tid; X.i = tid >> 3; X.p = tid & 7;
+      X.t = tid; X.i = tid >> C::LS; X.p = tid & (C::L - 1);
       X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
-      X.myoff = (X.li * kTKC + 2 * X.p) * 8u;
-      role_T2<STAGE>(M, P, S, X, NCh, tid);
+      X.myoff = (X.li * C::KC + 2 * X.p) * 8u;
+      role_T2<C, STAGE>(M, P, S, X, NCh, tid);
    }
 }
 
-template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    static bool attr = false;
    if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT2<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT2<C, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(typename C::Smem)));
       attr = true;
    }
-   k_fCT2<STAGE><<<(unsigned)D.Tiles.NTiles, kT2Threads, sizeof(TileSmem), St>>>(D, ca, D.K / kTKC);
+   static const int pf = getenv("OMEGA_TILE_PF") ? atoi(getenv("OMEGA_TILE_PF")) : 1;
+   k_fCT2<C, STAGE><<<(unsigned)D.Tiles.NTiles, C::NT, sizeof(typename C::Smem), St>>>(D, ca, D.K / C::KC, pf);
    return 0;
+}
+template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+   // OMEGA_TILE_KC=16: one 768-thread CTA per SM; default 8: two 384-thread CTAs per SM
+   static const int kc = getenv("OMEGA_TILE_KC") ? atoi(getenv("OMEGA_TILE_KC")) : 8;
+   static const int rs = getenv("OMEGA_TILE_RS") ? atoi(getenv("OMEGA_TILE_RS")) : 2;
+   (void)kc;
+   return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
