@@ -526,7 +526,7 @@ k_fCT(DMesh M, CellArgs P, int NChunks) {
 // per chunk, 384 threads, two CTAs per SM.  The second keeps the SM busy while one CTA
 // sits in the latency of its chunk prologue or at a barrier.
 // ---------------------------------------------------------------------------
-template <int KC_, int RS_ = 0> struct Cfg2 {
+template <int KC_, int RS_ = 0, int CP_ = 0> struct Cfg2 {
    static constexpr int KC = KC_;
    static constexpr int RS = RS_;            // 0: T 96 / R 40 registers, 2: 96/48, 3: 96/40 with 384 R threads            // levels per chunk
    static constexpr int L  = KC / 2;         // threads per row piece set (2 levels each)
@@ -536,11 +536,37 @@ template <int KC_, int RS_ = 0> struct Cfg2 {
    static constexpr int NT = TT + RT;
    static constexpr int NS = 4;              // tracer row-set buffers (copy lead 3 needs 4)
    static constexpr int CTAs = KC == 16 ? 1 : 2;
+   static constexpr bool BULK = CP_ == 1;    // row copies: 0 = cp.async 16-byte pieces (LSU), 1 = one bulk copy per row (TMA unit, mbarrier)
    struct Smem : TileSmemT<KC, NS> {
       double2 W[3][TT]; // per T thread: the three per-level weights of the RK update (private slots, spares 12 registers)
+      unsigned long long Bar[NS + 1]; // BULK: "landed" barriers of the tracer buffers and of h
    };
 };
 static_assert(sizeof(Cfg2<16>::Smem) <= 232448, "k_fCT2 shared memory");
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// wait for the phase of parity `par`; a copy that never lands traps instead of hanging the device
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned par) {
+   unsigned done = 0;
+   for (int spin = 0; spin < (1 << 22); ++spin) {
+      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                   : "=r"(done)
+                   : "r"(bar), "r"(par)
+                   : "memory");
+      if (done) return;
+   }
+   __trap();
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                "r"(bytes), "r"(bar)
+                : "memory");
+}
 
 template <class C>
 __device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, int K, int r, const double *F, const void *Dst, int kc) {
@@ -553,6 +579,26 @@ __device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, i
    }
 }
 
+// one item of the copy stream: a row set (h or a tracer) of level chunk kc into Dst; bar = its barrier (BULK)
+template <class C>
+__device__ __forceinline__ void issue_rows(typename C::Smem &S, int nR, int K, int r, int grow, const double *F, void *Dst, int kc,
+                                           int bar) {
+   if (C::BULK) {
+      const unsigned b = smem_u32(&S.Bar[bar]);
+      if (r == 0) mbar_expect_tx(b, (unsigned)nR * (C::KC * 8));
+      if (r < nR) bulk_g2s(smem_u32(Dst) + r * (C::KC * 8), F + ((size_t)grow * K + kc), C::KC * 8, b);
+   } else {
+      copy_rows_n<C>(S, nR, K, r, F, Dst, kc);
+      cp_commit();
+   }
+}
+template <class C> __device__ __forceinline__ void wait_item(typename C::Smem &S, int item) { // tracer item of the copy stream
+   if (C::BULK) mbar_wait(smem_u32(&S.Bar[item % C::NS]), (item / C::NS) & 1);
+}
+template <class C> __device__ __forceinline__ void wait_h(typename C::Smem &S, int chunk) {
+   if (C::BULK) mbar_wait(smem_u32(&S.Bar[C::NS]), chunk & 1);
+}
+
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // R role: copies (tracer i+3 while tracer i is worked on) and Del2 of the ring-1 rows
@@ -562,12 +608,11 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    constexpr int KC = C::KC, L = C::L, RT = C::RT, NS = C::NS;
    const int T = P.NTracers, K = M.K, r = tid - C::TT, p = r & (L - 1);
    const size_t CS = (size_t)M.NCellsSize * K;
-   copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], 0);
-   cp_commit();
-   copy_rows_n<C>(S, nR, K, r, P.Trs, &S.Phi[0][0][0], 0);
-   cp_commit();
-   copy_rows_n<C>(S, nR, K, r, P.Trs + CS, &S.Phi[1][0][0], 0);
-   cp_commit();
+   static_assert(!C::BULK || C::RT >= kTileRows, "bulk copies: one row per R thread");
+   const int grow = r < nR ? S.GRow[r] : 0;
+   issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], 0, NS);
+   issue_rows<C>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], 0, 0);
+   issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], 0, 1);
    load_tables<C::NT>(M, S, tid, nc + n1, nc);
    // ring-1 row pieces of this thread: items r and r + RT of n1*L (n1 <= 56)
    const int nTask = (r < n1 * L) + (r + RT < n1 * L);
@@ -575,10 +620,10 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
    for (int c = 0; c < NCh; ++c) {
       const int it0 = c * T, kc = c * KC;
-      if (c == 0) copy_rows_n<C>(S, nR, K, r, P.Trs + 2 * CS, &S.Phi[2][0][0], 0);
-      if (c == 0) cp_commit();
-      cp_wait<2>();    // h and tracer 0 of this chunk have landed (this thread's pieces)
-      __syncthreads(); // ... and everybody else's; tables are visible; the T role is done with the previous chunk
+      if (c == 0) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], 0, 2);
+      if (!C::BULK) cp_wait<2>(); // h and tracer 0 of this chunk have landed (this thread's pieces)
+      __syncthreads();            // ... and everybody else's; tables are visible; the T role is done with the previous chunk
+      wait_h<C>(S, c);
       for (int u = 0; u < nTask; ++u) { // coefficients of the ring rows: -(1/A) G mean thickness, private slots in Cf1
          const int ri = (r >> C::LS) + u * (RT / L), row = nc + ri;
          unsigned char *Cb = reinterpret_cast<unsigned char *>(&S.Cf1[ri][0][0]) + 16u * p;
@@ -593,16 +638,15 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
          }
       }
       for (int i = 0; i <= T; ++i) {
-         if (i > 0 && i < T) cp_wait<2>(); // tracer i has landed (this thread's pieces)
-         __syncthreads();                  // iteration i: the T role has finished iteration i-1
+         if (!C::BULK && i > 0 && i < T) cp_wait<2>(); // tracer i has landed (this thread's pieces)
+         __syncthreads();                              // iteration i: the T role has finished iteration i-1
          {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
             const int n = i + 3;
-            if (n < T) copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc);
+            if (n < T) issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc, (it0 + n) % NS);
             else if (c + 1 < NCh) {
-               if (n == T) copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], kc + KC);
-               else copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % NS][0][0], kc + KC);
-            }
-            cp_commit();
+               if (n == T) issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
+               else issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % NS][0][0], kc + KC, (it0 + n - 1) % NS);
+            } else if (!C::BULK) cp_commit(); // keeps the group count of cp_wait<2> uniform
          }
          if (i == 1 && c + 1 < NCh && Pf) {
             // pull what the T role's next chunk prologue reads from global memory into L2:
@@ -615,6 +659,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
             }
          }
          if (i < T) {
+            wait_item<C>(S, it0 + i);
             const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
             unsigned char *Db       = reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]);
             for (int u = 0; u < nTask; ++u) {
@@ -636,7 +681,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
          }
       }
    }
-   cp_wait<0>();
+   if (!C::BULK) cp_wait<0>();
 }
 
 // global accesses of the T role that bypass L1 allocation: what little L1 is left beside
@@ -685,6 +730,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          if (!First || P.WSel) ldg_na(hnext_old, P.Hnext + o);
       }
       __syncthreads(); // h and tracer 0 of this chunk are in shared memory; tables are visible
+      wait_h<C>(S, ch);
       unsigned nb2[3]; // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
       {
          const uint4 tt = *reinterpret_cast<const uint4 *>(&S.Nbl[li][0]);
@@ -782,6 +828,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
          double advn[2] = {0, 0}, tsn[2] = {0, 0};
          if (i < T) { // ---- pass A of tracer i: every neighbour row once, two sums
+            wait_item<C>(S, it0 + i);
             const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
             const double2 ts = lds2(Pb, myoff);
             double d0 = 0, d1 = 0;
@@ -856,6 +903,10 @@ k_fCT2(DMesh M, CellArgs P, int NCh, int Pf) {
    const int tid = threadIdx.x, tile = blockIdx.x;
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
+   if (C::BULK && tid == 32) {
+      for (int b = 0; b <= C::NS; ++b) mbar_init(smem_u32(&S.Bar[b]), 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+   }
    __syncthreads();
    TileCtx X;
    X.c0 = S.Hdr.C0; X.nc = S.Hdr.NC; X.n1 = S.Hdr.N1; X.nR1 = X.nc + X.n1; X.nR = X.nR1 + S.Hdr.N2;
@@ -889,6 +940,8 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    static const int kc = getenv("OMEGA_TILE_KC") ? atoi(getenv("OMEGA_TILE_KC")) : 8;
    static const int rs = getenv("OMEGA_TILE_RS") ? atoi(getenv("OMEGA_TILE_RS")) : 2;
    (void)kc;
+   static const int cp = getenv("OMEGA_TILE_CP") ? atoi(getenv("OMEGA_TILE_CP")) : 0;
+   if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
