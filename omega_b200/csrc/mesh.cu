@@ -331,6 +331,17 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    OMEGA_REQUIRE(D->NCellsSize == D->NCellsAll + 1 && D->NEdgesSize == D->NEdgesAll + 1 &&
                      D->NVerticesSize == D->NVerticesAll + 1,
                  "omega_mesh_create: N*Size must equal N*All+1 (Decomp.cpp:1081-1082)");
+   {
+      // omega_field_to_device/_to_host stage whole fields through stream-ordered allocations; keep the
+      // freed blocks in the device's pool (default threshold 0 hands them back to the driver at every
+      // synchronisation, and a multi-GB cudaMalloc per field per step then dominates the transfer)
+      int dev = 0;
+      cudaMemPool_t pool;
+      unsigned long long keep = ~0ull;
+      OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+      OMEGA_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
+      OMEGA_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+   }
    OmegaMesh *M = new OmegaMesh();
    M->Sizes     = *D;
    M->Reordered = Reorder;
