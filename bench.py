@@ -320,7 +320,7 @@ def main():
         tr_path = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr_path) and args.workload == "config3" and world == 1:
             traffic = json.load(open(tr_path)).get("k_fCT_dram_bytes_per_launch")
-        roofline = {"bound": "hbm", "kernel": "k_fCT (tiled cell pass: thickness + all tracer tendencies + RK updates)",
+        roofline = {"bound": "hbm", "kernel": "k_fCT2 (tiled cell pass: thickness + all tracer tendencies + RK updates)",
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg_fc}
