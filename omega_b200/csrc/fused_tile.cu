@@ -540,6 +540,7 @@ template <int KC_, int RS_ = 0, int CP_ = 0> struct Cfg2 {
    struct Smem : TileSmemT<KC, NS> {
       double2 W[3][TT]; // per T thread: the three per-level weights of the RK update (private slots, spares 12 registers)
       unsigned long long Bar[NS + 1]; // BULK: "landed" barriers of the tracer buffers and of h
+      double SHc[kTileCells];         // own rows: -sum_j ch_j (the self coefficient of the Del4 sum)
    };
 };
 static_assert(sizeof(Cfg2<16>::Smem) <= 232448, "k_fCT2 shared memory");
@@ -757,6 +758,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             const double cd = -k2 * g, chj = -k4 * g, ga = -InvA * g;
             SH -= chj;
             if (own && p == (j & (C::L - 1))) S.Ch[li][j] = chj;
+            if (j == kME - 1 && own && p == C::L - 1) S.SHc[li] = SH;
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                const double mean = 0.5 * (hh[q] + hn[q]);
@@ -850,7 +852,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             const int l = i - 1;
             const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
             const double2 ds = lds2(Db, myoff);
-            double tend[2] = {adv[0] + ds.x * SH, adv[1] + ds.y * SH};
+            const double SHl = S.SHc[li];
+            double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
 #pragma unroll
             for (int j = 0; j < kME; j += 2) {
                const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
@@ -861,6 +864,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
                tend[1] += c2.y * db.y;
             }
             if (own) {
+               // the element offset of this thread's piece, rebuilt from the tile header each time: holding
+               // it across pass A costs the register that otherwise spills
                double out[2];
                double2 w0v = make_double2(0, 0);
                if (First || Last) w0v = S.W[0][tid];
