@@ -605,23 +605,23 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 // R role: copies (tracer i+3 while tracer i is worked on) and Del2 of the ring-1 rows
 template <class C>
 __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typename C::Smem &S, int c0, int nc, int n1, int nR,
-                                       int NCh, int tid, bool Pf) {
+                                       int NCh, int tid, bool Pf, int kb) {
    constexpr int KC = C::KC, L = C::L, RT = C::RT, NS = C::NS;
    const int T = P.NTracers, K = M.K, r = tid - C::TT, p = r & (L - 1);
    const size_t CS = (size_t)M.NCellsSize * K;
    static_assert(!C::BULK || C::RT >= kTileRows, "bulk copies: one row per R thread");
    const int grow = r < nR ? S.GRow[r] : 0;
-   issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], 0, NS);
-   issue_rows<C>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], 0, 0);
-   issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], 0, 1);
+   issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kb, NS); // kb: first level of this CTA's chunks
+   issue_rows<C>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], kb, 0);
+   issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], kb, 1);
    load_tables<C::NT>(M, S, tid, nc + n1, nc);
    // ring-1 row pieces of this thread: items r and r + RT of n1*L (n1 <= 56)
    const int nTask = (r < n1 * L) + (r + RT < n1 * L);
    const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
    const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
    for (int c = 0; c < NCh; ++c) {
-      const int it0 = c * T, kc = c * KC;
-      if (c == 0) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], 0, 2);
+      const int it0 = c * T, kc = kb + c * KC;
+      if (c == 0) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], kb, 2);
       if (!C::BULK) cp_wait<2>(); // h and tracer 0 of this chunk have landed (this thread's pieces)
       __syncthreads();            // ... and everybody else's; tables are visible; the T role is done with the previous chunk
       wait_h<C>(S, c);
@@ -699,7 +699,8 @@ __device__ __forceinline__ void stg_na(double *p, const double (&r)[2]) {
 
 // T role of k_fCT2
 template <class C, int STAGE>
-__device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typename C::Smem &S, const TileCtx &X, int NCh, int tid) {
+__device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typename C::Smem &S, const TileCtx &X, int NCh, int tid,
+                                        int kb) {
    constexpr bool First = STAGE == 0, Last = STAGE == 2;
    constexpr int KC = C::KC, NS = C::NS;
    const int K = M.K, T = P.NTracers, p = X.p, li = X.li;
@@ -714,7 +715,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    const bool tcur_is_ts = First && P.TrCur == P.Trs;
    const bool need_cur   = !tcur_is_ts && (First || !Last);
    for (int ch = 0; ch < NCh; ++ch) {
-      const int k = ch * KC + 2 * p, it0 = ch * T;
+      const int k = kb + ch * KC + 2 * p, it0 = ch * T;
       const size_t o = (size_t)c * K + k;
       // velocity rows of the own cell and the thickness operands: in flight while h lands
       double us[kME][2];
@@ -902,10 +903,19 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
 
 template <class C, int STAGE>
 __global__ void __launch_bounds__(C::NT, C::CTAs)
-k_fCT2(DMesh M, CellArgs P, int NCh, int Pf) {
+k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    typename C::Smem &S = *reinterpret_cast<typename C::Smem *>(smem_raw);
-   const int tid = threadIdx.x, tile = blockIdx.x;
+   // CTAs below NWhole take a whole tile (all NChAll chunks); the tiles of the last, partial round of
+   // CTAs are split into one CTA per chunk so that the tail of the grid costs a fraction of a round
+   const int tid = threadIdx.x;
+   int tile = blockIdx.x, kb = 0, NCh = NChAll;
+   if ((int)blockIdx.x >= NWhole) {
+      const int q = blockIdx.x - NWhole;
+      tile = NWhole + q / NChAll;
+      kb   = (q % NChAll) * C::KC;
+      NCh  = 1;
+   }
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
    if (C::BULK && tid == 32) {
@@ -920,13 +930,13 @@ k_fCT2(DMesh M, CellArgs P, int NCh, int Pf) {
    if (tid >= C::TT) {
       if (C::RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
       else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-      role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0);
+      role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
    } else {
       asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
       X.t = tid; X.i = tid >> C::LS; X.p = tid & (C::L - 1);
       X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
       X.myoff = (X.li * C::KC + 2 * X.p) * 8u;
-      role_T2<C, STAGE>(M, P, S, X, NCh, tid);
+      role_T2<C, STAGE>(M, P, S, X, NCh, tid, kb);
    }
 }
 
@@ -937,7 +947,23 @@ template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const Cel
       attr = true;
    }
    static const int pf = getenv("OMEGA_TILE_PF") ? atoi(getenv("OMEGA_TILE_PF")) : 1;
-   k_fCT2<C, STAGE><<<(unsigned)D.Tiles.NTiles, C::NT, sizeof(typename C::Smem), St>>>(D, ca, D.K / C::KC, pf);
+   // one CTA per tile; the tiles of the last partial round of CTAs are split into one CTA per chunk when
+   // that shortens the tail (matters on multi-GPU partitions with ~10 rounds)
+   static const int split = getenv("OMEGA_TILE_SPLIT") ? atoi(getenv("OMEGA_TILE_SPLIT")) : 1;
+   static int sm = 0;
+   if (!sm) {
+      int dev = 0;
+      OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+      OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+   }
+   const int nch = D.K / C::KC, nt = D.Tiles.NTiles;
+   int whole = nt;
+   if (split && nch > 1) {
+      const int tail = nt % sm;
+      const double cost = ((tail * nch + sm - 1) / sm) * 1.15 / nch; // rounds, a single-chunk CTA costs ~15 % more per chunk
+      if (tail > 0 && cost < 0.85) whole = nt - tail;
+   }
+   k_fCT2<C, STAGE><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole);
    return 0;
 }
 template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
