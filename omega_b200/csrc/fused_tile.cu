@@ -714,23 +714,31 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    const bool hcur_is_hs = First && P.Hcur == P.Hs;
    const bool tcur_is_ts = First && P.TrCur == P.Trs;
    const bool need_cur   = !tcur_is_ts && (First || !Last);
-   for (int ch = 0; ch < NCh; ++ch) {
-      const int k = kb + ch * KC + 2 * p, it0 = ch * T;
-      const size_t o = (size_t)c * K + k;
-      // velocity rows of the own cell and the thickness operands: in flight while h lands
-      double us[kME][2];
-      {
-         int e[kME];
+   // The global operands of a chunk's prologue (six velocity rows of the own cell, thickness
+   // operands) are loaded one chunk ahead: for chunk 0 here, for chunk ch+1 in the last iteration
+   // of chunk ch, where the registers of the tracer coefficients are free again.
+   double us[kME][2], hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
+   auto load_prologue = [&](int ch) {
+      const int k = kb + ch * KC + 2 * p;
+      int e[kME];
 #pragma unroll
-         for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
+      for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
 #pragma unroll
-         for (int j = 0; j < kME; ++j) ldg_nc_na(us[j], P.Us + (size_t)e[j] * K + k);
-      }
-      double hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
+      for (int j = 0; j < kME; ++j) ldg_nc_na(us[j], P.Us + (size_t)e[j] * K + k);
       if (own) {
+         const size_t o = (size_t)c * K + k;
          if (!hcur_is_hs) ldg_na(hcur, P.Hcur + o);
          if (!First || P.WSel) ldg_na(hnext_old, P.Hnext + o);
       }
+   };
+#ifndef OMEGA_T2_HOIST
+#define OMEGA_T2_HOIST 0
+#endif
+   if (OMEGA_T2_HOIST) load_prologue(0);
+   for (int ch = 0; ch < NCh; ++ch) {
+      const int k = kb + ch * KC + 2 * p, it0 = ch * T;
+      const size_t o = (size_t)c * K + k;
+      if (!OMEGA_T2_HOIST) load_prologue(ch); // in flight while h lands
       __syncthreads(); // h and tracer 0 of this chunk are in shared memory; tables are visible
       wait_h<C>(S, ch);
       unsigned nb2[3]; // byte offsets of the six neighbour pieces inside a [row][16] buffer, two per register
@@ -746,9 +754,9 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
       // per-edge coefficients of the own cell, for all tracers:
       //   A:  adv = phi(self)*S0 + sum_j E_j*phi(nbr_j)     d2(self) = sum_j cfA_j*(phi(self) - phi(nbr_j))
       //   B:  tend = adv + d2(self)*SH + sum_j ch_j*d2(nbr_j)
-      double E[kME][2], cfA[kME][2], S0[2] = {0, 0}, SH = 0.0, hT[2] = {0, 0};
-      {
-         const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = P.EddyDiff4 * InvA;
+      double E[kME][2], cfA[kME][2], S0[2] = {0, 0}, hT[2] = {0, 0};
+      { // first the sums that need the velocity rows (they retire one after the other) ...
+         const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0;
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
             const double2 hn2 = lds2(Hb, NBOFF(j));
@@ -756,10 +764,13 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             const double g   = S.G[li][j];
             const double cfu = S.CfU[li][j];
             const double wa  = P.AdvOn ? S.Wa[li][j] : 0.0;
-            const double cd = -k2 * g, chj = -k4 * g, ga = -InvA * g;
-            SH -= chj;
-            if (own && p == (j & (C::L - 1))) S.Ch[li][j] = chj;
-            if (j == kME - 1 && own && p == C::L - 1) S.SHc[li] = SH;
+            const double cd  = -k2 * g;
+            double ua[2] = {us[j][0], us[j][1]}; // velocity the tracer advection sees
+            if (!sameU && P.AdvOn) {
+               // stage 0 of an odd step with raw time-level indexing: tracer advection sees the
+               // other velocity level (cold path)
+               ldg_nc_na(ua, P.UTr + (size_t)S.Eoc[li][j] * K + k);
+            }
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                const double mean = 0.5 * (hh[q] + hn[q]);
@@ -768,26 +779,27 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
                const double D = cd * mean;
                E[j][q]        = 0.5 * hn[q] * w - D;
                S0[q] += 0.5 * hh[q] * w + D;
-               cfA[j][q] = ga * mean;
-            }
-         }
-         if (!sameU && P.AdvOn) {
-            // stage 0 of an odd step with raw time-level indexing: tracer advection sees the
-            // other velocity level; redo the advective part with it (cold path)
-#pragma unroll
-            for (int j = 0; j < kME; ++j) {
-               double ut[2];
-               ldg_nc_na(ut, P.UTr + (size_t)S.Eoc[li][j] * K + k);
-               const double2 hn2 = lds2(Hb, NBOFF(j));
-               const double wa = S.Wa[li][j];
-               const double hn[2] = {hn2.x, hn2.y}, hh[2] = {hs.x, hs.y};
-#pragma unroll
-               for (int q = 0; q < 2; ++q) {
-                  const double dw = wa * (ut[q] - us[j][q]) * InvA;
+               if (!sameU && P.AdvOn) {
+                  const double dw = wa * (ua[q] - us[j][q]) * InvA;
                   E[j][q] += 0.5 * hn[q] * dw;
                   S0[q] += 0.5 * hh[q] * dw;
                }
             }
+         }
+      }
+      { // ... then the Del2 / Del4 coefficients, which need h only
+         const double k4 = P.EddyDiff4 * InvA;
+         double SH = 0.0;
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const double2 hn2 = lds2(Hb, NBOFF(j));
+            const double g    = S.G[li][j];
+            const double chj = -k4 * g, ga = -InvA * g;
+            SH -= chj;
+            if (own && p == (j & (C::L - 1))) S.Ch[li][j] = chj;
+            if (j == kME - 1 && own && p == C::L - 1) S.SHc[li] = SH;
+            cfA[j][0] = ga * (0.5 * (hs.x + hn2.x));
+            cfA[j][1] = ga * (0.5 * (hs.y + hn2.y));
          }
       }
       if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
@@ -827,10 +839,53 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          if (!First) ldg_na(acc, P.TrNext + o);
       }
       double adv[2] = {0, 0}, tsp[2] = {0, 0}; // advective part and own value of the tracer pass A handled last
-      for (int i = 0; i <= T; ++i) {
+      // ---- pass B of tracer l: Del4 from the Del2 rows, then the RK update
+      auto pass_B = [&](int l) {
+         const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
+         const double2 ds = lds2(Db, myoff);
+         const double SHl = S.SHc[li];
+         double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
+#pragma unroll
+         for (int j = 0; j < kME; j += 2) {
+            const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
+            const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
+            tend[0] += c2.x * da.x;
+            tend[1] += c2.x * da.y;
+            tend[0] += c2.y * db.x;
+            tend[1] += c2.y * db.y;
+         }
+         if (own) {
+            double out[2];
+            double2 w0v = make_double2(0, 0);
+            if (First || Last) w0v = S.W[0][tid];
+            const double w0[2] = {w0v.x, w0v.y};
+            if (tcur_is_ts) {
+               tcur[0] = tsp[0];
+               tcur[1] = tsp[1];
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+               out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
+               if (Last) out[q] *= w0[q];
+            }
+            stg_na(P.TrNext + l * CS + o, out);
+            if (!Last) {
+               const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
+               const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
+#pragma unroll
+               for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
+               stg_na(P.TrProv + l * CS + o, out);
+            }
+            if (l + 1 < T) {
+               if (need_cur) ldg_na(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
+               if (!First) ldg_na(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+            }
+         }
+      };
+      for (int i = 0; i < T; ++i) {
          __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
-         double advn[2] = {0, 0}, tsn[2] = {0, 0};
-         if (i < T) { // ---- pass A of tracer i: every neighbour row once, two sums
+         double advn[2], tsn[2];
+         { // ---- pass A of tracer i: every neighbour row once, two sums
             wait_item<C>(S, it0 + i);
             const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
             const double2 ts = lds2(Pb, myoff);
@@ -849,54 +904,15 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             tsn[0] = ts.x;
             tsn[1] = ts.y;
          }
-         if (i > 0) { // ---- pass B of tracer l = i-1: Del4 from the Del2 rows, then the RK update
-            const int l = i - 1;
-            const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
-            const double2 ds = lds2(Db, myoff);
-            const double SHl = S.SHc[li];
-            double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
-#pragma unroll
-            for (int j = 0; j < kME; j += 2) {
-               const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
-               const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
-               tend[0] += c2.x * da.x;
-               tend[1] += c2.x * da.y;
-               tend[0] += c2.y * db.x;
-               tend[1] += c2.y * db.y;
-            }
-            if (own) {
-               // the element offset of this thread's piece, rebuilt from the tile header each time: holding
-               // it across pass A costs the register that otherwise spills
-               double out[2];
-               double2 w0v = make_double2(0, 0);
-               if (First || Last) w0v = S.W[0][tid];
-               const double w0[2] = {w0v.x, w0v.y};
-               if (tcur_is_ts) {
-                  tcur[0] = tsp[0];
-                  tcur[1] = tsp[1];
-               }
-#pragma unroll
-               for (int q = 0; q < 2; ++q) {
-                  out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
-                  if (Last) out[q] *= w0[q];
-               }
-               stg_na(P.TrNext + l * CS + o, out);
-               if (!Last) {
-                  const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
-                  const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
-#pragma unroll
-                  for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
-                  stg_na(P.TrProv + l * CS + o, out);
-               }
-               if (l + 1 < T) {
-                  if (need_cur) ldg_na(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
-                  if (!First) ldg_na(acc, P.TrNext + (size_t)(l + 1) * CS + o);
-               }
-            }
-         }
+         if (i > 0) pass_B(i - 1);
          adv[0] = advn[0]; adv[1] = advn[1];
          tsp[0] = tsn[0]; tsp[1] = tsn[1];
       }
+      // last iteration: only pass B of the last tracer is left, the coefficient registers are free:
+      // the next chunk's prologue operands start their way from global memory now
+      __syncthreads();
+      if (OMEGA_T2_HOIST && ch + 1 < NCh) load_prologue(ch + 1);
+      pass_B(T - 1);
 #undef NBOFF
    }
 }
