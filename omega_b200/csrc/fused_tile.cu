@@ -1051,7 +1051,7 @@ struct ETileSmem {
 };
 
 __global__ void __launch_bounds__(kEThreads, 2)
-k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
+k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    ETileSmem &S = *reinterpret_cast<ETileSmem *>(smem_raw);
    const int tid = threadIdx.x;
@@ -1072,6 +1072,29 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks) {
    }
    __syncthreads();
    const int p = tid & 7, k = kc0 + 2 * p;
+   if (Pf) {
+      // the eight gathered rows of pass 2a (X, Y of both cells, Z of both vertices, u_cur, u_next) of this
+      // thread's own edges: one of the eight lanes of an edge each, pulled into L2 while pass 1 runs
+#pragma unroll
+      for (int it = 0; it < kTileEdgesOwn * kTLanes / kEThreads; ++it) {
+         const int r = (tid >> 3) + it * (kEThreads / kTLanes);
+         if (r < nOwn) {
+            const int4 cv = S.CV[r];
+            const double *q;
+            switch (p) {
+            case 0: q = P.X + (size_t)cv.x * K; break;
+            case 1: q = P.X + (size_t)cv.y * K; break;
+            case 2: q = P.Y + (size_t)cv.x * K; break;
+            case 3: q = P.Y + (size_t)cv.y * K; break;
+            case 4: q = P.Z + (size_t)cv.z * K; break;
+            case 5: q = P.Z + (size_t)cv.w * K; break;
+            case 6: q = (P.First && P.Ucur == P.Us ? P.Us : P.Ucur) + (size_t)S.SRow[r] * K; break;
+            default: q = P.Unext + (size_t)S.SRow[r] * K; break;
+            }
+            prefetch_l2(q + kc0);
+         }
+      }
+   }
    // ---- pass 1: F and q of every staged edge, two edges per trip (ten gathered rows in flight)
    auto fq = [&](int r, double (&u)[2], double (&h0)[2], double (&h1)[2], double (&a)[2], double (&b)[2]) {
       const int e   = S.SRow[r];
@@ -1181,7 +1204,8 @@ int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St) {
       attr = true;
    }
    const int nch = D.K / kTKC;
-   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch);
+   static const int pf = getenv("OMEGA_TILE_EPF") ? atoi(getenv("OMEGA_TILE_EPF")) : 1;
+   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf);
    return 0;
 }
 
