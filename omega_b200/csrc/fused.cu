@@ -182,6 +182,86 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
    }
 }
 
+// k_fB with every gathered row read once (tables B3*, mesh.cu): 13 rows per cell and 7 per vertex
+// instead of 19 and 10.  X != nullptr: the cell result is W = Y - X, the one cell field the tiled
+// edge pass then differences for KE + SSH gradient, Del2 and Del4 divergence parts together.
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort, double *__restrict__ Del2Div,
+      double *__restrict__ Del2RelVort, int YMode, double Nu2, double Nu4Div, double Nu4, const double *__restrict__ X) {
+   const int KV = M.K / V;
+   int r0, n;
+   cta_rows(M.NCellsAll, r0, n);
+   OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
+      int ix[12];
+      double cf[12];
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+         const int4 t4 = M.B3CellIdx[c * 3 + q];
+         ix[4 * q] = t4.x; ix[4 * q + 1] = t4.y; ix[4 * q + 2] = t4.z; ix[4 * q + 3] = t4.w;
+      }
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+         const double2 t2 = M.B3CellCf[c * 6 + q];
+         cf[2 * q] = t2.x; cf[2 * q + 1] = t2.y;
+      }
+      double ds[V], xs[V] = {0}, t[V] = {0}, g[12][V];
+      ldv<V>(ds, Div + (size_t)c * M.K + k);
+      if (X) ldv<V>(xs, X + (size_t)c * M.K + k);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) ldv<V>(g[j], Div + (size_t)ix[j] * M.K + k);
+#pragma unroll
+      for (int j = 6; j < 12; ++j) ldv<V>(g[j], RelVort + (size_t)ix[j] * M.K + k);
+#pragma unroll
+      for (int j = 0; j < 6; ++j)
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] += cf[j] * (g[j][q] - ds[q]);
+#pragma unroll
+      for (int j = 6; j < 12; ++j)
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] += cf[j] * g[j][q];
+      if (YMode) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * ds[q] - Nu4Div * t[q] - xs[q];
+      }
+      stv<V>(Del2Div + (size_t)c * M.K + k, t);
+   }
+   cta_rows(M.NVerticesAll, r0, n);
+   OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
+      int ix[8];
+      double cf[8];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+         const int4 t4 = M.B3VertIdx[v * 2 + q];
+         ix[4 * q] = t4.x; ix[4 * q + 1] = t4.y; ix[4 * q + 2] = t4.z; ix[4 * q + 3] = t4.w;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+         const double2 t2 = M.B3VertCf[v * 4 + q];
+         cf[2 * q] = t2.x; cf[2 * q + 1] = t2.y;
+      }
+      double zs[V], t[V] = {0}, g[7][V];
+      ldv<V>(zs, RelVort + (size_t)v * M.K + k);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ldv<V>(g[j], Div + (size_t)ix[j] * M.K + k);
+#pragma unroll
+      for (int j = 4; j < 7; ++j) ldv<V>(g[j], RelVort + (size_t)ix[j] * M.K + k);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] += cf[j] * g[j][q];
+#pragma unroll
+      for (int j = 4; j < 7; ++j)
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] += cf[j] * (g[j][q] - zs[q]);
+      if (YMode) {
+#pragma unroll
+         for (int q = 0; q < V; ++q) t[q] = Nu2 * zs[q] - Nu4 * t[q];
+      }
+      stv<V>(Del2RelVort + (size_t)v * M.K + k, t);
+   }
+}
+
 // ---------------------------------------------------------------------------
 // fT2: TracerAuxVars::computeVarsOnCells (TracerAuxVars.h:61-91) for every
 // tracer; MeanLayerThickEdge is recomputed from h.  s*(phi(c1)-phi(c0)) ==
@@ -818,7 +898,14 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       const double nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
       LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
                G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0);
-      if (vel4)
+      // W = Y - X folded into fB's cell result when the tiled edge pass follows (one gathered cell field less)
+      const bool xOn    = G.KETendencyEnable || G.SSHTendencyEnable;
+      const bool fB3    = vel4 && D.B3OK && env_int("OMEGA_FB3", 1);
+      const bool wMerge = fB3 && tiledE && xOn && env_int("OMEGA_FUSE_W", 1);
+      if (fB3)
+         LAUNCH_V(kFB, k_fB3, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
+                  G.ViscDel4 * G.DivFactor, G.ViscDel4, wMerge ? S->A.KE : nullptr);
+      else if (vel4)
          LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
                   G.ViscDel4 * G.DivFactor, G.ViscDel4);
       // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
@@ -879,7 +966,7 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
          ta.SY = vel4 ? 1.0 : nu2; ta.SZ = ta.SY;
          ta.Ucur = Ucur; ta.Unext = Unext; ta.Uprov = Up;
          ta.A = ca.A; ta.B = ca.B; ta.First = ca.First; ta.Last = ca.Last;
-         ta.PVOn = G.PVTendencyEnable; ta.XOn = G.KETendencyEnable || G.SSHTendencyEnable;
+         ta.PVOn = G.PVTendencyEnable; ta.XOn = xOn && !wMerge;
          if (launch_fET(D, ta, St)) return 1;
          ++S->Launches;
       } else {

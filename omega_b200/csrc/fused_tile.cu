@@ -1091,7 +1091,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
             case 6: q = (P.First && P.Ucur == P.Us ? P.Us : P.Ucur) + (size_t)S.SRow[r] * K; break;
             default: q = P.Unext + (size_t)S.SRow[r] * K; break;
             }
-            prefetch_l2(q + kc0);
+            if (p >= 2 || P.XOn) prefetch_l2(q + kc0);
          }
       }
    }
@@ -1136,9 +1136,11 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
          const double mask = M.EdgeMask[e];
          const double InvDc = M.InvDcEdge[e] * mask, InvDv = M.InvDvEdge[e] * mask;
          if (P.PVOn) prefetch_row(M.WeightsOnEdge + (size_t)e * M.MaxEdges2 + p, 1); // weights towards L1 for pass 2b
-         double x0[2], x1[2], y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
-         ldv<2>(x0, P.X + (size_t)cv.x * K + k);
-         ldv<2>(x1, P.X + (size_t)cv.y * K + k);
+         double x0[2] = {0, 0}, x1[2] = {0, 0}, y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
+         if (P.XOn) { // off when k_fB3 already folded X into Y (W = Y - X)
+            ldv<2>(x0, P.X + (size_t)cv.x * K + k);
+            ldv<2>(x1, P.X + (size_t)cv.y * K + k);
+         }
          ldv<2>(y0, P.Y + (size_t)cv.x * K + k);
          ldv<2>(y1, P.Y + (size_t)cv.y * K + k);
          ldv<2>(z0, P.Z + (size_t)cv.z * K + k);

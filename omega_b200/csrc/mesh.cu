@@ -596,6 +596,56 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
          rc |= to_device(M, ac, &qd2); G.ACellCf = reinterpret_cast<const double2 *>(qd2);
          rc |= to_device(M, avc, &qd2); G.AVertCf = reinterpret_cast<const double2 *>(qd2);
       }
+      {
+         // k_fB3 tables: the same sums with every gathered row read once.  Around a cell each vertex is the
+         // end of two consecutive edges, around a vertex each cell borders two of its three edges, so
+         //   sum_j B_j (z(v1_j) - z(v0_j)) = sum_v z(v) * (sum of +-B_j),   sum_j A'_j (D(c1_j) - D(c0_j)) = sum_c D(c) * (+-A'_j)
+         // cell row: 6 neighbour cells + 6 vertices (indices [12], coefficients [12]);
+         // vertex row: 4 cells + 3 opposite vertices (+ pad) (indices [8], coefficients [8])
+         std::vector<int> ci3((size_t)(NC + 1) * 12, 0), vi3((size_t)(NV + 1) * 8, 0);
+         std::vector<double> cc3((size_t)(NC + 1) * 12, 0.0), vc3((size_t)(NV + 1) * 8, 0.0);
+         bool ok = true;
+         auto merge = [](int *idx, double *cf, int cap, int skip, int i, double c, bool &good) {
+            if (c == 0.0 || i == skip) return; // the boundary-slot row is zero
+            for (int q = 0; q < cap; ++q) {
+               if (cf[q] != 0.0 && idx[q] == i) { cf[q] += c; return; }
+            }
+            for (int q = 0; q < cap; ++q) {
+               if (cf[q] == 0.0) { idx[q] = i; cf[q] = c; return; }
+            }
+            good = false;
+         };
+         for (int c = 0; c <= NC; ++c) {
+            int *ix = &ci3[(size_t)c * 12];
+            double *cf = &cc3[(size_t)c * 12];
+            for (int j = 0; j < 6; ++j) { ix[j] = c; ix[6 + j] = NV; }
+            for (int j = 0; j < 6; ++j) {
+               const size_t o = (size_t)c * 6 + j;
+               ix[j] = ci[o * 4]; cf[j] = cc[o * 2];
+               merge(ix + 6, cf + 6, 6, NV, ci[o * 4 + 2], cc[o * 2 + 1], ok);
+               merge(ix + 6, cf + 6, 6, NV, ci[o * 4 + 1], -cc[o * 2 + 1], ok);
+            }
+         }
+         for (int v = 0; v <= NV; ++v) {
+            int *ix = &vi3[(size_t)v * 8];
+            double *cf = &vc3[(size_t)v * 8];
+            for (int j = 0; j < 4; ++j) ix[j] = NC;
+            for (int j = 0; j < 4; ++j) ix[4 + j] = v;
+            for (int j = 0; j < 3; ++j) {
+               const size_t o = (size_t)v * 3 + j;
+               merge(ix, cf, 4, NC, vi[o * 4 + 1], vc[o * 2], ok);
+               merge(ix, cf, 4, NC, vi[o * 4], -vc[o * 2], ok);
+               ix[4 + j] = vi[o * 4 + 2]; cf[4 + j] = vc[o * 2 + 1];
+            }
+         }
+         G.B3OK = ok ? 1 : 0;
+         const int *qi3 = nullptr;
+         const double *qd3 = nullptr;
+         rc |= to_device(M, ci3, &qi3); G.B3CellIdx = reinterpret_cast<const int4 *>(qi3);
+         rc |= to_device(M, vi3, &qi3); G.B3VertIdx = reinterpret_cast<const int4 *>(qi3);
+         rc |= to_device(M, cc3, &qd3); G.B3CellCf = reinterpret_cast<const double2 *>(qd3);
+         rc |= to_device(M, vc3, &qd3); G.B3VertCf = reinterpret_cast<const double2 *>(qd3);
+      }
       const int *qi = nullptr;
       const double *qd = nullptr;
       rc |= to_device(M, ci, &qi); G.B2CellIdx = reinterpret_cast<const int4 *>(qi);

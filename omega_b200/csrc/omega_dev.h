@@ -101,6 +101,8 @@ struct DMesh {
    // per (vertex, edge j) the rows {c0, c1, other vertex} and {A', B'} of
    //   Del2RelVort(v) = sum_j A'_j (Div(c1_j) - Div(c0_j)) + B'_j (RelVort(vo_j) - RelVort(v))
    const int4 *B2CellIdx, *B2VertIdx;
+   const int4 *B3CellIdx, *B3VertIdx; // k_fB3: every gathered row once (cell: 6 cells + 6 vertices; vertex: 4 cells + 3 vertices)
+   int B3OK;
    // flattened stencils of k_fA: per (cell, edge j) the edge row (B2... not needed: AEdge) and {KE, Div}
    // coefficients; per (vertex, j) the {cell, edge} rows and {kite/At, dc*sign/At}
    const int *ACellEdge;     // [C][6] edge row, boundary slot when none
@@ -108,6 +110,7 @@ struct DMesh {
    const int2 *AVertIdx;     // [V][3] {cell, edge}
    const double2 *AVertCf;   // [V][3] {kite / At, dc sign / At}
    const double2 *B2CellCf, *B2VertCf;
+   const double2 *B3CellCf, *B3VertCf;
    DTiles Tiles; // NTiles == 0 when the mesh has cells with more than 6 edges
 };
 
