@@ -29,6 +29,8 @@ WORKLOADS = {
     # name: (icosahedral level, levels, tracers, dt seconds, CPU-sample levels)
     "config3": (8, 64, 10, 60.0, 8),
     "config2": (6, 64, 2, 240.0, 16),
+    "config4": (9, 80, 2, 30.0, 8),       # BASELINE configs[3]: 2,621,442 cells x 80 levels, 2 tracers
+    "config5": (8, 64, 32, 60.0, 4),      # BASELINE configs[4]: BGC-like, 32 tracers
     "small": (5, 16, 3, 480.0, 16),
 }
 

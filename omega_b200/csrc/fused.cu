@@ -909,7 +909,8 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
          LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
                   G.ViscDel4 * G.DivFactor, G.ViscDel4);
       // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
-      const bool tiled = !upw && V == 2 && (T >= 2 || (T == 1 && !tr4)) && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
+      const bool tiled = !upw && V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) &&
+                         env_int("OMEGA_TILE", 1);
       if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
       // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
       // advection reads the stale next-level velocity the edge pass overwrites

@@ -613,7 +613,10 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    const int grow = r < nR ? S.GRow[r] : 0;
    issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kb, NS); // kb: first level of this CTA's chunks
    issue_rows<C>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], kb, 0);
-   issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], kb, 1);
+   if (T >= 2) issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], kb, 1);
+   // T >= 3: tracer i+3 goes out in iteration i (then h and tracers 0..2 of the next chunk).  Shorter tracer
+   // lists: h and the tracers of chunk c+1 go out in iterations 0, 1, .. of chunk c (four buffers hold two chunks)
+   const bool shortT = T < 3;
    load_tables<C::NT>(M, S, tid, nc + n1, nc);
    // ring-1 row pieces of this thread: items r and r + RT of n1*L (n1 <= 56)
    const int nTask = (r < n1 * L) + (r + RT < n1 * L);
@@ -621,8 +624,12 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
    for (int c = 0; c < NCh; ++c) {
       const int it0 = c * T, kc = kb + c * KC;
-      if (c == 0) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], kb, 2);
-      if (!C::BULK) cp_wait<2>(); // h and tracer 0 of this chunk have landed (this thread's pieces)
+      if (c == 0 && !shortT) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], kb, 2);
+      if (!C::BULK) { // h and tracer 0 of this chunk have landed (this thread's pieces)
+         if (!shortT) cp_wait<2>();
+         else if (T == 2) cp_wait<1>();
+         else cp_wait<0>();
+      }
       __syncthreads();            // ... and everybody else's; tables are visible; the T role is done with the previous chunk
       wait_h<C>(S, c);
       for (int u = 0; u < nTask; ++u) { // coefficients of the ring rows: -(1/A) G mean thickness, private slots in Cf1
@@ -639,9 +646,17 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
          }
       }
       for (int i = 0; i <= T; ++i) {
-         if (!C::BULK && i > 0 && i < T) cp_wait<2>(); // tracer i has landed (this thread's pieces)
+         if (!C::BULK && i > 0 && i < T) { // tracer i has landed (this thread's pieces)
+            if (!shortT) cp_wait<2>();
+            else cp_wait<1>();
+         }
          __syncthreads();                              // iteration i: the T role has finished iteration i-1
-         {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
+         if (shortT) {
+            if (c + 1 < NCh) {
+               if (i == 0) issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
+               else issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)(i - 1) * CS, &S.Phi[(it0 + T + i - 1) % NS][0][0], kc + KC, (it0 + T + i - 1) % NS);
+            } else if (!C::BULK) cp_commit();
+         } else {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
             const int n = i + 3;
             if (n < T) issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc, (it0 + n) % NS);
             else if (c + 1 < NCh) {
@@ -1018,13 +1033,17 @@ int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    OMEGA_REQUIRE(!(ca.First && ca.Last), "launch_fCT: a stage cannot be both first and last");
    const int stage = ca.First ? 0 : (ca.Last ? 2 : 1);
    static const int v2 = getenv("OMEGA_TILE_V2") ? atoi(getenv("OMEGA_TILE_V2")) : 1;
-   if (ca.HypOn && v2 && ca.NTracers >= 3 && !ca.MS.Enabled)
+   if (ca.HypOn && v2 && ca.NTracers >= 1 && !ca.MS.Enabled)
       return stage == 0 ? launch_fCT2_t<0>(D, ca, St) : stage == 1 ? launch_fCT2_t<1>(D, ca, St) : launch_fCT2_t<2>(D, ca, St);
    if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St) : launch_fCT_t<true, 2>(D, ca, St);
    return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St) : launch_fCT_t<false, 2>(D, ca, St);
 }
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
+bool tile_v2_enabled() {
+   static const int v2 = getenv("OMEGA_TILE_V2") ? atoi(getenv("OMEGA_TILE_V2")) : 1;
+   return v2 != 0;
+}
 
 // ---------------------------------------------------------------------------
 // k_fET: shared-memory staged edge pass (the work of k_fE, fused.cu).  A CTA owns the

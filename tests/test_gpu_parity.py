@@ -31,6 +31,7 @@ CASES = {
     # K % 16 == 0 -> the shared-memory tiled cell pass (fused_tile.cu); 41 tiles incl. the 12 pentagons
     "sphere4_K16_T3": lambda: cases.sphere_case(4, 16, 3),
     "plane16_K32_T2": lambda: cases.plane_case(16, 32, 2),
+    "sphere3_K16_T1": lambda: cases.sphere_case(3, 16, 1),    # one tracer: the short copy schedule of k_fCT2
     # tracer hyperdiffusion off -> the tiled pass without its Del2 phase
     "sphere3_K16_T2_nodel4": lambda: cases.sphere_case(3, 16, 2, TracerHyperDiffTendencyEnable=0),
 }
