@@ -998,10 +998,10 @@ template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const Cel
    return 0;
 }
 template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
-   // OMEGA_TILE_KC=16: one 768-thread CTA per SM; default 8: two 384-thread CTAs per SM
-   static const int kc = getenv("OMEGA_TILE_KC") ? atoi(getenv("OMEGA_TILE_KC")) : 8;
+   // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
+   // R-role width (OMEGA_TILE_RS = 0, 2, 3) and bulk row copies (OMEGA_TILE_CP = 1).  The 8-level shape
+   // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
    static const int rs = getenv("OMEGA_TILE_RS") ? atoi(getenv("OMEGA_TILE_RS")) : 2;
-   (void)kc;
    static const int cp = getenv("OMEGA_TILE_CP") ? atoi(getenv("OMEGA_TILE_CP")) : 0;
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St);
