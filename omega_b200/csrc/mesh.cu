@@ -194,48 +194,54 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
       h.C0 = c0; h.NC = nc; h.N1 = (int)r1.size(); h.N2 = (int)r2.size();
       h.RowOff = (int)rows.size(); h.NblOff = (int)(nbl.size() / 8); h.Pad0 = h.Pad1 = 0;
       // ---- edge side: own edges = edges whose lowest-ranked valid cell is an own cell; staged =
-      // every edge of the own + ring-1 cells (all EdgesOnEdge entries of the own edges are among them)
+      // the own edges and every EdgesOnEdge entry of an own edge
       h.NEOwn = h.NEStaged = 0; h.ERowOff = (int)erows.size(); h.EoEOff = (int)(eoel.size() / 10);
       if (edgeOK) {
          std::vector<int> own_e, oth_e;
-         auto visit = [&](int c) {
+         for (int i = 0; i < nc; ++i) { // an own edge always has an own cell as its lowest-ranked cell
+            const int c = c0 + i;
             for (int j = 0; j < nec[c]; ++j) {
                const int e = eoc[(size_t)c * ME + j];
                if (eloc[e] >= 0) continue;
                const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
                const int lo = std::min(a < NC ? a : INT32_MAX, b < NC ? b : INT32_MAX);
-               eloc[e] = 1 << 20;
-               (lo >= c0 && lo < c0 + nc ? own_e : oth_e).push_back(e);
+               if (lo >= c0 && lo < c0 + nc) {
+                  eloc[e] = 1 << 20;
+                  own_e.push_back(e);
+               }
             }
-         };
-         for (int i = 0; i < nc; ++i) visit(c0 + i);
-         for (int n : r1)
-            if (n < NC) visit(n);
+         }
          std::sort(own_e.begin(), own_e.end());
-         std::sort(oth_e.begin(), oth_e.end());
-         if ((int)own_e.size() > kTileEdgesOwn || (int)(own_e.size() + oth_e.size()) > kTileEdges ) edgeOK = false;
-         for (size_t i = 0; i < own_e.size(); ++i) eloc[own_e[i]] = (int)i;
-         for (size_t i = 0; i < oth_e.size(); ++i) eloc[oth_e[i]] = (int)(own_e.size() + i);
+         if ((int)own_e.size() > kTileEdgesOwn) edgeOK = false;
+         // the other staged edges: exactly the EdgesOnEdge entries of the own edges that are not own edges
+         // themselves (about 40 % of an own edge count; staging every edge of the ring-1 cells would be 80 %)
          for (size_t i = 0; edgeOK && i < own_e.size(); ++i) {
             const int e = own_e[i];
             if (neoe[e] > 10) { // cells of at most 6 edges give at most 10 entries
                edgeOK = false;
                if (getenv("OMEGA_DEBUG")) fprintf(stderr, "edge tiles off: edge %d has %d EdgesOnEdge entries\n", e, neoe[e]);
+               break;
             }
+            for (int j = 0; j < neoe[e]; ++j) {
+               const int je = eoe[(size_t)e * ME2 + j];
+               if (je < NE && eloc[je] < 0) {
+                  eloc[je] = 1 << 20;
+                  oth_e.push_back(je);
+               }
+            }
+         }
+         std::sort(oth_e.begin(), oth_e.end());
+         if ((int)(own_e.size() + oth_e.size()) > kTileEdges) edgeOK = false;
+         for (size_t i = 0; i < own_e.size(); ++i) eloc[own_e[i]] = (int)i;
+         for (size_t i = 0; i < oth_e.size(); ++i) eloc[oth_e[i]] = (int)(own_e.size() + i);
+         for (size_t i = 0; edgeOK && i < own_e.size(); ++i) {
+            const int e = own_e[i];
             for (int j = 0; j < 10; ++j) {
                int l = (int)i;
                if (j < neoe[e]) {
                   const int je = eoe[(size_t)e * ME2 + j];
-                  if (je < NE) {
-                     // an entry that is not an edge of the own + ring-1 cells: only behind a rim edge whose
-                     // second cell is the boundary slot (outermost halo); stage it as well
-                     if (eloc[je] < 0) {
-                        eloc[je] = (int)(own_e.size() + oth_e.size());
-                        oth_e.push_back(je);
-                     }
-                     l = eloc[je];
-                  } // boundary-slot entries carry zero weight: any staged row serves
-               }
+                  if (je < NE) l = eloc[je];
+               } // boundary-slot entries carry zero weight: any staged row serves
                eoel.push_back((unsigned short)l);
             }
          }
