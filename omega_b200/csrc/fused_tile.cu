@@ -1069,7 +1069,6 @@ struct ETileSmem {
    TileHdr Hdr;
 };
 
-template <int Mode>
 __global__ void __launch_bounds__(kEThreads, 2)
 k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1137,73 +1136,6 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
       if (r2 < nSt) fq(r2, u2, g0, g1, a2, b2);
       put(r, u, h0, h1, a, b);
       if (r2 < nSt) put(r2, u2, g0, g1, a2, b2);
-   }
-   if (Mode == 1) {
-      // ---- pass 2, one own edge at a time: its gathered rows (L2-resident: prefetched at the start of the
-      // CTA) travel while its neighbour sum runs from shared memory, so the global latency hides under
-      // shared-memory work and no per-edge state crosses the barrier
-      __syncthreads();
-      constexpr int kItems = kTileEdgesOwn * kTLanes / kEThreads;
-      const bool ucur_is_us = P.First && P.Ucur == P.Us;
-      const unsigned char *Fb = reinterpret_cast<const unsigned char *>(&S.F[0][0]);
-      const unsigned char *Qb = reinterpret_cast<const unsigned char *>(&S.Q[0][0]);
-      const unsigned po = (unsigned)(2 * p) * 8u;
-#pragma unroll 1
-      for (int it = 0; it < kItems; ++it) {
-         const int r = (tid >> 3) + it * (kEThreads / kTLanes);
-         if (r >= nOwn) break;
-         const int e    = S.SRow[r];
-         const size_t o = (size_t)e * K + k;
-         const int4 cv  = S.CV[r];
-         // the gathered rows of this edge start now and are consumed after the neighbour sum
-         double x0[2] = {0, 0}, x1[2] = {0, 0}, y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
-         if (P.XOn) {
-            ldv<2>(x0, P.X + (size_t)cv.x * K + k);
-            ldv<2>(x1, P.X + (size_t)cv.y * K + k);
-         }
-         ldv<2>(y0, P.Y + (size_t)cv.x * K + k);
-         ldv<2>(y1, P.Y + (size_t)cv.y * K + k);
-         ldv<2>(z0, P.Z + (size_t)cv.z * K + k);
-         ldv<2>(z1, P.Z + (size_t)cv.w * K + k);
-         if (P.First || !P.Last) ldp<2>(ucur, (ucur_is_us ? P.Us : P.Ucur) + o);
-         if (!P.First) ldp<2>(base, P.Unext + o);
-         const double mask = M.EdgeMask[e];
-         const double InvDc = M.InvDcEdge[e] * mask, InvDv = M.InvDvEdge[e] * mask;
-         double acc0 = 0, acc1 = 0;
-         if (P.PVOn) {
-            const double2 qe = lds2(Qb, r * (kTKC * 8u) + po);
-            const double2 *W = reinterpret_cast<const double2 *>(M.WeightsOnEdge + (size_t)e * M.MaxEdges2);
-#pragma unroll
-            for (int j2 = 0; j2 < 5; ++j2) {
-               const double2 w = __ldg(W + j2);
-               const unsigned ix = *reinterpret_cast<const unsigned *>(&S.EoE[r][2 * j2]);
-               const unsigned la = (ix & 0xffffu) * (kTKC * 8u) + po, lb = (ix >> 16) * (kTKC * 8u) + po;
-               const double2 fa = lds2(Fb, la), qa = lds2(Qb, la), fb = lds2(Fb, lb), qb = lds2(Qb, lb);
-               acc0 += w.x * fa.x * ((qe.x + qa.x) * 0.5);
-               acc1 += w.x * fa.y * ((qe.y + qa.y) * 0.5);
-               acc0 += w.y * fb.x * ((qe.x + qb.x) * 0.5);
-               acc1 += w.y * fb.y * ((qe.y + qb.y) * 0.5);
-            }
-            acc0 *= mask;
-            acc1 *= mask;
-         }
-         double g[2];
-#pragma unroll
-         for (int q2 = 0; q2 < 2; ++q2) {
-            g[q2] = (P.SY * (y1[q2] - y0[q2])) * InvDc - (P.SZ * (z1[q2] - z0[q2])) * InvDv;
-            if (P.XOn) g[q2] -= (x1[q2] - x0[q2]) * InvDc;
-         }
-         // same operation order as the two-pass form: p1 = base + B*g, then + B*acc
-         double out[2] = {((P.First ? ucur[0] : base[0]) + P.B * g[0]) + P.B * acc0,
-                          ((P.First ? ucur[1] : base[1]) + P.B * g[1]) + P.B * acc1};
-         stv<2>(P.Unext + o, out);
-         if (!P.Last) {
-            out[0] = (ucur[0] + P.A * g[0]) + P.A * acc0;
-            out[1] = (ucur[1] + P.A * g[1]) + P.A * acc1;
-            stv<2>(P.Uprov + o, out);
-         }
-      }
-      return;
    }
    // ---- pass 2a: gradient / diffusion terms and RK operands of the own edges.  A thread owns
    // the same (edge, piece) items as in pass 1, at most kTileEdgesOwn*8/512 = 4 of them; all
@@ -1289,16 +1221,12 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
 int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St) {
    static bool attr = false;
    if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fET<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ETileSmem)));
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fET<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ETileSmem)));
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fET, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ETileSmem)));
       attr = true;
    }
    const int nch = D.K / kTKC;
    static const int pf = getenv("OMEGA_TILE_EPF") ? atoi(getenv("OMEGA_TILE_EPF")) : 1;
-   // OMEGA_TILE_EMODE: 0 = gathers of all own edges before the barrier, 1 = pipelined per own edge behind it
-   static const int mode = getenv("OMEGA_TILE_EMODE") ? atoi(getenv("OMEGA_TILE_EMODE")) : 0;
-   if (mode == 1) k_fET<1><<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf);
-   else k_fET<0><<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf);
+   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf);
    return 0;
 }
 
