@@ -62,6 +62,16 @@ def test_permutation_and_transfer_bit_exact(case, reorder):
     if tr.shape[0]:
         d = mesh.to_device(capi.ON_CELL, tr)
         assert np.array_equal(mesh.to_host(capi.ON_CELL, d), tr)
+    # omega_field_to_host_async: pinned destination, ordered by the stream, on a side stream
+    import torch
+    pin = torch.empty(u.shape, dtype=torch.float64).pin_memory()
+    d = mesh.to_device(capi.ON_EDGE, u)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        mesh.to_host(capi.ON_EDGE, d, pin.numpy(), sync=False)
+    side.synchronize()
+    assert np.array_equal(pin.numpy(), u)
     st.close(); mesh.close()
 
 
