@@ -878,7 +878,7 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       double *Up = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
       double *Tp = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
       // sweep iterations per CTA (tuning knobs, defaults from profiles/r01 measurements)
-      const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 1),
+      const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 2),
                        itT = env_int("OMEGA_ITERS_T2", 1), itC = env_int("OMEGA_ITERS_C", 1),
                        itE = env_int("OMEGA_ITERS_E", 8);
       const unsigned gc = fused_grid(D.NCellsAll, D.K, V, kBlock, itC), ge = fused_grid(D.NEdgesAll, D.K, V, kBlock, itE);
