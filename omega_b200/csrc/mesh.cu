@@ -154,26 +154,37 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
                   if (loc[m] < 0) { loc[m] = 1 << 21; r2.push_back(m); }
                }
          std::sort(r2.begin(), r2.end());
-         // edge side of the same tile: own edges (lowest-ranked valid cell is an own cell) and
-         // staged edges (every edge of the own + ring-1 cells) must fit their caps as well
+         // edge side of the same tile: own edges (lowest-ranked valid cell is an own cell) and staged
+         // edges (the own edges and the EdgesOnEdge entries they reference) must fit their caps as well
          int nOwnE = 0, nStE = 0;
          {
             std::vector<int> seen;
-            auto count = [&](int c) {
+            for (int i = 0; i < nc; ++i) {
+               const int c = c0 + i;
                for (int j = 0; j < nec[c]; ++j) {
                   const int e = eoc[(size_t)c * ME + j];
                   if (eloc[e] >= 0) continue;
-                  eloc[e] = 0;
-                  seen.push_back(e);
                   const int a = coe[(size_t)e * 2], b = coe[(size_t)e * 2 + 1];
                   const int lo = std::min(a < NC ? a : INT32_MAX, b < NC ? b : INT32_MAX);
-                  ++nStE;
-                  if (lo >= c0 && lo < c0 + nc) ++nOwnE;
+                  if (lo >= c0 && lo < c0 + nc) {
+                     eloc[e] = 0;
+                     seen.push_back(e);
+                     ++nOwnE;
+                  }
                }
-            };
-            for (int i = 0; i < nc; ++i) count(c0 + i);
-            for (int n : r1)
-               if (n < NC) count(n);
+            }
+            nStE = nOwnE;
+            for (int q = 0; q < nOwnE; ++q) {
+               const int e = seen[q];
+               for (int j = 0; j < neoe[e] && j < ME2; ++j) {
+                  const int je = eoe[(size_t)e * ME2 + j];
+                  if (je < NE && eloc[je] < 0) {
+                     eloc[je] = 0;
+                     seen.push_back(je);
+                     ++nStE;
+                  }
+               }
+            }
             for (int e : seen) eloc[e] = -1;
          }
          const bool ok = (int)r1.size() <= kTileRing1 && nc + (int)r1.size() + (int)r2.size() <= kTileRows &&
@@ -305,6 +316,16 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    rc |= to_device(M, eoel, &T.EoELocal);
    T.EdgeTilesOK = edgeOK && !rc;
    T.NTiles = rc ? 0 : (int)hdr.size();
+   if (getenv("OMEGA_DEBUG")) {
+      int mxS = 0, mxO = 0, small = 0;
+      long long sumS = 0;
+      for (const TileHdr &h : hdr) {
+         mxS = std::max(mxS, h.NEStaged); mxO = std::max(mxO, h.NEOwn); sumS += h.NEStaged;
+         small += h.NC < kTileCells;
+      }
+      fprintf(stderr, "build_tiles: %d tiles (%d below %d cells), staged edges mean %.1f max %d, own max %d, edge tiles %s\n",
+              (int)hdr.size(), small, kTileCells, hdr.empty() ? 0.0 : (double)sumS / hdr.size(), mxS, mxO, edgeOK ? "on" : "off");
+   }
    return rc;
 }
 

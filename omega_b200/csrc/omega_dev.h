@@ -39,7 +39,7 @@ constexpr int kTileRing1 = 56;  // cap on ring-1 rows
 constexpr int kTileRows1 = kTileCells + kTileRing1; // cap on own + ring-1 rows
 constexpr int kTileRows  = 176; // cap on own + ring-1 + ring-2 rows
 constexpr int kTileEdgesOwn = 256; // cap on own edges of a tile (edges whose lowest-ranked cell is an own cell)
-constexpr int kTileEdges    = 400; // cap on staged edges: every edge of the own + ring-1 cells, own edges first
+constexpr int kTileEdges    = 400; // cap on staged edges: the own edges first, then the EdgesOnEdge entries they reference
 struct TileHdr {
    int C0, NC, N1, N2; // first own cell, counts
    int RowOff;         // offset of the tile's ring rows in HaloRows
