@@ -26,11 +26,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (icosahedral level, levels, tracers, dt seconds, CPU-sample levels)
+    # name: (icosahedral level | -nx of the planar hex mesh, levels, tracers, dt seconds, CPU-sample levels)
     "config3": (8, 64, 10, 60.0, 8),
     "config2": (6, 64, 2, 240.0, 16),
     "config4": (9, 80, 2, 30.0, 8),       # BASELINE configs[3]: 2,621,442 cells x 80 levels, 2 tracers
     "config5": (8, 64, 32, 60.0, 4),      # BASELINE configs[4]: BGC-like, 32 tracers
+    "config1": (-64, 1, 0, 120.0, 1),     # BASELINE configs[0]: planar hex 64 x 64, 1 level, manufactured solution
     "small": (5, 16, 3, 480.0, 16),
 }
 
@@ -44,10 +45,42 @@ def workload_cfg(capi, dc):
 def build_problem(name, ntasks):
     from omega_b200 import analytic, capi, decomp, meshgen
     level, K, T, dt, ks = WORKLOADS[name]
+    if level < 0:   # config 1: doubly periodic planar hex, manufactured solution (Default.yml wavelength = domain)
+        nx = -level
+        m = meshgen.planar_hex(nx, nx, 5.0e6 / nx, f0=1.0e-4, bottom_depth=1000.0)
+        cfg = capi.TendConfig.default(ManufacturedSolutionTendency=1, ManufacturedWavelengthX=float(m.Lx),
+                                      ManufacturedWavelengthY=float(m.Ly), TracerHorzAdvTendencyEnable=0,
+                                      TracerDiffTendencyEnable=0, TracerHyperDiffTendencyEnable=0)
+        return m, cfg, K, T, dt, ks
     m = meshgen.icosahedral(level)
     m.bottomDepth = analytic.tc5_bottom_depth(m)
     cfg = workload_cfg(capi, float(np.mean(m.dcEdge)))
     return m, cfg, K, T, dt, ks
+
+
+def initial_state(name, L, cfg, T):
+    from omega_b200 import analytic
+    if WORKLOADS[name][0] < 0:
+        h, u = analytic.manufactured(L, cfg)
+        return h, u, np.zeros((0, h.shape[0], h.shape[1]))
+    return analytic.tc5(L, T)
+
+
+def describe(name, m, K, T, dt):
+    if WORKLOADS[name][0] < 0:
+        return (f"{name}: planar hex {m.nCells} cells x {K} level, no tracers, RK4 dt={dt:g}s, manufactured-solution "
+                "source terms, Del2+Del4 on velocity")
+    return (f"{name}: icosahedral {m.nCells} cells x {K} levels, {T} tracers, RK4 dt={dt:g}s, "
+            "Del2+Del4 on velocity and tracers, TC5-style state")
+
+
+def host_threads():
+    """Threads the CPU arm may use: the cores this process is allowed on (torch.distributed.run exports
+    OMP_NUM_THREADS=1 to its workers, which is not the machine's core count)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 class ClockSampler:
@@ -90,24 +123,49 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_rate(name, steps, warmup, threads=None):
-    """Reference CPU implementation of the same step on the host cores: the
-    reference's own sources over the host Kokkos stand-in (oracle/_ref) when
-    built, else the plain-C port (oracle/).  Bounded sample: the full
-    horizontal mesh with `ks` of the K levels (levels are independent in
-    Omega-0, cost is linear in them)."""
-    from omega_b200 import analytic, capi, decomp
+def cpu_reference_rate(name, steps, warmup, full_depth):
+    """The reference's CPU implementation of the same step on the host cores: the reference's own sources over
+    the host Kokkos stand-in with OpenMP (oracle/_ref/libomega_ref_fast.so) when built, else the plain-C port
+    (oracle/).  full_depth: all K levels (the --impl reference arm); otherwise a bounded sample, the full
+    horizontal mesh with `ks` of the K levels (levels are independent in Omega-0, cost is linear in them)."""
+    nthr = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(nthr)      # before libgomp initialises (first load of the oracle library)
+    os.environ.setdefault("OMP_PROC_BIND", "spread")
+    os.environ.setdefault("OMP_PLACES", "threads")
+    import ctypes
+    from omega_b200 import capi, decomp
     from tests import oracle_lib
     m, cfg, K, T, dt, ks = build_problem(name, 1)
-    L = decomp.build_all(m, 1, ks)[0]
-    h, u, tr = analytic.tc5(L, T)
-    if os.path.exists(oracle_lib.REF_FAST) and ks % 8 == 0:
+    if full_depth:
+        # footprint of the reference's arrays (SURVEY 8: (177 + 24 T) doubles per cell-layer incl. HTracersEdge)
+        need = m.nCells * K * 8.0 * (60 + 9 * T) * 1.3
+        avail = 0.0
+        try:
+            for ln in open("/proc/meminfo"):
+                if ln.startswith("MemAvailable"):
+                    avail = float(ln.split()[1]) * 1024
+        except OSError:
+            pass
+        if avail and need > 0.8 * avail:
+            full_depth = False
+    kl = K if full_depth else min(ks, K)
+    L = decomp.build_all(m, 1, kl)[0]
+    h, u, tr = initial_state(name, L, cfg, T)
+    if os.path.exists(oracle_lib.REF_FAST) and kl % 8 == 0:
         path, kind = oracle_lib.REF_FAST, "reference"
     else:
         if not os.path.exists(oracle_lib.FAST):
             oracle_lib.build_oracle()
         path, kind = oracle_lib.FAST, "port"
     o = oracle_lib.Oracle(L, cfg, T, lib_path=path)
+    try:
+        # libgomp may already be initialised (torch loads it) with torchrun's OMP_NUM_THREADS=1: set the
+        # thread count of this thread's parallel regions explicitly, then read back what will be used
+        gomp = ctypes.CDLL("libgomp.so.1")
+        gomp.omp_set_num_threads(nthr)
+        used = int(gomp.omp_get_max_threads())
+    except OSError:
+        used = 1
     o.make_state(h, u, tr)
     co = capi.rk_coeffs(capi.RK4, dt)
     for _ in range(warmup):
@@ -117,27 +175,30 @@ def cpu_reference_rate(name, steps, warmup, threads=None):
         o.do_step(capi.RK4, co, compat=1)
     el = time.perf_counter() - t0
     o.close()
-    rate = m.nCells * ks * steps / el
-    return {"value": rate, "unit": "cell-layer updates/s", "cores": os.cpu_count(), "kind": kind,
-            "sample": f"{m.nCells} cells x {ks} of {K} levels, {T} tracers, {steps} RK4 step(s), "
-                      f"{el / steps:.2f} s/step, OpenMP over all host cores"}, el / steps, dt, m.nCells, ks
+    rate = m.nCells * kl * steps / el
+    what = "all" if kl == K else f"{kl} of the"
+    return {"value": rate, "unit": "cell-layer updates/s", "cores": used, "kind": kind,
+            "sample": f"{m.nCells} cells x {what} {K} levels, {T} tracers, {warmup} warm-up + {steps} timed RK4 step(s), "
+                      f"{el / steps:.2f} s/step, OpenMP threads {used} (omp_get_max_threads; {nthr} cores available)",
+            "extrapolated": kl != K}, el / steps, dt, m, kl
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warm = max(1, min(args.steps, 3)), min(args.warmup, 1)
-    cb, s_per_step, dt, ncells, ks = cpu_reference_rate(args.workload, steps, warm)
     level, K, T, _, _ = WORKLOADS[args.workload]
-    # seconds per full-depth step = sample time scaled by K/ks
-    full = s_per_step * K / ks
+    # a full-depth config-3 step costs ~25 s on the box's host cores: at most 3 timed steps after one warm-up
+    big = level >= 8
+    steps, warm = (max(1, min(args.steps, 3)), min(args.warmup, 1)) if big else (args.steps, args.warmup)
+    cb, s_per_step, dt, m, kl = cpu_reference_rate(args.workload, steps, warm, full_depth=True)
+    full = s_per_step * K / kl
     line = {"impl": "reference", "metric": "cell-layer updates/s", "value": cb["value"], "unit": "cell-layer updates/s",
             "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": full * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "sypd": dt / (365.0 * full),
-            "config": {"workload": f"{args.workload}: icosahedral {ncells} cells x {K} levels, {T} tracers, RK4 dt={dt:g}s, "
-                                   "Del2+Del4 (CPU sample scaled by levels)"},
+            "config": {"workload": describe(args.workload, m, K, T, dt), "path": "reference CPU sources, OpenMP host shim",
+                       "levels_run": kl},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "cell-layer updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -183,11 +244,11 @@ def main():
         # HaloWidth 4: with the biharmonic terms on, the default 3 makes the reference algorithm itself
         # partition dependent (tests/test_multirank_cpu.py::test_reference_needs_halo_width_4_with_del4)
         L, halo_desc = parallel.local_problem(m, world, rank, K, halo_width=4)
-    h, u, tr = analytic.tc5(L, T)
+    h, u, tr = initial_state(args.workload, L, cfg, T)
     mesh = model.HorzMesh(L, reorder=True, device=dev)
     st = model.Stepper(mesh, cfg, T)
     state = model.OceanState(mesh, T)
-    state.copyToDevice(h, u, tr)
+    state.copyToDevice(h, u, tr if T else None)
     if world > 1:
         halo = parallel.HaloExchanger(mesh, halo_desc, T)
 
@@ -231,6 +292,20 @@ def main():
     # sanity: the state must still be finite after W + K steps
     hh = state.getLayerThickness(0)
     assert bool(torch.isfinite(hh).all()), "state blew up"
+    # checksum over OWNED elements, reduced over ranks: sum(A h), sum(A h phi_l) per tracer, sum(u^2).  The result
+    # of W + K steps must not depend on the partition (HaloWidth 4, tests/test_multirank_cpu.py), so the N-GPU
+    # values equal the one-GPU values to rounding of the reduction order: a wrong exchange list shows here.
+    pc, _ = mesh.perm(capi.ON_CELL)
+    nco, neo = mesh.NOwned[0], mesh.NOwned[1]
+    area = torch.from_numpy(np.ascontiguousarray(np.asarray(L.AreaCell)[pc][:nco])).to(dev)
+    ah = area[:, None] * hh[:nco]
+    cs = [ah.sum()]
+    cs += [(ah * state.getTracers(0)[l, :nco]).sum() for l in range(T)]
+    cs.append((state.getNormalVelocity(0)[:neo] ** 2).sum())
+    cs = torch.stack(cs)
+    if world > 1:
+        dist.all_reduce(cs, op=dist.ReduceOp.SUM)
+    checksum = [float(x) for x in cs.cpu()]
 
     ncl = m.nCells * K                       # cell-layers of the whole job
     t_step = ms / 1e3 / K_steps
@@ -251,7 +326,7 @@ def main():
     # counted step and ends with a device synchronisation.
     e2e = None
     if not args.no_e2e and world == 1:
-        hp = [torch.from_numpy(a).pin_memory() for a in (h, u, tr)]
+        hp = [torch.from_numpy(a).pin_memory() for a in ((h, u, tr) if T else (h, u))]
         NS = 3
         slots = [state] + [model.OceanState(mesh, T) for _ in range(NS - 1)]
         outp = [[torch.empty_like(x).pin_memory() for x in hp] for _ in range(2)]
@@ -270,7 +345,8 @@ def main():
                             s_in.wait_event(ev_out[i % NS])   # the slot's previous result has left
                         mesh.to_device(capi.ON_CELL, hp[0].numpy(), sl.getLayerThickness(0), sync=False)
                         mesh.to_device(capi.ON_EDGE, hp[1].numpy(), sl.getNormalVelocity(0), sync=False)
-                        mesh.to_device(capi.ON_CELL, hp[2].numpy(), sl.getTracers(0), sync=False)
+                        if T:
+                            mesh.to_device(capi.ON_CELL, hp[2].numpy(), sl.getTracers(0), sync=False)
                         ev_in[i % NS].record(s_in)
                 j = i - 1
                 if 0 <= j < n:                  # step j
@@ -285,7 +361,8 @@ def main():
                         s_out.wait_event(ev_cmp[j % NS])
                         mesh.to_host(capi.ON_CELL, sl.getLayerThickness(0), o[0].numpy(), sync=False)
                         mesh.to_host(capi.ON_EDGE, sl.getNormalVelocity(0), o[1].numpy(), sync=False)
-                        mesh.to_host(capi.ON_CELL, sl.getTracers(0), o[2].numpy(), sync=False)
+                        if T:
+                            mesh.to_host(capi.ON_CELL, sl.getTracers(0), o[2].numpy(), sync=False)
                         ev_out[j % NS].record(s_out)
             torch.cuda.synchronize()
 
@@ -316,6 +393,7 @@ def main():
         # = (3+5+5+3)/4 * 8 * (1+T) bytes per cell-layer on average
         cl_local = mesh.NAll[0] * K
         alg_fc = 32.0 * (1 + T) * cl_local
+        alg_stage = [8.0 * n * (1 + T) * cl_local for n in (3, 5, 5, 3)]   # per RK4 stage
         ach = alg_fc / (kms[3] / kcnt[3] * 1e-3) / 1e9
         # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/)
         traffic = None
@@ -325,16 +403,20 @@ def main():
         roofline = {"bound": "hbm", "kernel": "k_fCT2 (tiled cell pass: thickness + all tracer tendencies + RK updates)",
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": traffic, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": alg_fc}
+                    "algorithmic_bytes_per_launch": alg_fc, "algorithmic_bytes_by_stage": alg_stage,
+                    "traffic_stage": 1 if traffic else None,
+                    "traffic_over_algorithmic": traffic / alg_stage[1] if traffic else None}
     ach_step = alg_step * ncl / world / t_step / 1e9
     line = {"metric": "cell-layer updates/s", "value": value, "unit": "cell-layer updates/s", "n_gpus": world,
             "steps": K_steps, "warmup": W, "ms_per_step": t_step * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "sypd": dt / (365.0 * t_step),
-            "config": {"workload": f"{args.workload}: icosahedral {m.nCells} cells x {K} levels, {T} tracers, RK4 dt={dt:g}s, "
-                                   "Del2+Del4 on velocity and tracers, TC5-style state",
+            "config": {"workload": describe(args.workload, m, K, T, dt),
                        "path": "fused" if fused else "kernel-per-term", "parallelism": f"domain decomposition x{world}",
-                       "l2": "state per step (>= 5 GB) exceeds the 126 MB L2; no flush needed"},
+                       "l2": ("state per step (>= 5 GB) exceeds the 126 MB L2; no flush needed" if ncl * (4 + T) * 8 > 2.5e8
+                              else "state fits L2 (launch-bound workload); no flush")},
+            "checksum": {"sum_A_h": checksum[0], "sum_A_h_phi": checksum[1:-1], "sum_u2": checksum[-1],
+                         "what": "owned elements, summed over ranks, after warmup + steps"},
             "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
             "roofline_step": {"bound": "hbm", "achieved": ach_step, "peak": peak, "unit": "GB/s", "frac": ach_step / peak,
                               "algorithmic_bytes_per_cell_layer_step": alg_step, "per_gpu": True},
@@ -344,7 +426,7 @@ def main():
         line["halo"] = {"rounds_per_step": 2, "send_bytes_per_round_rank0": bytes_round, "halo_width": 4,
                         "transport": "NCCL send/recv (torch.distributed batch_isend_irecv), pack/unpack CUDA kernels"}
     if world == 1 and not args.no_cpu_baseline:
-        cb, *_ = cpu_reference_rate(args.workload, 1, 0)
+        cb, *_ = cpu_reference_rate(args.workload, 2, 1, full_depth=False)
         line["cpu_baseline"] = cb
     else:
         line["cpu_baseline"] = None

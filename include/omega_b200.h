@@ -236,6 +236,10 @@ int omega_state_rotate(OmegaStateArrays *State);
 int omega_stepper_provis_arrays(OmegaStepper *Stepper, double **H, double **U, double **Tr);
 /* kernels launched by this stepper since creation (bench gpu_launches) */
 long long omega_stepper_launch_count(const OmegaStepper *S);
+/* which kernels the last omega_stepper_step_phase / do_step ran: OMEGA_PATH_* bits (0 = the
+ * kernel-per-term path).  Tests assert through this that a case exercised the tiled kernels. */
+enum { OMEGA_PATH_FUSED = 1, OMEGA_PATH_TILED_CELL = 2, OMEGA_PATH_CELL_V2 = 4, OMEGA_PATH_TILED_EDGE = 8 };
+int omega_stepper_last_path(const OmegaStepper *S);
 /* per-kernel CUDA-event timing of the fused pipeline: sums in ms and launch
  * counts per kernel kind (0 fA, 1 fB, 2 fT2, 3 fC, 4 fE) since the last call;
  * get_profile synchronises the device. */

@@ -173,7 +173,8 @@ def rk_coeffs(stepper: int, dt: float, t0: float = 0.0) -> StepCoeffs:
 
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200.so")
+# OMEGA_B200_LIB: another build of the same library (profiling experiments); never a CPU fallback
+LIB_PATH = os.environ.get("OMEGA_B200_LIB") or os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200.so")
 
 
 def load_library(path: str = LIB_PATH) -> C.CDLL:

@@ -909,8 +909,11 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
          LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
                   G.ViscDel4 * G.DivFactor, G.ViscDel4);
       // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
-      const bool tiled = !upw && V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) &&
-                         env_int("OMEGA_TILE", 1);
+      // (one tracer + tracer hyperdiffusion needs k_fCT2, which has no manufactured thickness source:
+      // k_fCT's D role assumes at least two tracers)
+      const bool tiled = !upw && V == 2 &&
+                         (T >= 2 || (T == 1 && (!tr4 || (tile_v2_enabled() && !G.ManufacturedSolutionTendency)))) &&
+                         tile_path_ok(D) && env_int("OMEGA_TILE", 1);
       if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
       // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
       // advection reads the stale next-level velocity the edge pass overwrites
@@ -928,6 +931,8 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
       ca.Prefetch = env_int("OMEGA_FC_PREFETCH", 0);
       ca.MS = manufactured(S, C->StageTime[s]);
+      S->LastPath = OMEGA_PATH_FUSED | (tiled ? OMEGA_PATH_TILED_CELL : 0) | (tiled && tile_v2_used(ca) ? OMEGA_PATH_CELL_V2 : 0) |
+                    (tiledE ? OMEGA_PATH_TILED_EDGE : 0);
       {
       ScopedTimer tm_(S, St, kFC);
       const int variant = env_int("OMEGA_FC_VARIANT", 3);

@@ -48,6 +48,7 @@ struct EdgeTileArgs {
 // fused_tile.cu
 bool tile_path_ok(const DMesh &D);
 bool tile_v2_enabled(); // k_fCT2 (any tracer count with tracer hyperdiffusion) is selectable
+bool tile_v2_used(const CellArgs &ca); // launch_fCT will run k_fCT2 for these arguments
 bool tile_edge_path_ok(const DMesh &D);
 int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St);
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St);

@@ -56,6 +56,33 @@ template <int KC, int NS> struct TileSmemT {
 };
 using TileSmem = TileSmemT<kTKC, kTStages>;
 
+// cudaFuncSetAttribute and the SM count are per DEVICE: a host process may drive several devices
+// (one OmegaMesh each), so the one-time set-up below is keyed by the current device.
+constexpr int kMaxDev = 64;
+struct DevOnce {
+   bool Done[kMaxDev] = {};
+   int Sm[kMaxDev]    = {};
+};
+static int cur_dev() {
+   int d = 0;
+   cudaGetDevice(&d);
+   return d >= 0 && d < kMaxDev ? d : 0;
+}
+template <class F> static int set_smem_once(DevOnce &O, F *Kernel, size_t Bytes, int *Sm = nullptr) {
+   const int d = cur_dev();
+   if (!O.Done[d]) {
+      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Bytes));
+      OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&O.Sm[d], cudaDevAttrMultiProcessorCount, d));
+      O.Done[d] = true;
+   }
+   if (Sm) *Sm = O.Sm[d];
+   return 0;
+}
+static int env_i(const char *Name, int Dflt) {
+   const char *v = getenv(Name);
+   return v ? atoi(v) : Dflt;
+}
+
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(unsigned dst, const void *src) {
    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
@@ -688,7 +715,11 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
 #pragma unroll
                for (int j = 0; j < kME; ++j) {
                   const double2 pn = lds2(Pb, (nbl_get(tt, j) * KC + 2 * p) * 8u);
+#ifdef OMEGA_EXP_NOPRIV // timing experiment only (wrong results): private coefficient reads removed
+                  const double2 cf = make_double2(1e-9 * j, 1e-9);
+#else
                   const double2 cf = lds2(Cb, j * (KC * 8u));
+#endif
                   e0 += cf.x * (pr.x - pn.x);
                   e1 += cf.y * (pr.y - pn.y);
                }
@@ -858,11 +889,19 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
       auto pass_B = [&](int l) {
          const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
          const double2 ds = lds2(Db, myoff);
+#ifdef OMEGA_EXP_NOPRIV
+         const double SHl = 1e-9;
+#else
          const double SHl = S.SHc[li];
+#endif
          double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
 #pragma unroll
          for (int j = 0; j < kME; j += 2) {
+#ifdef OMEGA_EXP_NOPRIV
+            const double2 c2 = make_double2(1e-9 * j, 1e-9);
+#else
             const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
+#endif
             const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
             tend[0] += c2.x * da.x;
             tend[1] += c2.x * da.y;
@@ -885,7 +924,11 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             }
             stg_na(P.TrNext + l * CS + o, out);
             if (!Last) {
+#ifdef OMEGA_EXP_NOPRIV
+               const double2 w1v = make_double2(1.0, 1.0), w2v = make_double2(P.A, P.A);
+#else
                const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
+#endif
                const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
 #pragma unroll
                for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
@@ -972,21 +1015,13 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole) {
 }
 
 template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
-   static bool attr = false;
-   if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT2<C, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(typename C::Smem)));
-      attr = true;
-   }
-   static const int pf = getenv("OMEGA_TILE_PF") ? atoi(getenv("OMEGA_TILE_PF")) : 1;
+   static DevOnce once;
+   int sm = 0;
+   if (set_smem_once(once, k_fCT2<C, STAGE>, sizeof(typename C::Smem), &sm)) return 1;
+   const int pf = env_i("OMEGA_TILE_PF", 1);
    // one CTA per tile; the tiles of the last partial round of CTAs are split into one CTA per chunk when
    // that shortens the tail (matters on multi-GPU partitions with ~10 rounds)
-   static const int split = getenv("OMEGA_TILE_SPLIT") ? atoi(getenv("OMEGA_TILE_SPLIT")) : 1;
-   static int sm = 0;
-   if (!sm) {
-      int dev = 0;
-      OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
-      OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
-   }
+   const int split = env_i("OMEGA_TILE_SPLIT", 1);
    const int nch = D.K / C::KC, nt = D.Tiles.NTiles;
    int whole = nt;
    if (split && nch > 1) {
@@ -1001,29 +1036,26 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
    // R-role width (OMEGA_TILE_RS = 0, 2, 3) and bulk row copies (OMEGA_TILE_CP = 1).  The 8-level shape
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
-   static const int rs = getenv("OMEGA_TILE_RS") ? atoi(getenv("OMEGA_TILE_RS")) : 2;
-   static const int cp = getenv("OMEGA_TILE_CP") ? atoi(getenv("OMEGA_TILE_CP")) : 0;
+   const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0);
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
 template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
-   static bool attr = false;
-   if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fCT<HYP, STAGE, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem)));
-      attr = true;
-   }
+   static DevOnce once;
+   if (set_smem_once(once, k_fCT<HYP, STAGE, RS>, sizeof(TileSmem))) return 1;
+   OMEGA_REQUIRE(!HYP || ca.NTracers >= 2, "k_fCT with tracer hyperdiffusion needs at least two tracers");
    const int nch = D.K / kTKC;
    // with the D role (which needs two tracers to prime its pipeline) a CTA walks all chunks of its tile
-   static const int persist = getenv("OMEGA_TILE_PERSIST") ? atoi(getenv("OMEGA_TILE_PERSIST")) : 1;
+   const int persist = env_i("OMEGA_TILE_PERSIST", 1);
    const bool walk = HYP && persist;
    const unsigned grid = (unsigned)D.Tiles.NTiles * (walk ? 1 : nch);
    k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, walk ? -nch : nch);
    return 0;
 }
 template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
-   static const int rs = getenv("OMEGA_TILE_REGS") ? atoi(getenv("OMEGA_TILE_REGS")) : 0;
+   const int rs = env_i("OMEGA_TILE_REGS", 0);
    if (HYP && rs == 1) return launch_fCT_r<HYP, STAGE, HYP ? 1 : 0>(D, ca, St);
    if (HYP && rs == 2) return launch_fCT_r<HYP, STAGE, HYP ? 2 : 0>(D, ca, St);
    return launch_fCT_r<HYP, STAGE, 0>(D, ca, St);
@@ -1032,18 +1064,16 @@ template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const Cel
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
    OMEGA_REQUIRE(!(ca.First && ca.Last), "launch_fCT: a stage cannot be both first and last");
    const int stage = ca.First ? 0 : (ca.Last ? 2 : 1);
-   static const int v2 = getenv("OMEGA_TILE_V2") ? atoi(getenv("OMEGA_TILE_V2")) : 1;
-   if (ca.HypOn && v2 && ca.NTracers >= 1 && !ca.MS.Enabled)
+   if (tile_v2_used(ca))
       return stage == 0 ? launch_fCT2_t<0>(D, ca, St) : stage == 1 ? launch_fCT2_t<1>(D, ca, St) : launch_fCT2_t<2>(D, ca, St);
    if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St) : launch_fCT_t<true, 2>(D, ca, St);
    return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St) : launch_fCT_t<false, 2>(D, ca, St);
 }
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
-bool tile_v2_enabled() {
-   static const int v2 = getenv("OMEGA_TILE_V2") ? atoi(getenv("OMEGA_TILE_V2")) : 1;
-   return v2 != 0;
-}
+bool tile_v2_enabled() { return env_i("OMEGA_TILE_V2", 1) != 0; }
+// k_fCT2 serves every tracer count with tracer hyperdiffusion on (no manufactured thickness source)
+bool tile_v2_used(const CellArgs &ca) { return ca.HypOn && tile_v2_enabled() && ca.NTracers >= 1 && !ca.MS.Enabled; }
 
 // ---------------------------------------------------------------------------
 // k_fET: shared-memory staged edge pass (the work of k_fE, fused.cu).  A CTA owns the
@@ -1070,7 +1100,7 @@ struct ETileSmem {
 };
 
 __global__ void __launch_bounds__(kEThreads, 2)
-k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
+k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    ETileSmem &S = *reinterpret_cast<ETileSmem *>(smem_raw);
    const int tid = threadIdx.x;
@@ -1091,7 +1121,28 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
    }
    __syncthreads();
    const int p = tid & 7, k = kc0 + 2 * p;
-   if (Pf) {
+   if ((Pf & 2) && tile + Ahead < M.Tiles.NTiles) {
+      // Cross-CTA software pipelining through L2: the pass-1 rows (u, h of both cells, PV of both vertices of
+      // every staged edge) of the tile-chunk that a CTA of the NEXT wave will work on are requested now, so
+      // that CTA finds them in L2 (~250 cycles) instead of in DRAM (~700): the kernel is bound by the latency
+      // of exactly these gathers (ncu: long_scoreboard at the first use of pass 1).
+      const TileHdr *Hn = M.Tiles.Hdr + tile + Ahead;
+      const int nS2 = Hn->NEStaged, off2 = Hn->ERowOff;
+      if (p < 5)
+         for (int r = tid >> 3; r < nS2; r += kEThreads / kTLanes) {
+            const int4 cv = M.Tiles.EdgeCV[off2 + r];
+            const double *q;
+            switch (p) {
+            case 0: q = P.Us + (size_t)M.Tiles.EdgeRows[off2 + r] * K; break;
+            case 1: q = P.Hs + (size_t)cv.x * K; break;
+            case 2: q = P.Hs + (size_t)cv.y * K; break;
+            case 3: q = P.PVv + (size_t)cv.z * K; break;
+            default: q = P.PVv + (size_t)cv.w * K; break;
+            }
+            prefetch_l2(q + kc0);
+         }
+   }
+   if (Pf & 1) {
       // the eight gathered rows of pass 2a (X, Y of both cells, Z of both vertices, u_cur, u_next) of this
       // thread's own edges: one of the eight lanes of an edge each, pulled into L2 while pass 1 runs
 #pragma unroll
@@ -1219,14 +1270,14 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf) {
 }
 
 int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St) {
-   static bool attr = false;
-   if (!attr) {
-      OMEGA_CUDA_CHECK(cudaFuncSetAttribute(k_fET, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ETileSmem)));
-      attr = true;
-   }
+   static DevOnce once;
+   int sm = 0;
+   if (set_smem_once(once, k_fET, sizeof(ETileSmem), &sm)) return 1;
    const int nch = D.K / kTKC;
-   static const int pf = getenv("OMEGA_TILE_EPF") ? atoi(getenv("OMEGA_TILE_EPF")) : 1;
-   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf);
+   // bit 0: own pass-2a rows, bit 1: pass-1 rows of the tile a CTA of the next wave takes (2 CTAs per SM)
+   const int pf = env_i("OMEGA_TILE_EPF", 3);
+   const int ahead = env_i("OMEGA_TILE_EAHEAD", (2 * sm + nch - 1) / nch);
+   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead);
    return 0;
 }
 

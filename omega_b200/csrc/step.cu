@@ -127,6 +127,7 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
    OMEGA_REQUIRE(Phase >= 0 && Phase < n_phases(Type), "omega_stepper_step_phase: bad phase");
    Ctx X{S, (cudaStream_t)Stream, RawTimeLevelCompat};
    int rc;
+   S->LastPath = 0;
    if (Type == OMEGA_STEPPER_RK4 && Fused)
       rc = fused_rk4_phase(S, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
    else if (Type == OMEGA_STEPPER_RK4)

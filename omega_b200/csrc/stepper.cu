@@ -17,7 +17,10 @@ int stepper_alloc(OmegaStepper *S, double **p, size_t n) {
    void *d = nullptr;
    const size_t bytes = (n ? n : 2) * sizeof(double);
    OMEGA_CUDA_CHECK(cudaMalloc(&d, bytes));
+   // the memset runs on the legacy default stream, which callers' non-blocking streams do not
+   // synchronise with: wait for it here so no later kernel can race with it (allocations are rare)
    OMEGA_CUDA_CHECK(cudaMemset(d, 0, bytes));
+   OMEGA_CUDA_CHECK(cudaStreamSynchronize(0));
    S->Allocs.push_back(d);
    *p = (double *)d;
    return 0;
@@ -59,6 +62,7 @@ int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int 
    S->NTracers = NTracers;
    S->Launches = 0;
    S->ProvisExchangeSlot = 0;
+   S->LastPath = 0;
    S->Profiling = 0;
    std::memset(&S->A, 0, sizeof(S->A));
    std::memset(&S->T, 0, sizeof(S->T));
@@ -151,6 +155,7 @@ int omega_stepper_set_wind_stress(OmegaStepper *S, const double *Zonal, const do
 }
 
 long long omega_stepper_launch_count(const OmegaStepper *S) { return S ? S->Launches : 0; }
+int omega_stepper_last_path(const OmegaStepper *S) { return S ? S->LastPath : 0; }
 
 int omega_stepper_set_profiling(OmegaStepper *S, int Enable) {
    OMEGA_REQUIRE(S, "omega_stepper_set_profiling: null argument");

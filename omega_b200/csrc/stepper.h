@@ -18,6 +18,7 @@ struct OmegaStepper {
    ProvisArrays P;
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
+   int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
    std::vector<void *> Allocs;
    // optional per-kernel CUDA-event timing of the fused pipeline (bench roofline)
    int Profiling;

@@ -225,6 +225,10 @@ class Stepper:
     def launch_count(self):
         return int(self.lib.omega_stepper_launch_count(self.h))
 
+    def last_path(self):
+        """OMEGA_PATH_* bits of the last step: 1 fused, 2 tiled cell pass, 4 k_fCT2, 8 tiled edge pass."""
+        return int(self.lib.omega_stepper_last_path(self.h))
+
     def close(self):
         if self.h:
             self.lib.omega_stepper_destroy(self.h)

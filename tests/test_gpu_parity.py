@@ -34,7 +34,13 @@ CASES = {
     "sphere3_K16_T1": lambda: cases.sphere_case(3, 16, 1),    # one tracer: the short copy schedule of k_fCT2
     # tracer hyperdiffusion off -> the tiled pass without its Del2 phase
     "sphere3_K16_T2_nodel4": lambda: cases.sphere_case(3, 16, 2, TracerHyperDiffTendencyEnable=0),
+    # shapes of BASELINE configs 5 and 4 on a small mesh: 32 tracers walk the four rotating tracer buffers of
+    # k_fCT2 eight times per chunk; 80 levels are five chunks (copy stream index it0 = chunk * T)
+    "sphere3_K64_T32": lambda: cases.sphere_case(3, 64, 32),
+    "sphere3_K80_T2": lambda: cases.sphere_case(3, 80, 2),
 }
+TILED = {"sphere4_K16_T3", "plane16_K32_T2", "sphere3_K16_T1", "sphere3_K16_T2_nodel4", "sphere3_K64_T32",
+         "sphere3_K80_T2", "sphere3_K64_T3"}
 
 
 @pytest.fixture(scope="module", params=list(CASES))
@@ -157,7 +163,12 @@ def test_manufactured_solution_rhs():
     o.close(); st.close(); mesh.close()
 
 
-def run_steps(L, cfg, init, dt, stepper, nsteps, fused, compat, reorder=True):
+PATH_FUSED, PATH_TILED_CELL, PATH_CELL_V2, PATH_TILED_EDGE = 1, 2, 4, 8
+
+
+def run_steps(L, cfg, init, dt, stepper, nsteps, fused, compat, reorder=True, want_path=0, t0=0.0):
+    """nsteps of `stepper` on the GPU and in the oracle; relative L2 errors of (h, u[, tracers]).
+    want_path: OMEGA_PATH_* bits the GPU step must have run (omega_stepper_last_path)."""
     from tests.oracle_lib import Oracle
     h, u, tr = init
     T = tr.shape[0]
@@ -165,10 +176,11 @@ def run_steps(L, cfg, init, dt, stepper, nsteps, fused, compat, reorder=True):
     o = Oracle(L, cfg, T)
     o.make_state(h, u, tr)
     state.copyToDevice(h, u, tr)
-    co = capi.rk_coeffs(stepper, dt)
-    for _ in range(nsteps):
+    for i in range(nsteps):
+        co = capi.rk_coeffs(stepper, dt, t0=t0 + i * dt)
         o.do_step(stepper, co, compat=int(compat))
         st.doStep(state, stepper, co, fused=fused, compat=compat)
+    assert st.last_path() & want_path == want_path, (st.last_path(), want_path)
     got, exp = state.copyToHost(0), o.current()
     errs = [rel_l2(got[0], exp[0]), rel_l2(got[1], exp[1])]
     if T:
@@ -189,16 +201,118 @@ def test_steppers_kernel_per_term_path(case, stepper, compat):
 @pytest.mark.parametrize("compat", [True, False])
 def test_rk4_fused_path(case, compat):
     name, (L, cfg, init, dt) = case
-    errs = run_steps(L, cfg, init, dt, capi.RK4, 5, fused=True, compat=compat)
+    want = PATH_FUSED
+    if name in TILED:   # the kernels bench.py times: k_fCT2 (k_fCT without tracer Del4) and k_fET
+        want |= PATH_TILED_CELL | PATH_TILED_EDGE | (0 if "nodel4" in name else PATH_CELL_V2)
+    errs = run_steps(L, cfg, init, dt, capi.RK4, 5, fused=True, compat=compat, want_path=want)
     assert max(errs) <= TOL_STATE, (name, errs)
 
 
 def test_rk4_100_steps_state_parity():
-    """BASELINE.json: prognostic state after 100 RK4 steps, relative L2 <= 1e-10."""
+    """BASELINE.json: prognostic state after 100 RK4 steps, relative L2 <= 1e-10 (untiled kernels: K = 8)."""
     L, cfg, init, dt = cases.sphere_case(3, 8, 3)
     for fused in (False, True):
         errs = run_steps(L, cfg, init, dt, capi.RK4, 100, fused=fused, compat=True)
         assert max(errs) <= TOL_STATE, (fused, errs)
+
+
+@pytest.mark.parametrize("compat", [True, False])
+def test_rk4_100_steps_state_parity_tiled_kernels(compat):
+    """The same gate on the kernels the bench times: K = 16 runs k_fCT2 + k_fET (asserted)."""
+    L, cfg, init, dt = cases.sphere_case(4, 16, 3)
+    errs = run_steps(L, cfg, init, dt, capi.RK4, 100, fused=True, compat=compat,
+                     want_path=PATH_FUSED | PATH_TILED_CELL | PATH_CELL_V2 | PATH_TILED_EDGE)
+    assert max(errs) <= TOL_STATE, errs
+
+
+def test_fused_manufactured_one_tracer_with_del4():
+    """Manufactured thickness source + ONE tracer + tracer hyperdiffusion at K = 32: k_fCT2 has no
+    manufactured source and k_fCT's Del2 role needs two tracers, so this must take the untiled cell pass
+    (it used to reach k_fCT and read past the tracer array)."""
+    L, cfg, _, dt = cases.plane_case(16, 32, 1, ManufacturedSolutionTendency=1, ManufacturedWavelengthX=16 * 5.0e6 / 64,
+                                     ManufacturedWavelengthY=16 * 5.0e6 / 64 * np.sqrt(3) / 2)
+    from omega_b200 import analytic
+    h, u = analytic.manufactured(L, cfg)
+    tr = np.ascontiguousarray(analytic.planar_state(L, 1)[2])
+    tr[0, :-1] = 2.0 + np.cos(2 * np.pi * L.XCell[:-1, None] / float(L.Lx))
+    for fused in (True, False):
+        errs = run_steps(L, cfg, (h, u, tr), dt, capi.RK4, 5, fused=fused, compat=True)
+        assert max(errs) <= TOL_STATE, (fused, errs)
+
+
+def config1_problem(nx):
+    """BASELINE configs[0]: planar hex nx x nx cells, ONE level, no tracers, the manufactured solution of
+    src/ocn/CustomTendencyTerms.cpp:18-210 with Default.yml's wavelength = domain size (5000 km)."""
+    from omega_b200 import analytic, decomp, meshgen
+    dc = 5.0e6 / nx
+    m = meshgen.planar_hex(nx, nx, dc, f0=1.0e-4, bottom_depth=1000.0)
+    L = decomp.build_all(m, 1, 1)[0]
+    cfg = capi.TendConfig.default(ManufacturedSolutionTendency=1, ManufacturedWavelengthX=float(L.Lx),
+                                  ManufacturedWavelengthY=float(L.Ly), TracerHorzAdvTendencyEnable=0,
+                                  TracerDiffTendencyEnable=0, TracerHyperDiffTendencyEnable=0)
+    h, u = analytic.manufactured(L, cfg)
+    return L, cfg, h, u
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_config1_manufactured_rk4_stepping_and_convergence(fused):
+    """Config 1 as a stepping test on the GPU: RK4 from t = 0 to a quarter period on nx = 16, 32, 64 with
+    dt ~ dc; (a) state against the oracle <= 1e-10, (b) the error against the exact solution converges at
+    second order in space (doc/design/OmegaV0ShallowWater.md:656-666; test/timeStepping/TimeStepperTest.cpp:
+    375-388 is the same rate check for the time discretisation)."""
+    from omega_b200 import analytic
+    t_end, errs_exact = 9600.0, []
+    for nx, dt in ((16, 480.0), (32, 240.0), (64, 120.0)):
+        L, cfg, h, u = config1_problem(nx)
+        tr = np.zeros((0, h.shape[0], 1))
+        n = int(round(t_end / dt))
+        mesh, st, state = gpu_objects(L, cfg, 0)
+        state.copyToDevice(h, u, None)
+        from tests.oracle_lib import Oracle
+        o = Oracle(L, cfg, 0)
+        o.make_state(h, u, tr)
+        for i in range(n):
+            co = capi.rk_coeffs(capi.RK4, dt, t0=i * dt)
+            st.doStep(state, capi.RK4, co, fused=fused, compat=True)
+            o.do_step(capi.RK4, co, compat=1)
+        gh, gu, _ = state.copyToHost(0)
+        eh, eu, _ = o.current()
+        assert rel_l2(gh, eh) <= TOL_STATE and rel_l2(gu, eu) <= TOL_STATE, (nx, rel_l2(gh, eh), rel_l2(gu, eu))
+        xh, xu = analytic.manufactured(L, cfg, t=n * dt)
+        H0 = float(L.BottomDepth[0])
+        errs_exact.append((np.sqrt(np.mean((gh[:-1] - xh[:-1]) ** 2)) / cfg.ManufacturedAmplitude,
+                           np.sqrt(np.mean((gu[:-1] - xu[:-1]) ** 2)) / cfg.ManufacturedAmplitude))
+        assert abs((L.AreaCell[:-1] * (gh[:-1, 0] - H0)).sum()) <= 1e-9 * (L.AreaCell[:-1] * H0).sum()
+        o.close(); st.close(); mesh.close()
+    rates = [np.log2(np.array(errs_exact[i]) / np.array(errs_exact[i + 1])) for i in range(2)]
+    print("config 1 errors (h, u) / eta0:", errs_exact, "rates:", rates)
+    assert all(abs(r - 2.0) <= 0.35 for r in rates[-1]), rates
+
+
+def test_wind_stress_anisotropic_interpolation():
+    """WindStressInterpType = 1 (HorzOperators.h:137-187, anisotropic branch): NormalStressEdge and the
+    velocity tendency against the oracle."""
+    from tests.oracle_lib import Oracle
+    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case()
+    cfg.WindStressInterpType = 1
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T)
+    o = Oracle(L, cfg, T)
+    o.set_wind_stress(zonal, merid)
+    st.set_wind_stress(zonal, merid)
+    o.tend_all(h, u, tr)
+    st.computeAllTendencies(mesh.to_device(capi.ON_CELL, h), mesh.to_device(capi.ON_EDGE, u), mesh.to_device(capi.ON_CELL, tr))
+    aux, tend = st.aux_to_host(("NormalStressEdge",)), st.tend_to_host()
+    assert np.abs(o.aux["NormalStressEdge"]).max() > 0
+    assert rel_max(aux["NormalStressEdge"], o.aux["NormalStressEdge"]) <= TOL_TEND
+    assert rel_max(tend["NormalVelocityTend"], o.tend["NormalVelocityTend"]) <= TOL_TEND
+    # and it differs from the isotropic interpolation, so the switch is live
+    cfg0 = capi.TendConfig.from_buffer_copy(cfg)
+    cfg0.WindStressInterpType = 0
+    o.set_config(cfg0)
+    o.tend_all(h, u, tr)
+    assert rel_max(aux["NormalStressEdge"], o.aux["NormalStressEdge"]) > 1e-6
+    o.close(); st.close(); mesh.close()
 
 
 def test_tiled_and_untiled_fused_paths_agree(monkeypatch):
