@@ -251,6 +251,7 @@ def main():
     state.copyToDevice(h, u, tr if T else None)
     if world > 1:
         halo = parallel.HaloExchanger(mesh, halo_desc, T)
+        halo.init_comm(world, rank)      # NCCL communicator of the library; torch.distributed only carries the id
 
     fused = not args.unfused
 
@@ -271,6 +272,8 @@ def main():
     barrier()
     n0 = st.launch_count()
     st.lib.omega_stepper_set_profiling(st.h, 1 if fused else 0)
+    if halo is not None:
+        halo.set_profiling(True)
     sampler = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -285,10 +288,14 @@ def main():
     kms, kcnt = (C.c_double * 5)(), (C.c_int * 5)()
     st.lib.omega_stepper_get_profile(st.h, kms, kcnt, 5)
     st.lib.omega_stepper_set_profiling(st.h, 0)
+    halo_prof = None
     if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        hms, hrounds, hbytes = halo.profile()     # CUDA events around pack .. unpack on the exchange stream
+        halo.set_profiling(False)
+        t = torch.tensor([ms, hms / max(hrounds, 1), float(hbytes) / max(hrounds, 1)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = float(t[0].item())
+        halo_prof = (float(t[1].item()), float(t[2].item()), halo.tile_classes())
     # sanity: the state must still be finite after W + K steps
     hh = state.getLayerThickness(0)
     assert bool(torch.isfinite(hh).all()), "state blew up"
@@ -423,8 +430,17 @@ def main():
             "kernels": kern}
     if world > 1:
         # two exchange rounds per RK4 step; bytes one rank sends per round, against NVLink 900 GB/s/direction
+        hms, hb, (nb, nown, ntl) = halo_prof
+        # bytes one rank moves per round (sent + received) / time of the round (pack .. unpack, device events,
+        # max over ranks) against NVLink: 900 GB/s nominal per direction, i.e. send and receive each at most that
+        gbs = hb / 2 / (hms * 1e-3) / 1e9 if hms > 0 else None
         line["halo"] = {"rounds_per_step": 2, "send_bytes_per_round_rank0": bytes_round, "halo_width": 4,
-                        "transport": "NCCL send/recv (torch.distributed batch_isend_irecv), pack/unpack CUDA kernels"}
+                        "ms_per_round": hms, "bytes_per_round_max_rank": hb,
+                        "achieved_gbs_per_direction": gbs, "frac_of_nvlink_900": gbs / 900.0 if gbs else None,
+                        "tiles_rank0": {"boundary": nb, "owned": nown, "all": ntl},
+                        "transport": "library: one pack kernel + grouped ncclSend/ncclRecv + one unpack kernel per round "
+                                     "(csrc/halo.cu), on its own stream behind the boundary tiles, overlapped with the "
+                                     "interior tiles"}
     if world == 1 and not args.no_cpu_baseline:
         cb, *_ = cpu_reference_rate(args.workload, 2, 1, full_depth=False)
         line["cpu_baseline"] = cb

@@ -134,6 +134,7 @@ int omega_b200_abi_version(void);
 /* ---- device memory (replaces Kokkos View allocation, zero-initialised) -- */
 int omega_dev_alloc(void **ptr, unsigned long long bytes);
 int omega_dev_free(void *ptr);
+int omega_dev_copy(void *dst, const void *src, unsigned long long bytes, void *stream); /* device to device, async */
 int omega_dev_sync(void *stream);
 
 /* ---- HorzMesh (src/ocn/HorzMesh.cpp:49-150,527-647) ---------------------- */
@@ -215,7 +216,12 @@ int omega_tend_all(OmegaStepper *S, const double *LayerThickCell,
  * Fused=0 the kernel-per-term path that fills every public array.
  * RawTimeLevelCompat=1 reproduces the reference's raw time-level indexing
  * (SURVEY.md 3.5 P1); 0 maps every level through the ring.
- * Halo may be NULL on a single rank. */
+ * Halo may be NULL on a single rank; with a Halo (communicator initialised) the step runs its
+ * exchange rounds itself, overlapped with the interior tiles on the fused tiled path.
+ * Fused=1 has no place for a host custom-tendency std::function (src/ocn/Tendencies.h:51-53,
+ * Tendencies.cpp:288-293,416-421): the built-in manufactured terms are the only custom terms the fused
+ * kernels evaluate; a host that installs its own must step with Fused=0 through
+ * omega_tend_* + its callback. */
 int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,
                           const OmegaStepCoeffs *Coeffs, OmegaHalo *Halo, int Fused,
                           int RawTimeLevelCompat, void *Stream);
@@ -229,6 +235,12 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
 int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type,
                                 const OmegaStateArrays *State, int Phase, double **Ptrs,
                                 int *Elems, int *NOuter, int *NArrays);
+/* Attach the rank's Halo to the stepper (do_step with a Halo does this itself).  The fused tiled path then
+ * (a) skips the halo tiles in the stages whose results the following exchange overwrites (RK4 stages 1
+ * and 3: every local non-owned cell / edge is in a receive list) and (b) launches the tiles that hold
+ * send-list rows first, so the exchange overlaps the interior tiles.  Callers of step_phase that run
+ * the exchange themselves may attach too; they must exchange after every phase. */
+int omega_stepper_attach_halo(OmegaStepper *S, OmegaHalo *Halo);
 /* OceanState::updateTimeLevels + Tracers::updateTimeLevels minus the exchange:
  * advance both ring indices (src/ocn/OceanState.cpp:348-365). */
 int omega_state_rotate(OmegaStateArrays *State);
@@ -238,7 +250,8 @@ int omega_stepper_provis_arrays(OmegaStepper *Stepper, double **H, double **U, d
 long long omega_stepper_launch_count(const OmegaStepper *S);
 /* which kernels the last omega_stepper_step_phase / do_step ran: OMEGA_PATH_* bits (0 = the
  * kernel-per-term path).  Tests assert through this that a case exercised the tiled kernels. */
-enum { OMEGA_PATH_FUSED = 1, OMEGA_PATH_TILED_CELL = 2, OMEGA_PATH_CELL_V2 = 4, OMEGA_PATH_TILED_EDGE = 8 };
+enum { OMEGA_PATH_FUSED = 1, OMEGA_PATH_TILED_CELL = 2, OMEGA_PATH_CELL_V2 = 4, OMEGA_PATH_TILED_EDGE = 8,
+       OMEGA_PATH_HALO_SPLIT = 16 /* boundary tiles first, halo tiles skipped (attached halo) */ };
 int omega_stepper_last_path(const OmegaStepper *S);
 /* per-kernel CUDA-event timing of the fused pipeline: sums in ms and launch
  * counts per kernel kind (0 fA, 1 fB, 2 fT2, 3 fC, 4 fE) since the last call;
@@ -258,18 +271,49 @@ typedef struct OmegaHaloDesc {
 } OmegaHaloDesc;
 int omega_halo_create(const OmegaMesh *Mesh, const OmegaHaloDesc *Desc, OmegaHalo **Halo);
 int omega_halo_destroy(OmegaHalo *Halo);
-/* Halo::exchangeFullArrayHalo split into its two device halves so the
- * transport (NCCL send/recv, peer copies, or an in-process loop) stays with
- * the caller: pack gathers [NOuter][elem][NInner] rows of every neighbour's
- * send list into one contiguous buffer per neighbour (Halo.h:304-502 buffer
- * order); unpack scatters a received buffer into the halo rows
- * (Halo.h:545-760). Counts are in doubles. */
+
+/* Transport: NCCL send/recv over NVLink, one rank per GPU, loaded at run time (libnccl.so.2).
+ * The host creates the id on one rank, broadcasts its 128 bytes with whatever it has (MPI_Bcast in
+ * Omega, where MachEnv owns the MPI communicator: src/base/MachEnv.h; torch.distributed in the
+ * Python mirror) and every rank calls comm_init with Rank == OmegaHaloDesc.MyTask.  A host that
+ * already owns an ncclComm_t over the same ranks hands it in with set_comm instead. */
+int omega_halo_nccl_unique_id(char *Id128);
+int omega_halo_comm_init(OmegaHalo *Halo, const char *Id128, int NRanks, int Rank);
+int omega_halo_set_comm(OmegaHalo *Halo, void *NcclComm, int NRanks);
+
+/* Halo::exchangeFullArrayHalo(Array, Elem) (src/base/Halo.h:768-915): the whole exchange of one
+ * array [NOuter][N*Size][NVertLayers] (device order) on Stream: pack kernel, grouped ncclSend /
+ * ncclRecv with every neighbour, unpack kernel.  Nothing synchronises the host. */
+int omega_halo_exchange(OmegaHalo *Halo, double *Array, OmegaMeshElement Elem, int NOuter, void *Stream);
+/* One exchange ROUND: up to three arrays (h, u, tracers of one exchange point of the stepper) in ONE
+ * pack launch, ONE message per neighbour, ONE unpack launch.  Buffers are owned by the Halo. */
+int omega_halo_exchange_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
+                              int NArrays, void *Stream);
+/* The two device halves of a round for callers that own the transport (peer copies, an in-process
+ * N-rank emulation): pack_round fills the Halo's send buffer (returned; neighbour n's message is the
+ * concatenation of its per-array buffers, each [outer][exchange index][level], Halo.h:304-502, and
+ * messages follow each other in neighbour order; round_counts gives their sizes in doubles);
+ * recv_buffer returns the buffer unpack_round scatters from, laid out the same way. */
+int omega_halo_round_counts(const OmegaHalo *Halo, const int *Elems, const int *NOuter, int NArrays,
+                            long long *SendCounts, long long *RecvCounts);
+int omega_halo_pack_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
+                          int NArrays, double **SendBuf, void *Stream);
+int omega_halo_recv_buffer(OmegaHalo *Halo, const int *Elems, const int *NOuter, int NArrays, double **RecvBuf);
+int omega_halo_unpack_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
+                            int NArrays, void *Stream);
+/* Per-array device halves with caller-owned buffers (Halo.h:304-502 buffer order; counts in doubles). */
 int omega_halo_buffer_counts(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter,
                              int NInner, long long *SendCounts, long long *RecvCounts);
 int omega_halo_pack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
                     const double *Array, double *SendBuf, void *Stream);
 int omega_halo_unpack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
                       const double *RecvBuf, double *Array, void *Stream);
+/* Tile classes used for the overlap: tiles with send-list rows, owned tiles, all tiles. */
+int omega_halo_tile_classes(const OmegaHalo *Halo, int *NBoundary, int *NOwned, int *NTiles);
+/* CUDA-event timing of the exchange rounds since the last call (pack .. unpack on the exchange
+ * stream): total ms, rounds, bytes sent + received; get_profile synchronises the device. */
+int omega_halo_set_profiling(OmegaHalo *Halo, int Enable);
+int omega_halo_get_profile(OmegaHalo *Halo, double *Ms, long long *Rounds, long long *Bytes);
 
 #ifdef __cplusplus
 }

@@ -29,6 +29,7 @@
 #include <cstdlib>
 
 #include "fused_args.h"
+#include "halo.h"
 #include "kernel_util.cuh"
 #include "omega_dev.h"
 #include "stepper.h"
@@ -933,11 +934,22 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.MS = manufactured(S, C->StageTime[s]);
       S->LastPath = OMEGA_PATH_FUSED | (tiled ? OMEGA_PATH_TILED_CELL : 0) | (tiled && tile_v2_used(ca) ? OMEGA_PATH_CELL_V2 : 0) |
                     (tiledE ? OMEGA_PATH_TILED_EDGE : 0);
+      // With a halo attached (multi-rank): the stages right before an exchange (1 and 3) need results on
+      // owned elements only -- the exchange overwrites every other row -- so the halo tiles are skipped,
+      // and the tiles that hold send-list rows run first: once they are done the exchange starts on the
+      // halo's own stream (step.cu) while the interior tiles below still compute.
+      const OmegaHalo *Hl = S->Halo;
+      const bool split = Hl && Hl->DTileOrder && Hl->HaloCovered && tiled && tiledE && (s == 1 || s == 3) &&
+                         env_int("OMEGA_HALO_OVERLAP", 1);
+      const TileRange trAll = all_tiles(D);
+      const TileRange trBnd = split ? TileRange{Hl->DTileOrder, 0, Hl->NTilesBoundary} : trAll;
+      const TileRange trInt = split ? TileRange{Hl->DTileOrder, Hl->NTilesBoundary, Hl->NTilesOwned - Hl->NTilesBoundary} : trAll;
+      if (split) S->LastPath |= OMEGA_PATH_HALO_SPLIT;
       {
       ScopedTimer tm_(S, St, kFC);
       const int variant = env_int("OMEGA_FC_VARIANT", 3);
       if (tiled) {
-         if (launch_fCT(D, ca, St)) return 1;
+         if (launch_fCT(D, ca, St, trBnd)) return 1;
       } else if (upw) {
          if (V == 2) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca);
       } else if (V == 1) {
@@ -964,16 +976,16 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
       ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
       ea.G = G; ea.MS = ca.MS;
+      EdgeTileArgs ta;
       if (tiledE) {
          ScopedTimer tm_(S, St, kFE);
-         EdgeTileArgs ta;
          ta.Us = Us; ta.Hs = Hs; ta.PVv = S->A.NormRelVort; ta.X = S->A.KE;
          ta.Y = vel4 ? S->A.Del2Div : S->A.Div; ta.Z = vel4 ? S->A.Del2RelVort : S->A.RelVort;
          ta.SY = vel4 ? 1.0 : nu2; ta.SZ = ta.SY;
          ta.Ucur = Ucur; ta.Unext = Unext; ta.Uprov = Up;
          ta.A = ca.A; ta.B = ca.B; ta.First = ca.First; ta.Last = ca.Last;
          ta.PVOn = G.PVTendencyEnable; ta.XOn = xOn && !wMerge;
-         if (launch_fET(D, ta, St)) return 1;
+         if (launch_fET(D, ta, St, trBnd)) return 1;
          ++S->Launches;
       } else {
          // occupancy variants measured on B200 (profiles/r01): 4 CTAs/SM (64 regs, some spills) is fastest
@@ -984,6 +996,21 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
          else if (fev == 3) k_fE<2, 4><<<ge, kBlock, 0, St>>>(D, ea);
          else k_fE<2, 2><<<ge, kBlock, 0, St>>>(D, ea);
          ++S->Launches;
+      }
+      if (split) {
+         // boundary tiles of both passes are queued: the exchange may start behind them
+         OMEGA_CUDA_CHECK(cudaEventRecord(Hl->EvReady, St));
+         S->SplitRecorded = 1;
+         {
+            ScopedTimer tm_(S, St, kFC);
+            if (launch_fCT(D, ca, St, trInt)) return 1;
+            ++S->Launches;
+         }
+         {
+            ScopedTimer tm_(S, St, kFE);
+            if (launch_fET(D, ta, St, trInt)) return 1;
+            ++S->Launches;
+         }
       }
 #undef LAUNCH_V
    }

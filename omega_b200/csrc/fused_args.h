@@ -45,12 +45,20 @@ struct EdgeTileArgs {
    int First, Last, PVOn, XOn;
 };
 
+// tiles Map[First .. First + Count) of the mesh (Map == nullptr: tiles First .. First + Count)
+struct TileRange {
+   const int *Map;
+   int First, Count;
+   __host__ __device__ int tile(int i) const { return Map ? Map[First + i] : First + i; }
+};
+inline TileRange all_tiles(const DMesh &D) { return TileRange{nullptr, 0, D.Tiles.NTiles}; }
+
 // fused_tile.cu
 bool tile_path_ok(const DMesh &D);
 bool tile_v2_enabled(); // k_fCT2 (any tracer count with tracer hyperdiffusion) is selectable
 bool tile_v2_used(const CellArgs &ca); // launch_fCT will run k_fCT2 for these arguments
 bool tile_edge_path_ok(const DMesh &D);
-int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St);
-int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St);
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR);
+int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR);
 
 } // namespace omega

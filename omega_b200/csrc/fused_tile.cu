@@ -498,14 +498,14 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
 
 template <bool HYP, int STAGE, int RS = 0>
 __global__ void __launch_bounds__(HYP ? 2 * kTRole : kTRole, 1)
-k_fCT(DMesh M, CellArgs P, int NChunks) {
+k_fCT(DMesh M, CellArgs P, int NChunks, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    TileSmem &S = *reinterpret_cast<TileSmem *>(smem_raw);
    constexpr int NT = HYP ? 2 * kTRole : kTRole;
    const int tid = threadIdx.x;
    // NChunks > 0: one CTA per (tile, level chunk); NChunks < 0: one CTA per tile walking -NChunks chunks
    const int NChunksPerCta = NChunks > 0 ? 1 : -NChunks;
-   const int tile = NChunks > 0 ? blockIdx.x / NChunks : blockIdx.x, kc0 = NChunks > 0 ? (blockIdx.x % NChunks) * kTKC : 0;
+   const int tile = TR.tile(NChunks > 0 ? blockIdx.x / NChunks : blockIdx.x), kc0 = NChunks > 0 ? (blockIdx.x % NChunks) * kTKC : 0;
 
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
@@ -977,7 +977,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
 
 template <class C, int STAGE>
 __global__ void __launch_bounds__(C::NT, C::CTAs)
-k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole) {
+k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    typename C::Smem &S = *reinterpret_cast<typename C::Smem *>(smem_raw);
    // CTAs below NWhole take a whole tile (all NChAll chunks); the tiles of the last, partial round of
@@ -990,6 +990,7 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole) {
       kb   = (q % NChAll) * C::KC;
       NCh  = 1;
    }
+   tile = TR.tile(tile);
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
    if (C::BULK && tid == 32) {
@@ -1014,7 +1015,7 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole) {
    }
 }
 
-template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    static DevOnce once;
    int sm = 0;
    if (set_smem_once(once, k_fCT2<C, STAGE>, sizeof(typename C::Smem), &sm)) return 1;
@@ -1022,27 +1023,28 @@ template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const Cel
    // one CTA per tile; the tiles of the last partial round of CTAs are split into one CTA per chunk when
    // that shortens the tail (matters on multi-GPU partitions with ~10 rounds)
    const int split = env_i("OMEGA_TILE_SPLIT", 1);
-   const int nch = D.K / C::KC, nt = D.Tiles.NTiles;
+   const int nch = D.K / C::KC, nt = TR.Count;
+   if (nt <= 0) return 0;
    int whole = nt;
    if (split && nch > 1) {
       const int tail = nt % sm;
       const double cost = ((tail * nch + sm - 1) / sm) * 1.15 / nch; // rounds, a single-chunk CTA costs ~15 % more per chunk
       if (tail > 0 && cost < 0.85) whole = nt - tail;
    }
-   k_fCT2<C, STAGE><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole);
+   k_fCT2<C, STAGE><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR);
    return 0;
 }
-template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
    // R-role width (OMEGA_TILE_RS = 0, 2, 3) and bulk row copies (OMEGA_TILE_CP = 1).  The 8-level shape
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
    const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0);
-   if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St);
-   return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St);
+   if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St, TR);
+   return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St, TR) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St, TR) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St, TR);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
 
-template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    static DevOnce once;
    if (set_smem_once(once, k_fCT<HYP, STAGE, RS>, sizeof(TileSmem))) return 1;
    OMEGA_REQUIRE(!HYP || ca.NTracers >= 2, "k_fCT with tracer hyperdiffusion needs at least two tracers");
@@ -1050,24 +1052,25 @@ template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, c
    // with the D role (which needs two tracers to prime its pipeline) a CTA walks all chunks of its tile
    const int persist = env_i("OMEGA_TILE_PERSIST", 1);
    const bool walk = HYP && persist;
-   const unsigned grid = (unsigned)D.Tiles.NTiles * (walk ? 1 : nch);
-   k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, walk ? -nch : nch);
+   if (TR.Count <= 0) return 0;
+   const unsigned grid = (unsigned)TR.Count * (walk ? 1 : nch);
+   k_fCT<HYP, STAGE, RS><<<grid, HYP ? 2 * kTRole : kTRole, sizeof(TileSmem), St>>>(D, ca, walk ? -nch : nch, TR);
    return 0;
 }
-template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+template <bool HYP, int STAGE> static int launch_fCT_t(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    const int rs = env_i("OMEGA_TILE_REGS", 0);
-   if (HYP && rs == 1) return launch_fCT_r<HYP, STAGE, HYP ? 1 : 0>(D, ca, St);
-   if (HYP && rs == 2) return launch_fCT_r<HYP, STAGE, HYP ? 2 : 0>(D, ca, St);
-   return launch_fCT_r<HYP, STAGE, 0>(D, ca, St);
+   if (HYP && rs == 1) return launch_fCT_r<HYP, STAGE, HYP ? 1 : 0>(D, ca, St, TR);
+   if (HYP && rs == 2) return launch_fCT_r<HYP, STAGE, HYP ? 2 : 0>(D, ca, St, TR);
+   return launch_fCT_r<HYP, STAGE, 0>(D, ca, St, TR);
 }
 
-int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St) {
+int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    OMEGA_REQUIRE(!(ca.First && ca.Last), "launch_fCT: a stage cannot be both first and last");
    const int stage = ca.First ? 0 : (ca.Last ? 2 : 1);
    if (tile_v2_used(ca))
-      return stage == 0 ? launch_fCT2_t<0>(D, ca, St) : stage == 1 ? launch_fCT2_t<1>(D, ca, St) : launch_fCT2_t<2>(D, ca, St);
-   if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St) : launch_fCT_t<true, 2>(D, ca, St);
-   return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St) : launch_fCT_t<false, 2>(D, ca, St);
+      return stage == 0 ? launch_fCT2_t<0>(D, ca, St, TR) : stage == 1 ? launch_fCT2_t<1>(D, ca, St, TR) : launch_fCT2_t<2>(D, ca, St, TR);
+   if (ca.HypOn) return stage == 0 ? launch_fCT_t<true, 0>(D, ca, St, TR) : stage == 1 ? launch_fCT_t<true, 1>(D, ca, St, TR) : launch_fCT_t<true, 2>(D, ca, St, TR);
+   return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St, TR) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St, TR) : launch_fCT_t<false, 2>(D, ca, St, TR);
 }
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
@@ -1100,11 +1103,12 @@ struct ETileSmem {
 };
 
 __global__ void __launch_bounds__(kEThreads, 2)
-k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead) {
+k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    ETileSmem &S = *reinterpret_cast<ETileSmem *>(smem_raw);
    const int tid = threadIdx.x;
-   const int tile = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
+   const int tix = blockIdx.x / NChunks, kc0 = (blockIdx.x % NChunks) * kTKC;
+   const int tile = TR.tile(tix);
    const int K = M.K;
    if (tid < (int)(sizeof(TileHdr) / sizeof(int)))
       reinterpret_cast<int *>(&S.Hdr)[tid] = reinterpret_cast<const int *>(M.Tiles.Hdr + tile)[tid];
@@ -1121,12 +1125,12 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead) {
    }
    __syncthreads();
    const int p = tid & 7, k = kc0 + 2 * p;
-   if ((Pf & 2) && tile + Ahead < M.Tiles.NTiles) {
+   if ((Pf & 2) && tix + Ahead < TR.Count) {
       // Cross-CTA software pipelining through L2: the pass-1 rows (u, h of both cells, PV of both vertices of
       // every staged edge) of the tile-chunk that a CTA of the NEXT wave will work on are requested now, so
       // that CTA finds them in L2 (~250 cycles) instead of in DRAM (~700): the kernel is bound by the latency
       // of exactly these gathers (ncu: long_scoreboard at the first use of pass 1).
-      const TileHdr *Hn = M.Tiles.Hdr + tile + Ahead;
+      const TileHdr *Hn = M.Tiles.Hdr + TR.tile(tix + Ahead);
       const int nS2 = Hn->NEStaged, off2 = Hn->ERowOff;
       if (p < 5)
          for (int r = tid >> 3; r < nS2; r += kEThreads / kTLanes) {
@@ -1269,15 +1273,17 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead) {
    }
 }
 
-int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St) {
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR) {
+   if (TR.Count <= 0) return 0;
    static DevOnce once;
    int sm = 0;
    if (set_smem_once(once, k_fET, sizeof(ETileSmem), &sm)) return 1;
    const int nch = D.K / kTKC;
-   // bit 0: own pass-2a rows, bit 1: pass-1 rows of the tile a CTA of the next wave takes (2 CTAs per SM)
-   const int pf = env_i("OMEGA_TILE_EPF", 3);
+   // bit 0: own pass-2a rows; bit 1: pass-1 rows of the tile a CTA of the next wave takes (measured on
+   // config 3 and rejected: 2.36 -> 2.85 ms, the extra requests cost more than the latency they hide)
+   const int pf = env_i("OMEGA_TILE_EPF", 1);
    const int ahead = env_i("OMEGA_TILE_EAHEAD", (2 * sm + nch - 1) / nch);
-   k_fET<<<(unsigned)D.Tiles.NTiles * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead);
+   k_fET<<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
    return 0;
 }
 

@@ -316,6 +316,17 @@ static int build_tiles(OmegaMesh *M, int NC, int NOwned, int ME, const std::vect
    rc |= to_device(M, eoel, &T.EoELocal);
    T.EdgeTilesOK = edgeOK && !rc;
    T.NTiles = rc ? 0 : (int)hdr.size();
+   if (T.NTiles) {
+      M->TileC0.resize(hdr.size());
+      M->TileOfCell.assign(NC + 1, -1);
+      M->TileOfEdge.assign(NE + 1, -1);
+      for (size_t t = 0; t < hdr.size(); ++t) {
+         M->TileC0[t] = hdr[t].C0;
+         for (int i = 0; i < hdr[t].NC; ++i) M->TileOfCell[hdr[t].C0 + i] = (int)t;
+         if (edgeOK)
+            for (int i = 0; i < hdr[t].NEOwn; ++i) M->TileOfEdge[erows[hdr[t].ERowOff + i]] = (int)t;
+      }
+   }
    if (getenv("OMEGA_DEBUG")) {
       int mxS = 0, mxO = 0, small = 0;
       long long sumS = 0;
@@ -345,6 +356,10 @@ int omega_dev_alloc(void **ptr, unsigned long long bytes) {
 }
 int omega_dev_free(void *ptr) {
    OMEGA_CUDA_CHECK(cudaFree(ptr));
+   return 0;
+}
+int omega_dev_copy(void *dst, const void *src, unsigned long long bytes, void *stream) {
+   if (bytes) OMEGA_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
    return 0;
 }
 int omega_dev_sync(void *stream) {

@@ -127,6 +127,9 @@ struct OmegaMesh {
    // device permutation tables for field transfers
    int *DPerm[3], *DIPerm[3];
    std::vector<void *> Allocs; // every device allocation owned by the mesh
+   // host view of the tiles (device order): first own cell of every tile, tile of a cell, tile whose OWN edge
+   // list holds an edge (-1: none); omega_halo_create classifies tiles with these
+   std::vector<int> TileC0, TileOfCell, TileOfEdge;
 };
 
 namespace omega {

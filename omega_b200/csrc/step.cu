@@ -4,6 +4,7 @@
 // Reference: components/omega/src/timeStepping/RungeKutta4Stepper.cpp:68-137,
 // RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:27-82,
 // TimeStepper.cpp:378-524; time-level ring: src/ocn/OceanState.cpp:394-407.
+#include "halo.h"
 #include "omega_dev.h"
 #include "stepper.h"
 
@@ -128,6 +129,7 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
    Ctx X{S, (cudaStream_t)Stream, RawTimeLevelCompat};
    int rc;
    S->LastPath = 0;
+   S->SplitRecorded = 0;
    if (Type == OMEGA_STEPPER_RK4 && Fused)
       rc = fused_rk4_phase(S, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
    else if (Type == OMEGA_STEPPER_RK4)
@@ -169,15 +171,39 @@ int omega_state_rotate(OmegaStateArrays *X) {
    return 0;
 }
 
+// TimeStepper::doStep.  With a Halo the step includes its halo exchanges (RungeKutta4Stepper.cpp:108-114,
+// 130-131; OceanState::updateTimeLevels / Tracers::updateTimeLevels, OceanState.cpp:348-365): after phase p
+// the arrays of omega_stepper_exchange_list go through ONE exchange round (halo.cu).  When the fused tiled
+// kernels ran the phase's last stage boundary-tiles-first, the round runs on the halo's own high-priority
+// stream behind the boundary tiles, concurrently with the interior tiles, and Stream waits for it before
+// the next phase; otherwise it runs in order on Stream.
 int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,
                           const OmegaStepCoeffs *Coeffs, OmegaHalo *Halo, int Fused, int RawTimeLevelCompat,
                           void *Stream) {
-   OMEGA_REQUIRE(Halo == nullptr,
-                 "omega_stepper_do_step: with a Halo the transport belongs to the caller; drive "
-                 "omega_stepper_step_phase / omega_halo_pack / omega_halo_unpack instead");
+   OMEGA_REQUIRE(S && State && Coeffs, "omega_stepper_do_step: null argument");
+   cudaStream_t St = (cudaStream_t)Stream;
+   if (Halo) {
+      OMEGA_REQUIRE(Halo->M == S->M, "omega_stepper_do_step: the Halo belongs to another mesh");
+      S->Halo = Halo;
+   }
    for (int p = 0; p < n_phases(Type); ++p) {
       int rc = omega_stepper_step_phase(S, Type, State, Coeffs, p, Fused, RawTimeLevelCompat, Stream);
       if (rc) return rc;
+      if (!Halo) continue;
+      double *ptrs[3];
+      int elems[3], nouter[3], n = 0;
+      rc = omega_stepper_exchange_list(S, Type, State, p, ptrs, elems, nouter, &n);
+      if (rc) return rc;
+      if (S->SplitRecorded) {
+         OMEGA_CUDA_CHECK(cudaStreamWaitEvent(Halo->CommStream, Halo->EvReady, 0));
+         rc = halo_exchange_round(Halo, ptrs, elems, nouter, n, Halo->CommStream);
+         if (rc) return rc;
+         OMEGA_CUDA_CHECK(cudaEventRecord(Halo->EvDone, Halo->CommStream));
+         OMEGA_CUDA_CHECK(cudaStreamWaitEvent(St, Halo->EvDone, 0));
+      } else {
+         rc = halo_exchange_round(Halo, ptrs, elems, nouter, n, St);
+         if (rc) return rc;
+      }
    }
    return omega_state_rotate(State);
 }

@@ -63,6 +63,8 @@ int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int 
    S->Launches = 0;
    S->ProvisExchangeSlot = 0;
    S->LastPath = 0;
+   S->Halo = nullptr;
+   S->SplitRecorded = 0;
    S->Profiling = 0;
    std::memset(&S->A, 0, sizeof(S->A));
    std::memset(&S->T, 0, sizeof(S->T));
@@ -156,6 +158,12 @@ int omega_stepper_set_wind_stress(OmegaStepper *S, const double *Zonal, const do
 
 long long omega_stepper_launch_count(const OmegaStepper *S) { return S ? S->Launches : 0; }
 int omega_stepper_last_path(const OmegaStepper *S) { return S ? S->LastPath : 0; }
+
+int omega_stepper_attach_halo(OmegaStepper *S, OmegaHalo *Halo) {
+   OMEGA_REQUIRE(S, "omega_stepper_attach_halo: null stepper");
+   S->Halo = Halo;
+   return 0;
+}
 
 int omega_stepper_set_profiling(OmegaStepper *S, int Enable) {
    OMEGA_REQUIRE(S, "omega_stepper_set_profiling: null argument");

@@ -4,6 +4,8 @@
 #pragma once
 #include "omega_dev.h"
 
+struct OmegaHalo;
+
 struct ProvisArrays {
    double *H[2], *U[2], *Tr[2];
 };
@@ -19,6 +21,8 @@ struct OmegaStepper {
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
    int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
+   struct OmegaHalo *Halo; // attached halo (omega_stepper_attach_halo): boundary tiles first, halo tiles skipped
+   int SplitRecorded;      // the last phase recorded Halo->EvReady after its boundary tiles
    std::vector<void *> Allocs;
    // optional per-kernel CUDA-event timing of the fused pipeline (bench roofline)
    int Profiling;

@@ -94,17 +94,15 @@ class HorzMesh {
    }
 };
 
-/// Halo: exchange lists on device; the transport (NCCL, peer copies) is supplied
-/// by the caller as a callback over the packed per-neighbour buffers.
+/// Halo: exchange lists on device and the exchange itself (src/base/Halo.h:62-917): pack kernel,
+/// NCCL send/recv with every neighbour, unpack kernel, all inside the library.  The host only
+/// bootstraps the communicator: one rank calls uniqueId(), the 128 bytes travel by the host's own
+/// means (MPI_Bcast over MachEnv's communicator in Omega) and every rank calls initComm().
 class Halo {
  public:
-   using Transport = int (*)(void *User, int NNeighbors, const int *Tasks, const double *SendBuf,
-                             const long long *SendCounts, double *RecvBuf, const long long *RecvCounts, void *Stream);
    OmegaHalo *Handle = nullptr;
    const HorzMesh *Mesh;
    std::vector<int> Neighbors;
-   Transport Xfer = nullptr;
-   void *XferUser = nullptr;
 
    Halo(const HorzMesh *M, const OmegaHaloDesc &D) : Mesh(M), Neighbors(D.NeighborTasks, D.NeighborTasks + D.NNeighbors) {
       OMEGA_B200_CHECK(omega_halo_create(M->Handle, &D, &Handle), "Halo: omega_halo_create");
@@ -112,23 +110,18 @@ class Halo {
    ~Halo() { omega_halo_destroy(Handle); }
    Halo(const Halo &) = delete;
 
+   static void uniqueId(char (&Id)[128]) { OMEGA_B200_CHECK(omega_halo_nccl_unique_id(Id), "Halo: omega_halo_nccl_unique_id"); }
+   void initComm(const char (&Id)[128], int NRanks, int Rank) {
+      OMEGA_B200_CHECK(omega_halo_comm_init(Handle, Id, NRanks, Rank), "Halo: omega_halo_comm_init");
+   }
+
    /// Halo::exchangeFullArrayHalo(Array, Elem), src/base/Halo.h:768-915.  The
    /// element dimension is second to last, as upstream.
    template <int Rank> int exchangeFullArrayHalo(DeviceArray<Rank> &Array, MeshElement Elem, void *Stream = nullptr) {
       static_assert(Rank == 2 || Rank == 3, "state arrays are [elem][level] or [tracer][elem][level]");
-      const int NOuter = Rank == 3 ? Array.extent_int(0) : 1, NInner = Array.extent_int(Rank - 1);
-      const int NN = (int)Neighbors.size();
-      if (NN == 0) return 0;
-      std::vector<long long> SC(NN), RC(NN);
-      if (omega_halo_buffer_counts(Handle, (OmegaMeshElement)Elem, NOuter, NInner, SC.data(), RC.data())) return -1;
-      long long ST = 0, RT = 0;
-      for (int i = 0; i < NN; ++i) { ST += SC[i]; RT += RC[i]; }
-      DeviceArray<1> SendBuf("HaloSend", {ST}), RecvBuf("HaloRecv", {RT});
-      if (omega_halo_pack(Handle, (OmegaMeshElement)Elem, NOuter, NInner, Array.data(), SendBuf.data(), Stream)) return -1;
-      if (!Xfer) return -2; // no transport installed
-      if (Xfer(XferUser, NN, Neighbors.data(), SendBuf.data(), SC.data(), RecvBuf.data(), RC.data(), Stream)) return -1;
-      if (omega_halo_unpack(Handle, (OmegaMeshElement)Elem, NOuter, NInner, RecvBuf.data(), Array.data(), Stream)) return -1;
-      return 0;
+      const int NOuter = Rank == 3 ? Array.extent_int(0) : 1;
+      if (Neighbors.empty()) return 0;
+      return omega_halo_exchange(Handle, Array.data(), (OmegaMeshElement)Elem, NOuter, Stream) ? -1 : 0;
    }
 };
 

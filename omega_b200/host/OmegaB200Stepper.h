@@ -3,6 +3,7 @@
 // objects; their public array members alias the library-owned device arrays
 // (src/ocn/AuxiliaryState.h:37-42, src/ocn/Tendencies.h:55-57).
 #pragma once
+#include <cmath>
 #include "OmegaB200.h"
 
 namespace OMEGA {
@@ -122,23 +123,44 @@ class TimeStepper {
    TimeStepper(TimeStepperType T, double Dt, Tendencies *Td, AuxiliaryState *Ax, Tracers *Trc) : Type(T), Tend(Td), AuxState(Ax), Tr(Trc) {
       setTimeStep(Dt);
    }
-   /// dt an integer number of seconds: b*dt for RKB = 1/6, 1/3 evaluated as Whole + Numer/Denom
+   /// Stage coefficients in seconds the way the reference forms them: RKB[s] * TimeStep in exact rational
+   /// arithmetic, evaluated as Whole + Numer/Denom (src/infra/TimeMgr.cpp:382-391,747-766).
+   /// Dt is taken as the rational with denominator <= 1e9 closest to it (continued fraction), which is
+   /// exact for every time step written with a few decimals (0.5, 30.5, 0.1 ...), as capi.rk_coeffs does.
+   static void toFraction(double X, long long &Num, long long &Den) {
+      long long p0 = 0, q0 = 1, p1 = 1, q1 = 0;
+      double r = X;
+      for (int it = 0; it < 64; ++it) {
+         const double fl = std::floor(r);
+         const long long a = (long long)fl;
+         const long long p2 = a * p1 + p0, q2 = a * q1 + q0;
+         if (q2 > 1000000000LL) break;
+         p0 = p1; q0 = q1; p1 = p2; q1 = q2;
+         const double f = r - fl;
+         if (f < 1e-15 || (double)p1 / (double)q1 == X) break;
+         r = 1.0 / f;
+      }
+      Num = p1; Den = q1;
+   }
    void setTimeStep(double Dt) {
       Coeffs = OmegaStepCoeffs();
-      Coeffs.Dt = Dt;
-      auto frac = [&](long long num, long long den) { // (num/den)*Dt for integer Dt
-         const long long d = (long long)Dt, n = num * d;
-         const long long whole = n / den, rem = n % den;
+      long long dn, dd;
+      toFraction(Dt, dn, dd);
+      auto frac = [&](long long num, long long den) { // (num/den) * (dn/dd) as Whole + Numer/Denom
+         long long n = num * dn, d = den * dd;
+         long long a = n < 0 ? -n : n, b = d; while (b) { long long t = a % b; a = b; b = t; }
+         if (a > 1) { n /= a; d /= a; }
+         const long long whole = n / d, rem = n % d;
          if (rem == 0) return (double)whole;
-         long long a = rem, b = den; while (b) { long long t = a % b; a = b; b = t; }
-         return (double)whole + (double)(rem / a) / (double)(den / a);
+         return (double)whole + (double)rem / (double)d;
       };
+      Coeffs.Dt = frac(1, 1);
       if (Type == TimeStepperType::RungeKutta4) {
          Coeffs.NStages = 4;
          const long long an[4] = {0, 1, 1, 1}, ad[4] = {1, 2, 2, 1}, bn[4] = {1, 1, 1, 1}, bd[4] = {6, 3, 3, 6};
          for (int s = 0; s < 4; ++s) { Coeffs.A[s] = frac(an[s], ad[s]); Coeffs.B[s] = frac(bn[s], bd[s]); }
       } else if (Type == TimeStepperType::RungeKutta2) {
-         Coeffs.NStages = 2; Coeffs.A[1] = frac(1, 2); Coeffs.B[1] = Dt;
+         Coeffs.NStages = 2; Coeffs.A[1] = frac(1, 2); Coeffs.B[1] = frac(1, 1);
       } else {
          Coeffs.NStages = 1;
       }
@@ -155,32 +177,13 @@ class TimeStepper {
       OmegaStepperType T = Type == TimeStepperType::RungeKutta4 ? OMEGA_STEPPER_RK4
                            : Type == TimeStepperType::RungeKutta2 ? OMEGA_STEPPER_RK2 : OMEGA_STEPPER_FB;
       for (int s = 0; s < 4; ++s) Coeffs.StageTime[s] = SimTime + (T == OMEGA_STEPPER_FB ? (s ? Coeffs.Dt : 0.0) : Coeffs.A[s]);
-      const int NPhases = T == OMEGA_STEPPER_RK4 ? 2 : 1;
-      for (int p = 0; p < NPhases; ++p) {
-         OMEGA_B200_CHECK(omega_stepper_step_phase(AuxState->Handle, T, &X, &Coeffs, p, Fused, RawTimeLevelCompat, Stream), "doStep");
-         if (State->MeshHalo && !State->MeshHalo->Neighbors.empty()) exchange(State, T, &X, p, Stream);
-      }
-      // State->updateTimeLevels(); Tracers::updateTimeLevels(): the exchange of level 1 ran above
-      State->CurTimeIndex = (State->CurTimeIndex + 1) % State->NTimeLevels;
-      Tr->CurTimeIndex    = (Tr->CurTimeIndex + 1) % Tr->NTimeLevels;
+      // the whole step in the library: stage kernels, the halo exchange rounds (overlapped with the
+      // interior tiles) and the rotation of both time-level rings (OceanState / Tracers::updateTimeLevels)
+      OmegaHalo *H = State->MeshHalo && !State->MeshHalo->Neighbors.empty() ? State->MeshHalo->Handle : nullptr;
+      OMEGA_B200_CHECK(omega_stepper_do_step(AuxState->Handle, T, &X, &Coeffs, H, Fused, RawTimeLevelCompat, Stream), "doStep");
+      State->CurTimeIndex = X.CurTimeIndex;
+      Tr->CurTimeIndex    = X.TracerCurTimeIndex;
       SimTime += Coeffs.Dt;
-   }
-
- private:
-   void exchange(OceanState *State, OmegaStepperType T, OmegaStateArrays *X, int Phase, void *Stream) {
-      double *Ptrs[3]; int Elems[3], NOuter[3], N = 0;
-      OMEGA_B200_CHECK(omega_stepper_exchange_list(AuxState->Handle, T, X, Phase, Ptrs, Elems, NOuter, &N), "exchange list");
-      const HorzMesh *M = State->Mesh;
-      for (int i = 0; i < N; ++i) {
-         const long K = State->NVertLayers, R = M->size((MeshElement)Elems[i]);
-         if (NOuter[i] > 1 || i == 2) {
-            Array3DReal A("exch", Ptrs[i], {NOuter[i], R, K});
-            OMEGA_B200_CHECK(State->MeshHalo->exchangeFullArrayHalo(A, (MeshElement)Elems[i], Stream), "halo exchange");
-         } else {
-            Array2DReal A("exch", Ptrs[i], {R, K});
-            OMEGA_B200_CHECK(State->MeshHalo->exchangeFullArrayHalo(A, (MeshElement)Elems[i], Stream), "halo exchange");
-         }
-      }
    }
 };
 

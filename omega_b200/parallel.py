@@ -11,10 +11,10 @@ indices (Loc(i,1)) form the owner's send list in the same order; neighbours
 are the tasks that own my halo elements or need mine, ascending.  Buffer
 order is [outer][exchange index][level] (src/base/Halo.h:304-502).
 
-Transport: torch.distributed P2P (NCCL send/recv over NVLink; gloo on CPU for
-the tests).  Pack / unpack are CUDA kernels of the library
-(omega_halo_pack / omega_halo_unpack); the numpy versions below serve the
-CPU tests and the in-process multi-rank emulation only.
+Transport on the GPU: the library itself (csrc/halo.cu: pack kernel, NCCL
+send/recv over NVLink, unpack kernel, inside omega_stepper_do_step);
+torch.distributed only broadcasts the NCCL unique id.  The numpy versions
+below and the gloo exchanger serve the CPU tests of the host logic.
 """
 from __future__ import annotations
 
@@ -130,8 +130,10 @@ class HostHaloExchanger:
 
 
 class HaloExchanger:
-    """Device halo exchange: pack kernel -> NCCL send/recv -> unpack kernel, one
-    grouped P2P batch per exchange round covering h, u and all tracers."""
+    """Device halo exchange through the library (csrc/halo.cu): one pack launch, one grouped NCCL
+    send/recv per neighbour and one unpack launch per exchange round (h, u and all tracers), run by
+    omega_stepper_do_step itself and overlapped with the interior tiles.  torch.distributed only
+    bootstraps the communicator (broadcast of the NCCL unique id)."""
 
     def __init__(self, mesh, lists, ntracers):
         import torch
@@ -159,57 +161,68 @@ class HaloExchanger:
         if rc:
             raise RuntimeError("omega_halo_create: " + self.lib.omega_last_error().decode())
         K = mesh.K
-        self.bufs = {}
-        for key, e, outer in (("h", 0, 1), ("u", 1, 1), ("tr", 0, max(ntracers, 1))):
-            so, ro = self.counts[e]
-            self.bufs[key] = (torch.empty(int(so[-1]) * outer * K, dtype=torch.float64, device=mesh.device),
-                              torch.empty(int(ro[-1]) * outer * K, dtype=torch.float64, device=mesh.device))
-        self.bytes_per_round = sum(b[0].numel() * 8 for b in self.bufs.values())
+        self.bytes_per_round = 8 * K * (int(self.counts[0][0][-1]) * (1 + ntracers) + int(self.counts[1][0][-1]))
+
+    def _chk(self, rc, what):
+        if rc:
+            raise RuntimeError(what + ": " + self.lib.omega_last_error().decode())
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
 
-    def pack(self, ptrs):
-        K = self.mesh.K
-        for key, e, outer, ptr in ptrs:
-            sb, _ = self.bufs[key]
-            rc = self.lib.omega_halo_pack(self.handle, e, outer, K, ptr, C.c_void_p(sb.data_ptr()), self._stream())
-            assert rc == 0, self.lib.omega_last_error()
+    def init_comm(self, world, rank):
+        """NCCL communicator over the ranks of torch.distributed's default group (one rank per GPU)."""
+        import torch.distributed as dist
+        ident = (C.c_char * 128)()
+        if rank == 0:
+            self._chk(self.lib.omega_halo_nccl_unique_id(ident), "omega_halo_nccl_unique_id")
+        dev = self.mesh.device if dist.get_backend() == "nccl" else "cpu"
+        t = self.torch.tensor(list(bytes(ident)), dtype=self.torch.uint8, device=dev)
+        dist.broadcast(t, 0)
+        ident = (C.c_char * 128).from_buffer_copy(bytes(t.cpu().tolist()))
+        self._chk(self.lib.omega_halo_comm_init(self.handle, ident, world, rank), "omega_halo_comm_init")
 
-    def unpack(self, ptrs):
-        K = self.mesh.K
-        for key, e, outer, ptr in ptrs:
-            _, rb = self.bufs[key]
-            rc = self.lib.omega_halo_unpack(self.handle, e, outer, K, C.c_void_p(rb.data_ptr()), ptr, self._stream())
-            assert rc == 0, self.lib.omega_last_error()
+    def attach(self, st):
+        self._chk(self.lib.omega_stepper_attach_halo(st.h, self.handle), "omega_stepper_attach_halo")
 
-    def segments(self, ptrs):
-        """[(neighbour task, send slice, recv slice)] for every array of the round."""
-        K = self.mesh.K
-        out = []
-        for key, e, outer, _ in ptrs:
-            sb, rb = self.bufs[key]
-            so, ro = self.counts[e]
-            for i, nbr in enumerate(self.nbrs):
-                s0, s1 = int(so[i]) * outer * K, int(so[i + 1]) * outer * K
-                r0, r1 = int(ro[i]) * outer * K, int(ro[i + 1]) * outer * K
-                out.append((nbr, sb[s0:s1], rb[r0:r1]))
-        return out
+    def tile_classes(self):
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        self.lib.omega_halo_tile_classes(self.handle, C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
+
+    # -- one round, cut into its device halves (tests: N ranks emulated on one GPU) --------------
+    @staticmethod
+    def _round(ptrs):
+        n = len(ptrs)
+        P = (C.c_void_p * 3)(*[p[3] for p in ptrs])
+        E = (C.c_int * 3)(*[p[1] for p in ptrs])
+        O = (C.c_int * 3)(*[p[2] for p in ptrs])
+        return P, E, O, n
+
+    def pack_round(self, ptrs):
+        """-> (send buffer address, [send counts per neighbour], [recv counts per neighbour]) in doubles"""
+        P, E, O, n = self._round(ptrs)
+        buf = C.c_void_p()
+        self._chk(self.lib.omega_halo_pack_round(self.handle, P, E, O, n, C.byref(buf), self._stream()), "omega_halo_pack_round")
+        nn = len(self.nbrs)
+        sc, rcv = (C.c_longlong * max(nn, 1))(), (C.c_longlong * max(nn, 1))()
+        self._chk(self.lib.omega_halo_round_counts(self.handle, E, O, n, sc, rcv), "omega_halo_round_counts")
+        return buf.value, list(sc)[:nn], list(rcv)[:nn]
+
+    def recv_buffer(self, ptrs):
+        P, E, O, n = self._round(ptrs)
+        buf = C.c_void_p()
+        self._chk(self.lib.omega_halo_recv_buffer(self.handle, E, O, n, C.byref(buf)), "omega_halo_recv_buffer")
+        return buf.value
+
+    def unpack_round(self, ptrs):
+        P, E, O, n = self._round(ptrs)
+        self._chk(self.lib.omega_halo_unpack_round(self.handle, P, E, O, n, self._stream()), "omega_halo_unpack_round")
 
     def exchange_round(self, ptrs):
-        """ptrs: [(key, elem kind, nouter, device pointer)] -- all arrays of one exchange point."""
-        import torch.distributed as dist
-        self.pack(ptrs)
-        ops = []
-        for nbr, s, r in self.segments(ptrs):
-            if s.numel():
-                ops.append(dist.P2POp(dist.isend, s, nbr))
-            if r.numel():
-                ops.append(dist.P2POp(dist.irecv, r, nbr))
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
-        self.unpack(ptrs)
+        """ptrs: [(key, elem kind, nouter, device pointer)] -- all arrays of one exchange point (NCCL)."""
+        P, E, O, n = self._round(ptrs)
+        self._chk(self.lib.omega_halo_exchange_round(self.handle, P, E, O, n, self._stream()), "omega_halo_exchange_round")
 
     def exchange_list(self, st, state, stepper, phase):
         ptrs = (C.c_void_p * 3)()
@@ -221,13 +234,18 @@ class HaloExchanger:
         return [(keys[i], int(elems[i]), int(nouter[i]), C.c_void_p(ptrs[i])) for i in range(n.value)]
 
     def do_step(self, st, state, stepper, coeffs, fused=True, compat=True):
-        """TimeStepper::doStep with the halo exchanges of RungeKutta4Stepper.cpp:108-114
-        and OceanState/Tracers::updateTimeLevels."""
-        nph = 2 if stepper == capi.RK4 else 1
-        for p in range(nph):
-            st.stepPhase(state, stepper, coeffs, p, fused=fused, compat=compat)
-            self.exchange_round(self.exchange_list(st, state, stepper, p))
-        self.lib.omega_state_rotate(C.byref(state.c))
+        """TimeStepper::doStep including the halo exchanges of RungeKutta4Stepper.cpp:108-114,130-131 and
+        OceanState/Tracers::updateTimeLevels: one library call."""
+        self._chk(self.lib.omega_stepper_do_step(st.h, stepper, C.byref(state.c), C.byref(coeffs), self.handle,
+                                                 int(fused), int(compat), self._stream()), "omega_stepper_do_step")
+
+    def set_profiling(self, on):
+        self.lib.omega_halo_set_profiling(self.handle, int(on))
+
+    def profile(self):
+        ms, rounds, nbytes = C.c_double(), C.c_longlong(), C.c_longlong()
+        self._chk(self.lib.omega_halo_get_profile(self.handle, C.byref(ms), C.byref(rounds), C.byref(nbytes)), "omega_halo_get_profile")
+        return ms.value, rounds.value, nbytes.value
 
     def close(self):
         if self.handle:

@@ -3,11 +3,16 @@
 // HorzMesh, OceanState, Tracers, AuxiliaryState, Tendencies, TimeStepper, call
 // computeAllTendencies and doStep.  Input arrays come from a directory of raw
 // .bin files written by tests/test_host_mirror.py, results go back the same way.
+#include <chrono>
 #include <cstdio>
+#include <cuda_runtime_api.h>
 #include <fstream>
+#include <thread>
 #include <iostream>
 #include <map>
 #include <sstream>
+
+#include <memory>
 
 #include "OmegaB200.h"
 
@@ -28,9 +33,15 @@ static void save(const std::string &Name, const std::vector<double> &V) {
    F.write(reinterpret_cast<const char *>(V.data()), V.size() * sizeof(double));
 }
 
+// usage: host_mirror_test <dir>                      one rank
+//        host_mirror_test <dir> <rank> <world>       rank `rank` of `world`: <dir> holds this rank's mesh, state
+//            and halo lists; the NCCL unique id travels through the file <dir>/../nccl_id.bin (the test's
+//            stand-in for the MPI_Bcast an Omega host would use), one GPU per rank.
 int main(int argc, char **argv) {
    if (argc < 2) return 2;
    Dir = argv[1];
+   const int Rank = argc >= 4 ? std::atoi(argv[2]) : 0, World = argc >= 4 ? std::atoi(argv[3]) : 1;
+   if (World > 1 && cudaSetDevice(Rank) != cudaSuccess) { std::fprintf(stderr, "rank %d: no device\n", Rank); return 3; }
    std::map<std::string, double> Meta;
    {
       std::ifstream F(Dir + "/meta.txt");
@@ -59,8 +70,43 @@ int main(int argc, char **argv) {
    const int Kind = (int)Meta["Stepper"]; // 0 RK4, 1 RK2, 2 FB
 
    HorzMesh Mesh(D, true);
-   OceanState State("Default", &Mesh, nullptr, K, 2);
-   Tracers Trc(&Mesh, nullptr, T, K, 2);
+   // Halo: exchange lists of this rank (Halo.cpp:455-600) + the library's NCCL transport
+   std::unique_ptr<Halo> MeshHalo;
+   std::map<std::string, std::vector<int>> HL;
+   std::vector<int> NbrTasks;
+   if (World > 1) {
+      OmegaHaloDesc HD{};
+      NbrTasks = load<int>("halo_neighbors");
+      HD.MyTask = Rank; HD.NNeighbors = (int)NbrTasks.size(); HD.NeighborTasks = NbrTasks.data();
+      const char *Kinds[3] = {"Cell", "Edge", "Vertex"};
+      for (int e = 0; e < 3; ++e) {
+         const std::string k = Kinds[e];
+         HL["so" + k] = load<int>("halo_send_off_" + k); HL["si" + k] = load<int>("halo_send_idx_" + k);
+         HL["ro" + k] = load<int>("halo_recv_off_" + k); HL["ri" + k] = load<int>("halo_recv_idx_" + k);
+         HD.SendOffsets[e] = HL["so" + k].data(); HD.SendIdx[e] = HL["si" + k].data();
+         HD.RecvOffsets[e] = HL["ro" + k].data(); HD.RecvIdx[e] = HL["ri" + k].data();
+      }
+      MeshHalo.reset(new Halo(&Mesh, HD));
+      char Id[128];
+      const std::string IdFile = Dir + "/../nccl_id.bin";
+      if (Rank == 0) {
+         Halo::uniqueId(Id);
+         std::ofstream F(IdFile + ".tmp", std::ios::binary);
+         F.write(Id, 128);
+         F.close();
+         std::rename((IdFile + ".tmp").c_str(), IdFile.c_str());
+      } else {
+         for (int i = 0; i < 600; ++i) {
+            std::ifstream F(IdFile, std::ios::binary);
+            if (F && F.read(Id, 128)) break;
+            std::this_thread::sleep_for(std::chrono::milliseconds(100));
+            if (i == 599) { std::fprintf(stderr, "rank %d: no NCCL id\n", Rank); return 4; }
+         }
+      }
+      MeshHalo->initComm(Id, World, Rank);
+   }
+   OceanState State("Default", &Mesh, MeshHalo.get(), K, 2);
+   Tracers Trc(&Mesh, MeshHalo.get(), T, K, 2);
    AuxiliaryState Aux("Default", &Mesh, nullptr, K, T, Cfg);
    Tendencies Tend("Default", &Mesh, &Aux, K);
    TimeStepper Stepper(Kind == 0 ? TimeStepperType::RungeKutta4 : Kind == 1 ? TimeStepperType::RungeKutta2

@@ -338,17 +338,18 @@ def test_tiled_and_untiled_fused_paths_agree(monkeypatch):
 @pytest.mark.parametrize("fused,K", [(False, 4), (True, 4), (True, 16)])
 @pytest.mark.parametrize("ntasks", [2, 3])
 def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
-    """N ranks' partitions stepped on one GPU in one process: the library's halo
-    pack/unpack kernels, exchange lists in device order and phase-split stepping,
-    with device-to-device copies standing in for NCCL.  Checked against the
-    1-rank oracle on every local element (HaloWidth 4: see
+    """N ranks' partitions stepped on one GPU in one process: the library's round pack / unpack kernels,
+    exchange lists in device order, phase-split stepping with the halo attached (boundary tiles first,
+    halo tiles skipped before an exchange), with device-to-device copies standing in for NCCL.  Checked
+    against the 1-rank oracle on every local element (HaloWidth 4: see
     test_multirank_cpu.test_reference_needs_halo_width_4_with_del4)."""
     import ctypes as C
     from omega_b200 import analytic, decomp, model, parallel
     from tests.oracle_lib import Oracle
     T, nsteps = 2, 3
-    mesh_g = cases.sphere_mesh(3)
-    L1, cfg, (h, u, tr), dt = cases.sphere_case(3, K, T)
+    level = 4 if K == 16 else 3          # level 4: 2562 cells, enough tiles for all three tile classes
+    mesh_g = cases.sphere_mesh(level)
+    L1, cfg, (h, u, tr), dt = cases.sphere_case(level, K, T)
     ref = Oracle(L1, cfg, T)
     ref.make_state(h, u, tr)
     for s in range(nsteps):
@@ -365,29 +366,42 @@ def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
         m = model.HorzMesh(L, reorder=True)
         st, state = model.Stepper(m, cfg, T), model.OceanState(m, T)
         state.copyToDevice(*analytic.tc5(L, T))
-        ranks.append((L, m, st, state, parallel.HaloExchanger(m, hl, T)))
+        ex = parallel.HaloExchanger(m, hl, T)
+        ex.attach(st)
+        ranks.append((L, m, st, state, ex))
+    lib = ranks[0][1].lib
+    stream = C.c_void_p(0)
+    import torch
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    split_seen = False
     for s in range(nsteps):
         co = capi.rk_coeffs(capi.RK4, dt, t0=s * dt)
         for p in range(2):
             rounds = []
             for L, m, st, state, ex in ranks:
                 st.stepPhase(state, capi.RK4, co, p, fused=fused, compat=True)
+                split_seen |= bool(st.last_path() & 16)
                 ptrs = ex.exchange_list(st, state, capi.RK4, p)
-                ex.pack(ptrs)
-                rounds.append(ptrs)
-            # transport: my send segment to nbr is nbr's recv segment from me
-            segs = [{} for _ in ranks]
-            for t, (rk, ptrs) in enumerate(zip(ranks, rounds)):
-                for i, (nbr, sb, rb) in enumerate(rk[4].segments(ptrs)):
-                    segs[t].setdefault(nbr, []).append((sb, rb))
-            for t in range(len(ranks)):
-                for nbr, pairs in segs[t].items():
-                    for (sb, _), (_, rb) in zip(pairs, segs[nbr][t]):
-                        rb.copy_(sb)
-            for (L, m, st, state, ex), ptrs in zip(ranks, rounds):
-                ex.unpack(ptrs)
+                sbuf, sc, rc = ex.pack_round(ptrs)
+                rounds.append((ptrs, sbuf, sc, rc, ex.recv_buffer(ptrs)))
+            # transport: my message to neighbour nbr is nbr's message from me (offsets in neighbour order)
+            for t, (rk, (ptrs, sbuf, sc, rc, rbuf)) in enumerate(zip(ranks, rounds)):
+                soff = np.concatenate(([0], np.cumsum(sc)))
+                for i, nbr in enumerate(rk[4].nbrs):
+                    _, _, sc2, rc2, rbuf2 = rounds[nbr]
+                    j = ranks[nbr][4].nbrs.index(t)
+                    roff2 = np.concatenate(([0], np.cumsum(rc2)))
+                    assert rc2[j] == sc[i]
+                    assert lib.omega_dev_copy(C.c_void_p(rbuf2 + 8 * int(roff2[j])), C.c_void_p(sbuf + 8 * int(soff[i])),
+                                              C.c_ulonglong(8 * sc[i]), stream) == 0
+            for (L, m, st, state, ex), (ptrs, *_rest) in zip(ranks, rounds):
+                ex.unpack_round(ptrs)
         for L, m, st, state, ex in ranks:
             m.lib.omega_state_rotate(C.byref(state.c))
+    if fused and K == 16:
+        assert split_seen, "the attached halo must switch the tiled path to boundary-first launches"
+        nb, nown, nall = ranks[0][4].tile_classes()
+        assert 0 < nb < nown < nall, (nb, nown, nall)
     worst = 0.0
     for L, m, st, state, ex in ranks:
         lh, lu, lt = state.copyToHost(0)
@@ -397,6 +411,23 @@ def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
         ex.close(); st.close(); m.close()
     ref.close()
     assert worst <= TOL_STATE, worst
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_nccl_ranks_match_oracle(nranks):
+    """The NCCL path itself (library exchange rounds inside omega_stepper_do_step, overlapped with the interior
+    tiles): N ranks, one GPU each, against the 1-rank oracle on every local element (tests/nccl_check.py)."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < nranks:
+        pytest.skip(f"needs {nranks} GPUs (gpurun --gpus {nranks})")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nranks}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29600 + nranks), os.path.join(root, "tests", "nccl_check.py"), "5" if nranks > 2 else "4", "16", "3", "4"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "NCCL_CHECK_OK" in out.stdout, (out.stdout[-2000:], out.stderr[-2000:])
 
 
 def test_config3_full_size_level_slices_and_conservation():

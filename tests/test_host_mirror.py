@@ -20,7 +20,8 @@ def build_exe():
     src = os.path.join(ROOT, "tests", "cpp", "host_mirror_test.cpp")
     lib_dir = os.path.join(ROOT, "omega_b200", "csrc")
     cmd = ["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "omega_b200", "host"),
-           src, "-o", EXE, "-L" + lib_dir, "-lomega_b200", "-Wl,-rpath," + lib_dir]
+           "-I/usr/local/cuda/include", src, "-o", EXE, "-L" + lib_dir, "-lomega_b200", "-L/usr/local/cuda/lib64", "-lcudart",
+           "-Wl,-rpath," + lib_dir, "-Wl,-rpath,/usr/local/cuda/lib64"]
     subprocess.run(cmd, check=True)
 
 
@@ -30,6 +31,72 @@ def test_host_mirror_compiles_against_the_c_abi():
         pytest.skip("libomega_b200.so not built")
     build_exe()
     assert os.path.exists(EXE)
+
+
+def write_case(d, L, cfg, h, u, tr, dt, stepper, fused, nsteps):
+    """mesh, config and state of one rank as raw files for tests/cpp/host_mirror_test"""
+    T = tr.shape[0]
+    os.makedirs(d, exist_ok=True)
+    for name, _ in capi.MeshDesc._fields_[13:]:
+        np.ascontiguousarray(L[name]).astype(np.int32 if name in (
+            "NEdgesOnCell", "EdgesOnCell", "CellsOnEdge", "VerticesOnEdge", "NEdgesOnEdge", "EdgesOnEdge",
+            "CellsOnVertex", "EdgesOnVertex") else np.float64).tofile(os.path.join(d, name + ".bin"))
+    with open(os.path.join(d, "meta.txt"), "w") as f:
+        for name, _ in capi.MeshDesc._fields_[:13]:
+            f.write(f"{name} {int(L[name])}\n")
+        f.write(f"NTracers {T}\nNSteps {nsteps}\nDt {dt}\nStepper {stepper}\nFused {fused}\n")
+    with open(os.path.join(d, "cfg.bin"), "wb") as f:
+        f.write(bytes(cfg))
+    h.tofile(os.path.join(d, "h.bin")); u.tofile(os.path.join(d, "u.bin")); tr.tofile(os.path.join(d, "tr.bin"))
+
+
+@pytest.mark.gpu
+def test_host_mirror_two_ranks_step_without_python_transport(tmp_path):
+    """Two C++ host processes, one GPU each, step RK4 through TimeStepper::doStep: the exchange rounds run
+    inside omega_stepper_do_step over NCCL (no Python, no caller-supplied transport).  Every local
+    element of both ranks against the 1-rank oracle."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    from omega_b200 import analytic, decomp, parallel
+    build_exe()
+    K, T, nsteps, world = 16, 2, 3, 2
+    mesh_g = cases.sphere_mesh(4)
+    L1, cfg, (h, u, tr), dt = cases.sphere_case(4, K, T)
+    locs = decomp.build_all(mesh_g, world, K, 4)
+    lists = parallel.build_halo_lists(locs)
+    for r, (L, hl) in enumerate(zip(locs, lists)):
+        d = str(tmp_path / f"r{r}")
+        lh, lu, ltr = analytic.tc5(L, T)
+        write_case(d, L, cfg, lh, lu, ltr, dt, capi.RK4, 1, nsteps)
+        np.array(hl["neighbors"], np.int32).tofile(os.path.join(d, "halo_neighbors.bin"))
+        flat = parallel.flatten_lists(hl)
+        for dirn, tag in (("send", "send"), ("recv", "recv")):
+            for kind in parallel.KINDS:
+                off, idx = flat[(dirn, kind)]
+                off.tofile(os.path.join(d, f"halo_{tag}_off_{kind}.bin"))
+                idx.tofile(os.path.join(d, f"halo_{tag}_idx_{kind}.bin"))
+    procs = [subprocess.Popen([EXE, str(tmp_path / f"r{r}"), str(r), str(world)]) for r in range(world)]
+    for p in procs:
+        assert p.wait(timeout=300) == 0
+    o = Oracle(L1, cfg, T)
+    o.make_state(h, u, tr)
+    for s in range(nsteps):
+        o.do_step(capi.RK4, capi.rk_coeffs(capi.RK4, dt, t0=s * dt))
+    gh, gu, gt = o.current()
+    cell_of, edge_of = L1.CellID[:-1] - 1, L1.EdgeID[:-1] - 1
+    H = np.empty_like(gh[:-1]); H[cell_of] = gh[:-1]
+    U = np.empty_like(gu[:-1]); U[edge_of] = gu[:-1]
+    TR = np.empty_like(gt[:, :-1]); TR[:, cell_of] = gt[:, :-1]
+    for r, L in enumerate(locs):
+        d = str(tmp_path / f"r{r}")
+        lh = np.fromfile(os.path.join(d, "out_h.bin")).reshape(-1, K)
+        lu = np.fromfile(os.path.join(d, "out_u.bin")).reshape(-1, K)
+        lt = np.fromfile(os.path.join(d, "out_tr.bin")).reshape(T, -1, K)
+        ci, ei = L.CellID[:L.NCellsAll] - 1, L.EdgeID[:L.NEdgesAll] - 1
+        for a, b in ((lh[:L.NCellsAll], H[ci]), (lu[:L.NEdgesAll], U[ei]), (lt[:, :L.NCellsAll], TR[:, ci])):
+            assert cases.rel_l2(a, b) <= 1e-10, (r, cases.rel_l2(a, b))
+    o.close()
 
 
 @pytest.mark.gpu
