@@ -236,8 +236,8 @@ int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type,
                                 const OmegaStateArrays *State, int Phase, double **Ptrs,
                                 int *Elems, int *NOuter, int *NArrays);
 /* Attach the rank's Halo to the stepper (do_step with a Halo does this itself).  The fused tiled path then
- * (a) skips the halo tiles in the stages whose results the following exchange overwrites (RK4 stages 1
- * and 3: every local non-owned cell / edge is in a receive list) and (b) launches the tiles that hold
+ * (a) skips the halo tiles in the stages whose results the following exchange overwrites (RK4 stage 3, and
+ * stage 1 unless the raw time-level indexing makes its halo thickness matter) and (b) launches the tiles that hold
  * send-list rows first, so the exchange overlaps the interior tiles.  Callers of step_phase that run
  * the exchange themselves may attach too; they must exchange after every phase. */
 int omega_stepper_attach_halo(OmegaStepper *S, OmegaHalo *Halo);

@@ -934,16 +934,29 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
       ca.MS = manufactured(S, C->StageTime[s]);
       S->LastPath = OMEGA_PATH_FUSED | (tiled ? OMEGA_PATH_TILED_CELL : 0) | (tiled && tile_v2_used(ca) ? OMEGA_PATH_CELL_V2 : 0) |
                     (tiledE ? OMEGA_PATH_TILED_EDGE : 0);
-      // With a halo attached (multi-rank): the stages right before an exchange (1 and 3) need results on
-      // owned elements only -- the exchange overwrites every other row -- so the halo tiles are skipped,
-      // and the tiles that hold send-list rows run first: once they are done the exchange starts on the
-      // halo's own stream (step.cu) while the interior tiles below still compute.
+      // With a halo attached (multi-rank): the tiles that hold send-list rows run first in the stages right
+      // before an exchange (1 and 3); once they are done the exchange starts on the halo's own stream
+      // (step.cu) while the interior tiles below still compute.  The halo tiles are skipped there -- the
+      // exchange overwrites every non-owned row -- except in stage 1 of a step with raw time-level indexing
+      // and CurTimeIndex == 1: the stage-2 tracer update then multiplies by the ACCUMULATING
+      // next-level thickness, whose stage-1 contribution on the first halo layer is valid and needed, so the
+      // halo tiles run with the boundary tiles (ahead of the exchange, which writes the same halo rows).
       const OmegaHalo *Hl = S->Halo;
       const bool split = Hl && Hl->DTileOrder && Hl->HaloCovered && tiled && tiledE && (s == 1 || s == 3) &&
                          env_int("OMEGA_HALO_OVERLAP", 1);
+      const bool skipHalo = s == 3 || !swapped;
       const TileRange trAll = all_tiles(D);
-      const TileRange trBnd = split ? TileRange{Hl->DTileOrder, 0, Hl->NTilesBoundary} : trAll;
-      const TileRange trInt = split ? TileRange{Hl->DTileOrder, Hl->NTilesBoundary, Hl->NTilesOwned - Hl->NTilesBoundary} : trAll;
+      TileRange trBnd = trAll, trInt = trAll;
+      if (split) {
+         const int nB = Hl->NTilesBoundary, nO = Hl->NTilesOwned, nH = D.Tiles.NTiles - nO;
+         if (skipHalo) {
+            trBnd = TileRange{Hl->DTileOrder, 0, nB};
+            trInt = TileRange{Hl->DTileOrder, nB, nO - nB};
+         } else {
+            trBnd = TileRange{Hl->DTileOrderBH, 0, nB + nH};
+            trInt = TileRange{Hl->DTileOrderBH, nB + nH, nO - nB};
+         }
+      }
       if (split) S->LastPath |= OMEGA_PATH_HALO_SPLIT;
       {
       ScopedTimer tm_(S, St, kFC);

@@ -563,7 +563,8 @@ template <int KC_, int RS_ = 0, int CP_ = 0> struct Cfg2 {
    static constexpr int NT = TT + RT;
    static constexpr int NS = 4;              // tracer row-set buffers (copy lead 3 needs 4)
    static constexpr int CTAs = KC == 16 ? 1 : 2;
-   static constexpr bool BULK = CP_ == 1;    // row copies: 0 = cp.async 16-byte pieces (LSU), 1 = one bulk copy per row (TMA unit, mbarrier)
+   static constexpr bool BULK = CP_ >= 1;    // row copies: 0 = cp.async 16-byte pieces (LSU), 1, 2 = one bulk copy per row (TMA unit, mbarrier)
+   static constexpr bool ONEWAIT = CP_ == 2; // 2: ONE thread waits on the "landed" barrier, ahead of the __syncthreads that hands the buffer over
    struct Smem : TileSmemT<KC, NS> {
       double2 W[3][TT]; // per T thread: the three per-level weights of the RK update (private slots, spares 12 registers)
       unsigned long long Bar[NS + 1]; // BULK: "landed" barriers of the tracer buffers and of h
@@ -621,10 +622,17 @@ __device__ __forceinline__ void issue_rows(typename C::Smem &S, int nR, int K, i
    }
 }
 template <class C> __device__ __forceinline__ void wait_item(typename C::Smem &S, int item) { // tracer item of the copy stream
-   if (C::BULK) mbar_wait(smem_u32(&S.Bar[item % C::NS]), (item / C::NS) & 1);
+   if (C::BULK && !C::ONEWAIT) mbar_wait(smem_u32(&S.Bar[item % C::NS]), (item / C::NS) & 1);
 }
 template <class C> __device__ __forceinline__ void wait_h(typename C::Smem &S, int chunk) {
-   if (C::BULK) mbar_wait(smem_u32(&S.Bar[C::NS]), chunk & 1);
+   if (C::BULK && !C::ONEWAIT) mbar_wait(smem_u32(&S.Bar[C::NS]), chunk & 1);
+}
+// ONEWAIT: called by the first R thread only, right before the barrier behind which the buffer is read
+template <class C> __device__ __forceinline__ void wait_item_one(typename C::Smem &S, int item) {
+   if (C::ONEWAIT) mbar_wait(smem_u32(&S.Bar[item % C::NS]), (item / C::NS) & 1);
+}
+template <class C> __device__ __forceinline__ void wait_h_one(typename C::Smem &S, int chunk) {
+   if (C::ONEWAIT) mbar_wait(smem_u32(&S.Bar[C::NS]), chunk & 1);
 }
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -657,6 +665,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
          else if (T == 2) cp_wait<1>();
          else cp_wait<0>();
       }
+      if (r == 0) wait_h_one<C>(S, c);
       __syncthreads();            // ... and everybody else's; tables are visible; the T role is done with the previous chunk
       wait_h<C>(S, c);
       for (int u = 0; u < nTask; ++u) { // coefficients of the ring rows: -(1/A) G mean thickness, private slots in Cf1
@@ -677,6 +686,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
             if (!shortT) cp_wait<2>();
             else cp_wait<1>();
          }
+         if (r == 0 && i < T) wait_item_one<C>(S, it0 + i);
          __syncthreads();                              // iteration i: the T role has finished iteration i-1
          if (shortT) {
             if (c + 1 < NCh) {
@@ -1040,6 +1050,7 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
    const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0);
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St, TR);
+   if (cp == 2) return launch_fCT2_c<Cfg2<16, 2, 2>, STAGE>(D, ca, St, TR);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St, TR) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St, TR) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St, TR);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }

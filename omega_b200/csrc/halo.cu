@@ -326,6 +326,13 @@ int omega_halo_create(const OmegaMesh *M, const OmegaHaloDesc *D, OmegaHalo **Ou
       H->Allocs.push_back(d);
       OMEGA_CUDA_CHECK(cudaMemcpy(d, order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice));
       H->DTileOrder = d;
+      std::vector<int> order2(order.begin(), order.begin() + H->NTilesBoundary);
+      order2.insert(order2.end(), order.begin() + nOwned, order.end());
+      order2.insert(order2.end(), order.begin() + H->NTilesBoundary, order.begin() + nOwned);
+      OMEGA_CUDA_CHECK(cudaMalloc((void **)&d, sizeof(int) * order2.size()));
+      H->Allocs.push_back(d);
+      OMEGA_CUDA_CHECK(cudaMemcpy(d, order2.data(), sizeof(int) * order2.size(), cudaMemcpyHostToDevice));
+      H->DTileOrderBH = d;
       // every local non-owned cell / edge must be covered by the receive lists, or skipping the
       // halo tiles in the stages before an exchange would leave stale rows
       H->HaloCovered = H->RecvOff[0][D->NNeighbors] == M->D.NCellsAll - M->D.NCellsOwned &&

@@ -35,7 +35,8 @@ struct OmegaHalo {
    // overlap with interior compute (step.cu)
    cudaStream_t CommStream = nullptr;
    cudaEvent_t EvReady = nullptr, EvDone = nullptr;
-   int *DTileOrder = nullptr; // [boundary tiles | other owned tiles | halo tiles]
+   int *DTileOrder = nullptr;   // [boundary tiles | other owned tiles | halo tiles]
+   int *DTileOrderBH = nullptr; // [boundary tiles | halo tiles | other owned tiles]
    int NTilesBoundary = 0, NTilesOwned = 0, HaloCovered = 0;
    // CUDA-event timing of the rounds (bench: ms per round, bytes against NVLink)
    int Profiling = 0;
