@@ -25,8 +25,11 @@
 // Reference semantics restated: src/timeStepping/RungeKutta4Stepper.cpp:68-137,
 // src/timeStepping/TimeStepper.cpp:378-524, src/ocn/Tendencies.cpp:257-486,
 // src/ocn/AuxiliaryState.cpp:60-185 and the functors cited at each block.
+#include <nvtx3/nvToolsExt.h>
+
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "fused_args.h"
 #include "halo.h"
@@ -62,7 +65,7 @@ template <int V>
 __global__ void __launch_bounds__(kBlock)
 k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double *__restrict__ KE,
      double *__restrict__ Div, double *__restrict__ RelVort, double *__restrict__ PVv, int XMode, double aKE,
-     double aSSH) {
+     double aSSH, double *__restrict__ KEBot) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
@@ -82,6 +85,7 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
             dv[q] -= cf.y * u[q];
          }
       }
+      if (KEBot && k + V == M.K) KEBot[c] = ke[V - 1]; // plain KE of the bottom layer for BottomDragOnEdge (k_edge_layer_terms)
       if (XMode) {
          // tiled edge pass: KE and SSH gradients share (X(c1)-X(c0))/dc, X = aKE*KE + aSSH*g*(h - b)
          // (KEGradOnEdge, SSHGradOnEdge, TendencyTerms.h:127-173; LayerThicknessAuxVars.h:63-82)
@@ -422,7 +426,7 @@ k_fC(DMesh M, CellArgs P) {
 #pragma unroll
       for (int q = 0; q < V; ++q) {
          hw[q]   = P.WSel ? hnext_old[q] : hcur[q];
-         h2[q]   = P.H2Sel ? hnext[q] : hcur[q];
+         h2[q]   = P.H2Sel == 2 ? hprov[q] : (P.H2Sel ? hnext[q] : hcur[q]);
          hfin[q] = P.FinSel ? hcur[q] : hnext[q];
       }
       for (int l = 0; l < P.NTracers; ++l) {
@@ -479,7 +483,7 @@ k_fC(DMesh M, CellArgs P) {
          stv<V>(P.TrNext + l * CS + o, out);
          if (!P.Last) {
 #pragma unroll
-            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / hprov[q];
+            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / (P.DivSel ? hcur[q] : hprov[q]);
             stv<V>(P.TrProv + l * CS + o, out);
          }
       }
@@ -585,7 +589,7 @@ k_fC_center(DMesh M, CellArgs P) {
 #pragma unroll
       for (int q = 0; q < V; ++q) {
          hx[q] = P.First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
-         h2[q] = P.H2Sel ? hnext[q] : hcur[q];
+         h2[q] = P.H2Sel == 2 ? hprov[q] : (P.H2Sel ? hnext[q] : hcur[q]);
       }
       for (int l = 0; l < P.NTracers; ++l) {
          const double *T  = P.Trs + l * CS;
@@ -642,7 +646,7 @@ k_fC_center(DMesh M, CellArgs P) {
          stv<V>(P.TrNext + l * CS + o, out);
          if (!P.Last) {
 #pragma unroll
-            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / hprov[q];
+            for (int q = 0; q < V; ++q) out[q] = (tcur[q] * h2[q] + P.A * tend[q]) / (P.DivSel ? hcur[q] : hprov[q]);
             stv<V>(P.TrProv + l * CS + o, out);
          }
       }
@@ -807,6 +811,94 @@ k_fE(DMesh M, EdgeArgs P) {
 }
 
 // ---------------------------------------------------------------------------
+// Terms the tiled kernels take as precomputed per-element values or as a single-layer correction.
+//
+// k_ms_sources: the manufactured-solution sources of src/ocn/CustomTendencyTerms.cpp:107-210 are the same on
+// every level, so they are evaluated once per cell / edge and stage (not per level in the hot kernels):
+// SrcH feeds the thickness tendency of the tiled cell pass, SrcU the velocity tendency of the tiled edge pass.
+//
+// k_edge_layer_terms: WindForcingOnEdge touches the top layer only and BottomDragOnEdge the bottom layer only
+// (TendencyTerms.h:291-334).  The RK update is linear in the tendency, u_next = base + B*(R + r), so the tiled
+// edge pass updates with R and this kernel adds B*r / A*r on the one layer concerned (the sum differs from the
+// reference's term order by rounding only).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock)
+k_ms_sources(DMesh M, ManufacturedParams MS, double TimeEdge, int Del2On, double Visc2, int Del4On, double Visc4,
+             double *__restrict__ SrcH, double *__restrict__ SrcU) {
+   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+   if (i < M.NCellsAll) {
+      const double Phase = MS.Kx * M.XCell[i] + MS.Ky * M.YCell[i] - MS.AngFreq * MS.Time;
+      SrcH[i] = MS.Eta0 * (-MS.H0 * (MS.Kx + MS.Ky) * sin(Phase) - MS.AngFreq * cos(Phase) +
+                           MS.Eta0 * (MS.Kx + MS.Ky) * cos(2.0 * Phase));
+   }
+   if (i < M.NEdgesAll) {
+      const int e = i;
+      const double Grav  = 9.80665;
+      const double Phase = MS.Kx * M.XEdge[e] + MS.Ky * M.YEdge[e] - MS.AngFreq * TimeEdge;
+      const double Src0  = MS.AngFreq * sin(Phase) - 0.5 * MS.Eta0 * (MS.Kx + MS.Ky) * sin(2.0 * Phase);
+      const double f     = M.FEdge[e];
+      double Uu = MS.Eta0 * ((-f + Grav * MS.Kx) * cos(Phase) + Src0);
+      double Vv = MS.Eta0 * ((f + Grav * MS.Ky) * cos(Phase) + Src0);
+      const double Kx2 = MS.Kx * MS.Kx, Ky2 = MS.Ky * MS.Ky;
+      if (Del2On) {
+         Uu += Visc2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
+         Vv += Visc2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
+      }
+      if (Del4On) {
+         const double Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
+         Uu -= Visc4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
+         Vv -= Visc4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
+      }
+      const double a = M.AngleEdge[e];
+      SrcU[e] = cos(a) * Uu + sin(a) * Vv;
+   }
+}
+
+__global__ void __launch_bounds__(kBlock)
+k_edge_layer_terms(DMesh M, const double *__restrict__ Hs, const double *__restrict__ URaw,
+                   const double *__restrict__ KEBot, const double *__restrict__ NormalStress, int WindOn, int DragOn,
+                   double InvRho0, double Cd, double *__restrict__ Unext, double *__restrict__ Uprov, double A, double B,
+                   TileRange TR, const int *__restrict__ EdgeRows, const TileHdr *__restrict__ Hdr) {
+   // EdgeRows == nullptr: every edge once; else the OWN edges of the tiles of TR (halo split: the same edges,
+   // in the same two groups, as the two launches of the tiled edge pass)
+   int e = blockIdx.x * blockDim.x + threadIdx.x;
+   if (EdgeRows) {
+      // thread -> (tile of the range, own edge slot): kTileEdgesOwn slots per tile
+      const int t = e / kTileEdgesOwn, q = e - t * kTileEdgesOwn;
+      if (t >= TR.Count) return;
+      const TileHdr h = Hdr[TR.tile(t)];
+      if (q >= h.NEOwn) return;
+      e = EdgeRows[h.ERowOff + q];
+   } else if (e >= M.NEdgesAll) return;
+   const int2 cc     = M.CellsOnEdge[e];
+   const double mask = M.EdgeMask[e];
+   const int K = M.K, KBot = K - 1;
+   double r0 = 0.0, rb = 0.0; // tendency of the top / bottom layer
+   if (WindOn) {
+      const double InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K] + Hs[(size_t)cc.y * K]));
+      r0 = mask * InvThick * NormalStress[e] * InvRho0;
+   }
+   if (DragOn) {
+      const double VelNorm  = sqrt(KEBot[cc.x] + KEBot[cc.y]);
+      const double InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K + KBot] + Hs[(size_t)cc.y * K + KBot]));
+      rb = -mask * Cd * VelNorm * InvThick * URaw[(size_t)e * K + KBot];
+   }
+   const size_t o = (size_t)e * K;
+   if (KBot == 0) {
+      r0 += rb;
+      rb = 0.0;
+   }
+   if (r0 != 0.0) {
+      Unext[o] += B * r0;
+      if (Uprov) Uprov[o] += A * r0;
+   }
+   if (rb != 0.0) {
+      Unext[o + KBot] += B * rb;
+      if (Uprov) Uprov[o + KBot] += A * rb;
+   }
+}
+
+// ---------------------------------------------------------------------------
 // host side: one RK4 phase on the fused kernels
 // ---------------------------------------------------------------------------
 static int env_int(const char *name, int dflt) {
@@ -825,6 +917,13 @@ static unsigned fused_grid(int NRows, int K, int V, int Threads = kBlock, int It
    const long long per = (long long)rowsPerIter * std::max(Iters, 1);
    return (unsigned)std::max<long long>(((long long)NRows + per - 1) / per, 1);
 }
+
+// NVTX range per stage and kernel (the reference marks its timers the same way through Pacer:
+// share/pacer/Pacer.cpp:157-158,191-192); a no-op without a profiler attached.
+struct NvtxRange {
+   explicit NvtxRange(const char *Name) { nvtxRangePushA(Name); }
+   ~NvtxRange() { nvtxRangePop(); }
+};
 
 struct ScopedTimer {
    OmegaStepper *S;
@@ -847,119 +946,107 @@ struct ScopedTimer {
    }
 };
 
-static inline int tix(int Level, int Cur, int NTL) { return (Level + Cur + NTL) % NTL; }
 
-int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
-                    cudaStream_t St) {
+// One stage of a fused stepper as the kernels see it: R = RHS(stage state), then
+//    next (+)= B R   (first stage: next = cur + B R; tracers weighted by thickness, TimeStepper.cpp:446-524)
+//    prov  = cur + A R   (tracers: (cur*h_mul + A tend) / h_div)
+// RK4 uses both outputs (accumulated next-level state + provisional state of the following stage); RK2 and
+// forward-backward are written with the provisional output alone (their "next" output goes to a sink buffer
+// with B = 0): a stage cannot update the next-level arrays in place, neighbours still read them.
+struct StageDesc {
+   const double *Hs, *Us, *Trs;      // stage state the tendencies are evaluated on
+   const double *HsMom;              // thickness the momentum aux + edge pass see (forward-backward: the NEW thickness)
+   const double *UTr, *URaw;         // velocity seen by tracer advection / bottom drag (raw time-level indexing, P1)
+   double *Hnext, *Unext, *TrNext;   // accumulated output
+   double *Hprov, *Uprov, *TrProv;   // provisional output (nullptr: none)
+   double A, B, TimeCell, TimeEdge;
+   int First, Last, WSel, H2Sel, FinSel, DivSel;
+   int BeforeExchange;               // the stage's results are exchanged right after it (halo split applies)
+   int SkipHaloOK;                   // ... and nothing else reads its halo rows (see fused_phase)
+};
+
+static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, const double *Ucur, const double *TrCur,
+                     cudaStream_t St) {
    const DMesh &D           = S->M->D;
    const OmegaTendConfig &G = S->Cfg;
-   OMEGA_REQUIRE(S->M->MaxEdgesUsed <= kME,
-                 "fused path supports at most 6 edges per cell; use Fused=0");
    const int V = (D.K & 1) ? 1 : 2, T = S->NTracers;
-   const int ci = X->CurTimeIndex, ni = tix(1, ci, 2);
-   const int tci = X->TracerCurTimeIndex, tni = tix(1, tci, 2);
-   double *Hcur = X->LayerThickness[ci], *Hnext = X->LayerThickness[ni];
-   double *Ucur = X->NormalVelocity[ci], *Unext = X->NormalVelocity[ni];
-   double *TrCur = X->Tracers[tci], *TrNext = X->Tracers[tni];
-   // raw time-level indexing of the reference: with
-   // CurTimeIndex == 1 the "current" raw slot is the NEXT buffer and vice versa
-   const bool swapped = Compat && ci == 1;
-   S->ProvisExchangeSlot = 0;
    const bool vel4 = G.VelHyperDiffTendencyEnable, tr4 = G.TracerHyperDiffTendencyEnable && T > 0;
    const bool upw = G.FluxThicknessType || G.FluxTracerType;
-   Launch L{St, &S->Launches};
-   if (G.WindForcingTendencyEnable && Phase == 0) launch_wind_aux(L, D, S->A, G.WindStressInterpType);
-   const int s0 = Phase == 0 ? 0 : 2, s1 = Phase == 0 ? 1 : 3;
-   for (int s = s0; s <= s1; ++s) {
-      // provisional state of stage s lives in P[s % 2] (stage 2 -> slot 0, the exchanged one)
-      const double *Hs = s == 0 ? Hcur : S->P.H[s % 2];
-      const double *Us = s == 0 ? Ucur : S->P.U[s % 2];
-      const double *Trs = s == 0 ? TrCur : S->P.Tr[s % 2];
-      double *Hp = s == 3 ? nullptr : S->P.H[(s + 1) % 2];
-      double *Up = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
-      double *Tp = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
-      // sweep iterations per CTA (tuning knobs, defaults from profiles/r01 measurements)
-      const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 2),
-                       itT = env_int("OMEGA_ITERS_T2", 1), itC = env_int("OMEGA_ITERS_C", 1),
-                       itE = env_int("OMEGA_ITERS_E", 8);
-      const unsigned gc = fused_grid(D.NCellsAll, D.K, V, kBlock, itC), ge = fused_grid(D.NEdgesAll, D.K, V, kBlock, itE);
-      const unsigned gA = fused_grid(D.NCellsAll, D.K, V, kBlock, itA), gB = fused_grid(D.NCellsAll, D.K, V, kBlock, itB),
-                     gT = fused_grid(D.NCellsAll, D.K, V, kBlock, itT);
+   // sweep iterations per CTA (tuning knobs, defaults from profiles/r01 measurements)
+   const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 2), itT = env_int("OMEGA_ITERS_T2", 1),
+             itC = env_int("OMEGA_ITERS_C", 1), itE = env_int("OMEGA_ITERS_E", 8);
+   const unsigned gc = fused_grid(D.NCellsAll, D.K, V, kBlock, itC), ge = fused_grid(D.NEdgesAll, D.K, V, kBlock, itE);
+   const unsigned gA = fused_grid(D.NCellsAll, D.K, V, kBlock, itA), gB = fused_grid(D.NCellsAll, D.K, V, kBlock, itB),
+                  gT = fused_grid(D.NCellsAll, D.K, V, kBlock, itT);
 #define LAUNCH_V(KIND, KERNEL, GRID, ...)                               \
    do {                                                                 \
       ScopedTimer tm_(S, St, KIND);                                     \
+      NvtxRange nv_(#KERNEL);                                           \
       if (V == 2) KERNEL<2><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);       \
       else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
       ++S->Launches;                                                    \
    } while (0)
-      // shared-memory staged edge pass (fused_tile.cu) replaces fE when it applies; fA / fB then
-      // write the combined fields it differences
-      const bool tiledE = V == 2 && tile_edge_path_ok(D) && !G.FluxThicknessType && !G.WindForcingTendencyEnable &&
-                          !G.BottomDragTendencyEnable && !G.ManufacturedSolutionTendency && env_int("OMEGA_TILE_E", 1);
-      const double nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
-      LAUNCH_V(kFA, k_fA, gA, D, Hs, Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
-               G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0);
-      // W = Y - X folded into fB's cell result when the tiled edge pass follows (one gathered cell field less)
-      const bool xOn    = G.KETendencyEnable || G.SSHTendencyEnable;
-      const bool fB3    = vel4 && D.B3OK && env_int("OMEGA_FB3", 1);
-      const bool wMerge = fB3 && tiledE && xOn && env_int("OMEGA_FUSE_W", 1);
-      if (fB3)
-         LAUNCH_V(kFB, k_fB3, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
-                  G.ViscDel4 * G.DivFactor, G.ViscDel4, wMerge ? S->A.KE : nullptr);
-      else if (vel4)
-         LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
-                  G.ViscDel4 * G.DivFactor, G.ViscDel4);
-      // shared-memory staged cell pass (fused_tile.cu) replaces fT2 + fC when it applies
-      // (one tracer + tracer hyperdiffusion needs k_fCT2, which has no manufactured thickness source:
-      // k_fCT's D role assumes at least two tracers)
-      const bool tiled = !upw && V == 2 &&
-                         (T >= 2 || (T == 1 && (!tr4 || (tile_v2_enabled() && !G.ManufacturedSolutionTendency)))) &&
-                         tile_path_ok(D) && env_int("OMEGA_TILE", 1);
-      if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, Hs, Trs, T, S->A.Del2Tr);
-      // cell pass BEFORE the edge pass: at stage 0 with raw indexing the tracer
-      // advection reads the stale next-level velocity the edge pass overwrites
-      CellArgs ca;
-      ca.Hs = Hs; ca.Us = Us; ca.Trs = Trs; ca.Del2Tr = S->A.Del2Tr;
-      ca.UTr = (s == 0 && swapped) ? Unext : Us;
-      ca.Hcur = Hcur; ca.Hnext = Hnext; ca.Hprov = Hp;
-      ca.TrCur = TrCur; ca.TrNext = TrNext; ca.TrProv = Tp;
-      ca.A = s < 3 ? C->A[s + 1] : 0.0; ca.B = C->B[s];
-      ca.First = s == 0; ca.Last = s == 3; ca.NTracers = T;
-      ca.WSel = swapped; ca.H2Sel = swapped; ca.FinSel = swapped;
-      ca.FluxDivOn = G.ThicknessFluxTendencyEnable; ca.AdvOn = G.TracerHorzAdvTendencyEnable;
-      ca.DiffOn = G.TracerDiffTendencyEnable; ca.HypOn = tr4;
-      ca.FluxUpwind = G.FluxThicknessType; ca.TrUpwind = G.FluxTracerType;
-      ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
-      ca.Prefetch = env_int("OMEGA_FC_PREFETCH", 0);
-      ca.MS = manufactured(S, C->StageTime[s]);
-      S->LastPath = OMEGA_PATH_FUSED | (tiled ? OMEGA_PATH_TILED_CELL : 0) | (tiled && tile_v2_used(ca) ? OMEGA_PATH_CELL_V2 : 0) |
-                    (tiledE ? OMEGA_PATH_TILED_EDGE : 0);
-      // With a halo attached (multi-rank): the tiles that hold send-list rows run first in the stages right
-      // before an exchange (1 and 3); once they are done the exchange starts on the halo's own stream
-      // (step.cu) while the interior tiles below still compute.  The halo tiles are skipped there -- the
-      // exchange overwrites every non-owned row -- except in stage 1 of a step with raw time-level indexing
-      // and CurTimeIndex == 1: the stage-2 tracer update then multiplies by the ACCUMULATING
-      // next-level thickness, whose stage-1 contribution on the first halo layer is valid and needed, so the
-      // halo tiles run with the boundary tiles (ahead of the exchange, which writes the same halo rows).
-      const OmegaHalo *Hl = S->Halo;
-      const bool split = Hl && Hl->DTileOrder && Hl->HaloCovered && tiled && tiledE && (s == 1 || s == 3) &&
-                         env_int("OMEGA_HALO_OVERLAP", 1);
-      const bool skipHalo = s == 3 || !swapped;
-      const TileRange trAll = all_tiles(D);
-      TileRange trBnd = trAll, trInt = trAll;
-      if (split) {
-         const int nB = Hl->NTilesBoundary, nO = Hl->NTilesOwned, nH = D.Tiles.NTiles - nO;
-         if (skipHalo) {
-            trBnd = TileRange{Hl->DTileOrder, 0, nB};
-            trInt = TileRange{Hl->DTileOrder, nB, nO - nB};
-         } else {
-            trBnd = TileRange{Hl->DTileOrderBH, 0, nB + nH};
-            trInt = TileRange{Hl->DTileOrderBH, nB + nH, nO - nB};
-         }
+   // shared-memory staged passes (fused_tile.cu) replace fT2 + fC and fE when they apply; fA / fB then write
+   // the combined fields the edge pass differences.  Upwind fluxes, the manufactured sources, wind forcing
+   // and bottom drag all run on the tiled kernels (coefficient selection in the prologues, k_ms_sources,
+   // k_edge_layer_terms).
+   const bool tiledE = V == 2 && tile_edge_path_ok(D) && env_int("OMEGA_TILE_E", 1);
+   const bool tiled  = V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
+   const bool msOn = G.ManufacturedSolutionTendency != 0;
+   const bool drag = G.BottomDragTendencyEnable != 0, wind = G.WindForcingTendencyEnable != 0;
+   const double nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
+   if (msOn && (tiled || tiledE)) {
+      const int n = std::max(D.NCellsAll, D.NEdgesAll);
+      k_ms_sources<<<grid_for(n), kBlock, 0, St>>>(D, manufactured(S, sd.TimeCell), sd.TimeEdge, G.VelDiffTendencyEnable, G.ViscDel2,
+                                                  G.VelHyperDiffTendencyEnable, G.ViscDel4, S->SrcH, S->SrcU);
+      ++S->Launches;
+   }
+   // ---- cell pass first: it depends on the stage state only (and, at stage 0 with raw indexing, on the
+   // stale next-level velocity the edge pass overwrites)
+   CellArgs ca;
+   ca.Hs = sd.Hs; ca.Us = sd.Us; ca.Trs = sd.Trs; ca.Del2Tr = S->A.Del2Tr;
+   ca.UTr = sd.UTr;
+   ca.Hcur = Hcur; ca.Hnext = sd.Hnext; ca.Hprov = sd.Hprov;
+   ca.TrCur = TrCur; ca.TrNext = sd.TrNext; ca.TrProv = sd.TrProv;
+   ca.A = sd.A; ca.B = sd.B;
+   ca.First = sd.First; ca.Last = sd.Last; ca.NTracers = T;
+   ca.WSel = sd.WSel; ca.H2Sel = sd.H2Sel; ca.FinSel = sd.FinSel; ca.DivSel = sd.DivSel;
+   ca.FluxDivOn = G.ThicknessFluxTendencyEnable; ca.AdvOn = G.TracerHorzAdvTendencyEnable;
+   ca.DiffOn = G.TracerDiffTendencyEnable; ca.HypOn = tr4;
+   ca.FluxUpwind = G.FluxThicknessType; ca.TrUpwind = G.FluxTracerType;
+   ca.EddyDiff2 = G.EddyDiff2; ca.EddyDiff4 = G.EddyDiff4;
+   ca.Prefetch = env_int("OMEGA_FC_PREFETCH", 0);
+   ca.MS = manufactured(S, sd.TimeCell);
+   ca.SrcH = msOn ? S->SrcH : nullptr;
+   S->LastPath = OMEGA_PATH_FUSED | (tiled ? OMEGA_PATH_TILED_CELL : 0) | (tiled && tile_v2_used(ca) ? OMEGA_PATH_CELL_V2 : 0) |
+                 (tiledE ? OMEGA_PATH_TILED_EDGE : 0);
+   // With a halo attached (multi-rank): the tiles that hold send-list rows run first in a stage right
+   // before an exchange; once they are done the exchange starts on the halo's own stream (step.cu) while the
+   // interior tiles still compute.  The halo tiles are skipped there -- the exchange overwrites every
+   // non-owned row -- unless the stage's halo rows are read again before that (SkipHaloOK = 0: RK4 stage 1
+   // with raw time-level indexing and CurTimeIndex == 1, SURVEY 3.5 P1: the stage-2 tracer update multiplies
+   // by the ACCUMULATING next-level thickness, whose stage-1 contribution on the first halo layer is valid and
+   // needed); the halo tiles then run with the boundary tiles, ahead of the exchange that writes the same rows.
+   const OmegaHalo *Hl = S->Halo;
+   const bool split = Hl && Hl->DTileOrder && Hl->HaloCovered && tiled && tiledE && sd.BeforeExchange &&
+                      env_int("OMEGA_HALO_OVERLAP", 1);
+   const TileRange trAll = all_tiles(D);
+   TileRange trBnd = trAll, trInt = trAll;
+   if (split) {
+      const int nB = Hl->NTilesBoundary, nO = Hl->NTilesOwned, nH = D.Tiles.NTiles - nO;
+      if (sd.SkipHaloOK) {
+         trBnd = TileRange{Hl->DTileOrder, 0, nB};
+         trInt = TileRange{Hl->DTileOrder, nB, nO - nB};
+      } else {
+         trBnd = TileRange{Hl->DTileOrderBH, 0, nB + nH};
+         trInt = TileRange{Hl->DTileOrderBH, nB + nH, nO - nB};
       }
-      if (split) S->LastPath |= OMEGA_PATH_HALO_SPLIT;
-      {
+      S->LastPath |= OMEGA_PATH_HALO_SPLIT;
+   }
+   if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, sd.Hs, sd.Trs, T, S->A.Del2Tr);
+   {
       ScopedTimer tm_(S, St, kFC);
+      NvtxRange nv_("cell pass");
       const int variant = env_int("OMEGA_FC_VARIANT", 3);
       if (tiled) {
          if (launch_fCT(D, ca, St, trBnd)) return 1;
@@ -981,53 +1068,179 @@ int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs 
          k_fC_center<2, 256, 2><<<fused_grid(D.NCellsAll, D.K, 2, 256, itC), 256, 0, St>>>(D, ca);
       }
       ++S->Launches;
-      }
-      EdgeArgs ea;
-      ea.Hs = Hs; ea.Us = Us; ea.URaw = (s == 0 && swapped) ? Unext : Us;
-      ea.KE = S->A.KE; ea.Div = S->A.Div; ea.RelVort = S->A.RelVort; ea.PVv = S->A.NormRelVort;
-      ea.Del2Div = S->A.Del2Div; ea.Del2RelVort = S->A.Del2RelVort; ea.NormalStress = S->A.NormalStress;
-      ea.Ucur = Ucur; ea.Unext = Unext; ea.Uprov = Up;
-      ea.A = ca.A; ea.B = ca.B; ea.First = ca.First; ea.Last = ca.Last;
-      ea.G = G; ea.MS = ca.MS;
-      EdgeTileArgs ta;
-      if (tiledE) {
-         ScopedTimer tm_(S, St, kFE);
-         ta.Us = Us; ta.Hs = Hs; ta.PVv = S->A.NormRelVort; ta.X = S->A.KE;
-         ta.Y = vel4 ? S->A.Del2Div : S->A.Div; ta.Z = vel4 ? S->A.Del2RelVort : S->A.RelVort;
-         ta.SY = vel4 ? 1.0 : nu2; ta.SZ = ta.SY;
-         ta.Ucur = Ucur; ta.Unext = Unext; ta.Uprov = Up;
-         ta.A = ca.A; ta.B = ca.B; ta.First = ca.First; ta.Last = ca.Last;
-         ta.PVOn = G.PVTendencyEnable; ta.XOn = xOn && !wMerge;
-         if (launch_fET(D, ta, St, trBnd)) return 1;
-         ++S->Launches;
-      } else {
-         // occupancy variants measured on B200 (profiles/r01): 4 CTAs/SM (64 regs, some spills) is fastest
-         const int fev = env_int("OMEGA_FE_VARIANT", 3);
-         ScopedTimer tm_(S, St, kFE);
-         if (V == 1) k_fE<1, 2><<<ge, kBlock, 0, St>>>(D, ea);
-         else if (fev == 2) k_fE<2, 3><<<ge, kBlock, 0, St>>>(D, ea);
-         else if (fev == 3) k_fE<2, 4><<<ge, kBlock, 0, St>>>(D, ea);
-         else k_fE<2, 2><<<ge, kBlock, 0, St>>>(D, ea);
-         ++S->Launches;
-      }
-      if (split) {
-         // boundary tiles of both passes are queued: the exchange may start behind them
-         OMEGA_CUDA_CHECK(cudaEventRecord(Hl->EvReady, St));
-         S->SplitRecorded = 1;
-         {
-            ScopedTimer tm_(S, St, kFC);
-            if (launch_fCT(D, ca, St, trInt)) return 1;
-            ++S->Launches;
-         }
-         {
-            ScopedTimer tm_(S, St, kFE);
-            if (launch_fET(D, ta, St, trInt)) return 1;
-            ++S->Launches;
-         }
-      }
-#undef LAUNCH_V
    }
+   // ---- momentum: aux fields, then the edge pass
+   const double *Hm = sd.HsMom;
+   LAUNCH_V(kFA, k_fA, gA, D, Hm, sd.Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
+            G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0, tiledE && drag ? S->A.ZonalStress2 : nullptr);
+   // W = Y - X folded into fB's cell result when the tiled edge pass follows (one gathered cell field less)
+   const bool xOn    = G.KETendencyEnable || G.SSHTendencyEnable;
+   const bool fB3    = vel4 && D.B3OK && env_int("OMEGA_FB3", 1);
+   const bool wMerge = fB3 && tiledE && xOn && env_int("OMEGA_FUSE_W", 1);
+   if (fB3)
+      LAUNCH_V(kFB, k_fB3, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
+               G.ViscDel4 * G.DivFactor, G.ViscDel4, wMerge ? S->A.KE : nullptr);
+   else if (vel4)
+      LAUNCH_V(kFB, k_fB, gB, D, S->A.Div, S->A.RelVort, S->A.Del2Div, S->A.Del2RelVort, tiledE ? 1 : 0, nu2,
+               G.ViscDel4 * G.DivFactor, G.ViscDel4);
+   EdgeArgs ea;
+   ea.Hs = Hm; ea.Us = sd.Us; ea.URaw = sd.URaw;
+   ea.KE = S->A.KE; ea.Div = S->A.Div; ea.RelVort = S->A.RelVort; ea.PVv = S->A.NormRelVort;
+   ea.Del2Div = S->A.Del2Div; ea.Del2RelVort = S->A.Del2RelVort; ea.NormalStress = S->A.NormalStress;
+   ea.Ucur = Ucur; ea.Unext = sd.Unext; ea.Uprov = sd.Uprov;
+   ea.A = sd.A; ea.B = sd.B; ea.First = sd.First; ea.Last = sd.Last;
+   ea.G = G; ea.MS = manufactured(S, sd.TimeEdge);
+   EdgeTileArgs ta;
+   if (tiledE) {
+      ScopedTimer tm_(S, St, kFE);
+      NvtxRange nv_("edge pass");
+      ta.Us = sd.Us; ta.Hs = Hm; ta.PVv = S->A.NormRelVort; ta.X = S->A.KE;
+      ta.Y = vel4 ? S->A.Del2Div : S->A.Div; ta.Z = vel4 ? S->A.Del2RelVort : S->A.RelVort;
+      ta.SY = vel4 ? 1.0 : nu2; ta.SZ = ta.SY;
+      ta.Ucur = Ucur; ta.Unext = sd.Unext; ta.Uprov = sd.Uprov;
+      ta.A = sd.A; ta.B = sd.B; ta.First = sd.First; ta.Last = sd.Last;
+      ta.PVOn = G.PVTendencyEnable; ta.XOn = xOn && !wMerge;
+      ta.FluxUpwind = G.FluxThicknessType; ta.SrcU = msOn ? S->SrcU : nullptr;
+      if (launch_fET(D, ta, St, trBnd)) return 1;
+      ++S->Launches;
+   } else {
+      // occupancy variants measured on B200 (profiles/r01): 4 CTAs/SM (64 regs, some spills) is fastest
+      const int fev = env_int("OMEGA_FE_VARIANT", 3);
+      ScopedTimer tm_(S, St, kFE);
+      NvtxRange nv_("edge pass");
+      if (V == 1) k_fE<1, 2><<<ge, kBlock, 0, St>>>(D, ea);
+      else if (fev == 2) k_fE<2, 3><<<ge, kBlock, 0, St>>>(D, ea);
+      else if (fev == 3) k_fE<2, 4><<<ge, kBlock, 0, St>>>(D, ea);
+      else k_fE<2, 2><<<ge, kBlock, 0, St>>>(D, ea);
+      ++S->Launches;
+   }
+   if (split) {
+      // boundary tiles of both passes are queued: the exchange may start behind them.  (The single-layer
+      // wind / drag correction below touches send rows too, so it must precede the event.)
+      if (wind || drag) {
+         k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
+                                                                     1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
+                                                                     trBnd, D.Tiles.EdgeRows, D.Tiles.Hdr);
+         ++S->Launches;
+      }
+      OMEGA_CUDA_CHECK(cudaEventRecord(Hl->EvReady, St));
+      S->SplitRecorded = 1;
+      {
+         ScopedTimer tm_(S, St, kFC);
+         if (launch_fCT(D, ca, St, trInt)) return 1;
+         ++S->Launches;
+      }
+      {
+         ScopedTimer tm_(S, St, kFE);
+         if (launch_fET(D, ta, St, trInt)) return 1;
+         ++S->Launches;
+      }
+      if (wind || drag) {
+         k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
+                                                                     1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
+                                                                     trInt, D.Tiles.EdgeRows, D.Tiles.Hdr);
+         ++S->Launches;
+      }
+   } else if (tiledE && (wind || drag)) {
+      k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
+                                                                  1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
+                                                                  TileRange{nullptr, 0, 0}, nullptr, nullptr);
+      ++S->Launches;
+   }
+#undef LAUNCH_V
    OMEGA_CUDA_CHECK(cudaGetLastError());
+   return 0;
+}
+
+static inline int tix(int Level, int Cur, int NTL) { return (Level + Cur + NTL) % NTL; }
+
+// One phase (everything up to the next halo exchange point) of a stepper on the fused kernels:
+// RungeKutta4Stepper.cpp:68-137 (two phases), RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:49-68.
+int fused_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
+                cudaStream_t St) {
+   const DMesh &D           = S->M->D;
+   const OmegaTendConfig &G = S->Cfg;
+   OMEGA_REQUIRE(S->M->MaxEdgesUsed <= kME, "fused path supports at most 6 edges per cell; use Fused=0");
+   const int ci = X->CurTimeIndex, ni = tix(1, ci, 2);
+   const int tci = X->TracerCurTimeIndex, tni = tix(1, tci, 2);
+   double *Hcur = X->LayerThickness[ci], *Hnext = X->LayerThickness[ni];
+   double *Ucur = X->NormalVelocity[ci], *Unext = X->NormalVelocity[ni];
+   double *TrCur = X->Tracers[tci], *TrNext = X->Tracers[tni];
+   // raw time-level indexing of the reference: with CurTimeIndex == 1 the "current" raw
+   // slot is the NEXT buffer and vice versa
+   const bool swapped = Compat && ci == 1;
+   S->ProvisExchangeSlot = 0;
+   Launch L{St, &S->Launches};
+   if (G.WindForcingTendencyEnable && Phase == 0) launch_wind_aux(L, D, S->A, G.WindStressInterpType);
+   StageDesc sd;
+   std::memset(&sd, 0, sizeof(sd));
+   if (Type == OMEGA_STEPPER_RK4) {
+      const int s0 = Phase == 0 ? 0 : 2, s1 = Phase == 0 ? 1 : 3;
+      for (int s = s0; s <= s1; ++s) {
+         NvtxRange nv_(s == 0 ? "RK4 stage 0" : s == 1 ? "RK4 stage 1" : s == 2 ? "RK4 stage 2" : "RK4 stage 3");
+         // provisional state of stage s lives in P[s % 2] (stage 2 -> slot 0, the exchanged one)
+         sd.Hs = s == 0 ? Hcur : S->P.H[s % 2];
+         sd.Us = s == 0 ? Ucur : S->P.U[s % 2];
+         sd.Trs = s == 0 ? TrCur : S->P.Tr[s % 2];
+         sd.HsMom = sd.Hs;
+         sd.Hprov = s == 3 ? nullptr : S->P.H[(s + 1) % 2];
+         sd.Uprov = s == 3 ? nullptr : S->P.U[(s + 1) % 2];
+         sd.TrProv = s == 3 ? nullptr : S->P.Tr[(s + 1) % 2];
+         sd.Hnext = Hnext; sd.Unext = Unext; sd.TrNext = TrNext;
+         sd.UTr = (s == 0 && swapped) ? Unext : sd.Us;
+         sd.URaw = sd.UTr;
+         sd.A = s < 3 ? C->A[s + 1] : 0.0; sd.B = C->B[s];
+         sd.TimeCell = sd.TimeEdge = C->StageTime[s];
+         sd.First = s == 0; sd.Last = s == 3;
+         sd.WSel = swapped; sd.H2Sel = swapped; sd.FinSel = swapped; sd.DivSel = 0;
+         sd.BeforeExchange = s == 1 || s == 3;
+         sd.SkipHaloOK = s == 3 || !swapped;
+         if (run_stage(S, sd, Hcur, Ucur, TrCur, St)) return 1;
+      }
+   } else if (Type == OMEGA_STEPPER_RK2) {
+      // both stages are "prov = cur + c R(in)": stage 0 into the provisional slot, stage 1 into the next-level arrays
+      // (the reference overwrites the next level in place, its tendencies sit in separate arrays).  Tracers:
+      // (cur * hraw(Cur) + c tend) / hraw(Next) -- raw slots, so with CurTimeIndex == 1 the roles of the
+      // current and the freshly updated thickness swap (RungeKutta2Stepper.cpp:44-47,64-67; P1).
+      for (int s = 0; s < 2; ++s) {
+         NvtxRange nv_(s == 0 ? "RK2 stage 0" : "RK2 stage 1");
+         sd.Hs = s == 0 ? Hcur : S->P.H[0];
+         sd.Us = s == 0 ? Ucur : S->P.U[0];
+         sd.Trs = s == 0 ? TrCur : S->P.Tr[0];
+         sd.HsMom = sd.Hs;
+         sd.Hprov = s == 0 ? S->P.H[0] : Hnext;
+         sd.Uprov = s == 0 ? S->P.U[0] : Unext;
+         sd.TrProv = s == 0 ? S->P.Tr[0] : TrNext;
+         sd.Hnext = S->P.H[1]; sd.Unext = S->P.U[1]; sd.TrNext = S->P.Tr[1]; // sink (B = 0)
+         // velocity by raw index VelTimeLevel: stage 0 raw 0, stage 1 raw 1
+         sd.UTr = !swapped ? sd.Us : (s == 0 ? Unext : Ucur);
+         sd.URaw = sd.UTr;
+         sd.A = s == 0 ? C->A[1] : C->B[1]; sd.B = 0.0;
+         sd.TimeCell = sd.TimeEdge = C->StageTime[s];
+         sd.First = s == 0; sd.Last = 0;
+         sd.WSel = 0; sd.FinSel = 0;
+         sd.H2Sel = swapped ? 2 : 0; sd.DivSel = swapped ? 1 : 0;
+         sd.BeforeExchange = s == 1; sd.SkipHaloOK = 1;
+         if (run_stage(S, sd, Hcur, Ucur, TrCur, St)) return 1;
+      }
+   } else {
+      // forward-backward: thickness and tracers from the current state, then the velocity tendency on the NEW
+      // thickness (ForwardBackwardStepper.cpp:49-68).  With raw indexing and CurTimeIndex == 1 the tracer
+      // fluxes would see the new thickness while the thickness flux sees the old one; step.cu sends that case
+      // to the kernel-per-term path.
+      NvtxRange nv_("forward-backward");
+      sd.Hs = Hcur; sd.Us = Ucur; sd.Trs = TrCur;
+      sd.HsMom = Hnext;
+      sd.Hprov = Hnext; sd.Uprov = Unext; sd.TrProv = TrNext;
+      sd.Hnext = S->P.H[1]; sd.Unext = S->P.U[1]; sd.TrNext = S->P.Tr[1]; // sink (B = 0)
+      sd.UTr = Ucur; sd.URaw = Ucur;
+      sd.A = C->Dt; sd.B = 0.0;
+      sd.TimeCell = C->StageTime[0]; sd.TimeEdge = C->StageTime[1];
+      sd.First = 1; sd.Last = 0;
+      sd.WSel = 0; sd.FinSel = 0; sd.H2Sel = 0; sd.DivSel = 0;
+      sd.BeforeExchange = 1; sd.SkipHaloOK = 1;
+      if (run_stage(S, sd, Hcur, Ucur, TrCur, St)) return 1;
+   }
    return 0;
 }
 

@@ -13,12 +13,14 @@ struct CellArgs {
    double A, B;                                // a_{s+1} dt, b_s dt
    int First, Last, NTracers;
    int WSel;   // stage-0 weight thickness: 0 = Hcur, 1 = Hnext before this stage writes it
-   int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext
+   int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext, 2 = new Hprov
+   int DivSel; // thickness dividing the provisional tracers: 0 = new Hprov, 1 = Hcur (RK2 with raw time-level indexing)
    int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
    int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
    int Prefetch; // 0 off, 1 next tracer's rows into L1, 2 into L2
    double EddyDiff2, EddyDiff4;
    ManufacturedParams MS;
+   const double *SrcH; // tiled kernels: manufactured thickness source per cell (k_ms_sources), nullptr when off
 };
 
 constexpr int kME = 6; // max edges per cell on the fused path (checked at launch)
@@ -43,6 +45,8 @@ struct EdgeTileArgs {
    double *Unext, *Uprov;
    double A, B;
    int First, Last, PVOn, XOn;
+   int FluxUpwind;     // FluxLayerThickEdge upwinded on the sign of u (LayerThicknessAuxVars.h:25-61)
+   const double *SrcU; // manufactured velocity source per edge (k_ms_sources), nullptr when off
 };
 
 // tiles Map[First .. First + Count) of the mesh (Map == nullptr: tiles First .. First + Count)

@@ -361,19 +361,23 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
 #pragma unroll
          for (int q = 0; q < 2; ++q) {
             const double mean = 0.5 * (hh[q] + hn[q]);
-            hT[q] += cfu * mean * us[j][q] * InvA;
+            // upwind options (LayerThicknessAuxVars.h:25-61, TracerAuxVars.h:25-59): the edge value is the one
+            // of the cell the stage velocity comes from; cell 0 of the edge is this cell iff the sign is -1
+            // (HorzMesh.cpp:536-548).  u == 0 multiplies either choice by zero.
+            const bool out = (cfu < 0.0) == (us[j][q] > 0.0); // flow leaves this cell through edge j
+            const double fl = P.FluxUpwind ? (out ? hh[q] : hn[q]) : mean;
+            hT[q] += cfu * fl * us[j][q] * InvA;
             const double w = wa * (sameU ? us[j][q] : ut[j][q]) * InvA;
             const double D = cd * mean;
-            E[j][q]        = 0.5 * hn[q] * w - D;
-            S0[q] += 0.5 * hh[q] * w + D;
+            const double as = P.TrUpwind ? (out ? 1.0 : 0.0) : 0.5;
+            E[j][q]        = (P.TrUpwind ? 1.0 - as : 0.5) * hn[q] * w - D;
+            S0[q] += as * hh[q] * w + D;
          }
       }
    }
    if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
-   if (P.MS.Enabled) {
-      const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
-      const double src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
-                                      P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * cos(2.0 * Phase));
+   if (P.SrcH) { // manufactured thickness source (CustomTendencyTerms.cpp:107-143), evaluated per cell by k_ms_sources
+      const double src = P.SrcH[c];
       hT[0] += src;
       hT[1] += src;
    }
@@ -394,8 +398,8 @@ __device__ __forceinline__ void role_T(const DMesh &M, const CellArgs &P, TileSm
          hnext[q] = (First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
          hprov[q] = hcur[q] + P.A * hT[q];
          const double hx  = First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
-         const double h2  = P.H2Sel ? hnext[q] : hcur[q];
-         const double rhp = 1.0 / hprov[q];
+         const double h2  = P.H2Sel == 2 ? hprov[q] : (P.H2Sel ? hnext[q] : hcur[q]);
+         const double rhp = 1.0 / (P.DivSel ? hcur[q] : hprov[q]);
          w0[q] = Last ? 1.0 / hx : hx;
          w1[q] = h2 * rhp;
          w2[q] = P.A * rhp;
@@ -830,15 +834,19 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                const double mean = 0.5 * (hh[q] + hn[q]);
-               hT[q] += cfu * mean * us[j][q] * InvA;
+               // upwind options: see role_T (the tracer edge value upwinds on the STAGE velocity, TracerAuxVars.h:25-59)
+               const bool out  = (cfu < 0.0) == (us[j][q] > 0.0);
+               const double fl = P.FluxUpwind ? (out ? hh[q] : hn[q]) : mean;
+               const double as = P.TrUpwind ? (out ? 1.0 : 0.0) : 0.5, an = P.TrUpwind ? 1.0 - as : 0.5;
+               hT[q] += cfu * fl * us[j][q] * InvA;
                const double w = wa * us[j][q] * InvA;
                const double D = cd * mean;
-               E[j][q]        = 0.5 * hn[q] * w - D;
-               S0[q] += 0.5 * hh[q] * w + D;
+               E[j][q]        = an * hn[q] * w - D;
+               S0[q] += as * hh[q] * w + D;
                if (!sameU && P.AdvOn) {
                   const double dw = wa * (ua[q] - us[j][q]) * InvA;
-                  E[j][q] += 0.5 * hn[q] * dw;
-                  S0[q] += 0.5 * hh[q] * dw;
+                  E[j][q] += an * hn[q] * dw;
+                  S0[q] += as * hh[q] * dw;
                }
             }
          }
@@ -859,6 +867,11 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          }
       }
       if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
+      if (P.SrcH) { // manufactured thickness source per cell (k_ms_sources)
+         const double src = P.SrcH[c];
+         hT[0] += src;
+         hT[1] += src;
+      }
       // thickness updates (updateThicknessByTend, TimeStepper.cpp:378-405) and the per-level
       // constants of the tracer updates (TimeStepper.cpp:446-524), as in role_T
       {
@@ -873,8 +886,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             hnext[q] = (First ? hcur[q] : hnext_old[q]) + P.B * hT[q];
             hprov[q] = hcur[q] + P.A * hT[q];
             const double hx  = First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
-            const double h2  = P.H2Sel ? hnext[q] : hcur[q];
-            const double rhp = 1.0 / hprov[q];
+            const double h2  = P.H2Sel == 2 ? hprov[q] : (P.H2Sel ? hnext[q] : hcur[q]);
+            const double rhp = 1.0 / (P.DivSel ? hcur[q] : hprov[q]);
             w0[q] = Last ? 1.0 / hx : hx;
             w1[q] = h2 * rhp;
             w2[q] = P.A * rhp;
@@ -1086,8 +1099,8 @@ int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRa
 
 bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
 bool tile_v2_enabled() { return env_i("OMEGA_TILE_V2", 1) != 0; }
-// k_fCT2 serves every tracer count with tracer hyperdiffusion on (no manufactured thickness source)
-bool tile_v2_used(const CellArgs &ca) { return ca.HypOn && tile_v2_enabled() && ca.NTracers >= 1 && !ca.MS.Enabled; }
+// k_fCT2 serves every tracer count with tracer hyperdiffusion on
+bool tile_v2_used(const CellArgs &ca) { return ca.HypOn && tile_v2_enabled() && ca.NTracers >= 1; }
 
 // ---------------------------------------------------------------------------
 // k_fET: shared-memory staged edge pass (the work of k_fE, fused.cu).  A CTA owns the
@@ -1192,7 +1205,12 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    };
    auto put = [&](int r, const double (&u)[2], const double (&h0)[2], const double (&h1)[2], const double (&a)[2],
                   const double (&b)[2]) {
-      *reinterpret_cast<double2 *>(&S.F[r][2 * p]) = make_double2(0.5 * (h0[0] + h1[0]) * u[0], 0.5 * (h0[1] + h1[1]) * u[1]);
+      double f0 = 0.5 * (h0[0] + h1[0]), f1 = 0.5 * (h0[1] + h1[1]);
+      if (P.FluxUpwind) { // u == 0: F = flux * u = 0 for either choice (the reference takes max(h0, h1))
+         f0 = u[0] > 0 ? h0[0] : h1[0];
+         f1 = u[1] > 0 ? h0[1] : h1[1];
+      }
+      *reinterpret_cast<double2 *>(&S.F[r][2 * p]) = make_double2(f0 * u[0], f1 * u[1]);
       *reinterpret_cast<double2 *>(&S.Q[r][2 * p]) = make_double2(0.5 * (a[0] + b[0]), 0.5 * (a[1] + b[1]));
    };
    for (int q = tid; q < nSt * kTLanes; q += 2 * kEThreads) {
@@ -1220,6 +1238,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
          const int4 cv  = S.CV[r];
          const double mask = M.EdgeMask[e];
          const double InvDc = M.InvDcEdge[e] * mask, InvDv = M.InvDvEdge[e] * mask;
+         const double srcu = P.SrcU ? P.SrcU[e] : 0.0; // manufactured velocity source (not masked, CustomTendencyTerms.cpp:145-210)
          if (P.PVOn) prefetch_row(M.WeightsOnEdge + (size_t)e * M.MaxEdges2 + p, 1); // weights towards L1 for pass 2b
          double x0[2] = {0, 0}, x1[2] = {0, 0}, y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
          if (P.XOn) { // off when k_fB3 already folded X into Y (W = Y - X)
@@ -1236,6 +1255,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
          for (int q2 = 0; q2 < 2; ++q2) {
             double g = (P.SY * (y1[q2] - y0[q2])) * InvDc - (P.SZ * (z1[q2] - z0[q2])) * InvDv;
             if (P.XOn) g -= (x1[q2] - x0[q2]) * InvDc;
+            g += srcu;
             p1[it][q2] = (P.First ? ucur[q2] : base[q2]) + P.B * g;
             p2[it][q2] = ucur[q2] + P.A * g;
          }

@@ -146,6 +146,7 @@ struct AuxPtrs {
    double *KE, *Div, *Flux, *Mean, *Ssh, *RelVort, *NormRelVort, *NormPlanetVort, *NormRelVortEdge,
        *NormPlanetVortEdge, *Del2Edge, *Del2Div, *Del2RelVort, *HTr, *Del2Tr, *NormalStress,
        *ZonalStress, *MeridStress;
+   double *ZonalStress2; // [NCellsSize] scratch of the fused path: kinetic energy of the bottom layer (bottom drag)
 };
 
 struct Launch {

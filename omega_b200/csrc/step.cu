@@ -130,8 +130,11 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
    int rc;
    S->LastPath = 0;
    S->SplitRecorded = 0;
-   if (Type == OMEGA_STEPPER_RK4 && Fused)
-      rc = fused_rk4_phase(S, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
+   // forward-backward with raw time-level indexing and CurTimeIndex == 1: the tracer fluxes see the NEW thickness
+   // while the thickness flux sees the old one (ForwardBackwardStepper.cpp:55-60, P1): not one fused cell pass
+   const bool fbRaw = Type == OMEGA_STEPPER_FB && RawTimeLevelCompat && State->CurTimeIndex == 1;
+   if (Fused && !fbRaw)
+      rc = fused_phase(S, Type, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
    else if (Type == OMEGA_STEPPER_RK4)
       rc = rk4_phase(X, State, Coeffs, Phase);
    else if (Type == OMEGA_STEPPER_RK2)

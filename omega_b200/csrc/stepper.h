@@ -18,6 +18,7 @@ struct OmegaStepper {
    omega::AuxPtrs A;
    OmegaTendArrays T;
    ProvisArrays P;
+   double *SrcH, *SrcU; // manufactured sources per cell / edge of the current stage (fused tiled path)
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
    int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
@@ -35,7 +36,7 @@ enum FusedKernel { kFA = 0, kFB = 1, kFT2 = 2, kFC = 3, kFE = 4, kNumFused = 5 }
 int stepper_alloc(OmegaStepper *S, double **p, size_t n);
 ManufacturedParams manufactured(const OmegaStepper *S, double Time);
 int ensure_htr(OmegaStepper *S);
-// fused.cu: one RK4 phase on the fused per-stage pipeline
-int fused_rk4_phase(OmegaStepper *S, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase, int Compat,
-                    cudaStream_t Stream);
+// fused.cu: one phase of RK4 / RK2 / forward-backward on the fused per-stage pipeline
+int fused_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *X, const OmegaStepCoeffs *C, int Phase,
+                int Compat, cudaStream_t Stream);
 } // namespace omega

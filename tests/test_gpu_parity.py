@@ -208,6 +208,23 @@ def test_rk4_fused_path(case, compat):
     assert max(errs) <= TOL_STATE, (name, errs)
 
 
+@pytest.mark.parametrize("stepper", [capi.RK2, capi.FB])
+@pytest.mark.parametrize("compat", [True, False])
+def test_rk2_and_forward_backward_fused_path(case, stepper, compat):
+    """RungeKutta2Stepper.cpp:27-73 and ForwardBackwardStepper.cpp:49-68 on the fused kernels
+    (tiled where the case allows).  Forward-backward with raw time-level indexing takes the kernel-per-term
+    path on odd steps (its tracer fluxes then see another thickness than its thickness flux), so five steps
+    mix both paths there."""
+    name, (L, cfg, init, dt) = case
+    errs = run_steps(L, cfg, init, dt, stepper, 5, fused=True, compat=compat)
+    assert max(errs) <= TOL_STATE, (name, errs)
+    if name in TILED and not (stepper == capi.FB and compat):
+        # the last step ran fused on the tiled kernels
+        errs = run_steps(L, cfg, init, dt, stepper, 2, fused=True, compat=compat,
+                         want_path=PATH_FUSED | PATH_TILED_CELL | PATH_TILED_EDGE)
+        assert max(errs) <= TOL_STATE, (name, errs)
+
+
 def test_rk4_100_steps_state_parity():
     """BASELINE.json: prognostic state after 100 RK4 steps, relative L2 <= 1e-10 (untiled kernels: K = 8)."""
     L, cfg, init, dt = cases.sphere_case(3, 8, 3)
@@ -225,10 +242,54 @@ def test_rk4_100_steps_state_parity_tiled_kernels(compat):
     assert max(errs) <= TOL_STATE, errs
 
 
+@pytest.mark.parametrize("compat", [True, False])
+@pytest.mark.parametrize("terms", ["upwind", "wind_drag", "all"])
+def test_fused_tiled_kernels_with_optional_terms(terms, compat):
+    """upwind flux options, wind forcing and bottom drag ON THE TILED fused kernels (k_fCT2 /
+    k_fET coefficient selection, k_edge_layer_terms), five RK4 steps against the oracle; the path is asserted."""
+    from tests.oracle_lib import Oracle
+    kw = {}
+    if terms in ("upwind", "all"):
+        kw.update(FluxThicknessType=1, FluxTracerType=1)
+    if terms in ("wind_drag", "all"):
+        kw.update(WindForcingTendencyEnable=1, BottomDragTendencyEnable=1, BottomDragCoeff=1.0e-3)
+    L, cfg, (h, u, tr), dt = cases.sphere_case(3, 16, 3, **kw)
+    zonal = np.ascontiguousarray(0.1 * np.cos(L.LatCell)); zonal[-1] = 0.0
+    merid = np.ascontiguousarray(0.05 * np.sin(2 * L.LonCell) * np.cos(L.LatCell)); merid[-1] = 0.0
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T)
+    o = Oracle(L, cfg, T)
+    o.set_wind_stress(zonal, merid); st.set_wind_stress(zonal, merid)
+    o.make_state(h, u, tr); state.copyToDevice(h, u, tr)
+    co = capi.rk_coeffs(capi.RK4, dt)
+    for _ in range(5):
+        o.do_step(capi.RK4, co, compat=int(compat))
+        st.doStep(state, capi.RK4, co, fused=True, compat=compat)
+    want = PATH_FUSED | PATH_TILED_CELL | PATH_CELL_V2 | PATH_TILED_EDGE
+    assert st.last_path() & want == want, st.last_path()
+    got, exp = state.copyToHost(0), o.current()
+    errs = [rel_l2(a, b) for a, b in zip(got, exp)]
+    o.close(); st.close(); mesh.close()
+    assert max(errs) <= TOL_STATE, (terms, errs)
+
+
+@pytest.mark.parametrize("T", [1, 2])
+def test_fused_tiled_kernels_with_manufactured_sources(T):
+    """The manufactured source terms on the tiled kernels (k_ms_sources feeds k_fCT2 / k_fET), K = 16."""
+    from omega_b200 import analytic
+    L, cfg, _, dt = cases.plane_case(16, 16, T, ManufacturedSolutionTendency=1, ManufacturedWavelengthX=16 * 5.0e6 / 64,
+                                     ManufacturedWavelengthY=16 * 5.0e6 / 64 * np.sqrt(3) / 2)
+    h, u = analytic.manufactured(L, cfg)
+    tr = np.ascontiguousarray(analytic.planar_state(L, T)[2])
+    want = PATH_FUSED | PATH_TILED_CELL | PATH_CELL_V2 | PATH_TILED_EDGE
+    errs = run_steps(L, cfg, (h, u, tr), dt, capi.RK4, 5, fused=True, compat=True, want_path=want)
+    assert max(errs) <= TOL_STATE, errs
+
+
 def test_fused_manufactured_one_tracer_with_del4():
-    """Manufactured thickness source + ONE tracer + tracer hyperdiffusion at K = 32: k_fCT2 has no
-    manufactured source and k_fCT's Del2 role needs two tracers, so this must take the untiled cell pass
-    (it used to reach k_fCT and read past the tracer array)."""
+    """Manufactured thickness source + ONE tracer + tracer hyperdiffusion at K = 32 (this used to
+    reach k_fCT, whose Del2 role needs two tracers, and read past the tracer array).  k_fCT2 now takes the
+    source per cell from k_ms_sources; with OMEGA_TILE_V2=0 the case must fall back to the untiled cell pass."""
     L, cfg, _, dt = cases.plane_case(16, 32, 1, ManufacturedSolutionTendency=1, ManufacturedWavelengthX=16 * 5.0e6 / 64,
                                      ManufacturedWavelengthY=16 * 5.0e6 / 64 * np.sqrt(3) / 2)
     from omega_b200 import analytic
@@ -411,6 +472,38 @@ def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
         ex.close(); st.close(); m.close()
     ref.close()
     assert worst <= TOL_STATE, worst
+
+
+@pytest.mark.parametrize("T,v2", [(1, "1"), (2, "1"), (3, "1"), (5, "1"), (10, "1"), (2, "0"), (5, "0")])
+def test_tiled_kernels_bit_reproducible_and_stay_in_bounds(monkeypatch, T, v2):
+    """compute-sanitizer is closed on this GPU pool, so the named-barrier / setmaxnreg / cp.async protocols
+    of fused_tile.cu are checked the way a race or a stray store would show: the same three fused steps run
+    three times from the same state must give bit-identical results (k_fCT2 with its short and long copy
+    schedules, and the older k_fCT with OMEGA_TILE_V2=0) and the boundary-slot rows (row N*All, zero by
+    construction, Decomp.cpp:1081-1082) must stay exactly zero
+    untouched where the step must not write."""
+    monkeypatch.setenv("OMEGA_TILE_V2", v2)
+    L, cfg, (h, u, tr), dt = cases.sphere_case(4, 32, T)
+    co = capi.rk_coeffs(capi.RK4, dt)
+    runs = []
+    mesh, st, state = gpu_objects(L, cfg, T)
+    for rep in range(3):
+        state.c.CurTimeIndex = 0
+        state.c.TracerCurTimeIndex = 0
+        state.copyToDevice(h, u, tr)
+        for _ in range(3):
+            st.doStep(state, capi.RK4, co, fused=True, compat=True)
+        assert st.last_path() & (PATH_TILED_CELL | PATH_TILED_EDGE) == PATH_TILED_CELL | PATH_TILED_EDGE
+        gh, gu, gt = state.copyToHost(0)
+        runs.append((gh.copy(), gu.copy(), gt.copy()))
+        for a in (gh, gu):
+            assert np.all(a[-1] == 0.0), "boundary slot row written"
+        assert np.all(gt[:, -1] == 0.0), "boundary slot row of a tracer written"
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+    for a, b in zip(runs[0], runs[2]):
+        assert np.array_equal(a, b)
+    st.close(); mesh.close()
 
 
 @pytest.mark.parametrize("nranks", [2, 4, 8])
