@@ -857,19 +857,11 @@ k_ms_sources(DMesh M, ManufacturedParams MS, double TimeEdge, int Del2On, double
 __global__ void __launch_bounds__(kBlock)
 k_edge_layer_terms(DMesh M, const double *__restrict__ Hs, const double *__restrict__ URaw,
                    const double *__restrict__ KEBot, const double *__restrict__ NormalStress, int WindOn, int DragOn,
-                   double InvRho0, double Cd, double *__restrict__ Unext, double *__restrict__ Uprov, double A, double B,
-                   TileRange TR, const int *__restrict__ EdgeRows, const TileHdr *__restrict__ Hdr) {
-   // EdgeRows == nullptr: every edge once; else the OWN edges of the tiles of TR (halo split: the same edges,
-   // in the same two groups, as the two launches of the tiled edge pass)
-   int e = blockIdx.x * blockDim.x + threadIdx.x;
-   if (EdgeRows) {
-      // thread -> (tile of the range, own edge slot): kTileEdgesOwn slots per tile
-      const int t = e / kTileEdgesOwn, q = e - t * kTileEdgesOwn;
-      if (t >= TR.Count) return;
-      const TileHdr h = Hdr[TR.tile(t)];
-      if (q >= h.NEOwn) return;
-      e = EdgeRows[h.ERowOff + q];
-   } else if (e >= M.NEdgesAll) return;
+                   double InvRho0, double Cd, double *__restrict__ RTop, double *__restrict__ RBot) {
+   // evaluated BEFORE the edge pass: with raw time-level indexing URaw may be the next-level array the edge
+   // pass is about to overwrite
+   const int e = blockIdx.x * blockDim.x + threadIdx.x;
+   if (e >= M.NEdgesAll) return;
    const int2 cc     = M.CellsOnEdge[e];
    const double mask = M.EdgeMask[e];
    const int K = M.K, KBot = K - 1;
@@ -883,11 +875,31 @@ k_edge_layer_terms(DMesh M, const double *__restrict__ Hs, const double *__restr
       const double InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K + KBot] + Hs[(size_t)cc.y * K + KBot]));
       rb = -mask * Cd * VelNorm * InvThick * URaw[(size_t)e * K + KBot];
    }
-   const size_t o = (size_t)e * K;
    if (KBot == 0) {
       r0 += rb;
       rb = 0.0;
    }
+   RTop[e] = r0;
+   RBot[e] = rb;
+}
+
+__global__ void __launch_bounds__(kBlock)
+k_edge_layer_apply(DMesh M, const double *__restrict__ RTop, const double *__restrict__ RBot, double *__restrict__ Unext,
+                   double *__restrict__ Uprov, double A, double B, TileRange TR, const int *__restrict__ EdgeRows,
+                   const TileHdr *__restrict__ Hdr) {
+   // EdgeRows == nullptr: every edge once; else the OWN edges of the tiles of TR (halo split: the same edges,
+   // in the same two groups, as the two launches of the tiled edge pass)
+   int e = blockIdx.x * blockDim.x + threadIdx.x;
+   if (EdgeRows) {
+      const int t = e / kTileEdgesOwn, q = e - t * kTileEdgesOwn; // kTileEdgesOwn slots per tile
+      if (t >= TR.Count) return;
+      const TileHdr h = Hdr[TR.tile(t)];
+      if (q >= h.NEOwn) return;
+      e = EdgeRows[h.ERowOff + q];
+   } else if (e >= M.NEdgesAll) return;
+   const int K = M.K, KBot = K - 1;
+   const double r0 = RTop[e], rb = RBot[e];
+   const size_t o = (size_t)e * K;
    if (r0 != 0.0) {
       Unext[o] += B * r0;
       if (Uprov) Uprov[o] += A * r0;
@@ -1091,6 +1103,11 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
    ea.A = sd.A; ea.B = sd.B; ea.First = sd.First; ea.Last = sd.Last;
    ea.G = G; ea.MS = manufactured(S, sd.TimeEdge);
    EdgeTileArgs ta;
+   if (tiledE && (wind || drag)) {
+      k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
+                                                                  1.0 / G.Density0, G.BottomDragCoeff, S->RTop, S->RBot);
+      ++S->Launches;
+   }
    if (tiledE) {
       ScopedTimer tm_(S, St, kFE);
       NvtxRange nv_("edge pass");
@@ -1117,10 +1134,9 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
    if (split) {
       // boundary tiles of both passes are queued: the exchange may start behind them.  (The single-layer
       // wind / drag correction below touches send rows too, so it must precede the event.)
-      if (wind || drag) {
-         k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
-                                                                     1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
-                                                                     trBnd, D.Tiles.EdgeRows, D.Tiles.Hdr);
+      if ((wind || drag) && trBnd.Count > 0) {
+         k_edge_layer_apply<<<grid_for((long long)trBnd.Count * kTileEdgesOwn), kBlock, 0, St>>>(D, S->RTop, S->RBot, sd.Unext, sd.Uprov, sd.A,
+                                                                                                sd.B, trBnd, D.Tiles.EdgeRows, D.Tiles.Hdr);
          ++S->Launches;
       }
       OMEGA_CUDA_CHECK(cudaEventRecord(Hl->EvReady, St));
@@ -1135,15 +1151,13 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
          if (launch_fET(D, ta, St, trInt)) return 1;
          ++S->Launches;
       }
-      if (wind || drag) {
-         k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
-                                                                     1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
-                                                                     trInt, D.Tiles.EdgeRows, D.Tiles.Hdr);
+      if ((wind || drag) && trInt.Count > 0) {
+         k_edge_layer_apply<<<grid_for((long long)trInt.Count * kTileEdgesOwn), kBlock, 0, St>>>(D, S->RTop, S->RBot, sd.Unext, sd.Uprov, sd.A,
+                                                                                                sd.B, trInt, D.Tiles.EdgeRows, D.Tiles.Hdr);
          ++S->Launches;
       }
    } else if (tiledE && (wind || drag)) {
-      k_edge_layer_terms<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, Hm, ea.URaw, S->A.ZonalStress2, S->A.NormalStress, wind, drag,
-                                                                  1.0 / G.Density0, G.BottomDragCoeff, sd.Unext, sd.Uprov, sd.A, sd.B,
+      k_edge_layer_apply<<<grid_for(D.NEdgesAll), kBlock, 0, St>>>(D, S->RTop, S->RBot, sd.Unext, sd.Uprov, sd.A, sd.B,
                                                                   TileRange{nullptr, 0, 0}, nullptr, nullptr);
       ++S->Launches;
    }

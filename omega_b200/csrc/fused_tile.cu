@@ -758,7 +758,9 @@ __device__ __forceinline__ void stg_na(double *p, const double (&r)[2]) {
 }
 
 // T role of k_fCT2
-template <class C, int STAGE>
+// OPT: the optional terms (upwind flux options, manufactured thickness source) are compiled in; the default
+// instantiation keeps them out of the prologue's register budget
+template <class C, int STAGE, bool OPT>
 __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typename C::Smem &S, const TileCtx &X, int NCh, int tid,
                                         int kb) {
    constexpr bool First = STAGE == 0, Last = STAGE == 2;
@@ -836,8 +838,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
                const double mean = 0.5 * (hh[q] + hn[q]);
                // upwind options: see role_T (the tracer edge value upwinds on the STAGE velocity, TracerAuxVars.h:25-59)
                const bool out  = (cfu < 0.0) == (us[j][q] > 0.0);
-               const double fl = P.FluxUpwind ? (out ? hh[q] : hn[q]) : mean;
-               const double as = P.TrUpwind ? (out ? 1.0 : 0.0) : 0.5, an = P.TrUpwind ? 1.0 - as : 0.5;
+               const double fl = OPT && P.FluxUpwind ? (out ? hh[q] : hn[q]) : mean;
+               const double as = OPT && P.TrUpwind ? (out ? 1.0 : 0.0) : 0.5, an = OPT && P.TrUpwind ? 1.0 - as : 0.5;
                hT[q] += cfu * fl * us[j][q] * InvA;
                const double w = wa * us[j][q] * InvA;
                const double D = cd * mean;
@@ -867,7 +869,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          }
       }
       if (!P.FluxDivOn) hT[0] = hT[1] = 0.0;
-      if (P.SrcH) { // manufactured thickness source per cell (k_ms_sources)
+      if (OPT && P.SrcH) { // manufactured thickness source per cell (k_ms_sources)
          const double src = P.SrcH[c];
          hT[0] += src;
          hT[1] += src;
@@ -998,7 +1000,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    }
 }
 
-template <class C, int STAGE>
+template <class C, int STAGE, bool OPT>
 __global__ void __launch_bounds__(C::NT, C::CTAs)
 k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1034,14 +1036,14 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
       X.t = tid; X.i = tid >> C::LS; X.p = tid & (C::L - 1);
       X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
       X.myoff = (X.li * C::KC + 2 * X.p) * 8u;
-      role_T2<C, STAGE>(M, P, S, X, NCh, tid, kb);
+      role_T2<C, STAGE, OPT>(M, P, S, X, NCh, tid, kb);
    }
 }
 
-template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
+template <class C, int STAGE, bool OPT> static int launch_fCT2_o(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    static DevOnce once;
    int sm = 0;
-   if (set_smem_once(once, k_fCT2<C, STAGE>, sizeof(typename C::Smem), &sm)) return 1;
+   if (set_smem_once(once, k_fCT2<C, STAGE, OPT>, sizeof(typename C::Smem), &sm)) return 1;
    const int pf = env_i("OMEGA_TILE_PF", 1);
    // one CTA per tile; the tiles of the last partial round of CTAs are split into one CTA per chunk when
    // that shortens the tail (matters on multi-GPU partitions with ~10 rounds)
@@ -1054,8 +1056,11 @@ template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const Cel
       const double cost = ((tail * nch + sm - 1) / sm) * 1.15 / nch; // rounds, a single-chunk CTA costs ~15 % more per chunk
       if (tail > 0 && cost < 0.85) whole = nt - tail;
    }
-   k_fCT2<C, STAGE><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR);
+   k_fCT2<C, STAGE, OPT><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR);
    return 0;
+}
+template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
+   return ca.FluxUpwind || ca.TrUpwind || ca.SrcH ? launch_fCT2_o<C, STAGE, true>(D, ca, St, TR) : launch_fCT2_o<C, STAGE, false>(D, ca, St, TR);
 }
 template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
@@ -1126,6 +1131,7 @@ struct ETileSmem {
    TileHdr Hdr;
 };
 
+template <bool OPT> // OPT: upwinded flux thickness, manufactured velocity source
 __global__ void __launch_bounds__(kEThreads, 2)
 k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1149,27 +1155,6 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    }
    __syncthreads();
    const int p = tid & 7, k = kc0 + 2 * p;
-   if ((Pf & 2) && tix + Ahead < TR.Count) {
-      // Cross-CTA software pipelining through L2: the pass-1 rows (u, h of both cells, PV of both vertices of
-      // every staged edge) of the tile-chunk that a CTA of the NEXT wave will work on are requested now, so
-      // that CTA finds them in L2 (~250 cycles) instead of in DRAM (~700): the kernel is bound by the latency
-      // of exactly these gathers (ncu: long_scoreboard at the first use of pass 1).
-      const TileHdr *Hn = M.Tiles.Hdr + TR.tile(tix + Ahead);
-      const int nS2 = Hn->NEStaged, off2 = Hn->ERowOff;
-      if (p < 5)
-         for (int r = tid >> 3; r < nS2; r += kEThreads / kTLanes) {
-            const int4 cv = M.Tiles.EdgeCV[off2 + r];
-            const double *q;
-            switch (p) {
-            case 0: q = P.Us + (size_t)M.Tiles.EdgeRows[off2 + r] * K; break;
-            case 1: q = P.Hs + (size_t)cv.x * K; break;
-            case 2: q = P.Hs + (size_t)cv.y * K; break;
-            case 3: q = P.PVv + (size_t)cv.z * K; break;
-            default: q = P.PVv + (size_t)cv.w * K; break;
-            }
-            prefetch_l2(q + kc0);
-         }
-   }
    if (Pf & 1) {
       // the eight gathered rows of pass 2a (X, Y of both cells, Z of both vertices, u_cur, u_next) of this
       // thread's own edges: one of the eight lanes of an edge each, pulled into L2 while pass 1 runs
@@ -1206,7 +1191,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    auto put = [&](int r, const double (&u)[2], const double (&h0)[2], const double (&h1)[2], const double (&a)[2],
                   const double (&b)[2]) {
       double f0 = 0.5 * (h0[0] + h1[0]), f1 = 0.5 * (h0[1] + h1[1]);
-      if (P.FluxUpwind) { // u == 0: F = flux * u = 0 for either choice (the reference takes max(h0, h1))
+      if (OPT && P.FluxUpwind) { // u == 0: F = flux * u = 0 for either choice (the reference takes max(h0, h1))
          f0 = u[0] > 0 ? h0[0] : h1[0];
          f1 = u[1] > 0 ? h0[1] : h1[1];
       }
@@ -1238,7 +1223,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
          const int4 cv  = S.CV[r];
          const double mask = M.EdgeMask[e];
          const double InvDc = M.InvDcEdge[e] * mask, InvDv = M.InvDvEdge[e] * mask;
-         const double srcu = P.SrcU ? P.SrcU[e] : 0.0; // manufactured velocity source (not masked, CustomTendencyTerms.cpp:145-210)
+         const double srcu = OPT && P.SrcU ? P.SrcU[e] : 0.0; // manufactured velocity source (not masked, CustomTendencyTerms.cpp:145-210)
          if (P.PVOn) prefetch_row(M.WeightsOnEdge + (size_t)e * M.MaxEdges2 + p, 1); // weights towards L1 for pass 2b
          double x0[2] = {0, 0}, x1[2] = {0, 0}, y0[2], y1[2], z0[2], z1[2], ucur[2] = {0, 0}, base[2] = {0, 0};
          if (P.XOn) { // off when k_fB3 already folded X into Y (W = Y - X)
@@ -1255,7 +1240,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
          for (int q2 = 0; q2 < 2; ++q2) {
             double g = (P.SY * (y1[q2] - y0[q2])) * InvDc - (P.SZ * (z1[q2] - z0[q2])) * InvDv;
             if (P.XOn) g -= (x1[q2] - x0[q2]) * InvDc;
-            g += srcu;
+            if (OPT) g += srcu;
             p1[it][q2] = (P.First ? ucur[q2] : base[q2]) + P.B * g;
             p2[it][q2] = ucur[q2] + P.A * g;
          }
@@ -1306,15 +1291,18 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
 
 int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR) {
    if (TR.Count <= 0) return 0;
-   static DevOnce once;
+   static DevOnce once, onceOpt;
    int sm = 0;
-   if (set_smem_once(once, k_fET, sizeof(ETileSmem), &sm)) return 1;
+   const bool opt = ea.FluxUpwind || ea.SrcU;
+   if (opt ? set_smem_once(onceOpt, k_fET<true>, sizeof(ETileSmem), &sm) : set_smem_once(once, k_fET<false>, sizeof(ETileSmem), &sm)) return 1;
    const int nch = D.K / kTKC;
-   // bit 0: own pass-2a rows; bit 1: pass-1 rows of the tile a CTA of the next wave takes (measured on
-   // config 3 and rejected: 2.36 -> 2.85 ms, the extra requests cost more than the latency they hide)
+   // L2 prefetch of the CTA's own pass-2a rows.  (Also tried: the pass-1 rows of the tile a CTA of the NEXT wave
+   // takes, requested one wave ahead -- 2.36 -> 2.85 ms on config 3, the extra requests cost more than the
+   // latency they hide; removed.)
    const int pf = env_i("OMEGA_TILE_EPF", 1);
    const int ahead = env_i("OMEGA_TILE_EAHEAD", (2 * sm + nch - 1) / nch);
-   k_fET<<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
+   if (opt) k_fET<true><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
+   else k_fET<false><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
    return 0;
 }
 

@@ -88,6 +88,8 @@ int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int 
    rc |= stepper_alloc(S, &A.ZonalStress2, D.NCellsSize);
    rc |= stepper_alloc(S, &S->SrcH, D.NCellsSize);
    rc |= stepper_alloc(S, &S->SrcU, D.NEdgesSize);
+   rc |= stepper_alloc(S, &S->RTop, D.NEdgesSize);
+   rc |= stepper_alloc(S, &S->RBot, D.NEdgesSize);
    rc |= stepper_alloc(S, &S->T.LayerThicknessTend, C);
    rc |= stepper_alloc(S, &S->T.NormalVelocityTend, E);
    rc |= stepper_alloc(S, &S->T.TracerTend, T * C);

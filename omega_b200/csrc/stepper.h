@@ -19,6 +19,7 @@ struct OmegaStepper {
    OmegaTendArrays T;
    ProvisArrays P;
    double *SrcH, *SrcU; // manufactured sources per cell / edge of the current stage (fused tiled path)
+   double *RTop, *RBot; // wind / bottom-drag tendency of the top / bottom layer per edge (k_edge_layer_terms)
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
    int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
