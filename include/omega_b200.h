@@ -315,6 +315,44 @@ int omega_halo_tile_classes(const OmegaHalo *Halo, int *NBoundary, int *NOwned, 
 int omega_halo_set_profiling(OmegaHalo *Halo, int Enable);
 int omega_halo_get_profile(OmegaHalo *Halo, double *Ms, long long *Rounds, long long *Bytes);
 
+/* ---- Decomp (src/base/Decomp.cpp) -- host code, no device work ------------------
+ * One rank's partition of the GLOBAL mesh in Omega's local numbering, the owner
+ * address of every local element (CellLoc / EdgeLoc / VertexLoc, Decomp.cpp:1094-1098,1639-1676) and the
+ * halo exchange lists (src/base/Halo.cpp:455-600), computed by the rank alone from the global
+ * connectivity and the partition: it also numbers its neighbours' partitions, which stands in for the
+ * reference's two MPI exchanges (broadcast of owned lists, mailing of the receive lists).
+ * Global arrays are 0-based with -1 for "none" (file values minus one). */
+typedef struct OmegaGlobalMesh {
+   int NCells, NEdges, NVertices, MaxEdges, MaxEdges2, VertexDegree;
+   const int *CellsOnCell, *EdgesOnCell, *VerticesOnCell; /* [NCells][MaxEdges] */
+   const int *CellsOnEdge, *VerticesOnEdge;               /* [NEdges][2] */
+   const int *EdgesOnEdge;                                /* [NEdges][MaxEdges2] */
+   const int *CellsOnVertex, *EdgesOnVertex;              /* [NVertices][VertexDegree] */
+   const double *XCell, *YCell, *ZCell;                   /* partitioner input */
+} OmegaGlobalMesh;
+typedef struct OmegaDecomp OmegaDecomp;
+/* Method 0: recursive coordinate bisection; 1: the same followed by boundary refinement of the edge cut
+ * (balance kept within 1 %).  The reference calls METIS_PartGraphKway (Decomp.cpp:968-971, third party);
+ * results on owned elements do not depend on the partition.  EdgeCut may be NULL. */
+int omega_decomp_partition(const OmegaGlobalMesh *Mesh, int NTasks, int Method, int *CellTask, long long *EdgeCut);
+int omega_decomp_edge_cut(const OmegaGlobalMesh *Mesh, const int *CellTask, long long *EdgeCut);
+int omega_decomp_create(const OmegaGlobalMesh *Mesh, const int *CellTask, int NTasks, int MyTask, int HaloWidth,
+                        OmegaDecomp **Decomp);
+int omega_decomp_destroy(OmegaDecomp *Decomp);
+/* per element kind (cell, edge, vertex): {NOwned, NAll, NHalo(0 .. HaloWidth-1)} = 3 * (2 + HaloWidth) ints */
+int omega_decomp_counts(const OmegaDecomp *Decomp, int *Counts);
+/* global 0-based ids of the local elements in local order [NAll]; owner address [NAll+1][2] */
+int omega_decomp_ids(const OmegaDecomp *Decomp, OmegaMeshElement Elem, int *IDs);
+int omega_decomp_loc(const OmegaDecomp *Decomp, OmegaMeshElement Elem, int *Loc);
+/* local connectivity, boundary slot for anything not local (Decomp.cpp:552-712).  Which: 0 CellsOnCell,
+ * 1 EdgesOnCell, 2 VerticesOnCell, 3 CellsOnEdge, 4 VerticesOnEdge, 5 EdgesOnEdge, 6 CellsOnVertex,
+ * 7 EdgesOnVertex; Out has NAll + 1 rows. */
+int omega_decomp_connectivity(const OmegaDecomp *Decomp, int Which, int *Out);
+/* halo lists in the layout of OmegaHaloDesc: neighbours ascending, CSR offsets [NNeighbors+1] per kind */
+int omega_decomp_halo_neighbors(const OmegaDecomp *Decomp, int *NNeighbors, int *Tasks);
+int omega_decomp_halo_lists(const OmegaDecomp *Decomp, OmegaMeshElement Elem, int *SendOff, int *SendIdx,
+                            int *RecvOff, int *RecvIdx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -232,3 +232,141 @@ def build_all(mesh: Mesh, ntasks: int, nlev: int, halo_width: int = HALO_WIDTH,
             loc[n_all] = (L.MyTask, n_all)
             L[kind + "Loc"] = loc
     return locs
+
+
+# ---------------------------------------------------------------------------
+# The compiled Decomp (csrc/decomp.cpp, omega_decomp_* of include/omega_b200.h): ONE rank's partition,
+# numbering, owner addresses and halo lists without building anybody else's mesh.  The numpy code above
+# stays as its cross-check (tests/test_decomp_lib.py: identical indices) and as the N-rank emulation.
+# ---------------------------------------------------------------------------
+class GlobalMeshDesc:
+    """ctypes view of OmegaGlobalMesh over a meshgen.Mesh (0-based, -1 = none)."""
+
+    def __init__(self, mesh: Mesh):
+        import ctypes as C
+        from . import capi
+        ip, dp = capi.c_int_p, capi.c_dbl_p
+
+        class S(C.Structure):
+            _fields_ = ([(n, C.c_int) for n in ("NCells", "NEdges", "NVertices", "MaxEdges", "MaxEdges2", "VertexDegree")]
+                        + [(n, ip) for n in ("CellsOnCell", "EdgesOnCell", "VerticesOnCell", "CellsOnEdge", "VerticesOnEdge",
+                                             "EdgesOnEdge", "CellsOnVertex", "EdgesOnVertex")]
+                        + [(n, dp) for n in ("XCell", "YCell", "ZCell")])
+        self.keep = []
+        d = S(NCells=mesh.nCells, NEdges=mesh.nEdges, NVertices=mesh.nVertices, MaxEdges=mesh.maxEdges,
+              MaxEdges2=mesh.maxEdges2, VertexDegree=mesh.vertexDegree)
+        for n, src in (("CellsOnCell", "cellsOnCell"), ("EdgesOnCell", "edgesOnCell"), ("VerticesOnCell", "verticesOnCell"),
+                       ("CellsOnEdge", "cellsOnEdge"), ("VerticesOnEdge", "verticesOnEdge"), ("EdgesOnEdge", "edgesOnEdge"),
+                       ("CellsOnVertex", "cellsOnVertex"), ("EdgesOnVertex", "edgesOnVertex")):
+            a = np.ascontiguousarray(mesh[src], np.int32)
+            self.keep.append(a)
+            setattr(d, n, a.ctypes.data_as(ip))
+        for n, src in (("XCell", "xCell"), ("YCell", "yCell"), ("ZCell", "zCell")):
+            a = np.ascontiguousarray(mesh[src], np.float64)
+            self.keep.append(a)
+            setattr(d, n, a.ctypes.data_as(dp))
+        self.c = d
+
+
+def _lib():
+    from . import capi
+    return capi.load_library()
+
+
+def partition_cells_lib(mesh: Mesh, ntasks: int, method: int = 0):
+    """(cell_task, edge_cut): 0 = recursive coordinate bisection (== partition_cells), 1 = + boundary refinement."""
+    import ctypes as C
+    lib, g = _lib(), GlobalMeshDesc(mesh)
+    task = np.zeros(mesh.nCells, np.int32)
+    cut = C.c_longlong()
+    rc = lib.omega_decomp_partition(C.byref(g.c), ntasks, method, task.ctypes.data_as(C.POINTER(C.c_int)), C.byref(cut))
+    if rc:
+        raise RuntimeError(lib.omega_last_error().decode())
+    return task, int(cut.value)
+
+
+def build_local_lib(mesh: Mesh, cell_task: np.ndarray, task: int, nlev: int, halo_width: int = HALO_WIDTH):
+    """(local mesh, halo lists) of ONE rank from the compiled Decomp; same contents as build_local +
+    EdgeLoc / VertexLoc + parallel.build_halo_lists()[task]."""
+    import ctypes as C
+    lib, g = _lib(), GlobalMeshDesc(mesh)
+    ip = C.POINTER(C.c_int)
+    cell_task = np.ascontiguousarray(cell_task, np.int32)
+    ntasks = int(cell_task.max()) + 1
+    h = C.c_void_p()
+    rc = lib.omega_decomp_create(C.byref(g.c), cell_task.ctypes.data_as(ip), ntasks, task, halo_width, C.byref(h))
+    if rc:
+        raise RuntimeError(lib.omega_last_error().decode())
+    try:
+        w = 2 + halo_width
+        cnt = np.zeros(3 * w, np.int32)
+        lib.omega_decomp_counts(h, cnt.ctypes.data_as(ip))
+        cnt = cnt.reshape(3, w)
+        ids, loc = [], []
+        for k in range(3):
+            a = np.zeros(cnt[k, 1], np.int32)
+            lib.omega_decomp_ids(h, k, a.ctypes.data_as(ip))
+            b = np.zeros((cnt[k, 1] + 1, 2), np.int32)
+            lib.omega_decomp_loc(h, k, b.ctypes.data_as(ip))
+            ids.append(a); loc.append(b)
+        widths = (mesh.maxEdges, mesh.maxEdges, mesh.maxEdges, 2, 2, mesh.maxEdges2, mesh.vertexDegree, mesh.vertexDegree)
+        rows = (0, 0, 0, 1, 1, 1, 2, 2)
+        conn = []
+        for which in range(8):
+            a = np.zeros((cnt[rows[which], 1] + 1, widths[which]), np.int32)
+            lib.omega_decomp_connectivity(h, which, a.ctypes.data_as(ip))
+            conn.append(a)
+        nn = C.c_int()
+        lib.omega_decomp_halo_neighbors(h, C.byref(nn), None)
+        nbrs = np.zeros(max(nn.value, 1), np.int32)
+        lib.omega_decomp_halo_neighbors(h, C.byref(nn), nbrs.ctypes.data_as(ip))
+        nbrs = [int(x) for x in nbrs[:nn.value]]
+        lists = dict(neighbors=nbrs, send={}, recv={})
+        for k, kind in enumerate(("Cell", "Edge", "Vertex")):
+            so, ro = np.zeros(nn.value + 1, np.int32), np.zeros(nn.value + 1, np.int32)
+            lib.omega_decomp_halo_lists(h, k, so.ctypes.data_as(ip), None, ro.ctypes.data_as(ip), None)
+            si, ri = np.zeros(max(so[-1], 1), np.int32), np.zeros(max(ro[-1], 1), np.int32)
+            lib.omega_decomp_halo_lists(h, k, None, si.ctypes.data_as(ip), None, ri.ctypes.data_as(ip))
+            lists["send"][kind] = {t: si[so[i]:so[i + 1]].copy() for i, t in enumerate(nbrs) if so[i + 1] > so[i]}
+            lists["recv"][kind] = {t: ri[ro[i]:ro[i + 1]].copy() for i, t in enumerate(nbrs) if ro[i + 1] > ro[i]}
+    finally:
+        lib.omega_decomp_destroy(h)
+    cell_ids, edge_ids, vert_ids = (a.astype(np.int64) for a in ids)
+    nC, nE, nV = mesh.nCells, mesh.nEdges, mesh.nVertices
+    L = Mesh()
+    L.geometry, L.sphere_radius = mesh.geometry, mesh.sphere_radius
+    for k in ("Lx", "Ly", "dc"):
+        if k in mesh:
+            L[k] = mesh[k]
+    L.MyTask, L.NumTasks, L.HaloWidth, L.NVertLayers = task, ntasks, halo_width, nlev
+    for k, nm in enumerate(("Cells", "Edges", "Vertices")):
+        L["N%sOwned" % nm], L["N%sAll" % nm], L["N%sSize" % nm] = int(cnt[k, 0]), int(cnt[k, 1]), int(cnt[k, 1]) + 1
+        L["N%sHalo" % nm] = cnt[k, 2:].copy()
+    L.MaxEdges, L.MaxEdges2, L.VertexDegree = mesh.maxEdges, mesh.maxEdges2, mesh.vertexDegree
+    L.NCellsGlobal, L.NEdgesGlobal, L.NVerticesGlobal = nC, nE, nV
+    pad = lambda i, n: np.concatenate([i + 1, [n + 1]]).astype(np.int32)
+    L.CellID, L.EdgeID, L.VertexID = pad(cell_ids, nC), pad(edge_ids, nE), pad(vert_ids, nV)
+    L.CellLoc, L.EdgeLoc, L.VertexLoc = loc
+    (L.CellsOnCell, L.EdgesOnCell, L.VerticesOnCell, L.CellsOnEdge, L.VerticesOnEdge, L.EdgesOnEdge,
+     L.CellsOnVertex, L.EdgesOnVertex) = conn
+    L.NEdgesOnCell = np.concatenate([(mesh.edgesOnCell[cell_ids] >= 0).sum(1), [0]]).astype(np.int32)
+    L.NEdgesOnEdge = np.concatenate([np.full(edge_ids.size, mesh.maxEdges2), [0]]).astype(np.int32)
+
+    def padf(a, i):
+        out = np.zeros((i.size + 1,) + a.shape[1:], a.dtype)
+        out[:i.size] = a[i]
+        return out
+
+    for nm, src in (("AreaCell", "areaCell"), ("BottomDepth", "bottomDepth"), ("XCell", "xCell"), ("YCell", "yCell"),
+                    ("ZCell", "zCell"), ("LonCell", "lonCell"), ("LatCell", "latCell"), ("FCell", "fCell")):
+        L[nm] = padf(mesh[src], cell_ids)
+    for nm, src in (("DcEdge", "dcEdge"), ("DvEdge", "dvEdge"), ("AngleEdge", "angleEdge"), ("FEdge", "fEdge"),
+                    ("XEdge", "xEdge"), ("YEdge", "yEdge"), ("ZEdge", "zEdge"), ("LonEdge", "lonEdge"),
+                    ("LatEdge", "latEdge"), ("WeightsOnEdge", "weightsOnEdge")):
+        L[nm] = padf(mesh[src], edge_ids)
+    for nm, src in (("AreaTriangle", "areaTriangle"), ("FVertex", "fVertex"), ("XVertex", "xVertex"), ("YVertex", "yVertex"),
+                    ("ZVertex", "zVertex"), ("LonVertex", "lonVertex"), ("LatVertex", "latVertex"),
+                    ("KiteAreasOnVertex", "kiteAreasOnVertex")):
+        L[nm] = padf(mesh[src], vert_ids)
+    L._cell_ids, L._edge_ids, L._vert_ids = cell_ids, edge_ids, vert_ids
+    return L, lists

@@ -70,9 +70,13 @@ def flatten_lists(h):
     return flat
 
 
-def local_problem(mesh, world, rank, nlev, halo_width=decomp.HALO_WIDTH):
-    """(local mesh of `rank`, its halo lists).  Every rank derives the same
-    partition deterministically, no communication needed."""
+def local_problem(mesh, world, rank, nlev, halo_width=decomp.HALO_WIDTH, method=0, use_lib=True):
+    """(local mesh of `rank`, its halo lists).  Every rank derives the same partition deterministically and
+    numbers only its own partition and its neighbours' (compiled Decomp, csrc/decomp.cpp); no communication.
+    use_lib=False: the numpy restatement, which builds every rank's mesh (tests, emulation)."""
+    if use_lib and world > 1:
+        task, _ = decomp.partition_cells_lib(mesh, world, method)
+        return decomp.build_local_lib(mesh, task, rank, nlev, halo_width)
     locs = decomp.build_all(mesh, world, nlev, halo_width)
     lists = build_halo_lists(locs)
     return locs[rank], lists[rank]
