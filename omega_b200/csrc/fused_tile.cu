@@ -557,7 +557,7 @@ k_fCT(DMesh M, CellArgs P, int NChunks, TileRange TR) {
 // per chunk, 384 threads, two CTAs per SM.  The second keeps the SM busy while one CTA
 // sits in the latency of its chunk prologue or at a barrier.
 // ---------------------------------------------------------------------------
-template <int KC_, int RS_ = 0, int CP_ = 0> struct Cfg2 {
+template <int KC_, int RS_ = 0, int CP_ = 0, int TM_ = 0> struct Cfg2 {
    static constexpr int KC = KC_;
    static constexpr int RS = RS_;            // 0: T 96 / R 40 registers, 2: 96/48, 3: 96/40 with 384 R threads            // levels per chunk
    static constexpr int L  = KC / 2;         // threads per row piece set (2 levels each)
@@ -569,10 +569,13 @@ template <int KC_, int RS_ = 0, int CP_ = 0> struct Cfg2 {
    static constexpr int CTAs = KC == 16 ? 1 : 2;
    static constexpr bool BULK = CP_ >= 1;    // row copies: 0 = cp.async 16-byte pieces (LSU), 1, 2 = one bulk copy per row (TMA unit, mbarrier)
    static constexpr bool ONEWAIT = CP_ == 2; // 2: ONE thread waits on the "landed" barrier, ahead of the __syncthreads that hands the buffer over
+   static constexpr int TM = TM_;            // tensor memory (TMEM) for per-thread private slots: 1 = the RK weights of the T role
+   static constexpr bool PAIR = false;       // one tracer per iteration (Cfg3: two)
    struct Smem : TileSmemT<KC, NS> {
       double2 W[3][TT]; // per T thread: the three per-level weights of the RK update (private slots, spares 12 registers)
       unsigned long long Bar[NS + 1]; // BULK: "landed" barriers of the tracer buffers and of h
       double SHc[kTileCells];         // own rows: -sum_j ch_j (the self coefficient of the Del4 sum)
+      unsigned TmemBase;              // TM: base address of the CTA's tensor-memory allocation
    };
 };
 static_assert(sizeof(Cfg2<16>::Smem) <= 232448, "k_fCT2 shared memory");
@@ -599,6 +602,37 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                 "r"(bytes), "r"(bar)
                 : "memory");
+}
+
+// ---- tensor memory (TMEM, 256 KB per SM: 128 lanes x 512 columns x 32 bit) as per-thread private storage.
+// Nothing here is a matrix product: TMEM serves as a second on-chip scratchpad with its own datapath
+// (tcgen05.st / tcgen05.ld, SASS STTM / LDTM) for values only the owning thread ever reads -- the RK weights
+// of a T thread, the Del2 coefficients of an R thread -- which otherwise compete with the stencil reads for
+// the shared-memory pipe this kernel is bound by.  With the 32x32b shape thread t of a warp owns lane
+// 32 * (warp % 4) + t; warps that share a lane quarter use different columns.
+__device__ __forceinline__ void tmem_alloc_all(unsigned *Slot) {
+   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(Slot)) : "memory");
+   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_free_all(unsigned Base) {
+   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(Base) : "memory");
+}
+__device__ __forceinline__ void tmem_st2(unsigned Addr, double a, double b) { // 4 columns: two doubles
+   unsigned a0, a1, b0, b1;
+   asm("mov.b64 {%0, %1}, %2;" : "=r"(a0), "=r"(a1) : "d"(a));
+   asm("mov.b64 {%0, %1}, %2;" : "=r"(b0), "=r"(b1) : "d"(b));
+   asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(Addr), "r"(a0), "r"(a1), "r"(b0), "r"(b1) : "memory");
+}
+__device__ __forceinline__ void tmem_ld2_issue(unsigned Addr, unsigned (&r)[4]) {
+   asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(Addr) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ double2 tmem_unpack2(const unsigned (&r)[4]) {
+   double2 v;
+   asm("mov.b64 %0, {%1, %2};" : "=d"(v.x) : "r"(r[0]), "r"(r[1]));
+   asm("mov.b64 %0, {%1, %2};" : "=d"(v.y) : "r"(r[2]), "r"(r[3]));
+   return v;
 }
 
 template <class C>
@@ -745,6 +779,148 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    if (!C::BULK) cp_wait<0>();
 }
 
+// ---------------------------------------------------------------------------
+// k_fCT3 = k_fCT2 with TWO tracers per iteration.  k_fCT2 is not bound by shared-memory wavefronts alone
+// (ncu r02a: LSU 72 % busy; removing every private coefficient read, 20 % of the wavefronts, gained 9 %):
+// with one __syncthreads per tracer all 24 warps refill and drain the load pipe once per tracer, and a warp
+// has one tracer's worth of independent loads to hide the shared-memory latency with.  A pair of tracers per
+// barrier halves the barriers and doubles the independent work between them.  That needs four Del2 buffers
+// (two pairs in flight); the room comes from moving the ring-row Del2 coefficients (Cf1, 43 KB, private to the
+// R thread that uses them) out of shared memory into TENSOR MEMORY (tcgen05.st / tcgen05.ld, see above):
+// an R thread loads the twelve coefficients of a ring piece once per pair instead of once per tracer.
+// ---------------------------------------------------------------------------
+struct Cfg3 {
+   static constexpr int KC = 16, RS = 2, L = 8, LS = 3;
+   static constexpr int TT = kTileCells * L, RT = TT / 2, NT = TT + RT, NS = 4, CTAs = 1;
+   static constexpr bool BULK = false, ONEWAIT = false, PAIR = true;
+   static constexpr int TM = 2; // tensor memory holds the ring-row coefficients of the R role
+   struct Smem {
+      double H[kTileRows][KC];
+      double Phi[NS][kTileRows][KC];
+      double D2[4][kTileRows1][KC]; // [2 * (pair parity) + tracer of the pair]
+      double G[kTileRows1][6];
+      double Ch[kTileCells][6];
+      double CfU[kTileCells][6], Wa[kTileCells][6];
+      double InvA[kTileRows1];
+      unsigned short Nbl[kTileRows1][8];
+      int GRow[kTileRows];
+      int Eoc[kTileCells][6];
+      TileHdr Hdr;
+      double2 W[3][TT];
+      unsigned long long Bar[NS + 1]; // unused (bulk copies are a Cfg2 variant)
+      double SHc[kTileCells];
+      unsigned TmemBase;
+   };
+};
+static_assert(sizeof(Cfg3::Smem) <= 232448, "k_fCT3 shared memory");
+
+// R role of k_fCT3: copies one PAIR ahead, Del2 of the ring-1 rows of both tracers of the pair
+template <class C>
+__device__ __forceinline__ void role_R3(const DMesh &M, const CellArgs &P, typename C::Smem &S, int c0, int nc, int n1, int nR,
+                                        int NCh, int tid, bool Pf, int kb) {
+   constexpr int KC = C::KC, L = C::L, RT = C::RT, NS = C::NS;
+   const int T = P.NTracers, K = M.K, r = tid - C::TT, p = r & (L - 1);
+   const size_t CS = (size_t)M.NCellsSize * K;
+   const int NP = (T + 1) >> 1; // pairs per chunk (the last one may hold one tracer)
+   // TMEM slot: lane quarter of the warp; the two R warps of a quarter own columns [64, 112) and [112, 160):
+   // 2 ring pieces x 6 coefficients x double2 = 48 columns per thread
+   const int w = tid >> 5;
+   const unsigned tmC = S.TmemBase + ((unsigned)(w & 3) << 21) + 64u + (unsigned)((w - C::TT / 32) >> 2) * 48u;
+   // tracer l of chunk c is item c*T + l of the copy stream and lives in Phi[item % NS]
+   copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], kb);
+   copy_rows_n<C>(S, nR, K, r, P.Trs, &S.Phi[0][0][0], kb);
+   if (T >= 2) copy_rows_n<C>(S, nR, K, r, P.Trs + CS, &S.Phi[1][0][0], kb);
+   cp_commit();
+   load_tables<C::NT>(M, S, tid, nc + n1, nc);
+   const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
+   const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
+   for (int c = 0; c < NCh; ++c) {
+      const int it0 = c * T, kc = kb + c * KC;
+      cp_wait<0>();
+      __syncthreads(); // h and the first pair of this chunk have landed; tables are visible; the T role is done with the previous chunk
+      // coefficients of this thread's two ring pieces, -(1/A) G mean thickness per edge, into its TMEM slot
+      // (warp-collective stores: every lane takes part, lanes without a piece store a clamped row's values)
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+         const int ri  = (r >> C::LS) + u * (RT / L);
+         const int row = nc + (ri < n1 ? ri : 0);
+         const double nia = -S.InvA[row];
+         const double2 hr = lds2(Hb, (row * KC + 2 * p) * 8u);
+         const uint4 tt   = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
+#pragma unroll
+         for (int j = 0; j < kME; ++j) {
+            const double2 hn = lds2(Hb, (nbl_get(tt, j) * KC + 2 * p) * 8u);
+            const double g   = S.G[row][j] * nia;
+            tmem_st2(tmC + u * 24 + j * 4, g * (0.5 * (hr.x + hn.x)), g * (0.5 * (hr.y + hn.y)));
+         }
+      }
+      tmem_wait_st();
+      for (int pi = 0; pi <= NP; ++pi) {
+         if (pi > 0) cp_wait<0>(); // the pair issued one iteration ago (this thread's pieces)
+         __syncthreads();          // iteration pi: the T role has finished iteration pi - 1
+         // next item of the copy stream: the next pair of this chunk, or h and the first pair of the next chunk
+         if (pi + 1 < NP) {
+            const int a = 2 * (pi + 1);
+            copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)a * CS, &S.Phi[(it0 + a) % NS][0][0], kc);
+            if (a + 1 < T) copy_rows_n<C>(S, nR, K, r, P.Trs + (size_t)(a + 1) * CS, &S.Phi[(it0 + a + 1) % NS][0][0], kc);
+         } else if (pi + 1 == NP && c + 1 < NCh) {
+            copy_rows_n<C>(S, nR, K, r, P.Hs, &S.H[0][0], kc + KC);
+            copy_rows_n<C>(S, nR, K, r, P.Trs, &S.Phi[(it0 + T) % NS][0][0], kc + KC);
+            if (T >= 2) copy_rows_n<C>(S, nR, K, r, P.Trs + CS, &S.Phi[(it0 + T + 1) % NS][0][0], kc + KC);
+         }
+         cp_commit();
+         if (pi == 0 && c + 1 < NCh && Pf) {
+            // pull what the T role's next chunk prologue reads from global memory into L2
+            for (int q = r; q < nc * 8; q += RT) {
+               const int cell = q >> 3, j = q & 7;
+               const size_t o = (size_t)(c0 + cell) * K + kc + KC;
+               if (j < 6) prefetch_l2(P.Us + (size_t)S.Eoc[cell][j] * K + kc + KC);
+               else if (j == 6 ? pfHcur : pfHnext) prefetch_l2((j == 6 ? P.Hcur : P.Hnext) + o);
+            }
+         }
+         if (pi < NP) {
+            const int a = 2 * pi, nb = T - a < 2 ? T - a : 2;
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+               const int ri   = (r >> C::LS) + u * (RT / L);
+               const bool act = ri < n1;
+               const int row  = nc + (act ? ri : 0);
+               const unsigned ro = (row * KC + 2 * p) * 8u;
+               const uint4 tt    = *reinterpret_cast<const uint4 *>(&S.Nbl[row][0]);
+               // both tracers of the pair share every coefficient load; three coefficients at a time keep the
+               // role within its 48 registers (setmaxnreg: the T role's 96 come out of what this role releases)
+               const unsigned char *Pb0 = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + a) % NS][0][0]);
+               const unsigned char *Pb1 = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + a + (nb > 1)) % NS][0][0]);
+               const double2 pr0 = lds2(Pb0, ro), pr1 = lds2(Pb1, ro);
+               double e00 = 0, e01 = 0, e10 = 0, e11 = 0;
+#pragma unroll
+               for (int jh = 0; jh < kME; jh += 3) {
+                  unsigned cw[3][4];
+#pragma unroll
+                  for (int j = 0; j < 3; ++j) tmem_ld2_issue(tmC + u * 24 + (jh + j) * 4, cw[j]);
+                  tmem_wait_ld();
+#pragma unroll
+                  for (int j = 0; j < 3; ++j) {
+                     const unsigned no = (nbl_get(tt, jh + j) * KC + 2 * p) * 8u;
+                     const double2 cf = tmem_unpack2(cw[j]);
+                     const double2 pn0 = lds2(Pb0, no), pn1 = lds2(Pb1, no);
+                     e00 += cf.x * (pr0.x - pn0.x);
+                     e01 += cf.y * (pr0.y - pn0.y);
+                     e10 += cf.x * (pr1.x - pn1.x);
+                     e11 += cf.y * (pr1.y - pn1.y);
+                  }
+               }
+               if (act) {
+                  sts2(reinterpret_cast<unsigned char *>(&S.D2[2 * (pi & 1)][0][0]), ro, e00, e01);
+                  if (nb > 1) sts2(reinterpret_cast<unsigned char *>(&S.D2[2 * (pi & 1) + 1][0][0]), ro, e10, e11);
+               }
+            }
+         }
+      }
+   }
+   cp_wait<0>();
+}
+
 // global accesses of the T role that bypass L1 allocation: what little L1 is left beside
 // 226 KB of shared memory then keeps the few spilled registers of the tracer loop
 __device__ __forceinline__ void ldg_na(double (&r)[2], const double *p) {
@@ -771,6 +947,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    load_tables<C::NT>(M, S, tid, X.nR1, X.nc);
    const int c = X.c0 + li;
    const unsigned myoff = X.myoff;
+   // TMEM address of this thread's private slot: lane quarter of the warp, 16 columns per warp of the quarter
+   const unsigned tmW = C::TM == 1 ? S.TmemBase + ((unsigned)((tid >> 5) & 3) << 21) + (unsigned)(tid >> 7) * 16u : 0u;
    const unsigned char *Hb = reinterpret_cast<const unsigned char *>(&S.H[0][0]);
    const bool sameU = P.UTr == P.Us;
    const bool hcur_is_hs = First && P.Hcur == P.Hs;
@@ -898,104 +1076,207 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             stg_na(P.Hnext + o, hnext);
             if (!Last) stg_na(P.Hprov + o, hprov);
          }
-         if (First || Last) S.W[0][tid] = make_double2(w0[0], w0[1]);
-         if (!Last) {
-            S.W[1][tid] = make_double2(w1[0], w1[1]);
-            S.W[2][tid] = make_double2(w2[0], w2[1]);
-         }
-      }
-      double tcur[2] = {0, 0}, acc[2] = {0, 0}; // cur / next of the tracer pass B handles next
-      if (own) {
-         if (need_cur) ldg_na(tcur, P.TrCur + o);
-         if (!First) ldg_na(acc, P.TrNext + o);
-      }
-      double adv[2] = {0, 0}, tsp[2] = {0, 0}; // advective part and own value of the tracer pass A handled last
-      // ---- pass B of tracer l: Del4 from the Del2 rows, then the RK update
-      auto pass_B = [&](int l) {
-         const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
-         const double2 ds = lds2(Db, myoff);
-#ifdef OMEGA_EXP_NOPRIV
-         const double SHl = 1e-9;
-#else
-         const double SHl = S.SHc[li];
-#endif
-         double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
-#pragma unroll
-         for (int j = 0; j < kME; j += 2) {
-#ifdef OMEGA_EXP_NOPRIV
-            const double2 c2 = make_double2(1e-9 * j, 1e-9);
-#else
-            const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
-#endif
-            const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
-            tend[0] += c2.x * da.x;
-            tend[1] += c2.x * da.y;
-            tend[0] += c2.y * db.x;
-            tend[1] += c2.y * db.y;
-         }
-         if (own) {
-            double out[2];
-            double2 w0v = make_double2(0, 0);
-            if (First || Last) w0v = S.W[0][tid];
-            const double w0[2] = {w0v.x, w0v.y};
-            if (tcur_is_ts) {
-               tcur[0] = tsp[0];
-               tcur[1] = tsp[1];
-            }
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-               out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
-               if (Last) out[q] *= w0[q];
-            }
-            stg_na(P.TrNext + l * CS + o, out);
+         if (C::TM == 1) { // RK weights into this thread's TMEM slot: columns {0,4,8} of its warp's 16
+            if (First || Last) tmem_st2(tmW, w0[0], w0[1]);
             if (!Last) {
-#ifdef OMEGA_EXP_NOPRIV
-               const double2 w1v = make_double2(1.0, 1.0), w2v = make_double2(P.A, P.A);
-#else
-               const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
-#endif
-               const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
-#pragma unroll
-               for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
-               stg_na(P.TrProv + l * CS + o, out);
+               tmem_st2(tmW + 4, w1[0], w1[1]);
+               tmem_st2(tmW + 8, w2[0], w2[1]);
             }
-            if (l + 1 < T) {
-               if (need_cur) ldg_na(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
-               if (!First) ldg_na(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+            tmem_wait_st();
+         } else {
+            if (First || Last) S.W[0][tid] = make_double2(w0[0], w0[1]);
+            if (!Last) {
+               S.W[1][tid] = make_double2(w1[0], w1[1]);
+               S.W[2][tid] = make_double2(w2[0], w2[1]);
             }
          }
-      };
-      for (int i = 0; i < T; ++i) {
-         __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
-         double advn[2], tsn[2];
-         { // ---- pass A of tracer i: every neighbour row once, two sums
-            wait_item<C>(S, it0 + i);
-            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
-            const double2 ts = lds2(Pb, myoff);
-            double d0 = 0, d1 = 0;
-            advn[0] = ts.x * S0[0];
-            advn[1] = ts.y * S0[1];
-#pragma unroll
-            for (int j = 0; j < kME; ++j) {
-               const double2 tn = lds2(Pb, NBOFF(j));
-               advn[0] += E[j][0] * tn.x;
-               advn[1] += E[j][1] * tn.y;
-               d0 += cfA[j][0] * (ts.x - tn.x);
-               d1 += cfA[j][1] * (ts.y - tn.y);
-            }
-            if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]), myoff, d0, d1);
-            tsn[0] = ts.x;
-            tsn[1] = ts.y;
-         }
-         if (i > 0) pass_B(i - 1);
-         adv[0] = advn[0]; adv[1] = advn[1];
-         tsp[0] = tsn[0]; tsp[1] = tsn[1];
       }
-      // last iteration: only pass B of the last tracer is left, the coefficient registers are free:
-      // the next chunk's prologue operands start their way from global memory now
-      __syncthreads();
-      if (OMEGA_T2_HOIST && ch + 1 < NCh) load_prologue(ch + 1);
-      pass_B(T - 1);
+      if constexpr (C::PAIR) {
+         // ---- two tracers per iteration: pass B of the previous pair, then pass A of this pair
+         const int NP = (T + 1) >> 1;
+         double tcur[2][2] = {{0, 0}, {0, 0}}, acc[2][2] = {{0, 0}, {0, 0}}, adv[2][2] = {{0, 0}, {0, 0}};
+         auto preload = [&](int l, int q) { // cur / next of tracer l: in flight until its pass B, one iteration later
+            if (own && l < T) {
+               if (need_cur) ldg_na(tcur[q], P.TrCur + (size_t)l * CS + o);
+               if (!First) ldg_na(acc[q], P.TrNext + (size_t)l * CS + o);
+            }
+         };
+         auto pass_B = [&](int l, int q, int db) {
+            const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[db][0][0]);
+            const double2 ds = lds2(Db, myoff);
+            const double SHl = S.SHc[li];
+            double tend[2] = {adv[q][0] + ds.x * SHl, adv[q][1] + ds.y * SHl};
+#pragma unroll
+            for (int j = 0; j < kME; j += 2) {
+               const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
+               const double2 da = lds2(Db, NBOFF(j)), dc = lds2(Db, NBOFF(j + 1));
+               tend[0] += c2.x * da.x;
+               tend[1] += c2.x * da.y;
+               tend[0] += c2.y * dc.x;
+               tend[1] += c2.y * dc.y;
+            }
+            if (own) {
+               double out[2];
+               double2 w0v = make_double2(0, 0);
+               if (First || Last) w0v = S.W[0][tid];
+               const double w0[2] = {w0v.x, w0v.y};
+#pragma unroll
+               for (int x = 0; x < 2; ++x) {
+                  out[x] = (First ? tcur[q][x] * w0[x] : acc[q][x]) + P.B * tend[x];
+                  if (Last) out[x] *= w0[x];
+               }
+               stg_na(P.TrNext + l * CS + o, out);
+               if (!Last) {
+                  const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
+                  out[0] = tcur[q][0] * w1v.x + tend[0] * w2v.x;
+                  out[1] = tcur[q][1] * w1v.y + tend[1] * w2v.y;
+                  stg_na(P.TrProv + l * CS + o, out);
+               }
+            }
+         };
+         if (!tcur_is_ts || !First) {
+            preload(0, 0);
+            preload(1, 1);
+         }
+         for (int pi = 0; pi <= NP; ++pi) {
+            __syncthreads(); // pair pi has landed; Del2 of pair pi-1 is complete (own rows: T role, ring 1: R role)
+            if (pi > 0) {
+               const int a = 2 * (pi - 1), db = 2 * ((pi - 1) & 1);
+               pass_B(a, 0, db);
+               if (a + 1 < T) pass_B(a + 1, 1, db + 1);
+               if (pi < NP) { // operands of this pair's pass B, one iteration from now
+                  preload(2 * pi, 0);
+                  preload(2 * pi + 1, 1);
+               }
+            }
+            if (pi < NP) {
+               const int a = 2 * pi, nb = T - a < 2 ? T - a : 2;
+               for (int q = 0; q < nb; ++q) { // pass A: every neighbour row once, two sums
+                  const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + a + q) % NS][0][0]);
+                  const double2 ts = lds2(Pb, myoff);
+                  double d0 = 0, d1 = 0, a0 = ts.x * S0[0], a1 = ts.y * S0[1];
+#pragma unroll
+                  for (int j = 0; j < kME; ++j) {
+                     const double2 tn = lds2(Pb, NBOFF(j));
+                     a0 += E[j][0] * tn.x;
+                     a1 += E[j][1] * tn.y;
+                     d0 += cfA[j][0] * (ts.x - tn.x);
+                     d1 += cfA[j][1] * (ts.y - tn.y);
+                  }
+                  if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[2 * (pi & 1) + q][0][0]), myoff, d0, d1);
+                  adv[q][0] = a0;
+                  adv[q][1] = a1;
+                  if (tcur_is_ts) { // first stage on the current state: cur is the stage value itself
+                     tcur[q][0] = ts.x;
+                     tcur[q][1] = ts.y;
+                  }
+               }
+            }
+         }
+      } else {
+         double tcur[2] = {0, 0}, acc[2] = {0, 0}; // cur / next of the tracer pass B handles next
+         if (own) {
+            if (need_cur) ldg_na(tcur, P.TrCur + o);
+            if (!First) ldg_na(acc, P.TrNext + o);
+         }
+         double adv[2] = {0, 0}, tsp[2] = {0, 0}; // advective part and own value of the tracer pass A handled last
+         // ---- pass B of tracer l: Del4 from the Del2 rows, then the RK update
+         auto pass_B = [&](int l) {
+            const unsigned char *Db = reinterpret_cast<const unsigned char *>(&S.D2[l & 1][0][0]);
+            const double2 ds = lds2(Db, myoff);
+   #ifdef OMEGA_EXP_NOPRIV
+            const double SHl = 1e-9;
+   #else
+            const double SHl = S.SHc[li];
+   #endif
+            double tend[2] = {adv[0] + ds.x * SHl, adv[1] + ds.y * SHl};
+   #pragma unroll
+            for (int j = 0; j < kME; j += 2) {
+   #ifdef OMEGA_EXP_NOPRIV
+               const double2 c2 = make_double2(1e-9 * j, 1e-9);
+   #else
+               const double2 c2 = *reinterpret_cast<const double2 *>(&S.Ch[li][j]);
+   #endif
+               const double2 da = lds2(Db, NBOFF(j)), db = lds2(Db, NBOFF(j + 1));
+               tend[0] += c2.x * da.x;
+               tend[1] += c2.x * da.y;
+               tend[0] += c2.y * db.x;
+               tend[1] += c2.y * db.y;
+            }
+            // TMEM loads are warp-collective (.sync.aligned): issued by every thread, before the own-cell branch
+            unsigned tw0[4] = {0, 0, 0, 0}, tw1[4] = {0, 0, 0, 0}, tw2[4] = {0, 0, 0, 0};
+            if (C::TM) {
+               if (First || Last) tmem_ld2_issue(tmW, tw0);
+               if (!Last) {
+                  tmem_ld2_issue(tmW + 4, tw1);
+                  tmem_ld2_issue(tmW + 8, tw2);
+               }
+               tmem_wait_ld();
+            }
+            if (own) {
+               double out[2];
+               double2 w0v = make_double2(0, 0);
+               if (First || Last) w0v = C::TM ? tmem_unpack2(tw0) : S.W[0][tid];
+               const double w0[2] = {w0v.x, w0v.y};
+               if (tcur_is_ts) {
+                  tcur[0] = tsp[0];
+                  tcur[1] = tsp[1];
+               }
+   #pragma unroll
+               for (int q = 0; q < 2; ++q) {
+                  out[q] = (First ? tcur[q] * w0[q] : acc[q]) + P.B * tend[q];
+                  if (Last) out[q] *= w0[q];
+               }
+               stg_na(P.TrNext + l * CS + o, out);
+               if (!Last) {
+   #ifdef OMEGA_EXP_NOPRIV
+                  const double2 w1v = make_double2(1.0, 1.0), w2v = make_double2(P.A, P.A);
+   #else
+                  const double2 w1v = C::TM ? tmem_unpack2(tw1) : S.W[1][tid], w2v = C::TM ? tmem_unpack2(tw2) : S.W[2][tid];
+   #endif
+                  const double w1[2] = {w1v.x, w1v.y}, w2[2] = {w2v.x, w2v.y};
+   #pragma unroll
+                  for (int q = 0; q < 2; ++q) out[q] = tcur[q] * w1[q] + tend[q] * w2[q];
+                  stg_na(P.TrProv + l * CS + o, out);
+               }
+               if (l + 1 < T) {
+                  if (need_cur) ldg_na(tcur, P.TrCur + (size_t)(l + 1) * CS + o);
+                  if (!First) ldg_na(acc, P.TrNext + (size_t)(l + 1) * CS + o);
+               }
+            }
+         };
+         for (int i = 0; i < T; ++i) {
+            __syncthreads(); // tracer i has landed; Del2 of tracer i-1 is complete (own rows: T role, ring 1: R role)
+            double advn[2], tsn[2];
+            { // ---- pass A of tracer i: every neighbour row once, two sums
+               wait_item<C>(S, it0 + i);
+               const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + i) % NS][0][0]);
+               const double2 ts = lds2(Pb, myoff);
+               double d0 = 0, d1 = 0;
+               advn[0] = ts.x * S0[0];
+               advn[1] = ts.y * S0[1];
+   #pragma unroll
+               for (int j = 0; j < kME; ++j) {
+                  const double2 tn = lds2(Pb, NBOFF(j));
+                  advn[0] += E[j][0] * tn.x;
+                  advn[1] += E[j][1] * tn.y;
+                  d0 += cfA[j][0] * (ts.x - tn.x);
+                  d1 += cfA[j][1] * (ts.y - tn.y);
+               }
+               if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[i & 1][0][0]), myoff, d0, d1);
+               tsn[0] = ts.x;
+               tsn[1] = ts.y;
+            }
+            if (i > 0) pass_B(i - 1);
+            adv[0] = advn[0]; adv[1] = advn[1];
+            tsp[0] = tsn[0]; tsp[1] = tsn[1];
+         }
+         // last iteration: only pass B of the last tracer is left, the coefficient registers are free:
+         // the next chunk's prologue operands start their way from global memory now
+         __syncthreads();
+         if (OMEGA_T2_HOIST && ch + 1 < NCh) load_prologue(ch + 1);
+         pass_B(T - 1);
+      }
 #undef NBOFF
    }
 }
@@ -1022,21 +1303,36 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
       for (int b = 0; b <= C::NS; ++b) mbar_init(smem_u32(&S.Bar[b]), 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
    }
+   if (C::TM) {
+      if (tid < 32) tmem_alloc_all(&S.TmemBase); // one CTA per SM: the whole tensor memory
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+   }
    __syncthreads();
+   if (C::TM) asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
    TileCtx X;
    X.c0 = S.Hdr.C0; X.nc = S.Hdr.NC; X.n1 = S.Hdr.N1; X.nR1 = X.nc + X.n1; X.nR = X.nR1 + S.Hdr.N2;
    for (int r = tid; r < X.nR; r += C::NT) S.GRow[r] = r < X.nc ? X.c0 + r : M.Tiles.HaloRows[S.Hdr.RowOff + r - X.nc];
    __syncthreads();
    if (tid >= C::TT) {
-      if (C::RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
-      else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-      role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
+      if constexpr (C::PAIR) {
+         asm volatile("setmaxnreg.dec.sync.aligned.u32 48;"); // releases exactly what the T role's 96 need (768 x 80 at launch)
+         role_R3<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
+      } else {
+         if (C::RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+         else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+         role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
+      }
    } else {
       asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
       X.t = tid; X.i = tid >> C::LS; X.p = tid & (C::L - 1);
       X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
       X.myoff = (X.li * C::KC + 2 * X.p) * 8u;
       role_T2<C, STAGE, OPT>(M, P, S, X, NCh, tid, kb);
+   }
+   if (C::TM) {
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncthreads();
+      if (tid < 32) tmem_free_all(S.TmemBase);
    }
 }
 
@@ -1066,7 +1362,13 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
    // R-role width (OMEGA_TILE_RS = 0, 2, 3) and bulk row copies (OMEGA_TILE_CP = 1).  The 8-level shape
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
-   const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0);
+   const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0), tm = env_i("OMEGA_TILE_TM", 0);
+   // k_fCT3 (OMEGA_TILE_V3=1): two tracers per iteration, ring coefficients in tensor memory.  Parity-green
+   // but measured slower on config 3 (6.75 ms per launch against 5.48): the second tracer's cur / next /
+   // advective registers push the T role past its 96 registers and ptxas spills the per-edge coefficients
+   // inside the tracer loop (ncu r02e: long_scoreboard on the pass-A FMAs); see profiles/r02_experiments.md
+   if (env_i("OMEGA_TILE_V3", 0)) return launch_fCT2_c<Cfg3, STAGE>(D, ca, St, TR);
+   if (tm == 1) return launch_fCT2_c<Cfg2<16, 2, 0, 1>, STAGE>(D, ca, St, TR);
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St, TR);
    if (cp == 2) return launch_fCT2_c<Cfg2<16, 2, 2>, STAGE>(D, ca, St, TR);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St, TR) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St, TR) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St, TR);
