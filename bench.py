@@ -407,7 +407,11 @@ def main():
         tr_path = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr_path) and args.workload == "config3" and world == 1:
             traffic = json.load(open(tr_path)).get("k_fCT_dram_bytes_per_launch")
-        roofline = {"bound": "hbm", "kernel": "k_fCT2 (tiled cell pass: thickness + all tracer tendencies + RK updates)",
+        path = st.last_path()
+        kname = ("k_fCT2 (tiled cell pass: thickness + all tracer tendencies + RK updates)" if path & 4 else
+                 "k_fCT (tiled cell pass without tracer hyperdiffusion)" if path & 2 else
+                 "k_fC_center (untiled cell pass: level count not a multiple of 16)")
+        roofline = {"bound": "hbm", "kernel": kname,
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg_fc, "algorithmic_bytes_by_stage": alg_stage,
