@@ -98,6 +98,28 @@ void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NT
    OMEGA_LAUNCH_TR(3, NAll, NSize, K, NTracers, Next, nullptr, H, nullptr, 0.0, nullptr);
 }
 
+// One slab of HOST rows [Row0, Row0 + NSlab) of one [NRows][NInner] field, staged contiguously in Stage:
+// ToDevice: Dev[DevRowOfHost[Row0 + i]] = Stage[i];  else: Stage[i] = Dev[DevRowOfHost[Row0 + i]]
+template <bool ToDevice>
+__global__ void __launch_bounds__(kBlock)
+k_slab_rows(int Row0, int NSlab, int NInner, const int *__restrict__ DevRowOfHost, double *__restrict__ Dev,
+            double *__restrict__ Stage) {
+   const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+   if (w >= (long long)NSlab * NInner) return;
+   const int i = (int)(w / NInner), k = (int)(w - (long long)i * NInner);
+   const size_t d = (size_t)DevRowOfHost[Row0 + i] * NInner + k;
+   if (ToDevice) Dev[d] = Stage[w];
+   else Stage[w] = Dev[d];
+}
+
+void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, double *Dev,
+                      double *Stage) {
+   const long long total = (long long)NSlab * NInner;
+   if (total <= 0) return;
+   if (ToDevice) k_slab_rows<true><<<grid_for(total), kBlock, 0, S>>>(Row0, NSlab, NInner, DevRowOfHost, Dev, Stage);
+   else k_slab_rows<false><<<grid_for(total), kBlock, 0, S>>>(Row0, NSlab, NInner, DevRowOfHost, Dev, Stage);
+}
+
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
                          const double *Src, double *Dst) {
    const long long total = (long long)NOuter * NRows * NInner;

@@ -190,6 +190,9 @@ void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int 
 void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
                              const double *H);
 
+// one slab of host rows of a field between a contiguous staging block and the device-order array
+void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, double *Dev,
+                      double *Stage);
 // gather/scatter rows through a permutation (field transfer, halo)
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
                          const double *Src, double *Dst);
