@@ -1,6 +1,8 @@
 // kernels_update.cu -- the stage-update kernels of TimeStepper
 // (components/omega/src/timeStepping/TimeStepper.cpp:378-524) and the row
 // permutation used by field transfers and the halo pack/unpack.
+#include <algorithm>
+
 #include "kernel_util.cuh"
 #include "omega_dev.h"
 
@@ -118,6 +120,46 @@ void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NI
    if (total <= 0) return;
    if (ToDevice) k_slab_rows<true><<<grid_for(total), kBlock, 0, S>>>(Row0, NSlab, NInner, DevRowOfHost, Dev, Stage);
    else k_slab_rows<false><<<grid_for(total), kBlock, 0, S>>>(Row0, NSlab, NInner, DevRowOfHost, Dev, Stage);
+}
+
+// The whole field between PINNED host memory (read / written by the kernel itself over PCIe, no staging) and
+// the device-order array: Dev[o][DevRowOfHost[r]][:] <-> Host[o][r][:].  A warp moves one row at a time with
+// 16-byte accesses (a 64-level row = 512 contiguous bytes on both sides).  Few small CTAs: the kernel lives
+// beside the stage kernels of another stream and is bound by the link, not by the SMs.
+template <bool ToDevice, int V>
+__global__ void __launch_bounds__(128)
+k_rows_hostmem(int NOuter, int NRows, int NInner, const int *__restrict__ DevRowOfHost, double *__restrict__ Dev,
+               double *__restrict__ Host) {
+   const int KV = NInner / V;
+   const long long total = (long long)NOuter * NRows * KV;
+   for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
+      const int kv      = (int)(w % KV);
+      const long long t = w / KV;
+      const int r = (int)(t % NRows), o = (int)(t / NRows);
+      const size_t h = (size_t)t * NInner + (size_t)kv * V;
+      const size_t d = ((size_t)o * NRows + DevRowOfHost[r]) * NInner + (size_t)kv * V;
+      if (V == 2) {
+         if (ToDevice) *reinterpret_cast<double2 *>(Dev + d) = __ldcs(reinterpret_cast<const double2 *>(Host + h));
+         else __stcs(reinterpret_cast<double2 *>(Host + h), *reinterpret_cast<const double2 *>(Dev + d));
+      } else {
+         if (ToDevice) Dev[d] = __ldcs(Host + h);
+         else __stcs(Host + h, Dev[d]);
+      }
+   }
+}
+
+void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, double *Dev,
+                         double *Host, int NCtas) {
+   const long long total = (long long)NOuter * NRows * NInner;
+   if (total <= 0) return;
+   const unsigned g = (unsigned)std::max(1, NCtas);
+   if ((NInner & 1) == 0) {
+      if (ToDevice) k_rows_hostmem<true, 2><<<g, 128, 0, S>>>(NOuter, NRows, NInner, DevRowOfHost, Dev, Host);
+      else k_rows_hostmem<false, 2><<<g, 128, 0, S>>>(NOuter, NRows, NInner, DevRowOfHost, Dev, Host);
+   } else {
+      if (ToDevice) k_rows_hostmem<true, 1><<<g, 128, 0, S>>>(NOuter, NRows, NInner, DevRowOfHost, Dev, Host);
+      else k_rows_hostmem<false, 1><<<g, 128, 0, S>>>(NOuter, NRows, NInner, DevRowOfHost, Dev, Host);
+   }
 }
 
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,

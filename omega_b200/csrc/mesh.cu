@@ -743,12 +743,10 @@ int omega_mesh_derived(const OmegaMesh *M, double *EdgeSignOnCell, double *EdgeS
    return 0;
 }
 
-// Field transfers with the permutation applied.  The host array moves in slabs of consecutive HOST rows through
-// ONE fixed-size staging block (64 MB, a stream-ordered allocation) instead of a second full-size copy of the
-// field (3.4 GB for the ten tracers of config 3, 10.7 GB at 32 tracers): a slab is copied, then scattered to /
-// gathered from its device rows (DIPerm: device row of a host row).  The permute kernel of a slab costs ~1.5 %
-// of its PCIe copy, so running the two in order on the caller's stream loses nothing measurable; transfers on
-// different streams (bench.py's e2e pipeline) overlap as before.
+// Field transfers with the permutation applied (see the three modes inside).  The slab path moves the host array
+// in slabs of consecutive HOST rows through ONE fixed-size staging block (64 MB) instead of a second full-size
+// copy of the field (3.4 GB for the ten tracers of config 3, 10.7 GB at 32 tracers): a slab is copied, then
+// scattered to / gathered from its device rows (DIPerm: device row of a host row).
 static constexpr size_t kSlabBytes = 64u << 20;
 
 static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, double *Dev, double *Host,
@@ -759,6 +757,49 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
    if (!M->Reordered) {
       if (ToDevice) OMEGA_CUDA_CHECK(cudaMemcpyAsync(Dev, Host, bytes, cudaMemcpyHostToDevice, S));
       else OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, Dev, bytes, cudaMemcpyDeviceToHost, S));
+      return 0;
+   }
+   // Three ways, measured on config 3 with the bench's three-stream e2e pipeline (uploads, steps and downloads
+   // of consecutive steps overlap; 4.7 GB each way per step):
+   //   full  (default)  one copy of the whole field through a full-size stream-ordered staging block + one
+   //                    permute kernel: 112 ms/step.  Costs a transient second copy of the field.
+   //   slab             64 MB slabs of host rows through one small block: 138 ms/step -- every slab's permute
+   //                    kernel waits for SM room beside the stage kernels of the compute stream.  Taken
+   //                    automatically for a field larger than an eighth of the device's memory.
+   //   zerocopy         the kernel reads / writes PINNED host memory itself over PCIe: 180 ms/step.
+   const char *mode = getenv("OMEGA_XFER");
+   // (the device's total memory is looked up once; a per-call cudaMemGetInfo would serialise the streams)
+   static size_t totalB = 0;
+   if (!totalB) {
+      size_t freeB = 0;
+      if (cudaMemGetInfo(&freeB, &totalB) != cudaSuccess) totalB = (size_t)16 << 30;
+   }
+   const bool wantSlab = mode && !strcmp(mode, "slab");
+   if (mode && !strcmp(mode, "zerocopy")) {
+      cudaPointerAttributes at;
+      const bool pinned = cudaPointerGetAttributes(&at, Host) == cudaSuccess && at.type == cudaMemoryTypeHost;
+      cudaGetLastError(); // a pageable pointer is not an error
+      if (pinned) {
+         int dev = 0, sm = 0;
+         OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+         OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+         launch_rows_hostmem(S, ToDevice, NOuter, NRows, NInner, M->DIPerm[Elem], Dev, (double *)at.devicePointer, 2 * sm);
+         OMEGA_CUDA_CHECK(cudaGetLastError());
+         return 0;
+      }
+   }
+   if (!wantSlab && bytes <= totalB / 8) {
+      double *stage = nullptr;
+      OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, bytes, S));
+      if (ToDevice) {
+         OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));
+         launch_permute_rows(S, NOuter, NRows, NInner, M->DPerm[Elem], stage, Dev);   // device row r <- host row Perm[r]
+      } else {
+         launch_permute_rows(S, NOuter, NRows, NInner, M->DIPerm[Elem], Dev, stage);  // host row r <- device row IPerm[r]
+         OMEGA_CUDA_CHECK(cudaMemcpyAsync(Host, stage, bytes, cudaMemcpyDeviceToHost, S));
+      }
+      OMEGA_CUDA_CHECK(cudaGetLastError());
+      OMEGA_CUDA_CHECK(cudaFreeAsync(stage, S));
       return 0;
    }
    const size_t rowBytes = (size_t)NInner * sizeof(double);

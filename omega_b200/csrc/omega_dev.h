@@ -193,6 +193,9 @@ void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NT
 // one slab of host rows of a field between a contiguous staging block and the device-order array
 void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, double *Dev,
                       double *Stage);
+// the whole field between pinned host memory and the device-order array, no staging
+void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, double *Dev,
+                         double *Host, int NCtas);
 // gather/scatter rows through a permutation (field transfer, halo)
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
                          const double *Src, double *Dst);

@@ -48,6 +48,31 @@ def case(request):
     return request.param, CASES[request.param]()
 
 
+@pytest.mark.parametrize("xfer", ["full", "slab", "zerocopy"])
+def test_field_transfer_modes_bit_exact(monkeypatch, xfer):
+    """omega_field_to_device / to_host with the permutation applied, all three transfer paths (full-size staging,
+    64 MB slabs, kernel access to pinned host memory), pageable and pinned host arrays, several slabs per field."""
+    import torch
+    monkeypatch.setenv("OMEGA_XFER", xfer)
+    L, cfg, (h, u, tr), dt = cases.sphere_case(5, 64, 12)      # tracers: 12 x 10 243 x 64 x 8 B = 63 MB -> slabs
+    big = np.ascontiguousarray(np.repeat(tr, 2, axis=0))       # 126 MB: the last slab is a partial one
+    mesh, st, state = gpu_objects(L, cfg, 0)
+    p, _ = mesh.perm(capi.ON_CELL)
+    for host in (big, u):
+        kind = capi.ON_CELL if host.ndim == 3 else capi.ON_EDGE
+        d = mesh.to_device(kind, host)
+        pe, _ = mesh.perm(kind)
+        assert np.array_equal(d.cpu().numpy(), host[..., pe, :]), "device order must be host[perm]"
+        assert np.array_equal(mesh.to_host(kind, d), host)
+        src = torch.from_numpy(host).pin_memory()
+        dst = torch.empty(host.shape, dtype=torch.float64).pin_memory()
+        d2 = mesh.to_device(kind, src.numpy())
+        mesh.to_host(kind, d2, dst.numpy(), sync=False)
+        torch.cuda.current_stream().synchronize()
+        assert np.array_equal(dst.numpy(), host)
+    st.close(); mesh.close()
+
+
 @pytest.mark.parametrize("reorder", [True, False])
 def test_permutation_and_transfer_bit_exact(case, reorder):
     _, (L, cfg, (h, u, tr), dt) = case
@@ -78,6 +103,17 @@ def test_permutation_and_transfer_bit_exact(case, reorder):
         mesh.to_host(capi.ON_EDGE, d, pin.numpy(), sync=False)
     side.synchronize()
     assert np.array_equal(pin.numpy(), u)
+    # pinned SOURCE: the library reads it over PCIe from the kernel itself (no staging), permutation applied
+    src = torch.from_numpy(np.ascontiguousarray(u)).pin_memory()
+    d2 = mesh.to_device(capi.ON_EDGE, src.numpy())
+    assert np.array_equal(mesh.to_host(capi.ON_EDGE, d2), u)
+    if tr.shape[0]:
+        srct = torch.from_numpy(np.ascontiguousarray(tr)).pin_memory()
+        pint = torch.empty(tr.shape, dtype=torch.float64).pin_memory()
+        dt_ = mesh.to_device(capi.ON_CELL, srct.numpy())
+        mesh.to_host(capi.ON_CELL, dt_, pint.numpy(), sync=False)
+        torch.cuda.current_stream().synchronize()
+        assert np.array_equal(pint.numpy(), tr)
     st.close(); mesh.close()
 
 
