@@ -315,6 +315,37 @@ int omega_halo_tile_classes(const OmegaHalo *Halo, int *NBoundary, int *NOwned, 
 int omega_halo_set_profiling(OmegaHalo *Halo, int Enable);
 int omega_halo_get_profile(OmegaHalo *Halo, double *Ms, long long *Rounds, long long *Bytes);
 
+/* ---- Omega-1 column pieces around the horizontal path ------------
+ * Device arrays in device order, [NCellsSize][NVertLayers] unless noted; MinLayerCell / MaxLayerCell
+ * [NCellsSize] int (device order): the active layer range of a column (VertCoord.h).
+ * VertCoord::computePressure / computeZHeight / computeGeopotential / computeTargetThickness
+ * (src/ocn/VertCoord.cpp:648-860): interfaces are [NCellsSize][NVertLayers + 1]; surface pressure, tidal
+ * potential, self attraction and loading [NCellsSize]; MovementWeights [NVertLayers]; BottomDepth is the mesh's. */
+int omega_vert_compute_pressure(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
+                                const double *LayerThickness, const double *SurfacePressure,
+                                double *PressureInterface, double *PressureMid, void *Stream);
+int omega_vert_compute_z_height(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
+                                const double *LayerThickness, const double *SpecVol, double *ZInterface,
+                                double *ZMid, void *Stream);
+int omega_vert_compute_geopotential(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell,
+                                    const double *ZMid, const double *TidalPotential,
+                                    const double *SelfAttractionLoading, double *GeopotentialMid, void *Stream);
+int omega_vert_compute_target_thickness(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell,
+                                        double Rho0, const double *PressureInterface, const double *RefLayerThickness,
+                                        const double *MovementWeights, double *LayerThicknessTarget, void *Stream);
+/* Eos::computeSpecVol / computeSpecVolDisp (src/ocn/Eos.h:29-292).  EosType 0: linear, 1 / (RhoT0S0 + DRhodT CT +
+ * DRhodS SA); 1: TEOS-10 75-term polynomial of Roquet et al. (2015), pressure in dbar.  KDisp != 0: specific volume
+ * of the parcel displaced to the pressure of layer clamp(k + KDisp) (TEOS-10). */
+int omega_eos_compute_spec_vol(const OmegaMesh *Mesh, int EosType, const double *ConservTemp, const double *AbsSalinity,
+                               const double *Pressure, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
+                               double *SpecVol, void *Stream);
+/* TriDiagSolver / TriDiagDiffSolver (src/base/TriDiagSolvers.h): NBatch independent systems of NRow <= 1024 rows,
+ * arrays [NBatch][NRow] on the device, X holds the right-hand side on entry and the solution on return.
+ * General form: DL(k) x(k-1) + D(k) x(k) + DU(k) x(k+1) = X(k).  Diffusion form: D(k) = H(k) + G(k-1) + G(k),
+ * DL(k) = -G(k-1), DU(k) = -G(k), solved without ever forming D (stable for abrupt jumps in G). */
+int omega_tridiag_solve(int NBatch, int NRow, const double *DL, const double *D, const double *DU, double *X, void *Stream);
+int omega_tridiag_diffusion_solve(int NBatch, int NRow, const double *G, const double *H, double *X, void *Stream);
+
 /* ---- Decomp (src/base/Decomp.cpp) -- host code, no device work ------------------
  * One rank's partition of the GLOBAL mesh in Omega's local numbering, the owner
  * address of every local element (CellLoc / EdgeLoc / VertexLoc, Decomp.cpp:1094-1098,1639-1676) and the
