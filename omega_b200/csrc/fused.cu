@@ -1046,13 +1046,14 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
    TileRange trBnd = trAll, trInt = trAll;
    if (split) {
       const int nB = Hl->NTilesBoundary, nO = Hl->NTilesOwned, nH = D.Tiles.NTiles - nO;
-      if (sd.SkipHaloOK) {
-         trBnd = TileRange{Hl->DTileOrder, 0, nB};
-         trInt = TileRange{Hl->DTileOrder, nB, nO - nB};
-      } else {
-         trBnd = TileRange{Hl->DTileOrderBH, 0, nB + nH};
-         trInt = TileRange{Hl->DTileOrderBH, nB + nH, nO - nB};
-      }
+      // the first launch is filled up with interior tiles to whole rounds of CTAs (one tile CTA per SM in the
+      // cell pass, 2 x 4 chunk CTAs per SM = 74 tiles per round in the edge pass): a launch of the boundary
+      // tiles alone is a fraction of a round and costs a whole one
+      const int first = sd.SkipHaloOK ? nB : nB + nH, total = sd.SkipHaloOK ? nO : nO + nH;
+      const int n1 = std::min(total, (first + Hl->NumSMs - 1) / Hl->NumSMs * Hl->NumSMs);
+      const int *map = sd.SkipHaloOK ? Hl->DTileOrder : Hl->DTileOrderBH;
+      trBnd = TileRange{map, 0, n1};
+      trInt = TileRange{map, n1, total - n1};
       S->LastPath |= OMEGA_PATH_HALO_SPLIT;
    }
    if (tr4 && !tiled) LAUNCH_V(kFT2, k_fT2, gT, D, sd.Hs, sd.Trs, T, S->A.Del2Tr);

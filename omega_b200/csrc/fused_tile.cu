@@ -1092,13 +1092,35 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
          }
       }
       if constexpr (C::PAIR) {
-         // ---- two tracers per iteration: pass B of the previous pair, then pass A of this pair
+         // ---- two tracers per barrier, ONE register set for the RK operands: within an iteration the four
+         // passes alternate B(a'), A(a), B(b'), A(b) (a', b' = the previous pair), so the cur / next values of
+         // b' load while pass A of a runs and those of the next iteration's a' while pass A of b runs
          const int NP = (T + 1) >> 1;
-         double tcur[2][2] = {{0, 0}, {0, 0}}, acc[2][2] = {{0, 0}, {0, 0}}, adv[2][2] = {{0, 0}, {0, 0}};
-         auto preload = [&](int l, int q) { // cur / next of tracer l: in flight until its pass B, one iteration later
+         double tcur[2] = {0, 0}, acc[2] = {0, 0}, adv[2][2] = {{0, 0}, {0, 0}}, tsp[2][2] = {{0, 0}, {0, 0}};
+         auto preload = [&](int l) {
             if (own && l < T) {
-               if (need_cur) ldg_na(tcur[q], P.TrCur + (size_t)l * CS + o);
-               if (!First) ldg_na(acc[q], P.TrNext + (size_t)l * CS + o);
+               if (need_cur) ldg_na(tcur, P.TrCur + (size_t)l * CS + o);
+               if (!First) ldg_na(acc, P.TrNext + (size_t)l * CS + o);
+            }
+         };
+         auto pass_A = [&](int l, int q, int db) { // every neighbour row once, two sums
+            const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + l) % NS][0][0]);
+            const double2 ts = lds2(Pb, myoff);
+            double d0 = 0, d1 = 0, a0 = ts.x * S0[0], a1 = ts.y * S0[1];
+#pragma unroll
+            for (int j = 0; j < kME; ++j) {
+               const double2 tn = lds2(Pb, NBOFF(j));
+               a0 += E[j][0] * tn.x;
+               a1 += E[j][1] * tn.y;
+               d0 += cfA[j][0] * (ts.x - tn.x);
+               d1 += cfA[j][1] * (ts.y - tn.y);
+            }
+            if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[db][0][0]), myoff, d0, d1);
+            adv[q][0] = a0;
+            adv[q][1] = a1;
+            if (tcur_is_ts) { // first stage on the current state: cur is the stage value itself
+               tsp[q][0] = ts.x;
+               tsp[q][1] = ts.y;
             }
          };
          auto pass_B = [&](int l, int q, int db) {
@@ -1120,57 +1142,34 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
                double2 w0v = make_double2(0, 0);
                if (First || Last) w0v = S.W[0][tid];
                const double w0[2] = {w0v.x, w0v.y};
+               const double tc[2] = {tcur_is_ts ? tsp[q][0] : tcur[0], tcur_is_ts ? tsp[q][1] : tcur[1]};
 #pragma unroll
                for (int x = 0; x < 2; ++x) {
-                  out[x] = (First ? tcur[q][x] * w0[x] : acc[q][x]) + P.B * tend[x];
+                  out[x] = (First ? tc[x] * w0[x] : acc[x]) + P.B * tend[x];
                   if (Last) out[x] *= w0[x];
                }
                stg_na(P.TrNext + l * CS + o, out);
                if (!Last) {
                   const double2 w1v = S.W[1][tid], w2v = S.W[2][tid];
-                  out[0] = tcur[q][0] * w1v.x + tend[0] * w2v.x;
-                  out[1] = tcur[q][1] * w1v.y + tend[1] * w2v.y;
+                  out[0] = tc[0] * w1v.x + tend[0] * w2v.x;
+                  out[1] = tc[1] * w1v.y + tend[1] * w2v.y;
                   stg_na(P.TrProv + l * CS + o, out);
                }
             }
          };
-         if (!tcur_is_ts || !First) {
-            preload(0, 0);
-            preload(1, 1);
-         }
+         preload(0);
          for (int pi = 0; pi <= NP; ++pi) {
             __syncthreads(); // pair pi has landed; Del2 of pair pi-1 is complete (own rows: T role, ring 1: R role)
+            const int a = 2 * pi, ap = a - 2, dbp = 2 * ((pi - 1) & 1), dbn = 2 * (pi & 1);
             if (pi > 0) {
-               const int a = 2 * (pi - 1), db = 2 * ((pi - 1) & 1);
-               pass_B(a, 0, db);
-               if (a + 1 < T) pass_B(a + 1, 1, db + 1);
-               if (pi < NP) { // operands of this pair's pass B, one iteration from now
-                  preload(2 * pi, 0);
-                  preload(2 * pi + 1, 1);
-               }
+               pass_B(ap, 0, dbp);
+               preload(ap + 1); // second tracer of the previous pair: lands while pass A of a runs
             }
+            if (pi < NP) pass_A(a, 0, dbn);
+            if (pi > 0 && ap + 1 < T) pass_B(ap + 1, 1, dbp + 1);
             if (pi < NP) {
-               const int a = 2 * pi, nb = T - a < 2 ? T - a : 2;
-               for (int q = 0; q < nb; ++q) { // pass A: every neighbour row once, two sums
-                  const unsigned char *Pb = reinterpret_cast<const unsigned char *>(&S.Phi[(it0 + a + q) % NS][0][0]);
-                  const double2 ts = lds2(Pb, myoff);
-                  double d0 = 0, d1 = 0, a0 = ts.x * S0[0], a1 = ts.y * S0[1];
-#pragma unroll
-                  for (int j = 0; j < kME; ++j) {
-                     const double2 tn = lds2(Pb, NBOFF(j));
-                     a0 += E[j][0] * tn.x;
-                     a1 += E[j][1] * tn.y;
-                     d0 += cfA[j][0] * (ts.x - tn.x);
-                     d1 += cfA[j][1] * (ts.y - tn.y);
-                  }
-                  if (own) sts2(reinterpret_cast<unsigned char *>(&S.D2[2 * (pi & 1) + q][0][0]), myoff, d0, d1);
-                  adv[q][0] = a0;
-                  adv[q][1] = a1;
-                  if (tcur_is_ts) { // first stage on the current state: cur is the stage value itself
-                     tcur[q][0] = ts.x;
-                     tcur[q][1] = ts.y;
-                  }
-               }
+               preload(a); // first pass B of the next iteration
+               if (a + 1 < T) pass_A(a + 1, 1, dbn + 1);
             }
          }
       } else {
@@ -1364,9 +1363,10 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
    const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0), tm = env_i("OMEGA_TILE_TM", 0);
    // k_fCT3 (OMEGA_TILE_V3=1): two tracers per iteration, ring coefficients in tensor memory.  Parity-green
-   // but measured slower on config 3 (6.75 ms per launch against 5.48): the second tracer's cur / next /
-   // advective registers push the T role past its 96 registers and ptxas spills the per-edge coefficients
-   // inside the tracer loop (ncu r02e: long_scoreboard on the pass-A FMAs); see profiles/r02_experiments.md
+   // but measured slower on config 3 (5.97 ms per launch against 5.47; a first form with two register sets
+   // of RK operands: 6.75, T-role spills): the R role -- half the warps, all copies, tcgen05.ld + wait in
+   // front of every ring Del2 sum -- becomes the critical path (ncu r02h: 16 % of the samples are T warps at
+   // the pair barrier); see profiles/r02_experiments.md
    if (env_i("OMEGA_TILE_V3", 0)) return launch_fCT2_c<Cfg3, STAGE>(D, ca, St, TR);
    if (tm == 1) return launch_fCT2_c<Cfg2<16, 2, 0, 1>, STAGE>(D, ca, St, TR);
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St, TR);

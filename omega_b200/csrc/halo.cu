@@ -338,6 +338,11 @@ int omega_halo_create(const OmegaMesh *M, const OmegaHaloDesc *D, OmegaHalo **Ou
       H->HaloCovered = H->RecvOff[0][D->NNeighbors] == M->D.NCellsAll - M->D.NCellsOwned &&
                        H->RecvOff[1][D->NNeighbors] == M->D.NEdgesAll - M->D.NEdgesOwned;
    }
+   {
+      int dev = 0;
+      OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+      OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&H->NumSMs, cudaDevAttrMultiProcessorCount, dev));
+   }
    int lo = 0, hi = 0;
    OMEGA_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
    OMEGA_CUDA_CHECK(cudaStreamCreateWithPriority(&H->CommStream, cudaStreamNonBlocking, hi));

@@ -37,7 +37,7 @@ struct OmegaHalo {
    cudaEvent_t EvReady = nullptr, EvDone = nullptr;
    int *DTileOrder = nullptr;   // [boundary tiles | other owned tiles | halo tiles]
    int *DTileOrderBH = nullptr; // [boundary tiles | halo tiles | other owned tiles]
-   int NTilesBoundary = 0, NTilesOwned = 0, HaloCovered = 0;
+   int NTilesBoundary = 0, NTilesOwned = 0, HaloCovered = 0, NumSMs = 148;
    // CUDA-event timing of the rounds (bench: ms per round, bytes against NVLink)
    int Profiling = 0;
    long long Rounds = 0;
