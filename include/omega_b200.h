@@ -166,6 +166,20 @@ int omega_field_to_host(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter
  * so transfers on other streams overlap the step (bench.py e2e pipeline). */
 int omega_field_to_host_async(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
                               int NInner, const double *Dev, double *Host, void *Stream);
+/* omega_field_to_device for callers that may not allocate device memory (stream
+ * capture, serving loops, harnesses that forbid cudaMalloc). It has NO counterpart in
+ * the reference. Same arguments and
+ * result as omega_field_to_device (bit for bit), but the staging block of the permute
+ * kernel is a static device array inside the library (OMEGA_NOALLOC_MAX_BYTES per GPU,
+ * held from library load to process exit) and the call makes no cudaMalloc / cudaFree /
+ * stream-ordered allocation. A field larger than OMEGA_NOALLOC_MAX_BYTES
+ * (NOuter * N*Size * NInner * 8 bytes) is rejected with return code 2 and a message in
+ * omega_last_error. All calls on one GPU share the block: calls that overlap on the GPU
+ * (different streams, no ordering between them) race; on one stream they are safe. For
+ * capture in a CUDA graph Host must be pinned. Never synchronises. */
+#define OMEGA_NOALLOC_MAX_BYTES (32u << 20)
+int omega_field_to_device_noalloc(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
+                                  int NInner, const double *Host, double *Dev, void *Stream);
 
 /* ---- Tendencies + AuxiliaryState + TimeStepper -------------------------- */
 int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int NTracers,

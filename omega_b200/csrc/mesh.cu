@@ -851,3 +851,53 @@ int omega_field_to_host_async(const OmegaMesh *M, OmegaMeshElement Elem, int NOu
 }
 
 } // extern "C"
+
+// ---- omega_field_to_device_noalloc: the upload with its staging block in a file-scope device array -------------
+// For callers that may not allocate (stream capture, serving loops, harnesses that forbid cudaMalloc).  The array is
+// part of the library image: every GPU that loads the library holds kNoAllocStageBytes until the process exits.
+// In host code the NAME below is a host-side stand-in, not a device address; the address a kernel or a copy may
+// use comes from cudaGetSymbolAddress, looked up once per device with that device current.
+namespace omega {
+constexpr size_t kNoAllocStageBytes = (size_t)OMEGA_NOALLOC_MAX_BYTES;
+static __device__ __align__(256) double g_noalloc_stage[kNoAllocStageBytes / sizeof(double)];
+
+static int noalloc_stage_ptr(double **Ptr) {
+   constexpr int kMaxDevices = 64;
+   static double *perDevice[kMaxDevices] = {};
+   int dev = 0;
+   OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+   OMEGA_REQUIRE(dev >= 0 && dev < kMaxDevices, "omega_field_to_device_noalloc: device ordinal beyond 63");
+   if (!perDevice[dev]) {
+      double *p = nullptr;
+      OMEGA_CUDA_CHECK(cudaGetSymbolAddress((void **)&p, g_noalloc_stage));
+      OMEGA_REQUIRE(p, "omega_field_to_device_noalloc: cudaGetSymbolAddress returned a null address");
+      perDevice[dev] = p;
+   }
+   *Ptr = perDevice[dev];
+   return 0;
+}
+} // namespace omega
+
+extern "C" int omega_field_to_device_noalloc(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
+                                             const double *Host, double *Dev, void *Stream) {
+   OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3 && NOuter >= 0 && NInner >= 0,
+                 "omega_field_to_device_noalloc: bad argument");
+   const int NRows    = n_size(M, Elem);
+   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
+   if (bytes == 0) return 0;
+   OMEGA_REQUIRE(bytes <= kNoAllocStageBytes,
+                 "omega_field_to_device_noalloc: field of " + std::to_string(bytes) + " bytes exceeds the static staging block (" +
+                     std::to_string(kNoAllocStageBytes) + " bytes, OMEGA_NOALLOC_MAX_BYTES); use omega_field_to_device");
+   cudaStream_t S = (cudaStream_t)Stream;
+   if (!M->Reordered) { // no permutation, no staging
+      OMEGA_CUDA_CHECK(cudaMemcpyAsync(Dev, Host, bytes, cudaMemcpyHostToDevice, S));
+      return 0;
+   }
+   double *stage = nullptr;
+   if (int rc = noalloc_stage_ptr(&stage)) return rc;
+   // every element of stage[0, bytes) is overwritten by the copy before the kernel reads it: nothing to clear
+   OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));
+   launch_permute_rows(S, NOuter, NRows, NInner, M->DPerm[Elem], stage, Dev); // device row r <- host row Perm[r]
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   return 0;
+}
