@@ -17,7 +17,7 @@
  *  - "device order" = the library's space-filling-curve order of the same
  *    rows (owned block and halo block sorted separately, boundary slot
  *    last); omega_mesh_perm() returns the bit-exact maps;
- *  - fields are fp64, layout [element][level] (LayoutRight,
+ *  - fields are OmegaReal (fp64; fp32 in libomega_b200_sp.so), layout [element][level] (LayoutRight,
  *    src/base/DataTypes.h:58-61), tracers [tracer][cell][level];
  *  - device pointers handed to compute entry points are in DEVICE order and
  *    must have been allocated with row count N*Size.
@@ -27,6 +27,17 @@
 
 #ifdef __cplusplus
 extern "C" {
+#endif
+
+/* Real of the reference (src/base/DataTypes.h:30-34): fp64 unless the library is built with
+ * -DOMEGA_SINGLE_PRECISION (libomega_b200_sp.so).  Every FIELD array of this header (state, auxiliary,
+ * tendency, halo and transfer buffers, the column pieces) is OmegaReal; mesh geometry handed to
+ * omega_mesh_create, configuration values, times and stage coefficients stay double in both builds and
+ * are converted inside.  omega_b200_real_bytes() tells a host which build it has loaded. */
+#ifdef OMEGA_SINGLE_PRECISION
+typedef float OmegaReal;
+#else
+typedef double OmegaReal;
 #endif
 
 /* src/base/Halo.h:45 */
@@ -82,21 +93,21 @@ typedef struct OmegaTendConfig {
  * HTracersEdge [NTracers][NEdgesSize][K]; Del2TracersCell
  * [NTracers][NCellsSize][K]; the three wind arrays are 1-D. */
 typedef struct OmegaAuxArrays {
-   double *KineticEnergyCell, *VelocityDivCell;
-   double *FluxLayerThickEdge, *MeanLayerThickEdge, *SshCell;
-   double *RelVortVertex, *NormRelVortVertex, *NormPlanetVortVertex;
-   double *NormRelVortEdge, *NormPlanetVortEdge;
-   double *Del2Edge, *Del2DivCell, *Del2RelVortVertex;
-   double *HTracersEdge, *Del2TracersCell;
-   double *NormalStressEdge, *ZonalStressCell, *MeridStressCell;
+   OmegaReal *KineticEnergyCell, *VelocityDivCell;
+   OmegaReal *FluxLayerThickEdge, *MeanLayerThickEdge, *SshCell;
+   OmegaReal *RelVortVertex, *NormRelVortVertex, *NormPlanetVortVertex;
+   OmegaReal *NormRelVortEdge, *NormPlanetVortEdge;
+   OmegaReal *Del2Edge, *Del2DivCell, *Del2RelVortVertex;
+   OmegaReal *HTracersEdge, *Del2TracersCell;
+   OmegaReal *NormalStressEdge, *ZonalStressCell, *MeridStressCell;
 } OmegaAuxArrays;
 
 /* Tendencies::LayerThicknessTend / NormalVelocityTend / TracerTend
  * (src/ocn/Tendencies.h:55-57). */
 typedef struct OmegaTendArrays {
-   double *LayerThicknessTend; /* [NCellsSize][K] */
-   double *NormalVelocityTend; /* [NEdgesSize][K] */
-   double *TracerTend;         /* [NTracers][NCellsSize][K] */
+   OmegaReal *LayerThicknessTend; /* [NCellsSize][K] */
+   OmegaReal *NormalVelocityTend; /* [NEdgesSize][K] */
+   OmegaReal *TracerTend;         /* [NTracers][NCellsSize][K] */
 } OmegaTendArrays;
 
 /* OceanState + Tracers time-level rings (src/ocn/OceanState.cpp:65-117,
@@ -106,9 +117,9 @@ typedef struct OmegaStateArrays {
    int CurTimeIndex;     /* OceanState::CurTimeIndex */
    int TracerCurTimeIndex; /* Tracers::CurTimeIndex */
    int NTracers;
-   double *LayerThickness[2]; /* [NCellsSize][K] per ring slot */
-   double *NormalVelocity[2]; /* [NEdgesSize][K] */
-   double *Tracers[2];        /* [NTracers][NCellsSize][K] */
+   OmegaReal *LayerThickness[2]; /* [NCellsSize][K] per ring slot */
+   OmegaReal *NormalVelocity[2]; /* [NEdgesSize][K] */
+   OmegaReal *Tracers[2];        /* [NTracers][NCellsSize][K] */
 } OmegaStateArrays;
 
 /* Stage coefficients already multiplied by the time step and evaluated the
@@ -130,6 +141,7 @@ typedef struct OmegaHalo OmegaHalo;       /* Halo exchange lists on device */
 
 const char *omega_last_error(void);
 int omega_b200_abi_version(void);
+int omega_b200_real_bytes(void); /* sizeof(OmegaReal): 8, or 4 in the single-precision build */
 
 /* ---- device memory (replaces Kokkos View allocation, zero-initialised) -- */
 int omega_dev_alloc(void **ptr, unsigned long long bytes);
@@ -157,15 +169,15 @@ int omega_mesh_derived(const OmegaMesh *Mesh, double *EdgeSignOnCell,
  * same shape in device order (OceanState::copyToDevice/copyToHost,
  * src/ocn/OceanState.cpp:300-328). Host may be pageable or pinned. */
 int omega_field_to_device(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
-                          int NInner, const double *Host, double *Dev, void *Stream);
+                          int NInner, const OmegaReal *Host, OmegaReal *Dev, void *Stream);
 int omega_field_to_host(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
-                        int NInner, const double *Dev, double *Host, void *Stream);
+                        int NInner, const OmegaReal *Dev, OmegaReal *Host, void *Stream);
 /* Same, without the final stream synchronisation: Host must be pinned and is valid
  * once the caller has synchronised Stream (or an event recorded after the call).
  * omega_field_to_device never synchronises; with a pinned Host it is asynchronous too,
  * so transfers on other streams overlap the step (bench.py e2e pipeline). */
 int omega_field_to_host_async(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
-                              int NInner, const double *Dev, double *Host, void *Stream);
+                              int NInner, const OmegaReal *Dev, OmegaReal *Host, void *Stream);
 /* omega_field_to_device for callers that may not allocate device memory (stream
  * capture, serving loops, harnesses that forbid cudaMalloc). It has NO counterpart in
  * the reference. Same arguments and
@@ -173,13 +185,13 @@ int omega_field_to_host_async(const OmegaMesh *Mesh, OmegaMeshElement Elem, int 
  * kernel is a static device array inside the library (OMEGA_NOALLOC_MAX_BYTES per GPU,
  * held from library load to process exit) and the call makes no cudaMalloc / cudaFree /
  * stream-ordered allocation. A field larger than OMEGA_NOALLOC_MAX_BYTES
- * (NOuter * N*Size * NInner * 8 bytes) is rejected with return code 2 and a message in
+ * (NOuter * N*Size * NInner * sizeof(OmegaReal) bytes) is rejected with return code 2 and a message in
  * omega_last_error. All calls on one GPU share the block: calls that overlap on the GPU
  * (different streams, no ordering between them) race; on one stream they are safe. For
  * capture in a CUDA graph Host must be pinned. Never synchronises. */
 #define OMEGA_NOALLOC_MAX_BYTES (32u << 20)
 int omega_field_to_device_noalloc(const OmegaMesh *Mesh, OmegaMeshElement Elem, int NOuter,
-                                  int NInner, const double *Host, double *Dev, void *Stream);
+                                  int NInner, const OmegaReal *Host, OmegaReal *Dev, void *Stream);
 
 /* ---- Tendencies + AuxiliaryState + TimeStepper -------------------------- */
 int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int NTracers,
@@ -192,36 +204,36 @@ int omega_stepper_set_config(OmegaStepper *Stepper, const OmegaTendConfig *Cfg);
 int omega_stepper_aux_arrays(OmegaStepper *Stepper, OmegaAuxArrays *Aux);
 int omega_stepper_tend_arrays(OmegaStepper *Stepper, OmegaTendArrays *Tend);
 /* wind stress input on cells, host order (WindForcingAuxVars.h:14-17) */
-int omega_stepper_set_wind_stress(OmegaStepper *Stepper, const double *ZonalStressCellHost,
-                                  const double *MeridStressCellHost, void *Stream);
+int omega_stepper_set_wind_stress(OmegaStepper *Stepper, const OmegaReal *ZonalStressCellHost,
+                                  const OmegaReal *MeridStressCellHost, void *Stream);
 
 /* AuxiliaryState::computeMomAux / computeAll (src/ocn/AuxiliaryState.cpp:60-185) */
-int omega_aux_compute_mom(OmegaStepper *S, const double *LayerThickCell,
-                          const double *NormalVelEdge, void *Stream);
-int omega_aux_compute_all(OmegaStepper *S, const double *LayerThickCell,
-                          const double *NormalVelEdge, const double *TracerArray,
+int omega_aux_compute_mom(OmegaStepper *S, const OmegaReal *LayerThickCell,
+                          const OmegaReal *NormalVelEdge, void *Stream);
+int omega_aux_compute_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
+                          const OmegaReal *NormalVelEdge, const OmegaReal *TracerArray,
                           void *Stream);
 /* Tendencies::compute*TendenciesOnly (src/ocn/Tendencies.cpp:257-486);
  * NormalVelEdgeRaw is State->NormalVelocity[VelTimeLevel] indexed RAW as the
  * reference does for bottom drag / tracer advection (:322,:445). */
-int omega_tend_thickness_only(OmegaStepper *S, const double *NormalVelEdge, double Time,
+int omega_tend_thickness_only(OmegaStepper *S, const OmegaReal *NormalVelEdge, double Time,
                               void *Stream);
-int omega_tend_velocity_only(OmegaStepper *S, const double *NormalVelEdge,
-                             const double *NormalVelEdgeRaw, double Time, void *Stream);
-int omega_tend_tracer_only(OmegaStepper *S, const double *NormalVelEdgeRaw,
-                           const double *TracerArray, void *Stream);
+int omega_tend_velocity_only(OmegaStepper *S, const OmegaReal *NormalVelEdge,
+                             const OmegaReal *NormalVelEdgeRaw, double Time, void *Stream);
+int omega_tend_tracer_only(OmegaStepper *S, const OmegaReal *NormalVelEdgeRaw,
+                           const OmegaReal *TracerArray, void *Stream);
 /* Tendencies::computeThickness/Velocity/Tracer/AllTendencies (:488-600) */
-int omega_tend_thickness(OmegaStepper *S, const double *LayerThickCell,
-                         const double *NormalVelEdge, double Time, void *Stream);
-int omega_tend_velocity(OmegaStepper *S, const double *LayerThickCell,
-                        const double *NormalVelEdge, const double *NormalVelEdgeRaw,
+int omega_tend_thickness(OmegaStepper *S, const OmegaReal *LayerThickCell,
+                         const OmegaReal *NormalVelEdge, double Time, void *Stream);
+int omega_tend_velocity(OmegaStepper *S, const OmegaReal *LayerThickCell,
+                        const OmegaReal *NormalVelEdge, const OmegaReal *NormalVelEdgeRaw,
                         double Time, void *Stream);
-int omega_tend_tracer(OmegaStepper *S, const double *LayerThickCellRaw,
-                      const double *NormalVelEdgeRaw, const double *TracerArray,
+int omega_tend_tracer(OmegaStepper *S, const OmegaReal *LayerThickCellRaw,
+                      const OmegaReal *NormalVelEdgeRaw, const OmegaReal *TracerArray,
                       void *Stream);
-int omega_tend_all(OmegaStepper *S, const double *LayerThickCell,
-                   const double *NormalVelEdge, const double *NormalVelEdgeRaw,
-                   const double *TracerArray, double Time, void *Stream);
+int omega_tend_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
+                   const OmegaReal *NormalVelEdge, const OmegaReal *NormalVelEdgeRaw,
+                   const OmegaReal *TracerArray, double Time, void *Stream);
 
 /* TimeStepper::doStep (src/timeStepping/RungeKutta4Stepper.cpp:68-137,
  * RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:27-82).
@@ -247,7 +259,7 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
                              int RawTimeLevelCompat, void *Stream);
 /* Arrays to exchange after Phase p (device pointers, element kind, NOuter). */
 int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type,
-                                const OmegaStateArrays *State, int Phase, double **Ptrs,
+                                const OmegaStateArrays *State, int Phase, OmegaReal **Ptrs,
                                 int *Elems, int *NOuter, int *NArrays);
 /* Attach the rank's Halo to the stepper (do_step with a Halo does this itself).  The fused tiled path then
  * (a) skips the halo tiles in the stages whose results the following exchange overwrites (RK4 stage 3, and
@@ -259,7 +271,7 @@ int omega_stepper_attach_halo(OmegaStepper *S, OmegaHalo *Halo);
  * advance both ring indices (src/ocn/OceanState.cpp:348-365). */
 int omega_state_rotate(OmegaStateArrays *State);
 /* ProvisState / ProvisTracers of the RK4 stepper (RungeKutta4Stepper.cpp:43-64) */
-int omega_stepper_provis_arrays(OmegaStepper *Stepper, double **H, double **U, double **Tr);
+int omega_stepper_provis_arrays(OmegaStepper *Stepper, OmegaReal **H, OmegaReal **U, OmegaReal **Tr);
 /* kernels launched by this stepper since creation (bench gpu_launches) */
 long long omega_stepper_launch_count(const OmegaStepper *S);
 /* which kernels the last omega_stepper_step_phase / do_step ran: OMEGA_PATH_* bits (0 = the
@@ -298,10 +310,10 @@ int omega_halo_set_comm(OmegaHalo *Halo, void *NcclComm, int NRanks);
 /* Halo::exchangeFullArrayHalo(Array, Elem) (src/base/Halo.h:768-915): the whole exchange of one
  * array [NOuter][N*Size][NVertLayers] (device order) on Stream: pack kernel, grouped ncclSend /
  * ncclRecv with every neighbour, unpack kernel.  Nothing synchronises the host. */
-int omega_halo_exchange(OmegaHalo *Halo, double *Array, OmegaMeshElement Elem, int NOuter, void *Stream);
+int omega_halo_exchange(OmegaHalo *Halo, OmegaReal *Array, OmegaMeshElement Elem, int NOuter, void *Stream);
 /* One exchange ROUND: up to three arrays (h, u, tracers of one exchange point of the stepper) in ONE
  * pack launch, ONE message per neighbour, ONE unpack launch.  Buffers are owned by the Halo. */
-int omega_halo_exchange_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
+int omega_halo_exchange_round(OmegaHalo *Halo, OmegaReal *const *Ptrs, const int *Elems, const int *NOuter,
                               int NArrays, void *Stream);
 /* The two device halves of a round for callers that own the transport (peer copies, an in-process
  * N-rank emulation): pack_round fills the Halo's send buffer (returned; neighbour n's message is the
@@ -310,18 +322,18 @@ int omega_halo_exchange_round(OmegaHalo *Halo, double *const *Ptrs, const int *E
  * recv_buffer returns the buffer unpack_round scatters from, laid out the same way. */
 int omega_halo_round_counts(const OmegaHalo *Halo, const int *Elems, const int *NOuter, int NArrays,
                             long long *SendCounts, long long *RecvCounts);
-int omega_halo_pack_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
-                          int NArrays, double **SendBuf, void *Stream);
-int omega_halo_recv_buffer(OmegaHalo *Halo, const int *Elems, const int *NOuter, int NArrays, double **RecvBuf);
-int omega_halo_unpack_round(OmegaHalo *Halo, double *const *Ptrs, const int *Elems, const int *NOuter,
+int omega_halo_pack_round(OmegaHalo *Halo, OmegaReal *const *Ptrs, const int *Elems, const int *NOuter,
+                          int NArrays, OmegaReal **SendBuf, void *Stream);
+int omega_halo_recv_buffer(OmegaHalo *Halo, const int *Elems, const int *NOuter, int NArrays, OmegaReal **RecvBuf);
+int omega_halo_unpack_round(OmegaHalo *Halo, OmegaReal *const *Ptrs, const int *Elems, const int *NOuter,
                             int NArrays, void *Stream);
 /* Per-array device halves with caller-owned buffers (Halo.h:304-502 buffer order; counts in doubles). */
 int omega_halo_buffer_counts(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter,
                              int NInner, long long *SendCounts, long long *RecvCounts);
 int omega_halo_pack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
-                    const double *Array, double *SendBuf, void *Stream);
+                    const OmegaReal *Array, OmegaReal *SendBuf, void *Stream);
 int omega_halo_unpack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
-                      const double *RecvBuf, double *Array, void *Stream);
+                      const OmegaReal *RecvBuf, OmegaReal *Array, void *Stream);
 /* Tile classes used for the overlap: tiles with send-list rows, owned tiles, all tiles. */
 int omega_halo_tile_classes(const OmegaHalo *Halo, int *NBoundary, int *NOwned, int *NTiles);
 /* CUDA-event timing of the exchange rounds since the last call (pack .. unpack on the exchange
@@ -336,29 +348,29 @@ int omega_halo_get_profile(OmegaHalo *Halo, double *Ms, long long *Rounds, long 
  * (src/ocn/VertCoord.cpp:648-860): interfaces are [NCellsSize][NVertLayers + 1]; surface pressure, tidal
  * potential, self attraction and loading [NCellsSize]; MovementWeights [NVertLayers]; BottomDepth is the mesh's. */
 int omega_vert_compute_pressure(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
-                                const double *LayerThickness, const double *SurfacePressure,
-                                double *PressureInterface, double *PressureMid, void *Stream);
+                                const OmegaReal *LayerThickness, const OmegaReal *SurfacePressure,
+                                OmegaReal *PressureInterface, OmegaReal *PressureMid, void *Stream);
 int omega_vert_compute_z_height(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
-                                const double *LayerThickness, const double *SpecVol, double *ZInterface,
-                                double *ZMid, void *Stream);
+                                const OmegaReal *LayerThickness, const OmegaReal *SpecVol, OmegaReal *ZInterface,
+                                OmegaReal *ZMid, void *Stream);
 int omega_vert_compute_geopotential(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell,
-                                    const double *ZMid, const double *TidalPotential,
-                                    const double *SelfAttractionLoading, double *GeopotentialMid, void *Stream);
+                                    const OmegaReal *ZMid, const OmegaReal *TidalPotential,
+                                    const OmegaReal *SelfAttractionLoading, OmegaReal *GeopotentialMid, void *Stream);
 int omega_vert_compute_target_thickness(const OmegaMesh *Mesh, const int *MinLayerCell, const int *MaxLayerCell,
-                                        double Rho0, const double *PressureInterface, const double *RefLayerThickness,
-                                        const double *MovementWeights, double *LayerThicknessTarget, void *Stream);
+                                        double Rho0, const OmegaReal *PressureInterface, const OmegaReal *RefLayerThickness,
+                                        const OmegaReal *MovementWeights, OmegaReal *LayerThicknessTarget, void *Stream);
 /* Eos::computeSpecVol / computeSpecVolDisp (src/ocn/Eos.h:29-292).  EosType 0: linear, 1 / (RhoT0S0 + DRhodT CT +
  * DRhodS SA); 1: TEOS-10 75-term polynomial of Roquet et al. (2015), pressure in dbar.  KDisp != 0: specific volume
  * of the parcel displaced to the pressure of layer clamp(k + KDisp) (TEOS-10). */
-int omega_eos_compute_spec_vol(const OmegaMesh *Mesh, int EosType, const double *ConservTemp, const double *AbsSalinity,
-                               const double *Pressure, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
-                               double *SpecVol, void *Stream);
+int omega_eos_compute_spec_vol(const OmegaMesh *Mesh, int EosType, const OmegaReal *ConservTemp, const OmegaReal *AbsSalinity,
+                               const OmegaReal *Pressure, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
+                               OmegaReal *SpecVol, void *Stream);
 /* TriDiagSolver / TriDiagDiffSolver (src/base/TriDiagSolvers.h): NBatch independent systems of NRow <= 1024 rows,
  * arrays [NBatch][NRow] on the device, X holds the right-hand side on entry and the solution on return.
  * General form: DL(k) x(k-1) + D(k) x(k) + DU(k) x(k+1) = X(k).  Diffusion form: D(k) = H(k) + G(k-1) + G(k),
  * DL(k) = -G(k-1), DU(k) = -G(k), solved without ever forming D (stable for abrupt jumps in G). */
-int omega_tridiag_solve(int NBatch, int NRow, const double *DL, const double *D, const double *DU, double *X, void *Stream);
-int omega_tridiag_diffusion_solve(int NBatch, int NRow, const double *G, const double *H, double *X, void *Stream);
+int omega_tridiag_solve(int NBatch, int NRow, const OmegaReal *DL, const OmegaReal *D, const OmegaReal *DU, OmegaReal *X, void *Stream);
+int omega_tridiag_diffusion_solve(int NBatch, int NRow, const OmegaReal *G, const OmegaReal *H, OmegaReal *X, void *Stream);
 
 /* ---- Decomp (src/base/Decomp.cpp) -- host code, no device work ------------------
  * One rank's partition of the GLOBAL mesh in Omega's local numbering, the owner

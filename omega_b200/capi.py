@@ -177,6 +177,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("OMEGA_B200_LIB") or os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200.so")
 
 
+# the single-precision build of the same sources (Real = float; -DOMEGA_SINGLE_PRECISION)
+LIB_PATH_SP = os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200_sp.so")
+
+
 def load_library(path: str = LIB_PATH) -> C.CDLL:
     """Load the CUDA library; raises (never falls back) when it is missing."""
     if not os.path.exists(path):

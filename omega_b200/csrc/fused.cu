@@ -63,21 +63,21 @@ __device__ __forceinline__ void cta_rows(int N, int &r0, int &n) {
 // ---------------------------------------------------------------------------
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double *__restrict__ KE,
-     double *__restrict__ Div, double *__restrict__ RelVort, double *__restrict__ PVv, int XMode, double aKE,
-     double aSSH, double *__restrict__ KEBot) {
+k_fA(DMesh M, const Real *__restrict__ H, const Real *__restrict__ U, Real *__restrict__ KE,
+     Real *__restrict__ Div, Real *__restrict__ RelVort, Real *__restrict__ PVv, int XMode, Real aKE,
+     Real aSSH, Real *__restrict__ KEBot) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      double ke[V] = {0}, dv[V] = {0};
+      Real ke[V] = {0}, dv[V] = {0};
       // six table entries per cell (omega_dev.h: ACell*; edge row = boundary slot and zero
       // coefficients when the cell has fewer edges): all u-row gathers in flight together
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
          const int e      = M.ACellEdge[c * 6 + j];
-         const double2 cf = M.ACellCf[c * 6 + j];
-         double u[V];
+         const Real2 cf = M.ACellCf[c * 6 + j];
+         Real u[V];
          ldv<V>(u, U + (size_t)e * M.K + k);
 #pragma unroll
          for (int q = 0; q < V; ++q) {
@@ -89,9 +89,9 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
       if (XMode) {
          // tiled edge pass: KE and SSH gradients share (X(c1)-X(c0))/dc, X = aKE*KE + aSSH*g*(h - b)
          // (KEGradOnEdge, SSHGradOnEdge, TendencyTerms.h:127-173; LayerThicknessAuxVars.h:63-82)
-         double h[V];
+         Real h[V];
          ldv<V>(h, H + (size_t)c * M.K + k);
-         const double b = M.BottomDepth[c];
+         const Real b = M.BottomDepth[c];
 #pragma unroll
          for (int q = 0; q < V; ++q) ke[q] = aKE * ke[q] + aSSH * (9.80665 * (h[q] - b));
       }
@@ -100,12 +100,12 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      double hv[V] = {0}, rv[V] = {0};
+      Real hv[V] = {0}, rv[V] = {0};
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
          const int2 ix    = M.AVertIdx[v * 3 + j];
-         const double2 cf = M.AVertCf[v * 3 + j];
-         double h[V], u[V];
+         const Real2 cf = M.AVertCf[v * 3 + j];
+         Real h[V], u[V];
          ldv<V>(h, H + (size_t)ix.x * M.K + k);
          ldv<V>(u, U + (size_t)ix.y * M.K + k);
 #pragma unroll
@@ -114,11 +114,11 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
             rv[q] += cf.y * u[q];
          }
       }
-      const double f = M.FVertex[v];
-      double pv[V];
+      const Real f = M.FVertex[v];
+      Real pv[V];
 #pragma unroll
       for (int q = 0; q < V; ++q) {
-         const double inv = 1.0 / hv[q];
+         const Real inv = 1.0 / hv[q];
          pv[q]            = rv[q] * inv + f * inv;
       }
       stv<V>(RelVort + (size_t)v * M.K + k, rv);
@@ -135,20 +135,20 @@ k_fA(DMesh M, const double *__restrict__ H, const double *__restrict__ U, double
 // ---------------------------------------------------------------------------
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort,
-     double *__restrict__ Del2Div, double *__restrict__ Del2RelVort, int YMode, double Nu2, double Nu4Div,
-     double Nu4) {
+k_fB(DMesh M, const Real *__restrict__ Div, const Real *__restrict__ RelVort,
+     Real *__restrict__ Del2Div, Real *__restrict__ Del2RelVort, int YMode, Real Nu2, Real Nu4Div,
+     Real Nu4) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      double ds[V], t[V] = {0};
+      Real ds[V], t[V] = {0};
       ldv<V>(ds, Div + (size_t)c * M.K + k);
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
          const int4 ix    = M.B2CellIdx[c * 6 + j];
-         const double2 cf = M.B2CellCf[c * 6 + j];
-         double dn[V], z0[V], z1[V];
+         const Real2 cf = M.B2CellCf[c * 6 + j];
+         Real dn[V], z0[V], z1[V];
          ldv<V>(dn, Div + (size_t)ix.x * M.K + k);
          ldv<V>(z0, RelVort + (size_t)ix.y * M.K + k);
          ldv<V>(z1, RelVort + (size_t)ix.z * M.K + k);
@@ -166,13 +166,13 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
    }
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
-      double zs[V], t[V] = {0};
+      Real zs[V], t[V] = {0};
       ldv<V>(zs, RelVort + (size_t)v * M.K + k);
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
          const int4 ix    = M.B2VertIdx[v * 3 + j];
-         const double2 cf = M.B2VertCf[v * 3 + j];
-         double d0[V], d1[V], zo[V];
+         const Real2 cf = M.B2VertCf[v * 3 + j];
+         Real d0[V], d1[V], zo[V];
          ldv<V>(d0, Div + (size_t)ix.x * M.K + k);
          ldv<V>(d1, Div + (size_t)ix.y * M.K + k);
          ldv<V>(zo, RelVort + (size_t)ix.z * M.K + k);
@@ -192,14 +192,14 @@ k_fB(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort
 // edge pass then differences for KE + SSH gradient, Del2 and Del4 divergence parts together.
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVort, double *__restrict__ Del2Div,
-      double *__restrict__ Del2RelVort, int YMode, double Nu2, double Nu4Div, double Nu4, const double *__restrict__ X) {
+k_fB3(DMesh M, const Real *__restrict__ Div, const Real *__restrict__ RelVort, Real *__restrict__ Del2Div,
+      Real *__restrict__ Del2RelVort, int YMode, Real Nu2, Real Nu4Div, Real Nu4, const Real *__restrict__ X) {
    const int KV = M.K / V;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
       int ix[12];
-      double cf[12];
+      Real cf[12];
 #pragma unroll
       for (int q = 0; q < 3; ++q) {
          const int4 t4 = M.B3CellIdx[c * 3 + q];
@@ -207,10 +207,10 @@ k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVor
       }
 #pragma unroll
       for (int q = 0; q < 6; ++q) {
-         const double2 t2 = M.B3CellCf[c * 6 + q];
+         const Real2 t2 = M.B3CellCf[c * 6 + q];
          cf[2 * q] = t2.x; cf[2 * q + 1] = t2.y;
       }
-      double ds[V], xs[V] = {0}, t[V] = {0}, g[12][V];
+      Real ds[V], xs[V] = {0}, t[V] = {0}, g[12][V];
       ldv<V>(ds, Div + (size_t)c * M.K + k);
       if (X) ldv<V>(xs, X + (size_t)c * M.K + k);
 #pragma unroll
@@ -234,7 +234,7 @@ k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVor
    cta_rows(M.NVerticesAll, r0, n);
    OMEGA_FOR_ROWS(v, k, r0, n, KV, V) {
       int ix[8];
-      double cf[8];
+      Real cf[8];
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
          const int4 t4 = M.B3VertIdx[v * 2 + q];
@@ -242,10 +242,10 @@ k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVor
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-         const double2 t2 = M.B3VertCf[v * 4 + q];
+         const Real2 t2 = M.B3VertCf[v * 4 + q];
          cf[2 * q] = t2.x; cf[2 * q + 1] = t2.y;
       }
-      double zs[V], t[V] = {0}, g[7][V];
+      Real zs[V], t[V] = {0}, g[7][V];
       ldv<V>(zs, RelVort + (size_t)v * M.K + k);
 #pragma unroll
       for (int j = 0; j < 4; ++j) ldv<V>(g[j], Div + (size_t)ix[j] * M.K + k);
@@ -274,20 +274,20 @@ k_fB3(DMesh M, const double *__restrict__ Div, const double *__restrict__ RelVor
 // ---------------------------------------------------------------------------
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_fT2(DMesh M, const double *__restrict__ H, const double *__restrict__ Tr, int NTracers,
-      double *__restrict__ Del2Tr) {
+k_fT2(DMesh M, const Real *__restrict__ H, const Real *__restrict__ Tr, int NTracers,
+      Real *__restrict__ Del2Tr) {
    const int KV = M.K / V;
    const size_t CS = (size_t)M.NCellsSize * M.K;
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const Real InvA = 1.0 / M.AreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       const size_t o    = (size_t)c * M.K + k;
-      double hs[V];
+      Real hs[V];
       ldv<V>(hs, H + o);
       // per-edge coefficient  mask*sign*(dv/dc)*mean  and neighbour offset
-      double cf[6][V];
+      Real cf[6][V];
       size_t on[6];
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
@@ -296,23 +296,23 @@ k_fT2(DMesh M, const double *__restrict__ H, const double *__restrict__ Tr, int 
             const int2 cc = M.CellsOnEdge[e];
             const int nb  = cc.x == c ? cc.y : cc.x;
             on[j]         = (size_t)nb * M.K + k;
-            const double g = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * (M.DvEdge[e] / M.DcEdge[e]);
-            double h0[V], h1[V];
+            const Real g = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * (M.DvEdge[e] / M.DcEdge[e]);
+            Real h0[V], h1[V];
             ldv<V>(h0, H + (size_t)cc.x * M.K + k);
             ldv<V>(h1, H + (size_t)cc.y * M.K + k);
-            const double sgn = cc.x == c ? -1.0 : 1.0; // phi(c1)-phi(c0) = sgn*(phi(self)-phi(nbr))
+            const Real sgn = cc.x == c ? -1.0 : 1.0; // phi(c1)-phi(c0) = sgn*(phi(self)-phi(nbr))
 #pragma unroll
             for (int q = 0; q < V; ++q) cf[j][q] = g * (0.5 * (h0[q] + h1[q])) * sgn;
          }
       }
       for (int l = 0; l < NTracers; ++l) {
-         const double *T = Tr + l * CS;
-         double ts[V], t[V] = {0};
+         const Real *T = Tr + l * CS;
+         Real ts[V], t[V] = {0};
          ldv<V>(ts, T + o);
 #pragma unroll
          for (int j = 0; j < 6; ++j) {
             if (j < ne) {
-               double tn[V];
+               Real tn[V];
                ldv<V>(tn, T + on[j]);
 #pragma unroll
                for (int q = 0; q < V; ++q) t[q] -= cf[j][q] * (ts[q] - tn[q]);
@@ -345,17 +345,17 @@ k_fC(DMesh M, CellArgs P) {
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const Real InvA = 1.0 / M.AreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       const size_t o    = (size_t)c * M.K + k;
-      double hs[V];
+      Real hs[V];
       ldv<V>(hs, P.Hs + o);
-      double hn[kME][V], w[kME][V]; // neighbour thickness; mask*dv*sign*u_tr/A
-      double cd[kME], ch[kME];      // -k2/A*mask*sign*scale2*dv/dc*sgn ; +k4/A*mask*sign*scale4*dv/dc*sgn
+      Real hn[kME][V], w[kME][V]; // neighbour thickness; mask*dv*sign*u_tr/A
+      Real cd[kME], ch[kME];      // -k2/A*mask*sign*scale2*dv/dc*sgn ; +k4/A*mask*sign*scale4*dv/dc*sgn
       int nb[kME];
       bool self0[kME];
-      double su[UPW ? kME : 1][V]; // sign of the stage velocity (upwind options only)
-      double hT[V] = {0};
+      Real su[UPW ? kME : 1][V]; // sign of the stage velocity (upwind options only)
+      Real hT[V] = {0};
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
          if (j < ne) {
@@ -363,13 +363,13 @@ k_fC(DMesh M, CellArgs P) {
             const int2 cc     = M.CellsOnEdge[e];
             self0[j]          = cc.x == c;
             nb[j]             = self0[j] ? cc.y : cc.x;
-            const double sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
-            const double mask = M.EdgeMask[e], dve = M.DvEdge[e];
-            const double rdc  = dve / M.DcEdge[e];
-            const double sgn  = self0[j] ? -1.0 : 1.0;
+            const Real sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
+            const Real mask = M.EdgeMask[e], dve = M.DvEdge[e];
+            const Real rdc  = dve / M.DcEdge[e];
+            const Real sgn  = self0[j] ? -1.0 : 1.0;
             cd[j] = -(P.EddyDiff2 * InvA) * (mask * sg * (M.MeshScalingDel2[e] * rdc)) * sgn;
             ch[j] = (P.EddyDiff4 * InvA) * (mask * sg * (M.MeshScalingDel4[e] * rdc)) * sgn;
-            double us[V], ut[V];
+            Real us[V], ut[V];
             ldv<V>(hn[j], P.Hs + (size_t)nb[j] * M.K + k);
             ldv<V>(us, P.Us + (size_t)e * M.K + k);
             if (P.UTr == P.Us) {
@@ -378,15 +378,15 @@ k_fC(DMesh M, CellArgs P) {
             } else {
                ldv<V>(ut, P.UTr + (size_t)e * M.K + k);
             }
-            const double cf = dve * sg;
+            const Real cf = dve * sg;
 #pragma unroll
             for (int q = 0; q < V; ++q) {
                // FluxLayerThickEdge: centred, or upwind on the sign of u (h0 is cell 0 of the edge)
-               double flux;
+               Real flux;
                if (UPW) su[j][q] = us[q] > 0 ? 1.0 : (us[q] < 0 ? -1.0 : 0.0);
                if (!UPW || !P.FluxUpwind) flux = 0.5 * (hs[q] + hn[j][q]);
                else {
-                  const double h0 = self0[j] ? hs[q] : hn[j][q], h1 = self0[j] ? hn[j][q] : hs[q];
+                  const Real h0 = self0[j] ? hs[q] : hn[j][q], h1 = self0[j] ? hn[j][q] : hs[q];
                   flux = us[q] > 0 ? h0 : (us[q] < 0 ? h1 : fmax(h0, h1));
                }
                hT[q] += cf * flux * us[q] * InvA; // Tend -= (-sum) (TendencyTerms.h:48-56)
@@ -399,14 +399,14 @@ k_fC(DMesh M, CellArgs P) {
          for (int q = 0; q < V; ++q) hT[q] = 0.0;
       }
       if (P.MS.Enabled) {
-         const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
-         const double src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
+         const Real Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
+         const Real src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
                                          P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * cos(2.0 * Phase));
 #pragma unroll
          for (int q = 0; q < V; ++q) hT[q] += src;
       }
       // ---- thickness updates (updateThicknessByTend) ----
-      double hcur[V], hnext_old[V], hnext[V], hprov[V];
+      Real hcur[V], hnext_old[V], hnext[V], hprov[V];
       if (P.First && P.Hcur == P.Hs) {
 #pragma unroll
          for (int q = 0; q < V; ++q) hcur[q] = hs[q];
@@ -422,7 +422,7 @@ k_fC(DMesh M, CellArgs P) {
       stv<V>(P.Hnext + o, hnext);
       if (!P.Last) stv<V>(P.Hprov + o, hprov);
       // ---- tracers ----
-      double hw[V], h2[V], hfin[V];
+      Real hw[V], h2[V], hfin[V];
 #pragma unroll
       for (int q = 0; q < V; ++q) {
          hw[q]   = P.WSel ? hnext_old[q] : hcur[q];
@@ -430,27 +430,27 @@ k_fC(DMesh M, CellArgs P) {
          hfin[q] = P.FinSel ? hcur[q] : hnext[q];
       }
       for (int l = 0; l < P.NTracers; ++l) {
-         const double *T  = P.Trs + l * CS;
-         const double *D2 = P.Del2Tr + l * CS;
-         double ts[V], d2s[V], tend[V] = {0};
+         const Real *T  = P.Trs + l * CS;
+         const Real *D2 = P.Del2Tr + l * CS;
+         Real ts[V], d2s[V], tend[V] = {0};
          ldv<V>(ts, T + o);
          if (P.HypOn) ldv<V>(d2s, D2 + o);
 #pragma unroll
          for (int j = 0; j < kME; ++j) {
             if (j < ne) {
                const size_t on = (size_t)nb[j] * M.K + k;
-               double tn[V];
+               Real tn[V];
                ldv<V>(tn, T + on);
 #pragma unroll
                for (int q = 0; q < V; ++q) {
                   if (P.AdvOn) {
-                     const double a = hs[q] * ts[q], b = hn[j][q] * tn[q];
-                     double htr;
+                     const Real a = hs[q] * ts[q], b = hn[j][q] * tn[q];
+                     Real htr;
                      if (!UPW || !P.TrUpwind) htr = 0.5 * (a + b);
                      else {
                         // TracerAuxVars upwinds on the velocity of the aux call (the stage velocity)
-                        const double h0t = self0[j] ? a : b, h1t = self0[j] ? b : a;
-                        const double sgnu = su[UPW ? j : 0][q];
+                        const Real h0t = self0[j] ? a : b, h1t = self0[j] ? b : a;
+                        const Real sgnu = su[UPW ? j : 0][q];
                         htr = sgnu > 0 ? h0t : (sgnu < 0 ? h1t : fmax(h0t, h1t));
                      }
                      tend[q] += htr * w[j][q];
@@ -458,7 +458,7 @@ k_fC(DMesh M, CellArgs P) {
                   if (P.DiffOn) tend[q] += cd[j] * (0.5 * (hs[q] + hn[j][q])) * (ts[q] - tn[q]);
                }
                if (P.HypOn) {
-                  double d2n[V];
+                  Real d2n[V];
                   ldv<V>(d2n, D2 + on);
 #pragma unroll
                   for (int q = 0; q < V; ++q) tend[q] += ch[j] * (d2s[q] - d2n[q]);
@@ -466,7 +466,7 @@ k_fC(DMesh M, CellArgs P) {
             }
          }
          // epilogue: weight/accumulate/provisional/finalise (TimeStepper.cpp:446-524)
-         double tcur[V], acc[V], out[V];
+         Real tcur[V], acc[V], out[V];
          if (P.First && P.TrCur == P.Trs) {
 #pragma unroll
             for (int q = 0; q < V; ++q) tcur[q] = ts[q];
@@ -476,7 +476,7 @@ k_fC(DMesh M, CellArgs P) {
          if (!P.First) ldp<V>(acc, P.TrNext + l * CS + o);
 #pragma unroll
          for (int q = 0; q < V; ++q) {
-            const double base = P.First ? tcur[q] * hw[q] : acc[q];
+            const Real base = P.First ? tcur[q] * hw[q] : acc[q];
             out[q]            = base + P.B * tend[q];
             if (P.Last) out[q] = out[q] / hfin[q];
          }
@@ -514,14 +514,14 @@ k_fC_center(DMesh M, CellArgs P) {
    int r0, n;
    cta_rows(M.NCellsAll, r0, n);
    OMEGA_FOR_ROWS(c, k, r0, n, KV, V) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const Real InvA = 1.0 / M.AreaCell[c];
       const int ne      = M.NEdgesOnCell[c];
       const size_t o    = (size_t)c * M.K + k;
-      double hs[V];
+      Real hs[V];
       ldv<V>(hs, P.Hs + o);
-      double E[kME][V], ch[kME], S0[V] = {0}, SH = 0.0, hT[V] = {0};
+      Real E[kME][V], ch[kME], S0[V] = {0}, SH = 0.0, hT[V] = {0};
       int nb[kME];
-      const double k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = P.HypOn ? P.EddyDiff4 * InvA : 0.0;
+      const Real k2 = P.DiffOn ? P.EddyDiff2 * InvA : 0.0, k4 = P.HypOn ? P.EddyDiff4 * InvA : 0.0;
 #pragma unroll
       for (int j = 0; j < kME; ++j) {
          if (j < ne) {
@@ -529,14 +529,14 @@ k_fC_center(DMesh M, CellArgs P) {
             const int2 cc     = M.CellsOnEdge[e];
             const bool self0  = cc.x == c;
             nb[j]             = self0 ? cc.y : cc.x;
-            const double sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
-            const double mask = M.EdgeMask[e], dve = M.DvEdge[e];
-            const double rdc  = dve / M.DcEdge[e];
-            const double sgn  = self0 ? -1.0 : 1.0;
-            const double cd   = -k2 * (mask * sg * (M.MeshScalingDel2[e] * rdc)) * sgn;
+            const Real sg   = M.EdgeSignOnCell[c * M.MaxEdges + j];
+            const Real mask = M.EdgeMask[e], dve = M.DvEdge[e];
+            const Real rdc  = dve / M.DcEdge[e];
+            const Real sgn  = self0 ? -1.0 : 1.0;
+            const Real cd   = -k2 * (mask * sg * (M.MeshScalingDel2[e] * rdc)) * sgn;
             ch[j]             = k4 * (mask * sg * (M.MeshScalingDel4[e] * rdc)) * sgn;
             SH += ch[j];
-            double hn[V], us[V], ut[V];
+            Real hn[V], us[V], ut[V];
             ldv<V>(hn, P.Hs + (size_t)nb[j] * M.K + k);
             ldv<V>(us, P.Us + (size_t)e * M.K + k);
             if (P.UTr == P.Us) {
@@ -545,14 +545,14 @@ k_fC_center(DMesh M, CellArgs P) {
             } else {
                ldv<V>(ut, P.UTr + (size_t)e * M.K + k);
             }
-            const double cf = dve * sg;
-            const double wa = P.AdvOn ? mask * dve * sg : 0.0;
+            const Real cf = dve * sg;
+            const Real wa = P.AdvOn ? mask * dve * sg : 0.0;
 #pragma unroll
             for (int q = 0; q < V; ++q) {
-               const double mean = 0.5 * (hs[q] + hn[q]);
+               const Real mean = 0.5 * (hs[q] + hn[q]);
                hT[q] += cf * mean * us[q] * InvA;
-               const double w = wa * ut[q] * InvA;
-               const double D = cd * mean;
+               const Real w = wa * ut[q] * InvA;
+               const Real D = cd * mean;
                E[j][q]        = 0.5 * hn[q] * w - D;
                S0[q] += 0.5 * hs[q] * w + D;
             }
@@ -563,13 +563,13 @@ k_fC_center(DMesh M, CellArgs P) {
          for (int q = 0; q < V; ++q) hT[q] = 0.0;
       }
       if (P.MS.Enabled) {
-         const double Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
-         const double src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
+         const Real Phase = P.MS.Kx * M.XCell[c] + P.MS.Ky * M.YCell[c] - P.MS.AngFreq * P.MS.Time;
+         const Real src   = P.MS.Eta0 * (-P.MS.H0 * (P.MS.Kx + P.MS.Ky) * sin(Phase) - P.MS.AngFreq * cos(Phase) +
                                          P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * cos(2.0 * Phase));
 #pragma unroll
          for (int q = 0; q < V; ++q) hT[q] += src;
       }
-      double hcur[V], hnext_old[V], hnext[V], hprov[V];
+      Real hcur[V], hnext_old[V], hnext[V], hprov[V];
       if (P.First && P.Hcur == P.Hs) {
 #pragma unroll
          for (int q = 0; q < V; ++q) hcur[q] = hs[q];
@@ -585,17 +585,17 @@ k_fC_center(DMesh M, CellArgs P) {
       stv<V>(P.Hnext + o, hnext);
       if (!P.Last) stv<V>(P.Hprov + o, hprov);
       // hx: stage 0 -> weight thickness; last stage -> final thickness; else unused
-      double hx[V], h2[V];
+      Real hx[V], h2[V];
 #pragma unroll
       for (int q = 0; q < V; ++q) {
          hx[q] = P.First ? (P.WSel ? hnext_old[q] : hcur[q]) : (P.FinSel ? hcur[q] : hnext[q]);
          h2[q] = P.H2Sel == 2 ? hprov[q] : (P.H2Sel ? hnext[q] : hcur[q]);
       }
       for (int l = 0; l < P.NTracers; ++l) {
-         const double *T  = P.Trs + l * CS;
-         const double *D2 = P.Del2Tr + l * CS;
+         const Real *T  = P.Trs + l * CS;
+         const Real *D2 = P.Del2Tr + l * CS;
          if (P.Prefetch && l + 1 < P.NTracers) {
-            const double *Tn = T + CS, *Dn = D2 + CS;
+            const Real *Tn = T + CS, *Dn = D2 + CS;
             prefetch_row(Tn + o, P.Prefetch);
             if (P.HypOn) prefetch_row(Dn + o, P.Prefetch);
 #pragma unroll
@@ -608,7 +608,7 @@ k_fC_center(DMesh M, CellArgs P) {
             if (!(P.First && P.TrCur == P.Trs) && (P.First || !P.Last)) prefetch_row(P.TrCur + (l + 1) * CS + o, P.Prefetch);
             if (!P.First) prefetch_row(P.TrNext + (l + 1) * CS + o, P.Prefetch);
          }
-         double ts[V], d2s[V], tend[V];
+         Real ts[V], d2s[V], tend[V];
          ldv<V>(ts, T + o);
          if (P.HypOn) ldv<V>(d2s, D2 + o);
 #pragma unroll
@@ -617,19 +617,19 @@ k_fC_center(DMesh M, CellArgs P) {
          for (int j = 0; j < kME; ++j) {
             if (j < ne) {
                const size_t on = (size_t)nb[j] * M.K + k;
-               double tn[V];
+               Real tn[V];
                ldv<V>(tn, T + on);
 #pragma unroll
                for (int q = 0; q < V; ++q) tend[q] += E[j][q] * tn[q];
                if (P.HypOn) {
-                  double d2n[V];
+                  Real d2n[V];
                   ldv<V>(d2n, D2 + on);
 #pragma unroll
                   for (int q = 0; q < V; ++q) tend[q] -= ch[j] * d2n[q];
                }
             }
          }
-         double tcur[V], acc[V], out[V];
+         Real tcur[V], acc[V], out[V];
          if (P.First && P.TrCur == P.Trs) {
 #pragma unroll
             for (int q = 0; q < V; ++q) tcur[q] = ts[q];
@@ -639,7 +639,7 @@ k_fC_center(DMesh M, CellArgs P) {
          if (!P.First) ldp<V>(acc, P.TrNext + l * CS + o);
 #pragma unroll
          for (int q = 0; q < V; ++q) {
-            const double base = P.First ? tcur[q] * hx[q] : acc[q];
+            const Real base = P.First ? tcur[q] * hx[q] : acc[q];
             out[q]            = base + P.B * tend[q];
             if (P.Last) out[q] = out[q] / hx[q];
          }
@@ -662,10 +662,10 @@ k_fC_center(DMesh M, CellArgs P) {
 // updateVelocityByTend (TimeStepper.cpp:407-430) as the epilogue.
 // ---------------------------------------------------------------------------
 
-template <int V> __device__ __forceinline__ void flux_edge(const DMesh &M, int e, int k, const double *H,
-                                                           const double (&u)[V], int Upwind, double (&flux)[V]) {
+template <int V> __device__ __forceinline__ void flux_edge(const DMesh &M, int e, int k, const Real *H,
+                                                           const Real (&u)[V], int Upwind, Real (&flux)[V]) {
    const int2 cc = M.CellsOnEdge[e];
-   double h0[V], h1[V];
+   Real h0[V], h1[V];
    ldv<V>(h0, H + (size_t)cc.x * M.K + k);
    ldv<V>(h1, H + (size_t)cc.y * M.K + k);
 #pragma unroll
@@ -675,10 +675,10 @@ template <int V> __device__ __forceinline__ void flux_edge(const DMesh &M, int e
    }
 }
 
-template <int V> __device__ __forceinline__ void pv_edge(const DMesh &M, int e, int k, const double *PVv,
-                                                         double (&pv)[V]) {
+template <int V> __device__ __forceinline__ void pv_edge(const DMesh &M, int e, int k, const Real *PVv,
+                                                         Real (&pv)[V]) {
    const int2 vv = M.VerticesOnEdge[e];
-   double a[V], b[V];
+   Real a[V], b[V];
    ldv<V>(a, PVv + (size_t)vv.x * M.K + k);
    ldv<V>(b, PVv + (size_t)vv.y * M.K + k);
 #pragma unroll
@@ -694,22 +694,22 @@ k_fE(DMesh M, EdgeArgs P) {
    cta_rows(M.NEdgesAll, r0, n);
    OMEGA_FOR_ROWS(e, k, r0, n, KV, V) {
       const size_t o    = (size_t)e * M.K + k;
-      const double mask = M.EdgeMask[e];
+      const Real mask = M.EdgeMask[e];
       const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
-      const double InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
-      double tend[V] = {0};
-      double us[V], h0[V], h1[V];
+      const Real InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
+      Real tend[V] = {0};
+      Real us[V], h0[V], h1[V];
       ldv<V>(us, P.Us + o);
       ldv<V>(h0, P.Hs + (size_t)cc.x * M.K + k);
       ldv<V>(h1, P.Hs + (size_t)cc.y * M.K + k);
       if (G.PVTendencyEnable) {
-         double qe[V], acc[V] = {0};
+         Real qe[V], acc[V] = {0};
          pv_edge<V>(M, e, k, P.PVv, qe);
          const int ne = M.NEdgesOnEdge[e];
          for (int j = 0; j < ne; ++j) {
             const int je   = M.EdgesOnEdge[e * M.MaxEdges2 + j];
-            const double w = M.WeightsOnEdge[e * M.MaxEdges2 + j];
-            double uj[V], fl[V], qj[V];
+            const Real w = M.WeightsOnEdge[e * M.MaxEdges2 + j];
+            Real uj[V], fl[V], qj[V];
             ldv<V>(uj, P.Us + (size_t)je * M.K + k);
             flux_edge<V>(M, je, k, P.Hs, uj, G.FluxThicknessType, fl);
             pv_edge<V>(M, je, k, P.PVv, qj);
@@ -720,7 +720,7 @@ k_fE(DMesh M, EdgeArgs P) {
          for (int q = 0; q < V; ++q) tend[q] += mask * acc[q];
       }
       if (G.KETendencyEnable || G.BottomDragTendencyEnable) {
-         double a0[V], a1[V];
+         Real a0[V], a1[V];
          ldv<V>(a0, P.KE + (size_t)cc.x * M.K + k);
          ldv<V>(a1, P.KE + (size_t)cc.y * M.K + k);
          if (G.KETendencyEnable) {
@@ -732,66 +732,66 @@ k_fE(DMesh M, EdgeArgs P) {
             const int KBot = M.K - 1;
             if (KBot >= k && KBot < k + V) {
                const int q           = KBot - k;
-               const double VelNorm  = sqrt(a0[q] + a1[q]);
-               const double InvThick = 1.0 / (0.5 * (h0[q] + h1[q]));
+               const Real VelNorm  = sqrt(a0[q] + a1[q]);
+               const Real InvThick = 1.0 / (0.5 * (h0[q] + h1[q]));
                tend[q] -= mask * G.BottomDragCoeff * VelNorm * InvThick * __ldg(P.URaw + (size_t)e * M.K + KBot);
             }
          }
       }
       if (G.SSHTendencyEnable) {
-         const double Grav = 9.80665, b0 = M.BottomDepth[cc.x], b1 = M.BottomDepth[cc.y];
+         const Real Grav = 9.80665, b0 = M.BottomDepth[cc.x], b1 = M.BottomDepth[cc.y];
 #pragma unroll
          for (int q = 0; q < V; ++q) tend[q] -= mask * Grav * ((h1[q] - b1) - (h0[q] - b0)) * InvDc;
       }
       if (G.VelDiffTendencyEnable) {
-         double d0[V], d1[V], q0[V], q1[V];
+         Real d0[V], d1[V], q0[V], q1[V];
          ldv<V>(d0, P.Div + (size_t)cc.x * M.K + k);
          ldv<V>(d1, P.Div + (size_t)cc.y * M.K + k);
          ldv<V>(q0, P.RelVort + (size_t)vv.x * M.K + k);
          ldv<V>(q1, P.RelVort + (size_t)vv.y * M.K + k);
-         const double cf = mask * G.ViscDel2 * M.MeshScalingDel2[e];
+         const Real cf = mask * G.ViscDel2 * M.MeshScalingDel2[e];
 #pragma unroll
          for (int q = 0; q < V; ++q) tend[q] += cf * ((d1[q] - d0[q]) * InvDc - (q1[q] - q0[q]) * InvDv);
       }
       if (G.VelHyperDiffTendencyEnable) {
-         double d0[V], d1[V], q0[V], q1[V];
+         Real d0[V], d1[V], q0[V], q1[V];
          ldv<V>(d0, P.Del2Div + (size_t)cc.x * M.K + k);
          ldv<V>(d1, P.Del2Div + (size_t)cc.y * M.K + k);
          ldv<V>(q0, P.Del2RelVort + (size_t)vv.x * M.K + k);
          ldv<V>(q1, P.Del2RelVort + (size_t)vv.y * M.K + k);
-         const double cf = mask * G.ViscDel4 * M.MeshScalingDel4[e];
+         const Real cf = mask * G.ViscDel4 * M.MeshScalingDel4[e];
 #pragma unroll
          for (int q = 0; q < V; ++q)
             tend[q] -= cf * (G.DivFactor * (d1[q] - d0[q]) * InvDc - (q1[q] - q0[q]) * InvDv);
       }
       if (G.WindForcingTendencyEnable && k == 0) {
-         const double InvThick = 1.0 / (0.5 * (h0[0] + h1[0]));
+         const Real InvThick = 1.0 / (0.5 * (h0[0] + h1[0]));
          tend[0] += mask * InvThick * P.NormalStress[e] / G.Density0;
       }
       if (P.MS.Enabled) {
-         const double Grav  = 9.80665;
-         const double Phase = P.MS.Kx * M.XEdge[e] + P.MS.Ky * M.YEdge[e] - P.MS.AngFreq * P.MS.Time;
-         const double Src0  = P.MS.AngFreq * sin(Phase) - 0.5 * P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * sin(2.0 * Phase);
-         const double f     = M.FEdge[e];
-         double Uu = P.MS.Eta0 * ((-f + Grav * P.MS.Kx) * cos(Phase) + Src0);
-         double Vv = P.MS.Eta0 * ((f + Grav * P.MS.Ky) * cos(Phase) + Src0);
-         const double Kx2 = P.MS.Kx * P.MS.Kx, Ky2 = P.MS.Ky * P.MS.Ky;
+         const Real Grav  = 9.80665;
+         const Real Phase = P.MS.Kx * M.XEdge[e] + P.MS.Ky * M.YEdge[e] - P.MS.AngFreq * P.MS.Time;
+         const Real Src0  = P.MS.AngFreq * sin(Phase) - 0.5 * P.MS.Eta0 * (P.MS.Kx + P.MS.Ky) * sin(2.0 * Phase);
+         const Real f     = M.FEdge[e];
+         Real Uu = P.MS.Eta0 * ((-f + Grav * P.MS.Kx) * cos(Phase) + Src0);
+         Real Vv = P.MS.Eta0 * ((f + Grav * P.MS.Ky) * cos(Phase) + Src0);
+         const Real Kx2 = P.MS.Kx * P.MS.Kx, Ky2 = P.MS.Ky * P.MS.Ky;
          if (G.VelDiffTendencyEnable) {
             Uu += G.ViscDel2 * P.MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
             Vv += G.ViscDel2 * P.MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
          }
          if (G.VelHyperDiffTendencyEnable) {
-            const double Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
+            const Real Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
             Uu -= G.ViscDel4 * P.MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
             Vv -= G.ViscDel4 * P.MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
          }
-         const double a   = M.AngleEdge[e];
-         const double src = cos(a) * Uu + sin(a) * Vv;
+         const Real a   = M.AngleEdge[e];
+         const Real src = cos(a) * Uu + sin(a) * Vv;
 #pragma unroll
          for (int q = 0; q < V; ++q) tend[q] += src;
       }
       // epilogue: updateVelocityByTend for the next-level and provisional states
-      double ucur[V], base[V], out[V];
+      Real ucur[V], base[V], out[V];
       if (P.First && P.Ucur == P.Us) {
 #pragma unroll
          for (int q = 0; q < V; ++q) ucur[q] = us[q];
@@ -823,56 +823,56 @@ k_fE(DMesh M, EdgeArgs P) {
 // reference's term order by rounding only).
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock)
-k_ms_sources(DMesh M, ManufacturedParams MS, double TimeEdge, int Del2On, double Visc2, int Del4On, double Visc4,
-             double *__restrict__ SrcH, double *__restrict__ SrcU) {
+k_ms_sources(DMesh M, ManufacturedParams MS, Real TimeEdge, int Del2On, Real Visc2, int Del4On, Real Visc4,
+             Real *__restrict__ SrcH, Real *__restrict__ SrcU) {
    const int i = blockIdx.x * blockDim.x + threadIdx.x;
    if (i < M.NCellsAll) {
-      const double Phase = MS.Kx * M.XCell[i] + MS.Ky * M.YCell[i] - MS.AngFreq * MS.Time;
+      const Real Phase = MS.Kx * M.XCell[i] + MS.Ky * M.YCell[i] - MS.AngFreq * MS.Time;
       SrcH[i] = MS.Eta0 * (-MS.H0 * (MS.Kx + MS.Ky) * sin(Phase) - MS.AngFreq * cos(Phase) +
                            MS.Eta0 * (MS.Kx + MS.Ky) * cos(2.0 * Phase));
    }
    if (i < M.NEdgesAll) {
       const int e = i;
-      const double Grav  = 9.80665;
-      const double Phase = MS.Kx * M.XEdge[e] + MS.Ky * M.YEdge[e] - MS.AngFreq * TimeEdge;
-      const double Src0  = MS.AngFreq * sin(Phase) - 0.5 * MS.Eta0 * (MS.Kx + MS.Ky) * sin(2.0 * Phase);
-      const double f     = M.FEdge[e];
-      double Uu = MS.Eta0 * ((-f + Grav * MS.Kx) * cos(Phase) + Src0);
-      double Vv = MS.Eta0 * ((f + Grav * MS.Ky) * cos(Phase) + Src0);
-      const double Kx2 = MS.Kx * MS.Kx, Ky2 = MS.Ky * MS.Ky;
+      const Real Grav  = 9.80665;
+      const Real Phase = MS.Kx * M.XEdge[e] + MS.Ky * M.YEdge[e] - MS.AngFreq * TimeEdge;
+      const Real Src0  = MS.AngFreq * sin(Phase) - 0.5 * MS.Eta0 * (MS.Kx + MS.Ky) * sin(2.0 * Phase);
+      const Real f     = M.FEdge[e];
+      Real Uu = MS.Eta0 * ((-f + Grav * MS.Kx) * cos(Phase) + Src0);
+      Real Vv = MS.Eta0 * ((f + Grav * MS.Ky) * cos(Phase) + Src0);
+      const Real Kx2 = MS.Kx * MS.Kx, Ky2 = MS.Ky * MS.Ky;
       if (Del2On) {
          Uu += Visc2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
          Vv += Visc2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
       }
       if (Del4On) {
-         const double Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
+         const Real Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
          Uu -= Visc4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
          Vv -= Visc4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
       }
-      const double a = M.AngleEdge[e];
+      const Real a = M.AngleEdge[e];
       SrcU[e] = cos(a) * Uu + sin(a) * Vv;
    }
 }
 
 __global__ void __launch_bounds__(kBlock)
-k_edge_layer_terms(DMesh M, const double *__restrict__ Hs, const double *__restrict__ URaw,
-                   const double *__restrict__ KEBot, const double *__restrict__ NormalStress, int WindOn, int DragOn,
-                   double InvRho0, double Cd, double *__restrict__ RTop, double *__restrict__ RBot) {
+k_edge_layer_terms(DMesh M, const Real *__restrict__ Hs, const Real *__restrict__ URaw,
+                   const Real *__restrict__ KEBot, const Real *__restrict__ NormalStress, int WindOn, int DragOn,
+                   Real InvRho0, Real Cd, Real *__restrict__ RTop, Real *__restrict__ RBot) {
    // evaluated BEFORE the edge pass: with raw time-level indexing URaw may be the next-level array the edge
    // pass is about to overwrite
    const int e = blockIdx.x * blockDim.x + threadIdx.x;
    if (e >= M.NEdgesAll) return;
    const int2 cc     = M.CellsOnEdge[e];
-   const double mask = M.EdgeMask[e];
+   const Real mask = M.EdgeMask[e];
    const int K = M.K, KBot = K - 1;
-   double r0 = 0.0, rb = 0.0; // tendency of the top / bottom layer
+   Real r0 = 0.0, rb = 0.0; // tendency of the top / bottom layer
    if (WindOn) {
-      const double InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K] + Hs[(size_t)cc.y * K]));
+      const Real InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K] + Hs[(size_t)cc.y * K]));
       r0 = mask * InvThick * NormalStress[e] * InvRho0;
    }
    if (DragOn) {
-      const double VelNorm  = sqrt(KEBot[cc.x] + KEBot[cc.y]);
-      const double InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K + KBot] + Hs[(size_t)cc.y * K + KBot]));
+      const Real VelNorm  = sqrt(KEBot[cc.x] + KEBot[cc.y]);
+      const Real InvThick = 1.0 / (0.5 * (Hs[(size_t)cc.x * K + KBot] + Hs[(size_t)cc.y * K + KBot]));
       rb = -mask * Cd * VelNorm * InvThick * URaw[(size_t)e * K + KBot];
    }
    if (KBot == 0) {
@@ -884,8 +884,8 @@ k_edge_layer_terms(DMesh M, const double *__restrict__ Hs, const double *__restr
 }
 
 __global__ void __launch_bounds__(kBlock)
-k_edge_layer_apply(DMesh M, const double *__restrict__ RTop, const double *__restrict__ RBot, double *__restrict__ Unext,
-                   double *__restrict__ Uprov, double A, double B, TileRange TR, const int *__restrict__ EdgeRows,
+k_edge_layer_apply(DMesh M, const Real *__restrict__ RTop, const Real *__restrict__ RBot, Real *__restrict__ Unext,
+                   Real *__restrict__ Uprov, Real A, Real B, TileRange TR, const int *__restrict__ EdgeRows,
                    const TileHdr *__restrict__ Hdr) {
    // EdgeRows == nullptr: every edge once; else the OWN edges of the tiles of TR (halo split: the same edges,
    // in the same two groups, as the two launches of the tiled edge pass)
@@ -898,7 +898,7 @@ k_edge_layer_apply(DMesh M, const double *__restrict__ RTop, const double *__res
       e = EdgeRows[h.ERowOff + q];
    } else if (e >= M.NEdgesAll) return;
    const int K = M.K, KBot = K - 1;
-   const double r0 = RTop[e], rb = RBot[e];
+   const Real r0 = RTop[e], rb = RBot[e];
    const size_t o = (size_t)e * K;
    if (r0 != 0.0) {
       Unext[o] += B * r0;
@@ -966,18 +966,18 @@ struct ScopedTimer {
 // forward-backward are written with the provisional output alone (their "next" output goes to a sink buffer
 // with B = 0): a stage cannot update the next-level arrays in place, neighbours still read them.
 struct StageDesc {
-   const double *Hs, *Us, *Trs;      // stage state the tendencies are evaluated on
-   const double *HsMom;              // thickness the momentum aux + edge pass see (forward-backward: the NEW thickness)
-   const double *UTr, *URaw;         // velocity seen by tracer advection / bottom drag (raw time-level indexing, P1)
-   double *Hnext, *Unext, *TrNext;   // accumulated output
-   double *Hprov, *Uprov, *TrProv;   // provisional output (nullptr: none)
-   double A, B, TimeCell, TimeEdge;
+   const Real *Hs, *Us, *Trs;      // stage state the tendencies are evaluated on
+   const Real *HsMom;              // thickness the momentum aux + edge pass see (forward-backward: the NEW thickness)
+   const Real *UTr, *URaw;         // velocity seen by tracer advection / bottom drag (raw time-level indexing, P1)
+   Real *Hnext, *Unext, *TrNext;   // accumulated output
+   Real *Hprov, *Uprov, *TrProv;   // provisional output (nullptr: none)
+   Real A, B, TimeCell, TimeEdge;
    int First, Last, WSel, H2Sel, FinSel, DivSel;
    int BeforeExchange;               // the stage's results are exchanged right after it (halo split applies)
    int SkipHaloOK;                   // ... and nothing else reads its halo rows (see fused_phase)
 };
 
-static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, const double *Ucur, const double *TrCur,
+static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, const Real *Ucur, const Real *TrCur,
                      cudaStream_t St) {
    const DMesh &D           = S->M->D;
    const OmegaTendConfig &G = S->Cfg;
@@ -1006,7 +1006,7 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
    const bool tiled  = V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
    const bool msOn = G.ManufacturedSolutionTendency != 0;
    const bool drag = G.BottomDragTendencyEnable != 0, wind = G.WindForcingTendencyEnable != 0;
-   const double nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
+   const Real nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;
    if (msOn && (tiled || tiledE)) {
       const int n = std::max(D.NCellsAll, D.NEdgesAll);
       k_ms_sources<<<grid_for(n), kBlock, 0, St>>>(D, manufactured(S, sd.TimeCell), sd.TimeEdge, G.VelDiffTendencyEnable, G.ViscDel2,
@@ -1083,7 +1083,7 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const double *Hcur, c
       ++S->Launches;
    }
    // ---- momentum: aux fields, then the edge pass
-   const double *Hm = sd.HsMom;
+   const Real *Hm = sd.HsMom;
    LAUNCH_V(kFA, k_fA, gA, D, Hm, sd.Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
             G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0, tiledE && drag ? S->A.ZonalStress2 : nullptr);
    // W = Y - X folded into fB's cell result when the tiled edge pass follows (one gathered cell field less)
@@ -1178,9 +1178,9 @@ int fused_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *X, con
    OMEGA_REQUIRE(S->M->MaxEdgesUsed <= kME, "fused path supports at most 6 edges per cell; use Fused=0");
    const int ci = X->CurTimeIndex, ni = tix(1, ci, 2);
    const int tci = X->TracerCurTimeIndex, tni = tix(1, tci, 2);
-   double *Hcur = X->LayerThickness[ci], *Hnext = X->LayerThickness[ni];
-   double *Ucur = X->NormalVelocity[ci], *Unext = X->NormalVelocity[ni];
-   double *TrCur = X->Tracers[tci], *TrNext = X->Tracers[tni];
+   Real *Hcur = X->LayerThickness[ci], *Hnext = X->LayerThickness[ni];
+   Real *Ucur = X->NormalVelocity[ci], *Unext = X->NormalVelocity[ni];
+   Real *TrCur = X->Tracers[tci], *TrNext = X->Tracers[tni];
    // raw time-level indexing of the reference: with CurTimeIndex == 1 the "current" raw
    // slot is the NEXT buffer and vice versa
    const bool swapped = Compat && ci == 1;

@@ -5,12 +5,12 @@
 namespace omega {
 
 struct CellArgs {
-   const double *Hs, *Us, *UTr, *Trs, *Del2Tr; // stage state; UTr = velocity seen by tracer advection
-   const double *Hcur;
-   double *Hnext, *Hprov;                      // Hprov == nullptr on the last stage
-   const double *TrCur;
-   double *TrNext, *TrProv;
-   double A, B;                                // a_{s+1} dt, b_s dt
+   const Real *Hs, *Us, *UTr, *Trs, *Del2Tr; // stage state; UTr = velocity seen by tracer advection
+   const Real *Hcur;
+   Real *Hnext, *Hprov;                      // Hprov == nullptr on the last stage
+   const Real *TrCur;
+   Real *TrNext, *TrProv;
+   Real A, B;                                // a_{s+1} dt, b_s dt
    int First, Last, NTracers;
    int WSel;   // stage-0 weight thickness: 0 = Hcur, 1 = Hnext before this stage writes it
    int H2Sel;  // thickness multiplying cur tracers in the provisional update: 0 = Hcur, 1 = new Hnext, 2 = new Hprov
@@ -18,19 +18,19 @@ struct CellArgs {
    int FinSel; // thickness dividing the final tracers: 0 = new Hnext, 1 = Hcur
    int FluxDivOn, AdvOn, DiffOn, HypOn, FluxUpwind, TrUpwind;
    int Prefetch; // 0 off, 1 next tracer's rows into L1, 2 into L2
-   double EddyDiff2, EddyDiff4;
+   Real EddyDiff2, EddyDiff4;
    ManufacturedParams MS;
-   const double *SrcH; // tiled kernels: manufactured thickness source per cell (k_ms_sources), nullptr when off
+   const Real *SrcH; // tiled kernels: manufactured thickness source per cell (k_ms_sources), nullptr when off
 };
 
 constexpr int kME = 6; // max edges per cell on the fused path (checked at launch)
 
 struct EdgeArgs {
-   const double *Hs, *Us, *URaw;                       // stage state; URaw = velocity seen by bottom drag
-   const double *KE, *Div, *RelVort, *PVv, *Del2Div, *Del2RelVort, *NormalStress;
-   const double *Ucur;
-   double *Unext, *Uprov;
-   double A, B;
+   const Real *Hs, *Us, *URaw;                       // stage state; URaw = velocity seen by bottom drag
+   const Real *KE, *Div, *RelVort, *PVv, *Del2Div, *Del2RelVort, *NormalStress;
+   const Real *Ucur;
+   Real *Unext, *Uprov;
+   Real A, B;
    int First, Last;
    OmegaTendConfig G;
    ManufacturedParams MS;
@@ -38,15 +38,15 @@ struct EdgeArgs {
 
 // tiled edge pass: tend = m*PV term + m*[(-(X1-X0) + SY*(Y1-Y0))/dc - SZ*(Z1-Z0)/dv]
 struct EdgeTileArgs {
-   const double *Us, *Hs, *PVv; // stage velocity / thickness, PV on vertices
-   const double *X, *Y, *Z;     // combined cell / cell / vertex fields written by fA and fB
-   double SY, SZ;
-   const double *Ucur;
-   double *Unext, *Uprov;
-   double A, B;
+   const Real *Us, *Hs, *PVv; // stage velocity / thickness, PV on vertices
+   const Real *X, *Y, *Z;     // combined cell / cell / vertex fields written by fA and fB
+   Real SY, SZ;
+   const Real *Ucur;
+   Real *Unext, *Uprov;
+   Real A, B;
    int First, Last, PVOn, XOn;
    int FluxUpwind;     // FluxLayerThickEdge upwinded on the sign of u (LayerThicknessAuxVars.h:25-61)
-   const double *SrcU; // manufactured velocity source per edge (k_ms_sources), nullptr when off
+   const Real *SrcU; // manufactured velocity source per edge (k_ms_sources), nullptr when off
 };
 
 // tiles Map[First .. First + Count) of the mesh (Map == nullptr: tiles First .. First + Count)

@@ -32,6 +32,24 @@
 #include "omega_dev.h"
 #include "stepper.h"
 
+#ifdef OMEGA_SINGLE_PRECISION
+// The tile kernels are written for fp64 rows (a 16-level chunk is one 128-byte row piece, a thread owns two
+// levels = one 16-byte shared-memory access).  The single-precision build steps through the untiled fused
+// kernels of fused.cu and the kernel-per-term path; these stand in for the tile launchers there.
+namespace omega {
+bool tile_path_ok(const DMesh &) { return false; }
+bool tile_v2_enabled() { return false; }
+bool tile_v2_used(const CellArgs &) { return false; }
+bool tile_edge_path_ok(const DMesh &) { return false; }
+size_t tile_smem_bytes() { return 0; }
+int launch_fET(const DMesh &, const EdgeTileArgs &, cudaStream_t, const TileRange &) {
+   OMEGA_REQUIRE(false, "launch_fET: the tile kernels are not part of the single-precision build");
+}
+int launch_fCT(const DMesh &, const CellArgs &, cudaStream_t, const TileRange &) {
+   OMEGA_REQUIRE(false, "launch_fCT: the tile kernels are not part of the single-precision build");
+}
+} // namespace omega
+#else
 namespace omega {
 
 constexpr int kTKC     = 16;                    // levels per tile
@@ -1611,3 +1629,4 @@ int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const Ti
 bool tile_edge_path_ok(const DMesh &D) { return tile_path_ok(D) && D.Tiles.EdgeTilesOK; }
 
 } // namespace omega
+#endif // OMEGA_SINGLE_PRECISION

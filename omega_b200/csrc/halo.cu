@@ -7,7 +7,7 @@
 // with ONE pack launch, ONE grouped NCCL send/recv per neighbour over NVLink
 // and ONE unpack launch:
 //   * k_halo_round<Pack>: every (neighbour, array) pair is a blockIdx.y slice;
-//     a thread moves a double2 (two levels) of one row, so a 64-level row is
+//     a thread moves a Real2 (two levels) of one row, so a 64-level row is
 //     one coalesced 512-byte access on both sides;
 //   * the message of neighbour n is the concatenation of its per-array
 //     buffers, each in the reference's order [outer][exchange index][level]
@@ -43,7 +43,7 @@ namespace omega {
 template <bool Pack>
 __global__ void __launch_bounds__(kBlock)
 k_halo_rows(int NNbr, const int *__restrict__ Off, const int *__restrict__ Idx, int NOuter, int NRows,
-            int NInner, double *__restrict__ Array, double *__restrict__ Buf) {
+            int NInner, Real *__restrict__ Array, Real *__restrict__ Buf) {
    const long long w     = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    const long long total = (long long)Off[NNbr] * NOuter * NInner;
    if (w >= total) return;
@@ -66,14 +66,14 @@ constexpr int kRoundThreads = 128; // small CTAs: they must find room beside a r
 
 template <bool Pack, int V>
 __global__ void __launch_bounds__(kRoundThreads)
-k_halo_round(HaloRoundArgs A, double *__restrict__ Buf) {
+k_halo_round(HaloRoundArgs A, Real *__restrict__ Buf) {
    const int n = blockIdx.y / A.NArr, a = blockIdx.y - n * A.NArr;
    const int *Off = A.Off[a];
    const int o0 = Off[n], cnt = Off[n + 1] - o0;
    const int KV = A.K / V;
    const long long items = (long long)cnt * A.NOuter[a] * KV;
-   double *Arr = A.Arr[a];
-   double *B   = Buf + A.Start[a][n];
+   Real *Arr = A.Arr[a];
+   Real *B   = Buf + A.Start[a][n];
    const int *Idx = A.Idx[a] + o0;
    for (long long w = blockIdx.x * (long long)kRoundThreads + threadIdx.x; w < items; w += (long long)gridDim.x * kRoundThreads) {
       const int kv      = (int)(w % KV);
@@ -82,8 +82,8 @@ k_halo_round(HaloRoundArgs A, double *__restrict__ Buf) {
       const size_t src = ((size_t)o * A.NRows[a] + Idx[i]) * A.K + (size_t)kv * V;
       const size_t dst = (size_t)t * A.K + (size_t)kv * V;
       if (V == 2) {
-         if (Pack) *reinterpret_cast<double2 *>(B + dst) = *reinterpret_cast<const double2 *>(Arr + src);
-         else *reinterpret_cast<double2 *>(Arr + src) = *reinterpret_cast<const double2 *>(B + dst);
+         if (Pack) *reinterpret_cast<Real2 *>(B + dst) = *reinterpret_cast<const Real2 *>(Arr + src);
+         else *reinterpret_cast<Real2 *>(Arr + src) = *reinterpret_cast<const Real2 *>(B + dst);
       } else {
          if (Pack) B[dst] = Arr[src];
          else Arr[src] = B[dst];
@@ -139,7 +139,7 @@ static int load_nccl() {
    } while (0)
 
 // (re)size the library-owned round buffers and fill the launch arguments
-static int round_args(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, bool Send,
+static int round_args(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, bool Send,
                       HaloRoundArgs &A, long long &Total) {
    const int NN = H->NNeighbors, K = H->M->D.K;
    OMEGA_REQUIRE(N >= 1 && N <= kHaloMaxArrays, "halo round: 1..3 arrays");
@@ -165,17 +165,17 @@ static int round_args(OmegaHalo *H, double *const *Ptrs, const int *Elems, const
    return 0;
 }
 
-static int ensure_buffer(OmegaHalo *H, double **Buf, size_t *Cap, long long Need) {
+static int ensure_buffer(OmegaHalo *H, Real **Buf, size_t *Cap, long long Need) {
    if ((size_t)Need <= *Cap) return 0;
    // growing frees the old block: wait for exchanges in flight (rare: first round, or a wider round later)
    OMEGA_CUDA_CHECK(cudaDeviceSynchronize());
    if (*Buf) cudaFree(*Buf);
-   OMEGA_CUDA_CHECK(cudaMalloc((void **)Buf, (size_t)Need * sizeof(double)));
+   OMEGA_CUDA_CHECK(cudaMalloc((void **)Buf, (size_t)Need * sizeof(Real)));
    *Cap = (size_t)Need;
    return 0;
 }
 
-template <bool Pack> static int launch_round(const OmegaHalo *H, const HaloRoundArgs &A, long long MaxItems, double *Buf, cudaStream_t St) {
+template <bool Pack> static int launch_round(const OmegaHalo *H, const HaloRoundArgs &A, long long MaxItems, Real *Buf, cudaStream_t St) {
    if (H->NNeighbors == 0 || MaxItems == 0) return 0;
    const int V = (A.K & 1) ? 1 : 2;
    const unsigned gx = (unsigned)std::min<long long>((MaxItems / V + kRoundThreads - 1) / kRoundThreads, 1024);
@@ -196,7 +196,7 @@ static long long max_items(const OmegaHalo *H, const int *Elems, const int *NOut
    return m;
 }
 
-int halo_pack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
+int halo_pack_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
    HaloRoundArgs A;
    long long total = 0;
    if (round_args(H, Ptrs, Elems, NOuter, N, true, A, total)) return 2;
@@ -205,7 +205,7 @@ int halo_pack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const i
    return launch_round<true>(H, A, max_items(H, Elems, NOuter, N, true), H->SendBuf, St);
 }
 
-int halo_unpack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
+int halo_unpack_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
    HaloRoundArgs A;
    long long total = 0;
    if (round_args(H, Ptrs, Elems, NOuter, N, false, A, total)) return 2;
@@ -224,7 +224,7 @@ static void round_counts(const OmegaHalo *H, const int *Elems, const int *NOuter
 }
 
 // pack -> grouped NCCL send/recv with every neighbour -> unpack, all on St
-int halo_exchange_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
+int halo_exchange_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St) {
    OMEGA_REQUIRE(H->NNeighbors == 0 || H->Comm, "omega_halo_exchange_round: no communicator (omega_halo_comm_init)");
    if (H->NNeighbors == 0) return 0;
    // both buffers sized before anything is enqueued (ensure_buffer may synchronise)
@@ -252,15 +252,15 @@ int halo_exchange_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, con
       long long s, r;
       round_counts(H, Elems, NOuter, N, n, s, r);
       const int peer = H->NeighborTasks[n];
-      if (s) OMEGA_NCCL_CHECK(g_nccl.Send(H->SendBuf + so, (size_t)s, ncclDouble, peer, comm, St));
-      if (r) OMEGA_NCCL_CHECK(g_nccl.Recv(H->RecvBuf + ro, (size_t)r, ncclDouble, peer, comm, St));
+      if (s) OMEGA_NCCL_CHECK(g_nccl.Send(H->SendBuf + so, (size_t)s, (kSinglePrecision ? ncclFloat : ncclDouble), peer, comm, St));
+      if (r) OMEGA_NCCL_CHECK(g_nccl.Recv(H->RecvBuf + ro, (size_t)r, (kSinglePrecision ? ncclFloat : ncclDouble), peer, comm, St));
       so += s; ro += r;
    }
    OMEGA_NCCL_CHECK(g_nccl.GroupEnd());
    if (halo_unpack_round(H, Ptrs, Elems, NOuter, N, St)) return 1;
    if (timed) {
       OMEGA_CUDA_CHECK(cudaEventRecord(tm.Stop, St));
-      tm.Bytes = (so + ro) * (long long)sizeof(double);
+      tm.Bytes = (so + ro) * (long long)sizeof(Real);
       H->Events.push_back(tm);
    }
    H->Rounds += 1;
@@ -377,28 +377,28 @@ int omega_halo_buffer_counts(const OmegaHalo *H, OmegaMeshElement Elem, int NOut
    return 0;
 }
 
-int omega_halo_pack(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, const double *Array,
-                    double *SendBuf, void *Stream) {
+int omega_halo_pack(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, const Real *Array,
+                    Real *SendBuf, void *Stream) {
    OMEGA_REQUIRE(H && Array && SendBuf && Elem >= 0 && Elem < 3, "omega_halo_pack: bad argument");
    const int NN = H->NNeighbors;
    const long long total = (long long)H->SendOff[Elem][NN] * NOuter * NInner;
    if (total == 0) return 0;
    const int *d = H->DSendIdx[Elem];
    k_halo_rows<true><<<grid_for(total), kBlock, 0, (cudaStream_t)Stream>>>(
-       NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner, const_cast<double *>(Array), SendBuf);
+       NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner, const_cast<Real *>(Array), SendBuf);
    OMEGA_CUDA_CHECK(cudaGetLastError());
    return 0;
 }
 
-int omega_halo_unpack(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, const double *RecvBuf,
-                      double *Array, void *Stream) {
+int omega_halo_unpack(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, const Real *RecvBuf,
+                      Real *Array, void *Stream) {
    OMEGA_REQUIRE(H && Array && RecvBuf && Elem >= 0 && Elem < 3, "omega_halo_unpack: bad argument");
    const int NN = H->NNeighbors;
    const long long total = (long long)H->RecvOff[Elem][NN] * NOuter * NInner;
    if (total == 0) return 0;
    const int *d = H->DRecvIdx[Elem];
    k_halo_rows<false><<<grid_for(total), kBlock, 0, (cudaStream_t)Stream>>>(
-       NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner, Array, const_cast<double *>(RecvBuf));
+       NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner, Array, const_cast<Real *>(RecvBuf));
    OMEGA_CUDA_CHECK(cudaGetLastError());
    return 0;
 }
@@ -416,15 +416,15 @@ int omega_halo_round_counts(const OmegaHalo *H, const int *Elems, const int *NOu
    return 0;
 }
 
-int omega_halo_pack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N,
-                          double **SendBuf, void *Stream) {
+int omega_halo_pack_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N,
+                          Real **SendBuf, void *Stream) {
    OMEGA_REQUIRE(H && Ptrs && Elems && NOuter, "omega_halo_pack_round: null argument");
    int rc = halo_pack_round(H, Ptrs, Elems, NOuter, N, (cudaStream_t)Stream);
    if (SendBuf) *SendBuf = H->SendBuf;
    return rc;
 }
 
-int omega_halo_recv_buffer(OmegaHalo *H, const int *Elems, const int *NOuter, int N, double **RecvBuf) {
+int omega_halo_recv_buffer(OmegaHalo *H, const int *Elems, const int *NOuter, int N, Real **RecvBuf) {
    OMEGA_REQUIRE(H && Elems && NOuter && RecvBuf, "omega_halo_recv_buffer: null argument");
    long long tr = 0;
    for (int n = 0; n < H->NNeighbors; ++n) {
@@ -437,7 +437,7 @@ int omega_halo_recv_buffer(OmegaHalo *H, const int *Elems, const int *NOuter, in
    return 0;
 }
 
-int omega_halo_unpack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, void *Stream) {
+int omega_halo_unpack_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, void *Stream) {
    OMEGA_REQUIRE(H && Ptrs && Elems && NOuter, "omega_halo_unpack_round: null argument");
    return halo_unpack_round(H, Ptrs, Elems, NOuter, N, (cudaStream_t)Stream);
 }
@@ -475,14 +475,14 @@ int omega_halo_set_comm(OmegaHalo *H, void *NcclComm, int NRanks) {
    return 0;
 }
 
-int omega_halo_exchange_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, void *Stream) {
+int omega_halo_exchange_round(OmegaHalo *H, Real *const *Ptrs, const int *Elems, const int *NOuter, int N, void *Stream) {
    OMEGA_REQUIRE(H && Ptrs && Elems && NOuter, "omega_halo_exchange_round: null argument");
    return halo_exchange_round(H, Ptrs, Elems, NOuter, N, (cudaStream_t)Stream);
 }
 
-int omega_halo_exchange(OmegaHalo *H, double *Array, OmegaMeshElement Elem, int NOuter, void *Stream) {
+int omega_halo_exchange(OmegaHalo *H, Real *Array, OmegaMeshElement Elem, int NOuter, void *Stream) {
    OMEGA_REQUIRE(H && Array, "omega_halo_exchange: null argument");
-   double *p[1] = {Array};
+   Real *p[1] = {Array};
    int e[1] = {(int)Elem}, o[1] = {NOuter};
    return halo_exchange_round(H, p, e, o, 1, (cudaStream_t)Stream);
 }

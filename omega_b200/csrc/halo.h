@@ -8,7 +8,7 @@ constexpr int kHaloMaxNeighbors = 32; // per-neighbour buffer offsets travel as 
 // launch arguments of k_halo_round: array a of neighbour n starts at Start[a][n] (doubles) of the round buffer
 struct HaloRoundArgs {
    int NArr, K;
-   double *Arr[kHaloMaxArrays];
+   omega::Real *Arr[kHaloMaxArrays];
    int NOuter[kHaloMaxArrays], NRows[kHaloMaxArrays];
    const int *Off[kHaloMaxArrays], *Idx[kHaloMaxArrays]; // exchange lists of the array's element kind (device order)
    long long Start[kHaloMaxArrays][kHaloMaxNeighbors];
@@ -26,7 +26,7 @@ struct OmegaHalo {
    std::vector<int> SendOff[3], RecvOff[3]; // [NNeighbors+1]
    int *DSendIdx[3] = {}, *DRecvIdx[3] = {}; // device: [offsets | indices in device order]
    // round buffers, library-owned (grown on demand)
-   double *SendBuf = nullptr, *RecvBuf = nullptr;
+   omega::Real *SendBuf = nullptr, *RecvBuf = nullptr;
    size_t SendCap = 0, RecvCap = 0;
    long long LastSendDoubles = 0;
    // transport
@@ -46,7 +46,7 @@ struct OmegaHalo {
 };
 
 namespace omega {
-int halo_pack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
-int halo_unpack_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
-int halo_exchange_round(OmegaHalo *H, double *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
+int halo_pack_round(OmegaHalo *H, omega::Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
+int halo_unpack_round(OmegaHalo *H, omega::Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
+int halo_exchange_round(OmegaHalo *H, omega::Real *const *Ptrs, const int *Elems, const int *NOuter, int N, cudaStream_t St);
 } // namespace omega

@@ -1,7 +1,7 @@
 // kernel_util.cuh -- thread mapping and vector load/store shared by all kernels.
 //
 // Fields are [element][level] with level innermost.  One thread owns V
-// consecutive levels (V=2 -> one 16-byte double2 access) of one element; the
+// consecutive levels (V=2 -> one 16-byte Real2 access) of one element; the
 // work index runs level-fastest so a warp covers 32*V consecutive levels of
 // as few elements as possible: with 64 levels a warp is exactly one 512-byte
 // element row, every neighbour gather is one fully coalesced row read and the
@@ -9,36 +9,38 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include "real.h"
+
 namespace omega {
 
 constexpr int kBlock = 256;
 
-template <int V> __device__ __forceinline__ void ldv(double (&r)[V], const double *__restrict__ p);
-template <> __device__ __forceinline__ void ldv<1>(double (&r)[1], const double *__restrict__ p) {
+template <int V> __device__ __forceinline__ void ldv(Real (&r)[V], const Real *__restrict__ p);
+template <> __device__ __forceinline__ void ldv<1>(Real (&r)[1], const Real *__restrict__ p) {
    r[0] = __ldg(p);
 }
-template <> __device__ __forceinline__ void ldv<2>(double (&r)[2], const double *__restrict__ p) {
-   const double2 t = __ldg(reinterpret_cast<const double2 *>(p));
+template <> __device__ __forceinline__ void ldv<2>(Real (&r)[2], const Real *__restrict__ p) {
+   const Real2 t = __ldg(reinterpret_cast<const Real2 *>(p));
    r[0] = t.x;
    r[1] = t.y;
 }
 // plain (coherent) load for read-modify-write targets
-template <int V> __device__ __forceinline__ void ldp(double (&r)[V], const double *p);
-template <> __device__ __forceinline__ void ldp<1>(double (&r)[1], const double *p) { r[0] = *p; }
-template <> __device__ __forceinline__ void ldp<2>(double (&r)[2], const double *p) {
-   const double2 t = *reinterpret_cast<const double2 *>(p);
+template <int V> __device__ __forceinline__ void ldp(Real (&r)[V], const Real *p);
+template <> __device__ __forceinline__ void ldp<1>(Real (&r)[1], const Real *p) { r[0] = *p; }
+template <> __device__ __forceinline__ void ldp<2>(Real (&r)[2], const Real *p) {
+   const Real2 t = *reinterpret_cast<const Real2 *>(p);
    r[0] = t.x;
    r[1] = t.y;
 }
-template <int V> __device__ __forceinline__ void stv(double *p, const double (&r)[V]);
-template <> __device__ __forceinline__ void stv<1>(double *p, const double (&r)[1]) { *p = r[0]; }
-template <> __device__ __forceinline__ void stv<2>(double *p, const double (&r)[2]) {
-   *reinterpret_cast<double2 *>(p) = make_double2(r[0], r[1]);
+template <int V> __device__ __forceinline__ void stv(Real *p, const Real (&r)[V]);
+template <> __device__ __forceinline__ void stv<1>(Real *p, const Real (&r)[1]) { *p = r[0]; }
+template <> __device__ __forceinline__ void stv<2>(Real *p, const Real (&r)[2]) {
+   *reinterpret_cast<Real2 *>(p) = make_real2(r[0], r[1]);
 }
 
 // fire-and-forget prefetch of this lane's part of a row: raises the bytes in flight
 // per SM without landing registers (mode 1: into L1, mode 2: into L2 only)
-__device__ __forceinline__ void prefetch_row(const double *p, int mode) {
+__device__ __forceinline__ void prefetch_row(const Real *p, int mode) {
    if (mode == 1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
    else if (mode == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }

@@ -13,19 +13,19 @@ namespace omega {
 // ManufacturedThicknessTendency (src/ocn/CustomTendencyTerms.cpp:107-140)
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_thick_tend(DMesh M, int FluxDivOn, const double *__restrict__ Flux, const double *__restrict__ U,
-             double *__restrict__ HTend, ManufacturedParams MS) {
+k_thick_tend(DMesh M, int FluxDivOn, const Real *__restrict__ Flux, const Real *__restrict__ U,
+             Real *__restrict__ HTend, ManufacturedParams MS) {
    int c, k;
    if (!elem_k<V>(M.NCellsAll, M.K, c, k)) return;
-   double tend[V] = {0};
+   Real tend[V] = {0};
    if (FluxDivOn) {
-      const double InvA = 1.0 / M.AreaCell[c];
+      const Real InvA = 1.0 / M.AreaCell[c];
       const int n       = M.NEdgesOnCell[c];
-      double d[V] = {0};
+      Real d[V] = {0};
       for (int j = 0; j < n; ++j) {
          const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
-         const double cf = M.DvEdge[e] * M.EdgeSignOnCell[c * M.MaxEdges + j];
-         double f[V], u[V];
+         const Real cf = M.DvEdge[e] * M.EdgeSignOnCell[c * M.MaxEdges + j];
+         Real f[V], u[V];
          ldv<V>(f, Flux + (size_t)e * M.K + k);
          ldv<V>(u, U + (size_t)e * M.K + k);
 #pragma unroll
@@ -35,8 +35,8 @@ k_thick_tend(DMesh M, int FluxDivOn, const double *__restrict__ Flux, const doub
       for (int q = 0; q < V; ++q) tend[q] -= d[q];
    }
    if (MS.Enabled) {
-      const double Phase = MS.Kx * M.XCell[c] + MS.Ky * M.YCell[c] - MS.AngFreq * MS.Time;
-      const double src   = MS.Eta0 * (-MS.H0 * (MS.Kx + MS.Ky) * sin(Phase) - MS.AngFreq * cos(Phase) +
+      const Real Phase = MS.Kx * M.XCell[c] + MS.Ky * M.YCell[c] - MS.AngFreq * MS.Time;
+      const Real src   = MS.Eta0 * (-MS.H0 * (MS.Kx + MS.Ky) * sin(Phase) - MS.AngFreq * cos(Phase) +
                                     MS.Eta0 * (MS.Kx + MS.Ky) * cos(2.0 * Phase));
 #pragma unroll
       for (int q = 0; q < V; ++q) tend[q] += src;
@@ -51,110 +51,110 @@ k_thick_tend(DMesh M, int FluxDivOn, const double *__restrict__ Flux, const doub
 // applied in the order of Tendencies.cpp:301-425.
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_vel_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ U,
-           const double *__restrict__ URaw, double *__restrict__ UTend, ManufacturedParams MS) {
+k_vel_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const Real *__restrict__ U,
+           const Real *__restrict__ URaw, Real *__restrict__ UTend, ManufacturedParams MS) {
    int e, k;
    if (!elem_k<V>(M.NEdgesAll, M.K, e, k)) return;
    const size_t o    = (size_t)e * M.K + k;
-   const double mask = M.EdgeMask[e];
+   const Real mask = M.EdgeMask[e];
    const int2 cc = M.CellsOnEdge[e], vv = M.VerticesOnEdge[e];
-   double tend[V] = {0};
+   Real tend[V] = {0};
    if (G.PVTendencyEnable) {
-      double qe[V], fe[V], acc[V] = {0};
+      Real qe[V], fe[V], acc[V] = {0};
       ldv<V>(qe, A.NormRelVortEdge + o);
       ldv<V>(fe, A.NormPlanetVortEdge + o);
       const int n = M.NEdgesOnEdge[e];
       for (int j = 0; j < n; ++j) {
          const int je   = M.EdgesOnEdge[e * M.MaxEdges2 + j];
-         const double w = M.WeightsOnEdge[e * M.MaxEdges2 + j];
+         const Real w = M.WeightsOnEdge[e * M.MaxEdges2 + j];
          const size_t oj = (size_t)je * M.K + k;
-         double qj[V], fj[V], fl[V], uj[V];
+         Real qj[V], fj[V], fl[V], uj[V];
          ldv<V>(qj, A.NormRelVortEdge + oj);
          ldv<V>(fj, A.NormPlanetVortEdge + oj);
          ldv<V>(fl, A.Flux + oj);
          ldv<V>(uj, U + oj);
 #pragma unroll
          for (int q = 0; q < V; ++q) {
-            const double NormVort = (qe[q] + fe[q] + qj[q] + fj[q]) * 0.5;
+            const Real NormVort = (qe[q] + fe[q] + qj[q] + fj[q]) * 0.5;
             acc[q] += w * fl[q] * uj[q] * NormVort;
          }
       }
 #pragma unroll
       for (int q = 0; q < V; ++q) tend[q] += mask * acc[q];
    }
-   const double InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
+   const Real InvDc = 1.0 / M.DcEdge[e], InvDv = 1.0 / M.DvEdge[e];
    if (G.KETendencyEnable) {
-      double a0[V], a1[V];
+      Real a0[V], a1[V];
       ldv<V>(a0, A.KE + (size_t)cc.x * M.K + k);
       ldv<V>(a1, A.KE + (size_t)cc.y * M.K + k);
 #pragma unroll
       for (int q = 0; q < V; ++q) tend[q] -= mask * (a1[q] - a0[q]) * InvDc;
    }
    if (G.SSHTendencyEnable) {
-      const double Grav = 9.80665;
-      double a0[V], a1[V];
+      const Real Grav = 9.80665;
+      Real a0[V], a1[V];
       ldv<V>(a0, A.Ssh + (size_t)cc.x * M.K + k);
       ldv<V>(a1, A.Ssh + (size_t)cc.y * M.K + k);
 #pragma unroll
       for (int q = 0; q < V; ++q) tend[q] -= mask * Grav * (a1[q] - a0[q]) * InvDc;
    }
    if (G.VelDiffTendencyEnable) {
-      double d0[V], d1[V], r0[V], r1[V];
+      Real d0[V], d1[V], r0[V], r1[V];
       ldv<V>(d0, A.Div + (size_t)cc.x * M.K + k);
       ldv<V>(d1, A.Div + (size_t)cc.y * M.K + k);
       ldv<V>(r0, A.RelVort + (size_t)vv.x * M.K + k);
       ldv<V>(r1, A.RelVort + (size_t)vv.y * M.K + k);
-      const double cf = mask * G.ViscDel2 * M.MeshScalingDel2[e];
+      const Real cf = mask * G.ViscDel2 * M.MeshScalingDel2[e];
 #pragma unroll
       for (int q = 0; q < V; ++q) {
-         const double Del2U = ((d1[q] - d0[q]) * InvDc - (r1[q] - r0[q]) * InvDv);
+         const Real Del2U = ((d1[q] - d0[q]) * InvDc - (r1[q] - r0[q]) * InvDv);
          tend[q] += cf * Del2U;
       }
    }
    if (G.VelHyperDiffTendencyEnable) {
-      double d0[V], d1[V], r0[V], r1[V];
+      Real d0[V], d1[V], r0[V], r1[V];
       ldv<V>(d0, A.Del2Div + (size_t)cc.x * M.K + k);
       ldv<V>(d1, A.Del2Div + (size_t)cc.y * M.K + k);
       ldv<V>(r0, A.Del2RelVort + (size_t)vv.x * M.K + k);
       ldv<V>(r1, A.Del2RelVort + (size_t)vv.y * M.K + k);
-      const double cf = mask * G.ViscDel4 * M.MeshScalingDel4[e];
+      const Real cf = mask * G.ViscDel4 * M.MeshScalingDel4[e];
 #pragma unroll
       for (int q = 0; q < V; ++q) {
-         const double Del2U = (G.DivFactor * (d1[q] - d0[q]) * InvDc - (r1[q] - r0[q]) * InvDv);
+         const Real Del2U = (G.DivFactor * (d1[q] - d0[q]) * InvDc - (r1[q] - r0[q]) * InvDv);
          tend[q] -= cf * Del2U;
       }
    }
    if (G.WindForcingTendencyEnable && k == 0) { // acts on layer 0 only (:294-300)
-      const double InvThick = 1.0 / A.Mean[(size_t)e * M.K];
+      const Real InvThick = 1.0 / A.Mean[(size_t)e * M.K];
       tend[0] += mask * InvThick * A.NormalStress[e] / G.Density0;
    }
    if (G.BottomDragTendencyEnable) { // bottom layer only (:323-333)
       const int KBot = M.K - 1;
       if (KBot >= k && KBot < k + V) {
-         const double VelNorm  = sqrt(A.KE[(size_t)cc.x * M.K + KBot] + A.KE[(size_t)cc.y * M.K + KBot]);
-         const double InvThick = 1.0 / A.Mean[(size_t)e * M.K + KBot];
+         const Real VelNorm  = sqrt(A.KE[(size_t)cc.x * M.K + KBot] + A.KE[(size_t)cc.y * M.K + KBot]);
+         const Real InvThick = 1.0 / A.Mean[(size_t)e * M.K + KBot];
          tend[KBot - k] -= mask * G.BottomDragCoeff * VelNorm * InvThick * URaw[(size_t)e * M.K + KBot];
       }
    }
    if (MS.Enabled) {
-      const double Grav  = 9.80665;
-      const double Phase = MS.Kx * M.XEdge[e] + MS.Ky * M.YEdge[e] - MS.AngFreq * MS.Time;
-      const double Src0  = MS.AngFreq * sin(Phase) - 0.5 * MS.Eta0 * (MS.Kx + MS.Ky) * sin(2.0 * Phase);
-      const double f     = M.FEdge[e];
-      double Uu = MS.Eta0 * ((-f + Grav * MS.Kx) * cos(Phase) + Src0);
-      double Vv = MS.Eta0 * ((f + Grav * MS.Ky) * cos(Phase) + Src0);
-      const double Kx2 = MS.Kx * MS.Kx, Ky2 = MS.Ky * MS.Ky;
+      const Real Grav  = 9.80665;
+      const Real Phase = MS.Kx * M.XEdge[e] + MS.Ky * M.YEdge[e] - MS.AngFreq * MS.Time;
+      const Real Src0  = MS.AngFreq * sin(Phase) - 0.5 * MS.Eta0 * (MS.Kx + MS.Ky) * sin(2.0 * Phase);
+      const Real f     = M.FEdge[e];
+      Real Uu = MS.Eta0 * ((-f + Grav * MS.Kx) * cos(Phase) + Src0);
+      Real Vv = MS.Eta0 * ((f + Grav * MS.Ky) * cos(Phase) + Src0);
+      const Real Kx2 = MS.Kx * MS.Kx, Ky2 = MS.Ky * MS.Ky;
       if (G.VelDiffTendencyEnable) {
          Uu += G.ViscDel2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
          Vv += G.ViscDel2 * MS.Eta0 * (Kx2 + Ky2) * cos(Phase);
       }
       if (G.VelHyperDiffTendencyEnable) {
-         const double Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
+         const Real Kx4 = Kx2 * Kx2, Ky4 = Ky2 * Ky2;
          Uu -= G.ViscDel4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
          Vv -= G.ViscDel4 * MS.Eta0 * ((Kx4 + Ky4 + Kx2 * Ky2) * cos(Phase));
       }
-      const double a   = M.AngleEdge[e];
-      const double src = cos(a) * Uu + sin(a) * Vv;
+      const Real a   = M.AngleEdge[e];
+      const Real src = cos(a) * Uu + sin(a) * Vv;
 #pragma unroll
       for (int q = 0; q < V; ++q) tend[q] += src;
    }
@@ -165,22 +165,22 @@ k_vel_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ U,
 // (src/ocn/TendencyTerms.h:349-480) for every tracer in one pass over cells.
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_tracer_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ URaw,
-              const double *__restrict__ Tr, int NTracers, double *__restrict__ TrTend) {
+k_tracer_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const Real *__restrict__ URaw,
+              const Real *__restrict__ Tr, int NTracers, Real *__restrict__ TrTend) {
    int c, k;
    if (!elem_k<V>(M.NCellsAll, M.K, c, k)) return;
-   const double InvA = 1.0 / M.AreaCell[c];
+   const Real InvA = 1.0 / M.AreaCell[c];
    const int n       = M.NEdgesOnCell[c];
    const size_t CS = (size_t)M.NCellsSize * M.K, ES = (size_t)M.NEdgesSize * M.K;
    for (int l = 0; l < NTracers; ++l) {
-      const double *T = Tr + l * CS, *HTr = A.HTr + l * ES, *D2 = A.Del2Tr + l * CS;
-      double tend[V] = {0};
+      const Real *T = Tr + l * CS, *HTr = A.HTr + l * ES, *D2 = A.Del2Tr + l * CS;
+      Real tend[V] = {0};
       if (G.TracerHorzAdvTendencyEnable) {
-         double t[V] = {0};
+         Real t[V] = {0};
          for (int j = 0; j < n; ++j) {
             const int e     = M.EdgesOnCell[c * M.MaxEdges + j];
-            const double cf = M.EdgeMask[e] * M.DvEdge[e] * M.EdgeSignOnCell[c * M.MaxEdges + j];
-            double ht[V], u[V];
+            const Real cf = M.EdgeMask[e] * M.DvEdge[e] * M.EdgeSignOnCell[c * M.MaxEdges + j];
+            Real ht[V], u[V];
             ldv<V>(ht, HTr + (size_t)e * M.K + k);
             ldv<V>(u, URaw + (size_t)e * M.K + k);
 #pragma unroll
@@ -190,13 +190,13 @@ k_tracer_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ 
          for (int q = 0; q < V; ++q) tend[q] -= t[q];
       }
       if (G.TracerDiffTendencyEnable) {
-         double t[V] = {0};
+         Real t[V] = {0};
          for (int j = 0; j < n; ++j) {
             const int e   = M.EdgesOnCell[c * M.MaxEdges + j];
             const int2 cc = M.CellsOnEdge[e];
-            const double RTemp = M.MeshScalingDel2[e] * M.DvEdge[e] / M.DcEdge[e];
-            const double cf    = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * RTemp;
-            double m[V], t0[V], t1[V];
+            const Real RTemp = M.MeshScalingDel2[e] * M.DvEdge[e] / M.DcEdge[e];
+            const Real cf    = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * RTemp;
+            Real m[V], t0[V], t1[V];
             ldv<V>(m, A.Mean + (size_t)e * M.K + k);
             ldv<V>(t0, T + (size_t)cc.x * M.K + k);
             ldv<V>(t1, T + (size_t)cc.y * M.K + k);
@@ -207,13 +207,13 @@ k_tracer_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ 
          for (int q = 0; q < V; ++q) tend[q] += G.EddyDiff2 * t[q] * InvA;
       }
       if (G.TracerHyperDiffTendencyEnable) {
-         double t[V] = {0};
+         Real t[V] = {0};
          for (int j = 0; j < n; ++j) {
             const int e   = M.EdgesOnCell[c * M.MaxEdges + j];
             const int2 cc = M.CellsOnEdge[e];
-            const double RTemp = M.MeshScalingDel4[e] * M.DvEdge[e] / M.DcEdge[e];
-            const double cf    = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * RTemp;
-            double t0[V], t1[V];
+            const Real RTemp = M.MeshScalingDel4[e] * M.DvEdge[e] / M.DcEdge[e];
+            const Real cf    = M.EdgeMask[e] * M.EdgeSignOnCell[c * M.MaxEdges + j] * RTemp;
+            Real t0[V], t1[V];
             ldv<V>(t0, D2 + (size_t)cc.x * M.K + k);
             ldv<V>(t1, D2 + (size_t)cc.y * M.K + k);
 #pragma unroll
@@ -227,17 +227,17 @@ k_tracer_tend(DMesh M, OmegaTendConfig G, AuxPtrs A, const double *__restrict__ 
 }
 
 void launch_thick_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                       const double *U, double *HTend, const ManufacturedParams &MS) {
+                       const Real *U, Real *HTend, const ManufacturedParams &MS) {
    OMEGA_LAUNCH_V(k_thick_tend, M.NCellsAll, M.K, L.Stream, M, G.ThicknessFluxTendencyEnable, A.Flux, U, HTend, MS);
    ++*L.Count;
 }
 void launch_vel_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                     const double *U, const double *URaw, double *UTend, const ManufacturedParams &MS) {
+                     const Real *U, const Real *URaw, Real *UTend, const ManufacturedParams &MS) {
    OMEGA_LAUNCH_V(k_vel_tend, M.NEdgesAll, M.K, L.Stream, M, G, A, U, URaw, UTend, MS);
    ++*L.Count;
 }
 void launch_tracer_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                        const double *URaw, const double *Tr, int NTracers, double *TrTend) {
+                        const Real *URaw, const Real *Tr, int NTracers, Real *TrTend) {
    if (NTracers == 0) return;
    OMEGA_LAUNCH_V(k_tracer_tend, M.NCellsAll, M.K, L.Stream, M, G, A, URaw, Tr, NTracers, TrTend);
    ++*L.Count;

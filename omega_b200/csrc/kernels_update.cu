@@ -11,11 +11,11 @@ namespace omega {
 // updateThicknessByTend / updateVelocityByTend (:378-430): Y1 = Y2 + c*T
 template <int V>
 __global__ void __launch_bounds__(kBlock)
-k_axpy(int N, int K, double *Y1, const double *Y2, double C, const double *__restrict__ T) {
+k_axpy(int N, int K, Real *Y1, const Real *Y2, Real C, const Real *__restrict__ T) {
    int i, k;
    if (!elem_k<V>(N, K, i, k)) return;
    const size_t o = (size_t)i * K + k;
-   double y[V], t[V];
+   Real y[V], t[V];
    ldp<V>(y, Y2 + o);
    ldv<V>(t, T + o);
 #pragma unroll
@@ -29,16 +29,16 @@ k_axpy(int N, int K, double *Y1, const double *Y2, double C, const double *__res
 // Mode 3 finalizeTracersUpdate (:511-524)   Next /= H1
 template <int V, int Mode>
 __global__ void __launch_bounds__(kBlock)
-k_tracer_update(int NAll, int NSize, int K, int NTracers, double *Next, const double *Cur,
-                const double *H1, const double *H2, double C, const double *__restrict__ T) {
+k_tracer_update(int NAll, int NSize, int K, int NTracers, Real *Next, const Real *Cur,
+                const Real *H1, const Real *H2, Real C, const Real *__restrict__ T) {
    int i, k;
    if (!elem_k<V>(NAll, K, i, k)) return;
    const size_t o = (size_t)i * K + k, CS = (size_t)NSize * K;
-   double h1[V], h2[V];
+   Real h1[V], h2[V];
    if (Mode != 2) ldp<V>(h1, H1 + o);
    if (Mode == 0) ldp<V>(h2, H2 + o);
    for (int l = 0; l < NTracers; ++l) {
-      double r[V], a[V], t[V];
+      Real r[V], a[V], t[V];
       if (Mode == 0 || Mode == 1) ldp<V>(a, Cur + l * CS + o);
       if (Mode == 2 || Mode == 3) ldp<V>(a, Next + l * CS + o);
       if (Mode == 0 || Mode == 2) ldv<V>(t, T + l * CS + o);
@@ -56,7 +56,7 @@ k_tracer_update(int NAll, int NSize, int K, int NTracers, double *Next, const do
 // Dst[o][r][:] = Src[o][SrcRowOfDst[r]][:]
 __global__ void __launch_bounds__(kBlock)
 k_permute_rows(int NOuter, int NRows, int NInner, const int *__restrict__ SrcRowOfDst,
-               const double *__restrict__ Src, double *__restrict__ Dst) {
+               const Real *__restrict__ Src, Real *__restrict__ Dst) {
    const long long w     = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    const long long total = (long long)NOuter * NRows * NInner;
    if (w >= total) return;
@@ -67,7 +67,7 @@ k_permute_rows(int NOuter, int NRows, int NInner, const int *__restrict__ SrcRow
    Dst[w] = Src[((size_t)o * NRows + SrcRowOfDst[r]) * NInner + k];
 }
 
-void launch_axpy(const Launch &L, int NAll, int K, double *Y1, const double *Y2, double C, const double *T) {
+void launch_axpy(const Launch &L, int NAll, int K, Real *Y1, const Real *Y2, Real C, const Real *T) {
    OMEGA_LAUNCH_V(k_axpy, NAll, K, L.Stream, NAll, K, Y1, Y2, C, T);
    ++*L.Count;
 }
@@ -83,20 +83,20 @@ void launch_axpy(const Launch &L, int NAll, int K, double *Y1, const double *Y2,
       }                                                                                           \
    } while (0)
 
-void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                           const double *Cur, const double *H1, const double *H2, double C, const double *T) {
+void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                           const Real *Cur, const Real *H1, const Real *H2, Real C, const Real *T) {
    OMEGA_LAUNCH_TR(0, NAll, NSize, K, NTracers, Next, Cur, H1, H2, C, T);
 }
-void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                           const double *Cur, const double *H) {
+void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                           const Real *Cur, const Real *H) {
    OMEGA_LAUNCH_TR(1, NAll, NSize, K, NTracers, Next, Cur, H, nullptr, 0.0, nullptr);
 }
-void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Accum,
-                               double C, const double *T) {
+void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Accum,
+                               Real C, const Real *T) {
    OMEGA_LAUNCH_TR(2, NAll, NSize, K, NTracers, Accum, nullptr, nullptr, nullptr, C, T);
 }
-void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                             const double *H) {
+void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                             const Real *H) {
    OMEGA_LAUNCH_TR(3, NAll, NSize, K, NTracers, Next, nullptr, H, nullptr, 0.0, nullptr);
 }
 
@@ -104,8 +104,8 @@ void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NT
 // ToDevice: Dev[DevRowOfHost[Row0 + i]] = Stage[i];  else: Stage[i] = Dev[DevRowOfHost[Row0 + i]]
 template <bool ToDevice>
 __global__ void __launch_bounds__(kBlock)
-k_slab_rows(int Row0, int NSlab, int NInner, const int *__restrict__ DevRowOfHost, double *__restrict__ Dev,
-            double *__restrict__ Stage) {
+k_slab_rows(int Row0, int NSlab, int NInner, const int *__restrict__ DevRowOfHost, Real *__restrict__ Dev,
+            Real *__restrict__ Stage) {
    const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    if (w >= (long long)NSlab * NInner) return;
    const int i = (int)(w / NInner), k = (int)(w - (long long)i * NInner);
@@ -114,8 +114,8 @@ k_slab_rows(int Row0, int NSlab, int NInner, const int *__restrict__ DevRowOfHos
    else Stage[w] = Dev[d];
 }
 
-void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, double *Dev,
-                      double *Stage) {
+void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, Real *Dev,
+                      Real *Stage) {
    const long long total = (long long)NSlab * NInner;
    if (total <= 0) return;
    if (ToDevice) k_slab_rows<true><<<grid_for(total), kBlock, 0, S>>>(Row0, NSlab, NInner, DevRowOfHost, Dev, Stage);
@@ -128,8 +128,8 @@ void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NI
 // beside the stage kernels of another stream and is bound by the link, not by the SMs.
 template <bool ToDevice, int V>
 __global__ void __launch_bounds__(128)
-k_rows_hostmem(int NOuter, int NRows, int NInner, const int *__restrict__ DevRowOfHost, double *__restrict__ Dev,
-               double *__restrict__ Host) {
+k_rows_hostmem(int NOuter, int NRows, int NInner, const int *__restrict__ DevRowOfHost, Real *__restrict__ Dev,
+               Real *__restrict__ Host) {
    const int KV = NInner / V;
    const long long total = (long long)NOuter * NRows * KV;
    for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
@@ -139,8 +139,8 @@ k_rows_hostmem(int NOuter, int NRows, int NInner, const int *__restrict__ DevRow
       const size_t h = (size_t)t * NInner + (size_t)kv * V;
       const size_t d = ((size_t)o * NRows + DevRowOfHost[r]) * NInner + (size_t)kv * V;
       if (V == 2) {
-         if (ToDevice) *reinterpret_cast<double2 *>(Dev + d) = __ldcs(reinterpret_cast<const double2 *>(Host + h));
-         else __stcs(reinterpret_cast<double2 *>(Host + h), *reinterpret_cast<const double2 *>(Dev + d));
+         if (ToDevice) *reinterpret_cast<Real2 *>(Dev + d) = __ldcs(reinterpret_cast<const Real2 *>(Host + h));
+         else __stcs(reinterpret_cast<Real2 *>(Host + h), *reinterpret_cast<const Real2 *>(Dev + d));
       } else {
          if (ToDevice) Dev[d] = __ldcs(Host + h);
          else __stcs(Host + h, Dev[d]);
@@ -148,8 +148,8 @@ k_rows_hostmem(int NOuter, int NRows, int NInner, const int *__restrict__ DevRow
    }
 }
 
-void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, double *Dev,
-                         double *Host, int NCtas) {
+void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, Real *Dev,
+                         Real *Host, int NCtas) {
    const long long total = (long long)NOuter * NRows * NInner;
    if (total <= 0) return;
    const unsigned g = (unsigned)std::max(1, NCtas);
@@ -163,7 +163,7 @@ void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, i
 }
 
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
-                         const double *Src, double *Dst) {
+                         const Real *Src, Real *Dst) {
    const long long total = (long long)NOuter * NRows * NInner;
    if (total > 0) k_permute_rows<<<grid_for(total), kBlock, 0, S>>>(NOuter, NRows, NInner, SrcRowOfDst, Src, Dst);
 }

@@ -85,6 +85,19 @@ template <class T> static int to_device(OmegaMesh *M, const std::vector<T> &h, c
    return 0;
 }
 
+#ifdef OMEGA_SINGLE_PRECISION
+// single-precision build: the tables are evaluated in fp64 on the host and rounded once when staged
+static int to_device(OmegaMesh *M, const std::vector<double> &h, const float **out) {
+   std::vector<float> f(h.begin(), h.end());
+   return to_device<float>(M, f, out);
+}
+static int to_device(OmegaMesh *M, const std::vector<double2> &h, const float2 **out) {
+   std::vector<float2> f(h.size());
+   for (size_t i = 0; i < h.size(); ++i) f[i] = make_float2((float)h[i].x, (float)h[i].y);
+   return to_device<float2>(M, f, out);
+}
+#endif
+
 // rows of a host-order table gathered into device order
 template <class T>
 static std::vector<T> gather_rows(const T *src, const std::vector<int> &perm, int width) {
@@ -348,6 +361,7 @@ extern "C" {
 
 const char *omega_last_error(void) { return g_last_error.c_str(); }
 int omega_b200_abi_version(void) { return 1; }
+int omega_b200_real_bytes(void) { return (int)sizeof(OmegaReal); }
 
 int omega_dev_alloc(void **ptr, unsigned long long bytes) {
    OMEGA_CUDA_CHECK(cudaMalloc(ptr, bytes ? bytes : 16));
@@ -632,11 +646,11 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
                }
             }
          const int *qi2 = nullptr;
-         const double *qd2 = nullptr;
+         const Real *qd2 = nullptr;
          rc |= to_device(M, ae, &G.ACellEdge);
          rc |= to_device(M, avi, &qi2); G.AVertIdx = reinterpret_cast<const int2 *>(qi2);
-         rc |= to_device(M, ac, &qd2); G.ACellCf = reinterpret_cast<const double2 *>(qd2);
-         rc |= to_device(M, avc, &qd2); G.AVertCf = reinterpret_cast<const double2 *>(qd2);
+         rc |= to_device(M, ac, &qd2); G.ACellCf = reinterpret_cast<const Real2 *>(qd2);
+         rc |= to_device(M, avc, &qd2); G.AVertCf = reinterpret_cast<const Real2 *>(qd2);
       }
       {
          // k_fB3 tables: the same sums with every gathered row read once.  Around a cell each vertex is the
@@ -682,18 +696,18 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
          }
          G.B3OK = ok ? 1 : 0;
          const int *qi3 = nullptr;
-         const double *qd3 = nullptr;
+         const Real *qd3 = nullptr;
          rc |= to_device(M, ci3, &qi3); G.B3CellIdx = reinterpret_cast<const int4 *>(qi3);
          rc |= to_device(M, vi3, &qi3); G.B3VertIdx = reinterpret_cast<const int4 *>(qi3);
-         rc |= to_device(M, cc3, &qd3); G.B3CellCf = reinterpret_cast<const double2 *>(qd3);
-         rc |= to_device(M, vc3, &qd3); G.B3VertCf = reinterpret_cast<const double2 *>(qd3);
+         rc |= to_device(M, cc3, &qd3); G.B3CellCf = reinterpret_cast<const Real2 *>(qd3);
+         rc |= to_device(M, vc3, &qd3); G.B3VertCf = reinterpret_cast<const Real2 *>(qd3);
       }
       const int *qi = nullptr;
-      const double *qd = nullptr;
+      const Real *qd = nullptr;
       rc |= to_device(M, ci, &qi); G.B2CellIdx = reinterpret_cast<const int4 *>(qi);
       rc |= to_device(M, vi, &qi); G.B2VertIdx = reinterpret_cast<const int4 *>(qi);
-      rc |= to_device(M, cc, &qd); G.B2CellCf = reinterpret_cast<const double2 *>(qd);
-      rc |= to_device(M, vc, &qd); G.B2VertCf = reinterpret_cast<const double2 *>(qd);
+      rc |= to_device(M, cc, &qd); G.B2CellCf = reinterpret_cast<const Real2 *>(qd);
+      rc |= to_device(M, vc, &qd); G.B2VertCf = reinterpret_cast<const Real2 *>(qd);
    }
 #undef STAGE
    if (!rc)
@@ -749,10 +763,10 @@ int omega_mesh_derived(const OmegaMesh *M, double *EdgeSignOnCell, double *EdgeS
 // scattered to / gathered from its device rows (DIPerm: device row of a host row).
 static constexpr size_t kSlabBytes = 64u << 20;
 
-static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, double *Dev, double *Host,
+static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, Real *Dev, Real *Host,
                           cudaStream_t S, bool ToDevice) {
    const int NRows    = n_size(M, Elem);
-   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
+   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(Real);
    if (bytes == 0) return 0;
    if (!M->Reordered) {
       if (ToDevice) OMEGA_CUDA_CHECK(cudaMemcpyAsync(Dev, Host, bytes, cudaMemcpyHostToDevice, S));
@@ -783,13 +797,13 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
          int dev = 0, sm = 0;
          OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
          OMEGA_CUDA_CHECK(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
-         launch_rows_hostmem(S, ToDevice, NOuter, NRows, NInner, M->DIPerm[Elem], Dev, (double *)at.devicePointer, 2 * sm);
+         launch_rows_hostmem(S, ToDevice, NOuter, NRows, NInner, M->DIPerm[Elem], Dev, (Real *)at.devicePointer, 2 * sm);
          OMEGA_CUDA_CHECK(cudaGetLastError());
          return 0;
       }
    }
    if (!wantSlab && bytes <= totalB / 8) {
-      double *stage = nullptr;
+      Real *stage = nullptr;
       OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, bytes, S));
       if (ToDevice) {
          OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));
@@ -802,13 +816,13 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
       OMEGA_CUDA_CHECK(cudaFreeAsync(stage, S));
       return 0;
    }
-   const size_t rowBytes = (size_t)NInner * sizeof(double);
+   const size_t rowBytes = (size_t)NInner * sizeof(Real);
    const int slabRows    = (int)std::max<size_t>(1, std::min<size_t>(NRows, kSlabBytes / rowBytes));
-   double *stage = nullptr;
+   Real *stage = nullptr;
    OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, (size_t)slabRows * rowBytes, S));
    for (int o = 0; o < NOuter; ++o) {
-      double *dev  = Dev + (size_t)o * NRows * NInner;
-      double *host = Host + (size_t)o * NRows * NInner;
+      Real *dev  = Dev + (size_t)o * NRows * NInner;
+      Real *host = Host + (size_t)o * NRows * NInner;
       for (int r0 = 0; r0 < NRows; r0 += slabRows) {
          const int n = std::min(slabRows, NRows - r0);
          if (ToDevice) {
@@ -826,27 +840,27 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
 }
 
 int omega_field_to_device(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
-                          const double *Host, double *Dev, void *Stream) {
+                          const Real *Host, Real *Dev, void *Stream) {
    OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3, "omega_field_to_device: bad argument");
-   return field_transfer(M, Elem, NOuter, NInner, Dev, const_cast<double *>(Host), (cudaStream_t)Stream, true);
+   return field_transfer(M, Elem, NOuter, NInner, Dev, const_cast<Real *>(Host), (cudaStream_t)Stream, true);
 }
 
-static int field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, const double *Dev,
-                         double *Host, void *Stream, bool Sync) {
+static int field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, const Real *Dev,
+                         Real *Host, void *Stream, bool Sync) {
    OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3, "omega_field_to_host: bad argument");
-   int rc = field_transfer(M, Elem, NOuter, NInner, const_cast<double *>(Dev), Host, (cudaStream_t)Stream, false);
+   int rc = field_transfer(M, Elem, NOuter, NInner, const_cast<Real *>(Dev), Host, (cudaStream_t)Stream, false);
    if (rc) return rc;
    if (Sync) OMEGA_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)Stream));
    return 0;
 }
 
 int omega_field_to_host(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
-                        const double *Dev, double *Host, void *Stream) {
+                        const Real *Dev, Real *Host, void *Stream) {
    return field_to_host(M, Elem, NOuter, NInner, Dev, Host, Stream, true);
 }
 
 int omega_field_to_host_async(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
-                              const double *Dev, double *Host, void *Stream) {
+                              const Real *Dev, Real *Host, void *Stream) {
    return field_to_host(M, Elem, NOuter, NInner, Dev, Host, Stream, false);
 }
 
@@ -859,16 +873,16 @@ int omega_field_to_host_async(const OmegaMesh *M, OmegaMeshElement Elem, int NOu
 // use comes from cudaGetSymbolAddress, looked up once per device with that device current.
 namespace omega {
 constexpr size_t kNoAllocStageBytes = (size_t)OMEGA_NOALLOC_MAX_BYTES;
-static __device__ __align__(256) double g_noalloc_stage[kNoAllocStageBytes / sizeof(double)];
+static __device__ __align__(256) Real g_noalloc_stage[kNoAllocStageBytes / sizeof(Real)];
 
-static int noalloc_stage_ptr(double **Ptr) {
+static int noalloc_stage_ptr(Real **Ptr) {
    constexpr int kMaxDevices = 64;
-   static double *perDevice[kMaxDevices] = {};
+   static Real *perDevice[kMaxDevices] = {};
    int dev = 0;
    OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
    OMEGA_REQUIRE(dev >= 0 && dev < kMaxDevices, "omega_field_to_device_noalloc: device ordinal beyond 63");
    if (!perDevice[dev]) {
-      double *p = nullptr;
+      Real *p = nullptr;
       OMEGA_CUDA_CHECK(cudaGetSymbolAddress((void **)&p, g_noalloc_stage));
       OMEGA_REQUIRE(p, "omega_field_to_device_noalloc: cudaGetSymbolAddress returned a null address");
       perDevice[dev] = p;
@@ -879,11 +893,11 @@ static int noalloc_stage_ptr(double **Ptr) {
 } // namespace omega
 
 extern "C" int omega_field_to_device_noalloc(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner,
-                                             const double *Host, double *Dev, void *Stream) {
+                                             const Real *Host, Real *Dev, void *Stream) {
    OMEGA_REQUIRE(M && Host && Dev && Elem >= 0 && Elem < 3 && NOuter >= 0 && NInner >= 0,
                  "omega_field_to_device_noalloc: bad argument");
    const int NRows    = n_size(M, Elem);
-   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(double);
+   const size_t bytes = (size_t)NOuter * NRows * NInner * sizeof(Real);
    if (bytes == 0) return 0;
    OMEGA_REQUIRE(bytes <= kNoAllocStageBytes,
                  "omega_field_to_device_noalloc: field of " + std::to_string(bytes) + " bytes exceeds the static staging block (" +
@@ -893,7 +907,7 @@ extern "C" int omega_field_to_device_noalloc(const OmegaMesh *M, OmegaMeshElemen
       OMEGA_CUDA_CHECK(cudaMemcpyAsync(Dev, Host, bytes, cudaMemcpyHostToDevice, S));
       return 0;
    }
-   double *stage = nullptr;
+   Real *stage = nullptr;
    if (int rc = noalloc_stage_ptr(&stage)) return rc;
    // every element of stage[0, bytes) is overwritten by the copy before the kernel reads it: nothing to clear
    OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));

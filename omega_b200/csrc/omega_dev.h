@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "omega_b200.h"
+#include "real.h"
 
 namespace omega {
 
@@ -54,16 +55,16 @@ struct DTiles {
    const TileHdr *Hdr;
    const int *HaloRows;       // ring-1 then ring-2 rows of every tile (device cell index)
    const unsigned short *Nbl; // [own + ring-1 rows][8]: local row of the cell across edge j (self when none)
-   const double *GCell;       // [NCellsSize][6]  EdgeMask*DvEdge/DcEdge of edge j of the cell, 0 when none
-   const double *CfUCell;     // [NCellsSize][6]  DvEdge*EdgeSignOnCell
-   const double *WaCell;      // [NCellsSize][6]  EdgeMask*DvEdge*EdgeSignOnCell
+   const Real *GCell;       // [NCellsSize][6]  EdgeMask*DvEdge/DcEdge of edge j of the cell, 0 when none
+   const Real *CfUCell;     // [NCellsSize][6]  DvEdge*EdgeSignOnCell
+   const Real *WaCell;      // [NCellsSize][6]  EdgeMask*DvEdge*EdgeSignOnCell
    const int *EocCell;        // [NCellsSize][6]  EdgesOnCell, boundary slot when none
    // edge side (the shared-memory staged edge pass): valid when EdgeTilesOK
    int EdgeTilesOK;
    const int *EdgeRows;            // staged edges of every tile (device edge index), own edges first
    const int4 *EdgeCV;             // per staged edge: CellsOnEdge (x,y), VerticesOnEdge (z,w), same order as EdgeRows
    const unsigned short *EoELocal; // [own edges][10]: staged row of EdgesOnEdge entry j (self when none)
-   const double *InvAreaCell; // [NCellsSize], 0 in the boundary slot
+   const Real *InvAreaCell; // [NCellsSize], 0 in the boundary slot
 };
 
 // Device-resident HorzMesh, structure of arrays, DEVICE order.  Passed to
@@ -78,23 +79,23 @@ struct DMesh {
    // cells
    const int *NEdgesOnCell;       // [C]
    const int *EdgesOnCell;        // [C][MaxEdges]
-   const double *EdgeSignOnCell;  // [C][MaxEdges]
-   const double *AreaCell, *BottomDepth, *XCell, *YCell;
+   const Real *EdgeSignOnCell;  // [C][MaxEdges]
+   const Real *AreaCell, *BottomDepth, *XCell, *YCell;
    // edges
    const int2 *CellsOnEdge, *VerticesOnEdge; // [E]
    const int *NEdgesOnEdge;                  // [E] trimmed of trailing boundary-slot entries
    const int *EdgesOnEdge;                   // [E][MaxEdges2]
-   const double *WeightsOnEdge;              // [E][MaxEdges2]
+   const Real *WeightsOnEdge;              // [E][MaxEdges2]
    const int2 *EoECells, *EoEVerts;          // [E][MaxEdges2] cells / vertices of each EdgesOnEdge entry
-   const double *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge;
-   const double *EdgeMask, *MeshScalingDel2, *MeshScalingDel4; // [E]
+   const Real *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge;
+   const Real *EdgeMask, *MeshScalingDel2, *MeshScalingDel4; // [E]
    // vertices (VertexDegree == 3)
    const int *CellsOnVertex, *EdgesOnVertex;               // [V][3]
-   const double *EdgeSignOnVertex, *KiteAreasOnVertex;     // [V][3]
-   const double *AreaTriangle, *FVertex;
+   const Real *EdgeSignOnVertex, *KiteAreasOnVertex;     // [V][3]
+   const Real *AreaTriangle, *FVertex;
    // reciprocals evaluated once on the host (IEEE division, the same bits the kernels' own
    // 1.0/x gave): 1/dc, 1/dv, 1/max(dv, 0.25 dc) per edge; 1/AreaCell; 1/AreaTriangle
-   const double *InvDcEdge, *InvDvEdge, *InvDvEffEdge, *InvAreaCell, *InvAreaTriangle;
+   const Real *InvDcEdge, *InvDvEdge, *InvDvEffEdge, *InvAreaCell, *InvAreaTriangle;
    // flattened stencils of k_fB (velocity Del2 of Del2): per (cell, edge j) the rows
    // {neighbour cell, v0, v1} and the coefficients {A, B} of
    //   Del2Div(c) = sum_j A_j (Div(nbr_j) - Div(c)) + B_j (RelVort(v1_j) - RelVort(v0_j)),
@@ -106,11 +107,11 @@ struct DMesh {
    // flattened stencils of k_fA: per (cell, edge j) the edge row (B2... not needed: AEdge) and {KE, Div}
    // coefficients; per (vertex, j) the {cell, edge} rows and {kite/At, dc*sign/At}
    const int *ACellEdge;     // [C][6] edge row, boundary slot when none
-   const double2 *ACellCf;   // [C][6] {0.25 dv dc / A, dv sign / A}
+   const Real2 *ACellCf;   // [C][6] {0.25 dv dc / A, dv sign / A}
    const int2 *AVertIdx;     // [V][3] {cell, edge}
-   const double2 *AVertCf;   // [V][3] {kite / At, dc sign / At}
-   const double2 *B2CellCf, *B2VertCf;
-   const double2 *B3CellCf, *B3VertCf;
+   const Real2 *AVertCf;   // [V][3] {kite / At, dc sign / At}
+   const Real2 *B2CellCf, *B2VertCf;
+   const Real2 *B3CellCf, *B3VertCf;
    DTiles Tiles; // NTiles == 0 when the mesh has cells with more than 6 edges
 };
 
@@ -143,10 +144,10 @@ inline int n_all(const OmegaMesh *M, int Elem) {
 
 // ---- kernels_aux.cu / kernels_tend.cu / kernels_update.cu launchers --------
 struct AuxPtrs {
-   double *KE, *Div, *Flux, *Mean, *Ssh, *RelVort, *NormRelVort, *NormPlanetVort, *NormRelVortEdge,
+   Real *KE, *Div, *Flux, *Mean, *Ssh, *RelVort, *NormRelVort, *NormPlanetVort, *NormRelVortEdge,
        *NormPlanetVortEdge, *Del2Edge, *Del2Div, *Del2RelVort, *HTr, *Del2Tr, *NormalStress,
        *ZonalStress, *MeridStress;
-   double *ZonalStress2; // [NCellsSize] scratch of the fused path: kinetic energy of the bottom layer (bottom drag)
+   Real *ZonalStress2; // [NCellsSize] scratch of the fused path: kinetic energy of the bottom layer (bottom drag)
 };
 
 struct Launch {
@@ -154,50 +155,50 @@ struct Launch {
    long long *Count; // launch counter of the owning stepper
 };
 
-void launch_vertex_aux1(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A);
-void launch_cell_aux1(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A);
+void launch_vertex_aux1(const Launch &L, const DMesh &M, const Real *H, const Real *U, const AuxPtrs &A);
+void launch_cell_aux1(const Launch &L, const DMesh &M, const Real *H, const Real *U, const AuxPtrs &A);
 void launch_wind_aux(const Launch &L, const DMesh &M, const AuxPtrs &A, int Aniso);
-void launch_edge_aux2(const Launch &L, const DMesh &M, const double *H, const double *U, const AuxPtrs &A,
+void launch_edge_aux2(const Launch &L, const DMesh &M, const Real *H, const Real *U, const AuxPtrs &A,
                       int FluxUpwind, int ThickOnly);
 void launch_vertex_aux2(const Launch &L, const DMesh &M, const AuxPtrs &A);
 void launch_cell_aux2(const Launch &L, const DMesh &M, const AuxPtrs &A);
-void launch_tracer_aux_edge(const Launch &L, const DMesh &M, const double *H, const double *U,
-                            const double *Tr, int NTracers, const AuxPtrs &A, int Upwind);
-void launch_tracer_aux_cell(const Launch &L, const DMesh &M, const double *Tr, int NTracers,
+void launch_tracer_aux_edge(const Launch &L, const DMesh &M, const Real *H, const Real *U,
+                            const Real *Tr, int NTracers, const AuxPtrs &A, int Upwind);
+void launch_tracer_aux_cell(const Launch &L, const DMesh &M, const Real *Tr, int NTracers,
                             const AuxPtrs &A);
 
 struct ManufacturedParams {
    int Enabled;
-   double H0, Eta0, Kx, Ky, AngFreq, Time;
+   Real H0, Eta0, Kx, Ky, AngFreq, Time;
 };
 
 void launch_thick_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                       const double *U, double *HTend, const ManufacturedParams &MS);
+                       const Real *U, Real *HTend, const ManufacturedParams &MS);
 void launch_vel_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                     const double *U, const double *URaw, double *UTend, const ManufacturedParams &MS);
+                     const Real *U, const Real *URaw, Real *UTend, const ManufacturedParams &MS);
 void launch_tracer_tend(const Launch &L, const DMesh &M, const OmegaTendConfig &G, const AuxPtrs &A,
-                        const double *URaw, const double *Tr, int NTracers, double *TrTend);
+                        const Real *URaw, const Real *Tr, int NTracers, Real *TrTend);
 
 // Y1 = Y2 + c*T over rows [0,NAll)
-void launch_axpy(const Launch &L, int NAll, int K, double *Y1, const double *Y2, double C, const double *T);
+void launch_axpy(const Launch &L, int NAll, int K, Real *Y1, const Real *Y2, Real C, const Real *T);
 // Next = (Cur*H2 + c*T)/H1 ; Next = Cur*H ; Accum += c*T ; Next /= H   (all tracers)
-void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                           const double *Cur, const double *H1, const double *H2, double C, const double *T);
-void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                           const double *Cur, const double *H);
-void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Accum,
-                               double C, const double *T);
-void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, double *Next,
-                             const double *H);
+void launch_update_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                           const Real *Cur, const Real *H1, const Real *H2, Real C, const Real *T);
+void launch_weight_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                           const Real *Cur, const Real *H);
+void launch_accumulate_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Accum,
+                               Real C, const Real *T);
+void launch_finalize_tracers(const Launch &L, int NAll, int NSize, int K, int NTracers, Real *Next,
+                             const Real *H);
 
 // one slab of host rows of a field between a contiguous staging block and the device-order array
-void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, double *Dev,
-                      double *Stage);
+void launch_slab_rows(cudaStream_t S, bool ToDevice, int Row0, int NSlab, int NInner, const int *DevRowOfHost, Real *Dev,
+                      Real *Stage);
 // the whole field between pinned host memory and the device-order array, no staging
-void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, double *Dev,
-                         double *Host, int NCtas);
+void launch_rows_hostmem(cudaStream_t S, bool ToDevice, int NOuter, int NRows, int NInner, const int *DevRowOfHost, Real *Dev,
+                         Real *Host, int NCtas);
 // gather/scatter rows through a permutation (field transfer, halo)
 void launch_permute_rows(cudaStream_t S, int NOuter, int NRows, int NInner, const int *SrcRowOfDst,
-                         const double *Src, double *Dst);
+                         const Real *Src, Real *Dst);
 
 } // namespace omega

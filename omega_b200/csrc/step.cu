@@ -17,12 +17,12 @@ inline int time_index(int Level, int Cur, int NTL) { return (Level + Cur + NTL) 
 // One OceanState as the steppers see it: ring-mapped getters and the raw
 // vector indexing several reference call sites use.
 struct StateView {
-   double *const *H, *const *U;
+   Real *const *H, *const *U;
    int NTL, Cur;
-   double *h(int Level) const { return H[time_index(Level, Cur, NTL)]; }
-   double *u(int Level) const { return U[time_index(Level, Cur, NTL)]; }
-   double *hraw(int Level, int Compat) const { return Compat ? H[Level] : h(Level); }
-   double *uraw(int Level, int Compat) const { return Compat ? U[Level] : u(Level); }
+   Real *h(int Level) const { return H[time_index(Level, Cur, NTL)]; }
+   Real *u(int Level) const { return U[time_index(Level, Cur, NTL)]; }
+   Real *hraw(int Level, int Compat) const { return Compat ? H[Level] : h(Level); }
+   Real *uraw(int Level, int Compat) const { return Compat ? U[Level] : u(Level); }
 };
 
 struct Ctx {
@@ -31,16 +31,16 @@ struct Ctx {
    int Compat;
    const DMesh &D() const { return S->M->D; }
    Launch L() const { return Launch{St, &S->Launches}; }
-   void update_thick(double *H1, const double *H2, double C) const {
+   void update_thick(Real *H1, const Real *H2, Real C) const {
       launch_axpy(L(), D().NCellsAll, D().K, H1, H2, C, S->T.LayerThicknessTend);
    }
-   void update_vel(double *U1, const double *U2, double C) const {
+   void update_vel(Real *U1, const Real *U2, Real C) const {
       launch_axpy(L(), D().NEdgesAll, D().K, U1, U2, C, S->T.NormalVelocityTend);
    }
-   void update_tracers(double *Next, const double *Cur, const double *H1, const double *H2, double C) const {
+   void update_tracers(Real *Next, const Real *Cur, const Real *H1, const Real *H2, Real C) const {
       launch_update_tracers(L(), D().NCellsAll, D().NCellsSize, D().K, S->NTracers, Next, Cur, H1, H2, C, S->T.TracerTend);
    }
-   int all_tend(const StateView &V, const double *Tr, int TL, int VL, double Time) const {
+   int all_tend(const StateView &V, const Real *Tr, int TL, int VL, Real Time) const {
       return omega_tend_all(S, V.h(TL), V.u(VL), V.uraw(VL, Compat), Tr, Time, St);
    }
 };
@@ -49,12 +49,12 @@ int rk4_phase(const Ctx &X, OmegaStateArrays *A, const OmegaStepCoeffs *C, int P
    OmegaStepper *S = X.S;
    const DMesh &D  = X.D();
    StateView St{A->LayerThickness, A->NormalVelocity, A->NTimeLevels, A->CurTimeIndex};
-   double *PH[1] = {S->P.H[0]}, *PU[1] = {S->P.U[0]};
+   Real *PH[1] = {S->P.H[0]}, *PU[1] = {S->P.U[0]};
    StateView Pv{PH, PU, 1, 0};
    const int Cur = 0, Next = 1, Compat = X.Compat;
-   double *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
-   double *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
-   double *PTr    = S->P.Tr[0];
+   Real *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *PTr    = S->P.Tr[0];
    const int s0 = Phase == 0 ? 0 : 2, s1 = Phase == 0 ? 2 : 3;
    for (int Stage = s0; Stage <= s1; ++Stage) {
       if (Stage == 0) {
@@ -83,8 +83,8 @@ int rk4_phase(const Ctx &X, OmegaStateArrays *A, const OmegaStepCoeffs *C, int P
 int rk2_phase(const Ctx &X, OmegaStateArrays *A, const OmegaStepCoeffs *C) {
    StateView St{A->LayerThickness, A->NormalVelocity, A->NTimeLevels, A->CurTimeIndex};
    const int Cur = 0, Next = 1, Compat = X.Compat;
-   double *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
-   double *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
    if (X.all_tend(St, CurTr, Cur, Cur, C->StageTime[0])) return 1;
    X.update_thick(St.h(Next), St.h(Cur), C->A[1]);
    X.update_vel(St.u(Next), St.u(Cur), C->A[1]);
@@ -100,8 +100,8 @@ int fb_phase(const Ctx &X, OmegaStateArrays *A, const OmegaStepCoeffs *C) {
    OmegaStepper *S = X.S;
    StateView St{A->LayerThickness, A->NormalVelocity, A->NTimeLevels, A->CurTimeIndex};
    const int Cur = 0, Next = 1, Compat = X.Compat;
-   double *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
-   double *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *CurTr  = A->Tracers[time_index(Cur, A->TracerCurTimeIndex, A->NTimeLevels)];
+   Real *NextTr = A->Tracers[time_index(Next, A->TracerCurTimeIndex, A->NTimeLevels)];
    if (omega_tend_thickness(S, St.h(Cur), St.u(Cur), C->StageTime[0], X.St)) return 1;
    X.update_thick(St.h(Next), St.h(Cur), C->Dt);
    if (S->NTracers) {
@@ -147,7 +147,7 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
 }
 
 int omega_stepper_exchange_list(OmegaStepper *S, OmegaStepperType Type, const OmegaStateArrays *X, int Phase,
-                                double **Ptrs, int *Elems, int *NOuter, int *NArrays) {
+                                Real **Ptrs, int *Elems, int *NOuter, int *NArrays) {
    OMEGA_REQUIRE(S && X && Ptrs && Elems && NOuter && NArrays, "omega_stepper_exchange_list: null argument");
    if (Type == OMEGA_STEPPER_RK4 && Phase == 0) {
       const int b = S->ProvisExchangeSlot;
@@ -193,7 +193,7 @@ int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArra
       int rc = omega_stepper_step_phase(S, Type, State, Coeffs, p, Fused, RawTimeLevelCompat, Stream);
       if (rc) return rc;
       if (!Halo) continue;
-      double *ptrs[3];
+      Real *ptrs[3];
       int elems[3], nouter[3], n = 0;
       rc = omega_stepper_exchange_list(S, Type, State, p, ptrs, elems, nouter, &n);
       if (rc) return rc;

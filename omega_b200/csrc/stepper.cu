@@ -13,16 +13,16 @@ using namespace omega;
 
 namespace omega {
 
-int stepper_alloc(OmegaStepper *S, double **p, size_t n) {
+int stepper_alloc(OmegaStepper *S, Real **p, size_t n) {
    void *d = nullptr;
-   const size_t bytes = (n ? n : 2) * sizeof(double);
+   const size_t bytes = (n ? n : 2) * sizeof(Real);
    OMEGA_CUDA_CHECK(cudaMalloc(&d, bytes));
    // the memset runs on the legacy default stream, which callers' non-blocking streams do not
    // synchronise with: wait for it here so no later kernel can race with it (allocations are rare)
    OMEGA_CUDA_CHECK(cudaMemset(d, 0, bytes));
    OMEGA_CUDA_CHECK(cudaStreamSynchronize(0));
    S->Allocs.push_back(d);
-   *p = (double *)d;
+   *p = (Real *)d;
    return 0;
 }
 
@@ -32,7 +32,7 @@ ManufacturedParams manufactured(const OmegaStepper *S, double Time) {
    std::memset(&P, 0, sizeof(P));
    P.Enabled = S->Cfg.ManufacturedSolutionTendency;
    if (!P.Enabled) return P;
-   const double Grav = 9.80665, Pii = 3.141592653589793;
+   const Real Grav = 9.80665, Pii = 3.141592653589793;
    P.H0      = S->BottomDepth0;
    P.Eta0    = S->Cfg.ManufacturedAmplitude;
    P.Kx      = 2.0 * Pii / S->Cfg.ManufacturedWavelengthX;
@@ -105,9 +105,9 @@ int omega_stepper_create(const OmegaMesh *Mesh, const OmegaTendConfig *Cfg, int 
       return 1;
    }
    // BottomDepthH(0) of the HOST-order mesh (CustomTendencyTerms.cpp:80)
-   double b0 = 0;
+   Real b0 = 0;
    const int dev_row_of_host0 = Mesh->IPerm[0][0];
-   OMEGA_CUDA_CHECK(cudaMemcpy(&b0, D.BottomDepth + dev_row_of_host0, sizeof(double), cudaMemcpyDeviceToHost));
+   OMEGA_CUDA_CHECK(cudaMemcpy(&b0, D.BottomDepth + dev_row_of_host0, sizeof(Real), cudaMemcpyDeviceToHost));
    S->BottomDepth0 = b0;
    *Out = S;
    return 0;
@@ -148,13 +148,13 @@ int omega_stepper_tend_arrays(OmegaStepper *S, OmegaTendArrays *Tend) {
    return 0;
 }
 
-int omega_stepper_provis_arrays(OmegaStepper *S, double **H, double **U, double **Tr) {
+int omega_stepper_provis_arrays(OmegaStepper *S, Real **H, Real **U, Real **Tr) {
    OMEGA_REQUIRE(S, "omega_stepper_provis_arrays: null argument");
    *H = S->P.H[0]; *U = S->P.U[0]; *Tr = S->P.Tr[0];
    return 0;
 }
 
-int omega_stepper_set_wind_stress(OmegaStepper *S, const double *Zonal, const double *Merid, void *Stream) {
+int omega_stepper_set_wind_stress(OmegaStepper *S, const Real *Zonal, const Real *Merid, void *Stream) {
    OMEGA_REQUIRE(S && Zonal && Merid, "omega_stepper_set_wind_stress: null argument");
    int rc = omega_field_to_device(S->M, OMEGA_ON_CELL, 1, 1, Zonal, S->A.ZonalStress, Stream);
    rc |= omega_field_to_device(S->M, OMEGA_ON_CELL, 1, 1, Merid, S->A.MeridStress, Stream);
@@ -195,7 +195,7 @@ int omega_stepper_get_profile(OmegaStepper *S, double *Ms, int *Counts, int NKin
 }
 
 // ---- AuxiliaryState ---------------------------------------------------------
-int omega_aux_compute_mom(OmegaStepper *S, const double *H, const double *U, void *Stream) {
+int omega_aux_compute_mom(OmegaStepper *S, const Real *H, const Real *U, void *Stream) {
    OMEGA_REQUIRE(S && H && U, "omega_aux_compute_mom: null argument");
    const DMesh &D = S->M->D;
    Launch L{(cudaStream_t)Stream, &S->Launches};
@@ -210,7 +210,7 @@ int omega_aux_compute_mom(OmegaStepper *S, const double *H, const double *U, voi
    return 0;
 }
 
-static int tracer_aux(OmegaStepper *S, const double *H, const double *U, const double *Tr, cudaStream_t St) {
+static int tracer_aux(OmegaStepper *S, const Real *H, const Real *U, const Real *Tr, cudaStream_t St) {
    if (S->NTracers == 0) return 0;
    if (ensure_htr(S)) return 1;
    Launch L{St, &S->Launches};
@@ -220,7 +220,7 @@ static int tracer_aux(OmegaStepper *S, const double *H, const double *U, const d
    return 0;
 }
 
-int omega_aux_compute_all(OmegaStepper *S, const double *H, const double *U, const double *Tr, void *Stream) {
+int omega_aux_compute_all(OmegaStepper *S, const Real *H, const Real *U, const Real *Tr, void *Stream) {
    OMEGA_REQUIRE(S && H && U && (Tr || S->NTracers == 0), "omega_aux_compute_all: null argument");
    int rc = omega_aux_compute_mom(S, H, U, Stream);
    if (rc) return rc;
@@ -228,7 +228,7 @@ int omega_aux_compute_all(OmegaStepper *S, const double *H, const double *U, con
 }
 
 // ---- Tendencies ---------------------------------------------------------------
-int omega_tend_thickness_only(OmegaStepper *S, const double *U, double Time, void *Stream) {
+int omega_tend_thickness_only(OmegaStepper *S, const Real *U, double Time, void *Stream) {
    OMEGA_REQUIRE(S && U, "omega_tend_thickness_only: null argument");
    Launch L{(cudaStream_t)Stream, &S->Launches};
    launch_thick_tend(L, S->M->D, S->Cfg, S->A, U, S->T.LayerThicknessTend, manufactured(S, Time));
@@ -236,7 +236,7 @@ int omega_tend_thickness_only(OmegaStepper *S, const double *U, double Time, voi
    return 0;
 }
 
-int omega_tend_velocity_only(OmegaStepper *S, const double *U, const double *URaw, double Time, void *Stream) {
+int omega_tend_velocity_only(OmegaStepper *S, const Real *U, const Real *URaw, double Time, void *Stream) {
    OMEGA_REQUIRE(S && U && URaw, "omega_tend_velocity_only: null argument");
    Launch L{(cudaStream_t)Stream, &S->Launches};
    launch_vel_tend(L, S->M->D, S->Cfg, S->A, U, URaw, S->T.NormalVelocityTend, manufactured(S, Time));
@@ -244,7 +244,7 @@ int omega_tend_velocity_only(OmegaStepper *S, const double *U, const double *URa
    return 0;
 }
 
-int omega_tend_tracer_only(OmegaStepper *S, const double *URaw, const double *Tr, void *Stream) {
+int omega_tend_tracer_only(OmegaStepper *S, const Real *URaw, const Real *Tr, void *Stream) {
    OMEGA_REQUIRE(S && URaw && (Tr || S->NTracers == 0), "omega_tend_tracer_only: null argument");
    if (S->NTracers == 0) return 0;
    if (ensure_htr(S)) return 1;
@@ -254,28 +254,28 @@ int omega_tend_tracer_only(OmegaStepper *S, const double *URaw, const double *Tr
    return 0;
 }
 
-int omega_tend_thickness(OmegaStepper *S, const double *H, const double *U, double Time, void *Stream) {
+int omega_tend_thickness(OmegaStepper *S, const Real *H, const Real *U, double Time, void *Stream) {
    OMEGA_REQUIRE(S && H && U, "omega_tend_thickness: null argument");
    Launch L{(cudaStream_t)Stream, &S->Launches};
    launch_edge_aux2(L, S->M->D, H, U, S->A, S->Cfg.FluxThicknessType, 1);
    return omega_tend_thickness_only(S, U, Time, Stream);
 }
 
-int omega_tend_velocity(OmegaStepper *S, const double *H, const double *U, const double *URaw, double Time,
+int omega_tend_velocity(OmegaStepper *S, const Real *H, const Real *U, const Real *URaw, double Time,
                         void *Stream) {
    int rc = omega_aux_compute_mom(S, H, U, Stream);
    if (rc) return rc;
    return omega_tend_velocity_only(S, U, URaw, Time, Stream);
 }
 
-int omega_tend_tracer(OmegaStepper *S, const double *HRaw, const double *URaw, const double *Tr, void *Stream) {
+int omega_tend_tracer(OmegaStepper *S, const Real *HRaw, const Real *URaw, const Real *Tr, void *Stream) {
    OMEGA_REQUIRE(S && HRaw && URaw, "omega_tend_tracer: null argument");
    int rc = tracer_aux(S, HRaw, URaw, Tr, (cudaStream_t)Stream);
    if (rc) return rc;
    return omega_tend_tracer_only(S, URaw, Tr, Stream);
 }
 
-int omega_tend_all(OmegaStepper *S, const double *H, const double *U, const double *URaw, const double *Tr,
+int omega_tend_all(OmegaStepper *S, const Real *H, const Real *U, const Real *URaw, const Real *Tr,
                    double Time, void *Stream) {
    int rc = omega_aux_compute_all(S, H, U, Tr, Stream);
    if (rc) return rc;

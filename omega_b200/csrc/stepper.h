@@ -7,19 +7,19 @@
 struct OmegaHalo;
 
 struct ProvisArrays {
-   double *H[2], *U[2], *Tr[2];
+   omega::Real *H[2], *U[2], *Tr[2];
 };
 
 struct OmegaStepper {
    const OmegaMesh *M;
    OmegaTendConfig Cfg;
    int NTracers;
-   double BottomDepth0;
+   omega::Real BottomDepth0;
    omega::AuxPtrs A;
    OmegaTendArrays T;
    ProvisArrays P;
-   double *SrcH, *SrcU; // manufactured sources per cell / edge of the current stage (fused tiled path)
-   double *RTop, *RBot; // wind / bottom-drag tendency of the top / bottom layer per edge (k_edge_layer_terms)
+   omega::Real *SrcH, *SrcU; // manufactured sources per cell / edge of the current stage (fused tiled path)
+   omega::Real *RTop, *RBot; // wind / bottom-drag tendency of the top / bottom layer per edge (k_edge_layer_terms)
    long long Launches;
    int ProvisExchangeSlot; // which P.*[i] holds the stage-2 provisional state to exchange
    int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
@@ -34,7 +34,7 @@ struct OmegaStepper {
 
 namespace omega {
 enum FusedKernel { kFA = 0, kFB = 1, kFT2 = 2, kFC = 3, kFE = 4, kNumFused = 5 };
-int stepper_alloc(OmegaStepper *S, double **p, size_t n);
+int stepper_alloc(OmegaStepper *S, omega::Real **p, size_t n);
 ManufacturedParams manufactured(const OmegaStepper *S, double Time);
 int ensure_htr(OmegaStepper *S);
 // fused.cu: one phase of RK4 / RK2 / forward-backward on the fused per-stage pipeline

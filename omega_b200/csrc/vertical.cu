@@ -16,17 +16,17 @@
 
 namespace omega {
 
-constexpr double kGravityVert = 9.80616; // VertCoord.cpp:659 (not the 9.80665 of the tendency terms)
+constexpr Real kGravityVert = 9.80616; // VertCoord.cpp:659 (not the 9.80665 of the tendency terms)
 
-__device__ __forceinline__ double warp_scan_incl(double v, int lane) {
+__device__ __forceinline__ Real warp_scan_incl(Real v, int lane) {
 #pragma unroll
    for (int d = 1; d < 32; d <<= 1) {
-      const double t = __shfl_up_sync(0xffffffffu, v, d);
+      const Real t = __shfl_up_sync(0xffffffffu, v, d);
       if (lane >= d) v += t;
    }
    return v;
 }
-__device__ __forceinline__ double warp_sum(double v) {
+__device__ __forceinline__ Real warp_sum(Real v) {
 #pragma unroll
    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
    return v;
@@ -35,18 +35,18 @@ __device__ __forceinline__ double warp_sum(double v) {
 // PressureInterface(i, KMin) = SurfacePressure(i); going down: + Gravity * Rho0 * h(i, k)  (VertCoord.cpp:652-690)
 __global__ void __launch_bounds__(kBlock)
 k_vert_pressure(int NCells, int K, const int *__restrict__ KMinC, const int *__restrict__ KMaxC, double Rho0,
-                const double *__restrict__ H, const double *__restrict__ SurfP, double *__restrict__ PInt,
-                double *__restrict__ PMid) {
+                const Real *__restrict__ H, const Real *__restrict__ SurfP, Real *__restrict__ PInt,
+                Real *__restrict__ PMid) {
    const int cell = (int)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
    if (cell >= NCells) return;
    const int kmin = KMinC[cell], kmax = KMaxC[cell];
-   const double p0 = SurfP[cell];
+   const Real p0 = SurfP[cell];
    if (lane == 0) PInt[(size_t)cell * (K + 1) + kmin] = p0;
-   double carry = 0.0;
+   Real carry = 0.0;
    for (int k0 = kmin; k0 <= kmax; k0 += 32) {
       const int k = k0 + lane;
-      const double inc = k <= kmax ? kGravityVert * Rho0 * H[(size_t)cell * K + k] : 0.0;
-      const double acc = carry + warp_scan_incl(inc, lane);
+      const Real inc = k <= kmax ? kGravityVert * Rho0 * H[(size_t)cell * K + k] : 0.0;
+      const Real acc = carry + warp_scan_incl(inc, lane);
       if (k <= kmax) {
          PInt[(size_t)cell * (K + 1) + k + 1] = p0 + acc;
          PMid[(size_t)cell * K + k]           = p0 + acc - 0.5 * inc;
@@ -58,19 +58,19 @@ k_vert_pressure(int NCells, int K, const int *__restrict__ KMinC, const int *__r
 // ZInterface(i, KMax+1) = -BottomDepth(i); going up: + Rho0 * SpecVol * h  (VertCoord.cpp:697-735)
 __global__ void __launch_bounds__(kBlock)
 k_vert_zheight(int NCells, int K, const int *__restrict__ KMinC, const int *__restrict__ KMaxC, double Rho0,
-               const double *__restrict__ BottomDepth, const double *__restrict__ H, const double *__restrict__ SpecVol,
-               double *__restrict__ ZInt, double *__restrict__ ZMid) {
+               const Real *__restrict__ BottomDepth, const Real *__restrict__ H, const Real *__restrict__ SpecVol,
+               Real *__restrict__ ZInt, Real *__restrict__ ZMid) {
    const int cell = (int)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
    if (cell >= NCells) return;
    const int kmin = KMinC[cell], kmax = KMaxC[cell];
-   const double zb = -BottomDepth[cell];
+   const Real zb = -BottomDepth[cell];
    if (lane == 0) ZInt[(size_t)cell * (K + 1) + kmax + 1] = zb;
-   double carry = 0.0;
+   Real carry = 0.0;
    for (int k0 = kmax; k0 >= kmin; k0 -= 32) {
       const int k = k0 - lane;
       const size_t o = (size_t)cell * K + (k >= kmin ? k : kmin);
-      const double dz = k >= kmin ? Rho0 * SpecVol[o] * H[o] : 0.0;
-      const double acc = carry + warp_scan_incl(dz, lane);
+      const Real dz = k >= kmin ? Rho0 * SpecVol[o] * H[o] : 0.0;
+      const Real acc = carry + warp_scan_incl(dz, lane);
       if (k >= kmin) {
          ZInt[(size_t)cell * (K + 1) + k] = zb + acc;
          ZMid[o]                          = zb + acc - 0.5 * dz;
@@ -82,8 +82,8 @@ k_vert_zheight(int NCells, int K, const int *__restrict__ KMinC, const int *__re
 // GeopotentialMid = Gravity * ZMid + TidalPotential + SelfAttractionLoading on the active layers (VertCoord.cpp:742-778)
 __global__ void __launch_bounds__(kBlock)
 k_vert_geopotential(int NCells, int K, const int *__restrict__ KMinC, const int *__restrict__ KMaxC,
-                    const double *__restrict__ ZMid, const double *__restrict__ Tidal, const double *__restrict__ Sal,
-                    double *__restrict__ Geop) {
+                    const Real *__restrict__ ZMid, const Real *__restrict__ Tidal, const Real *__restrict__ Sal,
+                    Real *__restrict__ Geop) {
    const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    if (w >= (long long)NCells * K) return;
    const int cell = (int)(w / K), k = (int)(w - (long long)cell * K);
@@ -95,20 +95,20 @@ k_vert_geopotential(int NCells, int K, const int *__restrict__ KMinC, const int 
 // minus the reference column height (VertCoord.cpp:786-851)
 __global__ void __launch_bounds__(kBlock)
 k_vert_target(int NCells, int K, const int *__restrict__ KMinC, const int *__restrict__ KMaxC, double Rho0,
-              const double *__restrict__ PInt, const double *__restrict__ RefH, const double *__restrict__ Wgt,
-              double *__restrict__ Target) {
+              const Real *__restrict__ PInt, const Real *__restrict__ RefH, const Real *__restrict__ Wgt,
+              Real *__restrict__ Target) {
    const int cell = (int)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
    if (cell >= NCells) return;
    const int kmin = KMinC[cell], kmax = KMaxC[cell];
-   double swh = 0.0, sref = 0.0;
+   Real swh = 0.0, sref = 0.0;
    for (int k = kmin + lane; k <= kmax; k += 32) {
-      const double r = RefH[(size_t)cell * K + k];
+      const Real r = RefH[(size_t)cell * K + k];
       swh += Wgt[k] * r;
       sref += r;
    }
    swh = warp_sum(swh);
    sref = warp_sum(sref);
-   const double coeff = (PInt[(size_t)cell * (K + 1) + kmax + 1] - PInt[(size_t)cell * (K + 1) + kmin]) / (kGravityVert * Rho0) - sref;
+   const Real coeff = (PInt[(size_t)cell * (K + 1) + kmax + 1] - PInt[(size_t)cell * (K + 1) + kmin]) / (kGravityVert * Rho0) - sref;
    for (int k = kmin + lane; k <= kmax; k += 32)
       Target[(size_t)cell * K + k] = RefH[(size_t)cell * K + k] * (1.0 + coeff * Wgt[k] / swh);
 }
@@ -119,7 +119,7 @@ k_vert_target(int NCells, int K, const int *__restrict__ KMinC, const int *__res
 // s = sqrt((SA + 24) / SAu), t = CT / 40, p = P / 1e4; delta = sum V_ijk s^i t^j p^k over i + j + k <= 6.
 // The 75 published coefficients V_ijk, stored [k][j][i] (missing entries 0) and evaluated by nested Horner in the
 // same order as Eos.h:51-189 (s innermost, then t, then p).
-__constant__ double cTeosV[6][7][7] = {
+__constant__ Real cTeosV[6][7][7] = {
     // k = 0
     {{1.0769995862e-03, -3.1038981976e-04, 6.6928067038e-04, -8.5047933937e-04, 5.8086069943e-04, -2.1092370507e-04, 3.1932457305e-05},
      {-1.5649734675e-05, 3.5009599764e-05, -4.3592678561e-05, 3.4532461828e-05, -1.1959409788e-05, 1.3864594581e-06, 0},
@@ -157,27 +157,27 @@ __constant__ double cTeosV[6][7][7] = {
     {{4.2369007180e-09, 0, 0, 0, 0, 0, 0},
      {0, 0, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 0, 0}}};
 // reference profile v0(p) = p (V00 + p (V01 + ...)), Eos.h:207-220
-__constant__ double cTeosV0[6] = {-4.4015007269e-05, 6.9232335784e-06, -7.5004675975e-07, 1.7009109288e-08, -1.6884162004e-08, 1.9613503930e-09};
+__constant__ Real cTeosV0[6] = {-4.4015007269e-05, 6.9232335784e-06, -7.5004675975e-07, 1.7009109288e-08, -1.6884162004e-08, 1.9613503930e-09};
 
-__device__ __forceinline__ double teos10_specvol(double Sa, double Ct, double P) {
-   const double ss = sqrt((Sa + 24.0) / (40.0 * 35.16504 / 35.0)), tt = Ct / 40.0, pp = P / 1.0e4;
+__device__ __forceinline__ Real teos10_specvol(Real Sa, Real Ct, Real P) {
+   const Real ss = sqrt((Sa + 24.0) / (40.0 * 35.16504 / 35.0)), tt = Ct / 40.0, pp = P / 1.0e4;
    // pressure coefficient k: polynomial in (s, t) of total degree 6 - k; Horner in t, and per step the s-part of
    // the coefficient first and its constant last -- the association of Eos.h:141-189
-   double delta = 0.0;
+   Real delta = 0.0;
 #pragma unroll
    for (int k = 5; k >= 0; --k) {
-      double ck = cTeosV[k][6 - k][0];
+      Real ck = cTeosV[k][6 - k][0];
 #pragma unroll
       for (int j = 5 - k; j >= 0; --j) {
          const int n = 6 - k - j;
-         double hs = cTeosV[k][j][n];
+         Real hs = cTeosV[k][j][n];
 #pragma unroll
          for (int i = n - 1; i >= 1; --i) hs = hs * ss + cTeosV[k][j][i];
          ck = ck * tt + hs * ss + cTeosV[k][j][0];
       }
       delta = delta * pp + ck;
    }
-   double v0 = 0.0;
+   Real v0 = 0.0;
 #pragma unroll
    for (int k = 5; k >= 0; --k) v0 = v0 * pp + cTeosV0[k];
    return v0 * pp + delta;
@@ -187,8 +187,8 @@ __device__ __forceinline__ double teos10_specvol(double Sa, double Ct, double P)
 // of layer clamp(k + KDisp) (Eos.h:36-48, TEOS-10 only; the linear form does not depend on pressure)
 __global__ void __launch_bounds__(kBlock)
 k_eos_specvol(int NCells, int K, int EosType, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
-              const double *__restrict__ Ct, const double *__restrict__ Sa, const double *__restrict__ P,
-              double *__restrict__ SpecVol) {
+              const Real *__restrict__ Ct, const Real *__restrict__ Sa, const Real *__restrict__ P,
+              Real *__restrict__ SpecVol) {
    const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    if (w >= (long long)NCells * K) return;
    if (EosType == 0) {
@@ -205,10 +205,10 @@ k_eos_specvol(int NCells, int K, int EosType, int KDisp, double DRhodT, double D
 // DL(k) x(k-1) + D(k) x(k) + DU(k) x(k+1) = X(k).  Each reduction step eliminates the couplings at distance s and
 // doubles s; after ceil(log2 NRow) steps every row stands alone.  Diffusion form (TriDiagSolvers.h:210-330): the
 // system of an implicit vertical diffusion step, DL(k) = -G(k-1), DU(k) = -G(k), D(k) = H(k) + G(k-1) + G(k).
-__global__ void k_tridiag_pcr(int NRow, const double *__restrict__ DL, const double *__restrict__ D,
-                              const double *__restrict__ DU, double *__restrict__ X) {
-   extern __shared__ double sm[];
-   double *a = sm, *b = sm + NRow, *c = sm + 2 * NRow, *d = sm + 3 * NRow;
+__global__ void k_tridiag_pcr(int NRow, const Real *__restrict__ DL, const Real *__restrict__ D,
+                              const Real *__restrict__ DU, Real *__restrict__ X) {
+   extern __shared__ Real sm[];
+   Real *a = sm, *b = sm + NRow, *c = sm + 2 * NRow, *d = sm + 3 * NRow;
    const int k = threadIdx.x;
    const size_t base = (size_t)blockIdx.x * NRow;
    if (k < NRow) {
@@ -219,10 +219,10 @@ __global__ void k_tridiag_pcr(int NRow, const double *__restrict__ DL, const dou
    }
    __syncthreads();
    for (int s = 1; s < NRow; s <<= 1) {
-      double na = 0, nb = 0, nc = 0, nd = 0;
+      Real na = 0, nb = 0, nc = 0, nd = 0;
       if (k < NRow) {
          const int km = k - s, kp = k + s;
-         const double al = km >= 0 ? -a[k] / b[km] : 0.0, ga = kp < NRow ? -c[k] / b[kp] : 0.0;
+         const Real al = km >= 0 ? -a[k] / b[km] : 0.0, ga = kp < NRow ? -c[k] / b[kp] : 0.0;
          nb = b[k] + (km >= 0 ? al * c[km] : 0.0) + (kp < NRow ? ga * a[kp] : 0.0);
          nd = d[k] + (km >= 0 ? al * d[km] : 0.0) + (kp < NRow ? ga * d[kp] : 0.0);
          na = km >= 0 ? al * a[km] : 0.0;
@@ -240,9 +240,9 @@ __global__ void k_tridiag_pcr(int NRow, const double *__restrict__ DL, const dou
 //    H'(k) = H(k) + al H(k-s) + be H(k+s),  gm'(k) = al gm(k-s),  gp'(k) = be gp(k+s),  al = gm(k) / D(k-s), be = gp(k) / D(k+s)
 // (no subtraction anywhere), which is what keeps an abrupt 1e14 jump in diffusivity finite where the general form
 // produces NaNs (test/base/TriDiagSolversTest.cpp:428-470).
-__global__ void k_tridiag_diff_pcr(int NRow, const double *__restrict__ G, const double *__restrict__ H, double *__restrict__ X) {
-   extern __shared__ double sm[];
-   double *h = sm, *gm = sm + NRow, *gp = sm + 2 * NRow, *x = sm + 3 * NRow;
+__global__ void k_tridiag_diff_pcr(int NRow, const Real *__restrict__ G, const Real *__restrict__ H, Real *__restrict__ X) {
+   extern __shared__ Real sm[];
+   Real *h = sm, *gm = sm + NRow, *gp = sm + 2 * NRow, *x = sm + 3 * NRow;
    const int k = threadIdx.x;
    const size_t base = (size_t)blockIdx.x * NRow;
    if (k < NRow) {
@@ -253,11 +253,11 @@ __global__ void k_tridiag_diff_pcr(int NRow, const double *__restrict__ G, const
    }
    __syncthreads();
    for (int s = 1; s < NRow; s <<= 1) {
-      double nh = 0, ngm = 0, ngp = 0, nx = 0;
+      Real nh = 0, ngm = 0, ngp = 0, nx = 0;
       if (k < NRow) {
          const int km = k - s, kp = k + s;
-         const double al = km >= 0 ? gm[k] / (h[km] + gm[km] + gp[km]) : 0.0;
-         const double be = kp < NRow ? gp[k] / (h[kp] + gm[kp] + gp[kp]) : 0.0;
+         const Real al = km >= 0 ? gm[k] / (h[km] + gm[km] + gp[km]) : 0.0;
+         const Real be = kp < NRow ? gp[k] / (h[kp] + gm[kp] + gp[kp]) : 0.0;
          nh  = h[k] + (km >= 0 ? al * h[km] : 0.0) + (kp < NRow ? be * h[kp] : 0.0);
          nx  = x[k] + (km >= 0 ? al * x[km] : 0.0) + (kp < NRow ? be * x[kp] : 0.0);
          ngm = km >= 0 ? al * gm[km] : 0.0;
@@ -277,8 +277,8 @@ using namespace omega;
 extern "C" {
 
 int omega_vert_compute_pressure(const OmegaMesh *M, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
-                                const double *LayerThickness, const double *SurfacePressure, double *PressureInterface,
-                                double *PressureMid, void *Stream) {
+                                const Real *LayerThickness, const Real *SurfacePressure, Real *PressureInterface,
+                                Real *PressureMid, void *Stream) {
    OMEGA_REQUIRE(M && MinLayerCell && MaxLayerCell && LayerThickness && SurfacePressure && PressureInterface && PressureMid,
                  "omega_vert_compute_pressure: null argument");
    const int n = M->D.NCellsAll;
@@ -289,7 +289,7 @@ int omega_vert_compute_pressure(const OmegaMesh *M, const int *MinLayerCell, con
 }
 
 int omega_vert_compute_z_height(const OmegaMesh *M, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
-                                const double *LayerThickness, const double *SpecVol, double *ZInterface, double *ZMid,
+                                const Real *LayerThickness, const Real *SpecVol, Real *ZInterface, Real *ZMid,
                                 void *Stream) {
    OMEGA_REQUIRE(M && MinLayerCell && MaxLayerCell && LayerThickness && SpecVol && ZInterface && ZMid,
                  "omega_vert_compute_z_height: null argument");
@@ -300,9 +300,9 @@ int omega_vert_compute_z_height(const OmegaMesh *M, const int *MinLayerCell, con
    return 0;
 }
 
-int omega_vert_compute_geopotential(const OmegaMesh *M, const int *MinLayerCell, const int *MaxLayerCell, const double *ZMid,
-                                    const double *TidalPotential, const double *SelfAttractionLoading,
-                                    double *GeopotentialMid, void *Stream) {
+int omega_vert_compute_geopotential(const OmegaMesh *M, const int *MinLayerCell, const int *MaxLayerCell, const Real *ZMid,
+                                    const Real *TidalPotential, const Real *SelfAttractionLoading,
+                                    Real *GeopotentialMid, void *Stream) {
    OMEGA_REQUIRE(M && MinLayerCell && MaxLayerCell && ZMid && TidalPotential && SelfAttractionLoading && GeopotentialMid,
                  "omega_vert_compute_geopotential: null argument");
    const long long n = (long long)M->D.NCellsAll * M->D.K;
@@ -313,8 +313,8 @@ int omega_vert_compute_geopotential(const OmegaMesh *M, const int *MinLayerCell,
 }
 
 int omega_vert_compute_target_thickness(const OmegaMesh *M, const int *MinLayerCell, const int *MaxLayerCell, double Rho0,
-                                        const double *PressureInterface, const double *RefLayerThickness,
-                                        const double *MovementWeights, double *LayerThicknessTarget, void *Stream) {
+                                        const Real *PressureInterface, const Real *RefLayerThickness,
+                                        const Real *MovementWeights, Real *LayerThicknessTarget, void *Stream) {
    OMEGA_REQUIRE(M && MinLayerCell && MaxLayerCell && PressureInterface && RefLayerThickness && MovementWeights &&
                      LayerThicknessTarget, "omega_vert_compute_target_thickness: null argument");
    const int n = M->D.NCellsAll;
@@ -324,9 +324,9 @@ int omega_vert_compute_target_thickness(const OmegaMesh *M, const int *MinLayerC
    return 0;
 }
 
-int omega_eos_compute_spec_vol(const OmegaMesh *M, int EosType, const double *ConservTemp, const double *AbsSalinity,
-                               const double *Pressure, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
-                               double *SpecVol, void *Stream) {
+int omega_eos_compute_spec_vol(const OmegaMesh *M, int EosType, const Real *ConservTemp, const Real *AbsSalinity,
+                               const Real *Pressure, int KDisp, double DRhodT, double DRhodS, double RhoT0S0,
+                               Real *SpecVol, void *Stream) {
    OMEGA_REQUIRE(M && ConservTemp && AbsSalinity && SpecVol && (EosType == 0 || (EosType == 1 && Pressure)),
                  "omega_eos_compute_spec_vol: bad argument");
    const long long n = (long long)M->D.NCellsAll * M->D.K;
@@ -336,20 +336,20 @@ int omega_eos_compute_spec_vol(const OmegaMesh *M, int EosType, const double *Co
    return 0;
 }
 
-int omega_tridiag_solve(int NBatch, int NRow, const double *DL, const double *D, const double *DU, double *X, void *Stream) {
+int omega_tridiag_solve(int NBatch, int NRow, const Real *DL, const Real *D, const Real *DU, Real *X, void *Stream) {
    OMEGA_REQUIRE(NBatch >= 0 && NRow >= 1 && NRow <= 1024 && DL && D && DU && X, "omega_tridiag_solve: bad argument");
    if (NBatch == 0) return 0;
    const int nt = (NRow + 31) / 32 * 32;
-   k_tridiag_pcr<<<NBatch, nt, 4 * NRow * sizeof(double), (cudaStream_t)Stream>>>(NRow, DL, D, DU, X);
+   k_tridiag_pcr<<<NBatch, nt, 4 * NRow * sizeof(Real), (cudaStream_t)Stream>>>(NRow, DL, D, DU, X);
    OMEGA_CUDA_CHECK(cudaGetLastError());
    return 0;
 }
 
-int omega_tridiag_diffusion_solve(int NBatch, int NRow, const double *G, const double *H, double *X, void *Stream) {
+int omega_tridiag_diffusion_solve(int NBatch, int NRow, const Real *G, const Real *H, Real *X, void *Stream) {
    OMEGA_REQUIRE(NBatch >= 0 && NRow >= 1 && NRow <= 1024 && G && H && X, "omega_tridiag_diffusion_solve: bad argument");
    if (NBatch == 0) return 0;
    const int nt = (NRow + 31) / 32 * 32;
-   k_tridiag_diff_pcr<<<NBatch, nt, 4 * NRow * sizeof(double), (cudaStream_t)Stream>>>(NRow, G, H, X);
+   k_tridiag_diff_pcr<<<NBatch, nt, 4 * NRow * sizeof(Real), (cudaStream_t)Stream>>>(NRow, G, H, X);
    OMEGA_CUDA_CHECK(cudaGetLastError());
    return 0;
 }

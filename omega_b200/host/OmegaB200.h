@@ -22,7 +22,9 @@ namespace OMEGA {
 
 using I4   = int;
 using R8   = double;
-using Real = double;
+using Real = OmegaReal;
+static_assert(sizeof(Real) == sizeof(double), "this mirror header is written for the fp64 build (libomega_b200.so); "
+                                              "the single-precision library is driven through the same C ABI with float arrays");
 
 [[noreturn]] inline void abortError(const std::string &Msg) { // ABORT_ERROR, src/infra/Error.h:207-210
    std::fprintf(stderr, "[omega_b200] %s: %s\n", Msg.c_str(), omega_last_error());

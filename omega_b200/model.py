@@ -38,6 +38,10 @@ class HorzMesh:
         if not torch.cuda.is_available():
             raise RuntimeError("omega_b200 needs a CUDA device; there is no CPU path")
         self.lib = lib or capi.load_library()
+        # Real of the loaded build: fp64, or fp32 for libomega_b200_sp.so (capi.load_library(capi.LIB_PATH_SP))
+        self.real_bytes = int(self.lib.omega_b200_real_bytes())
+        self.dtype = torch.float64 if self.real_bytes == 8 else torch.float32
+        self.np_dtype = np.float64 if self.real_bytes == 8 else np.float32
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         self.L = L
@@ -65,16 +69,16 @@ class HorzMesh:
 
     def alloc(self, kind, nouter=0, levels=True):
         shape = ((nouter,) if nouter else ()) + (self.NSize[kind],) + ((self.K,) if levels else ())
-        return torch.zeros(shape, dtype=torch.float64, device=self.device)
+        return torch.zeros(shape, dtype=self.dtype, device=self.device)
 
     def to_device(self, kind, host: np.ndarray, out: torch.Tensor | None = None, sync: bool = True):
         """host-order numpy [..., NSize, K] -> device-order tensor.  sync=False: asynchronous on the
         current stream (host must be pinned and stay alive until the stream has passed the copy)."""
-        host = np.ascontiguousarray(host, np.float64)
+        host = np.ascontiguousarray(host, self.np_dtype)
         nouter = host.shape[0] if host.ndim == 3 else 1
         ninner = host.shape[-1] if host.ndim >= 2 else 1
         if out is None:
-            out = torch.empty(host.shape, dtype=torch.float64, device=self.device)
+            out = torch.empty(host.shape, dtype=self.dtype, device=self.device)
         _chk(self.lib, self.lib.omega_field_to_device(self.h, kind, nouter, ninner, host.ctypes.data_as(capi.c_dbl_p), _dptr(out), _stream()), "omega_field_to_device")
         if sync:
             torch.cuda.current_stream().synchronize()  # host buffer may be a temporary
@@ -85,7 +89,7 @@ class HorzMesh:
         nouter = dev.shape[0] if dev.dim() == 3 else 1
         ninner = dev.shape[-1] if dev.dim() >= 2 else 1
         if out is None:
-            out = np.empty(tuple(dev.shape), np.float64)
+            out = np.empty(tuple(dev.shape), self.np_dtype)
         fn = self.lib.omega_field_to_host if sync else self.lib.omega_field_to_host_async
         _chk(self.lib, fn(self.h, kind, nouter, ninner, _dptr(dev), out.ctypes.data_as(capi.c_dbl_p), _stream()), "omega_field_to_host")
         return out
@@ -160,8 +164,8 @@ class Stepper:
         shape = ((self.T,) if has_t else ()) + (m.NSize[kind],) + ((m.K,) if has_k else ())
         n = int(np.prod(shape))
         if n == 0 or not ptr:
-            return np.zeros(shape)
-        out = np.empty(shape, np.float64)
+            return np.zeros(shape, m.np_dtype)
+        out = np.empty(shape, m.np_dtype)
         nouter = self.T if has_t else 1
         ninner = m.K if has_k else 1
         _chk(self.lib, self.lib.omega_field_to_host(m.h, kind, nouter, ninner, ptr, out.ctypes.data_as(capi.c_dbl_p), _stream()), "omega_field_to_host")
@@ -176,7 +180,7 @@ class Stepper:
         aux = capi.AuxArrays()
         _chk(self.lib, self.lib.omega_stepper_aux_arrays(self.h, C.byref(aux)), "omega_stepper_aux_arrays")
         kind, has_k, has_t = capi.AUX_KIND[name]
-        host = np.ascontiguousarray(host, np.float64)
+        host = np.ascontiguousarray(host, self.mesh.np_dtype)
         _chk(self.lib, self.lib.omega_field_to_device(self.mesh.h, kind, self.T if has_t else 1, self.mesh.K if has_k else 1,
                                                       host.ctypes.data_as(capi.c_dbl_p), getattr(aux, name), _stream()), "omega_field_to_device")
         torch.cuda.current_stream().synchronize()
@@ -189,7 +193,7 @@ class Stepper:
                 "TracerTend": self._wrap(t.TracerTend, ON_CELL, 1, 1)}
 
     def set_wind_stress(self, zonal, merid):
-        z, m = np.ascontiguousarray(zonal), np.ascontiguousarray(merid)
+        z, m = np.ascontiguousarray(zonal, self.mesh.np_dtype), np.ascontiguousarray(merid, self.mesh.np_dtype)
         _chk(self.lib, self.lib.omega_stepper_set_wind_stress(self.h, z.ctypes.data_as(capi.c_dbl_p), m.ctypes.data_as(capi.c_dbl_p), _stream()), "set_wind_stress")
         torch.cuda.current_stream().synchronize()
 

@@ -27,7 +27,7 @@ class VertCoord:
         K, n = mesh.K, mesh.NSize[0]
         self.MinLayerCell = torch.from_numpy(np.ascontiguousarray(np.asarray(min_layer_cell, np.int32)[p])).to(mesh.device)
         self.MaxLayerCell = torch.from_numpy(np.ascontiguousarray(np.asarray(max_layer_cell, np.int32)[p])).to(mesh.device)
-        z = lambda w: torch.zeros((n, w), dtype=torch.float64, device=mesh.device)
+        z = lambda w: torch.zeros((n, w), dtype=mesh.dtype, device=mesh.device)
         self.PressureInterface, self.PressureMid = z(K + 1), z(K)
         self.ZInterface, self.ZMid, self.GeopotentialMid, self.LayerThicknessTarget = z(K + 1), z(K), z(K), z(K)
 

@@ -42,7 +42,7 @@ def test_ctypes_struct_fields_follow_the_header():
             decl = decl.strip()
             if not decl:
                 continue
-            decl = re.sub(r"^(const\s+)?(int|double)\s*", "", decl)
+            decl = re.sub(r"^(const\s+)?(int|double|OmegaReal)\s*", "", decl)
             for part in decl.split(","):
                 out.append(re.sub(r"[\*\s]|\[\d+\]", "", part))
         return out
