@@ -334,6 +334,17 @@ int omega_halo_pack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, in
                     const OmegaReal *Array, OmegaReal *SendBuf, void *Stream);
 int omega_halo_unpack(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner,
                       const OmegaReal *RecvBuf, OmegaReal *Array, void *Stream);
+/* The same exchange for arrays of any element type the reference's Halo moves (I4, I8, R4, R8; 1 to 5
+ * dimensions, Halo.h:768-915, test/base/HaloTest.cpp:41-99): Array is [NOuter][N*Size][NInner] in device
+ * order with NOuter the product of the dimensions in front of the element dimension and NInner the
+ * dimension behind it (1 for a 1-D array); ElemBytes is 4 or 8.  pack_any / unpack_any are the device
+ * halves with caller-owned buffers (omega_halo_buffer_counts entries, times ElemBytes, in bytes). */
+int omega_halo_exchange_any(OmegaHalo *Halo, void *Array, OmegaMeshElement Elem, int NOuter, int NInner,
+                            int ElemBytes, void *Stream);
+int omega_halo_pack_any(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner, int ElemBytes,
+                        const void *Array, void *SendBuf, void *Stream);
+int omega_halo_unpack_any(const OmegaHalo *Halo, OmegaMeshElement Elem, int NOuter, int NInner, int ElemBytes,
+                          const void *RecvBuf, void *Array, void *Stream);
 /* Tile classes used for the overlap: tiles with send-list rows, owned tiles, all tiles. */
 int omega_halo_tile_classes(const OmegaHalo *Halo, int *NBoundary, int *NOwned, int *NTiles);
 /* CUDA-event timing of the exchange rounds since the last call (pack .. unpack on the exchange

@@ -40,10 +40,10 @@ namespace omega {
 // Buf[n-block][o][i][k] <-> Array[o][Idx[i]][k]; one launch covers every neighbour:
 // the per-neighbour blocks are contiguous in list order, block n starts at
 // NOuter*NInner*Off[n].
-template <bool Pack>
+template <bool Pack, class T = Real>
 __global__ void __launch_bounds__(kBlock)
 k_halo_rows(int NNbr, const int *__restrict__ Off, const int *__restrict__ Idx, int NOuter, int NRows,
-            int NInner, Real *__restrict__ Array, Real *__restrict__ Buf) {
+            int NInner, T *__restrict__ Array, T *__restrict__ Buf) {
    const long long w     = blockIdx.x * (long long)blockDim.x + threadIdx.x;
    const long long total = (long long)Off[NNbr] * NOuter * NInner;
    if (w >= total) return;
@@ -401,6 +401,69 @@ int omega_halo_unpack(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int
        NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner, Array, const_cast<Real *>(RecvBuf));
    OMEGA_CUDA_CHECK(cudaGetLastError());
    return 0;
+}
+
+// ---- arrays of any element type (Halo.h:62-917 exchanges I4, I8, R4, R8 arrays of 1 to 5 dimensions) ----------
+// An array [d0]..[element][last] is NOuter = product of the dimensions in front of the element dimension and
+// NInner = the one behind it (1 for a 1-D array); elements are moved as 4- or 8-byte words.
+extern "C++" {
+template <bool Pack>
+static int rows_any(const OmegaHalo *H, int Elem, int NOuter, int NInner, int ElemBytes, void *Array, void *Buf, cudaStream_t St) {
+   const int NN = H->NNeighbors;
+   const std::vector<int> &off = Pack ? H->SendOff[Elem] : H->RecvOff[Elem];
+   const long long total = (long long)off[NN] * NOuter * NInner;
+   if (total == 0) return 0;
+   const int *d = Pack ? H->DSendIdx[Elem] : H->DRecvIdx[Elem];
+   if (ElemBytes == 8)
+      k_halo_rows<Pack, unsigned long long><<<grid_for(total), kBlock, 0, St>>>(NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner,
+                                                                                 (unsigned long long *)Array, (unsigned long long *)Buf);
+   else
+      k_halo_rows<Pack, unsigned><<<grid_for(total), kBlock, 0, St>>>(NN, d, d + NN + 1, NOuter, n_size(H->M, Elem), NInner,
+                                                                      (unsigned *)Array, (unsigned *)Buf);
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   return 0;
+}
+} // extern "C++"
+
+int omega_halo_pack_any(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, int ElemBytes, const void *Array,
+                        void *SendBuf, void *Stream) {
+   OMEGA_REQUIRE(H && Array && SendBuf && Elem >= 0 && Elem < 3 && NOuter >= 1 && NInner >= 1 && (ElemBytes == 4 || ElemBytes == 8),
+                 "omega_halo_pack_any: bad argument (elements of 4 or 8 bytes)");
+   return rows_any<true>(H, Elem, NOuter, NInner, ElemBytes, const_cast<void *>(Array), SendBuf, (cudaStream_t)Stream);
+}
+
+int omega_halo_unpack_any(const OmegaHalo *H, OmegaMeshElement Elem, int NOuter, int NInner, int ElemBytes, const void *RecvBuf,
+                          void *Array, void *Stream) {
+   OMEGA_REQUIRE(H && Array && RecvBuf && Elem >= 0 && Elem < 3 && NOuter >= 1 && NInner >= 1 && (ElemBytes == 4 || ElemBytes == 8),
+                 "omega_halo_unpack_any: bad argument (elements of 4 or 8 bytes)");
+   return rows_any<false>(H, Elem, NOuter, NInner, ElemBytes, Array, const_cast<void *>(RecvBuf), (cudaStream_t)Stream);
+}
+
+int omega_halo_exchange_any(OmegaHalo *H, void *Array, OmegaMeshElement Elem, int NOuter, int NInner, int ElemBytes, void *Stream) {
+   OMEGA_REQUIRE(H && Array && Elem >= 0 && Elem < 3 && NOuter >= 1 && NInner >= 1 && (ElemBytes == 4 || ElemBytes == 8),
+                 "omega_halo_exchange_any: bad argument (elements of 4 or 8 bytes)");
+   OMEGA_REQUIRE(H->NNeighbors == 0 || H->Comm, "omega_halo_exchange_any: no communicator (omega_halo_comm_init)");
+   const int NN = H->NNeighbors;
+   if (NN == 0) return 0;
+   cudaStream_t St = (cudaStream_t)Stream;
+   const size_t per = (size_t)NOuter * NInner * ElemBytes; // bytes per list entry
+   const size_t sb = (size_t)H->SendOff[Elem][NN] * per, rb = (size_t)H->RecvOff[Elem][NN] * per;
+   // the library's round buffers, sized in Reals
+   if (ensure_buffer(H, &H->SendBuf, &H->SendCap, (long long)((sb + sizeof(Real) - 1) / sizeof(Real))) ||
+       ensure_buffer(H, &H->RecvBuf, &H->RecvCap, (long long)((rb + sizeof(Real) - 1) / sizeof(Real))))
+      return 1;
+   if (rows_any<true>(H, Elem, NOuter, NInner, ElemBytes, Array, H->SendBuf, St)) return 1;
+   ncclComm_t comm = (ncclComm_t)H->Comm;
+   OMEGA_NCCL_CHECK(g_nccl.GroupStart());
+   for (int n = 0; n < NN; ++n) {
+      const size_t s = (size_t)(H->SendOff[Elem][n + 1] - H->SendOff[Elem][n]) * per, so = (size_t)H->SendOff[Elem][n] * per;
+      const size_t r = (size_t)(H->RecvOff[Elem][n + 1] - H->RecvOff[Elem][n]) * per, ro = (size_t)H->RecvOff[Elem][n] * per;
+      const int peer = H->NeighborTasks[n];
+      if (s) OMEGA_NCCL_CHECK(g_nccl.Send((const char *)H->SendBuf + so, s, ncclChar, peer, comm, St));
+      if (r) OMEGA_NCCL_CHECK(g_nccl.Recv((char *)H->RecvBuf + ro, r, ncclChar, peer, comm, St));
+   }
+   OMEGA_NCCL_CHECK(g_nccl.GroupEnd());
+   return rows_any<false>(H, Elem, NOuter, NInner, ElemBytes, Array, H->RecvBuf, St);
 }
 
 // ---- exchange rounds ---------------------------------------------------------------

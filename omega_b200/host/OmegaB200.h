@@ -125,6 +125,14 @@ class Halo {
       if (Neighbors.empty()) return 0;
       return omega_halo_exchange(Handle, Array.data(), (OmegaMeshElement)Elem, NOuter, Stream) ? -1 : 0;
    }
+   /// The other instantiations of the reference's template (I4, I8, R4, R8 arrays of one to five dimensions,
+   /// test/base/HaloTest.cpp:41-99): Ptr is the device array [NOuter][N*Size][NInner], NOuter the product of the
+   /// dimensions in front of the element dimension, NInner the one behind it (1 for a 1-D array).
+   template <class T> int exchangeFullArrayHalo(T *Ptr, MeshElement Elem, int NOuter, int NInner, void *Stream = nullptr) {
+      static_assert(sizeof(T) == 4 || sizeof(T) == 8, "elements of 4 or 8 bytes");
+      if (Neighbors.empty()) return 0;
+      return omega_halo_exchange_any(Handle, Ptr, (OmegaMeshElement)Elem, NOuter, NInner, (int)sizeof(T), Stream) ? -1 : 0;
+   }
 };
 
 /// OceanState: h and u time-level rings (src/ocn/OceanState.cpp:65-117,333-407)

@@ -47,11 +47,32 @@ def main():
     TR = np.empty_like(gt[:, :-1]); TR[:, cell_of] = gt[:, :-1]
     ci, ei = L.CellID[:L.NCellsAll] - 1, L.EdgeID[:L.NEdgesAll] - 1
     worst = max(cases.rel_l2(a, b) for a, b in ((lh[:L.NCellsAll], H[ci]), (lu[:L.NEdgesAll], U[ei]), (lt[:, :L.NCellsAll], TR[:, ci])))
-    t = torch.tensor([worst, 0.0 if split else 1.0], dtype=torch.float64, device=dev)
+    # test/base/HaloTest.cpp:41-99 over NCCL: arrays of every element type hold global IDs in their owned entries
+    # only, omega_halo_exchange_any fills the halo entries, the result must equal the fully initialised array
+    import ctypes as C
+    bad = 0
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for kind, ids, nall, nown in ((capi.ON_CELL, L.CellID, L.NCellsAll, L.NCellsOwned), (capi.ON_EDGE, L.EdgeID, L.NEdgesAll, L.NEdgesOwned),
+                                  (capi.ON_VERTEX, L.VertexID, L.NVerticesAll, L.NVerticesOwned)):
+        for npdt, nouter, ninner in ((np.int32, 1, 1), (np.int64, 2, 3), (np.float32, 1, 5), (np.float64, 3, 2)):
+            n = mesh.NSize[kind]
+            o, i = np.arange(nouter).reshape(nouter, 1, 1), np.arange(ninner).reshape(1, 1, ninner)
+            full = ((np.asarray(ids, np.int64)[:n].reshape(1, n, 1) * 7 + o) * 5 + i).astype(npdt)
+            full[:, int(nall):] = 0
+            part = full.copy()
+            part[:, int(nown):int(nall)] = npdt(-1)
+            p, _ = mesh.perm(kind)
+            d = torch.from_numpy(np.ascontiguousarray(part[:, p])).to(dev)
+            rc = mesh.lib.omega_halo_exchange_any(ex.handle, C.c_void_p(d.data_ptr()), kind, nouter, ninner, np.dtype(npdt).itemsize, stream)
+            torch.cuda.synchronize()
+            if rc != 0 or not np.array_equal(d.cpu().numpy(), full[:, p]):
+                bad += 1
+    t = torch.tensor([worst, 0.0 if split else 1.0, float(bad)], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ok = float(t[0]) <= 1e-10 and (K % 16 != 0 or float(t[1]) == 0.0)
+    ok = float(t[0]) <= 1e-10 and (K % 16 != 0 or float(t[1]) == 0.0) and float(t[2]) == 0.0
     if rank == 0:
-        print(("NCCL_CHECK_OK" if ok else "NCCL_CHECK_FAILED"), float(t[0]), "overlap split on every rank:", float(t[1]) == 0.0, flush=True)
+        print(("NCCL_CHECK_OK" if ok else "NCCL_CHECK_FAILED"), float(t[0]), "overlap split on every rank:", float(t[1]) == 0.0,
+              "any-type exchanges wrong:", int(t[2]), flush=True)
     ex.close(); st.close(); mesh.close()
     dist.barrier()
     dist.destroy_process_group()
