@@ -214,6 +214,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--unfused", action="store_true", help="time the kernel-per-term path instead")
+    ap.add_argument("--precision", default="double", choices=["double", "single"],
+                    help="single: libomega_b200_sp.so (Real = float as in the reference's OMEGA_SINGLE_PRECISION build; "
+                         "untiled fused kernels); not the BASELINE metric, which is fp64")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -245,7 +248,9 @@ def main():
         # partition dependent (tests/test_multirank_cpu.py::test_reference_needs_halo_width_4_with_del4)
         L, halo_desc = parallel.local_problem(m, world, rank, K, halo_width=4)
     h, u, tr = initial_state(args.workload, L, cfg, T)
-    mesh = model.HorzMesh(L, reorder=True, device=dev)
+    sp = args.precision == "single"
+    mesh = model.HorzMesh(L, reorder=True, device=dev, lib=capi.load_library(capi.LIB_PATH_SP) if sp else None)
+    rb = mesh.real_bytes
     st = model.Stepper(mesh, cfg, T)
     state = model.OceanState(mesh, T)
     state.copyToDevice(h, u, tr if T else None)
@@ -322,7 +327,7 @@ def main():
     if os.path.exists(pk_path):
         peaks = json.load(open(pk_path))
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    alg_step = 128.0 * (4 + T)               # bytes per cell-layer per RK4 step
+    alg_step = 16.0 * rb * (4 + T)           # bytes per cell-layer per RK4 step (128 (4 + T) in fp64)
 
     # ---- e2e: HOST buffers in, HOST buffers out, every step -----------------
     # The public API a driver calls: omega_field_to_device (pinned host -> device order),
@@ -333,7 +338,7 @@ def main():
     # counted step and ends with a device synchronisation.
     e2e = None
     if not args.no_e2e and world == 1:
-        hp = [torch.from_numpy(a).pin_memory() for a in ((h, u, tr) if T else (h, u))]
+        hp = [torch.from_numpy(np.ascontiguousarray(a, mesh.np_dtype)).pin_memory() for a in ((h, u, tr) if T else (h, u))]
         NS = 3
         slots = [state] + [model.OceanState(mesh, T) for _ in range(NS - 1)]
         outp = [[torch.empty_like(x).pin_memory() for x in hp] for _ in range(2)]
@@ -378,7 +383,7 @@ def main():
         run_pipeline(ne)
         te = (time.perf_counter() - t0) / ne
         assert bool(np.isfinite(outp[(ne - 1) % 2][0].numpy()).all())
-        nbytes = sum(x.numel() * 8 for x in hp)
+        nbytes = sum(x.numel() * rb for x in hp)
         e2e = {"value": ncl / te, "unit": "cell-layer updates/s", "h2d_bytes_per_step": nbytes,
                "d2h_bytes_per_step": nbytes, "ms_per_step": te * 1e3, "steps": ne,
                "api": "omega_field_to_device x3 | omega_stepper_do_step | omega_field_to_host_async x3 per step, pinned host "
@@ -399,13 +404,13 @@ def main():
         # dominant kernel fC: per launch it owns the (1+T) cell-centred fields of one stage
         # = (3+5+5+3)/4 * 8 * (1+T) bytes per cell-layer on average
         cl_local = mesh.NAll[0] * K
-        alg_fc = 32.0 * (1 + T) * cl_local
-        alg_stage = [8.0 * n * (1 + T) * cl_local for n in (3, 5, 5, 3)]   # per RK4 stage
+        alg_fc = 4.0 * rb * (1 + T) * cl_local
+        alg_stage = [float(rb) * n * (1 + T) * cl_local for n in (3, 5, 5, 3)]   # per RK4 stage
         ach = alg_fc / (kms[3] / kcnt[3] * 1e-3) / 1e9
         # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/)
         traffic = None
         tr_path = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr_path) and args.workload == "config3" and world == 1:
+        if os.path.exists(tr_path) and args.workload == "config3" and world == 1 and not sp:
             traffic = json.load(open(tr_path)).get("k_fCT_dram_bytes_per_launch")
         path = st.last_path()
         kname = ("k_fCT2 (tiled cell pass: thickness + all tracer tendencies + RK updates)" if path & 4 else
@@ -420,10 +425,10 @@ def main():
     ach_step = alg_step * ncl / world / t_step / 1e9
     line = {"metric": "cell-layer updates/s", "value": value, "unit": "cell-layer updates/s", "n_gpus": world,
             "steps": K_steps, "warmup": W, "ms_per_step": t_step * 1e3, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if sp else "f64", "data": "synthetic",
             "sypd": dt / (365.0 * t_step),
             "config": {"workload": describe(args.workload, m, K, T, dt),
-                       "path": "fused" if fused else "kernel-per-term", "parallelism": f"domain decomposition x{world}",
+                       "path": ("fused" if fused else "kernel-per-term") + (", single-precision build" if sp else ""), "parallelism": f"domain decomposition x{world}",
                        "l2": ("state per step (>= 5 GB) exceeds the 126 MB L2; no flush needed" if ncl * (4 + T) * 8 > 2.5e8
                               else "state fits L2 (launch-bound workload); no flush")},
             "checksum": {"sum_A_h": checksum[0], "sum_A_h_phi": checksum[1:-1], "sum_u2": checksum[-1],
@@ -445,7 +450,7 @@ def main():
                         "transport": "library: one pack kernel + grouped ncclSend/ncclRecv + one unpack kernel per round "
                                      "(csrc/halo.cu), on its own stream behind the boundary tiles, overlapped with the "
                                      "interior tiles"}
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and not sp:
         cb, *_ = cpu_reference_rate(args.workload, 2, 1, full_depth=False)
         line["cpu_baseline"] = cb
     else:
