@@ -387,17 +387,6 @@ int omega_mesh_create(const OmegaMeshDesc *D, int Reorder, OmegaMesh **Out) {
    OMEGA_REQUIRE(D->NCellsSize == D->NCellsAll + 1 && D->NEdgesSize == D->NEdgesAll + 1 &&
                      D->NVerticesSize == D->NVerticesAll + 1,
                  "omega_mesh_create: N*Size must equal N*All+1 (Decomp.cpp:1081-1082)");
-   {
-      // omega_field_to_device/_to_host stage whole fields through stream-ordered allocations; keep the
-      // freed blocks in the device's pool (default threshold 0 hands them back to the driver at every
-      // synchronisation, and a multi-GB cudaMalloc per field per step then dominates the transfer)
-      int dev = 0;
-      cudaMemPool_t pool;
-      unsigned long long keep = ~0ull;
-      OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
-      OMEGA_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
-      OMEGA_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-   }
    OmegaMesh *M = new OmegaMesh();
    M->Sizes     = *D;
    M->Reordered = Reorder;
@@ -763,6 +752,32 @@ int omega_mesh_derived(const OmegaMesh *M, double *EdgeSignOnCell, double *EdgeS
 // scattered to / gathered from its device rows (DIPerm: device row of a host row).
 static constexpr size_t kSlabBytes = 64u << 20;
 
+// The staging blocks come from a pool of the library's own, one per device, that keeps freed blocks (release
+// threshold: never): with the default threshold a multi-GB block would go back to the driver at every
+// synchronisation and be allocated again for every field of every step.  The process's default pool, which the
+// host application may use itself, is left alone.
+static int stage_pool(cudaMemPool_t *Pool) {
+   constexpr int kMaxDevices = 64;
+   static cudaMemPool_t pools[kMaxDevices] = {};
+   int dev = 0;
+   OMEGA_CUDA_CHECK(cudaGetDevice(&dev));
+   OMEGA_REQUIRE(dev >= 0 && dev < kMaxDevices, "field transfer: device ordinal beyond 63");
+   if (!pools[dev]) {
+      cudaMemPoolProps props = {};
+      props.allocType     = cudaMemAllocationTypePinned;
+      props.handleTypes   = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id   = dev;
+      cudaMemPool_t p;
+      OMEGA_CUDA_CHECK(cudaMemPoolCreate(&p, &props));
+      unsigned long long keep = ~0ull;
+      OMEGA_CUDA_CHECK(cudaMemPoolSetAttribute(p, cudaMemPoolAttrReleaseThreshold, &keep));
+      pools[dev] = p;
+   }
+   *Pool = pools[dev];
+   return 0;
+}
+
 static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter, int NInner, Real *Dev, Real *Host,
                           cudaStream_t S, bool ToDevice) {
    const int NRows    = n_size(M, Elem);
@@ -804,7 +819,9 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
    }
    if (!wantSlab && bytes <= totalB / 8) {
       Real *stage = nullptr;
-      OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, bytes, S));
+      cudaMemPool_t pool;
+      if (int rc = stage_pool(&pool)) return rc;
+      OMEGA_CUDA_CHECK(cudaMallocFromPoolAsync((void **)&stage, bytes, pool, S));
       if (ToDevice) {
          OMEGA_CUDA_CHECK(cudaMemcpyAsync(stage, Host, bytes, cudaMemcpyHostToDevice, S));
          launch_permute_rows(S, NOuter, NRows, NInner, M->DPerm[Elem], stage, Dev);   // device row r <- host row Perm[r]
@@ -819,7 +836,9 @@ static int field_transfer(const OmegaMesh *M, OmegaMeshElement Elem, int NOuter,
    const size_t rowBytes = (size_t)NInner * sizeof(Real);
    const int slabRows    = (int)std::max<size_t>(1, std::min<size_t>(NRows, kSlabBytes / rowBytes));
    Real *stage = nullptr;
-   OMEGA_CUDA_CHECK(cudaMallocAsync((void **)&stage, (size_t)slabRows * rowBytes, S));
+   cudaMemPool_t pool;
+   if (int rc = stage_pool(&pool)) return rc;
+   OMEGA_CUDA_CHECK(cudaMallocFromPoolAsync((void **)&stage, (size_t)slabRows * rowBytes, pool, S));
    for (int o = 0; o < NOuter; ++o) {
       Real *dev  = Dev + (size_t)o * NRows * NInner;
       Real *host = Host + (size_t)o * NRows * NInner;
