@@ -244,6 +244,41 @@ def test_rk4_fused_path(case, compat):
     assert max(errs) <= TOL_STATE, (name, errs)
 
 
+def test_fused_kernels_right_hand_side_direct(case):
+    """The <= 1e-12 per-field tendency gate ON the fused (tiled) kernels themselves.  They never store a stage's
+    right-hand side R, but with stage coefficients B = (2^20, 0, 0, 0), A = 0 the first RK4 phase leaves
+    next = cur + 2^20 R(cur) (tracers: cur h + 2^20 R in thickness-weighted form, TimeStepper.cpp:446-524), the
+    second stage adding 0 x R(cur); scaling by a power of two is exact, so R is recovered to rounding."""
+    from tests.oracle_lib import Oracle
+    name, (L, cfg, (h, u, tr), dt) = case
+    T = tr.shape[0]
+    mesh, st, state = gpu_objects(L, cfg, T)
+    o = Oracle(L, cfg, T)
+    o.tend_all(h, u, tr, time=0.0)
+    state.copyToDevice(h, u, tr)
+    big = float(2 ** 20)
+    co = capi.StepCoeffs()
+    co.NStages, co.Dt = 4, 1.0
+    for s in range(4):
+        co.A[s], co.B[s], co.StageTime[s] = 0.0, (big if s == 0 else 0.0), 0.0
+    st.stepPhase(state, capi.RK4, co, 0, fused=True, compat=True)
+    if name in TILED:
+        assert st.last_path() & (PATH_TILED_CELL | PATH_TILED_EDGE) == PATH_TILED_CELL | PATH_TILED_EDGE, st.last_path()
+    hn = mesh.to_host(capi.ON_CELL, state.LayerThickness[1])
+    un = mesh.to_host(capi.ON_EDGE, state.NormalVelocity[1])
+    nc, ne = int(L.NCellsAll), int(L.NEdgesAll)
+    got = {"LayerThicknessTend": (hn - h) / big, "NormalVelocityTend": (un - u) / big}
+    if T:
+        trn = mesh.to_host(capi.ON_CELL, state.Tracers[1])
+        got["TracerTend"] = (trn - tr * h[None]) / big
+    for n, g in got.items():
+        w = o.tend[n]
+        rows = ne if n == "NormalVelocityTend" else nc
+        err = rel_max(g[..., :rows, :], w[..., :rows, :])
+        assert err <= TOL_TEND, (name, n, err)
+    o.close(); st.close(); mesh.close()
+
+
 @pytest.mark.parametrize("stepper", [capi.RK2, capi.FB])
 @pytest.mark.parametrize("compat", [True, False])
 def test_rk2_and_forward_backward_fused_path(case, stepper, compat):
