@@ -1084,6 +1084,31 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
    }
    // ---- momentum: aux fields, then the edge pass
    const Real *Hm = sd.HsMom;
+   // OMEGA_PDL=1 (measured, off by default): k_fA reads the stage state only and writes auxiliary fields the cell
+   // pass never touches, so behind the tiled cell pass (which signals griddepcontrol.launch_dependents) it can be
+   // launched with programmatic stream serialization and run on the SMs the cell pass's last round of CTAs
+   // leaves idle; the same for the interior tiles' edge pass behind their cell pass.  Config 3 on one GPU:
+   // 36.9 -> 37.0 ms/step -- the tail it fills is 0.3 of a round on a fifth of the SMs (< 0.01 ms of work) and the
+   // early kernel competes with the cell pass's last CTAs for HBM.  Not while per-kernel events are recorded
+   // between the launches (profiling), and not when the momentum thickness is one the cell pass writes
+   // (forward-backward).
+   const bool pdl = tiled && V == 2 && !S->Profiling && Hm != sd.Hnext && Hm != sd.Hprov && env_int("OMEGA_PDL", 0);
+   if (pdl) {
+      NvtxRange nv_("k_fA");
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(gA);
+      cfg.blockDim = dim3(kBlock);
+      cfg.stream = St;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      OMEGA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fA<2>, D, Hm, sd.Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
+                                          (Real)(G.KETendencyEnable ? 1.0 : 0.0), (Real)(G.SSHTendencyEnable ? 1.0 : 0.0),
+                                          tiledE && drag ? S->A.ZonalStress2 : (Real *)nullptr));
+      ++S->Launches;
+   } else
    LAUNCH_V(kFA, k_fA, gA, D, Hm, sd.Us, S->A.KE, S->A.Div, S->A.RelVort, S->A.NormRelVort, tiledE ? 1 : 0,
             G.KETendencyEnable ? 1.0 : 0.0, G.SSHTendencyEnable ? 1.0 : 0.0, tiledE && drag ? S->A.ZonalStress2 : nullptr);
    // W = Y - X folded into fB's cell result when the tiled edge pass follows (one gathered cell field less)
@@ -1148,8 +1173,11 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
          ++S->Launches;
       }
       {
+         // the edge pass of the interior tiles does not depend on their cell pass queued right before it (unless
+         // it writes the velocity level the cell pass still reads: stage 0 with raw time-level indexing)
+         const bool pdlE = pdl && sd.Unext != sd.Us && sd.Unext != sd.UTr && sd.Uprov != sd.Us && sd.Uprov != sd.UTr;
          ScopedTimer tm_(S, St, kFE);
-         if (launch_fET(D, ta, St, trInt)) return 1;
+         if (launch_fET(D, ta, St, trInt, pdlE)) return 1;
          ++S->Launches;
       }
       if ((wind || drag) && trInt.Count > 0) {

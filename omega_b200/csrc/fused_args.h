@@ -62,7 +62,9 @@ bool tile_path_ok(const DMesh &D);
 bool tile_v2_enabled(); // k_fCT2 (any tracer count with tracer hyperdiffusion) is selectable
 bool tile_v2_used(const CellArgs &ca); // launch_fCT will run k_fCT2 for these arguments
 bool tile_edge_path_ok(const DMesh &D);
-int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR);
+// Overlap: the launch does not depend on the kernel queued right before it on St (the tiled cell pass), so it
+// is launched with programmatic stream serialization and its CTAs fill the SMs that kernel's tail leaves idle
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR, bool Overlap = false);
 int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR);
 
 } // namespace omega

@@ -42,7 +42,7 @@ bool tile_v2_enabled() { return false; }
 bool tile_v2_used(const CellArgs &) { return false; }
 bool tile_edge_path_ok(const DMesh &) { return false; }
 size_t tile_smem_bytes() { return 0; }
-int launch_fET(const DMesh &, const EdgeTileArgs &, cudaStream_t, const TileRange &) {
+int launch_fET(const DMesh &, const EdgeTileArgs &, cudaStream_t, const TileRange &, bool) {
    OMEGA_REQUIRE(false, "launch_fET: the tile kernels are not part of the single-precision build");
 }
 int launch_fCT(const DMesh &, const CellArgs &, cudaStream_t, const TileRange &) {
@@ -1303,6 +1303,10 @@ __global__ void __launch_bounds__(C::NT, C::CTAs)
 k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    typename C::Smem &S = *reinterpret_cast<typename C::Smem *>(smem_raw);
+   // A kernel queued behind this one with programmatic stream serialization (fused.cu: k_fA, or the edge pass of
+   // the interior tiles -- neither reads what this pass writes) may start on the SMs this grid's last round of
+   // CTAs leaves idle: every CTA has started once all have signalled.  Without such a launch this is a no-op.
+   asm volatile("griddepcontrol.launch_dependents;");
    // CTAs below NWhole take a whole tile (all NChAll chunks); the tiles of the last, partial round of
    // CTAs are split into one CTA per chunk so that the tail of the grid costs a fraction of a round
    const int tid = threadIdx.x;
@@ -1609,7 +1613,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    }
 }
 
-int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR) {
+int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const TileRange &TR, bool Overlap) {
    if (TR.Count <= 0) return 0;
    static DevOnce once, onceOpt;
    int sm = 0;
@@ -1621,6 +1625,21 @@ int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const Ti
    // latency they hide; removed.)
    const int pf = env_i("OMEGA_TILE_EPF", 1);
    const int ahead = env_i("OMEGA_TILE_EAHEAD", (2 * sm + nch - 1) / nch);
+   if (Overlap) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)TR.Count * nch);
+      cfg.blockDim = dim3(kEThreads);
+      cfg.dynamicSmemBytes = sizeof(ETileSmem);
+      cfg.stream = St;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      if (opt) OMEGA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fET<true>, D, ea, nch, pf, ahead, TR));
+      else OMEGA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fET<false>, D, ea, nch, pf, ahead, TR));
+      return 0;
+   }
    if (opt) k_fET<true><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
    else k_fET<false><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
    return 0;
