@@ -25,7 +25,10 @@
 // (TendencyTerms.h:35-58,349-480, TracerAuxVars.h:25-91,
 // LayerThicknessAuxVars.h:25-61, TimeStepper.cpp:378-524); MeshScalingDel2/4
 // are 1 (HorzMesh.cpp:604-626), which the per-cell tables assume.
+#include <cuda.h> // CUtensorMap (type and enums only: the encoder is looked up through cudaGetDriverEntryPoint)
+
 #include <cstdlib>
+#include <cstring>
 
 #include "fused_args.h"
 #include "kernel_util.cuh"
@@ -586,6 +589,7 @@ template <int KC_, int RS_ = 0, int CP_ = 0, int TM_ = 0> struct Cfg2 {
    static constexpr int NS = 4;              // tracer row-set buffers (copy lead 3 needs 4)
    static constexpr int CTAs = KC == 16 ? 1 : 2;
    static constexpr bool BULK = CP_ >= 1;    // row copies: 0 = cp.async 16-byte pieces (LSU), 1, 2 = one bulk copy per row (TMA unit, mbarrier)
+   static constexpr bool TMAP = CP_ == 3;    // 3: tensor-map copies, FOUR rows per instruction (cp.async.bulk.tensor tile::gather4, sm_100)
    static constexpr bool ONEWAIT = CP_ == 2; // 2: ONE thread waits on the "landed" barrier, ahead of the __syncthreads that hands the buffer over
    static constexpr int TM = TM_;            // tensor memory (TMEM) for per-thread private slots: 1 = the RK weights of the T role
    static constexpr bool PAIR = false;       // one tracer per iteration (Cfg3: two)
@@ -594,6 +598,8 @@ template <int KC_, int RS_ = 0, int CP_ = 0, int TM_ = 0> struct Cfg2 {
       unsigned long long Bar[NS + 1]; // BULK: "landed" barriers of the tracer buffers and of h
       double SHc[kTileCells];         // own rows: -sum_j ch_j (the self coefficient of the Del4 sum)
       unsigned TmemBase;              // TM: base address of the CTA's tensor-memory allocation
+      const void *MapH, *MapT;        // TMAP: tensor maps of the stage thickness [NCellsSize][K] and tracers [T NCellsSize][K]
+      const double *HsBase, *TrsBase; //       and the arrays they describe (a copy's row offset follows from its source pointer)
    };
 };
 static_assert(sizeof(Cfg2<16>::Smem) <= 232448, "k_fCT2 shared memory");
@@ -619,6 +625,13 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned par) {
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                 "r"(bytes), "r"(bar)
+                : "memory");
+}
+
+// four rows (128 bytes each: 16 levels from column Col) of a 2-D tensor map into four consecutive 128-byte rows at Dst
+__device__ __forceinline__ void tma_gather4(unsigned Dst, const void *Map, int Col, int R0, int R1, int R2, int R3, unsigned Bar) {
+   asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                ::"r"(Dst), "l"(Map), "r"(Col), "r"(R0), "r"(R1), "r"(R2), "r"(R3), "r"(Bar)
                 : "memory");
 }
 
@@ -668,7 +681,22 @@ __device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, i
 template <class C>
 __device__ __forceinline__ void issue_rows(typename C::Smem &S, int nR, int K, int r, int grow, const double *F, void *Dst, int kc,
                                            int bar) {
-   if (C::BULK) {
+   if (C::TMAP) {
+      // rows 4r .. 4r+3 of the tile's row list by one instruction (the last group repeats the last row: the
+      // buffer holds kTileRows rows, a multiple of four)
+      const unsigned b = smem_u32(&S.Bar[bar]);
+      const int ng = (nR + 3) >> 2;
+      if (r == 0) mbar_expect_tx(b, (unsigned)ng * (4 * C::KC * 8));
+      if (r < ng) {
+         const bool isH   = F == S.HsBase;
+         const int base   = isH ? 0 : (int)((F - S.TrsBase) / K);
+         const int4 g     = *reinterpret_cast<const int4 *>(&S.GRow[4 * r]);
+         const int last   = S.GRow[nR - 1];
+         const int q      = 4 * r;
+         tma_gather4(smem_u32(Dst) + r * (4 * C::KC * 8), isH ? S.MapH : S.MapT, kc, base + g.x, base + (q + 1 < nR ? g.y : last),
+                     base + (q + 2 < nR ? g.z : last), base + (q + 3 < nR ? g.w : last), b);
+      }
+   } else if (C::BULK) {
       const unsigned b = smem_u32(&S.Bar[bar]);
       if (r == 0) mbar_expect_tx(b, (unsigned)nR * (C::KC * 8));
       if (r < nR) bulk_g2s(smem_u32(Dst) + r * (C::KC * 8), F + ((size_t)grow * K + kc), C::KC * 8, b);
@@ -810,7 +838,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
 struct Cfg3 {
    static constexpr int KC = 16, RS = 2, L = 8, LS = 3;
    static constexpr int TT = kTileCells * L, RT = TT / 2, NT = TT + RT, NS = 4, CTAs = 1;
-   static constexpr bool BULK = false, ONEWAIT = false, PAIR = true;
+   static constexpr bool BULK = false, ONEWAIT = false, PAIR = true, TMAP = false;
    static constexpr int TM = 2; // tensor memory holds the ring-row coefficients of the R role
    struct Smem {
       double H[kTileRows][KC];
@@ -1300,7 +1328,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
 
 template <class C, int STAGE, bool OPT>
 __global__ void __launch_bounds__(C::NT, C::CTAs)
-k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
+k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR, const __grid_constant__ CUtensorMap MapH,
+       const __grid_constant__ CUtensorMap MapT) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
    typename C::Smem &S = *reinterpret_cast<typename C::Smem *>(smem_raw);
    // A kernel queued behind this one with programmatic stream serialization (fused.cu: k_fA, or the edge pass of
@@ -1323,6 +1352,10 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
    if (C::BULK && tid == 32) {
       for (int b = 0; b <= C::NS; ++b) mbar_init(smem_u32(&S.Bar[b]), 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      if constexpr (C::TMAP) {
+         S.MapH = &MapH; S.MapT = &MapT;
+         S.HsBase = P.Hs; S.TrsBase = P.Trs;
+      }
    }
    if (C::TM) {
       if (tid < 32) tmem_alloc_all(&S.TmemBase); // one CTA per SM: the whole tensor memory
@@ -1357,6 +1390,29 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR) {
    }
 }
 
+// tensor maps of the TMAP row copies: a [rows][K] fp64 array read in boxes of one row x KC levels (four such
+// rows per tile::gather4 instruction).  The encoder is a driver entry point, looked up once.
+static int encode_row_map(CUtensorMap *Map, const double *Base, long long Rows, int K, int KC) {
+   typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+   static EncodeFn enc = nullptr;
+   if (!enc) {
+      cudaDriverEntryPointQueryResult qr;
+      void *fn = nullptr;
+      OMEGA_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+      OMEGA_REQUIRE(fn && qr == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+      enc = (EncodeFn)fn;
+   }
+   const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Rows}, strides[1] = {(cuuint64_t)K * 8};
+   const cuuint32_t box[2] = {(cuuint32_t)KC, 1}, es[2] = {1, 1};
+   const CUresult rc = enc(Map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double *>(Base), dims, strides, box, es,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+   OMEGA_REQUIRE(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (" + std::to_string((int)rc) + ")");
+   return 0;
+}
+
 template <class C, int STAGE, bool OPT> static int launch_fCT2_o(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    static DevOnce once;
    int sm = 0;
@@ -1373,7 +1429,14 @@ template <class C, int STAGE, bool OPT> static int launch_fCT2_o(const DMesh &D,
       const double cost = ((tail * nch + sm - 1) / sm) * 1.15 / nch; // rounds, a single-chunk CTA costs ~15 % more per chunk
       if (tail > 0 && cost < 0.85) whole = nt - tail;
    }
-   k_fCT2<C, STAGE, OPT><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR);
+   CUtensorMap mapH, mapT;
+   std::memset(&mapH, 0, sizeof(mapH));
+   std::memset(&mapT, 0, sizeof(mapT));
+   if constexpr (C::TMAP) {
+      if (encode_row_map(&mapH, ca.Hs, D.NCellsSize, D.K, C::KC)) return 1;
+      if (encode_row_map(&mapT, ca.Trs, (long long)ca.NTracers * D.NCellsSize, D.K, C::KC)) return 1;
+   }
+   k_fCT2<C, STAGE, OPT><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR, mapH, mapT);
    return 0;
 }
 template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
@@ -1381,7 +1444,8 @@ template <class C, int STAGE> static int launch_fCT2_c(const DMesh &D, const Cel
 }
 template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRange &TR) {
    // measured variants, selectable for profiling (profiles/r01e_ncu_full_summary.md): register split /
-   // R-role width (OMEGA_TILE_RS = 0, 2, 3) and bulk row copies (OMEGA_TILE_CP = 1).  The 8-level shape
+   // R-role width (OMEGA_TILE_RS = 0, 2, 3), bulk row copies (OMEGA_TILE_CP = 1, 2) and tensor-map gather4 copies
+   // (OMEGA_TILE_CP = 3: 7.33 ms per launch against 5.44 -- the copy engine is slow on 128-byte row pieces).  The 8-level shape
    // Cfg2<8> (two CTAs per SM) is not instantiated: its 64-byte row pieces conflict in the banks.
    const int rs = env_i("OMEGA_TILE_RS", 2), cp = env_i("OMEGA_TILE_CP", 0), tm = env_i("OMEGA_TILE_TM", 0);
    // k_fCT3 (OMEGA_TILE_V3=1): two tracers per iteration, ring coefficients in tensor memory.  Parity-green
@@ -1393,6 +1457,7 @@ template <int STAGE> static int launch_fCT2_t(const DMesh &D, const CellArgs &ca
    if (tm == 1) return launch_fCT2_c<Cfg2<16, 2, 0, 1>, STAGE>(D, ca, St, TR);
    if (cp == 1) return launch_fCT2_c<Cfg2<16, 2, 1>, STAGE>(D, ca, St, TR);
    if (cp == 2) return launch_fCT2_c<Cfg2<16, 2, 2>, STAGE>(D, ca, St, TR);
+   if (cp == 3) return launch_fCT2_c<Cfg2<16, 2, 3>, STAGE>(D, ca, St, TR);
    return rs == 3 ? launch_fCT2_c<Cfg2<16, 3>, STAGE>(D, ca, St, TR) : rs == 2 ? launch_fCT2_c<Cfg2<16, 2>, STAGE>(D, ca, St, TR) : launch_fCT2_c<Cfg2<16, 0>, STAGE>(D, ca, St, TR);
 }
 size_t tile_smem_bytes() { return sizeof(TileSmem); }
