@@ -148,6 +148,10 @@ int omega_dev_alloc(void **ptr, unsigned long long bytes);
 int omega_dev_free(void *ptr);
 int omega_dev_copy(void *dst, const void *src, unsigned long long bytes, void *stream); /* device to device, async */
 int omega_dev_sync(void *stream);
+/* plain byte copies between host and device memory (Kokkos::deep_copy of index arrays and the like);
+ * both return when the copy is complete */
+int omega_dev_upload(void *dev_dst, const void *host_src, unsigned long long bytes);
+int omega_dev_download(void *host_dst, const void *dev_src, unsigned long long bytes);
 
 /* ---- HorzMesh (src/ocn/HorzMesh.cpp:49-150,527-647) ---------------------- */
 /* Builds the SFC permutation (Reorder=1) or keeps host order (Reorder=0),

@@ -363,6 +363,16 @@ const char *omega_last_error(void) { return g_last_error.c_str(); }
 int omega_b200_abi_version(void) { return 1; }
 int omega_b200_real_bytes(void) { return (int)sizeof(OmegaReal); }
 
+int omega_dev_upload(void *dst, const void *src, unsigned long long bytes) {
+   OMEGA_REQUIRE((dst && src) || bytes == 0, "omega_dev_upload: null argument");
+   if (bytes) OMEGA_CUDA_CHECK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+   return 0;
+}
+int omega_dev_download(void *dst, const void *src, unsigned long long bytes) {
+   OMEGA_REQUIRE((dst && src) || bytes == 0, "omega_dev_download: null argument");
+   if (bytes) OMEGA_CUDA_CHECK(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+   return 0;
+}
 int omega_dev_alloc(void **ptr, unsigned long long bytes) {
    OMEGA_CUDA_CHECK(cudaMalloc(ptr, bytes ? bytes : 16));
    OMEGA_CUDA_CHECK(cudaMemset(*ptr, 0, bytes));

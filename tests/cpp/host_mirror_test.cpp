@@ -15,6 +15,7 @@
 #include <memory>
 
 #include "OmegaB200.h"
+#include "OmegaB200Vertical.h"
 
 using namespace OMEGA;
 
@@ -134,6 +135,86 @@ int main(int argc, char **argv) {
    Trc.getAll(Cur, 0);
    if (T) Mesh.copyToHost(OnCell, T, K, Cur.data(), TR.data());
    save("out_h", H); save("out_u", U); save("out_tr", TR);
+   // the Omega-1 column pieces through their reference-named mirror (OmegaB200Vertical.h), on the stepped thickness:
+   // pressure, TEOS-10 specific volume (plain and displaced by one layer), z height, geopotential, target
+   // thickness, and the two tridiagonal solvers on systems derived from the thickness
+   if (World == 1 && K >= 2) {
+      const int NC = D.NCellsSize;
+      std::vector<int> Lo(NC, 0), Hi(NC, K - 1);
+      for (int i = 0; i < NC; ++i) { Lo[i] = i % 3 == 0 && K > 3 ? 1 : 0; Hi[i] = i % 5 == 0 && K > 3 ? K - 2 : K - 1; }
+      VertCoord VC(&Mesh, K, Lo.data(), Hi.data());
+      Eos Es(&Mesh, K);
+      Array2DReal HNow, Ct("ConservTemp", {NC, K}), Sa("AbsSalinity", {NC, K});
+      Array1DReal Surf("SurfacePressure", {NC}), Tid("TidalPotential", {NC}), Sal("SelfAttractionLoading", {NC});
+      State.getLayerThickness(HNow, 0);
+      std::vector<double> CtH((size_t)NC * K), SaH((size_t)NC * K), SurfH(NC), TidH(NC), SalH(NC), Wt(K), RefH((size_t)NC * K);
+      for (int i = 0; i < NC; ++i) {
+         SurfH[i] = 100.0 + i % 7; TidH[i] = 0.01 * (i % 11); SalH[i] = 0.002 * (i % 13);
+         for (int k = 0; k < K; ++k) {
+            CtH[(size_t)i * K + k] = 2.0 + 0.01 * (i % 100) + 0.5 * k;
+            SaH[(size_t)i * K + k] = 33.0 + 0.02 * (i % 50) + 0.1 * k;
+            RefH[(size_t)i * K + k] = H[(size_t)i * K + k] * 0.9;
+         }
+      }
+      for (int k = 0; k < K; ++k) Wt[k] = 1.0 + 0.1 * k;
+      Mesh.copyToDevice(OnCell, 1, K, CtH.data(), Ct.data());
+      Mesh.copyToDevice(OnCell, 1, K, SaH.data(), Sa.data());
+      Mesh.copyToDevice(OnCell, 1, 1, SurfH.data(), Surf.data());
+      Mesh.copyToDevice(OnCell, 1, 1, TidH.data(), Tid.data());
+      Mesh.copyToDevice(OnCell, 1, 1, SalH.data(), Sal.data());
+      Mesh.copyToDevice(OnCell, 1, K, RefH.data(), VC.RefLayerThickness.data());
+      OMEGA_B200_CHECK(omega_dev_upload(VC.VertCoordMovementWeights.data(), Wt.data(), K * sizeof(double)), "weights");
+      VC.computePressure(HNow, Surf);
+      std::vector<double> O1((size_t)NC * K), O2((size_t)NC * (K + 1));
+      // TEOS-10 takes dbar (Eos.h:36-48): Pa -> dbar on the host, as the reference's caller does
+      Array2DReal Pd("PressureDbar", {NC, K});
+      Mesh.copyToHost(OnCell, 1, K, VC.PressureMid.data(), O1.data());
+      for (double &v : O1) v *= 1.0e-4;
+      Mesh.copyToDevice(OnCell, 1, K, O1.data(), Pd.data());
+      Es.computeSpecVol(Ct, Sa, Pd);
+      Es.computeSpecVolDisp(Ct, Sa, Pd, 1);
+      VC.computeZHeight(HNow, Es.SpecVol);
+      VC.computeGeopotential(Tid, Sal);
+      VC.computeTargetThickness();
+      auto out2 = [&](const char *Nm, const Array2DReal &A, int W) {
+         std::vector<double> &O = W == K ? O1 : O2;
+         Mesh.copyToHost(OnCell, 1, W, A.data(), O.data());
+         save(Nm, O);
+      };
+      out2("out_pint", VC.PressureInterface, K + 1); out2("out_pmid", VC.PressureMid, K);
+      out2("out_specvol", Es.SpecVol, K); out2("out_specvol_disp", Es.SpecVolDisplaced, K);
+      out2("out_zint", VC.ZInterface, K + 1); out2("out_zmid", VC.ZMid, K);
+      out2("out_geop", VC.GeopotentialMid, K); out2("out_target", VC.LayerThicknessTarget, K);
+      // tridiagonal systems, one per cell, rows = levels: diffusion form with G from the thickness, and the
+      // general form of the same matrix
+      const int NB = D.NCellsAll;
+      Array2DReal G("G", {NB, K}), Hd("H", {NB, K}), X("X", {NB, K}), DL("DL", {NB, K}), Dd("D", {NB, K}), DU("DU", {NB, K}), X2("X2", {NB, K});
+      std::vector<double> g((size_t)NB * K), hd((size_t)NB * K), x((size_t)NB * K), dl((size_t)NB * K), dd((size_t)NB * K), du((size_t)NB * K);
+      for (int i = 0; i < NB; ++i)
+         for (int k = 0; k < K; ++k) {
+            const size_t o = (size_t)i * K + k;
+            g[o] = k + 1 < K ? 2.0 / (H[o] + H[o + 1]) * 50.0 : 0.0;
+            hd[o] = H[o] / 100.0;
+            x[o] = 1.0 + 0.01 * k + 0.001 * (i % 17);
+         }
+      for (int i = 0; i < NB; ++i)
+         for (int k = 0; k < K; ++k) {
+            const size_t o = (size_t)i * K + k;
+            const double gm = k > 0 ? g[o - 1] : 0.0, gp = k + 1 < K ? g[o] : 0.0;
+            dl[o] = -gm; du[o] = -gp; dd[o] = hd[o] + gm + gp;
+         }
+      const unsigned long long B = (unsigned long long)NB * K * sizeof(double);
+      omega_dev_upload(G.data(), g.data(), B); omega_dev_upload(Hd.data(), hd.data(), B); omega_dev_upload(X.data(), x.data(), B);
+      omega_dev_upload(DL.data(), dl.data(), B); omega_dev_upload(Dd.data(), dd.data(), B); omega_dev_upload(DU.data(), du.data(), B);
+      omega_dev_upload(X2.data(), x.data(), B);
+      TriDiagDiffSolver::solve(G, Hd, X);
+      TriDiagSolver::solve(DL, Dd, DU, X2);
+      omega_dev_sync(nullptr);
+      std::vector<double> xs((size_t)NB * K), xs2((size_t)NB * K);
+      omega_dev_download(xs.data(), X.data(), B); omega_dev_download(xs2.data(), X2.data(), B);
+      save("out_tridiag_diff", xs); save("out_tridiag", xs2);
+      save("in_tridiag_g", g); save("in_tridiag_h", hd); save("in_tridiag_x", x);
+   }
    std::printf("host mirror: %d steps, SimTime %.1f\n", NSteps, SimTime);
    return 0;
 }

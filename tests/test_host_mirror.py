@@ -132,3 +132,60 @@ def test_host_mirror_matches_oracle(tmp_path, stepper, fused):
         got = np.fromfile(os.path.join(d, nm + ".bin")).reshape(exp.shape)
         assert cases.rel_l2(got, exp) <= 1e-10, nm
     o.close()
+    _check_vertical_mirror(d, L, np.fromfile(os.path.join(d, "out_h.bin")).reshape(h.shape))
+
+
+def _check_vertical_mirror(d, L, hnow):
+    """OmegaB200Vertical.h (VertCoord, Eos, TriDiagSolver, TriDiagDiffSolver) in the C++ driver against the C oracle,
+    on the inputs the driver builds from the stepped thickness (tests/cpp/host_mirror_test.cpp)."""
+    import ctypes as C
+    from tests import oracle_lib
+    if not os.path.exists(oracle_lib.STRICT):
+        oracle_lib.build_oracle()
+    lib = C.CDLL(oracle_lib.STRICT)
+    P = lambda a: a.ctypes.data_as(capi.c_dbl_p)
+    PI = lambda a: a.ctypes.data_as(capi.c_int_p)
+    n, K = hnow.shape
+    i = np.arange(n)
+    lo = np.where((i % 3 == 0) & (K > 3), 1, 0).astype(np.int32)
+    hi = np.where((i % 5 == 0) & (K > 3), K - 2, K - 1).astype(np.int32)
+    k = np.arange(K)[None, :]
+    ct = 2.0 + 0.01 * (i % 100)[:, None] + 0.5 * k
+    sa = 33.0 + 0.02 * (i % 50)[:, None] + 0.1 * k
+    surf, tid, sal = 100.0 + i % 7, 0.01 * (i % 11), 0.002 * (i % 13)
+    ref_h, wt = np.ascontiguousarray(hnow * 0.9), 1.0 + 0.1 * np.arange(K)
+    rho0 = C.c_double(1026.0)
+    bot = np.ascontiguousarray(L.BottomDepth, np.float64)
+    pint, pmid = np.zeros((n, K + 1)), np.zeros((n, K))
+    lib.oracle_vert_pressure(n, K, PI(lo), PI(hi), rho0, P(hnow), P(np.ascontiguousarray(surf, np.float64)), P(pint), P(pmid))
+    pd = np.ascontiguousarray(pmid * 1.0e-4)
+    sv, svd = np.zeros((n, K)), np.zeros((n, K))
+    lib.oracle_eos_specvol(n, K, 1, 0, C.c_double(-0.2), C.c_double(0.8), C.c_double(1000.0), P(np.ascontiguousarray(ct)), P(np.ascontiguousarray(sa)), P(pd), P(sv))
+    lib.oracle_eos_specvol(n, K, 1, 1, C.c_double(-0.2), C.c_double(0.8), C.c_double(1000.0), P(np.ascontiguousarray(ct)), P(np.ascontiguousarray(sa)), P(pd), P(svd))
+    zint, zmid, geo, tgt = np.zeros((n, K + 1)), np.zeros((n, K)), np.zeros((n, K)), np.zeros((n, K))
+    lib.oracle_vert_zheight(n, K, PI(lo), PI(hi), rho0, P(bot), P(hnow), P(sv), P(zint), P(zmid))
+    lib.oracle_vert_geopotential(n, K, PI(lo), PI(hi), P(zmid), P(np.ascontiguousarray(tid, np.float64)), P(np.ascontiguousarray(sal, np.float64)), P(geo))
+    lib.oracle_vert_target(n, K, PI(lo), PI(hi), rho0, P(pint), P(ref_h), P(np.ascontiguousarray(wt)), P(tgt))
+    nall = int(L.NCellsAll)
+    active = (k >= lo[:, None]) & (k <= hi[:, None])
+    active[nall:] = False
+    act1 = np.zeros((n, K + 1), bool)
+    act1[:, :-1] |= active
+    act1[:, 1:] |= active
+    for nm, exp, m in (("out_pint", pint, act1), ("out_pmid", pmid, active), ("out_specvol", sv, None), ("out_specvol_disp", svd, None),
+                       ("out_zint", zint, act1), ("out_zmid", zmid, active), ("out_geop", geo, active), ("out_target", tgt, active)):
+        got = np.fromfile(os.path.join(d, nm + ".bin")).reshape(exp.shape)
+        if m is None:
+            m = np.zeros(exp.shape, bool)
+            m[:nall] = True
+        err = np.abs(got - exp)[m].max() / np.abs(exp[m]).max()
+        assert err <= 1e-12, (nm, err)
+    # tridiagonal solvers: the driver's systems, solved by the oracle's Thomas forms
+    g = np.fromfile(os.path.join(d, "in_tridiag_g.bin")).reshape(nall, K)
+    hd = np.fromfile(os.path.join(d, "in_tridiag_h.bin")).reshape(nall, K)
+    x = np.fromfile(os.path.join(d, "in_tridiag_x.bin")).reshape(nall, K)
+    xr, hh, al = x.copy(), hd.copy(), np.zeros((nall, K))
+    lib.oracle_tridiag_diffusion_thomas(nall, K, P(g), P(hh), P(xr), P(al))
+    for nm in ("out_tridiag_diff", "out_tridiag"):
+        got = np.fromfile(os.path.join(d, nm + ".bin")).reshape(nall, K)
+        assert np.abs(got - xr).max() / np.abs(xr).max() <= 1e-12, nm
