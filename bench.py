@@ -288,6 +288,10 @@ def main():
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if sampler else None
     launches = st.launch_count() - n0
+    halo_raw = None
+    if world > 1:
+        halo_raw = halo.profile()      # CUDA events around pack .. unpack on the exchange stream, timed region only
+        halo.set_profiling(False)
     # per-kernel breakdown: a second, shorter pass with CUDA events around every launch of the fused pipeline.
     # Kept out of the timed region: the events sit between the launches and switch off the overlap of
     # independent consecutive kernels (programmatic stream serialization, csrc/fused.cu)
@@ -306,8 +310,7 @@ def main():
     st.lib.omega_stepper_set_profiling(st.h, 0)
     halo_prof = None
     if world > 1:
-        hms, hrounds, hbytes = halo.profile()     # CUDA events around pack .. unpack on the exchange stream
-        halo.set_profiling(False)
+        hms, hrounds, hbytes = halo_raw
         t = torch.tensor([ms, hms / max(hrounds, 1), float(hbytes) / max(hrounds, 1)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t[0].item())
