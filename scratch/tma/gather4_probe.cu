@@ -1,3 +1,4 @@
+// build: nvcc -O2 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o gather4_probe gather4_probe.cu ; run: ./gather4_probe 1
 // probe: cp.async.bulk.tensor.2d tile::gather4 on sm_100a -- which box shape does the tensor map need, and how do the
 // four rows land in shared memory?  Also the plain 2D tile copy of 64 contiguous rows x 16 doubles.
 #include <cuda.h>
