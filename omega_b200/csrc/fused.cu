@@ -1003,7 +1003,8 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
    // and bottom drag all run on the tiled kernels (coefficient selection in the prologues, k_ms_sources,
    // k_edge_layer_terms).
    const bool tiledE = V == 2 && tile_edge_path_ok(D) && env_int("OMEGA_TILE_E", 1);
-   const bool tiled  = V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) && env_int("OMEGA_TILE", 1);
+   const bool tiled  = V == 2 && (T >= 2 || (T == 1 && (!tr4 || tile_v2_enabled()))) && tile_path_ok(D) && env_int("OMEGA_TILE", 1) &&
+                       (!tile_partial_chunk(D) || (tr4 && tile_v2_enabled()));
    const bool msOn = G.ManufacturedSolutionTendency != 0;
    const bool drag = G.BottomDragTendencyEnable != 0, wind = G.WindForcingTendencyEnable != 0;
    const Real nu2 = G.VelDiffTendencyEnable ? G.ViscDel2 : 0.0;

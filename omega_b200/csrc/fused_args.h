@@ -59,6 +59,7 @@ inline TileRange all_tiles(const DMesh &D) { return TileRange{nullptr, 0, D.Tile
 
 // fused_tile.cu
 bool tile_path_ok(const DMesh &D);
+bool tile_partial_chunk(const DMesh &D); // K is not a multiple of 16: only k_fCT2 / k_fET take the cell / edge pass
 bool tile_v2_enabled(); // k_fCT2 (any tracer count with tracer hyperdiffusion) is selectable
 bool tile_v2_used(const CellArgs &ca); // launch_fCT will run k_fCT2 for these arguments
 bool tile_edge_path_ok(const DMesh &D);

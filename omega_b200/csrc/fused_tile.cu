@@ -41,6 +41,7 @@
 // kernels of fused.cu and the kernel-per-term path; these stand in for the tile launchers there.
 namespace omega {
 bool tile_path_ok(const DMesh &) { return false; }
+bool tile_partial_chunk(const DMesh &) { return false; }
 bool tile_v2_enabled() { return false; }
 bool tile_v2_used(const CellArgs &) { return false; }
 bool tile_edge_path_ok(const DMesh &) { return false; }
@@ -666,10 +667,13 @@ __device__ __forceinline__ double2 tmem_unpack2(const unsigned (&r)[4]) {
    return v;
 }
 
-template <class C>
+template <class C, bool PART = false>
 __device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, int K, int r, const double *F, const void *Dst, int kc) {
    // item q = r + RT i of a row-set copy is row q/L, 16-byte piece q%L, and lands at byte 16 q
    const unsigned d = smem_u32(Dst) + 16u * r;
+   // last chunk of a level count that is not a multiple of KC: the pieces behind level K are not copied (their
+   // shared-memory lanes hold stale values that only threads of the same, inactive lanes ever read)
+   if (PART && kc + 2 * (r & (C::L - 1)) >= K) return;
 #pragma unroll
    for (int i = 0; i < (kTileRows * C::L + C::RT - 1) / C::RT; ++i) {
       const int row = (r >> C::LS) + i * (C::RT / C::L);
@@ -678,7 +682,7 @@ __device__ __forceinline__ void copy_rows_n(const typename C::Smem &S, int nR, i
 }
 
 // one item of the copy stream: a row set (h or a tracer) of level chunk kc into Dst; bar = its barrier (BULK)
-template <class C>
+template <class C, bool PART = false>
 __device__ __forceinline__ void issue_rows(typename C::Smem &S, int nR, int K, int r, int grow, const double *F, void *Dst, int kc,
                                            int bar) {
    if (C::TMAP) {
@@ -701,7 +705,7 @@ __device__ __forceinline__ void issue_rows(typename C::Smem &S, int nR, int K, i
       if (r == 0) mbar_expect_tx(b, (unsigned)nR * (C::KC * 8));
       if (r < nR) bulk_g2s(smem_u32(Dst) + r * (C::KC * 8), F + ((size_t)grow * K + kc), C::KC * 8, b);
    } else {
-      copy_rows_n<C>(S, nR, K, r, F, Dst, kc);
+      copy_rows_n<C, PART>(S, nR, K, r, F, Dst, kc);
       cp_commit();
    }
 }
@@ -722,7 +726,7 @@ template <class C> __device__ __forceinline__ void wait_h_one(typename C::Smem &
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // R role: copies (tracer i+3 while tracer i is worked on) and Del2 of the ring-1 rows
-template <class C>
+template <class C, bool PART = false>
 __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typename C::Smem &S, int c0, int nc, int n1, int nR,
                                        int NCh, int tid, bool Pf, int kb) {
    constexpr int KC = C::KC, L = C::L, RT = C::RT, NS = C::NS;
@@ -730,9 +734,9 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    const size_t CS = (size_t)M.NCellsSize * K;
    static_assert(!C::BULK || C::RT >= kTileRows, "bulk copies: one row per R thread");
    const int grow = r < nR ? S.GRow[r] : 0;
-   issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kb, NS); // kb: first level of this CTA's chunks
-   issue_rows<C>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], kb, 0);
-   if (T >= 2) issue_rows<C>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], kb, 1);
+   issue_rows<C, PART>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kb, NS); // kb: first level of this CTA's chunks
+   issue_rows<C, PART>(S, nR, K, r, grow, P.Trs, &S.Phi[0][0][0], kb, 0);
+   if (T >= 2) issue_rows<C, PART>(S, nR, K, r, grow, P.Trs + CS, &S.Phi[1][0][0], kb, 1);
    // T >= 3: tracer i+3 goes out in iteration i (then h and tracers 0..2 of the next chunk).  Shorter tracer
    // lists: h and the tracers of chunk c+1 go out in iterations 0, 1, .. of chunk c (four buffers hold two chunks)
    const bool shortT = T < 3;
@@ -743,7 +747,7 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
    const bool pfHcur = !(P.First && P.Hcur == P.Hs), pfHnext = !P.First || P.WSel;
    for (int c = 0; c < NCh; ++c) {
       const int it0 = c * T, kc = kb + c * KC;
-      if (c == 0 && !shortT) issue_rows<C>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], kb, 2);
+      if (c == 0 && !shortT) issue_rows<C, PART>(S, nR, K, r, grow, P.Trs + 2 * CS, &S.Phi[2][0][0], kb, 2);
       if (!C::BULK) { // h and tracer 0 of this chunk have landed (this thread's pieces)
          if (!shortT) cp_wait<2>();
          else if (T == 2) cp_wait<1>();
@@ -774,18 +778,18 @@ __device__ __forceinline__ void role_R(const DMesh &M, const CellArgs &P, typena
          __syncthreads();                              // iteration i: the T role has finished iteration i-1
          if (shortT) {
             if (c + 1 < NCh) {
-               if (i == 0) issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
-               else issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)(i - 1) * CS, &S.Phi[(it0 + T + i - 1) % NS][0][0], kc + KC, (it0 + T + i - 1) % NS);
+               if (i == 0) issue_rows<C, PART>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
+               else issue_rows<C, PART>(S, nR, K, r, grow, P.Trs + (size_t)(i - 1) * CS, &S.Phi[(it0 + T + i - 1) % NS][0][0], kc + KC, (it0 + T + i - 1) % NS);
             } else if (!C::BULK) cp_commit();
          } else {  // next item of the copy stream: a tracer of this chunk, then h and tracers 0..2 of the next
             const int n = i + 3;
-            if (n < T) issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc, (it0 + n) % NS);
+            if (n < T) issue_rows<C, PART>(S, nR, K, r, grow, P.Trs + (size_t)n * CS, &S.Phi[(it0 + n) % NS][0][0], kc, (it0 + n) % NS);
             else if (c + 1 < NCh) {
-               if (n == T) issue_rows<C>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
-               else issue_rows<C>(S, nR, K, r, grow, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % NS][0][0], kc + KC, (it0 + n - 1) % NS);
+               if (n == T) issue_rows<C, PART>(S, nR, K, r, grow, P.Hs, &S.H[0][0], kc + KC, NS);
+               else issue_rows<C, PART>(S, nR, K, r, grow, P.Trs + (size_t)(n - T - 1) * CS, &S.Phi[(it0 + n - 1) % NS][0][0], kc + KC, (it0 + n - 1) % NS);
             } else if (!C::BULK) cp_commit(); // keeps the group count of cp_wait<2> uniform
          }
-         if (i == 1 && c + 1 < NCh && Pf) {
+         if (i == 1 && c + 1 < NCh && Pf && (!PART || kc + 2 * KC <= K)) { // (a partial next chunk is not prefetched)
             // pull what the T role's next chunk prologue reads from global memory into L2:
             // six velocity rows per own cell, and the thickness operands
             for (int q = r; q < nc * 8; q += RT) {
@@ -982,14 +986,14 @@ __device__ __forceinline__ void stg_na(double *p, const double (&r)[2]) {
 // T role of k_fCT2
 // OPT: the optional terms (upwind flux options, manufactured thickness source) are compiled in; the default
 // instantiation keeps them out of the prologue's register budget
-template <class C, int STAGE, bool OPT>
+template <class C, int STAGE, bool OPT, bool PART = false>
 __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typename C::Smem &S, const TileCtx &X, int NCh, int tid,
                                         int kb) {
    constexpr bool First = STAGE == 0, Last = STAGE == 2;
    constexpr int KC = C::KC, NS = C::NS;
    const int K = M.K, T = P.NTracers, p = X.p, li = X.li;
    const size_t CS = (size_t)M.NCellsSize * K;
-   const bool own  = X.own;
+   const bool own  = X.own; // (shadowed per chunk below by own-cell-and-existing-level)
    load_tables<C::NT>(M, S, tid, X.nR1, X.nc);
    const int c = X.c0 + li;
    const unsigned myoff = X.myoff;
@@ -1005,7 +1009,9 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    // of chunk ch, where the registers of the tracer coefficients are free again.
    double us[kME][2], hcur[2] = {0, 0}, hnext_old[2] = {1.0, 1.0};
    auto load_prologue = [&](int ch) {
-      const int k = kb + ch * KC + 2 * p;
+      // (lanes behind level K in the last chunk of a level count that is not a multiple of KC load row K-2 and
+      // never store)
+      const int k = PART ? min(kb + ch * KC + 2 * p, K - 2) : kb + ch * KC + 2 * p;
       int e[kME];
 #pragma unroll
       for (int j = 0; j < kME; ++j) e[j] = ch == 0 ? M.Tiles.EocCell[(size_t)c * 6 + j] : S.Eoc[li][j];
@@ -1021,8 +1027,10 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
 #define OMEGA_T2_HOIST 0
 #endif
    if (OMEGA_T2_HOIST) load_prologue(0);
+   const bool ownTile = X.own;
    for (int ch = 0; ch < NCh; ++ch) {
-      const int k = kb + ch * KC + 2 * p, it0 = ch * T;
+      const int kraw = kb + ch * KC + 2 * p, k = PART ? min(kraw, K - 2) : kraw, it0 = ch * T;
+      const bool own = ownTile && (!PART || kraw < K); // own cell AND an existing level: loads its operands, stores results
       const size_t o = (size_t)c * K + k;
       if (!OMEGA_T2_HOIST) load_prologue(ch); // in flight while h lands
       __syncthreads(); // h and tracer 0 of this chunk are in shared memory; tables are visible
@@ -1086,8 +1094,8 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
             const double g    = S.G[li][j];
             const double chj = -k4 * g, ga = -InvA * g;
             SH -= chj;
-            if (own && p == (j & (C::L - 1))) S.Ch[li][j] = chj;
-            if (j == kME - 1 && own && p == C::L - 1) S.SHc[li] = SH;
+            if (ownTile && p == (j & (C::L - 1))) S.Ch[li][j] = chj; // (level independent: written by inactive lanes too)
+            if (j == kME - 1 && ownTile && p == C::L - 1) S.SHc[li] = SH;
             cfA[j][0] = ga * (0.5 * (hs.x + hn2.x));
             cfA[j][1] = ga * (0.5 * (hs.y + hn2.y));
          }
@@ -1326,7 +1334,7 @@ __device__ __forceinline__ void role_T2(const DMesh &M, const CellArgs &P, typen
    }
 }
 
-template <class C, int STAGE, bool OPT>
+template <class C, int STAGE, bool OPT, bool PART = false>
 __global__ void __launch_bounds__(C::NT, C::CTAs)
 k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR, const __grid_constant__ CUtensorMap MapH,
        const __grid_constant__ CUtensorMap MapT) {
@@ -1374,14 +1382,14 @@ k_fCT2(DMesh M, CellArgs P, int NChAll, int Pf, int NWhole, TileRange TR, const 
       } else {
          if (C::RS == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
          else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-         role_R<C>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
+         role_R<C, PART>(M, P, S, X.c0, X.nc, X.n1, X.nR, NCh, tid, Pf != 0, kb);
       }
    } else {
       asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
       X.t = tid; X.i = tid >> C::LS; X.p = tid & (C::L - 1);
       X.own = X.i < X.nc; X.li = X.own ? X.i : 0;
       X.myoff = (X.li * C::KC + 2 * X.p) * 8u;
-      role_T2<C, STAGE, OPT>(M, P, S, X, NCh, tid, kb);
+      role_T2<C, STAGE, OPT, PART>(M, P, S, X, NCh, tid, kb);
    }
    if (C::TM) {
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -1421,7 +1429,8 @@ template <class C, int STAGE, bool OPT> static int launch_fCT2_o(const DMesh &D,
    // one CTA per tile; the tiles of the last partial round of CTAs are split into one CTA per chunk when
    // that shortens the tail (matters on multi-GPU partitions with ~10 rounds)
    const int split = env_i("OMEGA_TILE_SPLIT", 1);
-   const int nch = D.K / C::KC, nt = TR.Count;
+   const int nch = (D.K + C::KC - 1) / C::KC, nt = TR.Count; // the last chunk may be partial (even level counts)
+   OMEGA_REQUIRE(D.K % C::KC == 0 || (!C::BULK && !C::PAIR && !C::TM), "k_fCT2: a partial last chunk needs the default copy path");
    if (nt <= 0) return 0;
    int whole = nt;
    if (split && nch > 1) {
@@ -1435,6 +1444,14 @@ template <class C, int STAGE, bool OPT> static int launch_fCT2_o(const DMesh &D,
    if constexpr (C::TMAP) {
       if (encode_row_map(&mapH, ca.Hs, D.NCellsSize, D.K, C::KC)) return 1;
       if (encode_row_map(&mapT, ca.Trs, (long long)ca.NTracers * D.NCellsSize, D.K, C::KC)) return 1;
+   }
+   if constexpr (!C::BULK && !C::PAIR && !C::TM) {
+      if (D.K % C::KC != 0) { // the last chunk is partial: the masked instantiation
+         static DevOnce oncePart;
+         if (set_smem_once(oncePart, k_fCT2<C, STAGE, OPT, true>, sizeof(typename C::Smem))) return 1;
+         k_fCT2<C, STAGE, OPT, true><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR, mapH, mapT);
+         return 0;
+      }
    }
    k_fCT2<C, STAGE, OPT><<<(unsigned)(whole + (nt - whole) * nch), C::NT, sizeof(typename C::Smem), St>>>(D, ca, nch, pf, whole, TR, mapH, mapT);
    return 0;
@@ -1466,6 +1483,7 @@ template <bool HYP, int STAGE, int RS> static int launch_fCT_r(const DMesh &D, c
    static DevOnce once;
    if (set_smem_once(once, k_fCT<HYP, STAGE, RS>, sizeof(TileSmem))) return 1;
    OMEGA_REQUIRE(!HYP || ca.NTracers >= 2, "k_fCT with tracer hyperdiffusion needs at least two tracers");
+   OMEGA_REQUIRE(D.K % kTKC == 0, "k_fCT needs a level count that is a multiple of 16");
    const int nch = D.K / kTKC;
    // with the D role (which needs two tracers to prime its pipeline) a CTA walks all chunks of its tile
    const int persist = env_i("OMEGA_TILE_PERSIST", 1);
@@ -1491,7 +1509,10 @@ int launch_fCT(const DMesh &D, const CellArgs &ca, cudaStream_t St, const TileRa
    return stage == 0 ? launch_fCT_t<false, 0>(D, ca, St, TR) : stage == 1 ? launch_fCT_t<false, 1>(D, ca, St, TR) : launch_fCT_t<false, 2>(D, ca, St, TR);
 }
 
-bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % kTKC == 0; }
+// Level counts: any even K.  A K that is not a multiple of 16 ends in a partial chunk, which k_fCT2 and k_fET mask
+// (tile_partial_chunk); the older k_fCT (tracer hyperdiffusion off) needs whole chunks.
+bool tile_path_ok(const DMesh &D) { return D.Tiles.NTiles > 0 && D.K % 2 == 0 && D.K >= 2; }
+bool tile_partial_chunk(const DMesh &D) { return D.K % kTKC != 0; }
 bool tile_v2_enabled() { return env_i("OMEGA_TILE_V2", 1) != 0; }
 // k_fCT2 serves every tracer count with tracer hyperdiffusion on
 bool tile_v2_used(const CellArgs &ca) { return ca.HypOn && tile_v2_enabled() && ca.NTracers >= 1; }
@@ -1520,7 +1541,7 @@ struct ETileSmem {
    TileHdr Hdr;
 };
 
-template <bool OPT> // OPT: upwinded flux thickness, manufactured velocity source
+template <bool OPT, bool PART = false> // OPT: upwinded flux thickness, manufactured velocity source; PART: masked last chunk
 __global__ void __launch_bounds__(kEThreads, 2)
 k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
    extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1543,7 +1564,9 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
       for (int q = tid; q < nOwn * 5; q += kEThreads) dst[q] = src[q];
    }
    __syncthreads();
-   const int p = tid & 7, k = kc0 + 2 * p;
+   // (last chunk of a level count that is not a multiple of 16: lanes behind level K load row K-2 and store nothing)
+   const int p = tid & 7, kraw = kc0 + 2 * p, k = PART ? min(kraw, K - 2) : kraw;
+   const bool kin = !PART || kraw < K;
    if (Pf & 1) {
       // the eight gathered rows of pass 2a (X, Y of both cells, Z of both vertices, u_cur, u_next) of this
       // thread's own edges: one of the eight lanes of an edge each, pulled into L2 while pass 1 runs
@@ -1645,7 +1668,7 @@ k_fET(DMesh M, EdgeTileArgs P, int NChunks, int Pf, int Ahead, TileRange TR) {
 #pragma unroll
    for (int it = 0; it < kItems; ++it) {
       const int r = (tid >> 3) + it * (kEThreads / kTLanes);
-      if (r < nOwn) {
+      if (r < nOwn && kin) {
          const int e    = S.SRow[r];
          const size_t o = (size_t)e * K + k;
          double acc0 = 0, acc1 = 0;
@@ -1684,12 +1707,20 @@ int launch_fET(const DMesh &D, const EdgeTileArgs &ea, cudaStream_t St, const Ti
    int sm = 0;
    const bool opt = ea.FluxUpwind || ea.SrcU;
    if (opt ? set_smem_once(onceOpt, k_fET<true>, sizeof(ETileSmem), &sm) : set_smem_once(once, k_fET<false>, sizeof(ETileSmem), &sm)) return 1;
-   const int nch = D.K / kTKC;
+   const int nch = (D.K + kTKC - 1) / kTKC; // the last chunk may be partial
    // L2 prefetch of the CTA's own pass-2a rows.  (Also tried: the pass-1 rows of the tile a CTA of the NEXT wave
    // takes, requested one wave ahead -- 2.36 -> 2.85 ms on config 3, the extra requests cost more than the
    // latency they hide; removed.)
    const int pf = env_i("OMEGA_TILE_EPF", 1);
    const int ahead = env_i("OMEGA_TILE_EAHEAD", (2 * sm + nch - 1) / nch);
+   if (D.K % kTKC != 0) { // the last chunk is partial: the masked instantiations
+      static DevOnce oncePart, oncePartOpt;
+      if (opt ? set_smem_once(oncePartOpt, k_fET<true, true>, sizeof(ETileSmem)) : set_smem_once(oncePart, k_fET<false, true>, sizeof(ETileSmem)))
+         return 1;
+      if (opt) k_fET<true, true><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
+      else k_fET<false, true><<<(unsigned)TR.Count * nch, kEThreads, sizeof(ETileSmem), St>>>(D, ea, nch, pf, ahead, TR);
+      return 0;
+   }
    if (Overlap) {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)TR.Count * nch);

@@ -38,9 +38,13 @@ CASES = {
     # k_fCT2 eight times per chunk; 80 levels are five chunks (copy stream index it0 = chunk * T)
     "sphere3_K64_T32": lambda: cases.sphere_case(3, 64, 32),
     "sphere3_K80_T2": lambda: cases.sphere_case(3, 80, 2),
+    # level counts that are not multiples of 16: the last chunk of the tile kernels is partial (masked lanes).
+    # 60 = 3 chunks + 12 levels, 24 = 1 chunk + 8 levels; K = 4 and K = 10 above are a single partial chunk
+    "sphere3_K60_T2": lambda: cases.sphere_case(3, 60, 2),
+    "sphere3_K24_T3": lambda: cases.sphere_case(3, 24, 3),
 }
 TILED = {"sphere4_K16_T3", "plane16_K32_T2", "sphere3_K16_T1", "sphere3_K16_T2_nodel4", "sphere3_K64_T32",
-         "sphere3_K80_T2", "sphere3_K64_T3"}
+         "sphere3_K80_T2", "sphere3_K64_T3", "sphere3_K60_T2", "sphere3_K24_T3", "sphere3_K4_T2", "plane12_K10_T2"}
 
 
 @pytest.fixture(scope="module", params=list(CASES))
