@@ -985,17 +985,23 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
    const bool vel4 = G.VelHyperDiffTendencyEnable, tr4 = G.TracerHyperDiffTendencyEnable && T > 0;
    const bool upw = G.FluxThicknessType || G.FluxTracerType;
    // sweep iterations per CTA (tuning knobs, defaults from profiles/r01 measurements)
-   const int itA = env_int("OMEGA_ITERS_A", 1), itB = env_int("OMEGA_ITERS_B", 2), itT = env_int("OMEGA_ITERS_T2", 1),
-             itC = env_int("OMEGA_ITERS_C", 1), itE = env_int("OMEGA_ITERS_E", 8);
-   const unsigned gc = fused_grid(D.NCellsAll, D.K, V, kBlock, itC), ge = fused_grid(D.NEdgesAll, D.K, V, kBlock, itE);
-   const unsigned gA = fused_grid(D.NCellsAll, D.K, V, kBlock, itA), gB = fused_grid(D.NCellsAll, D.K, V, kBlock, itB),
-                  gT = fused_grid(D.NCellsAll, D.K, V, kBlock, itT);
+   // A mesh with fewer (row, level-vector) items than two 256-thread CTAs per SM (config 1: 4 096 cells x 1
+   // level) is bound by the latency of each thread's dependent gathers: 64-thread CTAs, one sweep iteration,
+   // put the same threads on four times as many SMs.
+   const bool small = (long long)D.NCellsAll * (D.K / V) < 2LL * 148 * kBlock && env_int("OMEGA_SMALL_MESH", 1);
+   const int blk = small ? 64 : kBlock;
+   const int itA = small ? 1 : env_int("OMEGA_ITERS_A", 1), itB = small ? 1 : env_int("OMEGA_ITERS_B", 2),
+             itT = small ? 1 : env_int("OMEGA_ITERS_T2", 1), itC = small ? 1 : env_int("OMEGA_ITERS_C", 1),
+             itE = small ? 1 : env_int("OMEGA_ITERS_E", 8);
+   const unsigned gc = fused_grid(D.NCellsAll, D.K, V, blk, itC), ge = fused_grid(D.NEdgesAll, D.K, V, blk, itE);
+   const unsigned gA = fused_grid(D.NCellsAll, D.K, V, blk, itA), gB = fused_grid(D.NCellsAll, D.K, V, blk, itB),
+                  gT = fused_grid(D.NCellsAll, D.K, V, blk, itT);
 #define LAUNCH_V(KIND, KERNEL, GRID, ...)                               \
    do {                                                                 \
       ScopedTimer tm_(S, St, KIND);                                     \
       NvtxRange nv_(#KERNEL);                                           \
-      if (V == 2) KERNEL<2><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);       \
-      else KERNEL<1><<<GRID, kBlock, 0, St>>>(__VA_ARGS__);              \
+      if (V == 2) KERNEL<2><<<GRID, blk, 0, St>>>(__VA_ARGS__);          \
+      else KERNEL<1><<<GRID, blk, 0, St>>>(__VA_ARGS__);                 \
       ++S->Launches;                                                    \
    } while (0)
    // shared-memory staged passes (fused_tile.cu) replace fT2 + fC and fE when they apply; fA / fB then write
@@ -1065,7 +1071,9 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
       if (tiled) {
          if (launch_fCT(D, ca, St, trBnd)) return 1;
       } else if (upw) {
-         if (V == 2) k_fC<2, true><<<gc, kBlock, 0, St>>>(D, ca); else k_fC<1, true><<<gc, kBlock, 0, St>>>(D, ca);
+         if (V == 2) k_fC<2, true><<<gc, blk, 0, St>>>(D, ca); else k_fC<1, true><<<gc, blk, 0, St>>>(D, ca);
+      } else if (small) {
+         if (V == 2) k_fC_center<2, 512, 1><<<gc, blk, 0, St>>>(D, ca); else k_fC_center<1, 512, 1><<<gc, blk, 0, St>>>(D, ca);
       } else if (V == 1) {
          k_fC_center<1, 512, 1><<<fused_grid(D.NCellsAll, D.K, 1, 512, itC), 512, 0, St>>>(D, ca);
       } else if (variant == 0) {
@@ -1098,7 +1106,7 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
       NvtxRange nv_("k_fA");
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(gA);
-      cfg.blockDim = dim3(kBlock);
+      cfg.blockDim = dim3(blk);
       cfg.stream = St;
       cudaLaunchAttribute at[1];
       at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -1152,10 +1160,10 @@ static int run_stage(OmegaStepper *S, const StageDesc &sd, const Real *Hcur, con
       const int fev = env_int("OMEGA_FE_VARIANT", 3);
       ScopedTimer tm_(S, St, kFE);
       NvtxRange nv_("edge pass");
-      if (V == 1) k_fE<1, 2><<<ge, kBlock, 0, St>>>(D, ea);
-      else if (fev == 2) k_fE<2, 3><<<ge, kBlock, 0, St>>>(D, ea);
-      else if (fev == 3) k_fE<2, 4><<<ge, kBlock, 0, St>>>(D, ea);
-      else k_fE<2, 2><<<ge, kBlock, 0, St>>>(D, ea);
+      if (V == 1) k_fE<1, 2><<<ge, blk, 0, St>>>(D, ea);
+      else if (fev == 2) k_fE<2, 3><<<ge, blk, 0, St>>>(D, ea);
+      else if (fev == 3) k_fE<2, 4><<<ge, blk, 0, St>>>(D, ea);
+      else k_fE<2, 2><<<ge, blk, 0, St>>>(D, ea);
       ++S->Launches;
    }
    if (split) {
