@@ -251,7 +251,9 @@ int omega_tend_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
  * Fused=1 has no place for a host custom-tendency std::function (src/ocn/Tendencies.h:51-53,
  * Tendencies.cpp:288-293,416-421): the built-in manufactured terms are the only custom terms the fused
  * kernels evaluate; a host that installs its own must step with Fused=0 through
- * omega_tend_* + its callback. */
+ * omega_tend_* + its callback.
+ * After one warm-up step with the same stepper and configuration the call allocates nothing and never
+ * synchronises (Halo == NULL, profiling off): a caller may capture it in a CUDA graph (scratch/probe_graph.py). */
 int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,
                           const OmegaStepCoeffs *Coeffs, OmegaHalo *Halo, int Fused,
                           int RawTimeLevelCompat, void *Stream);
