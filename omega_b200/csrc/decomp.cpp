@@ -256,7 +256,8 @@ int omega_decomp_create(const OmegaGlobalMesh *G, const int *CellTask, int NTask
          D->Loc[k][2 * i] = o; D->Loc[k][2 * i + 1] = a;
          if (i >= L.NOwned[k] && o != MyTask) { recv[k][o].push_back(i); nbset.insert(o); } // ascending local index
       }
-      D->Loc[k][2 * nAll] = MyTask; D->Loc[k][2 * nAll + 1] = nAll;
+      // boundary slot: (task, NAll) for edges and vertices; the reference never writes the cell entry (zero)
+      if (k != 0) { D->Loc[k][2 * nAll] = MyTask; D->Loc[k][2 * nAll + 1] = nAll; }
       // what the others receive from me, in THEIR halo order, as MY local indices = my owned index
       for (auto &kv : nbr) {
          const LocalOrder &N = kv.second;

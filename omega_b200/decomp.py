@@ -149,6 +149,9 @@ def build_local(mesh: Mesh, cell_task: np.ndarray, task: int, nlev: int,
         return np.concatenate([ids + 1, [nglob + 1]]).astype(np.int32)  # 1-based IDs
 
     L.CellID, L.EdgeID, L.VertexID = ids_padded(cell_ids, nC), ids_padded(edge_ids, nE), ids_padded(vert_ids, nV)
+    # the reference never writes the boundary-slot entry of CellID / CellLoc (Decomp.cpp:1081-1098: Kokkos leaves it
+    # zero), unlike those of the edge and vertex arrays; tests/test_decomp_vs_reference.py compares every entry
+    L.CellID[-1] = 0
 
     # owner address (task, local index on owner) -- CellLoc / EdgeLoc / VertexLoc
     def loc_table(ids, owner, n_all, owned_rank_of):
@@ -159,6 +162,7 @@ def build_local(mesh: Mesh, cell_task: np.ndarray, task: int, nlev: int,
         return loc
 
     L.CellLoc = loc_table(cell_ids, cell_task, n_cells_all, loc_on_owner)
+    L.CellLoc[-1] = 0
     L._edge_owner, L._vert_owner = edge_owner[edge_ids], vert_owner[vert_ids]
 
     # global -> local maps; everything else -> boundary slot
@@ -346,6 +350,7 @@ def build_local_lib(mesh: Mesh, cell_task: np.ndarray, task: int, nlev: int, hal
     L.NCellsGlobal, L.NEdgesGlobal, L.NVerticesGlobal = nC, nE, nV
     pad = lambda i, n: np.concatenate([i + 1, [n + 1]]).astype(np.int32)
     L.CellID, L.EdgeID, L.VertexID = pad(cell_ids, nC), pad(edge_ids, nE), pad(vert_ids, nV)
+    L.CellID[-1] = 0     # as the reference leaves it (see build_local)
     L.CellLoc, L.EdgeLoc, L.VertexLoc = loc
     (L.CellsOnCell, L.EdgesOnCell, L.VerticesOnCell, L.CellsOnEdge, L.VerticesOnEdge, L.EdgesOnEdge,
      L.CellsOnVertex, L.EdgesOnVertex) = conn

@@ -1,0 +1,112 @@
+// ref_decomp_driver.cpp -- TEST INFRASTRUCTURE.  Runs the reference's own Decomp constructor
+// (src/base/Decomp.cpp:445-760, compiled unmodified over decomp_shim.h) as NTasks threads of one process on a
+// global mesh held in memory, with the cell partition supplied by the caller, and hands every task's local
+// numbering back through a C interface (tests/test_decomp_vs_reference.py).
+#define private public // the constructor is private (Decomp::create would store the object in a static map)
+#include "Decomp.h"
+#undef private
+
+#include <thread>
+
+using namespace OMEGA;
+
+static std::vector<std::unique_ptr<Decomp>> g_decomps;
+static const int *g_cell_task = nullptr;
+static int g_ncells = 0;
+
+extern "C" int METIS_PartGraphKway(idx_t *nvtxs, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, real_t *, real_t *,
+                                   idx_t *, idx_t *edgecut, idx_t *part) {
+   for (int i = 0; i < *nvtxs; ++i) part[i] = g_cell_task[i];
+   *edgecut = 0;
+   return METIS_OK;
+}
+extern "C" int ParMETIS_V3_PartKway(idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, idx_t *, real_t *, real_t *,
+                                    idx_t *, idx_t *, idx_t *, MPI_Comm *) {
+   std::fprintf(stderr, "ref_decomp: the ParMETIS method is not emulated\n");
+   std::abort();
+}
+
+extern "C" {
+
+// Connectivity as a mesh file holds it: 1-based global IDs, 0 = none.
+int ref_decomp_run(int NTasks, int HaloWidth, int NCells, int NEdges, int NVertices, int MaxEdges, int VertexDegree,
+                   const int *CellsOnCell, const int *EdgesOnCell, const int *VerticesOnCell, const int *CellsOnEdge,
+                   const int *EdgesOnEdge, const int *VerticesOnEdge, const int *CellsOnVertex, const int *EdgesOnVertex,
+                   const int *CellTask) {
+   static bool kokkos = false;
+   if (!kokkos) {
+      Kokkos::initialize();
+      kokkos = true;
+   }
+   IO::RefMeshFile &F = IO::RefMeshFile::get();
+   F.Dims = {{"NCells", NCells}, {"NEdges", NEdges}, {"NVertices", NVertices}, {"MaxEdges", MaxEdges},
+             {"VertexDegree", VertexDegree}, {"MaxCellsOnEdge", 2}};
+   F.Arrays = {{"CellsOnCell", CellsOnCell}, {"EdgesOnCell", EdgesOnCell}, {"VerticesOnCell", VerticesOnCell},
+               {"CellsOnEdge", CellsOnEdge}, {"EdgesOnEdge", EdgesOnEdge}, {"VerticesOnEdge", VerticesOnEdge},
+               {"CellsOnVertex", CellsOnVertex}, {"EdgesOnVertex", EdgesOnVertex}};
+   g_cell_task = CellTask;
+   g_ncells    = NCells;
+   RefDecompWorld &W = RefDecompWorld::get();
+   W.NumTasks = NTasks;
+   W.Arrived  = 0;
+   g_decomps.clear();
+   g_decomps.resize(NTasks);
+   std::vector<MachEnv> envs;
+   for (int t = 0; t < NTasks; ++t) envs.emplace_back(t, NTasks);
+   std::vector<std::thread> th;
+   for (int t = 0; t < NTasks; ++t)
+      th.emplace_back([&, t] {
+         g_decomps[t].reset(new Decomp("RefDecomp" + std::to_string(t), &envs[t], NTasks, PartMethodMetisKWay, HaloWidth, "memory"));
+      });
+   for (auto &x : th) x.join();
+   return 0;
+}
+
+// {NOwned, NAll, NHalo(0 .. HaloWidth-1)} for cells, edges, vertices: 3 * (2 + HaloWidth) ints
+int ref_decomp_counts(int Task, int *Out) {
+   const Decomp &D = *g_decomps[Task];
+   const int HW = D.HaloWidth;
+   int *o = Out;
+   *o++ = D.NCellsOwned; *o++ = D.NCellsAll;
+   for (int h = 0; h < HW; ++h) *o++ = D.NCellsHaloH(h);
+   *o++ = D.NEdgesOwned; *o++ = D.NEdgesAll;
+   for (int h = 0; h < HW; ++h) *o++ = D.NEdgesHaloH(h);
+   *o++ = D.NVerticesOwned; *o++ = D.NVerticesAll;
+   for (int h = 0; h < HW; ++h) *o++ = D.NVerticesHaloH(h);
+   return 0;
+}
+
+// Which: 0 CellID, 1 EdgeID, 2 VertexID [N*Size]; 3 CellLoc, 4 EdgeLoc, 5 VertexLoc [N*Size][2];
+// 10 CellsOnCell, 11 EdgesOnCell, 12 VerticesOnCell [NCellsSize][MaxEdges]; 13 CellsOnEdge, 14 VerticesOnEdge
+// [NEdgesSize][2]; 15 EdgesOnEdge [NEdgesSize][2 MaxEdges]; 16 CellsOnVertex, 17 EdgesOnVertex
+// [NVerticesSize][VertexDegree]; 18 NEdgesOnCell [NCellsSize]; 19 NEdgesOnEdge [NEdgesSize].  Returns the count.
+int ref_decomp_get(int Task, int Which, int *Out) {
+   const Decomp &D = *g_decomps[Task];
+   auto c1 = [&](const HostArray1DI4 &A) { const int n = (int)A.extent(0); if (Out) for (int i = 0; i < n; ++i) Out[i] = A(i); return n; };
+   auto c2 = [&](const HostArray2DI4 &A) {
+      const int n = (int)A.extent(0), m = (int)A.extent(1);
+      if (Out) for (int i = 0; i < n; ++i) for (int j = 0; j < m; ++j) Out[i * m + j] = A(i, j);
+      return n * m;
+   };
+   switch (Which) {
+   case 0: return c1(D.CellIDH);
+   case 1: return c1(D.EdgeIDH);
+   case 2: return c1(D.VertexIDH);
+   case 3: return c2(D.CellLocH);
+   case 4: return c2(D.EdgeLocH);
+   case 5: return c2(D.VertexLocH);
+   case 10: return c2(D.CellsOnCellH);
+   case 11: return c2(D.EdgesOnCellH);
+   case 12: return c2(D.VerticesOnCellH);
+   case 13: return c2(D.CellsOnEdgeH);
+   case 14: return c2(D.VerticesOnEdgeH);
+   case 15: return c2(D.EdgesOnEdgeH);
+   case 16: return c2(D.CellsOnVertexH);
+   case 17: return c2(D.EdgesOnVertexH);
+   case 18: return c1(D.NEdgesOnCellH);
+   case 19: return c1(D.NEdgesOnEdgeH);
+   }
+   return -1;
+}
+
+} // extern "C"

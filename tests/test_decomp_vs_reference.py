@@ -1,0 +1,79 @@
+"""Pins the multi-task local numbering against the REFERENCE ITSELF: src/base/Decomp.cpp, compiled unmodified over
+oracle/ref_decomp/decomp_shim.h and run as N tasks = N threads of one process (Broadcast = thread rendezvous, the mesh
+file = memory, METIS = the partition handed in).  Every count, halo-layer count, global ID, owner address and local
+connectivity entry of every task must equal both the numpy restatement (omega_b200/decomp.py) and the compiled
+Decomp of the library (csrc/decomp.cpp) -- including the boundary-slot entries.  This is what SURVEY.md 3.5 P4 (reverse
+first-halo edge order etc.) and VERDICT r1 called parity unpinned."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from omega_b200 import decomp
+from tests import cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref", "libomega_ref_decomp.so")
+ip = C.POINTER(C.c_int)
+P = lambda a: a.ctypes.data_as(ip)
+NAMES = {0: "CellID", 1: "EdgeID", 2: "VertexID", 3: "CellLoc", 4: "EdgeLoc", 5: "VertexLoc", 10: "CellsOnCell",
+         11: "EdgesOnCell", 12: "VerticesOnCell", 13: "CellsOnEdge", 14: "VerticesOnEdge", 15: "EdgesOnEdge",
+         16: "CellsOnVertex", 17: "EdgesOnVertex", 18: "NEdgesOnCell", 19: "NEdgesOnEdge"}
+
+
+def ref_lib():
+    if not os.path.exists(REF):
+        mk = os.path.join(ROOT, "oracle", "ref_decomp")
+        if not os.path.isdir("/root/reference/components/omega/src"):
+            pytest.skip("oracle/_ref/libomega_ref_decomp.so not built and /root/reference absent")
+        import subprocess
+        subprocess.run(["make", "-s", "-C", mk], check=True)
+    return C.CDLL(REF)
+
+
+def run_reference(lib, m, ntasks, hw, task):
+    """the reference's Decomp on ntasks thread-tasks; file conventions: 1-based IDs, 0 = none"""
+    a = {n: np.ascontiguousarray(np.asarray(m[n]) + 1, np.int32) for n in (
+        "cellsOnCell", "edgesOnCell", "verticesOnCell", "cellsOnEdge", "edgesOnEdge", "verticesOnEdge", "cellsOnVertex", "edgesOnVertex")}
+    assert m.maxEdges2 == 2 * m.maxEdges
+    task = np.ascontiguousarray(task, np.int32)
+    rc = lib.ref_decomp_run(ntasks, hw, m.nCells, m.nEdges, m.nVertices, m.maxEdges, m.vertexDegree, P(a["cellsOnCell"]),
+                            P(a["edgesOnCell"]), P(a["verticesOnCell"]), P(a["cellsOnEdge"]), P(a["edgesOnEdge"]),
+                            P(a["verticesOnEdge"]), P(a["cellsOnVertex"]), P(a["edgesOnVertex"]), P(task))
+    assert rc == 0
+    out = []
+    for t in range(ntasks):
+        cnt = np.zeros(3 * (2 + hw), np.int32)
+        lib.ref_decomp_counts(t, P(cnt))
+        d = {"counts": cnt.reshape(3, 2 + hw)}
+        for w, nm in NAMES.items():
+            n = lib.ref_decomp_get(t, w, None)
+            v = np.zeros(n, np.int32)
+            lib.ref_decomp_get(t, w, P(v))
+            d[nm] = v
+        out.append(d)
+    return out
+
+
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3)])
+def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
+    lib = ref_lib()
+    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    task = decomp.partition_cells(m, ntasks) if ntasks > 1 else np.zeros(m.nCells, np.int32)
+    ref = run_reference(lib, m, ntasks, hw, task)
+    locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
+    have_lib = os.path.exists(os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200.so"))
+    for t in range(ntasks):
+        R = ref[t]
+        ours = [("numpy restatement", locs[t])]
+        if have_lib:
+            ours.append(("csrc/decomp.cpp", decomp.build_local_lib(m, np.ascontiguousarray(task, np.int32), t, 3, hw)[0]))
+        for label, L in ours:
+            for k, nm in enumerate(("Cells", "Edges", "Vertices")):
+                assert int(L["N%sOwned" % nm]) == R["counts"][k, 0] and int(L["N%sAll" % nm]) == R["counts"][k, 1], (label, t, nm)
+                assert np.array_equal(np.asarray(L["N%sHalo" % nm]), R["counts"][k, 2:]), (label, t, nm, "halo layers")
+            for nm in NAMES.values():
+                a, b = R[nm], np.asarray(L[nm]).astype(np.int32).ravel()
+                assert a.size == b.size and np.array_equal(a, b), (label, t, nm, int(np.argmax(a != b)) if a.size == b.size else "size")
