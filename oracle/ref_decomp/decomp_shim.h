@@ -7,8 +7,10 @@
 //                readArray gathers through the offsets of the linear decomposition Decomp.cpp itself builds;
 //   METIS_PartGraphKway   returns the partition handed in by the driver (METIS is third party and absent; the
 //                result on owned elements does not depend on the partition).
-// Everything that numbers cells, edges and vertices, builds the halos and the local connectivity is the reference's
-// code.  Used by tests/test_decomp_vs_reference.py to pin omega_b200/csrc/decomp.cpp on several tasks.
+//   mpi.h        (this directory) the few MPI calls of src/base/Halo.cpp over the same threads.
+// Everything that numbers cells, edges and vertices, builds the halos, the local connectivity and the exchange lists
+// is the reference's code.  Used by tests/test_decomp_vs_reference.py to pin omega_b200/csrc/decomp.cpp and the halo
+// lists on several tasks.
 #pragma once
 
 #define OMEGA_MACH_ENV_H

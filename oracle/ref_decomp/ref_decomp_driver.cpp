@@ -2,8 +2,9 @@
 // (src/base/Decomp.cpp:445-760, compiled unmodified over decomp_shim.h) as NTasks threads of one process on a
 // global mesh held in memory, with the cell partition supplied by the caller, and hands every task's local
 // numbering back through a C interface (tests/test_decomp_vs_reference.py).
-#define private public // the constructor is private (Decomp::create would store the object in a static map)
+#define private public // the constructors are private (create() would store the objects in static maps), so are the lists
 #include "Decomp.h"
+#include "Halo.h"
 #undef private
 
 #include <thread>
@@ -11,6 +12,7 @@
 using namespace OMEGA;
 
 static std::vector<std::unique_ptr<Decomp>> g_decomps;
+static std::vector<std::unique_ptr<Halo>> g_halos; // src/base/Halo.cpp:150-280 on the decompositions above
 static const int *g_cell_task = nullptr;
 static int g_ncells = 0;
 
@@ -49,6 +51,13 @@ int ref_decomp_run(int NTasks, int HaloWidth, int NCells, int NEdges, int NVerti
    RefDecompWorld &W = RefDecompWorld::get();
    W.NumTasks = NTasks;
    W.Arrived  = 0;
+   RefMpiWorld &MW = RefMpiWorld::get();
+   MW.NumTasks = NTasks;
+   MW.Arrived  = 0;
+   MW.Box.clear();
+   MW.A2A.clear();
+   g_halos.clear();
+   g_halos.resize(NTasks);
    g_decomps.clear();
    g_decomps.resize(NTasks);
    std::vector<MachEnv> envs;
@@ -56,7 +65,9 @@ int ref_decomp_run(int NTasks, int HaloWidth, int NCells, int NEdges, int NVerti
    std::vector<std::thread> th;
    for (int t = 0; t < NTasks; ++t)
       th.emplace_back([&, t] {
+         RefMpiWorld::rank() = t;
          g_decomps[t].reset(new Decomp("RefDecomp" + std::to_string(t), &envs[t], NTasks, PartMethodMetisKWay, HaloWidth, "memory"));
+         g_halos[t].reset(new Halo("RefHalo" + std::to_string(t), &envs[t], g_decomps[t].get()));
       });
    for (auto &x : th) x.join();
    return 0;
@@ -107,6 +118,22 @@ int ref_decomp_get(int Task, int Which, int *Out) {
    case 19: return c1(D.NEdgesOnEdgeH);
    }
    return -1;
+}
+
+// the reference Halo's neighbour tasks (ascending); returns their number
+int ref_halo_neighbors(int Task, int *Out) {
+   const Halo &H = *g_halos[Task];
+   if (Out) for (size_t i = 0; i < H.NeighborList.size(); ++i) Out[i] = H.NeighborList[i];
+   return (int)H.NeighborList.size();
+}
+// exchange list of neighbour number Nbr (position in the list above), index space Elem, Dir 0 = send, 1 = receive:
+// local indices concatenated over the halo layers (Halo.cpp:40-110), per-layer counts in NHalo[HaloWidth]; returns NTot
+int ref_halo_list(int Task, int Nbr, int Elem, int Dir, int *Idx, int *NHalo) {
+   const Halo &H = *g_halos[Task];
+   const auto &L = Dir ? H.Neighbors[Nbr].RecvLists[Elem] : H.Neighbors[Nbr].SendLists[Elem];
+   if (Idx) for (int i = 0; i < L.NTot; ++i) Idx[i] = L.IndexH(i);
+   if (NHalo) for (size_t h = 0; h < L.NHalo.size(); ++h) NHalo[h] = L.NHalo[h];
+   return L.NTot;
 }
 
 } // extern "C"

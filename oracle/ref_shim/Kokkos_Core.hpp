@@ -123,6 +123,14 @@ template <class T> struct is_view : std::false_type {};
 template <class D, class... P> struct is_view<View<D, P...>> : std::true_type {};
 template <class D, class... P> struct is_view<const View<D, P...>> : std::true_type {};
 
+// ---- make_pair / subview of a rank-1 view over a half-open index range (Halo.h:874-878, Halo.cpp:734-737) ----
+using std::make_pair;
+template <class D, class... P, class I1, class I2>
+View<D, P...> subview(const View<D, P...> &V, const std::pair<I1, I2> &R) {
+   static_assert(View<D, P...>::rank == 1, "stand-in: subview of rank-1 views only");
+   return View<D, P...>(V.data() + R.first, static_cast<std::size_t>(R.second - R.first));
+}
+
 // ---- deep_copy / mirrors ------------------------------------------------------
 template <class D, class... P, class S, std::enable_if_t<std::is_arithmetic_v<S>, int> = 0>
 void deep_copy(const View<D, P...> &Dst, const S &Val) {

@@ -77,3 +77,47 @@ def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
             for nm in NAMES.values():
                 a, b = R[nm], np.asarray(L[nm]).astype(np.int32).ravel()
                 assert a.size == b.size and np.array_equal(a, b), (label, t, nm, int(np.argmax(a != b)) if a.size == b.size else "size")
+
+
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2)])
+def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
+    """src/base/Halo.cpp (constructor: neighbours, send / receive lists per index space and halo layer), compiled
+    unmodified and run on the reference Decomp of every thread-task over a thread MPI (oracle/ref_decomp/mpi.h:
+    MPI_Alltoall, Isend / Irecv / Waitall).  Neighbour tasks, every list's indices in order, and the per-layer counts
+    equal the lists the library is given (parallel.build_halo_lists, and omega_decomp_halo_lists of csrc/decomp.cpp)."""
+    from omega_b200 import parallel
+    lib = ref_lib()
+    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    task = decomp.partition_cells(m, ntasks)
+    run_reference(lib, m, ntasks, hw, task)
+    locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
+    lists = parallel.build_halo_lists(locs)
+    have_lib = os.path.exists(os.path.join(ROOT, "omega_b200", "csrc", "libomega_b200.so"))
+    for t in range(ntasks):
+        nn = lib.ref_halo_neighbors(t, None)
+        nb = np.zeros(max(nn, 1), np.int32)
+        lib.ref_halo_neighbors(t, P(nb))
+        assert nb[:nn].tolist() == lists[t]["neighbors"], (t, "neighbours")
+        ours = [("numpy", lists[t])]
+        if have_lib:
+            ours.append(("csrc/decomp.cpp", decomp.build_local_lib(m, np.ascontiguousarray(task, np.int32), t, 3, hw)[1]))
+        L = locs[t]
+        for i, nbr in enumerate(nb[:nn].tolist()):
+            for e, k in enumerate(parallel.KINDS):
+                for d, dname in ((0, "send"), (1, "recv")):
+                    n = lib.ref_halo_list(t, i, e, d, None, None)
+                    nl = hw if k == "Cell" else hw + 1       # edges and vertices: one layer more (Halo.cpp:469-499)
+                    idx, nh = np.zeros(max(n, 1), np.int32), np.zeros(nl, np.int32)
+                    lib.ref_halo_list(t, i, e, d, P(idx), P(nh))
+                    assert int(nh.sum()) == n
+                    for label, o in ours:
+                        mine = o[dname][k].get(nbr, np.zeros(0, np.int32))
+                        assert np.array_equal(idx[:n], np.asarray(mine)), (label, t, nbr, k, dname)
+                    if d == 1 and n:
+                        # receive lists are grouped by halo layer, ascending inside (Halo.cpp:455-600): the per-layer
+                        # counts are the elements of that owner in each layer of the local numbering
+                        kk = "Vertices" if k == "Vertex" else k + "s"
+                        bounds = np.concatenate(([int(L["N%sOwned" % kk])], np.asarray(L["N%sHalo" % kk]), [int(L["N%sAll" % kk])]))
+                        want = [int(((idx[:n] >= bounds[h]) & (idx[:n] < bounds[h + 1])).sum()) for h in range(nl)]
+                        assert nh.tolist() == want, (t, nbr, k, "layer counts")
