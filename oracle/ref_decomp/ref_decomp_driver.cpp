@@ -136,4 +136,40 @@ int ref_halo_list(int Task, int Nbr, int Elem, int Dir, int *Idx, int *NHalo) {
    return L.NTot;
 }
 
+// Halo::exchangeFullArrayHalo (src/base/Halo.h:768-915) on every task at once: Arrays[t] is task t's array
+// [NOuter][N*Size][NInner] (NOuter == 0: a 2-D array [N*Size][NInner]; NInner == 0 too: 1-D), double.
+int ref_halo_exchange(int Elem, int NOuter, int NInner, double **Arrays) {
+   const int NTasks = (int)g_halos.size();
+   std::vector<std::thread> th;
+   std::vector<int> err(NTasks, 0);
+   for (int t = 0; t < NTasks; ++t)
+      th.emplace_back([&, t] {
+         RefMpiWorld::rank() = t;
+         const Decomp &D = *g_decomps[t];
+         const int N = Elem == 0 ? D.NCellsSize : Elem == 1 ? D.NEdgesSize : D.NVerticesSize;
+         if (NOuter > 0) {
+            Array3DR8 A(Arrays[t], NOuter, N, NInner);
+            err[t] = g_halos[t]->exchangeFullArrayHalo(A, (MeshElement)Elem);
+         } else if (NInner > 0) {
+            Array2DR8 A(Arrays[t], N, NInner);
+            err[t] = g_halos[t]->exchangeFullArrayHalo(A, (MeshElement)Elem);
+         } else {
+            Array1DR8 A(Arrays[t], N);
+            err[t] = g_halos[t]->exchangeFullArrayHalo(A, (MeshElement)Elem);
+         }
+      });
+   for (auto &x : th) x.join();
+   int e = 0;
+   for (int v : err) e |= v;
+   return e;
+}
+// what task Task sent to its neighbour number Nbr in the last exchange: the packed message (Halo.h:304-502)
+int ref_halo_send_buffer(int Task, int Nbr, int Count, double *Out) {
+   const Halo &H = *g_halos[Task];
+   const auto &B = H.Neighbors[Nbr].SendBufferH;
+   const int n = std::min<int>(Count, (int)B.extent(0));
+   for (int i = 0; i < n; ++i) Out[i] = B(i);
+   return (int)B.extent(0);
+}
+
 } // extern "C"

@@ -65,8 +65,13 @@ template <class DataType, class... Props> class View {
    using data_type            = DataType;
    using value_type           = typename ViewTraits<DataType>::value_type;
    using non_const_value_type = std::remove_const_t<value_type>;
-   static constexpr int rank         = ViewTraits<DataType>::rank;
-   static constexpr int Rank         = rank;
+   // usable as a value and as a call, like Kokkos' integral constant (Halo.h:795 writes Array.rank())
+   struct RankT {
+      constexpr operator int() const { return ViewTraits<DataType>::rank; }
+      constexpr int operator()() const { return ViewTraits<DataType>::rank; }
+   };
+   static constexpr RankT rank{};
+   static constexpr int Rank         = ViewTraits<DataType>::rank;
    static constexpr bool is_hostspace = true;
 
    View() = default;

@@ -121,3 +121,50 @@ def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
                         bounds = np.concatenate(([int(L["N%sOwned" % kk])], np.asarray(L["N%sHalo" % kk]), [int(L["N%sAll" % kk])]))
                         want = [int(((idx[:n] >= bounds[h]) & (idx[:n] < bounds[h + 1])).sum()) for h in range(nl)]
                         assert nh.tolist() == want, (t, nbr, k, "layer counts")
+
+
+def _ref_exchange(lib, locs, kind_idx, nouter, ninner, arrays):
+    ptrs = (C.POINTER(C.c_double) * len(arrays))(*[a.ctypes.data_as(C.POINTER(C.c_double)) for a in arrays])
+    assert lib.ref_halo_exchange(kind_idx, nouter, ninner, ptrs) == 0
+
+
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2)])
+def test_reference_exchange_and_message_layout(kind, ntasks, hw):
+    """Halo::exchangeFullArrayHalo of the reference itself (Halo.h:768-915) on the thread-tasks: (1) its own HaloTest
+    (test/base/HaloTest.cpp:41-99) passes on them -- arrays holding f(global ID) in the owned entries equal the fully
+    initialised arrays after the exchange, 1-D, 2-D and 3-D, cells, edges, vertices; (2) the message it packs for a
+    neighbour is [outer][position in the send list][inner], the layout csrc/halo.cu restates
+    (tests/test_halo_any_type.py::test_pack_layout_equals_the_reference_message checks the kernel against it)."""
+    from omega_b200 import parallel
+    lib = ref_lib()
+    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    task = decomp.partition_cells(m, ntasks)
+    run_reference(lib, m, ntasks, hw, task)
+    locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
+    lists = parallel.build_halo_lists(locs)
+    for e, (k, idn, kk) in enumerate((("Cell", "CellID", "Cells"), ("Edge", "EdgeID", "Edges"), ("Vertex", "VertexID", "Vertices"))):
+        for nouter, ninner in ((0, 0), (0, 5), (2, 3)):
+            full, part = [], []
+            for L in locs:
+                n, nall, nown = int(L["N%sSize" % kk]), int(L["N%sAll" % kk]), int(L["N%sOwned" % kk])
+                ids = np.asarray(L[idn], np.float64)[:n]
+                o = np.arange(max(nouter, 1)).reshape(-1, 1, 1)
+                i = np.arange(max(ninner, 1)).reshape(1, 1, -1)
+                f = (ids.reshape(1, n, 1) * 7 + o) * 5 + i
+                f[:, nall:] = 0.0
+                p = f.copy()
+                p[:, nown:nall] = -1.0
+                shape = ((nouter,) if nouter else ()) + (n,) + ((ninner,) if ninner else ())
+                full.append(np.ascontiguousarray(f.reshape(shape)))
+                part.append(np.ascontiguousarray(p.reshape(shape)))
+            _ref_exchange(lib, locs, e, nouter, ninner, part)
+            for t in range(ntasks):
+                assert np.array_equal(part[t], full[t]), (k, nouter, ninner, t)
+                for j, nbr in enumerate(lists[t]["neighbors"]):
+                    idx = lists[t]["send"][k].get(nbr, np.zeros(0, np.int32))
+                    cnt = idx.size * max(nouter, 1) * max(ninner, 1)
+                    buf = np.zeros(max(cnt, 1))
+                    have = lib.ref_halo_send_buffer(t, j, cnt, buf.ctypes.data_as(C.POINTER(C.c_double)))
+                    assert have >= cnt
+                    a = full[t].reshape(max(nouter, 1), -1, max(ninner, 1))
+                    assert np.array_equal(buf[:cnt], a[:, idx, :].ravel()), (k, nouter, ninner, t, nbr, "message layout")

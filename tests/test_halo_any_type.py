@@ -78,3 +78,40 @@ def test_exchange_any_type_any_rank(ntasks):
     assert lib.omega_halo_pack_any(ranks[0][2].handle, 0, 1, 1, 2, C.c_void_p(1), C.c_void_p(1), stream) == 2      # 2-byte elements: rejected
     for L, m, ex in ranks:
         ex.close(); m.close()
+
+
+def test_pack_layout_equals_the_reference_message():
+    """The message the pack kernel builds for a neighbour is the one the reference's Halo packs -- [outer][position in
+    the send list][inner] (Halo.h:304-502), pinned on the reference's own code by
+    tests/test_decomp_vs_reference.py::test_reference_exchange_and_message_layout."""
+    import torch
+    from omega_b200 import decomp, model, parallel
+    mesh_g = cases.sphere_mesh(3)
+    ntasks, K = 3, 5
+    locs = decomp.build_all(mesh_g, ntasks, K, 3)
+    lists = parallel.build_halo_lists(locs)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for t, (L, hl) in enumerate(zip(locs, lists)):
+        m = model.HorzMesh(L, reorder=True)
+        ex = parallel.HaloExchanger(m, hl, 0)
+        lib = m.lib
+        for kind, k in ((capi.ON_CELL, "Cell"), (capi.ON_EDGE, "Edge"), (capi.ON_VERTEX, "Vertex")):
+            n = m.NSize[kind]
+            for nouter in (1, 2):
+                host = np.random.default_rng(5 + t).standard_normal((nouter, n, K))
+                p, _ = m.perm(kind)
+                d = torch.from_numpy(np.ascontiguousarray(host[:, p])).to("cuda:0")
+                sc = (C.c_longlong * max(len(ex.nbrs), 1))()
+                rc = (C.c_longlong * max(len(ex.nbrs), 1))()
+                assert lib.omega_halo_buffer_counts(ex.handle, kind, nouter, K, sc, rc) == 0
+                sc = list(sc)[:len(ex.nbrs)]
+                sb = torch.zeros(max(sum(sc), 1), dtype=torch.float64, device="cuda:0")
+                assert lib.omega_halo_pack_any(ex.handle, kind, nouter, K, 8, C.c_void_p(d.data_ptr()), C.c_void_p(sb.data_ptr()), stream) == 0
+                torch.cuda.synchronize()
+                got, off = sb.cpu().numpy(), 0
+                for j, nbr in enumerate(ex.nbrs):
+                    idx = hl["send"][k].get(nbr, np.zeros(0, np.int32))
+                    assert sc[j] == idx.size * nouter * K
+                    assert np.array_equal(got[off:off + sc[j]], host[:, idx, :].ravel()), (t, k, nouter, nbr)
+                    off += sc[j]
+        ex.close(); m.close()
