@@ -57,6 +57,28 @@ template <class DT> struct ViewTraits<DT *> {
    static constexpr int rank = ViewTraits<DT>::rank + 1;
 };
 
+// trailing compile-time extent: View<Real *[VecLength], ...> (TriDiagSolvers.h:37-39)
+template <class DT, std::size_t N> struct ViewTraits<DT[N]> {
+   using value_type                  = typename ViewTraits<DT>::value_type;
+   static constexpr int rank         = ViewTraits<DT>::rank + 1;
+   static constexpr std::size_t tail = N;
+};
+template <class T, class = void> struct StaticTail { static constexpr std::size_t value = 0; };
+template <class T> struct StaticTail<T, std::void_t<decltype(ViewTraits<T>::tail)>> { static constexpr std::size_t value = ViewTraits<T>::tail; };
+
+// per-team scratch memory: a bump allocator over a buffer the team loop owns (TeamPolicy::set_scratch_size)
+struct ScratchArena {
+   char *Base       = nullptr;
+   std::size_t *Off = nullptr; // shared by the copies handed out by team_scratch()
+   std::size_t Cap  = 0;
+   void *alloc(std::size_t Bytes) const {
+      const std::size_t a = (*Off + 15) & ~std::size_t(15);
+      if (a + Bytes > Cap) { std::fprintf(stderr, "Kokkos stand-in: team scratch exhausted\n"); std::abort(); }
+      *Off = a + Bytes;
+      return Base + a;
+   }
+};
+
 struct ALL_t {};
 constexpr ALL_t ALL{};
 
@@ -97,6 +119,18 @@ template <class DataType, class... Props> class View {
          Ext_[i] = e[i];
          Size_ *= e[i];
       }
+   }
+
+   // view in team scratch memory: dynamic extents as given, a trailing static extent from the type
+   template <class... Ns> View(const ScratchArena &S, Ns... ns) : Label_("scratch") {
+      const std::size_t e[] = {static_cast<std::size_t>(ns)..., 1};
+      constexpr int nd      = static_cast<int>(sizeof...(Ns));
+      Size_                 = 1;
+      for (int i = 0; i < rank; ++i) {
+         Ext_[i] = i < nd ? e[i] : StaticTail<DataType>::value;
+         Size_ *= Ext_[i];
+      }
+      Ptr_ = static_cast<value_type *>(S.alloc(Size_ * sizeof(value_type)));
    }
 
    template <class... Is> value_type &operator()(Is... is) const {
@@ -179,10 +213,73 @@ template <class Exec, int N, Iterate O, Iterate I, class... Rest> struct MDRange
    }
 };
 
-template <class Exec = OpenMP> struct TeamPolicy {
-   struct member_type {};
+// ---- hierarchical parallelism, serial: a league of one-thread teams (VertCoord.cpp:648-860) ----------------
+struct PerTeamValue {
+   std::size_t Bytes;
 };
-struct TeamThreadRange {};
+inline PerTeamValue PerTeam(std::size_t Bytes) { return {Bytes}; }
+struct HostTeamMember {
+   int League = 0;
+   ScratchArena Scratch;
+   const ScratchArena &team_scratch(int) const { return Scratch; }
+   int league_rank() const { return League; }
+   int team_rank() const { return 0; }
+   int team_size() const { return 1; }
+   void team_barrier() const {}
+};
+template <class Exec = OpenMP> struct TeamPolicy {
+   using member_type = HostTeamMember;
+   int LeagueSize    = 0;
+   TeamPolicy() = default;
+   std::size_t ScratchBytes = 0;
+   TeamPolicy(int League, int /*TeamSize*/, int /*VectorLength*/ = 1) : LeagueSize(League) {}
+   TeamPolicy &set_scratch_size(int, const PerTeamValue &V) {
+      ScratchBytes = V.Bytes;
+      return *this;
+   }
+};
+struct TeamThreadRangeT {
+   int Begin, End;
+};
+inline TeamThreadRangeT TeamThreadRange(const HostTeamMember &, int N) { return {0, N}; }
+inline TeamThreadRangeT TeamThreadRange(const HostTeamMember &, int B, int E) { return {B, E}; }
+template <class Exec, class F> void parallel_for(const std::string &, const TeamPolicy<Exec> &Pol, const F &Fun) {
+   std::vector<char> buf(Pol.ScratchBytes + 64);
+   for (int l = 0; l < Pol.LeagueSize; ++l) {
+      std::size_t off = 0;
+      HostTeamMember M;
+      M.League  = l;
+      M.Scratch = ScratchArena{buf.data(), &off, buf.size()};
+      Fun(M);
+   }
+}
+template <class Exec, class F> void parallel_for(const TeamPolicy<Exec> &Pol, const F &Fun) { parallel_for(std::string(), Pol, Fun); }
+template <class F> void parallel_for(const TeamThreadRangeT &R, const F &Fun) {
+   for (int i = R.Begin; i < R.End; ++i) Fun(i);
+}
+// the functor adds its contribution to the running value and, when IsFinal, uses it: one pass, in index order
+template <class F, class C, class T> void team_scan_impl(const TeamThreadRangeT &R, const F &Fun, void (C::*)(int, T &, bool) const);
+template <class F> void parallel_scan(const TeamThreadRangeT &R, const F &Fun) {
+   // value type = second parameter of the functor's call operator
+   using Traits = decltype(&F::operator());
+   team_scan_impl(R, Fun, Traits{});
+}
+template <class F, class C, class T> void team_scan_impl(const TeamThreadRangeT &R, const F &Fun, void (C::*)(int, T &, bool) const) {
+   T Acc{};
+   for (int i = R.Begin; i < R.End; ++i) Fun(i, Acc, true);
+}
+template <class F, class T> void parallel_reduce(const TeamThreadRangeT &R, const F &Fun, T &Result) {
+   T Acc{};
+   for (int i = R.Begin; i < R.End; ++i) Fun(i, Acc);
+   Result = Acc;
+}
+template <class F, class T1, class T2> void parallel_reduce(const TeamThreadRangeT &R, const F &Fun, T1 &R1, T2 &R2) {
+   T1 A1{};
+   T2 A2{};
+   for (int i = R.Begin; i < R.End; ++i) Fun(i, A1, A2);
+   R1 = A1;
+   R2 = A2;
+}
 
 // ---- parallel_for ---------------------------------------------------------------
 template <class... P, class F> void parallel_for(const std::string &, const RangePolicy<P...> &Pol, const F &Fun) {
@@ -245,6 +342,8 @@ template <class... P, class F, class T> void parallel_reduce(const std::string &
 
 // ---- math -------------------------------------------------------------------
 using std::abs;
+using std::ceil;
+using std::log2;
 using std::cos;
 using std::fabs;
 using std::sin;

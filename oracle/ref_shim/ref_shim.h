@@ -18,7 +18,9 @@
 #define OMEGA_HALO_H
 #define OMEGA_HORZMESH_H
 #define OMEGA_TRACERS_H
+#ifndef REF_SHIM_REAL_VERTCOORD // (ref_vertcoord.cpp compiles the reference's own VertCoord.cpp)
 #define OMEGA_VERTCOORD_H
+#endif
 #define OMEGA_DECOMP_H
 #define OMEGA_MACH_ENV_H
 #define OMEGA_LOG_H
@@ -171,6 +173,11 @@ class FieldGroup {
 // ---- Decomp.h ------------------------------------------------------------------------
 class Decomp {
  public:
+   // sizes the reference's VertCoord constructor reads (VertCoord.cpp:50-128); filled by ref_vertcoord.cpp
+   I4 NCellsOwned = 0, NCellsAll = 0, NCellsSize = 0, NEdgesOwned = 0, NEdgesAll = 0, NEdgesSize = 0, NVerticesOwned = 0,
+      NVerticesAll = 0, NVerticesSize = 0, VertexDegree = 3, MaxEdges = 6, HaloWidth = 1;
+   std::string MeshFileName = "memory";
+   Array2DI4 CellsOnEdge, CellsOnVertex;
    static Decomp *getDefault() { return nullptr; }
 };
 
@@ -186,7 +193,38 @@ class Halo {
    template <class T> int exchangeFullArrayHalo(T &, MeshElement) { return 0; }
 };
 
+#ifdef REF_SHIM_REAL_VERTCOORD
+// ---- what the reference's VertCoord.cpp touches besides the stand-ins above (ref_vertcoord.cpp) ----
+inline int &refNVertLayers() { // the "nVertLevels" dimension of the mesh "file"
+   static int N = 1;
+   return N;
+}
+namespace IO {
+enum Mode { ModeUnknown, ModeRead, ModeWrite };
+inline void openFile(int &FileID, const std::string &, Mode) { FileID = 1; }
+inline void closeFile(int &) {}
+inline Error getDimFromFile(int, const std::string &, int &DimID, int &DimLength) {
+   DimID     = 0;
+   DimLength = refNVertLayers();
+   return Error();
+}
+} // namespace IO
+class Dimension {
+ public:
+   static std::shared_ptr<Dimension> create(const std::string &, int) { return std::make_shared<Dimension>(); }
+   static void destroy(const std::string &) {}
+};
+class IOStream {
+ public:
+   static std::shared_ptr<IOStream> get(const std::string &) { return std::make_shared<IOStream>(); }
+   bool validate() const { return false; } // no InitialVertCoord stream: the driver fills the members itself
+   static Error read(const std::string &) { return Error(ErrorCode::Fail, "no stream"); }
+   template <class... A> static Error read(const std::string &, A &&...) { return Error(ErrorCode::Fail, "no stream"); }
+};
+#endif
+
 // ---- VertCoord.h: the hot path only reads NVertLayers -------------------------------------
+#ifndef REF_SHIM_REAL_VERTCOORD
 class VertCoord {
  public:
    I4 NVertLayers = 1;
@@ -196,6 +234,7 @@ class VertCoord {
    }
    static VertCoord *getDefault() { return defaultPtr(); }
 };
+#endif
 
 // ---- HorzMesh.h: public members the compiled sources read (src/ocn/HorzMesh.h:100-265) ------
 class HorzMesh {

@@ -230,3 +230,63 @@ def test_gpu_tridiagonal_solvers(nr):
         got = xg.cpu().numpy()
         assert np.isfinite(got).all()
         assert np.abs(got - want).max() <= 1e-11 * np.abs(want).max(), (nr, jump, np.abs(got - want).max())
+
+
+def test_vert_coord_oracle_equals_the_reference_vertcoord():
+    """oracle/vertical_oracle.c against the reference's own src/ocn/VertCoord.cpp (compiled unmodified,
+    oracle/_ref/libomega_ref_vertcoord.so: Kokkos team scans as one-thread teams in index order): pressure, z height,
+    geopotential and target thickness of random columns with partial layer ranges, bit for bit."""
+    ref_path = os.path.join(os.path.dirname(oracle_lib.REF), "libomega_ref_vertcoord.so")
+    if not os.path.exists(ref_path):
+        pytest.skip("oracle/_ref/libomega_ref_vertcoord.so not built")
+    lib, ref = oracle(), C.CDLL(ref_path)
+    kmin, kmax, h, surf, bot, ct, sa = column_case(n=53, K=40, seed=11)
+    n, K = h.shape
+    rng = np.random.default_rng(2)
+    sv = 9.6e-4 + 2.0e-5 * rng.random((n, K))
+    tid, sal = 0.3 * rng.random(n), 0.05 * rng.random(n)
+    refh, wt = np.ascontiguousarray(h * (0.8 + 0.4 * rng.random((n, K)))), 0.5 + rng.random(K)
+    d = C.c_double(1026.0)
+    o = {k: np.zeros((n, K + 1)) for k in ("pint", "zint")}
+    o.update({k: np.zeros((n, K)) for k in ("pmid", "zmid", "geo", "tgt")})
+    r = {k: np.zeros_like(v) for k, v in o.items()}
+    lib.oracle_vert_pressure(n, K, PI(kmin), PI(kmax), d, P(h), P(surf), P(o["pint"]), P(o["pmid"]))
+    lib.oracle_vert_zheight(n, K, PI(kmin), PI(kmax), d, P(bot), P(h), P(sv), P(o["zint"]), P(o["zmid"]))
+    lib.oracle_vert_geopotential(n, K, PI(kmin), PI(kmax), P(o["zmid"]), P(tid), P(sal), P(o["geo"]))
+    lib.oracle_vert_target(n, K, PI(kmin), PI(kmax), d, P(o["pint"]), P(refh), P(wt), P(o["tgt"]))
+    assert ref.ref_vertcoord_run(n, K, PI(kmin), PI(kmax), d, P(bot), P(h), P(surf), P(sv), P(tid), P(sal), P(refh), P(wt),
+                                 P(r["pint"]), P(r["pmid"]), P(r["zint"]), P(r["zmid"]), P(r["geo"]), P(r["tgt"])) == 0
+    k = np.arange(K)[None, :]
+    act = (k >= kmin[:, None]) & (k <= kmax[:, None])
+    act1 = np.zeros((n, K + 1), bool)
+    act1[:, :-1] |= act
+    act1[:, 1:] |= act
+    for nm in o:
+        m = act1 if o[nm].shape[1] == K + 1 else act
+        assert np.abs(r[nm][m]).max() > 0
+        assert np.array_equal(o[nm][m], r[nm][m]), (nm, np.abs(o[nm][m] - r[nm][m]).max())
+
+
+def test_tridiagonal_oracle_equals_the_reference_thomas_solvers():
+    """oracle_tridiag_thomas / oracle_tridiag_diffusion_thomas against the reference's own ThomasSolver::solve and
+    ThomasDiffusionSolver::solve (src/base/TriDiagSolvers.h, compiled unmodified), bit for bit -- including the system
+    with a 1e14 jump in diffusivity of test/base/TriDiagSolversTest.cpp:428-470."""
+    ref_path = os.path.join(os.path.dirname(oracle_lib.REF), "libomega_ref_vertcoord.so")
+    if not os.path.exists(ref_path):
+        pytest.skip("oracle/_ref/libomega_ref_vertcoord.so not built")
+    lib, ref = oracle(), C.CDLL(ref_path)
+    dl, d, du, x = tridiag_case(nb=7, nr=50, seed=9)
+    xo, do = x.copy(), d.copy()
+    lib.oracle_tridiag_thomas(7, 50, P(dl), P(do), P(du), P(xo))
+    xr = x.copy()
+    assert ref.ref_tridiag_thomas(7, 50, P(dl), P(d), P(du), P(xr)) == 0
+    assert np.array_equal(xo, xr), np.abs(xo - xr).max()
+    rng = np.random.default_rng(4)
+    g, h, x2 = rng.random((5, 40)) * 3.0, 0.5 + rng.random((5, 40)), rng.standard_normal((5, 40))
+    g[2, 17] = 1.0e14                      # abrupt jump in diffusivity
+    g[:, -1] = 0.0
+    xo, ho, al = x2.copy(), h.copy(), np.zeros((5, 40))
+    lib.oracle_tridiag_diffusion_thomas(5, 40, P(g), P(ho), P(xo), P(al))
+    xr = x2.copy()
+    assert ref.ref_tridiag_diffusion_thomas(5, 40, P(g), P(h), P(xr)) == 0
+    assert np.all(np.isfinite(xr)) and np.array_equal(xo, xr), np.abs(xo - xr).max()
