@@ -20,6 +20,8 @@
 #define OMEGA_ERROR_H
 #define OMEGA_LOG_H
 #define OMEGA_LOG_FORMATTERS_H
+#define OMEGA_DIMENSION_H
+#define OMEGA_VERTCOORD_H // HorzMesh.h includes it; HorzMesh::init (compiled, never called) reads NVertLayers from it
 
 #include <Kokkos_Core.hpp>
 
@@ -138,8 +140,10 @@ enum IODataType { IOTypeI4, IOTypeI8, IOTypeR4, IOTypeR8, IOTypeChar, IOTypeLogi
 struct RefMeshFile { // global arrays as a mesh file holds them: 1-based IDs, 0 = none
    std::map<std::string, int> Dims;
    std::map<std::string, const int *> Arrays;
+   std::map<std::string, const double *> ArraysR8; // geometry of the global mesh (HorzMesh.cpp:420-520)
    std::mutex Mu;
    std::map<int, std::vector<int>> Decomps;
+   std::map<int, int> DecompType;
    int NextDecomp = 1;
    static RefMeshFile &get() {
       static RefMeshFile F;
@@ -159,11 +163,12 @@ inline Error getDimFromFile(int, const std::string &DimName, int &DimID, int &Di
    DimLength = it->second;
    return Error();
 }
-inline int createDecomp(IODataType, int, const std::vector<int> &, int, const std::vector<int> &GlobalIndx, Rearranger) {
+inline int createDecomp(IODataType T, int, const std::vector<int> &, int, const std::vector<int> &GlobalIndx, Rearranger) {
    RefMeshFile &F = RefMeshFile::get();
    std::lock_guard<std::mutex> L(F.Mu);
    const int id = F.NextDecomp++;
-   F.Decomps[id] = GlobalIndx;
+   F.Decomps[id]    = GlobalIndx;
+   F.DecompType[id] = (int)T;
    return id;
 }
 inline void destroyDecomp(int &DecompID) {
@@ -173,13 +178,24 @@ inline void destroyDecomp(int &DecompID) {
 }
 inline Error readArray(void *Array, int Size, const std::string &VarName, int, int DecompID, int &VarID, int = -1) {
    RefMeshFile &F = RefMeshFile::get();
-   auto it = F.Arrays.find(VarName);
-   if (it == F.Arrays.end()) return Error(ErrorCode::Fail);
    std::vector<int> Idx;
+   int Type;
    {
       std::lock_guard<std::mutex> L(F.Mu);
-      Idx = F.Decomps.at(DecompID);
+      Idx  = F.Decomps.at(DecompID);
+      Type = F.DecompType.at(DecompID);
    }
+   if (Type == (int)IOTypeR8) {
+      auto r = F.ArraysR8.find(VarName);
+      if (r == F.ArraysR8.end()) return Error(ErrorCode::Fail);
+      double *Out = static_cast<double *>(Array);
+      for (int i = 0; i < Size && i < (int)Idx.size(); ++i)
+         if (Idx[i] >= 0) Out[i] = r->second ? r->second[Idx[i]] : 0.0; // (a null entry: a variable the test does not supply)
+      VarID = 0;
+      return Error();
+   }
+   auto it = F.Arrays.find(VarName);
+   if (it == F.Arrays.end()) return Error(ErrorCode::Fail);
    int *Out = static_cast<int *>(Array);
    for (int i = 0; i < Size; ++i) // entries past a task's share of the linear distribution keep offset -1
       if (Idx[i] >= 0) Out[i] = it->second[Idx[i]];
@@ -187,4 +203,20 @@ inline Error readArray(void *Array, int Size, const std::string &VarName, int, i
    return Error();
 }
 } // namespace IO
+
+// ---- Dimension.h, VertCoord.h: names only ---------------------------------------------------------------------
+class Dimension {
+ public:
+   template <class... A> static std::shared_ptr<Dimension> create(A &&...) { return std::make_shared<Dimension>(); }
+   static bool exists(const std::string &) { return false; }
+   static void destroy(const std::string &) {}
+};
+class VertCoord {
+ public:
+   I4 NVertLayers = 1;
+   static VertCoord *getDefault() {
+      static VertCoord V;
+      return &V;
+   }
+};
 } // namespace OMEGA

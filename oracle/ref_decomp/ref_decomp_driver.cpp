@@ -5,6 +5,7 @@
 #define private public // the constructors are private (create() would store the objects in static maps), so are the lists
 #include "Decomp.h"
 #include "Halo.h"
+#include "HorzMesh.h"
 #undef private
 
 #include <thread>
@@ -13,6 +14,7 @@ using namespace OMEGA;
 
 static std::vector<std::unique_ptr<Decomp>> g_decomps;
 static std::vector<std::unique_ptr<Halo>> g_halos; // src/base/Halo.cpp:150-280 on the decompositions above
+static std::vector<std::unique_ptr<HorzMesh>> g_meshes; // src/ocn/HorzMesh.cpp:49-150 on the decompositions above
 static const int *g_cell_task = nullptr;
 static int g_ncells = 0;
 
@@ -56,6 +58,7 @@ int ref_decomp_run(int NTasks, int HaloWidth, int NCells, int NEdges, int NVerti
    MW.Arrived  = 0;
    MW.Box.clear();
    MW.A2A.clear();
+   g_meshes.clear();
    g_halos.clear();
    g_halos.resize(NTasks);
    g_decomps.clear();
@@ -116,6 +119,56 @@ int ref_decomp_get(int Task, int Which, int *Out) {
    case 17: return c2(D.EdgesOnVertexH);
    case 18: return c1(D.NEdgesOnCellH);
    case 19: return c1(D.NEdgesOnEdgeH);
+   }
+   return -1;
+}
+
+// Geometry of the global mesh for HorzMesh (file variable name -> global array; a null pointer = all zeros).  Call before
+// ref_horzmesh_run; the names are those of HorzMesh.cpp:420-520 ("xCell", "areaCell", "dcEdge", "weightsOnEdge", ...).
+int ref_mesh_set_r8(const char *Name, const double *Ptr) {
+   IO::RefMeshFile::get().ArraysR8[Name] = Ptr;
+   return 0;
+}
+// HorzMesh::HorzMesh (reads its local geometry through the linear IO decompositions it builds from the Decomp's global
+// IDs, then computeEdgeSign, setMasks, setMeshScaling) for every task of the last ref_decomp_run
+int ref_horzmesh_run(int NVertLayers) {
+   g_meshes.clear();
+   for (size_t t = 0; t < g_decomps.size(); ++t)
+      g_meshes.emplace_back(new HorzMesh("RefMesh" + std::to_string(t), g_decomps[t].get(), NVertLayers));
+   return 0;
+}
+// Which: 0 EdgeSignOnCell [NCellsSize][MaxEdges], 1 EdgeSignOnVertex [NVerticesSize][VertexDegree], 2 EdgeMask
+// [NEdgesSize][NVertLayers], 3 AreaCell, 4 DcEdge, 5 DvEdge, 6 AngleEdge, 7 FEdge, 8 FVertex, 9 AreaTriangle,
+// 10 BottomDepth, 11 WeightsOnEdge [NEdgesSize][2 MaxEdges], 12 KiteAreasOnVertex [NVerticesSize][VertexDegree],
+// 13 MeshScalingDel2, 14 MeshScalingDel4, 15 XCell, 16 YCell, 17 XEdge, 18 YEdge.  Returns the count.
+int ref_horzmesh_get(int Task, int Which, double *Out) {
+   const HorzMesh &M = *g_meshes[Task];
+   auto c1 = [&](const HostArray1DReal &A) { const int n = (int)A.extent(0); if (Out) for (int i = 0; i < n; ++i) Out[i] = A(i); return n; };
+   auto c2 = [&](const HostArray2DReal &A) {
+      const int n = (int)A.extent(0), m = (int)A.extent(1);
+      if (Out) for (int i = 0; i < n; ++i) for (int j = 0; j < m; ++j) Out[i * m + j] = A(i, j);
+      return n * m;
+   };
+   switch (Which) {
+   case 0: return c2(M.EdgeSignOnCellH);
+   case 1: return c2(M.EdgeSignOnVertexH);
+   case 2: return c2(createHostMirrorCopy(M.EdgeMask));
+   case 3: return c1(M.AreaCellH);
+   case 4: return c1(M.DcEdgeH);
+   case 5: return c1(M.DvEdgeH);
+   case 6: return c1(M.AngleEdgeH);
+   case 7: return c1(M.FEdgeH);
+   case 8: return c1(M.FVertexH);
+   case 9: return c1(M.AreaTriangleH);
+   case 10: return c1(M.BottomDepthH);
+   case 11: return c2(M.WeightsOnEdgeH);
+   case 12: return c2(M.KiteAreasOnVertexH);
+   case 13: return c1(createHostMirrorCopy(M.MeshScalingDel2));
+   case 14: return c1(createHostMirrorCopy(M.MeshScalingDel4));
+   case 15: return c1(M.XCellH);
+   case 16: return c1(M.YCellH);
+   case 17: return c1(M.XEdgeH);
+   case 18: return c1(M.YEdgeH);
    }
    return -1;
 }

@@ -168,3 +168,56 @@ def test_reference_exchange_and_message_layout(kind, ntasks, hw):
                     assert have >= cnt
                     a = full[t].reshape(max(nouter, 1), -1, max(ninner, 1))
                     assert np.array_equal(buf[:cnt], a[:, idx, :].ravel()), (k, nouter, ninner, t, nbr, "message layout")
+
+
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 1, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2)])
+def test_horzmesh_local_geometry_and_derived_fields_equal_the_reference(kind, ntasks, hw):
+    """src/ocn/HorzMesh.cpp compiled unmodified and constructed on every task's reference Decomp (reads its local
+    geometry through the IO decompositions it builds from the global IDs; computeEdgeSign, setMasks, setMeshScaling:
+    HorzMesh.cpp:527-647).  The local geometry arrays equal those of omega_b200/decomp.py entry for entry, and
+    EdgeSignOnCell / EdgeSignOnVertex / EdgeMask equal what the C oracle derives (the same arrays the library's
+    omega_mesh_derived is held to bit for bit on the GPU)."""
+    from omega_b200 import capi
+    from tests.oracle_lib import Oracle
+    lib = ref_lib()
+    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    task = decomp.partition_cells(m, ntasks) if ntasks > 1 else np.zeros(m.nCells, np.int32)
+    run_reference(lib, m, ntasks, hw, task)
+    keep = []
+    for nm in ("xCell", "yCell", "zCell", "lonCell", "latCell", "xEdge", "yEdge", "zEdge", "lonEdge", "latEdge", "xVertex", "yVertex",
+               "zVertex", "lonVertex", "latVertex", "bottomDepth", "areaCell", "areaTriangle", "dvEdge", "dcEdge", "angleEdge",
+               "meshDensity", "fCell", "fVertex", "fEdge", "kiteAreasOnVertex", "weightsOnEdge"):
+        a = np.ascontiguousarray(m[nm], np.float64) if nm in m else None
+        keep.append(a)
+        lib.ref_mesh_set_r8(nm.encode(), a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else None)
+    K = 3
+    assert lib.ref_horzmesh_run(K) == 0
+    locs = decomp.build_all(m, ntasks, K, hw, cell_task=task)
+    dp = C.POINTER(C.c_double)
+
+    def get(t, w):
+        n = lib.ref_horzmesh_get(t, w, None)
+        v = np.zeros(n)
+        lib.ref_horzmesh_get(t, w, v.ctypes.data_as(dp))
+        return v
+
+    geo = {3: "AreaCell", 4: "DcEdge", 5: "DvEdge", 6: "AngleEdge", 7: "FEdge", 8: "FVertex", 9: "AreaTriangle", 10: "BottomDepth",
+           11: "WeightsOnEdge", 12: "KiteAreasOnVertex", 15: "XCell", 16: "YCell", 17: "XEdge", 18: "YEdge"}
+    cfg = capi.TendConfig.default()
+    for t in range(ntasks):
+        L = locs[t]
+        for w, nm in geo.items():
+            a, b = get(t, w), np.asarray(L[nm], np.float64)
+            rows = b.shape[0] - 1                                  # every local element; the boundary slot apart
+            width = 1 if b.ndim == 1 else b.shape[1]
+            assert a.size == b.size, (t, nm)
+            assert np.array_equal(a.reshape(-1, width)[:rows], b.reshape(-1, width)[:rows]), (t, nm)
+        o = Oracle(L, cfg, 0)
+        esc, esv, mask = o.derived()
+        assert np.array_equal(get(t, 0).reshape(esc.shape), esc), (t, "EdgeSignOnCell")
+        assert np.array_equal(get(t, 1).reshape(esv.shape), esv), (t, "EdgeSignOnVertex")
+        em = get(t, 2).reshape(mask.shape[0], K)
+        for k in range(K):
+            assert np.array_equal(em[:, k], mask), (t, "EdgeMask", k)
+        assert np.all(get(t, 13)[:int(L.NEdgesAll)] == 1.0) and np.all(get(t, 14)[:int(L.NEdgesAll)] == 1.0)   # HorzMesh.cpp:604-626
+        o.close()
