@@ -118,6 +118,12 @@ Array3DReal wrap_tracers(RefStepper *R, const double *Tr) {
 
 extern "C" {
 
+// Multi-task tests: Fn is called at every halo exchange the reference's steppers perform (see ref_shim.h)
+int ref_set_halo_callback(void (*Fn)(void *, int, int, int)) {
+   Halo::callback() = Fn;
+   return 0;
+}
+
 int oracle_stepper_destroy(RefStepper *R);
 
 int oracle_stepper_create(const OmegaMeshDesc *D, const OmegaTendConfig *Cfg, int NTracers, RefStepper **Out) {

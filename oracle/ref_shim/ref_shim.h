@@ -181,16 +181,30 @@ class Decomp {
    static Decomp *getDefault() { return nullptr; }
 };
 
-// ---- Halo.h: one task, closed mesh -> the exchange is the identity ------------------------
+// ---- Halo.h: one task, closed mesh -> the exchange is the identity.  A multi-task test may install a callback:
+// the reference's steppers then call it at their own exchange points (OceanState.cpp:333-344,
+// RungeKutta4Stepper.cpp:108-114,130-131, Tracers.cpp:457-476) with the array to exchange, and the test moves the
+// halo values between its task processes (tests/test_multirank_cpu.py).  Arrays are [NOuter][N*Size][NInner] Real.
 enum MeshElement { OnCell, OnEdge, OnVertex }; // src/base/Halo.h:45
 class Halo {
  public:
+   using Callback = void (*)(void *Data, int Elem, int NOuter, int NInner);
+   static Callback &callback() {
+      static Callback C = nullptr;
+      return C;
+   }
    static Halo *getDefault() {
       static Halo H;
       return &H;
    }
    MPI_Comm getComm() const { return 0; }
-   template <class T> int exchangeFullArrayHalo(T &, MeshElement) { return 0; }
+   template <class T> int exchangeFullArrayHalo(T &A, MeshElement E) {
+      if (!callback()) return 0;
+      const int R = A.rank();
+      const int NOuter = R == 3 ? A.extent_int(0) : 1, NInner = R == 1 ? 1 : A.extent_int(R - 1);
+      callback()(static_cast<void *>(A.data()), static_cast<int>(E), NOuter, NInner);
+      return 0;
+   }
 };
 
 #ifdef REF_SHIM_REAL_VERTCOORD
@@ -289,7 +303,12 @@ class Tracers {
       TracerArray = arrays()[TimeIndex];
       return Err;
    }
-   static I4 exchangeHalo(const I4) { return 0; }
+   static I4 exchangeHalo(const I4 TimeLevel) { // Tracers.cpp:457-470
+      I4 TimeIndex;
+      getTimeIndex(TimeIndex, TimeLevel);
+      if (numTracers() > 0) Halo::getDefault()->exchangeFullArrayHalo(arrays()[TimeIndex], OnCell);
+      return 0;
+   }
    static void updateTimeLevels() {
       exchangeHalo(1);
       curTimeIndex() = (curTimeIndex() + 1) % numTimeLevels();
