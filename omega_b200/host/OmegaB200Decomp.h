@@ -217,4 +217,56 @@ class Decomp {
    }
 };
 
+/// Global-order geometry arrays of the mesh file, the ones HorzMesh reads (src/ocn/HorzMesh.cpp:262-525)
+struct GlobalGeometry {
+   const double *AreaCell, *BottomDepth, *XCell, *YCell, *ZCell;     ///< [NCells]
+   const double *DcEdge, *DvEdge, *AngleEdge, *FEdge, *XEdge, *YEdge; ///< [NEdges]
+   const double *WeightsOnEdge;                                       ///< [NEdges][MaxEdges2]
+   const double *AreaTriangle, *FVertex;                              ///< [NVertices]
+   const double *KiteAreasOnVertex;                                   ///< [NVertices][VertexDegree]
+};
+
+/// Local[o][i][k] = Global[o][ID(i) - 1][k] for the NAll local elements of a kind, the boundary row zero: what the
+/// reference's decomposed read of a mesh or state array leaves in a local array (HorzMesh.cpp:262-330)
+inline void gatherField(const Decomp &D, MeshElement E, int NOuter, int NInner, const double *Global, double *Local) {
+   const HostArray1DI4 &ID = E == OnCell ? D.CellIDH : E == OnEdge ? D.EdgeIDH : D.VertexIDH;
+   const size_t NAll = E == OnCell ? D.NCellsAll : E == OnEdge ? D.NEdgesAll : D.NVerticesAll;
+   const size_t NGlob = E == OnCell ? D.NCellsGlobal : E == OnEdge ? D.NEdgesGlobal : D.NVerticesGlobal;
+   for (int o = 0; o < NOuter; ++o) {
+      double *L = Local + (size_t)o * (NAll + 1) * NInner;
+      const double *G = Global + (size_t)o * NGlob * NInner;
+      for (size_t i = 0; i < NAll; ++i)
+         for (int k = 0; k < NInner; ++k) L[i * NInner + k] = G[(size_t)(ID((int)i) - 1) * NInner + k];
+      for (int k = 0; k < NInner; ++k) L[NAll * NInner + k] = 0.0;
+   }
+}
+
+/// The geometry of one task's local mesh in Omega's local numbering
+class LocalGeometry {
+ public:
+   std::vector<double> AreaCell, BottomDepth, XCell, YCell, ZCell, DcEdge, DvEdge, AngleEdge, FEdge, XEdge, YEdge, WeightsOnEdge,
+       AreaTriangle, FVertex, KiteAreasOnVertex;
+   LocalGeometry(const Decomp &D, const GlobalGeometry &G) {
+      auto get = [&](std::vector<double> &Out, MeshElement E, int NInner, const double *Src) {
+         const size_t N = E == OnCell ? D.NCellsSize : E == OnEdge ? D.NEdgesSize : D.NVerticesSize;
+         Out.resize(N * NInner);
+         gatherField(D, E, 1, NInner, Src, Out.data());
+      };
+      get(AreaCell, OnCell, 1, G.AreaCell); get(BottomDepth, OnCell, 1, G.BottomDepth);
+      get(XCell, OnCell, 1, G.XCell); get(YCell, OnCell, 1, G.YCell); get(ZCell, OnCell, 1, G.ZCell);
+      get(DcEdge, OnEdge, 1, G.DcEdge); get(DvEdge, OnEdge, 1, G.DvEdge); get(AngleEdge, OnEdge, 1, G.AngleEdge);
+      get(FEdge, OnEdge, 1, G.FEdge); get(XEdge, OnEdge, 1, G.XEdge); get(YEdge, OnEdge, 1, G.YEdge);
+      get(WeightsOnEdge, OnEdge, D.MaxEdges2, G.WeightsOnEdge);
+      get(AreaTriangle, OnVertex, 1, G.AreaTriangle); get(FVertex, OnVertex, 1, G.FVertex);
+      get(KiteAreasOnVertex, OnVertex, D.VertexDegree, G.KiteAreasOnVertex);
+   }
+   /// the geometry part of an OmegaMeshDesc (Decomp::fillMeshDesc fills the index part)
+   void fillMeshDesc(OmegaMeshDesc &M) const {
+      M.AreaCell = AreaCell.data(); M.BottomDepth = BottomDepth.data(); M.XCell = XCell.data(); M.YCell = YCell.data(); M.ZCell = ZCell.data();
+      M.DcEdge = DcEdge.data(); M.DvEdge = DvEdge.data(); M.AngleEdge = AngleEdge.data(); M.FEdge = FEdge.data();
+      M.XEdge = XEdge.data(); M.YEdge = YEdge.data(); M.WeightsOnEdge = WeightsOnEdge.data();
+      M.AreaTriangle = AreaTriangle.data(); M.FVertex = FVertex.data(); M.KiteAreasOnVertex = KiteAreasOnVertex.data();
+   }
+};
+
 } // namespace OMEGA
