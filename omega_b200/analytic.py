@@ -7,6 +7,9 @@
   ``SshCell = h - BottomDepth`` (LayerThicknessAuxVars.h:63-82) is the free
   surface.  Layers get slightly different velocities so a level-index bug
   cannot hide.
+* ``tc2``  -- Williamson test case 2 (mpas_sw_test_cases.F:223): solid-body zonal flow in geostrophic balance over a
+  flat bottom, an exact STEADY solution of the shallow-water equations, so whatever changes in a run is the
+  discretisation error (tests/test_tc2_steady.py).
 * ``manufactured`` -- initial condition of the manufactured shallow-water
   solution whose source terms are src/ocn/CustomTendencyTerms.cpp:107-210
   (doc/design/OmegaV0ShallowWater.md:656-666), config 1.
@@ -30,6 +33,31 @@ def tc5_bottom_depth(mesh, h0=5960.0, hs0=2000.0):
     dlon = np.minimum(dlon, 2 * np.pi - dlon)
     r = np.minimum(R, np.sqrt(dlon**2 + (lat - np.pi / 6.0) ** 2))
     return h0 - hs0 * (1.0 - r / R)
+
+
+TC2_U0 = 2.0 * np.pi * 6371220.0 / (12.0 * 86400.0)   # one revolution in 12 days
+TC2_H0 = 2.94e4 / GRAV                                  # g h0 = 2.94e4 m^2 / s^2
+
+
+def tc2_bottom_depth(mesh, h0=TC2_H0):
+    """flat bottom at the reference depth (SshCell = h - BottomDepth is then the free-surface deviation)"""
+    return np.full(mesh.nCells, h0)
+
+
+def tc2(L, ntracers, u0=TC2_U0, h0=TC2_H0):
+    """(h, u, tracers) of the steady zonal flow; every layer the same solution (no level factor: a layer with a
+    different velocity would not be in balance with its own thickness)."""
+    K = int(L.NVertLayers)
+    if np.ptp(L.BottomDepth[:-1]) != 0.0:
+        raise ValueError("tc2 needs a flat bottom: set mesh.bottomDepth = tc2_bottom_depth(mesh) before decomposing")
+    a = float(L.sphere_radius)
+    surf = h0 - (a * OMEGA_EARTH * u0 + 0.5 * u0 * u0) * np.sin(L.LatCell) ** 2 / GRAV
+    depth = surf - (h0 - L.BottomDepth)
+    h = np.repeat(depth[:, None], K, 1)
+    u = np.repeat((u0 * np.cos(L.LatEdge) * np.cos(L.AngleEdge))[:, None], K, 1)
+    h[-1], u[-1] = 0.0, 0.0
+    _, _, tr = tc5(L, ntracers)
+    return np.ascontiguousarray(h), np.ascontiguousarray(u), tr
 
 
 def tc5(L, ntracers, u0=20.0, h0=5960.0):
