@@ -59,9 +59,10 @@ def test_tc2_stays_steady_and_the_error_falls_with_resolution():
 
 
 def test_reference_time_level_indexing_lets_a_constant_tracer_drift():
-    """Finding (RawTimeLevelCompat): stepped exactly as the reference indexes its time levels, the
-    tracer update divides by a thickness of another level than the one its flux was built with, and a tracer == 1 does
-    not stay 1; with the levels mapped it does, to the last bit."""
+    """Finding (RawTimeLevelCompat): stepped exactly as the reference indexes its time levels
+    (raw ring indices in Tendencies.cpp:445,546-547 and TimeStepper.cpp:452-453,477,515: on odd steps the tracer update
+    takes thickness and velocity from the other ring buffer, the previous step's), a tracer == 1 does not stay 1; with
+    the levels mapped through the ring it does, to the last bit."""
     _, e1, _, one_ref = _drift(3, hours=1.0, compat=1)
     _, e0, _, one_fix = _drift(3, hours=1.0, compat=0)
     assert one_fix == 0.0 and 1e-6 < one_ref < 1e-2
