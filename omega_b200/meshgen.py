@@ -154,12 +154,14 @@ def _trisk(m: Mesh) -> None:
     e_ids = np.arange(n_edges)
     for side in (0, 1):
         cell = m.cellsOnEdge[:, side].astype(np.int64)
-        n = nn[cell].astype(np.int64)
+        there = cell >= 0                       # a coastal edge has one cell only (cull_cells)
+        cell = np.where(there, cell, 0)
+        n = np.where(there, nn[cell], 1).astype(np.int64)
         pos = (eoc[cell] == e_ids[:, None]).argmax(1)
         sum_r = np.zeros(n_edges)
         sgn = 1.0 if side == 0 else -1.0
         for j in range(1, me):
-            act = j < n
+            act = (j < n) & there
             idx = (pos + j) % n
             vidx = (pos + j - 1) % n
             sum_r = sum_r + R[cell, vidx]
@@ -174,6 +176,65 @@ def _trisk(m: Mesh) -> None:
         base = base + n - 1
     neoe[:] = base
     m.edgesOnEdge, m.weightsOnEdge, m.nEdgesOnEdge = eoe, woe, neoe
+
+
+# --------------------------------------------------------------------------
+# land: remove cells, as the MPAS cell culler does for ocean meshes
+# --------------------------------------------------------------------------
+def cull_cells(m: Mesh, keep) -> Mesh:
+    """The mesh without the cells where `keep` is False (land), in the conventions ocean meshes come in:
+
+    * an edge stays when one of its cells stays, a vertex when one of its cells stays; everything is renumbered in
+      the old order;
+    * references to removed elements become -1 IN PLACE (0 in the file): cellsOnCell keeps its alignment with
+      edgesOnCell, cellsOnVertex with kiteAreasOnVertex (whose values all stay: the geometry did not change);
+    * a coastal edge lists its ocean cell FIRST -- the owner rule of the reference's Decomp ("the first cell ID
+      associated with an edge ... is assumed to own the edge", src/base/Decomp.h:96-99) needs it; where that swaps
+      the cells, the vertices swap and angleEdge turns by pi, so v0 -> v1 = k x n still holds;
+    * edgesOnEdge / weightsOnEdge are rebuilt from the kites of the cells that are left (a coastal edge has the
+      other edges of its one cell), nEdgesOnEdge counts them.
+    The reference reads such a mesh as it reads any (HorzMesh.cpp:262-525); the coast shows up as boundary-slot
+    entries in the local connectivity and EdgeMask = 0 on coastal edges (HorzMesh.cpp:590-598)."""
+    keep = np.asarray(keep, bool)
+    if keep.shape != (m.nCells,) or not keep.any():
+        raise ValueError("keep: one flag per cell, at least one cell left")
+
+    def renumber(flags):
+        mp = np.full(flags.size + 1, -1, np.int64)      # index -1 ("none") maps to -1
+        mp[:-1][flags] = np.arange(int(flags.sum()))
+        return mp
+
+    coe, cov = m.cellsOnEdge.astype(np.int64), m.cellsOnVertex.astype(np.int64)
+    ekeep = keep[coe].any(1)
+    vkeep = keep[cov].any(1)
+    cmap, emap, vmap = renumber(keep), renumber(ekeep), renumber(vkeep)
+    o = Mesh()
+    o.geometry, o.sphere_radius = m.geometry, m.sphere_radius
+    for k in ("Lx", "Ly", "dc"):
+        if k in m:
+            o[k] = m[k]
+    o.nCells, o.nEdges, o.nVertices = int(keep.sum()), int(ekeep.sum()), int(vkeep.sum())
+    o.maxEdges, o.maxEdges2, o.vertexDegree = m.maxEdges, m.maxEdges2, m.vertexDegree
+    i32 = lambda a: a.astype(np.int32)
+    o.cellsOnCell, o.edgesOnCell = i32(cmap[m.cellsOnCell[keep]]), i32(emap[m.edgesOnCell[keep]])
+    o.verticesOnCell, o.nEdgesOnCell = i32(vmap[m.verticesOnCell[keep]]), m.nEdgesOnCell[keep].copy()
+    o.cellsOnVertex, o.edgesOnVertex = i32(cmap[cov[vkeep]]), i32(emap[m.edgesOnVertex[vkeep]])
+    ce, ve = cmap[coe[ekeep]], vmap[m.verticesOnEdge[ekeep]]
+    swap = ce[:, 0] < 0
+    ce[swap], ve[swap] = ce[swap][:, ::-1], ve[swap][:, ::-1]
+    o.cellsOnEdge, o.verticesOnEdge = i32(ce), i32(ve)
+    ang = m.angleEdge[ekeep].copy()
+    ang[swap] = np.where(ang[swap] > 0, ang[swap] - np.pi, ang[swap] + np.pi)
+    o.angleEdge = ang
+    for nm in ("areaCell", "bottomDepth", "meshDensity", "fCell", "xCell", "yCell", "zCell", "lonCell", "latCell"):
+        o[nm] = m[nm][keep].copy()
+    for nm in ("dcEdge", "dvEdge", "fEdge", "xEdge", "yEdge", "zEdge", "lonEdge", "latEdge"):
+        o[nm] = m[nm][ekeep].copy()
+    for nm in ("areaTriangle", "fVertex", "xVertex", "yVertex", "zVertex", "lonVertex", "latVertex", "kiteAreasOnVertex"):
+        o[nm] = m[nm][vkeep].copy()
+    _trisk(o)
+    o.culled_from = dict(cells=np.nonzero(keep)[0], edges=np.nonzero(ekeep)[0], vertices=np.nonzero(vkeep)[0], swapped=swap)
+    return o
 
 
 # --------------------------------------------------------------------------

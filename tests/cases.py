@@ -62,6 +62,37 @@ def plane_case(nx, K, T, **cfgkw):
     return L, cfg, (h, u, tr), dt
 
 
+@functools.lru_cache(maxsize=None)
+def land_mesh(level):
+    """The sphere with a continent (a cap of 25 degrees, which takes a pentagon with it), two islands of one cell and
+    one of two cells removed: coastal edges with one cell, vertices with one or two cells, cells with one to three
+    land neighbours."""
+    m = sphere_mesh(level)
+    d = np.arccos(np.clip(np.cos(m.latCell) * np.cos(0.3) * np.cos(m.lonCell - 1.0) + np.sin(m.latCell) * np.sin(0.3), -1, 1))
+    keep = d > np.radians(25.0)
+    far = np.nonzero(d > np.radians(60.0))[0]
+    islands = [far[7], far[far.size // 2]]
+    pair = far[far.size // 3]
+    islands += [pair, m.cellsOnCell[pair, 0]]
+    keep[islands] = False
+    return meshgen.cull_cells(m, keep)
+
+
+def land_case(level, K, T, **cfgkw):
+    """TC5-style state on the mesh with land; the flow runs into the coast (u is not zero on coastal edges at t = 0,
+    their tendency is masked), every Default.yml term on plus tracer hyperdiffusion."""
+    m = land_mesh(level)
+    L = decomp.build_all(m, 1, K)[0]
+    dc = float(np.mean(m.dcEdge))
+    kw = dict(ViscDel2=1.0e-4 * dc**2 / 60.0 * 10, ViscDel4=1.0e-3 * dc**4 / 600.0,
+              EddyDiff2=1.0e-4 * dc**2 / 60.0, EddyDiff4=1.0e-4 * dc**4 / 600.0)
+    kw.update(cfgkw)
+    cfg = capi.TendConfig.default(**kw)
+    h, u, tr = analytic.tc5(L, T)
+    dt = 6.0 * max(1, int(0.25 * dc / 250.0 / 6.0))
+    return L, cfg, (h, u, tr), dt
+
+
 def all_terms_case(level=3, K=4, T=2):
     """Wind forcing, bottom drag, upwind fluxes on as well."""
     L, cfg, st, dt = sphere_case(level, K, T, WindForcingTendencyEnable=1, BottomDragTendencyEnable=1,

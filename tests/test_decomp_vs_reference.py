@@ -22,6 +22,14 @@ NAMES = {0: "CellID", 1: "EdgeID", 2: "VertexID", 3: "CellLoc", 4: "EdgeLoc", 5:
          16: "CellsOnVertex", 17: "EdgesOnVertex", 18: "NEdgesOnCell", 19: "NEdgesOnEdge"}
 
 
+def _mesh(kind):
+    if kind.startswith("sphere"):
+        return cases.sphere_mesh(int(kind[-1]))
+    if kind.startswith("land"):
+        return cases.land_mesh(int(kind[-1]))      # coastline: -1 entries in every connectivity array
+    return cases.plane_mesh(16, 16, 1000.0)
+
+
 def ref_lib():
     if not os.path.exists(REF):
         mk = os.path.join(ROOT, "oracle", "ref_decomp")
@@ -57,10 +65,11 @@ def run_reference(lib, m, ntasks, hw, task):
 
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
-                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3)])
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3),
+                                            ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4)])
 def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
     lib = ref_lib()
-    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    m = _mesh(kind)
     task = decomp.partition_cells(m, ntasks) if ntasks > 1 else np.zeros(m.nCells, np.int32)
     ref = run_reference(lib, m, ntasks, hw, task)
     locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
@@ -80,7 +89,7 @@ def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
 
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
-                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2)])
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4)])
 def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
     """src/base/Halo.cpp (constructor: neighbours, send / receive lists per index space and halo layer), compiled
     unmodified and run on the reference Decomp of every thread-task over a thread MPI (oracle/ref_decomp/mpi.h:
@@ -88,7 +97,7 @@ def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
     equal the lists the library is given (parallel.build_halo_lists, and omega_decomp_halo_lists of csrc/decomp.cpp)."""
     from omega_b200 import parallel
     lib = ref_lib()
-    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    m = _mesh(kind)
     task = decomp.partition_cells(m, ntasks)
     run_reference(lib, m, ntasks, hw, task)
     locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
@@ -128,7 +137,7 @@ def _ref_exchange(lib, locs, kind_idx, nouter, ninner, arrays):
     assert lib.ref_halo_exchange(kind_idx, nouter, ninner, ptrs) == 0
 
 
-@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2)])
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2), ("land3", 3, 3)])
 def test_reference_exchange_and_message_layout(kind, ntasks, hw):
     """Halo::exchangeFullArrayHalo of the reference itself (Halo.h:768-915) on the thread-tasks: (1) its own HaloTest
     (test/base/HaloTest.cpp:41-99) passes on them -- arrays holding f(global ID) in the owned entries equal the fully
@@ -137,7 +146,7 @@ def test_reference_exchange_and_message_layout(kind, ntasks, hw):
     (tests/test_halo_any_type.py::test_pack_layout_equals_the_reference_message checks the kernel against it)."""
     from omega_b200 import parallel
     lib = ref_lib()
-    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    m = _mesh(kind)
     task = decomp.partition_cells(m, ntasks)
     run_reference(lib, m, ntasks, hw, task)
     locs = decomp.build_all(m, ntasks, 3, hw, cell_task=task)
@@ -170,7 +179,8 @@ def test_reference_exchange_and_message_layout(kind, ntasks, hw):
                     assert np.array_equal(buf[:cnt], a[:, idx, :].ravel()), (k, nouter, ninner, t, nbr, "message layout")
 
 
-@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 1, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2)])
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 1, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2),
+                                            ("land3", 1, 3), ("land4", 4, 3)])
 def test_horzmesh_local_geometry_and_derived_fields_equal_the_reference(kind, ntasks, hw):
     """src/ocn/HorzMesh.cpp compiled unmodified and constructed on every task's reference Decomp (reads its local
     geometry through the IO decompositions it builds from the global IDs; computeEdgeSign, setMasks, setMeshScaling:
@@ -180,7 +190,7 @@ def test_horzmesh_local_geometry_and_derived_fields_equal_the_reference(kind, nt
     from omega_b200 import capi
     from tests.oracle_lib import Oracle
     lib = ref_lib()
-    m = cases.sphere_mesh(int(kind[-1])) if kind.startswith("sphere") else cases.plane_mesh(16, 16, 1000.0)
+    m = _mesh(kind)
     task = decomp.partition_cells(m, ntasks) if ntasks > 1 else np.zeros(m.nCells, np.int32)
     run_reference(lib, m, ntasks, hw, task)
     keep = []

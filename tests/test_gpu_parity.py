@@ -42,9 +42,15 @@ CASES = {
     # 60 = 3 chunks + 12 levels, 24 = 1 chunk + 8 levels; K = 4 and K = 10 above are a single partial chunk
     "sphere3_K60_T2": lambda: cases.sphere_case(3, 60, 2),
     "sphere3_K24_T3": lambda: cases.sphere_case(3, 24, 3),
+    # a coastline (cases.land_mesh): coastal edges with one cell and EdgeMask = 0, vertices with missing cells and
+    # edges, cells with land neighbours -- boundary-slot reads that change OWNED results, which a closed mesh never has
+    "land3_K4_T2": lambda: cases.land_case(3, 4, 2),
+    "land4_K16_T3": lambda: cases.land_case(4, 16, 3),
+    "land3_K3_T1": lambda: cases.land_case(3, 3, 1),
 }
 TILED = {"sphere4_K16_T3", "plane16_K32_T2", "sphere3_K16_T1", "sphere3_K16_T2_nodel4", "sphere3_K64_T32",
-         "sphere3_K80_T2", "sphere3_K64_T3", "sphere3_K60_T2", "sphere3_K24_T3", "sphere3_K4_T2", "plane12_K10_T2"}
+         "sphere3_K80_T2", "sphere3_K64_T3", "sphere3_K60_T2", "sphere3_K24_T3", "sphere3_K4_T2", "plane12_K10_T2",
+         "land3_K4_T2", "land4_K16_T3"}
 
 
 @pytest.fixture(scope="module", params=list(CASES))
@@ -471,9 +477,9 @@ def test_tiled_and_untiled_fused_paths_agree(monkeypatch):
         assert rel_l2(a, b) <= 1e-13, rel_l2(a, b)
 
 
-@pytest.mark.parametrize("fused,K", [(False, 4), (True, 4), (True, 16)])
+@pytest.mark.parametrize("fused,K,land", [(False, 4, False), (True, 4, False), (True, 16, False), (True, 16, True)])
 @pytest.mark.parametrize("ntasks", [2, 3])
-def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
+def test_multirank_emulated_on_one_gpu(ntasks, fused, K, land):
     """N ranks' partitions stepped on one GPU in one process: the library's round pack / unpack kernels,
     exchange lists in device order, phase-split stepping with the halo attached (boundary tiles first,
     halo tiles skipped before an exchange), with device-to-device copies standing in for NCCL.  Checked
@@ -484,8 +490,8 @@ def test_multirank_emulated_on_one_gpu(ntasks, fused, K):
     from tests.oracle_lib import Oracle
     T, nsteps = 2, 3
     level = 4 if K == 16 else 3          # level 4: 2562 cells, enough tiles for all three tile classes
-    mesh_g = cases.sphere_mesh(level)
-    L1, cfg, (h, u, tr), dt = cases.sphere_case(level, K, T)
+    mesh_g = cases.land_mesh(level) if land else cases.sphere_mesh(level)
+    L1, cfg, (h, u, tr), dt = (cases.land_case if land else cases.sphere_case)(level, K, T)
     ref = Oracle(L1, cfg, T)
     ref.make_state(h, u, tr)
     for s in range(nsteps):

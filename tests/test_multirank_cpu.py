@@ -109,12 +109,12 @@ def _multirank_oracle(mesh, ntasks, K, T, cfg, nsteps, dt, stepper, halo_width):
     return locs, orcs
 
 
-def partition_error(ntasks, stepper, halo_width, **cfgkw):
+def partition_error(ntasks, stepper, halo_width, land=False, **cfgkw):
     """max over fields of rel-max difference between the N-rank emulation of
     the reference algorithm and its 1-rank run, over ALL local elements."""
     K, T, nsteps = 3, 2, 4
-    mesh = cases.sphere_mesh(4)
-    L1, cfg, (h, u, tr), dt = cases.sphere_case(4, K, T, **cfgkw)
+    mesh = cases.land_mesh(4) if land else cases.sphere_mesh(4)
+    L1, cfg, (h, u, tr), dt = (cases.land_case if land else cases.sphere_case)(4, K, T, **cfgkw)
     ref = Oracle(L1, cfg, T)
     ref.make_state(h, u, tr)
     for s in range(nsteps):
@@ -146,6 +146,12 @@ NO_DEL4 = dict(VelHyperDiffTendencyEnable=0, TracerHyperDiffTendencyEnable=0)
 def test_results_do_not_depend_on_partition(ntasks, stepper, halo_width, cfgkw):
     """bit-for-bit partition independence (doc/design/OmegaV0ShallowWater.md:57-59)."""
     assert partition_error(ntasks, stepper, halo_width, **cfgkw) == 0.0
+
+
+@pytest.mark.parametrize("ntasks", [2, 5])
+def test_results_do_not_depend_on_partition_with_a_coastline(ntasks):
+    """the same on the mesh with land (cases.land_mesh): partitions that cut the coast"""
+    assert partition_error(ntasks, capi.RK4, 4, land=True) == 0.0
 
 
 def test_reference_needs_halo_width_4_with_del4():
