@@ -93,10 +93,10 @@ def land_case(level, K, T, **cfgkw):
     return L, cfg, (h, u, tr), dt
 
 
-def all_terms_case(level=3, K=4, T=2):
+def all_terms_case(level=3, K=4, T=2, land=False):
     """Wind forcing, bottom drag, upwind fluxes on as well."""
-    L, cfg, st, dt = sphere_case(level, K, T, WindForcingTendencyEnable=1, BottomDragTendencyEnable=1,
-                                 BottomDragCoeff=1.0e-3, FluxThicknessType=1, FluxTracerType=1)
+    L, cfg, st, dt = (land_case if land else sphere_case)(level, K, T, WindForcingTendencyEnable=1, BottomDragTendencyEnable=1,
+                                                          BottomDragCoeff=1.0e-3, FluxThicknessType=1, FluxTracerType=1)
     zonal = 0.1 * np.cos(L.LatCell)
     merid = 0.05 * np.sin(2 * L.LonCell) * np.cos(L.LatCell)
     zonal[-1] = merid[-1] = 0.0

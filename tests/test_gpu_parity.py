@@ -169,10 +169,12 @@ def test_aux_and_tendencies_one_rhs(case, reorder):
     o.close(); st.close(); mesh.close()
 
 
-def test_all_optional_terms_one_rhs():
-    """wind forcing + bottom drag + upwind fluxes (off in Default.yml)."""
+@pytest.mark.parametrize("land", [False, True])
+def test_all_optional_terms_one_rhs(land):
+    """wind forcing + bottom drag + upwind fluxes (off in Default.yml); with a coastline: upwind picks between an
+    ocean cell and the boundary slot, the wind stress is interpolated over vertices with missing cells."""
     from tests.oracle_lib import Oracle
-    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case()
+    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case(land=land)
     T = tr.shape[0]
     mesh, st, state = gpu_objects(L, cfg, T)
     o = Oracle(L, cfg, T)
@@ -324,17 +326,17 @@ def test_rk4_100_steps_state_parity_tiled_kernels(compat):
 
 
 @pytest.mark.parametrize("compat", [True, False])
-@pytest.mark.parametrize("terms", ["upwind", "wind_drag", "all"])
+@pytest.mark.parametrize("terms", ["upwind", "wind_drag", "all", "all_land"])
 def test_fused_tiled_kernels_with_optional_terms(terms, compat):
     """upwind flux options, wind forcing and bottom drag ON THE TILED fused kernels (k_fCT2 /
     k_fET coefficient selection, k_edge_layer_terms), five RK4 steps against the oracle; the path is asserted."""
     from tests.oracle_lib import Oracle
     kw = {}
-    if terms in ("upwind", "all"):
+    if terms in ("upwind", "all", "all_land"):
         kw.update(FluxThicknessType=1, FluxTracerType=1)
-    if terms in ("wind_drag", "all"):
+    if terms in ("wind_drag", "all", "all_land"):
         kw.update(WindForcingTendencyEnable=1, BottomDragTendencyEnable=1, BottomDragCoeff=1.0e-3)
-    L, cfg, (h, u, tr), dt = cases.sphere_case(3, 16, 3, **kw)
+    L, cfg, (h, u, tr), dt = (cases.land_case if terms == "all_land" else cases.sphere_case)(3, 16, 3, **kw)
     zonal = np.ascontiguousarray(0.1 * np.cos(L.LatCell)); zonal[-1] = 0.0
     merid = np.ascontiguousarray(0.05 * np.sin(2 * L.LonCell) * np.cos(L.LatCell)); merid[-1] = 0.0
     T = tr.shape[0]

@@ -48,8 +48,9 @@ def test_rhs_bit_exact(name):
     a.close(); b.close()
 
 
-def test_optional_terms_bit_exact():
-    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case()
+@pytest.mark.parametrize("land", [False, True])
+def test_optional_terms_bit_exact(land):
+    L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case(land=land)
     a, b = pair(L, cfg, tr.shape[0])
     for o in (a, b):
         o.set_wind_stress(zonal, merid)
