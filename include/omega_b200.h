@@ -243,7 +243,9 @@ int omega_tend_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
  * RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:27-82).
  * Advances State by one step and rotates both time-level rings.  Fused=1
  * runs the fused per-stage pipeline (no aux/tendency arrays materialised),
- * Fused=0 the kernel-per-term path that fills every public array.
+ * Fused=0 the kernel-per-term path that fills every public array.  The fused kernels are written for at most six
+ * edges per cell: on a mesh with heptagons (MaxEdges >= 7 in use) Fused=1 steps on the kernel-per-term path, same
+ * results (omega_stepper_last_path tells which path ran).
  * RawTimeLevelCompat=1 reproduces the reference's raw time-level indexing
  * (SURVEY.md 3.5 P1); 0 maps every level through the ring.
  * Halo may be NULL on a single rank; with a Halo (communicator initialised) the step runs its

@@ -133,7 +133,9 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
    // forward-backward with raw time-level indexing and CurTimeIndex == 1: the tracer fluxes see the NEW thickness
    // while the thickness flux sees the old one (ForwardBackwardStepper.cpp:55-60, P1): not one fused cell pass
    const bool fbRaw = Type == OMEGA_STEPPER_FB && RawTimeLevelCompat && State->CurTimeIndex == 1;
-   if (Fused && !fbRaw)
+   // the fused kernels unroll six edges per cell (fused.cu kME); a mesh with heptagons steps on the general kernels
+   const bool wide = S->M->MaxEdgesUsed > 6;
+   if (Fused && !fbRaw && !wide)
       rc = fused_phase(S, Type, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
    else if (Type == OMEGA_STEPPER_RK4)
       rc = rk4_phase(X, State, Coeffs, Phase);

@@ -357,10 +357,52 @@ def icosahedral(level: int, radius: float = SPHERE_RADIUS, bottom_depth: float =
     nrm = np.cross(v[f[:, 1]] - v[f[:, 0]], v[f[:, 2]] - v[f[:, 0]])
     bad = np.einsum("ij,ij->i", nrm, v[f[:, 0]]) < 0
     f[bad] = f[bad][:, [0, 2, 1]]
+    return _sphere_mesh(v, f, 6, radius, bottom_depth)
+
+
+def icosahedral_with_heptagons(level: int, nflips: int = 6, radius: float = SPHERE_RADIUS, bottom_depth: float = 5960.0) -> Mesh:
+    """The icosahedral mesh with `nflips` diagonals of its triangulation flipped: each flip turns two hexagons into
+    pentagons and two into HEPTAGONS (maxEdges = 7, up to 11 edgesOnEdge), the cell shapes variable-resolution ocean
+    meshes have.  The flipped pairs are no longer Delaunay (a vertex lands on a cell centre): geometrically poor,
+    every array finite and consistent -- a connectivity test mesh, not one to measure convergence on."""
+    v, f = _icosahedron()
+    for _ in range(level):
+        v, f = _subdivide(v, f)
+    nrm = np.cross(v[f[:, 1]] - v[f[:, 0]], v[f[:, 2]] - v[f[:, 0]])
+    bad = np.einsum("ij,ij->i", nrm, v[f[:, 0]]) < 0
+    f[bad] = f[bad][:, [0, 2, 1]]
+    f = f.copy()
+    deg = np.bincount(f.reshape(-1), minlength=v.shape[0])
+    touched = np.zeros(v.shape[0], bool)
+    done = 0
+    stride = next(p for p in (211, 223, 227, 229, 233) if f.shape[0] % p)      # spreads the flips over the sphere
+    for t in (np.arange(f.shape[0]) * stride) % f.shape[0]:
+        if done == nflips:
+            break
+        a, b, c = f[t]
+        # the triangle on the other side of a -> b is (b, a, d)
+        cand = np.nonzero((f == a).any(1) & (f == b).any(1))[0]
+        other = [x for x in cand if x != t]
+        if len(other) == 1:
+            t2 = other[0]
+            d = [x for x in f[t2] if x != a and x != b][0]
+            quad = np.array([a, b, c, d])
+            if (deg[quad] == 6).all() and not touched[quad].any():
+                f[t], f[t2] = (a, d, c), (d, b, c)      # a, d, b, c is the quadrilateral in CCW order
+                touched[quad] = True
+                touched[f[(f == a).any(1) | (f == b).any(1) | (f == c).any(1) | (f == d).any(1)].reshape(-1)] = True
+                done += 1
+    if done < nflips:
+        raise ValueError("not enough separate all-hexagon quadrilaterals for %d flips" % nflips)
+    return _sphere_mesh(v, f, 7, radius, bottom_depth)
+
+
+def _sphere_mesh(v, f, max_edges, radius, bottom_depth) -> Mesh:
+    """Voronoi-style mesh on the sphere from a closed CCW triangulation f of the unit vectors v (cell centres)."""
     # spatially coherent file order (z-band then longitude) is NOT applied:
     # file order is subdivision order, the device layer does its own SFC sort
     n_cells = v.shape[0]
-    m = _connectivity(f, n_cells, 6)
+    m = _connectivity(f, n_cells, max_edges)
     m.geometry, m.sphere_radius = "sphere", radius
     pc = v
     t = m.cellsOnVertex

@@ -93,6 +93,27 @@ def land_case(level, K, T, **cfgkw):
     return L, cfg, (h, u, tr), dt
 
 
+@functools.lru_cache(maxsize=None)
+def hept_mesh(level):
+    """12 heptagons and 12 extra pentagons (maxEdges = 7, up to 12 edgesOnEdge): meshgen.icosahedral_with_heptagons"""
+    m = meshgen.icosahedral_with_heptagons(level, 6)
+    m.bottomDepth = analytic.tc5_bottom_depth(m)
+    return m
+
+
+def hept_case(level, K, T, **cfgkw):
+    m = hept_mesh(level)
+    L = decomp.build_all(m, 1, K)[0]
+    dc = float(np.mean(m.dcEdge))
+    kw = dict(ViscDel2=1.0e-4 * dc**2 / 60.0 * 10, ViscDel4=1.0e-3 * dc**4 / 600.0,
+              EddyDiff2=1.0e-4 * dc**2 / 60.0, EddyDiff4=1.0e-4 * dc**4 / 600.0)
+    kw.update(cfgkw)
+    cfg = capi.TendConfig.default(**kw)
+    h, u, tr = analytic.tc5(L, T)
+    dt = 6.0 * max(1, int(0.1 * dc / 250.0 / 6.0))       # the flipped pairs have short dual edges
+    return L, cfg, (h, u, tr), dt
+
+
 def all_terms_case(level=3, K=4, T=2, land=False):
     """Wind forcing, bottom drag, upwind fluxes on as well."""
     L, cfg, st, dt = (land_case if land else sphere_case)(level, K, T, WindForcingTendencyEnable=1, BottomDragTendencyEnable=1,

@@ -25,6 +25,8 @@ NAMES = {0: "CellID", 1: "EdgeID", 2: "VertexID", 3: "CellLoc", 4: "EdgeLoc", 5:
 def _mesh(kind):
     if kind.startswith("sphere"):
         return cases.sphere_mesh(int(kind[-1]))
+    if kind.startswith("hept"):
+        return cases.hept_mesh(int(kind[-1]))      # maxEdges = 7, maxEdges2 = 14
     if kind.startswith("land"):
         return cases.land_mesh(int(kind[-1]))      # coastline: -1 entries in every connectivity array
     return cases.plane_mesh(16, 16, 1000.0)
@@ -66,7 +68,7 @@ def run_reference(lib, m, ntasks, hw, task):
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
                                             ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3),
-                                            ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4)])
+                                            ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3)])
 def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
     lib = ref_lib()
     m = _mesh(kind)
@@ -89,7 +91,7 @@ def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
 
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
-                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4)])
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3)])
 def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
     """src/base/Halo.cpp (constructor: neighbours, send / receive lists per index space and halo layer), compiled
     unmodified and run on the reference Decomp of every thread-task over a thread MPI (oracle/ref_decomp/mpi.h:
@@ -180,7 +182,7 @@ def test_reference_exchange_and_message_layout(kind, ntasks, hw):
 
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 1, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2),
-                                            ("land3", 1, 3), ("land4", 4, 3)])
+                                            ("land3", 1, 3), ("land4", 4, 3), ("hept3", 2, 3)])
 def test_horzmesh_local_geometry_and_derived_fields_equal_the_reference(kind, ntasks, hw):
     """src/ocn/HorzMesh.cpp compiled unmodified and constructed on every task's reference Decomp (reads its local
     geometry through the IO decompositions it builds from the global IDs; computeEdgeSign, setMasks, setMeshScaling:

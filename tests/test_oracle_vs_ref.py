@@ -30,6 +30,7 @@ CASES = {
     "plane12_K5_T2": lambda: cases.plane_case(12, 5, 2),
     "plane16_K1_T0": lambda: cases.plane_case(16, 1, 0),
     "land3_K4_T2": lambda: cases.land_case(3, 4, 2),      # coastline: one-cell edges, EdgeMask = 0, boundary-slot reads
+    "hept3_K4_T2": lambda: cases.hept_case(3, 4, 2),      # maxEdges = 7, rows of 11 and 12 edgesOnEdge
 }
 
 
@@ -78,7 +79,7 @@ def test_manufactured_terms_bit_exact():
 
 
 @pytest.mark.parametrize("stepper", [capi.RK4, capi.RK2, capi.FB])
-@pytest.mark.parametrize("name,dt_override", [("sphere3_K4_T2", None), ("plane12_K5_T2", 10.0), ("land3_K4_T2", None)])
+@pytest.mark.parametrize("name,dt_override", [("sphere3_K4_T2", None), ("plane12_K5_T2", 10.0), ("land3_K4_T2", None), ("hept3_K4_T2", None)])
 def test_steppers_bit_exact(name, stepper, dt_override):
     """5 steps: odd steps exercise the raw time-level indexing; dt = 10 s makes
     RKB*dt = 10/6, 10/3 go through the reference's rational time arithmetic."""
