@@ -239,6 +239,19 @@ int omega_tend_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
                    const OmegaReal *NormalVelEdge, const OmegaReal *NormalVelEdgeRaw,
                    const OmegaReal *TracerArray, double Time, void *Stream);
 
+/* Tendencies::CustomTendencyType (src/ocn/Tendencies.h:51-53; invoked at Tendencies.cpp:288-293 for the thickness
+ * and :416-421 for the velocity): a host term that runs AFTER the built-in terms of a thickness / velocity tendency
+ * evaluation and adds into the tendency array.  Tend, LayerThickness and NormalVelocity are DEVICE arrays in device
+ * order ([NCellsSize][K] / [NEdgesSize][K] rows permuted as omega_mesh_perm says; an element-wise term does not
+ * care); LayerThickness is NULL in the ...Only evaluations, which take no thickness.  The callback enqueues its
+ * work on Stream and returns 0; it runs on the calling host thread, inside omega_tend_* and inside every stage of
+ * omega_stepper_do_step / step_phase.  While a custom term is installed, Fused=1 steps on the kernel-per-term
+ * path (the fused stages never materialise the tendency arrays).  NULL, NULL removes both. */
+typedef int (*OmegaCustomTendency)(void *User, OmegaReal *Tend, const OmegaReal *LayerThickness,
+                                   const OmegaReal *NormalVelocity, double Time, void *Stream);
+int omega_stepper_set_custom_tendencies(OmegaStepper *S, OmegaCustomTendency Thickness, OmegaCustomTendency Velocity,
+                                        void *User);
+
 /* TimeStepper::doStep (src/timeStepping/RungeKutta4Stepper.cpp:68-137,
  * RungeKutta2Stepper.cpp:27-73, ForwardBackwardStepper.cpp:27-82).
  * Advances State by one step and rotates both time-level rings.  Fused=1
@@ -252,8 +265,8 @@ int omega_tend_all(OmegaStepper *S, const OmegaReal *LayerThickCell,
  * exchange rounds itself, overlapped with the interior tiles on the fused tiled path.
  * Fused=1 has no place for a host custom-tendency std::function (src/ocn/Tendencies.h:51-53,
  * Tendencies.cpp:288-293,416-421): the built-in manufactured terms are the only custom terms the fused
- * kernels evaluate; a host that installs its own must step with Fused=0 through
- * omega_tend_* + its callback.
+ * kernels evaluate; with omega_stepper_set_custom_tendencies in force the step runs on the kernel-per-term path,
+ * the callbacks called in every stage.
  * After one warm-up step with the same stepper and configuration the call allocates nothing and never
  * synchronises (Halo == NULL, profiling off): a caller may capture it in a CUDA graph (scratch/probe_graph.py). */
 int omega_stepper_do_step(OmegaStepper *S, OmegaStepperType Type, OmegaStateArrays *State,

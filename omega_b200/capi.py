@@ -11,6 +11,8 @@ c_int_p = C.POINTER(C.c_int)
 c_dbl_p = C.POINTER(C.c_double)
 
 ON_CELL, ON_EDGE, ON_VERTEX = 0, 1, 2
+# OmegaCustomTendency: int (*)(void *User, Real *Tend, const Real *H, const Real *U, double Time, void *Stream)
+CUSTOM_TENDENCY = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p)
 RK4, RK2, FB = 0, 1, 2
 
 

@@ -135,7 +135,9 @@ int omega_stepper_step_phase(OmegaStepper *S, OmegaStepperType Type, OmegaStateA
    const bool fbRaw = Type == OMEGA_STEPPER_FB && RawTimeLevelCompat && State->CurTimeIndex == 1;
    // the fused kernels unroll six edges per cell (fused.cu kME); a mesh with heptagons steps on the general kernels
    const bool wide = S->M->MaxEdgesUsed > 6;
-   if (Fused && !fbRaw && !wide)
+   // a host custom tendency runs between the built-in terms and the stage update: not inside a fused stage
+   const bool custom = S->CustomThick || S->CustomVel;
+   if (Fused && !fbRaw && !wide && !custom)
       rc = fused_phase(S, Type, State, Coeffs, Phase, RawTimeLevelCompat, (cudaStream_t)Stream);
    else if (Type == OMEGA_STEPPER_RK4)
       rc = rk4_phase(X, State, Coeffs, Phase);

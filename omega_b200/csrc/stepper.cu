@@ -228,20 +228,45 @@ int omega_aux_compute_all(OmegaStepper *S, const Real *H, const Real *U, const R
 }
 
 // ---- Tendencies ---------------------------------------------------------------
-int omega_tend_thickness_only(OmegaStepper *S, const Real *U, double Time, void *Stream) {
-   OMEGA_REQUIRE(S && U, "omega_tend_thickness_only: null argument");
+// built-in terms, then the host's custom term if one is installed (Tendencies.cpp:288-293, 416-421); H is the
+// thickness of the evaluation when the caller has one (the ...Only entry points of the C ABI do not)
+static int thick_tend(OmegaStepper *S, const Real *H, const Real *U, double Time, void *Stream) {
    Launch L{(cudaStream_t)Stream, &S->Launches};
    launch_thick_tend(L, S->M->D, S->Cfg, S->A, U, S->T.LayerThicknessTend, manufactured(S, Time));
    OMEGA_CUDA_CHECK(cudaGetLastError());
+   if (S->CustomThick) {
+      const int rc = S->CustomThick(S->CustomUser, S->T.LayerThicknessTend, H, U, Time, Stream);
+      OMEGA_REQUIRE(rc == 0, "custom thickness tendency returned an error");
+   }
    return 0;
+}
+static int vel_tend(OmegaStepper *S, const Real *H, const Real *U, const Real *URaw, double Time, void *Stream) {
+   Launch L{(cudaStream_t)Stream, &S->Launches};
+   launch_vel_tend(L, S->M->D, S->Cfg, S->A, U, URaw, S->T.NormalVelocityTend, manufactured(S, Time));
+   OMEGA_CUDA_CHECK(cudaGetLastError());
+   if (S->CustomVel) {
+      const int rc = S->CustomVel(S->CustomUser, S->T.NormalVelocityTend, H, U, Time, Stream);
+      OMEGA_REQUIRE(rc == 0, "custom velocity tendency returned an error");
+   }
+   return 0;
+}
+
+int omega_stepper_set_custom_tendencies(OmegaStepper *S, OmegaCustomTendency Thickness, OmegaCustomTendency Velocity, void *User) {
+   OMEGA_REQUIRE(S, "omega_stepper_set_custom_tendencies: null stepper");
+   S->CustomThick = Thickness;
+   S->CustomVel   = Velocity;
+   S->CustomUser  = User;
+   return 0;
+}
+
+int omega_tend_thickness_only(OmegaStepper *S, const Real *U, double Time, void *Stream) {
+   OMEGA_REQUIRE(S && U, "omega_tend_thickness_only: null argument");
+   return thick_tend(S, nullptr, U, Time, Stream);
 }
 
 int omega_tend_velocity_only(OmegaStepper *S, const Real *U, const Real *URaw, double Time, void *Stream) {
    OMEGA_REQUIRE(S && U && URaw, "omega_tend_velocity_only: null argument");
-   Launch L{(cudaStream_t)Stream, &S->Launches};
-   launch_vel_tend(L, S->M->D, S->Cfg, S->A, U, URaw, S->T.NormalVelocityTend, manufactured(S, Time));
-   OMEGA_CUDA_CHECK(cudaGetLastError());
-   return 0;
+   return vel_tend(S, nullptr, U, URaw, Time, Stream);
 }
 
 int omega_tend_tracer_only(OmegaStepper *S, const Real *URaw, const Real *Tr, void *Stream) {
@@ -258,14 +283,15 @@ int omega_tend_thickness(OmegaStepper *S, const Real *H, const Real *U, double T
    OMEGA_REQUIRE(S && H && U, "omega_tend_thickness: null argument");
    Launch L{(cudaStream_t)Stream, &S->Launches};
    launch_edge_aux2(L, S->M->D, H, U, S->A, S->Cfg.FluxThicknessType, 1);
-   return omega_tend_thickness_only(S, U, Time, Stream);
+   return thick_tend(S, H, U, Time, Stream);
 }
 
 int omega_tend_velocity(OmegaStepper *S, const Real *H, const Real *U, const Real *URaw, double Time,
                         void *Stream) {
+   OMEGA_REQUIRE(URaw, "omega_tend_velocity: null argument");
    int rc = omega_aux_compute_mom(S, H, U, Stream);
    if (rc) return rc;
-   return omega_tend_velocity_only(S, U, URaw, Time, Stream);
+   return vel_tend(S, H, U, URaw, Time, Stream);
 }
 
 int omega_tend_tracer(OmegaStepper *S, const Real *HRaw, const Real *URaw, const Real *Tr, void *Stream) {
@@ -279,9 +305,10 @@ int omega_tend_all(OmegaStepper *S, const Real *H, const Real *U, const Real *UR
                    double Time, void *Stream) {
    int rc = omega_aux_compute_all(S, H, U, Tr, Stream);
    if (rc) return rc;
-   rc = omega_tend_thickness_only(S, U, Time, Stream);
+   OMEGA_REQUIRE(URaw, "omega_tend_all: null argument");
+   rc = thick_tend(S, H, U, Time, Stream);
    if (rc) return rc;
-   rc = omega_tend_velocity_only(S, U, URaw, Time, Stream);
+   rc = vel_tend(S, H, U, URaw, Time, Stream);
    if (rc) return rc;
    return omega_tend_tracer_only(S, URaw, Tr, Stream);
 }

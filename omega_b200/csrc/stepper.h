@@ -25,6 +25,9 @@ struct OmegaStepper {
    int LastPath;           // OMEGA_PATH_* bits of the kernels the last step phase ran
    struct OmegaHalo *Halo; // attached halo (omega_stepper_attach_halo): boundary tiles first, halo tiles skipped
    int SplitRecorded;      // the last phase recorded Halo->EvReady after its boundary tiles
+   // host custom tendencies (Tendencies.h:51-53): called after the built-in terms of the kernel-per-term path
+   OmegaCustomTendency CustomThick = nullptr, CustomVel = nullptr;
+   void *CustomUser = nullptr;
    std::vector<void *> Allocs;
    // optional per-kernel CUDA-event timing of the fused pipeline (bench roofline)
    int Profiling;

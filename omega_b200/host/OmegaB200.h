@@ -11,6 +11,7 @@
 #pragma once
 #include <cstdio>
 #include <cstdlib>
+#include <functional>
 #include <map>
 #include <memory>
 #include <string>
@@ -149,6 +150,12 @@ class OceanState {
          LayerThickness.emplace_back("LayerThickness" + Name + std::to_string(i), std::initializer_list<long>{M->NCellsSize, NVertLayers});
          NormalVelocity.emplace_back("NormalVelocity" + Name + std::to_string(i), std::initializer_list<long>{M->NEdgesSize, NVertLayers});
       }
+   }
+   /// one time level over arrays somebody else owns: the state a custom tendency is handed for a stage
+   /// (the reference passes its one-level ProvisState there, RungeKutta4Stepper.cpp:57-58)
+   OceanState(const HorzMesh *M, double *H, double *U, int NVertLayers_) : NTimeLevels(1), NVertLayers(NVertLayers_), Mesh(M), MeshHalo(nullptr) {
+      LayerThickness.emplace_back("LayerThicknessStage", H, std::initializer_list<long>{M->NCellsSize, NVertLayers});
+      NormalVelocity.emplace_back("NormalVelocityStage", U, std::initializer_list<long>{M->NEdgesSize, NVertLayers});
    }
    I4 getTimeIndex(I4 &TimeIndex, I4 TimeLevel) const { // OceanState.cpp:394-407
       if (NTimeLevels > 1 && (TimeLevel > 1 || (TimeLevel + NTimeLevels) <= 1)) return -1;

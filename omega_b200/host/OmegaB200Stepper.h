@@ -3,6 +3,7 @@
 // objects; their public array members alias the library-owned device arrays
 // (src/ocn/AuxiliaryState.h:37-42, src/ocn/Tendencies.h:55-57).
 #pragma once
+#include <functional>
 #include <cmath>
 #include "OmegaB200.h"
 
@@ -61,11 +62,35 @@ class AuxiliaryState {
 
 class Tendencies {
  public:
+   /// src/ocn/Tendencies.h:51-53: a host term called after the built-in terms of a thickness / velocity tendency
+   /// evaluation; it adds into the tendency array (first argument).  Here the arrays are device arrays in device
+   /// order, the state is a one-level view of the thickness and velocity of the evaluation (levels 0, 0; the
+   /// thickness is empty in the ...Only evaluations), the time is in seconds, and the work goes on customStream().
+   using CustomTendencyType = std::function<void(Array2DReal, const OceanState *, const AuxiliaryState *, int, int, double)>;
+
    Array2DReal LayerThicknessTend, NormalVelocityTend;
    Array3DReal TracerTend;
    OmegaStepper *Handle; // shared with the AuxiliaryState it was built on
 
-   Tendencies(const std::string &Name, const HorzMesh *M, const AuxiliaryState *Aux, int NVertLayers) : Handle(Aux->Handle) {
+   /// Tendencies::create with custom terms (Tendencies.h:150-157); while one is installed TimeStepper::doStep runs
+   /// the kernel-per-term path, the callbacks called in every stage (Tendencies.cpp:288-293, 416-421)
+   Tendencies(const std::string &Name, const HorzMesh *M, const AuxiliaryState *Aux, int NVertLayers, CustomTendencyType CustomThick,
+              CustomTendencyType CustomVel)
+       : Tendencies(Name, M, Aux, NVertLayers) {
+      setCustomTendencies(std::move(CustomThick), std::move(CustomVel));
+   }
+   void setCustomTendencies(CustomTendencyType CustomThick, CustomTendencyType CustomVel) {
+      CustomThicknessTend = std::move(CustomThick);
+      CustomVelocityTend  = std::move(CustomVel);
+      OMEGA_B200_CHECK(omega_stepper_set_custom_tendencies(Handle, CustomThicknessTend ? &thickTrampoline : nullptr,
+                                                           CustomVelocityTend ? &velTrampoline : nullptr, this),
+                       "Tendencies: omega_stepper_set_custom_tendencies");
+   }
+   void *customStream() const { return CustomStream; }
+   Tendencies(const Tendencies &) = delete; // the library holds `this` while a custom term is installed
+
+   Tendencies(const std::string &Name, const HorzMesh *M, const AuxiliaryState *Aux, int NVertLayers)
+       : Handle(Aux->Handle), Mesh(M), AuxState(Aux), NVertLayersT(NVertLayers) {
       OmegaTendArrays T;
       OMEGA_B200_CHECK(omega_stepper_tend_arrays(Handle, &T), "omega_stepper_tend_arrays");
       const long K = NVertLayers;
@@ -103,6 +128,27 @@ class Tendencies {
    }
    void computeAllTendencies(const OceanState *S, const AuxiliaryState *, const Array3DReal &Tr, int ThickLvl, int VelLvl, double Time, void *St = nullptr) {
       OMEGA_B200_CHECK(omega_tend_all(Handle, mapH(S, ThickLvl), mapU(S, VelLvl), rawU(S, VelLvl), Tr.data(), Time, St), "computeAllTendencies");
+   }
+
+ private:
+   const HorzMesh *Mesh;
+   const AuxiliaryState *AuxState;
+   int NVertLayersT;
+   CustomTendencyType CustomThicknessTend, CustomVelocityTend;
+   void *CustomStream = nullptr;
+   static int trampoline(void *User, bool Vel, double *, const double *H, const double *U, double Time, void *Stream) {
+      auto *Self = static_cast<Tendencies *>(User);
+      OceanState Stage(Self->Mesh, const_cast<double *>(H), const_cast<double *>(U), Self->NVertLayersT);
+      Self->CustomStream = Stream;
+      if (Vel) Self->CustomVelocityTend(Self->NormalVelocityTend, &Stage, Self->AuxState, 0, 0, Time);
+      else Self->CustomThicknessTend(Self->LayerThicknessTend, &Stage, Self->AuxState, 0, 0, Time);
+      return 0;
+   }
+   static int thickTrampoline(void *User, double *T, const double *H, const double *U, double Time, void *Stream) {
+      return trampoline(User, false, T, H, U, Time, Stream);
+   }
+   static int velTrampoline(void *User, double *T, const double *H, const double *U, double Time, void *Stream) {
+      return trampoline(User, true, T, H, U, Time, Stream);
    }
 };
 

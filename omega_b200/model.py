@@ -197,6 +197,41 @@ class Stepper:
         _chk(self.lib, self.lib.omega_stepper_set_wind_stress(self.h, z.ctypes.data_as(capi.c_dbl_p), m.ctypes.data_as(capi.c_dbl_p), _stream()), "set_wind_stress")
         torch.cuda.current_stream().synchronize()
 
+    # -- custom tendencies (Tendencies.h:51-53) ------------------------------------
+    def _device_tensor(self, ptr, kind):
+        """torch view (no copy) of a library-owned [N*Size][K] device array in device order"""
+        if not ptr:
+            return None
+
+        class _Dev:
+            pass
+        d = _Dev()
+        m = self.mesh
+        d.__cuda_array_interface__ = dict(shape=(m.NSize[kind], m.K), typestr="<f8" if m.real_bytes == 8 else "<f4",
+                                          data=(int(ptr), False), version=2)
+        return torch.as_tensor(d, device=m.device)
+
+    def set_custom_tendencies(self, thickness=None, velocity=None):
+        """thickness / velocity: callables fn(tend, h, u, time) on torch views of the device arrays (device order;
+        h is None in the ...Only evaluations) that ADD their term into tend on torch's current stream -- the role of
+        Tendencies::CustomThicknessTend / CustomVelocityTend.  None, None removes them."""
+        def make(fn, kind):
+            if fn is None:
+                return capi.CUSTOM_TENDENCY(0)
+
+            def cb(user, tend, h, u, time, stream):
+                try:
+                    fn(self._device_tensor(tend, kind), self._device_tensor(h, ON_CELL), self._device_tensor(u, ON_EDGE), float(time))
+                    return 0
+                except Exception as e:   # an exception must not cross the C frame
+                    self._custom_error = e
+                    return 1
+            return capi.CUSTOM_TENDENCY(cb)
+        self._custom_error = None
+        self._custom = (make(thickness, ON_CELL), make(velocity, ON_EDGE))   # keep the trampolines alive
+        _chk(self.lib, self.lib.omega_stepper_set_custom_tendencies(self.h, self._custom[0], self._custom[1], None),
+             "omega_stepper_set_custom_tendencies")
+
     # -- AuxiliaryState / Tendencies ---------------------------------------------
     def computeMomAux(self, h, u):
         _chk(self.lib, self.lib.omega_aux_compute_mom(self.h, _dptr(h), _dptr(u), _stream()), "omega_aux_compute_mom")

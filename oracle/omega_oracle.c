@@ -41,6 +41,9 @@ typedef struct OracleStepper {
    OmegaTendArrays Tend;
    /* RungeKutta4Stepper::finalizeInit, src/timeStepping/RungeKutta4Stepper.cpp:43-64 */
    double *ProvisH, *ProvisU, *ProvisTr;
+   /* Tendencies::CustomThicknessTend / CustomVelocityTend, src/ocn/Tendencies.h:51-53,182-183 */
+   OmegaCustomTendency CustomThick, CustomVel;
+   void *CustomUser;
 } OracleStepper;
 
 static double *zalloc(size_t n) {
@@ -410,7 +413,7 @@ static void manufactured_vel(OracleStepper *S, double Time) {
 
 /* Tendencies::computeThicknessTendenciesOnly, src/ocn/Tendencies.cpp:257-297
    functor ThicknessFluxDivOnCell, src/ocn/TendencyTerms.h:35-58 */
-int oracle_tend_thickness_only(OracleStepper *S, const double *U, double Time) {
+static int thick_tend(OracleStepper *S, const double *H, const double *U, double Time) {
    const OmegaMeshDesc *M = &S->M;
    const int K = S->K, ME = M->MaxEdges;
    double *Tend = S->Tend.LayerThicknessTend;
@@ -430,13 +433,16 @@ int oracle_tend_thickness_only(OracleStepper *S, const double *U, double Time) {
       }
    }
    if (S->Cfg.ManufacturedSolutionTendency) manufactured_thick(S, Time);
+   /* a custom term installed by the host, Tendencies.cpp:288-293 */
+   if (S->CustomThick && S->CustomThick(S->CustomUser, Tend, H, U, Time, NULL)) return 1;
    return 0;
 }
+int oracle_tend_thickness_only(OracleStepper *S, const double *U, double Time) { return thick_tend(S, NULL, U, Time); }
 
 /* Tendencies::computeVelocityTendenciesOnly, src/ocn/Tendencies.cpp:301-425;
    functors src/ocn/TendencyTerms.h:81-334.  U = getNormalVelocity(VelTimeLevel)
    view, URaw = State->NormalVelocity[VelTimeLevel] (raw index, :322). */
-int oracle_tend_velocity_only(OracleStepper *S, const double *U, const double *URaw, double Time) {
+static int vel_tend(OracleStepper *S, const double *H, const double *U, const double *URaw, double Time) {
    const OmegaMeshDesc *M = &S->M;
    const OmegaAuxArrays *A = &S->Aux;
    const OmegaTendConfig *G = &S->Cfg;
@@ -517,6 +523,17 @@ int oracle_tend_velocity_only(OracleStepper *S, const double *U, const double *U
       }
    }
    if (G->ManufacturedSolutionTendency) manufactured_vel(S, Time);
+   /* a custom term installed by the host, Tendencies.cpp:416-421 */
+   if (S->CustomVel && S->CustomVel(S->CustomUser, Tend, H, U, Time, NULL)) return 1;
+   return 0;
+}
+int oracle_tend_velocity_only(OracleStepper *S, const double *U, const double *URaw, double Time) {
+   return vel_tend(S, NULL, U, URaw, Time);
+}
+int oracle_stepper_set_custom_tendencies(OracleStepper *S, OmegaCustomTendency Thickness, OmegaCustomTendency Velocity, void *User) {
+   S->CustomThick = Thickness;
+   S->CustomVel   = Velocity;
+   S->CustomUser  = User;
    return 0;
 }
 
@@ -588,13 +605,13 @@ int oracle_tend_tracer_only(OracleStepper *S, const double *URaw, const double *
 /* Tendencies::computeThicknessTendencies, src/ocn/Tendencies.cpp:488-519 */
 int oracle_tend_thickness(OracleStepper *S, const double *H, const double *U, double Time) {
    aux_thick_edge(S, H, U);
-   return oracle_tend_thickness_only(S, U, Time);
+   return thick_tend(S, H, U, Time);
 }
 /* Tendencies::computeVelocityTendencies, :521-535 */
 int oracle_tend_velocity(OracleStepper *S, const double *H, const double *U, const double *URaw,
                          double Time) {
    oracle_aux_compute_mom(S, H, U);
-   return oracle_tend_velocity_only(S, U, URaw, Time);
+   return vel_tend(S, H, U, URaw, Time);
 }
 /* Tendencies::computeTracerTendencies, :537-575 (raw-indexed H and U, :546-547) */
 int oracle_tend_tracer(OracleStepper *S, const double *HRaw, const double *URaw, const double *Tr) {
@@ -605,8 +622,8 @@ int oracle_tend_tracer(OracleStepper *S, const double *HRaw, const double *URaw,
 int oracle_tend_all(OracleStepper *S, const double *H, const double *U, const double *URaw,
                     const double *Tr, double Time) {
    oracle_aux_compute_all(S, H, U, Tr);
-   oracle_tend_thickness_only(S, U, Time);
-   oracle_tend_velocity_only(S, U, URaw, Time);
+   thick_tend(S, H, U, Time);
+   vel_tend(S, H, U, URaw, Time);
    oracle_tend_tracer_only(S, URaw, Tr);
    return 0;
 }

@@ -75,6 +75,25 @@ const char *stepper_name(int Kind) {
    return Kind == OMEGA_STEPPER_RK4 ? "RungeKutta4" : Kind == OMEGA_STEPPER_RK2 ? "RungeKutta2" : "Forward-Backward";
 }
 
+// Host custom tendencies (TimeStepperTest.cpp:49-72 installs one through the public Tendencies::create): a second
+// Tendencies object "Custom" whose two std::function members forward to C function pointers
+OmegaCustomTendency GThick = nullptr, GVel = nullptr;
+void *GUser                = nullptr;
+Tendencies *CustomTend     = nullptr;
+Tendencies *active_tend() { return CustomTend ? CustomTend : Tendencies::getDefault(); }
+
+Tendencies::CustomTendencyType forward_to(OmegaCustomTendency *Slot) {
+   return [Slot](Array2DReal Tend, const OceanState *State, const AuxiliaryState *, int ThickLevel, int VelLevel, TimeInstant Time) {
+      if (!*Slot) return;
+      Array2DReal H, U;
+      State->getLayerThickness(H, ThickLevel);
+      State->getNormalVelocity(U, VelLevel);
+      R8 Seconds;
+      (Time - TimeStepper::getDefault()->getStartTime()).get(Seconds, TimeUnits::Seconds);
+      (*Slot)(GUser, Tend.data(), H.data(), U.data(), Seconds, nullptr);
+   };
+}
+
 // (re)create the default time stepper with the reference's two-phase init
 void init_stepper(RefStepper *R, int Kind, double Dt, bool Attach) {
    TimeStepper::clear();
@@ -91,7 +110,9 @@ void init_stepper(RefStepper *R, int Kind, double Dt, bool Attach) {
    S["StopTime"] = "0101-01-01_00:00:00";
    S["RunDuration"] = "none";
    TimeStepper::init1(); // src/timeStepping/TimeStepper.cpp:226-305
-   if (Attach) TimeStepper::init2();
+   if (Attach) { // TimeStepper::init2 (TimeStepper.cpp:302-312) with the tendencies in force
+      TimeStepper::getDefault()->attachData(active_tend(), AuxiliaryState::getDefault(), HorzMesh::getDefault(), Halo::getDefault());
+   }
    R->StepperKind = Kind;
    R->Dt = Dt;
 }
@@ -193,6 +214,8 @@ int oracle_stepper_create(const OmegaMeshDesc *D, const OmegaTendConfig *Cfg, in
    OceanState::init();      // src/ocn/OceanState.cpp:30-60
    AuxiliaryState::init();  // src/ocn/AuxiliaryState.cpp:206-219
    Tendencies::init();      // src/ocn/Tendencies.cpp:26-72 (reads the config, builds the manufactured terms)
+   CustomTend = nullptr;
+   GThick = GVel = nullptr;
    TimeStepper::init2();
    Live = R;
    *Out = R;
@@ -204,6 +227,8 @@ int oracle_stepper_destroy(RefStepper *R) {
    if (Live == R) {
       TimeStepper::clear();
       Tendencies::clear();
+      CustomTend = nullptr;
+      GThick = GVel = nullptr;
       AuxiliaryState::clear();
       OceanState::clear();
       Tracers::arrays().clear();
@@ -219,6 +244,7 @@ int oracle_stepper_set_config(RefStepper *R, const OmegaTendConfig *Cfg) {
    push_config(*Cfg);
    Config TendConfig("Tendencies");
    Tendencies::getDefault()->readTendConfig(&TendConfig);
+   if (CustomTend) CustomTend->readTendConfig(&TendConfig);
    AuxiliaryState::getDefault()->readConfigOptions(Config::getOmegaConfig());
    return 0;
 }
@@ -246,8 +272,25 @@ int oracle_stepper_aux_arrays(RefStepper *, OmegaAuxArrays *A) {
    return 0;
 }
 
+int oracle_stepper_set_custom_tendencies(RefStepper *R, OmegaCustomTendency Thickness, OmegaCustomTendency Velocity, void *User) {
+   if (R->Cfg.ManufacturedSolutionTendency) return 2; // Tendencies::init gave those slots to the manufactured terms
+   GThick = Thickness;
+   GVel   = Velocity;
+   GUser  = User;
+   if ((Thickness || Velocity) && !CustomTend) {
+      Config TendConfig("Tendencies");
+      Config::getOmegaConfig()->get(TendConfig);
+      CustomTend = Tendencies::create("Custom", HorzMesh::getDefault(), VertCoord::getDefault(), R->T, &TendConfig, forward_to(&GThick),
+                                      forward_to(&GVel));
+      if (!CustomTend) return 1;
+      CustomTend->readTendConfig(&TendConfig);
+   }
+   init_stepper(R, R->StepperKind, R->Dt, true);
+   return 0;
+}
+
 int oracle_stepper_tend_arrays(RefStepper *, OmegaTendArrays *T) {
-   Tendencies *X = Tendencies::getDefault();
+   Tendencies *X = active_tend();
    T->LayerThicknessTend = X->LayerThicknessTend.data();
    T->NormalVelocityTend = X->NormalVelocityTend.data();
    T->TracerTend = X->TracerTend.data();
@@ -285,28 +328,28 @@ int oracle_aux_compute_all(RefStepper *R, const double *H, const double *U, cons
 // indexing requires StateIdx == 0 (always true before the first doStep)
 int oracle_tend_thickness_only(RefStepper *R, const double *U, double Time) {
    load_state(R, nullptr, U);
-   Tendencies::getDefault()->computeThicknessTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), 0, 0, time_at(Time));
+   active_tend()->computeThicknessTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), 0, 0, time_at(Time));
    return 0;
 }
 
 int oracle_tend_velocity_only(RefStepper *R, const double *U, const double *URaw, double Time) {
    if (U != URaw || R->StateIdx != 0) return 2;
    load_state(R, nullptr, U);
-   Tendencies::getDefault()->computeVelocityTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), 0, 0, time_at(Time));
+   active_tend()->computeVelocityTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), 0, 0, time_at(Time));
    return 0;
 }
 
 int oracle_tend_tracer_only(RefStepper *R, const double *URaw, const double *Tr) {
    if (R->StateIdx != 0) return 2;
    load_state(R, nullptr, URaw);
-   Tendencies::getDefault()->computeTracerTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), wrap_tracers(R, Tr), 0, 0, time_at(0.0));
+   active_tend()->computeTracerTendenciesOnly(OceanState::getDefault(), AuxiliaryState::getDefault(), wrap_tracers(R, Tr), 0, 0, time_at(0.0));
    return 0;
 }
 
 int oracle_tend_all(RefStepper *R, const double *H, const double *U, const double *URaw, const double *Tr, double Time) {
    if (U != URaw || R->StateIdx != 0) return 2;
    load_state(R, H, U);
-   Tendencies::getDefault()->computeAllTendencies(OceanState::getDefault(), AuxiliaryState::getDefault(), wrap_tracers(R, Tr), 0, 0, time_at(Time));
+   active_tend()->computeAllTendencies(OceanState::getDefault(), AuxiliaryState::getDefault(), wrap_tracers(R, Tr), 0, 0, time_at(Time));
    return 0;
 }
 

@@ -5,6 +5,7 @@
 // .bin files written by tests/test_host_mirror.py, results go back the same way.
 #include <chrono>
 #include <cstdio>
+#include <cublas_v2.h>
 #include <cuda_runtime_api.h>
 #include <fstream>
 #include <thread>
@@ -110,6 +111,20 @@ int main(int argc, char **argv) {
    Tracers Trc(&Mesh, MeshHalo.get(), T, K, 2);
    AuxiliaryState Aux("Default", &Mesh, nullptr, K, T, Cfg);
    Tendencies Tend("Default", &Mesh, &Aux, K);
+   // "Custom 1": the custom velocity tendency of the reference's TimeStepperTest (du/dt -= 0.5 u,
+   // test/timeStepping/TimeStepperTest.cpp:49-72) installed the way that test does, as a std::function; the device
+   // work is one cuBLAS axpy on the stream the library hands over
+   cublasHandle_t Blas = nullptr;
+   if (Meta["Custom"] != 0) {
+      if (cublasCreate(&Blas) != CUBLAS_STATUS_SUCCESS) { std::fprintf(stderr, "cublasCreate failed\n"); return 5; }
+      Tend.setCustomTendencies(nullptr, [&](Array2DReal VelTend, const OceanState *Stage, const AuxiliaryState *, int, int VelLevel, double) {
+         Array2DReal U;
+         Stage->getNormalVelocity(U, VelLevel);
+         const double Alpha = -0.5;
+         cublasSetStream(Blas, static_cast<cudaStream_t>(Tend.customStream()));
+         if (cublasDaxpy(Blas, (int)VelTend.size(), &Alpha, U.data(), 1, VelTend.data(), 1) != CUBLAS_STATUS_SUCCESS) std::abort();
+      });
+   }
    TimeStepper Stepper(Kind == 0 ? TimeStepperType::RungeKutta4 : Kind == 1 ? TimeStepperType::RungeKutta2
                                                                           : TimeStepperType::ForwardBackward,
                        Dt, &Tend, &Aux, &Trc);
@@ -214,6 +229,10 @@ int main(int argc, char **argv) {
       omega_dev_download(xs.data(), X.data(), B); omega_dev_download(xs2.data(), X2.data(), B);
       save("out_tridiag_diff", xs); save("out_tridiag", xs2);
       save("in_tridiag_g", g); save("in_tridiag_h", hd); save("in_tridiag_x", x);
+   }
+   if (Blas) {
+      Tend.setCustomTendencies(nullptr, nullptr);
+      cublasDestroy(Blas);
    }
    std::printf("host mirror: %d steps, SimTime %.1f\n", NSteps, SimTime);
    return 0;

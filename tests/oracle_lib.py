@@ -64,6 +64,28 @@ class Oracle:
             return np.zeros(shape)
         return np.ctypeslib.as_array(ptr, shape=(n,)).reshape(shape)
 
+    def set_custom_tendencies(self, thickness=None, velocity=None):
+        """fn(tend, h, u, time) on numpy views (host order; h is None in the ...Only evaluations of the C oracle) that
+        ADD into tend: Tendencies::CustomThicknessTend / CustomVelocityTend (Tendencies.h:51-53)."""
+        def make(fn, kind):
+            if fn is None:
+                return capi.CUSTOM_TENDENCY(0)
+
+            def cb(user, tend, h, u, time, stream):
+                dp = C.POINTER(C.c_double)
+                v = lambda p, k: None if not p else self._view(C.cast(p, dp), k, 1, 0)
+                fn(v(tend, kind), v(h, capi.ON_CELL), v(u, capi.ON_EDGE), float(time))
+                return 0
+            return capi.CUSTOM_TENDENCY(cb)
+        self._custom = (make(thickness, capi.ON_CELL), make(velocity, capi.ON_EDGE))
+        rc = self.lib.oracle_stepper_set_custom_tendencies(self.h, self._custom[0], self._custom[1], None)
+        assert rc == 0, rc
+        tend = capi.TendArrays()
+        self.lib.oracle_stepper_tend_arrays(self.h, C.byref(tend))     # the reference build switches to another object
+        self.tend = {"LayerThicknessTend": self._view(tend.LayerThicknessTend, capi.ON_CELL, 1, 0),
+                     "NormalVelocityTend": self._view(tend.NormalVelocityTend, capi.ON_EDGE, 1, 0),
+                     "TracerTend": self._view(tend.TracerTend, capi.ON_CELL, 1, 1)}
+
     def close(self):
         if self.h:
             self.lib.oracle_stepper_destroy(self.h)

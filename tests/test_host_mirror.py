@@ -20,7 +20,7 @@ def build_exe():
     src = os.path.join(ROOT, "tests", "cpp", "host_mirror_test.cpp")
     lib_dir = os.path.join(ROOT, "omega_b200", "csrc")
     cmd = ["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "omega_b200", "host"),
-           "-I/usr/local/cuda/include", src, "-o", EXE, "-L" + lib_dir, "-lomega_b200", "-L/usr/local/cuda/lib64", "-lcudart",
+           "-I/usr/local/cuda/include", src, "-o", EXE, "-L" + lib_dir, "-lomega_b200", "-L/usr/local/cuda/lib64", "-lcudart", "-lcublas",
            "-Wl,-rpath," + lib_dir, "-Wl,-rpath,/usr/local/cuda/lib64"]
     subprocess.run(cmd, check=True)
 
@@ -100,8 +100,10 @@ def test_host_mirror_two_ranks_step_without_python_transport(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("stepper,fused", [(capi.RK4, 1), (capi.RK4, 0), (capi.FB, 0)])
-def test_host_mirror_matches_oracle(tmp_path, stepper, fused):
+@pytest.mark.parametrize("stepper,fused,custom", [(capi.RK4, 1, 0), (capi.RK4, 0, 0), (capi.FB, 0, 0), (capi.RK4, 1, 1)])
+def test_host_mirror_matches_oracle(tmp_path, stepper, fused, custom):
+    """custom = 1: a std::function custom velocity tendency installed on the Tendencies mirror as the reference's
+    TimeStepperTest installs its own (Tendencies.h:51-53), on top of every built-in term"""
     if not os.path.exists(EXE):
         build_exe()
     L, cfg, (h, u, tr), dt = cases.sphere_case(3, 6, 2)
@@ -115,12 +117,16 @@ def test_host_mirror_matches_oracle(tmp_path, stepper, fused):
     with open(os.path.join(d, "meta.txt"), "w") as f:
         for name, _ in capi.MeshDesc._fields_[:13]:
             f.write(f"{name} {int(L[name])}\n")
-        f.write(f"NTracers {T}\nNSteps {nsteps}\nDt {dt}\nStepper {stepper}\nFused {fused}\n")
+        f.write(f"NTracers {T}\nNSteps {nsteps}\nDt {dt}\nStepper {stepper}\nFused {fused}\nCustom {custom}\n")
     with open(os.path.join(d, "cfg.bin"), "wb") as f:
         f.write(bytes(cfg))
     h.tofile(os.path.join(d, "h.bin")); u.tofile(os.path.join(d, "u.bin")); tr.tofile(os.path.join(d, "tr.bin"))
     subprocess.run([EXE, d], check=True)
     o = Oracle(L, cfg, T)
+    if custom:
+        def decay(tend, hh, uu, time):
+            tend -= 0.5 * uu
+        o.set_custom_tendencies(None, decay)
     o.tend_all(h, u, tr)
     for nm, key in (("out_htend", "LayerThicknessTend"), ("out_utend", "NormalVelocityTend"), ("out_trtend", "TracerTend")):
         got = np.fromfile(os.path.join(d, nm + ".bin")).reshape(o.tend[key].shape)
