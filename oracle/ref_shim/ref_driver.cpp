@@ -139,6 +139,17 @@ Array3DReal wrap_tracers(RefStepper *R, const double *Tr) {
 
 extern "C" {
 
+// The reference's time arithmetic on a stage coefficient: Mult * TimeStep as the steppers form it
+// (RungeKutta4Stepper.cpp:96-118: RKA[Stage] * TimeStep), evaluated in seconds (TimeMgr.cpp:382-391)
+int ref_time_coeff(double Dt, double Mult, double *Out) {
+   TimeInterval TimeStep(Dt, TimeUnits::Seconds);
+   TimeInterval Coeff = Mult * TimeStep;
+   R8 Seconds;
+   Coeff.get(Seconds, TimeUnits::Seconds);
+   *Out = Seconds;
+   return 0;
+}
+
 // Multi-task tests: Fn is called at every halo exchange the reference's steppers perform (see ref_shim.h)
 int ref_set_halo_callback(void (*Fn)(void *, int, int, int)) {
    Halo::callback() = Fn;
