@@ -16,13 +16,15 @@ class AuxiliaryState {
        RelVortVertex, NormRelVortVertex, NormPlanetVortVertex, NormRelVortEdge, NormPlanetVortEdge,
        Del2Edge, Del2DivCell, Del2RelVortVertex;
    Array3DReal HTracersEdge, Del2TracersCell;
+   Array1DReal ZonalStressCell, MeridStressCell, NormalStressEdge; ///< WindForcingAuxVars.h:16-20
    OmegaStepper *Handle = nullptr;
    const HorzMesh *Mesh;
+   Halo *MeshHalo;
    I4 NTracers;
 
-   AuxiliaryState(const std::string &Name, const HorzMesh *M, Halo *, int NVertLayers, int NTracers_,
+   AuxiliaryState(const std::string &Name, const HorzMesh *M, Halo *H, int NVertLayers, int NTracers_,
                   const OmegaTendConfig &Cfg)
-       : Mesh(M), NTracers(NTracers_) {
+       : Mesh(M), MeshHalo(H), NTracers(NTracers_) {
       OMEGA_B200_CHECK(omega_stepper_create(M->Handle, &Cfg, NTracers, &Handle), "AuxiliaryState: omega_stepper_create");
       OmegaAuxArrays A;
       OMEGA_B200_CHECK(omega_stepper_aux_arrays(Handle, &A), "omega_stepper_aux_arrays");
@@ -36,6 +38,20 @@ class AuxiliaryState {
 #undef OMEGA_ALIAS2
       HTracersEdge    = Array3DReal("HTracersEdge" + Name, A.HTracersEdge, {T, E, K});
       Del2TracersCell = Array3DReal("Del2TracersCell" + Name, A.Del2TracersCell, {T, C, K});
+      ZonalStressCell  = Array1DReal("ZonalStressCell" + Name, A.ZonalStressCell, {C});
+      MeridStressCell  = Array1DReal("MeridStressCell" + Name, A.MeridStressCell, {C});
+      NormalStressEdge = Array1DReal("NormalStressEdge" + Name, A.NormalStressEdge, {E});
+   }
+   /// the two forcing arrays a host reads from its forcing file (host order, [NCellsSize])
+   void setWindStress(const double *ZonalHost, const double *MeridHost, void *Stream = nullptr) {
+      OMEGA_B200_CHECK(omega_stepper_set_wind_stress(Handle, ZonalHost, MeridHost, Stream), "AuxiliaryState::setWindStress");
+   }
+   /// src/ocn/AuxiliaryState.cpp:313-323: only the variables that are not computed need an exchange
+   I4 exchangeHalo(void *Stream = nullptr) {
+      if (!MeshHalo) return 0;
+      I4 Err = MeshHalo->exchangeFullArrayHalo(ZonalStressCell.data(), OnCell, 1, 1, Stream);
+      Err += MeshHalo->exchangeFullArrayHalo(MeridStressCell.data(), OnCell, 1, 1, Stream);
+      return Err;
    }
    ~AuxiliaryState() { omega_stepper_destroy(Handle); }
    AuxiliaryState(const AuxiliaryState &) = delete;

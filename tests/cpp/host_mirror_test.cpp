@@ -109,7 +109,14 @@ int main(int argc, char **argv) {
    }
    OceanState State("Default", &Mesh, MeshHalo.get(), K, 2);
    Tracers Trc(&Mesh, MeshHalo.get(), T, K, 2);
-   AuxiliaryState Aux("Default", &Mesh, nullptr, K, T, Cfg);
+   AuxiliaryState Aux("Default", &Mesh, MeshHalo.get(), K, T, Cfg);
+   // "Wind 1": the forcing arrays as a host reads them (owned cells and, here, the halo too), then the exchange the
+   // reference's init does for them (OceanInit.cpp:188, AuxiliaryState.cpp:313-323)
+   if (Meta["Wind"] != 0) {
+      auto Zonal = load<double>("zonal"), Merid = load<double>("merid");
+      Aux.setWindStress(Zonal.data(), Merid.data());
+      if (Aux.exchangeHalo() != 0) { std::fprintf(stderr, "AuxiliaryState::exchangeHalo failed\n"); return 6; }
+   }
    Tendencies Tend("Default", &Mesh, &Aux, K);
    // "Custom 1": the custom velocity tendency of the reference's TimeStepperTest (du/dt -= 0.5 u,
    // test/timeStepping/TimeStepperTest.cpp:49-72) installed the way that test does, as a std::function; the device

@@ -100,13 +100,18 @@ def test_host_mirror_two_ranks_step_without_python_transport(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("stepper,fused,custom", [(capi.RK4, 1, 0), (capi.RK4, 0, 0), (capi.FB, 0, 0), (capi.RK4, 1, 1)])
-def test_host_mirror_matches_oracle(tmp_path, stepper, fused, custom):
+@pytest.mark.parametrize("stepper,fused,custom,wind", [(capi.RK4, 1, 0, 0), (capi.RK4, 0, 0, 0), (capi.FB, 0, 0, 0), (capi.RK4, 1, 1, 0),
+                                                       (capi.RK4, 1, 0, 1)])
+def test_host_mirror_matches_oracle(tmp_path, stepper, fused, custom, wind):
     """custom = 1: a std::function custom velocity tendency installed on the Tendencies mirror as the reference's
-    TimeStepperTest installs its own (Tendencies.h:51-53), on top of every built-in term"""
-    if not os.path.exists(EXE):
-        build_exe()
-    L, cfg, (h, u, tr), dt = cases.sphere_case(3, 6, 2)
+    TimeStepperTest installs its own (Tendencies.h:51-53), on top of every built-in term.  wind = 1: wind forcing,
+    bottom drag and upwind fluxes on, the stress arrays through AuxiliaryState::setWindStress / exchangeHalo"""
+    build_exe()
+    if wind:
+        L, cfg, (h, u, tr), dt, (zonal, merid) = cases.all_terms_case(3, 6, 2)
+        zonal.tofile(os.path.join(str(tmp_path), "zonal.bin")); merid.tofile(os.path.join(str(tmp_path), "merid.bin"))
+    else:
+        L, cfg, (h, u, tr), dt = cases.sphere_case(3, 6, 2)
     T, nsteps = tr.shape[0], 3
     desc, keep = capi.make_mesh_desc(L)
     d = str(tmp_path)
@@ -117,12 +122,14 @@ def test_host_mirror_matches_oracle(tmp_path, stepper, fused, custom):
     with open(os.path.join(d, "meta.txt"), "w") as f:
         for name, _ in capi.MeshDesc._fields_[:13]:
             f.write(f"{name} {int(L[name])}\n")
-        f.write(f"NTracers {T}\nNSteps {nsteps}\nDt {dt}\nStepper {stepper}\nFused {fused}\nCustom {custom}\n")
+        f.write(f"NTracers {T}\nNSteps {nsteps}\nDt {dt}\nStepper {stepper}\nFused {fused}\nCustom {custom}\nWind {wind}\n")
     with open(os.path.join(d, "cfg.bin"), "wb") as f:
         f.write(bytes(cfg))
     h.tofile(os.path.join(d, "h.bin")); u.tofile(os.path.join(d, "u.bin")); tr.tofile(os.path.join(d, "tr.bin"))
     subprocess.run([EXE, d], check=True)
     o = Oracle(L, cfg, T)
+    if wind:
+        o.set_wind_stress(zonal, merid)
     if custom:
         def decay(tend, hh, uu, time):
             tend -= 0.5 * uu
