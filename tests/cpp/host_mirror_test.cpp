@@ -118,16 +118,16 @@ int main(int argc, char **argv) {
       if (Aux.exchangeHalo() != 0) { std::fprintf(stderr, "AuxiliaryState::exchangeHalo failed\n"); return 6; }
    }
    Tendencies Tend("Default", &Mesh, &Aux, K);
-   // "Custom 1": the custom velocity tendency of the reference's TimeStepperTest (du/dt -= 0.5 u,
-   // test/timeStepping/TimeStepperTest.cpp:49-72) installed the way that test does, as a std::function; the device
-   // work is one cuBLAS axpy on the stream the library hands over
+   // "Custom 1": the custom velocity tendency of the reference's TimeStepperTest (du/dt -= Coeff u,
+   // test/timeStepping/TimeStepperTest.cpp:49-72; Coeff = 1e-5 / s here, the steps are minutes long) installed the
+   // way that test does, as a std::function; the device work is one cuBLAS axpy on the stream the library hands over
    cublasHandle_t Blas = nullptr;
    if (Meta["Custom"] != 0) {
       if (cublasCreate(&Blas) != CUBLAS_STATUS_SUCCESS) { std::fprintf(stderr, "cublasCreate failed\n"); return 5; }
       Tend.setCustomTendencies(nullptr, [&](Array2DReal VelTend, const OceanState *Stage, const AuxiliaryState *, int, int VelLevel, double) {
          Array2DReal U;
          Stage->getNormalVelocity(U, VelLevel);
-         const double Alpha = -0.5;
+         const double Alpha = -1.0e-5;
          cublasSetStream(Blas, static_cast<cudaStream_t>(Tend.customStream()));
          if (cublasDaxpy(Blas, (int)VelTend.size(), &Alpha, U.data(), 1, VelTend.data(), 1) != CUBLAS_STATUS_SUCCESS) std::abort();
       });
