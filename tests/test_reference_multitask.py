@@ -23,15 +23,15 @@ K, T, NSTEPS, LEVEL = 3, 2, 3, 3
 NO_DEL4 = dict(VelHyperDiffTendencyEnable=0, TracerHyperDiffTendencyEnable=0)
 
 
-def _task(rank, world, port, q, stepper, halo_width, cfgkw):
+def _task(rank, world, port, q, stepper, halo_width, cfgkw, land=False):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        m = cases.sphere_mesh(LEVEL)
+        m = cases.land_mesh(LEVEL) if land else cases.sphere_mesh(LEVEL)
         L, lists = parallel.local_problem(m, world, rank, K, halo_width=halo_width)
-        _, cfg, _, dt = cases.sphere_case(LEVEL, K, T, **cfgkw)
+        _, cfg, _, dt = (cases.land_case if land else cases.sphere_case)(LEVEL, K, T, **cfgkw)
         ex = parallel.HostHaloExchanger(lists)
         o = Oracle(L, cfg, T, lib_path=REF)
         calls = []
@@ -61,12 +61,12 @@ def _task(rank, world, port, q, stepper, halo_width, cfgkw):
     dist.destroy_process_group()
 
 
-def _run_tasks(world, stepper, halo_width, cfgkw):
+def _run_tasks(world, stepper, halo_width, cfgkw, land=False):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 31000 + (os.getpid() * 7 + world + 13 * halo_width + 3 * stepper) % 2000
-    procs = [ctx.Process(target=_task, args=(r, world, port, q, stepper, halo_width, cfgkw)) for r in range(world)]
+    procs = [ctx.Process(target=_task, args=(r, world, port, q, stepper, halo_width, cfgkw, land)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=300) for _ in procs]
@@ -77,8 +77,8 @@ def _run_tasks(world, stepper, halo_width, cfgkw):
     return sorted(res, key=lambda r: r[0])
 
 
-def _one_task_reference(stepper, cfgkw):
-    L1, cfg, (h, u, tr), dt = cases.sphere_case(LEVEL, K, T, **cfgkw)
+def _one_task_reference(stepper, cfgkw, land=False):
+    L1, cfg, (h, u, tr), dt = (cases.land_case if land else cases.sphere_case)(LEVEL, K, T, **cfgkw)
     ref = Oracle(L1, cfg, T, lib_path=REF)
     ref.make_state(h, u, tr)
     for s in range(NSTEPS):
@@ -92,12 +92,12 @@ def _one_task_reference(stepper, cfgkw):
     return H, U, TR
 
 
-def _partition_error(world, stepper, halo_width, cfgkw):
+def _partition_error(world, stepper, halo_width, cfgkw, land=False):
     build_oracle()
     if not os.path.exists(REF):
         pytest.skip("oracle/_ref was not built (the reference sources are not on this machine)")
-    H, U, TR = _one_task_reference(stepper, cfgkw)
-    res = _run_tasks(world, stepper, halo_width, cfgkw)
+    H, U, TR = _one_task_reference(stepper, cfgkw, land)
+    res = _run_tasks(world, stepper, halo_width, cfgkw, land)
     worst = 0.0
     for rank, ci, ei, h, u, tr, per_step in res:
         for a, b in ((h, H[ci]), (u, U[ei]), (tr, TR[:, ci])):
@@ -110,6 +110,12 @@ def _partition_error(world, stepper, halo_width, cfgkw):
 def test_reference_tasks_equal_one_task_bit_for_bit(world, stepper, halo_width, cfgkw):
     """every local element (owned and halo) of every task equals the 1-task run of the same reference code"""
     worst, _ = _partition_error(world, stepper, halo_width, cfgkw)
+    assert worst == 0.0
+
+
+def test_reference_tasks_with_a_coastline_equal_one_task_bit_for_bit():
+    """the same on the mesh with land (cases.land_mesh): three partitions that cut the coast, the reference's own code"""
+    worst, _ = _partition_error(3, capi.RK4, 4, {}, land=True)
     assert worst == 0.0
 
 
