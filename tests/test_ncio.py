@@ -165,3 +165,25 @@ def test_restart_from_device_state_resumes_bit_identically(tmp_path):
     for x, y in zip(c.copyToHost(0), want):
         assert np.array_equal(x, y)
     st.close(); mesh.close()
+
+
+@pytest.mark.parametrize("kind", ["land", "hept"])
+def test_mesh_files_with_coastlines_and_heptagons(tmp_path, kind):
+    """the reference's mesh file schema for the meshes with holes in their connectivity: missing neighbours are 0 in
+    the file (1-based IDs), the rows of edgesOnEdge hold nEdgesOnEdge valid entries first; read back (scipy and the
+    library-free reader) and decomposed, the local meshes equal those of the mesh in memory"""
+    m = cases.land_mesh(3) if kind == "land" else cases.hept_mesh(3)
+    p = str(tmp_path / "mesh.nc")
+    meshgen.write_netcdf(m, p)
+    r = ncio.CDFReader(p)
+    assert r.dim("maxEdges") == m.maxEdges and r.dim("maxEdges2") == m.maxEdges2
+    coe = r.read("cellsOnEdge")
+    assert coe.min() == (0 if kind == "land" else 1) and np.array_equal(coe, m.cellsOnEdge + 1)
+    assert np.array_equal(r.read("nEdgesOnEdge"), m.nEdgesOnEdge)
+    back, _ = meshgen.read_netcdf(p)
+    for k in ("cellsOnCell", "edgesOnCell", "verticesOnCell", "cellsOnEdge", "verticesOnEdge", "edgesOnEdge", "cellsOnVertex",
+              "edgesOnVertex", "nEdgesOnCell", "nEdgesOnEdge", "weightsOnEdge", "kiteAreasOnVertex", "angleEdge", "bottomDepth"):
+        assert np.array_equal(back[k], m[k]), k
+    a, b = decomp.build_all(m, 3, 2)[1], decomp.build_all(back, 3, 2)[1]
+    for k in ("CellID", "EdgeID", "VertexID", "CellsOnEdge", "EdgesOnEdge", "CellsOnVertex", "WeightsOnEdge", "AreaCell"):
+        assert np.array_equal(a[k], b[k]), k
