@@ -15,6 +15,8 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <type_traits>
+#include <utility>
 #include <vector>
 
 #include "omega_b200.h"
@@ -35,6 +37,57 @@ static_assert(sizeof(Real) == sizeof(double), "this mirror header is written for
    do { if ((call) != 0) ::OMEGA::abortError(what); } while (0)
 
 enum MeshElement { OnCell = OMEGA_ON_CELL, OnEdge = OMEGA_ON_EDGE, OnVertex = OMEGA_ON_VERTEX };
+
+/// The ownership convention of the reference's classes (e.g. src/ocn/OceanState.cpp:30-62,369-407,
+/// src/ocn/Tendencies.cpp:75-121, src/ocn/HorzMesh.cpp:29-47,651-690): objects are made by a static create(Name, ...)
+/// that refuses a name in use, live in a static map, are found again with get(Name) / getDefault() (the one
+/// called "Default") and end with erase(Name) / clear().  T::create(Name, args...) builds T(Name, args...) where T
+/// has such a constructor, T(args...) otherwise.  Plain construction stays possible (the tests use both).
+template <class T> class Registry {
+ public:
+   template <class... A> static T *create(const std::string &Name, A &&...Args) {
+      if (all().count(Name)) {
+         std::fprintf(stderr, "[omega_b200] Attempted to create an object with name %s but it already exists\n", Name.c_str());
+         return nullptr;
+      }
+      T *Obj;
+      if constexpr (std::is_constructible_v<T, const std::string &, A...>) Obj = new T(Name, std::forward<A>(Args)...);
+      else Obj = new T(std::forward<A>(Args)...);
+      all()[Name].reset(Obj);
+      if (Name == "Default") defaultPtr() = Obj;
+      return Obj;
+   }
+   static T *getDefault() { return defaultPtr(); }
+   static T *get(const std::string &Name) {
+      auto It = all().find(Name);
+      if (It == all().end()) {
+         std::fprintf(stderr, "[omega_b200] Attempt to retrieve non-existent object: %s\n", Name.c_str());
+         return nullptr;
+      }
+      return It->second.get();
+   }
+   static void erase(const std::string &Name) {
+      auto It = all().find(Name);
+      if (It == all().end()) return;
+      if (It->second.get() == defaultPtr()) defaultPtr() = nullptr;
+      all().erase(It);
+   }
+   /// objects go in reverse order of creation is NOT promised: erase dependants first, as upstream's finalize does
+   static void clear() {
+      all().clear();
+      defaultPtr() = nullptr;
+   }
+
+ private:
+   static std::map<std::string, std::unique_ptr<T>> &all() {
+      static std::map<std::string, std::unique_ptr<T>> M;
+      return M;
+   }
+   static T *&defaultPtr() {
+      static T *D = nullptr;
+      return D;
+   }
+};
 
 /// Device array handle: ref-counted, zero-initialised (like Kokkos::View)
 template <int Rank> class DeviceArray {
@@ -72,7 +125,7 @@ using Array2DReal = DeviceArray<2>;
 using Array3DReal = DeviceArray<3>;
 
 /// HorzMesh: device-resident mesh built from host-order arrays
-class HorzMesh {
+class HorzMesh : public Registry<HorzMesh> {
  public:
    I4 NCellsOwned, NCellsAll, NCellsSize, NEdgesOwned, NEdgesAll, NEdgesSize;
    I4 NVerticesOwned, NVerticesAll, NVerticesSize, MaxEdges, MaxEdges2, VertexDegree, NVertLayers;
@@ -101,7 +154,7 @@ class HorzMesh {
 /// NCCL send/recv with every neighbour, unpack kernel, all inside the library.  The host only
 /// bootstraps the communicator: one rank calls uniqueId(), the 128 bytes travel by the host's own
 /// means (MPI_Bcast over MachEnv's communicator in Omega) and every rank calls initComm().
-class Halo {
+class Halo : public Registry<Halo> {
  public:
    OmegaHalo *Handle = nullptr;
    const HorzMesh *Mesh;
@@ -137,7 +190,7 @@ class Halo {
 };
 
 /// OceanState: h and u time-level rings (src/ocn/OceanState.cpp:65-117,333-407)
-class OceanState {
+class OceanState : public Registry<OceanState> {
  public:
    std::vector<Array2DReal> LayerThickness, NormalVelocity;
    I4 NTimeLevels, NVertLayers, CurTimeIndex = 0;

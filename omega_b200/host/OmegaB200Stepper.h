@@ -9,7 +9,7 @@
 
 namespace OMEGA {
 
-class AuxiliaryState {
+class AuxiliaryState : public Registry<AuxiliaryState> {
  public:
    // the public arrays of the six aux-var groups, flattened
    Array2DReal KineticEnergyCell, VelocityDivCell, FluxLayerThickEdge, MeanLayerThickEdge, SshCell,
@@ -76,7 +76,7 @@ class AuxiliaryState {
    }
 };
 
-class Tendencies {
+class Tendencies : public Registry<Tendencies> {
  public:
    /// src/ocn/Tendencies.h:51-53: a host term called after the built-in terms of a thickness / velocity tendency
    /// evaluation; it adds into the tendency array (first argument).  Here the arrays are device arrays in device
@@ -173,7 +173,7 @@ enum class TimeStepperType { ForwardBackward, RungeKutta4, RungeKutta2, Invalid 
 /// TimeStepper::doStep (src/timeStepping/TimeStepper.h:82-84).  SimTime is
 /// elapsed seconds; Coeffs are the stage coefficients in seconds as
 /// TimeInterval::get evaluates them (src/infra/TimeMgr.cpp:382-391).
-class TimeStepper {
+class TimeStepper : public Registry<TimeStepper> {
  public:
    TimeStepperType Type;
    OmegaStepCoeffs Coeffs;

@@ -57,3 +57,17 @@ def test_rk_coeffs_equal_the_reference_time_arithmetic(dt):
     assert [rk4.A[s] for s in range(4)] == [ref(0.0), ref(0.5), ref(0.5), ref(1.0)]
     assert [rk4.B[s] for s in range(4)] == [ref(1.0 / 6), ref(1.0 / 3), ref(1.0 / 3), ref(1.0 / 6)]
     assert rk2.A[1] == ref(0.5) and rk2.B[1] == ref(1.0)
+
+
+def test_mirror_classes_follow_the_ownership_convention():
+    """create / get / getDefault / erase / clear of the reference's classes (Ownership) on the mirror:
+    tests/cpp/registry_test.cpp, host code only"""
+    if not os.path.exists(capi.LIB_PATH):
+        pytest.skip("libomega_b200.so not built")
+    lib_dir = os.path.join(ROOT, "omega_b200", "csrc")
+    exe = os.path.join(ROOT, "tests", "cpp", "registry_test")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "omega_b200", "host"),
+                    os.path.join(ROOT, "tests", "cpp", "registry_test.cpp"), "-o", exe, "-L" + lib_dir, "-lomega_b200",
+                    "-L/usr/local/cuda/lib64", "-lcudart", "-Wl,-rpath," + lib_dir, "-Wl,-rpath,/usr/local/cuda/lib64"], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and "registry ok" in r.stdout, r.stderr
