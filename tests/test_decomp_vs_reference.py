@@ -68,7 +68,9 @@ def run_reference(lib, m, ntasks, hw, task):
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
                                             ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3),
-                                            ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3)])
+                                            ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3),
+                                            # small partitions: halos that reach beyond the neighbours' neighbours
+                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2)])
 def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
     lib = ref_lib()
     m = _mesh(kind)
@@ -91,7 +93,8 @@ def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
 
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
-                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3)])
+                                            ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3),
+                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2)])
 def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
     """src/base/Halo.cpp (constructor: neighbours, send / receive lists per index space and halo layer), compiled
     unmodified and run on the reference Decomp of every thread-task over a thread MPI (oracle/ref_decomp/mpi.h:
@@ -139,7 +142,7 @@ def _ref_exchange(lib, locs, kind_idx, nouter, ninner, arrays):
     assert lib.ref_halo_exchange(kind_idx, nouter, ninner, ptrs) == 0
 
 
-@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2), ("land3", 3, 3)])
+@pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 3, 3), ("sphere4", 5, 4), ("plane", 4, 2), ("land3", 3, 3), ("sphere2", 8, 3)])
 def test_reference_exchange_and_message_layout(kind, ntasks, hw):
     """Halo::exchangeFullArrayHalo of the reference itself (Halo.h:768-915) on the thread-tasks: (1) its own HaloTest
     (test/base/HaloTest.cpp:41-99) passes on them -- arrays holding f(global ID) in the owned entries equal the fully
