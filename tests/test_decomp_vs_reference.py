@@ -70,7 +70,9 @@ def run_reference(lib, m, ntasks, hw, task):
                                             ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("sphere3", 1, 3),
                                             ("land3", 1, 3), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3),
                                             # small partitions: halos that reach beyond the neighbours' neighbours
-                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2)])
+                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2),
+                                            # periodic plane: halos that wrap around and meet themselves
+                                            ("plane", 2, 5), ("plane", 3, 4)])
 def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
     lib = ref_lib()
     m = _mesh(kind)
@@ -94,7 +96,7 @@ def test_local_numbering_equals_the_reference_decomp(kind, ntasks, hw):
 
 @pytest.mark.parametrize("kind,ntasks,hw", [("sphere3", 2, 3), ("sphere3", 3, 3), ("sphere4", 5, 4), ("sphere4", 8, 3),
                                             ("sphere3", 4, 1), ("plane", 4, 3), ("plane", 6, 2), ("land3", 3, 3), ("land4", 4, 4), ("hept3", 3, 3),
-                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2)])
+                                            ("sphere2", 8, 3), ("sphere3", 16, 3), ("sphere3", 24, 5), ("land3", 7, 2), ("plane", 2, 5), ("plane", 3, 4)])
 def test_halo_exchange_lists_equal_the_reference_halo(kind, ntasks, hw):
     """src/base/Halo.cpp (constructor: neighbours, send / receive lists per index space and halo layer), compiled
     unmodified and run on the reference Decomp of every thread-task over a thread MPI (oracle/ref_decomp/mpi.h:
