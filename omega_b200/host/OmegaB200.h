@@ -108,6 +108,18 @@ template <int Rank> class DeviceArray {
       for (long e : Ext) { Ext_[i++] = e; Size_ *= e; }
       Data_ = std::shared_ptr<double>(Ptr, [](double *) {});
    }
+   /// [i][...] of this array as an array of one rank less that SHARES the allocation: the role of
+   /// Kokkos::subview(A, i, ALL, ALL) in Tracers::getByIndex (src/ocn/Tracers.cpp:292-293)
+   DeviceArray<Rank - 1> slice(long i, const std::string &Label = "") const {
+      static_assert(Rank >= 2, "slice needs a leading dimension");
+      DeviceArray<Rank - 1> Out;
+      long Inner = 1;
+      for (int d = 1; d < Rank; ++d) { Out.Ext_[d - 1] = Ext_[d]; Inner *= Ext_[d]; }
+      Out.Size_  = Inner;
+      Out.Label_ = Label.empty() ? Label_ : Label;
+      Out.Data_  = std::shared_ptr<double>(Data_, Data_.get() + i * Inner); // aliasing constructor: same owner
+      return Out;
+   }
    double *data() const { return Data_.get(); }
    long extent(int i) const { return Ext_[i]; }
    int extent_int(int i) const { return (int)Ext_[i]; }
@@ -115,6 +127,7 @@ template <int Rank> class DeviceArray {
    const std::string &label() const { return Label_; }
 
  private:
+   template <int R2> friend class DeviceArray;
    std::string Label_;
    std::shared_ptr<double> Data_;
    long Ext_[Rank > 0 ? Rank : 1] = {0};
@@ -251,6 +264,41 @@ class OceanState : public Registry<OceanState> {
    }
 };
 
+/// Tracer names and indices (src/ocn/Tracers.cpp:135-190: define; :244-263: getIndex / getName).  The reference
+/// fills them from the Tracers: group of the configuration (Base: [Temperature, Salinity], ...); here the host hands
+/// the names over, in index order.
+class TracerNames {
+ public:
+   static constexpr I4 IndxInvalid = -1; // Tracers.h:43
+   void define(const std::vector<std::string> &InNames) {
+      Names = InNames;
+      Indexes.clear();
+      for (I4 i = 0; i < (I4)Names.size(); ++i) Indexes[Names[i]] = i;
+   }
+   I4 getIndex(I4 &TracerIndex, const std::string &TracerName) const {
+      auto It = Indexes.find(TracerName);
+      if (It == Indexes.end()) {
+         std::fprintf(stderr, "[omega_b200] Tracers: Tracer index for '%s' is not found.\n", TracerName.c_str());
+         return -1;
+      }
+      TracerIndex = It->second;
+      return 0;
+   }
+   I4 getName(std::string &TracerName, I4 TracerIndex) const {
+      if (TracerIndex < 0 || TracerIndex >= (I4)Names.size()) {
+         std::fprintf(stderr, "[omega_b200] Tracers: Tracer name for index '%d' is not found.\n", TracerIndex);
+         return -1;
+      }
+      TracerName = Names[TracerIndex];
+      return 0;
+   }
+   I4 size() const { return (I4)Names.size(); }
+
+ private:
+   std::vector<std::string> Names;
+   std::map<std::string, I4> Indexes;
+};
+
 /// Tracers: [NTracers][NCellsSize][NVertLayers] per time level (src/ocn/Tracers.cpp:269-277,457-525).
 /// An instance instead of the reference's static class; NTracers is a plain integer.
 class Tracers {
@@ -258,12 +306,33 @@ class Tracers {
    std::vector<Array3DReal> TracerArrays;
    I4 NTracers, NTimeLevels, CurTimeIndex = 0;
    Halo *MeshHalo;
-   Tracers(const HorzMesh *M, Halo *H, int NTracers_, int NVertLayers, int NTimeLevels_)
+   TracerNames Names;
+   /// InNames: one name per tracer in index order; left out, the tracers are called Tracer0, Tracer1, ...
+   Tracers(const HorzMesh *M, Halo *H, int NTracers_, int NVertLayers, int NTimeLevels_, std::vector<std::string> InNames = {})
        : NTracers(NTracers_), NTimeLevels(NTimeLevels_), MeshHalo(H) {
+      if (InNames.empty())
+         for (int i = 0; i < NTracers; ++i) InNames.push_back("Tracer" + std::to_string(i));
+      if ((int)InNames.size() != NTracers) abortError("Tracers: one name per tracer");
+      Names.define(InNames);
       for (int i = 0; i < NTimeLevels; ++i)
          TracerArrays.emplace_back("Tracers" + std::to_string(i), std::initializer_list<long>{NTracers, M->NCellsSize, NVertLayers});
    }
    I4 getNumTracers() const { return NTracers; }
+   I4 getIndex(I4 &TracerIndex, const std::string &TracerName) const { return Names.getIndex(TracerIndex, TracerName); }
+   I4 getName(std::string &TracerName, I4 TracerIndex) const { return Names.getName(TracerName, TracerIndex); }
+   /// Tracers.cpp:279-295: one tracer of a time level, sharing the allocation
+   I4 getByIndex(Array2DReal &Out, I4 TimeLevel, I4 TracerIndex) const {
+      if (TracerIndex < 0 || TracerIndex >= NTracers) return -2;
+      I4 i; I4 Err = getTimeIndex(i, TimeLevel);
+      if (!Err) Out = TracerArrays[i].slice(TracerIndex);
+      return Err;
+   }
+   /// Tracers.cpp:297-310
+   I4 getByName(Array2DReal &Out, I4 TimeLevel, const std::string &TracerName) const {
+      I4 Idx;
+      if (Names.getIndex(Idx, TracerName)) return -1;
+      return getByIndex(Out, TimeLevel, Idx) ? -2 : 0;
+   }
    I4 getTimeIndex(I4 &TimeIndex, I4 TimeLevel) const {
       if (NTimeLevels > 1 && (TimeLevel > 1 || (TimeLevel + NTimeLevels) <= 1)) return -1;
       TimeIndex = (TimeLevel + CurTimeIndex + NTimeLevels) % NTimeLevels;

@@ -3,6 +3,7 @@
 // every mirror class carries it.  Host code only.
 #include <cstdio>
 #include <string>
+#include <vector>
 
 #include "OmegaB200.h"
 
@@ -48,6 +49,22 @@ int main() {
    Plain *P = Plain::create("Default", 7);
    REQUIRE(P && P->Value == 7 && Plain::getDefault() == P);
    Plain::clear();
+   // DeviceArray::slice (the subview of Tracers::getByIndex) over memory the test owns, and the tracer names
+   {
+      std::vector<double> Buf(2 * 3 * 4);
+      for (size_t i = 0; i < Buf.size(); ++i) Buf[i] = (double)i;
+      Array3DReal A("tracers", Buf.data(), {2, 3, 4});
+      Array2DReal S1 = A.slice(1);
+      REQUIRE(S1.data() == Buf.data() + 12 && S1.extent(0) == 3 && S1.extent(1) == 4 && S1.size() == 12 && S1.label() == "tracers");
+      Array1DReal Row = S1.slice(2, "row");
+      REQUIRE(Row.data() == Buf.data() + 12 + 8 && Row.extent(0) == 4 && Row.data()[3] == 23.0 && Row.label() == "row");
+      TracerNames N;
+      N.define({"Temperature", "Salinity", "Debug1"});
+      I4 Idx = TracerNames::IndxInvalid;
+      std::string Name;
+      REQUIRE(N.getIndex(Idx, "Salinity") == 0 && Idx == 1 && N.getName(Name, 2) == 0 && Name == "Debug1" && N.size() == 3);
+      REQUIRE(N.getIndex(Idx, "Oxygen") == -1 && Idx == 1 && N.getName(Name, 3) == -1 && N.getName(Name, -1) == -1);
+   }
    std::printf("registry ok\n");
    return 0;
 }
